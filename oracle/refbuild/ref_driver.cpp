@@ -1,0 +1,599 @@
+// ref_driver.cpp -- TEST INFRASTRUCTURE ONLY (oracle/README.md).
+//
+// Links against objects compiled from the UNMODIFIED-ARITHMETIC reference
+// sources (see build_ref.sh / patch_ref.py) and drives the reference's own
+// pbrt*() API directly, because the reference's scene parser needs flex, which
+// is not in this image.  It runs the reference's own
+// MultipoleSubsurfaceIntegrator / BVHAccel / LayeredSkin / MPC_* code and dumps
+// the intermediate streams that pin parity for the B200 path:
+//   surface points, irradiance points, flat BVH, profile + rho tables,
+//   camera rays, closest hits, per-hit Mo, per-sample radiance, PFM image.
+// Nothing here is product code; nothing in the product path calls it.
+//
+// The translation unit textually includes the reference's core/api.cpp so that
+// the file-static RenderOptions (MakeScene / MakeRenderer) is reachable.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <limits>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <sstream>
+#include <string>
+#include <typeinfo>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+// Open up the reference classes: the dumps need private members.
+#define private public
+#define protected public
+#include "core/api.cpp"
+#include "integrators/diffusionutil.h"
+#include "materials/layeredskin.h"
+#include "materials/skincoeffs.h"
+#include "accelerators/bvh.h"
+#include "renderers/samplerrenderer.h"
+#include "renderers/surfacepoints.h"
+#include "shapes/trianglemesh.h"
+#include "shapes/sphere.h"
+#include "lights/diffuse.h"
+#include "core/multipole.h"
+#include "core/reflection.h"
+#include "core/film.h"
+#include "film/image.h"
+#include "core/sampler.h"
+#include "core/camera.h"
+#include "core/parallel.h"
+#include "core/rng.h"
+#include "multipole/MultipoleProfileCalculator/MultipoleProfileCalculator.h"
+#undef private
+#undef protected
+
+// parser.cpp is not linked (needs flex/bison output); api.cpp only needs these.
+string current_file;
+int line_num = 0;
+bool ParseFile(const string &) { Severe("ref_driver: parser not available"); return false; }
+
+// Mirrors of the file-local structs in core/multipole.cpp:40-56,95-101 (layout only).
+struct DrvProfileEntry { float reflectance; };
+struct DrvProfile {
+    std::vector<DrvProfileEntry> data;
+    float dsqSpacing, rcpDsqSpacing, totalReflectance, totalTransmittance;
+};
+struct DrvProfileData { DrvProfile spectralProfile[nSpectralSamples]; bool isRGBProfile; };
+
+// Mirror of the file-local LinearBVHNode in accelerators/bvh.cpp:113-123.
+struct DrvLinearBVHNode {
+    BBox bounds;
+    union { uint32_t primitivesOffset; uint32_t secondChildOffset; };
+    uint8_t nPrimitives, axis, pad[2];
+};
+
+static double now_s() {
+    using namespace std::chrono;
+    return duration_cast<duration<double>>(steady_clock::now().time_since_epoch()).count();
+}
+
+template <class T>
+static void dump(const std::string &path, const T *data, size_t n) {
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) { fprintf(stderr, "cannot write %s\n", path.c_str()); exit(2); }
+    if (n) fwrite(data, sizeof(T), n, f);
+    fclose(f);
+}
+
+// ---------------------------------------------------------------------------
+// Scene description shared with the B200 host code (tests/golden/*.scene):
+//   film W H | lookat 9f | fov f | spp n
+//   integrator key value ...   (maxerror minsampledistance mix maxdepth)
+//   light tx ty tz radius Lr Lg Lb nsamples
+//   skin key value ...  (roughness nmperunit f_mel f_eu f_blood f_ohg desiredlength
+//                        layers t0 ior0 t1 ior1)
+//   xform translate|rotate|scale ...   (applied, in order, to the next mesh)
+//   mesh file.bin       (int32 nv,nt,hasN,hasUV; P[3nv]; N[3nv]; uv[2nv]; idx[3nt])
+// ---------------------------------------------------------------------------
+struct SceneDesc {
+    int xres = 320, yres = 180, spp = 4;
+    float lookat[9] = {0, -5, 0, 0, 0, 0, 0, 0, 1};
+    float fov = 30.f;
+    std::map<std::string, float> integ;
+    struct Light { float t[3], radius, L[3]; int ns; };
+    std::vector<Light> lights;
+    std::map<std::string, float> skin;
+    float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
+    struct Xf { std::string kind; float v[4]; };
+    struct Mesh { std::vector<Xf> xf; std::string file; };
+    std::vector<Mesh> meshes;
+};
+
+static SceneDesc parseScene(const std::string &path) {
+    SceneDesc sd;
+    std::ifstream in(path);
+    if (!in) { fprintf(stderr, "cannot open scene %s\n", path.c_str()); exit(2); }
+    std::string dir = path.substr(0, path.find_last_of('/') + 1);
+    std::string line;
+    std::vector<SceneDesc::Xf> pending;
+    while (std::getline(in, line)) {
+        std::istringstream ls(line);
+        std::string key;
+        if (!(ls >> key) || key[0] == '#') continue;
+        if (key == "film") ls >> sd.xres >> sd.yres;
+        else if (key == "lookat") { for (int i = 0; i < 9; ++i) ls >> sd.lookat[i]; }
+        else if (key == "fov") ls >> sd.fov;
+        else if (key == "spp") ls >> sd.spp;
+        else if (key == "integrator") { std::string k; float v; while (ls >> k >> v) sd.integ[k] = v; }
+        else if (key == "light") {
+            SceneDesc::Light l;
+            ls >> l.t[0] >> l.t[1] >> l.t[2] >> l.radius >> l.L[0] >> l.L[1] >> l.L[2] >> l.ns;
+            sd.lights.push_back(l);
+        }
+        else if (key == "skin") {
+            std::string k;
+            while (ls >> k) {
+                if (k == "layers") { for (int i = 0; i < 4; ++i) ls >> sd.layers[i]; }
+                else { float v; ls >> v; sd.skin[k] = v; }
+            }
+        }
+        else if (key == "xform") {
+            SceneDesc::Xf x; ls >> x.kind;
+            int n = x.kind == "rotate" ? 4 : 3;
+            for (int i = 0; i < n; ++i) ls >> x.v[i];
+            pending.push_back(x);
+        }
+        else if (key == "mesh") {
+            SceneDesc::Mesh m; ls >> m.file;
+            if (m.file[0] != '/') m.file = dir + m.file;
+            m.xf = pending; pending.clear();
+            sd.meshes.push_back(m);
+        }
+        else { fprintf(stderr, "scene: unknown key %s\n", key.c_str()); exit(2); }
+    }
+    return sd;
+}
+
+static void addF(ParamSet &ps, const char *n, float v) { ps.AddFloat(n, &v, 1); }
+static void addI(ParamSet &ps, const char *n, int v) { ps.AddInt(n, &v, 1); }
+
+// Issues the same pbrt*() calls the reference's parser would for this scene.
+static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
+    {
+        ParamSet ps; addI(ps, "xresolution", sd.xres); addI(ps, "yresolution", sd.yres);
+        std::string fn = pfmOut; ps.AddString("filename", &fn, 1);
+        pbrtFilm("image", ps);
+    }
+    pbrtLookAt(sd.lookat[0], sd.lookat[1], sd.lookat[2], sd.lookat[3], sd.lookat[4], sd.lookat[5],
+               sd.lookat[6], sd.lookat[7], sd.lookat[8]);
+    { ParamSet ps; addF(ps, "fov", sd.fov); pbrtCamera("perspective", ps); }
+    { ParamSet ps; addI(ps, "pixelsamples", sd.spp); pbrtSampler("lowdiscrepancy", ps); }
+    {
+        ParamSet ps;
+        for (auto &kv : sd.integ) {
+            if (kv.first == "maxdepth") addI(ps, "maxdepth", (int)kv.second);
+            else addF(ps, kv.first.c_str(), kv.second);
+        }
+        pbrtSurfaceIntegrator("multipolesubsurface", ps);
+    }
+    pbrtWorldBegin();
+    for (auto &l : sd.lights) {
+        pbrtAttributeBegin();
+        { ParamSet ps; ps.AddRGBSpectrum("L", l.L, 3); addI(ps, "nsamples", l.ns); pbrtAreaLightSource("area", ps); }
+        pbrtTranslate(l.t[0], l.t[1], l.t[2]);
+        { ParamSet ps; addF(ps, "radius", l.radius); pbrtShape("sphere", ps); }
+        pbrtAttributeEnd();
+    }
+    for (auto &m : sd.meshes) {
+        pbrtAttributeBegin();
+        for (auto &x : m.xf) {
+            if (x.kind == "translate") pbrtTranslate(x.v[0], x.v[1], x.v[2]);
+            else if (x.kind == "rotate") pbrtRotate(x.v[0], x.v[1], x.v[2], x.v[3]);
+            else if (x.kind == "scale") pbrtScale(x.v[0], x.v[1], x.v[2]);
+        }
+        {
+            ParamSet ps;
+            for (auto &kv : sd.skin) {
+                if (kv.first == "desiredlength") addI(ps, "desiredlength", (int)kv.second);
+                else addF(ps, kv.first.c_str(), kv.second);
+            }
+            float one[3] = {1, 1, 1}, zero[3] = {0, 0, 0};
+            ps.AddRGBSpectrum("Kr", one, 3); ps.AddRGBSpectrum("Kt", zero, 3);
+            SkinLayer sl[2]; sl[0].thickness = sd.layers[0]; sl[0].ior = sd.layers[1];
+            sl[1].thickness = sd.layers[2]; sl[1].ior = sd.layers[3];
+            ps.AddSkinLayer("layers", sl, 2);
+            pbrtMaterial("layeredskin", ps);
+        }
+        {
+            FILE *f = fopen(m.file.c_str(), "rb");
+            if (!f) { fprintf(stderr, "cannot open mesh %s\n", m.file.c_str()); exit(2); }
+            int32_t hdr[4];
+            if (fread(hdr, 4, 4, f) != 4) exit(2);
+            int nv = hdr[0], nt = hdr[1];
+            std::vector<Point> P(nv); std::vector<Normal> N(nv); std::vector<float> uv(2 * nv); std::vector<int> idx(3 * nt);
+            if (fread(P.data(), 12, nv, f) != (size_t)nv) exit(2);
+            if (hdr[2] && fread(N.data(), 12, nv, f) != (size_t)nv) exit(2);
+            if (hdr[3] && fread(uv.data(), 8, nv, f) != (size_t)nv) exit(2);
+            if (fread(idx.data(), 12, nt, f) != (size_t)nt) exit(2);
+            fclose(f);
+            ParamSet ps;
+            ps.AddInt("indices", idx.data(), 3 * nt);
+            ps.AddPoint("P", P.data(), nv);
+            if (hdr[2]) ps.AddNormal("N", N.data(), nv);
+            if (hdr[3]) ps.AddFloat("uv", uv.data(), 2 * nv);
+            pbrtShape("trianglemesh", ps);
+        }
+        pbrtAttributeEnd();
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Dumps.  All files are raw little-endian arrays; meta.txt lists counts.
+// ---------------------------------------------------------------------------
+struct Meta {
+    std::ostringstream s;
+    template <class T> void kv(const char *k, T v) { s << k << " " << v << "\n"; }
+};
+
+static void dumpTransform(std::vector<float> &out, const Transform &t) {
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out.push_back(t.GetMatrix().m[i][j]);
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out.push_back(t.GetInverseMatrix().m[i][j]);
+}
+
+static void dumpSpectrumConsts(const std::string &dir) {
+    // SampledSpectrum::X/Y/Z (core/spectrum.cpp Init) + the CIE_Y integral used by ToXYZ.
+    std::vector<float> v;
+    for (int i = 0; i < nSpectralSamples; ++i) v.push_back(SampledSpectrum::X.c[i]);
+    for (int i = 0; i < nSpectralSamples; ++i) v.push_back(SampledSpectrum::Y.c[i]);
+    for (int i = 0; i < nSpectralSamples; ++i) v.push_back(SampledSpectrum::Z.c[i]);
+    dump(dir + "/cie_xyz30.bin", v.data(), v.size());
+}
+
+static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
+    const MultipoleBSSRDFData *bd = skin->preparedBSSRDFData;
+    std::vector<float> coeff;   // [layer][mua30 | musp30], then eta[2], thickness[2]
+    for (int l = 0; l < 2; ++l) {
+        for (int i = 0; i < nSpectralSamples; ++i) coeff.push_back(bd->sig_a[l].c[i]);
+        for (int i = 0; i < nSpectralSamples; ++i) coeff.push_back(bd->sigp_s[l].c[i]);
+    }
+    for (int l = 0; l < 2; ++l) coeff.push_back(bd->e[l]);
+    for (int l = 0; l < 2; ++l) coeff.push_back(bd->d[l]);
+    dump(dir + "/skin_coeffs.bin", coeff.data(), coeff.size());
+    const DrvProfileData *pd = reinterpret_cast<const DrvProfileData *>(skin->profileData);
+    std::vector<float> hdr, tab;
+    uint32_t len = (uint32_t)pd->spectralProfile[0].data.size();
+    for (int i = 0; i < nSpectralSamples; ++i) {
+        const DrvProfile &p = pd->spectralProfile[i];
+        if (p.data.size() != len) { fprintf(stderr, "profile lengths differ\n"); exit(2); }
+        hdr.push_back(p.dsqSpacing); hdr.push_back(p.rcpDsqSpacing);
+        hdr.push_back(p.totalReflectance); hdr.push_back(p.totalTransmittance);
+        for (uint32_t k = 0; k < len; ++k) tab.push_back(p.data[k].reflectance);
+    }
+    meta.kv("profile_len", len);
+    dump(dir + "/profile_hdr.bin", hdr.data(), hdr.size());     // [30][4]
+    dump(dir + "/profile_rd.bin", tab.data(), tab.size());      // [30][len]
+    std::vector<float> rho;
+    for (size_t k = 0; k < bd->rhoData.hd.size(); ++k)
+        for (int i = 0; i < nSpectralSamples; ++i) rho.push_back(bd->rhoData.hd[k].c[i]);
+    for (int i = 0; i < nSpectralSamples; ++i) rho.push_back(bd->rhoData.hh.c[i]);
+    meta.kv("rho_len", bd->rhoData.hd.size());
+    dump(dir + "/rho_hd.bin", rho.data(), rho.size());          // [1025][30] + hh[30]
+}
+
+static uint32_t countNodes(const DrvLinearBVHNode *nodes, uint32_t i) {
+    if (nodes[i].nPrimitives > 0) return 1;
+    return 1 + countNodes(nodes, i + 1) + countNodes(nodes, nodes[i].secondChildOffset);
+}
+
+struct DrvPrim { int32_t type, mesh, index, primitiveId; };   // type 0 = triangle, 1 = sphere (index = light no.)
+
+static void dumpBVH(const std::string &dir, const Scene *scene, Meta &meta,
+                    std::vector<const TriangleMesh *> &meshes) {
+    const BVHAccel *bvh = dynamic_cast<const BVHAccel *>(scene->aggregate);
+    if (!bvh) { fprintf(stderr, "aggregate is not a BVHAccel\n"); exit(2); }
+    const DrvLinearBVHNode *nodes = reinterpret_cast<const DrvLinearBVHNode *>(bvh->nodes);
+    uint32_t nNodes = countNodes(nodes, 0);
+    dump(dir + "/bvh_nodes.bin", nodes, nNodes);
+    std::vector<DrvPrim> prims;
+    std::vector<const Sphere *> spheres;
+    for (auto &pr : bvh->primitives) {
+        const GeometricPrimitive *gp = dynamic_cast<const GeometricPrimitive *>(pr.GetPtr());
+        if (!gp) { fprintf(stderr, "non-geometric primitive in BVH\n"); exit(2); }
+        const Shape *sh = gp->shape.GetPtr();
+        DrvPrim dp; dp.primitiveId = (int32_t)pr->primitiveId;
+        if (const Triangle *tri = dynamic_cast<const Triangle *>(sh)) {
+            const TriangleMesh *m = tri->mesh.GetPtr();
+            size_t mi = std::find(meshes.begin(), meshes.end(), m) - meshes.begin();
+            if (mi == meshes.size()) meshes.push_back(m);
+            dp.type = 0; dp.mesh = (int32_t)mi; dp.index = (int32_t)((tri->v - m->vertexIndex) / 3);
+        } else if (const Sphere *sp = dynamic_cast<const Sphere *>(sh)) {
+            size_t si = std::find(spheres.begin(), spheres.end(), sp) - spheres.begin();
+            if (si == spheres.size()) spheres.push_back(sp);
+            dp.type = 1; dp.mesh = -1; dp.index = (int32_t)si;
+        } else { fprintf(stderr, "unsupported shape in BVH\n"); exit(2); }
+        prims.push_back(dp);
+    }
+    dump(dir + "/bvh_prims.bin", prims.data(), prims.size());
+    meta.kv("bvh_nodes", nNodes);
+    meta.kv("bvh_prims", prims.size());
+    // World-space meshes exactly as the reference holds them (shapes/trianglemesh.cpp:72-73).
+    meta.kv("meshes", meshes.size());
+    for (size_t mi = 0; mi < meshes.size(); ++mi) {
+        const TriangleMesh *m = meshes[mi];
+        char nm[64];
+        snprintf(nm, sizeof nm, "/mesh%zu_", mi);
+        std::string b = dir + nm;
+        dump(b + "P.bin", m->p, m->nverts);
+        if (m->n) dump(b + "N.bin", m->n, m->nverts);
+        if (m->uvs) dump(b + "uv.bin", m->uvs, 2 * m->nverts);
+        dump(b + "idx.bin", m->vertexIndex, 3 * m->ntris);
+        std::vector<float> xf; dumpTransform(xf, *m->ObjectToWorld);
+        dump(b + "o2w.bin", xf.data(), xf.size());
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_nverts").c_str(), m->nverts);
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_ntris").c_str(), m->ntris);
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_hasN").c_str(), m->n ? 1 : 0);
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_hasUV").c_str(), m->uvs ? 1 : 0);
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_reverse").c_str(), (int)m->ReverseOrientation);
+        meta.kv((std::string("mesh") + std::to_string(mi) + "_swaps").c_str(), (int)m->TransformSwapsHandedness);
+    }
+}
+
+static void dumpLights(const std::string &dir, const Scene *scene, Meta &meta) {
+    // Per light: o2w(16) w2o(16) radius zmin zmax phiMax nSamples reverse Lemit[30]
+    std::vector<float> out;
+    for (const Light *l : scene->lights) {
+        const DiffuseAreaLight *dl = dynamic_cast<const DiffuseAreaLight *>(l);
+        if (!dl || dl->shapeSet->shapes.size() != 1) { fprintf(stderr, "unsupported light\n"); exit(2); }
+        const Sphere *sp = dynamic_cast<const Sphere *>(dl->shapeSet->shapes[0].GetPtr());
+        if (!sp) { fprintf(stderr, "light shape is not a sphere\n"); exit(2); }
+        dumpTransform(out, *sp->ObjectToWorld);
+        out.push_back(sp->radius); out.push_back(sp->zmin); out.push_back(sp->zmax); out.push_back(sp->phiMax);
+        out.push_back((float)dl->nSamples); out.push_back(sp->ReverseOrientation ? 1.f : 0.f);
+        out.push_back(sp->thetaMin); out.push_back(sp->thetaMax);
+        for (int i = 0; i < nSpectralSamples; ++i) out.push_back(dl->Lemit.c[i]);
+    }
+    meta.kv("lights", scene->lights.size());
+    dump(dir + "/lights.bin", out.data(), out.size());      // [nLights][32+8+30]
+}
+
+// Same functor as integrators/multipolesubsurface.cpp:241-251 (file-local there).
+class MultipoleReflectanceDrv {
+public:
+    MultipoleReflectanceDrv(const MultipoleBSSRDF *b) : bssrdf(b) {}
+    Spectrum operator()(float d2) const { return bssrdf->reflectance(d2); }
+private:
+    const MultipoleBSSRDF *bssrdf;
+};
+
+struct DrvRay { float o[3], d[3], mint, maxt; };                       // 32 B
+struct DrvHit { int32_t hit, prim; float t, rayEpsilon; float p[3], n[3], wo[3]; int32_t hasBssrdf; };  // 56 B
+
+static int runScene(int argc, char **argv) {
+    if (argc < 4) { fprintf(stderr, "usage: ref_driver scene <scene.txt> <outdir> [--ncores N] [--noexport] [--nocamera]\n"); return 2; }
+    std::string scenePath = argv[2], dir = argv[3];
+    int ncores = 1; bool doExport = true, doCamera = true;
+    for (int i = 4; i < argc; ++i) {
+        if (!strcmp(argv[i], "--ncores")) ncores = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--noexport")) doExport = false;
+        else if (!strcmp(argv[i], "--nocamera")) doCamera = false;
+    }
+    Options options; options.nCores = ncores; options.quiet = true;
+    pbrtInit(options);
+    SceneDesc sd = parseScene(scenePath);
+    Meta meta; meta.kv("ncores", ncores);
+    double t0 = now_s();
+    buildScene(sd, dir + "/image.pfm");     // LayeredSkin ctor builds profile + rho tables here
+    double tMaterial = now_s() - t0;
+    t0 = now_s();
+    Renderer *renderer = renderOptions->MakeRenderer();
+    Scene *scene = renderOptions->MakeScene();
+    double tAccel = now_s() - t0;
+    SamplerRenderer *sr = dynamic_cast<SamplerRenderer *>(renderer);
+    MultipoleSubsurfaceIntegrator *integ = dynamic_cast<MultipoleSubsurfaceIntegrator *>(sr->surfaceIntegrator);
+    Camera *camera = sr->camera;
+    std::vector<const TriangleMesh *> meshes;
+    if (doExport) {
+        dumpSpectrumConsts(dir);
+        for (auto &kv : scene->materials) {
+            const LayeredSkin *skin = dynamic_cast<const LayeredSkin *>(kv.second.GetPtr());
+            if (skin) { meta.kv("skin_material_id", kv.first); dumpMaterial(dir, skin, meta); break; }
+        }
+        dumpBVH(dir, scene, meta, meshes);
+        dumpLights(dir, scene, meta);
+        // Surface points exactly as Preprocess will regenerate them (deterministic tessellation).
+        vector<SurfacePoint> pts;
+        GetSurfacePointsThroughTessellation(camera->shutterOpen, integ->minSampleDist, scene,
+                                            &integ->originalPrimitives, &pts, integ->incenter);
+        dump(dir + "/surface_points.bin", pts.data(), pts.size());
+        meta.kv("surface_points", pts.size());
+    }
+    // ---- Preprocess: irradiance pass + octree (integrators/multipolesubsurface.cpp:170-238)
+    t0 = now_s();
+    sr->surfaceIntegrator->Preprocess(scene, camera, sr);
+    double tPre = now_s() - t0;
+    meta.kv("irradiance_points", integ->irradiancePoints.size());
+    {
+        int nPoints = (int)integ->irradiancePoints.size();
+        int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPoints / 4096));
+        meta.kv("irradiance_tasks", nTasks);
+    }
+    if (doExport) {
+        dump(dir + "/irradiance_points.bin", integ->irradiancePoints.data(), integ->irradiancePoints.size());
+        float ob[6] = {integ->octreeBounds.pMin.x, integ->octreeBounds.pMin.y, integ->octreeBounds.pMin.z,
+                       integ->octreeBounds.pMax.x, integ->octreeBounds.pMax.y, integ->octreeBounds.pMax.z};
+        dump(dir + "/octree_bounds.bin", ob, 6);
+        if (integ->octree) {
+            std::vector<float> root;
+            root.push_back(integ->octree->p.x); root.push_back(integ->octree->p.y); root.push_back(integ->octree->p.z);
+            root.push_back(integ->octree->sumArea);
+            for (int i = 0; i < nSpectralSamples; ++i) root.push_back(integ->octree->Et.c[i]);
+            dump(dir + "/octree_root.bin", root.data(), root.size());
+        }
+    }
+    meta.kv("maxError", integ->maxError);
+    meta.kv("mix", integ->mix);
+    meta.kv("minSampleDist", integ->minSampleDist);
+    // ---- Camera pass (renderers/samplerrenderer.cpp:59-167,191-225), single thread, task order
+    double tRender = 0;
+    if (doCamera && !doExport) {
+        t0 = now_s();
+        // timing path: the reference's own render loop (Preprocess already done -> skip it)
+        Sample *sample = new Sample(sr->sampler, sr->surfaceIntegrator, sr->volumeIntegrator, scene);
+        int nPixels = camera->film->xResolution * camera->film->yResolution;
+        int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPixels / (16 * 16)));
+        ProgressReporter reporter(nTasks, "Rendering");
+        vector<Task *> tasks;
+        for (int i = 0; i < nTasks; ++i)
+            tasks.push_back(new SamplerRendererTask(scene, sr, camera, reporter, sr->sampler, sample, false,
+                                                    nTasks - 1 - i, nTasks));
+        EnqueueTasks(tasks); WaitForAllTasks();
+        for (Task *t : tasks) delete t;
+        reporter.Done();
+        delete sample;
+        camera->film->WriteImage();
+        tRender = now_s() - t0;
+    }
+    if (doCamera && doExport) {
+        t0 = now_s();
+        const BVHAccel *bvh = dynamic_cast<const BVHAccel *>(scene->aggregate);
+        std::unordered_map<const Primitive *, int> primIndex;
+        for (size_t i = 0; i < bvh->primitives.size(); ++i) primIndex[bvh->primitives[i].GetPtr()] = (int)i;
+        Sample *origSample = new Sample(sr->sampler, sr->surfaceIntegrator, sr->volumeIntegrator, scene);
+        int nPixels = camera->film->xResolution * camera->film->yResolution;
+        int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPixels / (16 * 16)));
+        std::vector<DrvRay> rays; std::vector<DrvHit> hits; std::vector<float> imgxy, mo, Lout, Lsss;
+        for (int ti = 0; ti < nTasks; ++ti) {
+            int taskNum = nTasks - 1 - ti;
+            Sampler *sampler = sr->sampler->GetSubSampler(taskNum, nTasks);
+            if (!sampler) continue;
+            MemoryArena arena; RNG rng(taskNum);
+            int maxSamples = sampler->MaximumSampleCount();
+            Sample *samples = origSample->Duplicate(maxSamples);
+            RayDifferential *rds = new RayDifferential[maxSamples];
+            Spectrum *Ls = new Spectrum[maxSamples];
+            Intersection *isects = new Intersection[maxSamples];
+            int sampleCount;
+            while ((sampleCount = sampler->GetMoreSamples(samples, rng)) > 0) {
+                for (int i = 0; i < sampleCount; ++i) {
+                    float rayWeight = camera->GenerateRayDifferential(samples[i], &rds[i]);
+                    rds[i].ScaleDifferentials(1.f / sqrtf(sampler->samplesPerPixel));
+                    DrvRay dr = {{rds[i].o.x, rds[i].o.y, rds[i].o.z}, {rds[i].d.x, rds[i].d.y, rds[i].d.z}, rds[i].mint, rds[i].maxt};
+                    rays.push_back(dr);
+                    imgxy.push_back(samples[i].imageX); imgxy.push_back(samples[i].imageY);
+                    DrvHit h; memset(&h, 0, sizeof h); h.prim = -1;
+                    Spectrum Mo(0.f), sss(0.f);
+                    {   // closest hit on a copy of the ray (Intersect shrinks maxt)
+                        RayDifferential r2 = rds[i]; Intersection is;
+                        if (scene->Intersect(r2, &is)) {
+                            h.hit = 1; h.t = r2.maxt; h.rayEpsilon = is.rayEpsilon;
+                            auto it = primIndex.find(is.primitive); h.prim = it == primIndex.end() ? -2 : it->second;
+                            Vector wo = -r2.d;
+                            BSDF *bsdf = is.GetBSDF(r2, arena);
+                            const Point &p = bsdf->dgShading.p; const Normal &n = bsdf->dgShading.nn;
+                            h.p[0] = p.x; h.p[1] = p.y; h.p[2] = p.z; h.n[0] = n.x; h.n[1] = n.y; h.n[2] = n.z;
+                            h.wo[0] = wo.x; h.wo[1] = wo.y; h.wo[2] = wo.z;
+                            const MultipoleBSSRDF *bssrdf = is.GetMultipoleBSSRDF(r2, arena);
+                            if (bssrdf && integ->octree) {
+                                h.hasBssrdf = 1;
+                                MultipoleReflectanceDrv mr(bssrdf);
+                                Mo = integ->octree->Mo(integ->octreeBounds, p, n, mr, integ->maxError);
+                                float costheta = min(AbsDot(wo, n), 1.f);
+                                Spectrum Ft = Spectrum(1.f) - bssrdf->rho(costheta);
+                                sss = ((INV_PI * Ft) * Mo * Pow(bssrdf->albedo(), 1.f - integ->mix)).Clamp(0.f);
+                            }
+                        }
+                    }
+                    hits.push_back(h);
+                    for (int c = 0; c < nSpectralSamples; ++c) { mo.push_back(Mo.c[c]); Lsss.push_back(sss.c[c]); }
+                    if (rayWeight > 0.f) Ls[i] = rayWeight * sr->Li(scene, rds[i], &samples[i], rng, arena, &isects[i], NULL);
+                    else Ls[i] = 0.f;
+                    if (Ls[i].HasNaNs() || Ls[i].y() < -1e-5 || isinf(Ls[i].y())) Ls[i] = Spectrum(0.f);
+                    for (int c = 0; c < nSpectralSamples; ++c) Lout.push_back(Ls[i].c[c]);
+                    arena.FreeAll();
+                }
+                if (sampler->ReportResults(samples, rds, Ls, isects, sampleCount))
+                    for (int i = 0; i < sampleCount; ++i) camera->film->AddSample(samples[i], Ls[i]);
+                arena.FreeAll();
+            }
+            delete sampler; delete[] samples; delete[] rds; delete[] Ls; delete[] isects;
+        }
+        camera->film->WriteImage();
+        tRender = now_s() - t0;
+        dump(dir + "/camera_rays.bin", rays.data(), rays.size());
+        dump(dir + "/camera_xy.bin", imgxy.data(), imgxy.size());
+        dump(dir + "/hits.bin", hits.data(), hits.size());
+        dump(dir + "/mo.bin", mo.data(), mo.size());
+        dump(dir + "/L_sss.bin", Lsss.data(), Lsss.size());
+        dump(dir + "/L.bin", Lout.data(), Lout.size());
+        meta.kv("camera_samples", rays.size());
+        meta.kv("camera_tasks", nTasks);
+        std::vector<float> cam; dumpTransform(cam, camera->CameraToWorld.startTransform ? *camera->CameraToWorld.startTransform : Transform());
+        dump(dir + "/camera_c2w.bin", cam.data(), cam.size());
+    }
+    meta.kv("t_material_s", tMaterial); meta.kv("t_accel_s", tAccel);
+    meta.kv("t_preprocess_s", tPre); meta.kv("t_render_s", tRender);
+    std::string ms = meta.s.str();
+    dump(dir + "/meta.txt", ms.data(), ms.size());
+    fputs(ms.c_str(), stdout);
+    TasksCleanup();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// mpc mode: the reference's MPC_* DLL API on a list of layer stacks.
+//   in.txt line:  nLayers desiredLength lerpOnThinSlab resample stepSize  {ior thickness mua musp} x nLayers
+//   stepSize <= 0  ->  12*mfp/desiredLength with mfp as in core/multipole.cpp:247-264
+//   out.bin per line: uint32 len; float totalR,totalT; float d2[len],R[len],T[len]
+// ---------------------------------------------------------------------------
+static int runMPC(int argc, char **argv) {
+    if (argc < 4) { fprintf(stderr, "usage: ref_driver mpc <in.txt> <out.bin>\n"); return 2; }
+    std::ifstream in(argv[2]);
+    FILE *out = fopen(argv[3], "wb");
+    if (!in || !out) { fprintf(stderr, "mpc: cannot open files\n"); return 2; }
+    std::string line; int n = 0; double total = 0;
+    while (std::getline(in, line)) {
+        std::istringstream ls(line);
+        int nLayers, desiredLength, lerp, resample; float stepSize;
+        if (!(ls >> nLayers >> desiredLength >> lerp >> resample >> stepSize)) continue;
+        std::vector<MPC_LayerSpec> specs(nLayers);
+        float mfpTotal = 0.f;
+        for (int l = 0; l < nLayers; ++l) {
+            ls >> specs[l].ior >> specs[l].thickness >> specs[l].mua >> specs[l].musp;
+            specs[l].g_HG = 0.f;
+            mfpTotal += 1.f / (specs[l].mua + specs[l].musp);
+        }
+        MPC_Options opt; opt.desiredLength = desiredLength; opt.lerpOnThinSlab = lerp != 0;
+        float mfp = mfpTotal / (float)nLayers;
+        opt.desiredStepSize = stepSize > 0.f ? stepSize : 12.f * mfp / (float)opt.desiredLength;
+        double t0 = now_s();
+        MPC_Output *o = NULL;
+        MPC_ComputeDiffusionProfile(nLayers, specs.data(), &opt, &o);
+        if (resample) MPC_ResampleForUniformDistanceSquaredDistribution(o);
+        total += now_s() - t0;
+        uint32_t len = o->length;
+        fwrite(&len, 4, 1, out);
+        fwrite(&o->totalReflectance, 4, 1, out); fwrite(&o->totalTransmittance, 4, 1, out);
+        fwrite(o->pDistanceSquared, 4, len, out); fwrite(o->pReflectance, 4, len, out); fwrite(o->pTransmittance, 4, len, out);
+        MPC_FreeOutput(o);
+        ++n;
+    }
+    MPC_ClearCache();
+    fclose(out);
+    printf("mpc_profiles %d\nmpc_seconds %.6f\n", n, total);
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver scene|mpc ...\n"); return 2; }
+    if (!strcmp(argv[1], "scene")) return runScene(argc, argv);
+    if (!strcmp(argv[1], "mpc")) return runMPC(argc, argv);
+    fprintf(stderr, "unknown mode %s\n", argv[1]);
+    return 2;
+}
