@@ -1,0 +1,167 @@
+/* skin_cuda.h -- C ABI of the B200 device layer for pbrt-v2-skin's subsurface hot path.
+ *
+ * This is the thin `extern "C"` boundary BASELINE.json's north_star asks for (the
+ * reference tree would hold it as src/cuda/skin_cuda.h).  Plain pointers and sizes only;
+ * every array is caller-owned HOST memory unless the name ends in `_dev`.  All calls are
+ * stream-ordered on the context's stream and return 0 on success; on failure they return
+ * non-zero and skc_last_error() describes why (the plugin maps that to pbrt's Severe()).
+ * There is no CPU fallback anywhere behind this header.
+ *
+ * Each entry point names the reference code (Thomi6York/pbrt-v2-skin, paths under src/)
+ * whose work it replaces.
+ */
+#ifndef SKIN_CUDA_H
+#define SKIN_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SKC_NSPECTRAL 30 /* core/spectrum.h:46 nSpectralSamples; Spectrum == SampledSpectrum (core/pbrt.h:160) */
+#define SKC_RHO_LEN 1025 /* core/multipole.cpp:521-549 rho_hd table length */
+
+typedef struct skc_ctx skc_ctx;
+
+/* accelerators/bvh.cpp:113-123 LinearBVHNode, byte-compatible (32 B). */
+typedef struct {
+    float pmin[3], pmax[3];
+    uint32_t offset;      /* leaf: primitivesOffset, interior: secondChildOffset */
+    uint8_t nPrimitives;  /* 0 -> interior */
+    uint8_t axis;
+    uint8_t pad[2];
+} skc_bvh_node;
+
+/* One entry of BVHAccel::primitives (accelerators/bvh.h:66): what the leaf's virtual
+ * Primitive::Intersect resolves to.  type 0 = triangle `index` of the (world-space) mesh,
+ * type 1 = quadric sphere `index` (the emitter shapes: SURVEY.md appendix A1). */
+typedef struct {
+    int32_t type, mesh, index, primitiveId;
+} skc_prim;
+
+/* shapes/sphere.h Sphere + lights/diffuse.h DiffuseAreaLight, as one 70-float record. */
+typedef struct {
+    float o2w[16], w2o[16];            /* ObjectToWorld matrix and its inverse, row-major */
+    float radius, zmin, zmax, phiMax;
+    float nSamples, reverseOrientation, thetaMin, thetaMax;
+    float Lemit[SKC_NSPECTRAL];
+} skc_light;
+
+/* core/geometry.h RayBase without time/depth (32 B). */
+typedef struct {
+    float o[3], d[3], mint, maxt;
+} skc_ray;
+
+/* Closest-hit record: what Intersection carries that the path consumes (56 B).
+ * p,n = bsdf->dgShading.{p,nn} (integrators/multipolesubsurface.cpp:263-265), wo = -ray.d. */
+typedef struct {
+    int32_t hit, prim;   /* prim = index into the uploaded skc_prim array, -1 on miss */
+    float t, rayEpsilon;
+    float p[3], n[3], wo[3];
+    int32_t hasBssrdf;   /* hit primitive is a subsurface (LayeredSkin) triangle */
+} skc_hit;
+
+/* renderers/surfacepoints.h:45-55 SurfacePoint, byte-compatible (44 B). */
+typedef struct {
+    float p[3], n[3];
+    float u, v;
+    uint32_t materialId;
+    float area, rayEpsilon;
+} skc_surface_point;
+
+/* integrators/irradiancepoint.h:36-45 IrradiancePoint, byte-compatible (152 B). */
+typedef struct {
+    float p[3], n[3];
+    float E[SKC_NSPECTRAL];
+    float area, rayEpsilon;
+} skc_irr_point;
+
+/* multipole/MultipoleProfileCalculator/MultipoleProfileCalculator.h:34-67 PODs. */
+typedef struct { float ior, thickness, mua, musp, g_HG; } skc_layer_spec;     /* MPC_LayerSpec */
+typedef struct { float desiredStepSize; uint32_t desiredLength; int32_t lerpOnThinSlab; } skc_mpc_options; /* MPC_Options */
+
+/* ---- context ----------------------------------------------------------------------- */
+/* One context per process/GPU.  device < 0 selects the current CUDA device. */
+skc_ctx *skc_create(int device);
+void skc_destroy(skc_ctx *ctx);
+const char *skc_last_error(const skc_ctx *ctx);   /* ctx may be NULL: last create error */
+int skc_synchronize(skc_ctx *ctx);
+/* Counters of kernels launched by this context since creation (bench.py gpu_launches). */
+uint64_t skc_launch_count(const skc_ctx *ctx);
+/* Device time of the last call of each stage in ms (CUDA events on the ctx stream).
+ * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile */
+float skc_stage_ms(const skc_ctx *ctx, int stage);
+
+/* ---- BVHAccel (accelerators/bvh.cpp) ------------------------------------------------ */
+/* Upload the flat tree BVHAccel::flattenBVHTree (bvh.cpp:362-380) produced, the ordered
+ * primitive list, the world-space triangle meshes (shapes/trianglemesh.cpp:72-73) and the
+ * quadric spheres.  Vertex normals `N` (object space) and `o2w` feed GetShadingGeometry
+ * (shapes/trianglemesh.inl:224-299); N/uv may be NULL. */
+int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t nNodes,
+                   const skc_prim *prims, uint32_t nPrims,
+                   const float *P, const float *N, const float *uv, uint32_t nVerts,
+                   const int32_t *indices, uint32_t nTris, const float *meshO2W /*[32] m,minv*/,
+                   int reverseOrientation, int transformSwapsHandedness,
+                   const skc_light *spheres, uint32_t nSpheres);
+/* BVHAccel::IntersectP (bvh.cpp:442-488): out[i] = 1 if occluded. */
+int skc_trace_any(skc_ctx *ctx, const skc_ray *rays, uint64_t n, uint8_t *out);
+/* BVHAccel::Intersect (bvh.cpp:388-439) + GeometricPrimitive::Intersect
+ * (core/primitive.cpp:180-193) + GetShadingGeometry for the shading point/normal. */
+int skc_trace_closest(skc_ctx *ctx, const skc_ray *rays, uint64_t n, skc_hit *out);
+
+/* ---- material tables (core/multipole.cpp) ------------------------------------------- */
+/* Rd table of MultipoleProfileData (core/multipole.cpp:95-113): table[lambda][len] plus the
+ * per-wavelength rcpDsqSpacing (core/multipole.cpp:274-275), and the rho_hd table
+ * rhoHd[1025][30] (core/multipole.cpp:458-463). */
+int skc_upload_profile(skc_ctx *ctx, const float *table, const float *rcpDsqSpacing,
+                       uint32_t len, const float *rhoHd);
+
+/* ---- MultipoleSubsurfaceIntegrator::Preprocess (integrators/multipolesubsurface.cpp) - */
+/* Lights sampled by the irradiance loop (lights/diffuse.cpp:69-81). */
+int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t nLights);
+/* IrradianceTask::Run (multipolesubsurface.cpp:72-152) for points [first, first+count) of
+ * the nTotal-point set cut into nTasks slices (:73-74, RNG(taskNum*47) :81).  albedo30 is
+ * the material's albedo texture value per point ([count][30]) or NULL for constant 1.
+ * Results stay on the device (appended to the context's irradiance-point set at index
+ * `first`); `out` may be NULL, else receives count records. */
+int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal,
+                   uint64_t first, uint64_t count, uint32_t nTasks, float mix,
+                   const float *albedo30, skc_irr_point *out);
+/* Replace the device irradiance-point set (e.g. the reference's exported points, or the
+ * all-gathered shards of the other GPUs). */
+int skc_set_irradiance_points(skc_ctx *ctx, const skc_irr_point *pts, uint64_t n);
+/* Device-resident packed record (p, area, E[30]) range access for the multi-GPU exchange:
+ * returns device pointers to the float4 {p,area} array and the [n][32] E array. */
+int skc_irradiance_dev(skc_ctx *ctx, uint64_t nTotal, void **posArea_dev, void **E_dev);
+/* SubsurfaceOctreeNode::Insert + InitHierarchy (integrators/diffusionutil.h:94-173) over
+ * the device irradiance-point set; the flat tree stays on the device.  Optional outputs:
+ * node count, root {p[3], sumArea, Et[30]} (34 floats), bounds (6 floats). */
+int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6);
+
+/* ---- MultipoleSubsurfaceIntegrator::Li, subsurface term ----------------------------- */
+/* SubsurfaceOctreeNode::Mo (diffusionutil.h:175-210) for n points: Mo30[n][30]. */
+int skc_mo(skc_ctx *ctx, const float *p3, uint64_t n, float maxError, float *Mo30);
+/* Li's subsurface term (multipolesubsurface.cpp:279-287) for closest-hit records:
+ * L[i] = clamp0(INV_PI * (1-rho_hd(cos)) * Mo * albedo^(1-mix)); albedo30 NULL = 1.
+ * Mo30 and/or L30 may be NULL. */
+int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float maxError, float mix,
+               const float *albedo30, float *Mo30, float *L30);
+/* Whole camera pass on device-resident data: closest hit -> Mo -> subsurface radiance.
+ * Only L30 (and optionally hits) crosses back to the host. */
+int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxError, float mix,
+                    skc_hit *hitsOut, float *L30);
+
+/* ---- MPC_* profile generator (multipole/MultipoleProfileCalculator) ------------------ */
+/* MPC_ComputeDiffusionProfile (+ optional MPC_ResampleForUniformDistanceSquaredDistribution)
+ * for nSets layer stacks in one batch.  specs holds layersPerSet[s] records per set, packed.
+ * Outputs: length (same for all sets with equal desiredLength), and per set
+ * d2[len], R[len], T[len], totals[2].  Call once with out arrays NULL to get *lenOut. */
+int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, const uint32_t *layersPerSet,
+                      const skc_mpc_options *opts, uint32_t nSets, int resample,
+                      uint32_t *lenOut, float *d2, float *R, float *T, float *totals);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SKIN_CUDA_H */

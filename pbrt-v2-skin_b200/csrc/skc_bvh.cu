@@ -1,0 +1,259 @@
+// skc_bvh.cu -- BVHAccel on the device: upload of the flat tree and the two ray kernels.
+// Reference: accelerators/bvh.cpp (LinearBVHNode :113-123, Intersect :388-439,
+// IntersectP :442-488), core/primitive.cpp:180-193, shapes/trianglemesh.inl:55-136,224-299.
+#include <vector>
+#include <string.h>
+#include "skc_bvh.cuh"
+#include "skc_internal.h"
+
+// ---- kernels --------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace_any(BvhView bv, const skc_ray *__restrict__ rays, uint64_t n,
+                                                  uint8_t *__restrict__ out, unsigned long long *cnt) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+    float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+    DRay ray; ray.o = mk3(r0.x, r0.y, r0.z); ray.d = mk3(r0.w, r1.x, r1.y); ray.mint = r1.z; ray.maxt = r1.w;
+    bool occ = cnt ? bvhOccluded<true>(bv, ray, cnt) : bvhOccluded<false>(bv, ray, nullptr);
+    out[i] = occ ? 1 : 0;
+}
+
+// core/geometry.h:564-574
+__device__ inline void coordinateSystem(f3 v1, f3 *v2, f3 *v3) {
+    if (fabsf(v1.x) > fabsf(v1.y)) {
+        float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z);
+        *v2 = mk3(-v1.z * invLen, 0.f, v1.x * invLen);
+    } else {
+        float invLen = 1.f / sqrtf(v1.y * v1.y + v1.z * v1.z);
+        *v2 = mk3(0.f, v1.z * invLen, -v1.y * invLen);
+    }
+    *v3 = cross3(v1, *v2);
+}
+
+__device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
+
+// Shading point/normal of a triangle hit: trianglemesh.inl:92-133 (dg), :224-299 (shading
+// geometry), core/diffgeom.cpp:40-55 (nn and the orientation flip).
+__device__ inline void triShading(const MeshView &mv, int prim, const DRay &ray, float t, float b1, float b2,
+                                  f3 *pOut, f3 *nOut) {
+    int4 vi = __ldg(&mv.primInfo[prim]);
+    f3 p1 = ld3(mv.P, vi.x), p2 = ld3(mv.P, vi.y), p3 = ld3(mv.P, vi.z);
+    f3 e1 = sub3(p2, p1), e2 = sub3(p3, p1);
+    float uvs[3][2];
+    if (mv.UV) {
+        uvs[0][0] = mv.UV[2 * vi.x]; uvs[0][1] = mv.UV[2 * vi.x + 1];
+        uvs[1][0] = mv.UV[2 * vi.y]; uvs[1][1] = mv.UV[2 * vi.y + 1];
+        uvs[2][0] = mv.UV[2 * vi.z]; uvs[2][1] = mv.UV[2 * vi.z + 1];
+    } else {
+        uvs[0][0] = 0.f; uvs[0][1] = 0.f; uvs[1][0] = 1.f; uvs[1][1] = 0.f; uvs[2][0] = 1.f; uvs[2][1] = 1.f;
+    }
+    float du1 = uvs[0][0] - uvs[2][0], du2 = uvs[1][0] - uvs[2][0];
+    float dv1 = uvs[0][1] - uvs[2][1], dv2 = uvs[1][1] - uvs[2][1];
+    f3 dp1 = sub3(p1, p3), dp2 = sub3(p2, p3);
+    f3 dpdu, dpdv;
+    float determinant = du1 * dv2 - dv1 * du2;
+    if (determinant == 0.f) {
+        coordinateSystem(normalize3(cross3(e2, e1)), &dpdu, &dpdv);
+    } else {
+        float invdet = 1.f / determinant;
+        dpdu = mul3(sub3(mul3(dp1, dv2), mul3(dp2, dv1)), invdet);
+        dpdv = mul3(add3(mul3(dp1, -du2), mul3(dp2, du1)), invdet);
+    }
+    float b0 = 1 - b1 - b2;
+    float tu = b0 * uvs[0][0] + b1 * uvs[1][0] + b2 * uvs[2][0];
+    float tv = b0 * uvs[0][1] + b1 * uvs[1][1] + b2 * uvs[2][1];
+    *pOut = add3(ray.o, mul3(ray.d, t));
+    f3 nn;
+    if (!mv.N) {
+        nn = normalize3(cross3(dpdu, dpdv));
+    } else {
+        float A00 = uvs[1][0] - uvs[0][0], A01 = uvs[2][0] - uvs[0][0];
+        float A10 = uvs[1][1] - uvs[0][1], A11 = uvs[2][1] - uvs[0][1];
+        float C0 = tu - uvs[0][0], C1 = tv - uvs[0][1];
+        float bb[3];
+        float det = A00 * A11 - A01 * A10;     // core/transform.cpp:39-49
+        bool ok = !(fabsf(det) < 1e-10f);
+        if (ok) {
+            bb[1] = (A11 * C0 - A01 * C1) / det;
+            bb[2] = (A00 * C1 - A10 * C0) / det;
+            if (isnan(bb[1]) || isnan(bb[2])) ok = false;
+        }
+        if (!ok) bb[0] = bb[1] = bb[2] = 1.f / 3.f;
+        else bb[0] = 1.f - bb[1] - bb[2];
+        f3 n0 = ld3(mv.N, vi.x), n1 = ld3(mv.N, vi.y), n2 = ld3(mv.N, vi.z);
+        f3 nsum = add3(add3(mul3(n0, bb[0]), mul3(n1, bb[1])), mul3(n2, bb[2]));
+        f3 ns = normalize3(xformNormal(mv.w2o, nsum));
+        f3 ss = normalize3(dpdu);
+        f3 ts = cross3(ss, ns);
+        if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) {
+            ts = normalize3(ts);
+            ss = cross3(ts, ns);
+        } else {
+            coordinateSystem(ns, &ss, &ts);
+        }
+        nn = normalize3(cross3(ss, ts));
+    }
+    if (mv.flip) nn = mul3(nn, -1.f);
+    *nOut = nn;
+}
+
+__global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, const skc_ray *__restrict__ rays,
+                                                      uint64_t n, skc_hit *__restrict__ out, unsigned long long *cnt) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+    float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+    DRay ray; ray.o = mk3(r0.x, r0.y, r0.z); ray.d = mk3(r0.w, r1.x, r1.y); ray.mint = r1.z; ray.maxt = r1.w;
+    float b1 = 0.f, b2 = 0.f;
+    int prim = cnt ? bvhClosest<true>(bv, ray, &b1, &b2, cnt) : bvhClosest<false>(bv, ray, &b1, &b2, nullptr);
+    skc_hit h;
+    h.hit = prim >= 0; h.prim = prim; h.t = 0.f; h.rayEpsilon = 0.f;
+    h.p[0] = h.p[1] = h.p[2] = 0.f; h.n[0] = h.n[1] = h.n[2] = 0.f;
+    h.wo[0] = h.wo[1] = h.wo[2] = 0.f; h.hasBssrdf = 0;
+    if (prim >= 0) {
+        float t = ray.maxt;
+        h.t = t;
+        h.wo[0] = -ray.d.x; h.wo[1] = -ray.d.y; h.wo[2] = -ray.d.z;
+        int type = __ldg(&mv.primInfo[prim]).w;
+        if (type == 0) {
+            f3 p, nn;
+            triShading(mv, prim, ray, t, b1, b2, &p, &nn);
+            h.p[0] = p.x; h.p[1] = p.y; h.p[2] = p.z; h.n[0] = nn.x; h.n[1] = nn.y; h.n[2] = nn.z;
+            h.rayEpsilon = 1e-3f * t;        // trianglemesh.inl:134
+            h.hasBssrdf = 1;
+        } else {
+            f3 p = add3(ray.o, mul3(ray.d, t));
+            h.p[0] = p.x; h.p[1] = p.y; h.p[2] = p.z;
+            h.rayEpsilon = 5e-4f * t;        // shapes/sphere.cpp:156
+        }
+    }
+    // 56 B record: write as 14 words
+    uint32_t *dst = reinterpret_cast<uint32_t *>(out + i);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(&h);
+#pragma unroll
+    for (int k = 0; k < 14; ++k) dst[k] = src[k];
+}
+
+// ---- host side --------------------------------------------------------------------------
+BvhView skc_bvh_view(const skc_ctx *ctx) {
+    BvhView bv; bv.nodes = ctx->bvhNodes; bv.prims = ctx->bvhPrims; bv.spheres = ctx->spheres; return bv;
+}
+MeshView skc_mesh_view(const skc_ctx *ctx) {
+    MeshView mv; mv.primInfo = ctx->primInfo; mv.P = ctx->meshP; mv.N = ctx->meshN; mv.UV = ctx->meshUV;
+    memcpy(mv.o2w, ctx->meshO2W, 64); memcpy(mv.w2o, ctx->meshO2W + 16, 64); mv.flip = ctx->meshFlip;
+    return mv;
+}
+
+template <class T> static int upload(skc_ctx *ctx, T **dst, const T *src, size_t n) {
+    if (*dst) { cudaFree(*dst); *dst = nullptr; }
+    if (!n || !src) return 0;
+    SKC_CUDA(cudaMalloc((void **)dst, n * sizeof(T)));
+    SKC_CUDA(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t nNodes,
+                              const skc_prim *prims, uint32_t nPrims,
+                              const float *P, const float *N, const float *uv, uint32_t nVerts,
+                              const int32_t *indices, uint32_t nTris, const float *meshO2W,
+                              int reverseOrientation, int transformSwapsHandedness,
+                              const skc_light *spheres, uint32_t nSpheres) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!nodes || !nNodes || !prims || !nPrims) return skc_fail(ctx, "skc_upload_bvh: empty tree");
+    std::vector<float4> dn(2 * (size_t)nNodes), dp(3 * (size_t)nPrims);
+    std::vector<int4> info(nPrims);
+    for (uint32_t i = 0; i < nNodes; ++i) {
+        const skc_bvh_node &nd = nodes[i];
+        uint32_t meta = nd.nPrimitives | ((uint32_t)nd.axis << 8);
+        float fo, fm; memcpy(&fo, &nd.offset, 4); memcpy(&fm, &meta, 4);
+        dn[2 * i] = make_float4(nd.pmin[0], nd.pmin[1], nd.pmin[2], nd.pmax[0]);
+        dn[2 * i + 1] = make_float4(nd.pmax[1], nd.pmax[2], fo, fm);
+        if (nd.nPrimitives && nd.offset + nd.nPrimitives > nPrims) return skc_fail(ctx, "skc_upload_bvh: leaf %u out of range", i);
+        if (!nd.nPrimitives && nd.offset >= nNodes) return skc_fail(ctx, "skc_upload_bvh: child of node %u out of range", i);
+    }
+    for (uint32_t i = 0; i < nPrims; ++i) {
+        const skc_prim &pr = prims[i];
+        float ft, fi; int32_t ty = pr.type, ix = pr.index; memcpy(&ft, &ty, 4); memcpy(&fi, &ix, 4);
+        if (pr.type == 0) {
+            if (!P || !indices || (uint32_t)pr.index >= nTris) return skc_fail(ctx, "skc_upload_bvh: triangle %u out of range", i);
+            int v0 = indices[3 * pr.index], v1 = indices[3 * pr.index + 1], v2 = indices[3 * pr.index + 2];
+            if ((uint32_t)v0 >= nVerts || (uint32_t)v1 >= nVerts || (uint32_t)v2 >= nVerts) return skc_fail(ctx, "skc_upload_bvh: vertex index out of range");
+            const float *p1 = P + 3 * v0, *p2 = P + 3 * v1, *p3 = P + 3 * v2;
+            float e1[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+            float e2[3] = {p3[0] - p1[0], p3[1] - p1[1], p3[2] - p1[2]};
+            dp[3 * i] = make_float4(p1[0], p1[1], p1[2], e1[0]);
+            dp[3 * i + 1] = make_float4(e1[1], e1[2], e2[0], e2[1]);
+            dp[3 * i + 2] = make_float4(e2[2], ft, fi, 0.f);
+            info[i] = make_int4(v0, v1, v2, 0);
+        } else if (pr.type == 1) {
+            if ((uint32_t)pr.index >= nSpheres) return skc_fail(ctx, "skc_upload_bvh: sphere %u out of range", i);
+            dp[3 * i] = make_float4(0, 0, 0, 0); dp[3 * i + 1] = make_float4(0, 0, 0, 0);
+            dp[3 * i + 2] = make_float4(0.f, ft, fi, 0.f);
+            info[i] = make_int4(0, 0, 0, 1);
+        } else return skc_fail(ctx, "skc_upload_bvh: unsupported primitive type %d", pr.type);
+    }
+    if (upload(ctx, &ctx->bvhNodes, dn.data(), dn.size())) return 1;
+    if (upload(ctx, &ctx->bvhPrims, dp.data(), dp.size())) return 1;
+    if (upload(ctx, &ctx->primInfo, info.data(), info.size())) return 1;
+    if (upload(ctx, &ctx->meshP, P, 3 * (size_t)nVerts)) return 1;
+    if (upload(ctx, &ctx->meshN, N, N ? 3 * (size_t)nVerts : 0)) return 1;
+    if (upload(ctx, &ctx->meshUV, uv, uv ? 2 * (size_t)nVerts : 0)) return 1;
+    if (upload(ctx, &ctx->spheres, spheres, nSpheres)) return 1;
+    ctx->nNodes = nNodes; ctx->nPrims = nPrims; ctx->nVerts = nVerts; ctx->nSpheres = nSpheres;
+    if (meshO2W) memcpy(ctx->meshO2W, meshO2W, 128);
+    else { float id[32] = {1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1, 1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1}; memcpy(ctx->meshO2W, id, 128); }
+    ctx->meshFlip = (reverseOrientation != 0) ^ (transformSwapsHandedness != 0);
+    return 0;
+}
+
+int skc_trace_any_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, uint8_t *outDev, unsigned long long *cntDev) {
+    if (!ctx->bvhNodes) return skc_fail(ctx, "skc_trace_any: no BVH uploaded");
+    if (!n) return 0;
+    uint64_t blocks = (n + 127) / 128;
+    k_trace_any<<<(unsigned)blocks, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), raysDev, n, outDev, cntDev);
+    SKC_LAUNCHED("k_trace_any");
+    return 0;
+}
+
+int skc_trace_closest_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, skc_hit *outDev, unsigned long long *cntDev) {
+    if (!ctx->bvhNodes) return skc_fail(ctx, "skc_trace_closest: no BVH uploaded");
+    if (!n) return 0;
+    uint64_t blocks = (n + 127) / 128;
+    k_trace_closest<<<(unsigned)blocks, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), raysDev, n, outDev, cntDev);
+    SKC_LAUNCHED("k_trace_closest");
+    return 0;
+}
+
+extern "C" int skc_trace_any(skc_ctx *ctx, const skc_ray *rays, uint64_t n, uint8_t *out) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    skc_ray *d = (skc_ray *)skc_scratch(ctx, 0, n * sizeof(skc_ray));
+    uint8_t *o = (uint8_t *)skc_scratch(ctx, 1, n);
+    if (!d || !o) return 1;
+    SKC_CUDA(cudaMemcpyAsync(d, rays, n * sizeof(skc_ray), cudaMemcpyHostToDevice, ctx->stream));
+    skc_stage_begin(ctx);
+    if (skc_trace_any_dev(ctx, d, n, o, nullptr)) return 1;
+    skc_stage_end(ctx, 5);
+    SKC_CUDA(cudaMemcpyAsync(out, o, n, cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int skc_trace_closest(skc_ctx *ctx, const skc_ray *rays, uint64_t n, skc_hit *out) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    skc_ray *d = (skc_ray *)skc_scratch(ctx, 0, n * sizeof(skc_ray));
+    skc_hit *o = (skc_hit *)skc_scratch(ctx, 1, n * sizeof(skc_hit));
+    if (!d || !o) return 1;
+    SKC_CUDA(cudaMemcpyAsync(d, rays, n * sizeof(skc_ray), cudaMemcpyHostToDevice, ctx->stream));
+    skc_stage_begin(ctx);
+    if (skc_trace_closest_dev(ctx, d, n, o, nullptr)) return 1;
+    skc_stage_end(ctx, 3);
+    SKC_CUDA(cudaMemcpyAsync(out, o, n * sizeof(skc_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}

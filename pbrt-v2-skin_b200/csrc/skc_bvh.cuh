@@ -1,0 +1,237 @@
+// skc_bvh.cuh -- device-side BVH traversal and primitive tests.
+//
+// Follows accelerators/bvh.cpp:126-148 (slab test), :388-439 (Intersect), :442-488
+// (IntersectP); shapes/trianglemesh.inl:55-136,140-210 (triangle); shapes/sphere.cpp:58-210
+// (quadric sphere) of the reference, operation for operation, so that hit/no-hit, the hit
+// primitive and t are bit-identical to the CPU code.
+//
+// Device layout: a node is two float4 (32 B, one 32 B sector):
+//   n0 = {min.x, min.y, min.z, max.x}   n1 = {max.y, max.z, offset, nPrims | axis << 8}
+// a primitive is three float4 (48 B): {p1.xyz, e1.x} {e1.yz, e2.xy} {e2.z, type, index, -}
+// with e1 = p2 - p1, e2 = p3 - p1 precomputed (the same fp32 subtraction the CPU does).
+#pragma once
+#include "skc_common.cuh"
+
+struct DRay { f3 o, d; float mint, maxt; };
+
+struct BvhView {
+    const float4 *nodes;
+    const float4 *prims;
+    const skc_light *spheres;
+};
+
+// What closest-hit shading needs of the triangle mesh (shapes/trianglemesh.inl:224-299).
+struct MeshView {
+    const int4 *primInfo;      // per BVH primitive: vertex ids v0,v1,v2 and type
+    const float *P, *N, *UV;   // world-space points, object-space normals, uv (N/UV may be null)
+    float o2w[16], w2o[16];    // mesh ObjectToWorld matrix and inverse
+    int flip;                  // ReverseOrientation ^ TransformSwapsHandedness
+};
+
+__device__ __forceinline__ f3 xformPoint(const float *m, f3 p) {
+    float xp = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];
+    float yp = m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7];
+    float zp = m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11];
+    float wp = m[12] * p.x + m[13] * p.y + m[14] * p.z + m[15];
+    if (wp != 1.f) { float inv = 1.f / wp; xp *= inv; yp *= inv; zp *= inv; }
+    return mk3(xp, yp, zp);
+}
+__device__ __forceinline__ f3 xformVector(const float *m, f3 v) {
+    return mk3(m[0] * v.x + m[1] * v.y + m[2] * v.z,
+               m[4] * v.x + m[5] * v.y + m[6] * v.z,
+               m[8] * v.x + m[9] * v.y + m[10] * v.z);
+}
+// Transform::operator()(Normal): transpose of the inverse (core/transform.h:232-237)
+__device__ __forceinline__ f3 xformNormal(const float *mInv, f3 n) {
+    return mk3(mInv[0] * n.x + mInv[4] * n.y + mInv[8] * n.z,
+               mInv[1] * n.x + mInv[5] * n.y + mInv[9] * n.z,
+               mInv[2] * n.x + mInv[6] * n.y + mInv[10] * n.z);
+}
+
+// core/pbrt.h:354-368
+__device__ __forceinline__ bool quadratic(float A, float B, float C, float *t0, float *t1) {
+    float discrim = B * B - 4.f * A * C;
+    if (discrim < 0.f) return false;
+    float rootDiscrim = sqrtf(discrim);
+    float q;
+    if (B < 0) q = -.5f * (B - rootDiscrim);
+    else       q = -.5f * (B + rootDiscrim);
+    *t0 = q / A;
+    *t1 = C / q;
+    if (*t0 > *t1) { float t = *t0; *t0 = *t1; *t1 = t; }
+    return true;
+}
+
+// shapes/sphere.cpp:58-101 / :160-210 -- returns true and thit (object == world parameter)
+__device__ inline bool sphereIntersect(const skc_light &s, const DRay &r, float *tHit) {
+    DRay ray;
+    ray.o = xformPoint(s.w2o, r.o);
+    ray.d = xformVector(s.w2o, r.d);
+    ray.mint = r.mint; ray.maxt = r.maxt;
+    float radius = s.radius;
+    float A = ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z;
+    float B = 2 * (ray.d.x * ray.o.x + ray.d.y * ray.o.y + ray.d.z * ray.o.z);
+    float C = ray.o.x * ray.o.x + ray.o.y * ray.o.y + ray.o.z * ray.o.z - radius * radius;
+    float t0, t1;
+    if (!quadratic(A, B, C, &t0, &t1)) return false;
+    if (t0 > ray.maxt || t1 < ray.mint) return false;
+    float thit = t0;
+    if (t0 < ray.mint) {
+        thit = t1;
+        if (thit > ray.maxt) return false;
+    }
+    f3 phit = add3(ray.o, mul3(ray.d, thit));
+    if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+    float phi = atan2f(phit.y, phit.x);
+    if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+    float zmin = s.zmin, zmax = s.zmax, phiMax = s.phiMax;
+    if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) {
+        if (thit == t1) return false;
+        if (t1 > ray.maxt) return false;
+        thit = t1;
+        phit = add3(ray.o, mul3(ray.d, thit));
+        if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+        phi = atan2f(phit.y, phit.x);
+        if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+        if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax)
+            return false;
+    }
+    *tHit = thit;
+    return true;
+}
+
+// shapes/trianglemesh.inl:55-90 (no alpha texture on this path).  b1/b2 returned for shading.
+__device__ __forceinline__ bool triIntersect(f3 p1, f3 e1, f3 e2, const DRay &ray,
+                                             float *tOut, float *b1Out, float *b2Out) {
+    f3 s1 = cross3(ray.d, e2);
+    float divisor = dot3(s1, e1);
+    if (divisor == 0.f) return false;
+    float invDivisor = 1.f / divisor;
+    f3 d = sub3(ray.o, p1);
+    float b1 = dot3(d, s1) * invDivisor;
+    if (b1 < 0.f || b1 > 1.f) return false;
+    f3 s2 = cross3(d, e1);
+    float b2 = dot3(ray.d, s2) * invDivisor;
+    if (b2 < 0.f || b1 + b2 > 1.f) return false;
+    float t = dot3(e2, s2) * invDivisor;
+    if (t < ray.mint || t > ray.maxt) return false;
+    *tOut = t; *b1Out = b1; *b2Out = b2;
+    return true;
+}
+
+struct SlabSetup { f3 invDir; int neg[3]; };
+__device__ __forceinline__ SlabSetup slabSetup(const DRay &r) {
+    SlabSetup s;
+    s.invDir = mk3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
+    s.neg[0] = s.invDir.x < 0; s.neg[1] = s.invDir.y < 0; s.neg[2] = s.invDir.z < 0;
+    return s;
+}
+// accelerators/bvh.cpp:126-148
+__device__ __forceinline__ bool slabTest(float4 n0, float4 n1, const DRay &ray, const SlabSetup &s) {
+    float minx = n0.x, miny = n0.y, minz = n0.z, maxx = n0.w, maxy = n1.x, maxz = n1.y;
+    float tmin = ((s.neg[0] ? maxx : minx) - ray.o.x) * s.invDir.x;
+    float tmax = ((s.neg[0] ? minx : maxx) - ray.o.x) * s.invDir.x;
+    float tymin = ((s.neg[1] ? maxy : miny) - ray.o.y) * s.invDir.y;
+    float tymax = ((s.neg[1] ? miny : maxy) - ray.o.y) * s.invDir.y;
+    if ((tmin > tymax) || (tymin > tmax)) return false;
+    if (tymin > tmin) tmin = tymin;
+    if (tymax < tmax) tmax = tymax;
+    float tzmin = ((s.neg[2] ? maxz : minz) - ray.o.z) * s.invDir.z;
+    float tzmax = ((s.neg[2] ? minz : maxz) - ray.o.z) * s.invDir.z;
+    if ((tmin > tzmax) || (tzmin > tmax)) return false;
+    if (tzmin > tmin) tmin = tzmin;
+    if (tzmax < tmax) tmax = tzmax;
+    return (tmin < ray.maxt) && (tmax > ray.mint);
+}
+
+#define SKC_BVH_STACK 64
+
+// BVHAccel::IntersectP (bvh.cpp:442-488).  counters (optional): [0] slab tests, [1] prim tests.
+template <bool COUNT>
+__device__ inline bool bvhOccluded(const BvhView &bv, const DRay &ray, unsigned long long *cnt) {
+    SlabSetup ss = slabSetup(ray);
+    uint32_t todo[SKC_BVH_STACK];
+    uint32_t todoOffset = 0, nodeNum = 0;
+    uint32_t nNode = 0, nPrim = 0;
+    bool occluded = false;
+    while (true) {
+        float4 n0 = __ldg(&bv.nodes[2 * nodeNum]);
+        float4 n1 = __ldg(&bv.nodes[2 * nodeNum + 1]);
+        if (COUNT) nNode++;
+        if (slabTest(n0, n1, ray, ss)) {
+            uint32_t offset = __float_as_uint(n1.z), meta = __float_as_uint(n1.w);
+            uint32_t nPrims = meta & 0xff;
+            if (nPrims > 0) {
+                for (uint32_t i = 0; i < nPrims; ++i) {
+                    const float4 *pp = &bv.prims[3 * (offset + i)];
+                    float4 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2);
+                    if (COUNT) nPrim++;
+                    float t, b1, b2;
+                    bool h;
+                    if (__float_as_int(c.y) == 0)
+                        h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
+                    else
+                        h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
+                    if (h) { occluded = true; break; }
+                }
+                if (occluded) break;
+                if (todoOffset == 0) break;
+                nodeNum = todo[--todoOffset];
+            } else {
+                uint32_t axis = (meta >> 8) & 3;
+                if (ss.neg[axis]) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
+                else              { todo[todoOffset++] = offset; nodeNum = nodeNum + 1; }
+            }
+        } else {
+            if (todoOffset == 0) break;
+            nodeNum = todo[--todoOffset];
+        }
+    }
+    if (COUNT && cnt) { atomicAdd(&cnt[0], (unsigned long long)nNode); atomicAdd(&cnt[1], (unsigned long long)nPrim); }
+    return occluded;
+}
+
+// BVHAccel::Intersect (bvh.cpp:388-439): closest hit; ray.maxt shrinks (primitive.cpp:191).
+template <bool COUNT>
+__device__ inline int bvhClosest(const BvhView &bv, DRay &ray, float *b1Hit, float *b2Hit,
+                                 unsigned long long *cnt) {
+    SlabSetup ss = slabSetup(ray);
+    uint32_t todo[SKC_BVH_STACK];
+    uint32_t todoOffset = 0, nodeNum = 0;
+    uint32_t nNode = 0, nPrim = 0;
+    int hitPrim = -1;
+    while (true) {
+        float4 n0 = __ldg(&bv.nodes[2 * nodeNum]);
+        float4 n1 = __ldg(&bv.nodes[2 * nodeNum + 1]);
+        if (COUNT) nNode++;
+        if (slabTest(n0, n1, ray, ss)) {
+            uint32_t offset = __float_as_uint(n1.z), meta = __float_as_uint(n1.w);
+            uint32_t nPrims = meta & 0xff;
+            if (nPrims > 0) {
+                for (uint32_t i = 0; i < nPrims; ++i) {
+                    const float4 *pp = &bv.prims[3 * (offset + i)];
+                    float4 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2);
+                    if (COUNT) nPrim++;
+                    float t, b1 = 0.f, b2 = 0.f;
+                    bool h;
+                    if (__float_as_int(c.y) == 0)
+                        h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
+                    else
+                        h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
+                    if (h) { ray.maxt = t; hitPrim = (int)(offset + i); *b1Hit = b1; *b2Hit = b2; }
+                }
+                if (todoOffset == 0) break;
+                nodeNum = todo[--todoOffset];
+            } else {
+                uint32_t axis = (meta >> 8) & 3;
+                if (ss.neg[axis]) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
+                else              { todo[todoOffset++] = offset; nodeNum = nodeNum + 1; }
+            }
+        } else {
+            if (todoOffset == 0) break;
+            nodeNum = todo[--todoOffset];
+        }
+    }
+    if (COUNT && cnt) { atomicAdd(&cnt[0], (unsigned long long)nNode); atomicAdd(&cnt[1], (unsigned long long)nPrim); }
+    return hitPrim;
+}

@@ -1,0 +1,104 @@
+// skc_common.cuh -- context object and arithmetic helpers shared by the kernels.
+//
+// Arithmetic convention (matters for parity, SURVEY.md section 7 "hard parts" #1):
+// the reference is plain x86-64 SSE2 code (no FMA contraction, IEEE div/sqrt, no FTZ),
+// so the whole library is compiled with -fmad=false -prec-div=true -prec-sqrt=true and
+// every helper below spells the reference's operation order.  Where the reference
+// promotes to double (Cross: core/geometry.h:529-536; anything touching M_PI) so do we.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include "../../include/skin_cuda.h"
+
+#define SKC_NS SKC_NSPECTRAL
+#define SKC_EPAD 32            // spectral rows are padded to 32 floats = one 128 B line
+#define SKC_NSTAGES 8
+
+struct skc_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    float stageMs[SKC_NSTAGES] = {0};
+
+    // --- BVH (skc_bvh.cu)
+    float4 *bvhNodes = nullptr;    // 2 x float4 per node
+    uint32_t nNodes = 0;
+    float4 *bvhPrims = nullptr;    // 3 x float4 per primitive (triangle: p1,e1,e2 | sphere tag)
+    uint32_t nPrims = 0;
+    int4 *primInfo = nullptr;      // per primitive: v0,v1,v2 (mesh vertex ids), type
+    float *meshP = nullptr, *meshN = nullptr, *meshUV = nullptr;
+    uint32_t nVerts = 0;
+    float meshO2W[32];
+    int meshFlip = 0;              // ReverseOrientation ^ TransformSwapsHandedness
+    skc_light *spheres = nullptr;  // quadric primitives in the BVH
+    uint32_t nSpheres = 0;
+
+    // --- material tables (skc_mo.cu)
+    float2 *profPairs = nullptr;   // [30][len] {data[i], data[i+1]}
+    float *profRcp = nullptr;      // [32]
+    float profMaxD2 = 0.f;         // beyond this d^2 every wavelength returns 0
+    uint32_t profLen = 0;
+    float *rhoHd = nullptr;        // [1025][32]
+
+    // --- lights (skc_irradiance.cu)
+    skc_light *lights = nullptr;
+    uint32_t nLights = 0;
+
+    // --- irradiance point set
+    float4 *ipPosArea = nullptr;   // {p.xyz, area}
+    float *ipE = nullptr;          // [n][32]
+    uint64_t ipCount = 0, ipCap = 0;
+
+    // --- octree (skc_octree.cu)
+    float4 *otGeo = nullptr;       // 3 x float4 per node: {p.xyz,sumArea} {min.xyz,max.x} {max.y,max.z,w0,w1}
+    float *otEt = nullptr;         // [nNodes][32]
+    uint32_t *otPointIdx = nullptr;// leaf-ordered permutation of irradiance points
+    float4 *otLeafPosArea = nullptr; // irradiance points gathered in leaf order
+    float *otLeafE = nullptr;        // [n][32] in leaf order
+    uint32_t otNodes = 0, otCap = 0;
+    uint64_t otPoints = 0;
+    float otBoundsHost[6];
+
+    // --- scratch
+    void *scratch[8] = {nullptr};
+    size_t scratchBytes[8] = {0};
+};
+
+// topology flags word: bits 0-7 child mask (interior) or point count (leaf),
+// bit 8 leaf, bit 9 Et black
+#define SKC_OT_LEAF 0x100u
+#define SKC_OT_BLACK 0x200u
+
+int skc_fail(skc_ctx *ctx, const char *fmt, ...);
+int skc_check(skc_ctx *ctx, cudaError_t e, const char *what);
+void *skc_scratch(skc_ctx *ctx, int slot, size_t bytes);
+void skc_stage_begin(skc_ctx *ctx);
+void skc_stage_end(skc_ctx *ctx, int stage);
+
+#define SKC_CUDA(call) do { if (skc_check(ctx, (call), #call)) return 1; } while (0)
+#define SKC_LAUNCHED(what) do { ctx->launches++; if (skc_check(ctx, cudaGetLastError(), what)) return 1; } while (0)
+
+// ------------------------------------------------------------------------------------
+// device helpers
+// ------------------------------------------------------------------------------------
+struct f3 { float x, y, z; };
+__host__ __device__ inline f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__host__ __device__ inline f3 sub3(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ inline f3 add3(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ inline f3 mul3(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ inline float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// core/geometry.h:529-536: products and differences in double, rounded once to float
+__host__ __device__ inline f3 cross3(f3 a, f3 b) {
+    double ax = a.x, ay = a.y, az = a.z, bx = b.x, by = b.y, bz = b.z;
+    return mk3((float)((ay * bz) - (az * by)), (float)((az * bx) - (ax * bz)), (float)((ax * by) - (ay * bx)));
+}
+__host__ __device__ inline float len3(f3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }
+// core/geometry.h:102-106,562: v / len == v * (1/len)
+__host__ __device__ inline f3 normalize3(f3 a) { float inv = 1.f / len3(a); return mk3(a.x * inv, a.y * inv, a.z * inv); }
+__host__ __device__ inline float dist2(f3 a, f3 b) { f3 d = sub3(a, b); return d.x * d.x + d.y * d.y + d.z * d.z; }
+
+#define SKC_PI_D 3.14159265358979323846  /* M_PI */

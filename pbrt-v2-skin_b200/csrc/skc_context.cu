@@ -1,0 +1,86 @@
+// skc_context.cu -- context lifetime, error reporting, scratch memory, stage timing.
+#include <stdarg.h>
+#include "skc_common.cuh"
+
+static std::string g_createError;
+
+int skc_fail(skc_ctx *ctx, const char *fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (ctx) ctx->err = buf; else g_createError = buf;
+    return 1;
+}
+
+int skc_check(skc_ctx *ctx, cudaError_t e, const char *what) {
+    if (e == cudaSuccess) return 0;
+    return skc_fail(ctx, "CUDA error %s (%s) at %s", cudaGetErrorName(e), cudaGetErrorString(e), what);
+}
+
+void *skc_scratch(skc_ctx *ctx, int slot, size_t bytes) {
+    if (ctx->scratchBytes[slot] >= bytes && ctx->scratch[slot]) return ctx->scratch[slot];
+    if (ctx->scratch[slot]) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->scratch[slot]); ctx->scratch[slot] = nullptr; }
+    size_t want = bytes + bytes / 8 + 256;
+    if (skc_check(ctx, cudaMalloc(&ctx->scratch[slot], want), "scratch cudaMalloc")) { ctx->scratchBytes[slot] = 0; return nullptr; }
+    ctx->scratchBytes[slot] = want;
+    return ctx->scratch[slot];
+}
+
+void skc_stage_begin(skc_ctx *ctx) { cudaEventRecord(ctx->ev0, ctx->stream); }
+void skc_stage_end(skc_ctx *ctx, int stage) {
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    cudaEventSynchronize(ctx->ev1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->stageMs[stage] = ms;
+}
+
+extern "C" skc_ctx *skc_create(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        skc_fail(nullptr, "skc_create: no CUDA device (%s); this library has no CPU fallback",
+                 e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) device = 0; }
+    if (device >= count) { skc_fail(nullptr, "skc_create: device %d out of range (%d devices)", device, count); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { skc_fail(nullptr, "skc_create: cudaSetDevice(%d) failed", device); return nullptr; }
+    skc_ctx *ctx = new skc_ctx();
+    ctx->device = device;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        skc_fail(nullptr, "skc_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return nullptr;
+    }
+    return ctx;
+}
+
+extern "C" void skc_destroy(skc_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    void *ptrs[] = {ctx->bvhNodes, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
+                    ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->lights, ctx->ipPosArea, ctx->ipE,
+                    ctx->otGeo, ctx->otEt, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" const char *skc_last_error(const skc_ctx *ctx) {
+    return ctx ? ctx->err.c_str() : g_createError.c_str();
+}
+
+extern "C" int skc_synchronize(skc_ctx *ctx) {
+    cudaSetDevice(ctx->device);
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
+extern "C" float skc_stage_ms(const skc_ctx *ctx, int stage) {
+    return (stage >= 0 && stage < SKC_NSTAGES) ? ctx->stageMs[stage] : -1.f;
+}

@@ -1,0 +1,11 @@
+// skc_internal.h -- device-pointer entry points shared between translation units.
+#pragma once
+#include "skc_common.cuh"
+#include "skc_bvh.cuh"
+
+BvhView skc_bvh_view(const skc_ctx *ctx);
+MeshView skc_mesh_view(const skc_ctx *ctx);
+int skc_trace_any_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, uint8_t *outDev, unsigned long long *cntDev);
+int skc_trace_closest_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, skc_hit *outDev, unsigned long long *cntDev);
+int skc_mo_dev(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, uint64_t n, float maxError, float *MoDev /*[n][32]*/);
+int skc_ensure_points(skc_ctx *ctx, uint64_t n);

@@ -1,0 +1,462 @@
+// skc_irradiance.cu -- MultipoleSubsurfaceIntegrator::Preprocess, irradiance pass.
+//
+// Reference: integrators/multipolesubsurface.cpp:72-152 (IrradianceTask::Run),
+// lights/diffuse.cpp:69-81, core/light.cpp:145-174 (ShapeSet::Sample/Pdf),
+// shapes/sphere.cpp:236-273 (Sphere::Sample/Pdf), core/light.h:87-92 (SetSegment),
+// core/montecarlo.h:278-301 ((0,2)-sequence), core/rng.cpp:43-110 (MT19937),
+// core/multipole.cpp:458-463 (rho_hd lookup).
+//
+// Two kernels:
+//   k_scrambles  one CTA per IrradianceTask: regenerates the task's MT19937 stream
+//                (RNG(taskNum*47)) 624 words at a time in shared memory and writes the three
+//                scramble words of every (point, light) pair -- the stream position depends
+//                only on (point index within task, light), SURVEY.md appendix A6.
+//   k_irradiance one thread per point for the geometric part (light sampling + shadow ray
+//                through the BVH), then the warp transposes: lane = wavelength, and the
+//                30-wide spectral accumulation runs with coalesced 120 B rows of the rho
+//                table, Lemit and the output E.
+#include "skc_bvh.cuh"
+#include "skc_internal.h"
+
+#define MT_N 624
+#define MT_M 397
+
+__device__ __forceinline__ uint32_t mtTwist(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+    return c ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+}
+
+// grid = tasks [taskFirst, taskFirst + gridDim.x); block = 256 threads
+__global__ void __launch_bounds__(256) k_scrambles(uint32_t taskFirst, uint32_t nTasks, uint64_t nTotal,
+                                                  uint64_t first, uint64_t count, uint32_t wordsPerPoint,
+                                                  uint32_t *__restrict__ out) {
+    __shared__ uint32_t mt[MT_N];
+    uint32_t task = taskFirst + blockIdx.x;
+    // multipolesubsurface.cpp:73-74 (the reference truncates through int)
+    uint64_t idxStart = (uint64_t)(int)((uint64_t)task * nTotal / nTasks);
+    uint64_t idxEnd = (uint64_t)(int)((uint64_t)(task + 1) * nTotal / nTasks);
+    if (idxStart == idxEnd) return;
+    uint64_t nWords = (idxEnd - idxStart) * wordsPerPoint;
+    int tid = threadIdx.x;
+    if (tid == 0) {   // RNG::Seed, core/rng.cpp:43-55
+        uint32_t s = task * 47u;
+        mt[0] = s;
+        for (int i = 1; i < MT_N; ++i) { s = 1812433253u * (s ^ (s >> 30)) + (uint32_t)i; mt[i] = s; }
+    }
+    __syncthreads();
+    for (uint64_t base = 0; base < nWords; base += MT_N) {
+        // regenerate the table (core/rng.cpp:84-103) in three dependency-free phases
+        uint32_t v = 0;
+        if (tid < 227) v = mtTwist(mt[tid], mt[tid + 1], mt[tid + MT_M]);
+        __syncthreads();
+        if (tid < 227) mt[tid] = v;
+        __syncthreads();
+        if (tid < 227) v = mtTwist(mt[tid + 227], mt[tid + 228], mt[tid]);
+        __syncthreads();
+        if (tid < 227) mt[tid + 227] = v;
+        __syncthreads();
+        if (tid < 169) v = mtTwist(mt[tid + 454], mt[tid + 455], mt[tid + 227]);
+        __syncthreads();
+        if (tid < 169) mt[tid + 454] = v;
+        __syncthreads();
+        if (tid == 0) mt[623] = mtTwist(mt[623], mt[0], mt[396]);
+        __syncthreads();
+        for (int k = tid; k < MT_N; k += 256) {
+            uint64_t w = base + k;
+            if (w < nWords) {
+                uint64_t point = idxStart + w / wordsPerPoint;
+                if (point >= first && point < first + count) {
+                    uint32_t y = mt[k];       // tempering, core/rng.cpp:105-110
+                    y ^= (y >> 11);
+                    y ^= (y << 7) & 0x9d2c5680u;
+                    y ^= (y << 15) & 0xefc60000u;
+                    y ^= (y >> 18);
+                    out[(point - first) * wordsPerPoint + w % wordsPerPoint] = y;
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// core/montecarlo.h:285-301
+__device__ __forceinline__ float vanDerCorput(uint32_t n, uint32_t scramble) {
+    n = __brev(n);
+    n ^= scramble;
+    return fminf(((n >> 8) & 0xffffff) / float(1 << 24), 0.99999994f /* OneMinusEpsilon */);
+}
+__device__ __forceinline__ float sobol2(uint32_t n, uint32_t scramble) {
+    for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+        if (n & 0x1) scramble ^= v;
+    return fminf(((scramble >> 8) & 0xffffff) / float(1 << 24), 0.99999994f);
+}
+
+__device__ inline void coordSys(f3 v1, f3 *v2, f3 *v3) {   // core/geometry.h:564-574
+    if (fabsf(v1.x) > fabsf(v1.y)) {
+        float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z);
+        *v2 = mk3(-v1.z * invLen, 0.f, v1.x * invLen);
+    } else {
+        float invLen = 1.f / sqrtf(v1.y * v1.y + v1.z * v1.z);
+        *v2 = mk3(0.f, v1.z * invLen, -v1.y * invLen);
+    }
+    *v3 = cross3(v1, *v2);
+}
+
+// glibc's sinf/cosf are correctly rounded in all but rare cases; rounding the fp64 result
+// reproduces them far more often than CUDA's 1-2 ulp fp32 versions do.
+__device__ __forceinline__ float cosf_cr(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float sinf_cr(float x) { return (float)sin((double)x); }
+
+// Sphere::Intersect's DifferentialGeometry normal (shapes/sphere.cpp:103-150 +
+// core/diffgeom.cpp:40-55), needed by ShapeSet::Sample (core/light.cpp:156).
+__device__ inline f3 sphereDgNormal(const skc_light &s, f3 phit /*object space, after phi fixups*/, float phi) {
+    (void)phi;
+    float radius = s.radius;
+    float theta = acosf(fminf(fmaxf(phit.z / radius, -1.f), 1.f));
+    float zradius = sqrtf(phit.x * phit.x + phit.y * phit.y);
+    float invzradius = 1.f / zradius;
+    float cosphi = phit.x * invzradius, sinphi = phit.y * invzradius;
+    f3 dpdu = mk3(-s.phiMax * phit.y, s.phiMax * phit.x, 0.f);
+    float dth = s.thetaMax - s.thetaMin;
+    f3 dpdv = mul3(mk3(phit.z * cosphi, phit.z * sinphi, -radius * sinf(theta)), dth);
+    f3 wu = xformVector(s.o2w, dpdu), wv = xformVector(s.o2w, dpdv);
+    return normalize3(cross3(wu, wv));   // orientation flip applied by the caller
+}
+
+// Sphere::Intersect restricted to what light sampling needs: thit and (optionally) dg.nn.
+__device__ inline bool sphereIntersectDg(const skc_light &s, const DRay &r, float *tHit, f3 *nn) {
+    DRay ray;
+    ray.o = xformPoint(s.w2o, r.o);
+    ray.d = xformVector(s.w2o, r.d);
+    ray.mint = r.mint; ray.maxt = r.maxt;
+    float radius = s.radius;
+    float A = ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z;
+    float B = 2 * (ray.d.x * ray.o.x + ray.d.y * ray.o.y + ray.d.z * ray.o.z);
+    float C = ray.o.x * ray.o.x + ray.o.y * ray.o.y + ray.o.z * ray.o.z - radius * radius;
+    float t0, t1;
+    if (!quadratic(A, B, C, &t0, &t1)) return false;
+    if (t0 > ray.maxt || t1 < ray.mint) return false;
+    float thit = t0;
+    if (t0 < ray.mint) { thit = t1; if (thit > ray.maxt) return false; }
+    f3 phit = add3(ray.o, mul3(ray.d, thit));
+    if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+    float phi = atan2f(phit.y, phit.x);
+    if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+    float zmin = s.zmin, zmax = s.zmax, phiMax = s.phiMax;
+    if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) {
+        if (thit == t1) return false;
+        if (t1 > ray.maxt) return false;
+        thit = t1;
+        phit = add3(ray.o, mul3(ray.d, thit));
+        if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+        phi = atan2f(phit.y, phit.x);
+        if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+        if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) return false;
+    }
+    *tHit = thit;
+    if (nn) *nn = sphereDgNormal(s, phit, phi);
+    return true;
+}
+
+// DiffuseAreaLight::Sample_L (lights/diffuse.cpp:69-81) for a one-sphere ShapeSet.
+// Returns false when the sample contributes nothing before the shadow test
+// (multipolesubsurface.cpp:125-126); else wi, pdf and the shadow segment.
+__device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f3 spn, float u1, float u2,
+                                         f3 *wiOut, float *pdfOut, DRay *shadow) {
+    f3 Pcenter = xformPoint(L.o2w, mk3(0.f, 0.f, 0.f));
+    float radius = L.radius;
+    bool reverse = L.reverseOrientation != 0.f;
+    f3 pt, ns;
+    float dc2 = dist2(p, Pcenter);
+    bool inside = dc2 - radius * radius < 1e-4f;
+    if (inside) {
+        // Sphere::Sample(u1,u2,ns) (sphere.cpp:229-234): uniform over the sphere
+        float z = 1.f - 2.f * u1;
+        float rr = sqrtf(fmaxf(0.f, 1.f - z * z));
+        float phi = (float)((double)(2.f) * SKC_PI_D * (double)u2);
+        f3 po = mk3(radius * (rr * cosf_cr(phi)), radius * (rr * sinf_cr(phi)), radius * z);
+        ns = normalize3(xformNormal(L.w2o, po));
+        if (reverse) ns = mul3(ns, -1.f);
+        pt = xformPoint(L.o2w, po);
+    } else {
+        f3 wc = normalize3(sub3(Pcenter, p));
+        f3 wcX, wcY;
+        coordSys(wc, &wcX, &wcY);
+        float sinThetaMax2 = radius * radius / dc2;
+        float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+        // UniformSampleCone (core/montecarlo.cpp:413-420)
+        float costheta = (1.f - u1) * cosThetaMax + u1 * 1.f;
+        float sintheta = sqrtf(1.f - costheta * costheta);
+        float phi = (float)((double)(u2 * 2.f) * SKC_PI_D);
+        f3 dir = add3(add3(mul3(wcX, cosf_cr(phi) * sintheta), mul3(wcY, sinf_cr(phi) * sintheta)), mul3(wc, costheta));
+        DRay r; r.o = p; r.d = dir; r.mint = 1e-3f; r.maxt = INFINITY;
+        float thit;
+        if (!sphereIntersectDg(L, r, &thit, nullptr)) thit = dot3(sub3(Pcenter, p), normalize3(r.d));
+        pt = add3(r.o, mul3(r.d, thit));
+        ns = normalize3(sub3(pt, Pcenter));
+        if (reverse) ns = mul3(ns, -1.f);
+    }
+    // ShapeSet::Sample (core/light.cpp:145-158): re-intersect p -> pt with the shape set
+    DRay r2; r2.o = p; r2.d = sub3(pt, p); r2.mint = 1e-3f; r2.maxt = INFINITY;
+    float thit = 1.f, th; f3 nn;
+    if (sphereIntersectDg(L, r2, &th, &nn)) { thit = th; if (reverse) nn = mul3(nn, -1.f); ns = nn; }
+    f3 ps = add3(r2.o, mul3(r2.d, thit));
+    f3 wi = normalize3(sub3(ps, p));
+    // ShapeSet::Pdf (light.cpp:161-166) with one shape: area * pdf / sumArea
+    float area = L.phiMax * radius * (L.zmax - L.zmin);
+    float spdf;
+    if (inside) {
+        // Shape::Pdf(p, wi) (core/shape.cpp): intersect and convert the area measure
+        DRay r3; r3.o = p; r3.d = wi; r3.mint = 1e-3f; r3.maxt = INFINITY;
+        float t3; f3 n3;
+        if (!sphereIntersectDg(L, r3, &t3, &n3)) spdf = 0.f;
+        else {
+            f3 ph = add3(r3.o, mul3(r3.d, t3));
+            spdf = dist2(p, ph) / (fabsf(dot3(n3, mul3(wi, -1.f))) * area);
+            if (isinf(spdf)) spdf = 0.f;
+        }
+    } else {
+        float sinThetaMax2 = radius * radius / dc2;
+        float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+        spdf = (float)(1.0 / ((double)2.f * SKC_PI_D * (double)(1.f - cosThetaMax)));   // UniformConePdf
+    }
+    float pdf = 0.f + area * spdf;
+    pdf = pdf / area;
+    // VisibilityTester::SetSegment (core/light.h:87-92)
+    float dist = len3(sub3(p, ps));
+    float invd = 1.f / dist;
+    shadow->o = p; shadow->d = mul3(sub3(ps, p), invd); shadow->mint = pEps; shadow->maxt = dist * (1.f - 1e-3f);
+    // L(ps, ns, -wi): lights/diffuse.h:51-53
+    bool lit = dot3(ns, mul3(wi, -1.f)) > 0.f;
+    *wiOut = wi; *pdfOut = pdf;
+    if (dot3(wi, spn) <= 0.f) return false;
+    if (!lit || pdf == 0.f) return false;
+    return true;
+}
+
+#define IRR_BLOCK 128
+#define IRR_CHUNK 8      // light samples handled per transposition pass
+
+// shared: per thread IRR_CHUNK x {costheta, pdf}
+__global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_light *__restrict__ lights, uint32_t nLights,
+        const skc_surface_point *__restrict__ pts, uint64_t count, const uint32_t *__restrict__ scr,
+        const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
+        float4 *__restrict__ posArea, float *__restrict__ Eout, uint64_t outBase, unsigned long long *cnt) {
+    __shared__ float sCos[IRR_BLOCK][IRR_CHUNK + 1];
+    __shared__ float sPdf[IRR_BLOCK][IRR_CHUNK + 1];
+    uint64_t i = (uint64_t)blockIdx.x * IRR_BLOCK + threadIdx.x;
+    int lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31;
+    bool live = i < count;
+    f3 p = mk3(0, 0, 0), n = mk3(0, 0, 1);
+    float eps = 0.f, area = 0.f;
+    if (live) {
+        const float *sp = reinterpret_cast<const float *>(pts + i);
+        p = mk3(__ldg(sp), __ldg(sp + 1), __ldg(sp + 2));
+        n = mk3(__ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
+        area = __ldg(sp + 9); eps = __ldg(sp + 10);
+    }
+    // transposed accumulators: lane = wavelength, register k = point k of this warp
+    float E[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) E[k] = 0.f;
+    for (uint32_t j = 0; j < nLights; ++j) {
+        const skc_light &L = lights[j];
+        int ns = (int)L.nSamples;
+        uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2
+        uint32_t s0 = 0, s1 = 0, sc = 0;
+        if (live) { const uint32_t *w = scr + (i * nLights + j) * 3; s0 = __ldg(w); s1 = __ldg(w + 1); sc = __ldg(w + 2); }
+        (void)sc;   // uComponent picks the shape of a ShapeSet; one sphere -> always shape 0
+        float Lc = lane < SKC_NS ? __ldg(&L.Lemit[lane]) : 0.f;
+        float El[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) El[k] = 0.f;
+        for (uint32_t sBase = 0; sBase < nS; sBase += IRR_CHUNK) {
+            uint32_t chunk = min((uint32_t)IRR_CHUNK, nS - sBase);
+            for (uint32_t c = 0; c < chunk; ++c) {
+                float cosT = 0.f, pdf = 0.f;
+                if (live) {
+                    uint32_t s = sBase + c;
+                    float u0 = vanDerCorput(s, s0), u1 = sobol2(s, s1);
+                    f3 wi; float lp; DRay sh;
+                    if (sampleSphereLight(L, p, eps, n, u0, u1, &wi, &lp, &sh)) {
+                        bool occ = cnt ? bvhOccluded<true>(bv, sh, cnt) : bvhOccluded<false>(bv, sh, nullptr);
+                        if (!occ) { cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp; }
+                    }
+                }
+                sCos[threadIdx.x][c] = cosT; sPdf[threadIdx.x][c] = pdf;
+            }
+            __syncwarp();
+            if (lane < SKC_NS) {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) {
+                    for (uint32_t c = 0; c < chunk; ++c) {
+                        float pdf = sPdf[warpBase + k][c];
+                        if (pdf != 0.f) {
+                            float cosT = sCos[warpBase + k][c];
+                            // MultipoleBSSRDFData::rho (core/multipole.cpp:458-463)
+                            float fid = cosT * (float)(SKC_RHO_LEN - 1);
+                            int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
+                            float lerp = fid - (float)id;
+                            float r0 = __ldg(&rhoHd[id * SKC_EPAD + lane]), r1 = __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
+                            float rho = (1.f - lerp) * r0 + lerp * r1;
+                            float Ft = 1.f - rho;
+                            El[k] += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int k = 0; k < 32; ++k) E[k] += El[k] / (float)(int)nS;      // :136
+    }
+    // write: lane = wavelength, coalesced 128 B row per point; lanes 30,31 write the zero pad
+    uint64_t warpFirst = (uint64_t)blockIdx.x * IRR_BLOCK + warpBase;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+        uint64_t pi = warpFirst + k;
+        if (pi < count) {
+            float e = lane < SKC_NS ? E[k] : 0.f;
+            if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
+            Eout[(outBase + pi) * SKC_EPAD + lane] = e;
+        }
+    }
+    if (live) posArea[outBase + i] = make_float4(p.x, p.y, p.z, area);
+}
+
+// AoS export of the device point set (IrradiancePoint records for the host / the oracle)
+__global__ void k_export_points(const skc_surface_point *__restrict__ pts, const float *__restrict__ E, uint64_t base,
+                                uint64_t count, skc_irr_point *__restrict__ out) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t i = t >> 5; int lane = t & 31;
+    if (i >= count) return;
+    float *o = reinterpret_cast<float *>(out + i);
+    const float *sp = reinterpret_cast<const float *>(pts + i);
+    if (lane < 6) o[lane] = sp[lane];
+    if (lane < SKC_NS) o[6 + lane] = E[(base + i) * SKC_EPAD + lane];
+    if (lane == 30) o[36] = sp[9];
+    if (lane == 31) o[37] = sp[10];
+}
+
+__global__ void k_import_points(const skc_irr_point *__restrict__ in, uint64_t count, float4 *__restrict__ posArea, float *__restrict__ E) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t i = t >> 5; int lane = t & 31;
+    if (i >= count) return;
+    const float *s = reinterpret_cast<const float *>(in + i);
+    E[i * SKC_EPAD + lane] = lane < SKC_NS ? s[6 + lane] : 0.f;
+    if (lane == 0) posArea[i] = make_float4(s[0], s[1], s[2], s[36]);
+}
+
+int skc_ensure_points(skc_ctx *ctx, uint64_t n) {
+    if (ctx->ipCap >= n && ctx->ipPosArea) return 0;
+    float4 *pa = nullptr; float *e = nullptr;
+    SKC_CUDA(cudaMalloc((void **)&pa, n * sizeof(float4)));
+    SKC_CUDA(cudaMalloc((void **)&e, n * SKC_EPAD * sizeof(float)));
+    if (ctx->ipPosArea && ctx->ipCount) {
+        uint64_t keep = ctx->ipCount < n ? ctx->ipCount : n;
+        SKC_CUDA(cudaMemcpyAsync(pa, ctx->ipPosArea, keep * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+        SKC_CUDA(cudaMemcpyAsync(e, ctx->ipE, keep * SKC_EPAD * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    if (ctx->ipPosArea) cudaFree(ctx->ipPosArea);
+    if (ctx->ipE) cudaFree(ctx->ipE);
+    ctx->ipPosArea = pa; ctx->ipE = e; ctx->ipCap = n;
+    return 0;
+}
+
+extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t nLights) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (ctx->lights) { cudaFree(ctx->lights); ctx->lights = nullptr; }
+    ctx->nLights = 0;
+    if (!nLights) return 0;
+    SKC_CUDA(cudaMalloc((void **)&ctx->lights, nLights * sizeof(skc_light)));
+    SKC_CUDA(cudaMemcpyAsync(ctx->lights, lights, nLights * sizeof(skc_light), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->nLights = nLights;
+    return 0;
+}
+
+extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal,
+                              uint64_t first, uint64_t count, uint32_t nTasks, float mix,
+                              const float *albedo30, skc_irr_point *out) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->bvhNodes) return skc_fail(ctx, "skc_irradiance: no BVH uploaded");
+    if (!ctx->nLights) return skc_fail(ctx, "skc_irradiance: no lights uploaded");
+    if (!ctx->rhoHd) return skc_fail(ctx, "skc_irradiance: no rho table uploaded (skc_upload_profile)");
+    if (first + count > nTotal || !nTasks) return skc_fail(ctx, "skc_irradiance: bad range");
+    if (nTotal > 0x7fffffffull) return skc_fail(ctx, "skc_irradiance: the reference's int slice arithmetic caps the point count at 2^31-1");
+    if (skc_ensure_points(ctx, nTotal)) return 1;
+    if (ctx->ipCount < nTotal) ctx->ipCount = nTotal;
+    if (!count) return 0;
+    uint32_t wpp = 3 * ctx->nLights;
+    skc_surface_point *dPts = (skc_surface_point *)skc_scratch(ctx, 0, count * sizeof(skc_surface_point));
+    uint32_t *dScr = (uint32_t *)skc_scratch(ctx, 1, count * wpp * sizeof(uint32_t));
+    if (!dPts || !dScr) return 1;
+    float *dAlb = nullptr;
+    if (albedo30) {
+        dAlb = (float *)skc_scratch(ctx, 2, count * SKC_NS * sizeof(float));
+        if (!dAlb) return 1;
+        SKC_CUDA(cudaMemcpyAsync(dAlb, albedo30, count * SKC_NS * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    SKC_CUDA(cudaMemcpyAsync(dPts, points + first, count * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
+    // tasks overlapping [first, first+count): slice t covers [t*N/nT, (t+1)*N/nT)
+    uint32_t t0 = 0, t1 = nTasks - 1;
+    {
+        // smallest t whose end > first ; largest t whose start < first+count
+        uint64_t lo = 0, hi = nTasks - 1;
+        while (lo < hi) { uint64_t m = (lo + hi) / 2; if ((m + 1) * nTotal / nTasks > first) hi = m; else lo = m + 1; }
+        t0 = (uint32_t)lo;
+        lo = 0; hi = nTasks - 1;
+        while (lo < hi) { uint64_t m = (lo + hi + 1) / 2; if (m * nTotal / nTasks < first + count) lo = m; else hi = m - 1; }
+        t1 = (uint32_t)lo;
+    }
+    skc_stage_begin(ctx);
+    k_scrambles<<<t1 - t0 + 1, 256, 0, ctx->stream>>>(t0, nTasks, nTotal, first, count, wpp, dScr);
+    SKC_LAUNCHED("k_scrambles");
+    skc_stage_end(ctx, 0);
+    skc_stage_begin(ctx);
+    uint64_t blocks = (count + IRR_BLOCK - 1) / IRR_BLOCK;
+    k_irradiance<<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
+                                                                  ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, nullptr);
+    SKC_LAUNCHED("k_irradiance");
+    skc_stage_end(ctx, 1);
+    if (out) {
+        skc_irr_point *dOut = (skc_irr_point *)skc_scratch(ctx, 3, count * sizeof(skc_irr_point));
+        if (!dOut) return 1;
+        uint64_t threads = count * 32;
+        k_export_points<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dPts, ctx->ipE, first, count, dOut);
+        SKC_LAUNCHED("k_export_points");
+        SKC_CUDA(cudaMemcpyAsync(out, dOut, count * sizeof(skc_irr_point), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int skc_set_irradiance_points(skc_ctx *ctx, const skc_irr_point *pts, uint64_t n) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    ctx->ipCount = 0;
+    if (!n) return 0;
+    if (skc_ensure_points(ctx, n)) return 1;
+    skc_irr_point *d = (skc_irr_point *)skc_scratch(ctx, 3, n * sizeof(skc_irr_point));
+    if (!d) return 1;
+    SKC_CUDA(cudaMemcpyAsync(d, pts, n * sizeof(skc_irr_point), cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t threads = n * 32;
+    k_import_points<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(d, n, ctx->ipPosArea, ctx->ipE);
+    SKC_LAUNCHED("k_import_points");
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->ipCount = n;
+    return 0;
+}
+
+extern "C" int skc_irradiance_dev(skc_ctx *ctx, uint64_t nTotal, void **posArea_dev, void **E_dev) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (skc_ensure_points(ctx, nTotal)) return 1;
+    if (ctx->ipCount < nTotal) ctx->ipCount = nTotal;
+    if (posArea_dev) *posArea_dev = ctx->ipPosArea;
+    if (E_dev) *E_dev = ctx->ipE;
+    return 0;
+}

@@ -1,0 +1,311 @@
+// skc_mo.cu -- SubsurfaceOctreeNode::Mo and the subsurface term of Li on the device.
+//
+// Reference: integrators/diffusionutil.h:175-210 (Mo), core/geometry.h:449-453 (Inside,
+// inclusive), core/multipole.cpp:60-83,103-113 (sampleProfile: Rd table lerp, one table and
+// one rcpDsqSpacing per wavelength), :458-463 (rho_hd), integrators/multipolesubsurface.cpp
+// :253-304 (Li).
+//
+// One warp per shading point.  Traversal is warp-cooperative: up to 32 pending entries
+// (octree nodes, or single irradiance points of an opened leaf) are popped from a per-warp
+// shared-memory stack and classified one per lane with the reference's own tests
+//     black -> drop;  dw = sumArea / d2;  (dw < maxError && !Inside) -> cluster contribution
+//     else leaf -> its points;  else -> its children
+// and the ballots of the classification drive (a) a shuffle-compacted push of the children
+// and (b) the spectral accumulation, where the warp turns round: lane = wavelength, so a
+// contribution costs one coalesced 120 B row (Et or E) and one 8 B table pair per lane.
+//
+// Exact-zero culling (not in the reference, results identical): Rd is 0 for every
+// wavelength once d2 * min(rcpDsqSpacing) >= len-1, so contributions beyond that range are
+// skipped, and so are subtrees whose box lies entirely beyond it.
+#include <vector>
+#include "skc_internal.h"
+
+#define MO_WARPS 4
+#define MO_STACK 1024
+#define MO_HIGH 256
+#define MO_POINT 0x80000000u
+
+struct MoTables {
+    const float2 *pairs;     // [30][len] {data[i], data[i+1]}
+    const float *rcp;        // [32] rcpDsqSpacing per wavelength
+    uint32_t len;
+    float rcpMin;            // smallest rcpDsqSpacing (longest table in d2)
+    float lenM1;             // (float)(len-1)
+};
+
+struct MoTree {
+    const float4 *nodes;     // 3 per node
+    const float *Et;         // [nodes][32]
+    const float4 *leafPosArea;
+    const float *leafE;      // [points][32]
+};
+
+// sampleProfile (core/multipole.cpp:60-73).  d2*rcp is an fp32 product there too (the
+// promotion to double happens after the multiply); the compare against size-1 and the
+// fractional part are exact in fp32 for len < 2^24.
+__device__ __forceinline__ float sampleRd(const MoTables &T, int lambda, float rcp, float d2) {
+    float f = d2 * rcp;
+    if (f >= T.lenM1) return 0.f;
+    uint32_t seg = (uint32_t)f;
+    float t = f - (float)seg;
+    float2 v = __ldg(&T.pairs[(size_t)lambda * T.len + seg]);
+    return (1.f - t) * v.x + t * v.y;
+}
+
+__device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float px, float py, float pz,
+                                      float maxError, uint32_t *stack, int lane, float &acc) {
+    const float rcp = __ldg(&T.rcp[lane]);
+    const int lam = lane < SKC_NS ? lane : 0;
+    int sp = 0;
+    if (lane == 0) stack[0] = 0u;
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+        int take = sp >= MO_HIGH ? 1 : min(sp, 32);
+        sp -= take;
+        uint32_t entry = lane < take ? stack[sp + lane] : 0u;
+        __syncwarp();
+        // ---- classify: one entry per lane
+        bool contrib = false;      // adds Rd(d2) * row * scale
+        uint32_t rowIdx = 0; float d2 = 0.f, scale = 1.f;
+        uint32_t pushFirst = 0, pushCount = 0;   // entries this lane pushes
+        bool pushPoints = false;
+        if (lane < take) {
+            if (entry & MO_POINT) {
+                uint32_t slot = entry & ~MO_POINT;
+                float4 pa = __ldg(&tr.leafPosArea[slot]);
+                float dx = px - pa.x, dy = py - pa.y, dz = pz - pa.z;
+                d2 = dx * dx + dy * dy + dz * dz;
+                if (d2 * T.rcpMin < T.lenM1) { contrib = true; rowIdx = slot | MO_POINT; scale = pa.w; }
+            } else {
+                const float4 *nd = tr.nodes + 3 * (size_t)entry;
+                float4 g = __ldg(nd), b0 = __ldg(nd + 1), b1 = __ldg(nd + 2);
+                uint32_t w0 = __float_as_uint(b1.z), w1 = __float_as_uint(b1.w);
+                if (!(w1 & SKC_OT_BLACK)) {
+                    float dx = px - g.x, dy = py - g.y, dz = pz - g.z;
+                    d2 = dx * dx + dy * dy + dz * dz;
+                    float dw = g.w / d2;
+                    bool inside = px >= b0.x && px <= b0.w && py >= b0.y && py <= b1.x && pz >= b0.z && pz <= b1.y;
+                    if (dw < maxError && !inside) {
+                        if (d2 * T.rcpMin < T.lenM1) { contrib = true; rowIdx = entry; scale = 1.f; }
+                    } else {
+                        // distance from pt to the cell: beyond the table range nothing below contributes
+                        float ex = fmaxf(fmaxf(b0.x - px, px - b0.w), 0.f);
+                        float ey = fmaxf(fmaxf(b0.y - py, py - b1.x), 0.f);
+                        float ez = fmaxf(fmaxf(b0.z - pz, pz - b1.y), 0.f);
+                        float db2 = ex * ex + ey * ey + ez * ez;
+                        if ((db2 * 0.999f) * T.rcpMin < T.lenM1) {
+                            if (w1 & SKC_OT_LEAF) { pushFirst = w0; pushCount = w1 & 0xffu; pushPoints = true; }
+                            else { pushFirst = w0; pushCount = __popc(w1 & 0xffu); }
+                        }
+                    }
+                }
+            }
+        }
+        // ---- push children / leaf points (exclusive scan of pushCount over lanes)
+        uint32_t incl = pushCount;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        uint32_t off = sp + incl - pushCount;
+        for (uint32_t k = 0; k < pushCount; ++k) stack[off + k] = (pushFirst + k) | (pushPoints ? MO_POINT : 0u);
+        sp += (int)total;
+        // ---- spectral accumulation: lane = wavelength
+        unsigned cm = __ballot_sync(0xffffffffu, contrib);
+        while (cm) {
+            int src = __ffs(cm) - 1; cm &= cm - 1;
+            uint32_t r = __shfl_sync(0xffffffffu, rowIdx, src);
+            float dd = __shfl_sync(0xffffffffu, d2, src);
+            float sc = __shfl_sync(0xffffffffu, scale, src);
+            const float *row = (r & MO_POINT) ? tr.leafE + (size_t)(r & ~MO_POINT) * SKC_EPAD : tr.Et + (size_t)r * SKC_EPAD;
+            float e = __ldg(&row[lane]);
+            float rd = sampleRd(T, lam, rcp, dd);
+            acc += (rd * e) * sc;          // diffusionutil.h:186 / :197
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+                                                     const int32_t *__restrict__ enable, uint64_t enableStrideInts,
+                                                     uint64_t n, float maxError, float *__restrict__ Mo) {
+    __shared__ uint32_t stacks[MO_WARPS][MO_STACK];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t nWarps = (uint64_t)gridDim.x * MO_WARPS;
+    for (uint64_t h = (uint64_t)blockIdx.x * MO_WARPS + warp; h < n; h += nWarps) {
+        float acc = 0.f;
+        bool on = enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true;
+        if (on) {
+            const float *pp = p3 + h * strideFloats;
+            float px = __ldg(pp), py = __ldg(pp + 1), pz = __ldg(pp + 2);
+            moOne(tr, T, px, py, pz, maxError, stacks[warp], lane, acc);
+        }
+        Mo[h * SKC_EPAD + lane] = lane < SKC_NS ? acc : 0.f;
+    }
+}
+
+// Li subsurface term (multipolesubsurface.cpp:279-287); one warp per hit, lane = wavelength
+__global__ void k_li_sss(const skc_hit *__restrict__ hits, uint64_t n, const float *__restrict__ Mo, const float *__restrict__ rhoHd,
+                         const float *__restrict__ albedo, float mix, float *__restrict__ L) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t h = t >> 5; int lane = t & 31;
+    if (h >= n) return;
+    const float *hp = reinterpret_cast<const float *>(hits + h);
+    int hasB = __float_as_int(__ldg(hp + 13));
+    float out = 0.f;
+    if (hasB && lane < SKC_NS) {
+        f3 nn = mk3(__ldg(hp + 7), __ldg(hp + 8), __ldg(hp + 9)), wo = mk3(__ldg(hp + 10), __ldg(hp + 11), __ldg(hp + 12));
+        float costheta = fminf(fabsf(dot3(wo, nn)), 1.f);
+        float fid = costheta * (float)(SKC_RHO_LEN - 1);
+        int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
+        float lerp = fid - (float)id;
+        float rho = (1.f - lerp) * __ldg(&rhoHd[id * SKC_EPAD + lane]) + lerp * __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
+        float Ft = 1.f - rho;
+        float a = 1.f;
+        if (albedo) a = (float)pow((double)__ldg(&albedo[h * SKC_NS + lane]), (double)(1.f - mix));
+        float v = ((0.31830988618379067154f * Ft) * Mo[h * SKC_EPAD + lane]) * a;
+        out = fmaxf(v, 0.f);       // Spectrum::Clamp(0)
+    }
+    if (lane < SKC_NS) L[h * SKC_NS + lane] = out;
+}
+
+__global__ void k_unpad(const float *__restrict__ in, uint64_t n, float *__restrict__ out) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t h = t >> 5; int lane = t & 31;
+    if (h < n && lane < SKC_NS) out[h * SKC_NS + lane] = in[h * SKC_EPAD + lane];
+}
+
+// ---- host side ------------------------------------------------------------------------------
+extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float *rcpDsqSpacing, uint32_t len, const float *rhoHd) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (table) {
+        if (len < 2 || len >= (1u << 24)) return skc_fail(ctx, "skc_upload_profile: table length %u out of range", len);
+        std::vector<float2> pairs((size_t)SKC_NS * len);
+        for (int l = 0; l < SKC_NS; ++l)
+            for (uint32_t i = 0; i < len; ++i)
+                pairs[(size_t)l * len + i] = make_float2(table[(size_t)l * len + i], i + 1 < len ? table[(size_t)l * len + i + 1] : 0.f);
+        float rcp[32]; float rmin = INFINITY;
+        for (int l = 0; l < 32; ++l) { rcp[l] = l < SKC_NS ? rcpDsqSpacing[l] : rcpDsqSpacing[SKC_NS - 1]; if (l < SKC_NS) rmin = fminf(rmin, rcp[l]); }
+        if (ctx->profPairs) cudaFree(ctx->profPairs);
+        if (ctx->profRcp) cudaFree(ctx->profRcp);
+        ctx->profPairs = nullptr; ctx->profRcp = nullptr;
+        SKC_CUDA(cudaMalloc((void **)&ctx->profPairs, pairs.size() * sizeof(float2)));
+        SKC_CUDA(cudaMalloc((void **)&ctx->profRcp, sizeof rcp));
+        SKC_CUDA(cudaMemcpyAsync(ctx->profPairs, pairs.data(), pairs.size() * sizeof(float2), cudaMemcpyHostToDevice, ctx->stream));
+        SKC_CUDA(cudaMemcpyAsync(ctx->profRcp, rcp, sizeof rcp, cudaMemcpyHostToDevice, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->profLen = len; ctx->profMaxD2 = rmin;   // rmin kept here: smallest rcpDsqSpacing
+    }
+    if (rhoHd) {
+        std::vector<float> pad((size_t)SKC_RHO_LEN * SKC_EPAD, 0.f);
+        for (int i = 0; i < SKC_RHO_LEN; ++i)
+            for (int l = 0; l < SKC_NS; ++l) pad[(size_t)i * SKC_EPAD + l] = rhoHd[(size_t)i * SKC_NS + l];
+        if (ctx->rhoHd) cudaFree(ctx->rhoHd);
+        ctx->rhoHd = nullptr;
+        SKC_CUDA(cudaMalloc((void **)&ctx->rhoHd, pad.size() * sizeof(float)));
+        SKC_CUDA(cudaMemcpyAsync(ctx->rhoHd, pad.data(), pad.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return 0;
+}
+
+static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride,
+                    uint64_t n, float maxError, float *MoDev) {
+    if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo: no octree built (skc_build_octree)");
+    if (!ctx->profPairs) return skc_fail(ctx, "skc_mo: no profile table uploaded (skc_upload_profile)");
+    if (!n) return 0;
+    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
+    MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
+    uint64_t blocks = (n + MO_WARPS - 1) / MO_WARPS;
+    uint64_t maxBlocks = 148ull * 16ull;
+    if (blocks > maxBlocks) blocks = maxBlocks;
+    k_mo<<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev);
+    SKC_LAUNCHED("k_mo");
+    return 0;
+}
+
+int skc_mo_dev(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, uint64_t n, float maxError, float *MoDev) {
+    return moLaunch(ctx, p3Dev, strideFloats, nullptr, 0, n, maxError, MoDev);
+}
+
+extern "C" int skc_mo(skc_ctx *ctx, const float *p3, uint64_t n, float maxError, float *Mo30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    float *dP = (float *)skc_scratch(ctx, 0, n * 3 * sizeof(float));
+    float *dMo = (float *)skc_scratch(ctx, 1, n * SKC_EPAD * sizeof(float));
+    float *dOut = (float *)skc_scratch(ctx, 2, n * SKC_NS * sizeof(float));
+    if (!dP || !dMo || !dOut) return 1;
+    SKC_CUDA(cudaMemcpyAsync(dP, p3, n * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    skc_stage_begin(ctx);
+    if (moLaunch(ctx, dP, 3, nullptr, 0, n, maxError, dMo)) return 1;
+    skc_stage_end(ctx, 4);
+    uint64_t threads = n * 32;
+    k_unpad<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dMo, n, dOut);
+    SKC_LAUNCHED("k_unpad");
+    SKC_CUDA(cudaMemcpyAsync(Mo30, dOut, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// hits on the device -> Mo (padded, scratch 1) -> L (scratch 2); shared by li_sss and camera_pass
+static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, const float *albedo30,
+                 float *Mo30, float *L30) {
+    float *dMo = (float *)skc_scratch(ctx, 4, n * SKC_EPAD * sizeof(float));
+    float *dL = (float *)skc_scratch(ctx, 2, n * SKC_NS * sizeof(float));
+    if (!dMo || !dL) return 1;
+    if (!ctx->rhoHd) return skc_fail(ctx, "skc_li_sss: no rho table uploaded (skc_upload_profile)");
+    float *dAlb = nullptr;
+    if (albedo30) {
+        dAlb = (float *)skc_scratch(ctx, 3, n * SKC_NS * sizeof(float));
+        if (!dAlb) return 1;
+        SKC_CUDA(cudaMemcpyAsync(dAlb, albedo30, n * SKC_NS * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    skc_stage_begin(ctx);
+    // p at float offset 4, hasBssrdf at int offset 13 of the 14-word hit record
+    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, dMo)) return 1;
+    skc_stage_end(ctx, 4);
+    uint64_t threads = n * 32;
+    if (L30) {
+        k_li_sss<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dHits, n, dMo, ctx->rhoHd, dAlb, mix, dL);
+        SKC_LAUNCHED("k_li_sss");
+        SKC_CUDA(cudaMemcpyAsync(L30, dL, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (Mo30) {
+        float *dOut = (float *)skc_scratch(ctx, 5, n * SKC_NS * sizeof(float));
+        if (!dOut) return 1;
+        k_unpad<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dMo, n, dOut);
+        SKC_LAUNCHED("k_unpad");
+        SKC_CUDA(cudaMemcpyAsync(Mo30, dOut, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float maxError, float mix,
+                          const float *albedo30, float *Mo30, float *L30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 1, n * sizeof(skc_hit));
+    if (!dHits) return 1;
+    SKC_CUDA(cudaMemcpyAsync(dHits, hits, n * sizeof(skc_hit), cudaMemcpyHostToDevice, ctx->stream));
+    return liDev(ctx, dHits, n, maxError, mix, albedo30, Mo30, L30);
+}
+
+extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxError, float mix,
+                               skc_hit *hitsOut, float *L30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    skc_ray *dRays = (skc_ray *)skc_scratch(ctx, 0, n * sizeof(skc_ray));
+    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 1, n * sizeof(skc_hit));
+    if (!dRays || !dHits) return 1;
+    SKC_CUDA(cudaMemcpyAsync(dRays, rays, n * sizeof(skc_ray), cudaMemcpyHostToDevice, ctx->stream));
+    skc_stage_begin(ctx);
+    if (skc_trace_closest_dev(ctx, dRays, n, dHits, nullptr)) return 1;
+    skc_stage_end(ctx, 3);
+    if (hitsOut) SKC_CUDA(cudaMemcpyAsync(hitsOut, dHits, n * sizeof(skc_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    return liDev(ctx, dHits, n, maxError, mix, nullptr, nullptr, L30);
+}
