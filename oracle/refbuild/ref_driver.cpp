@@ -302,7 +302,14 @@ static void dumpBVH(const std::string &dir, const Scene *scene, Meta &meta,
     uint32_t nNodes = countNodes(nodes, 0);
     dump(dir + "/bvh_nodes.bin", nodes, nNodes);
     std::vector<DrvPrim> prims;
+    // sphere index = light number (the emitter shapes are the only quadrics in these scenes)
     std::vector<const Sphere *> spheres;
+    for (const Light *l : scene->lights) {
+        const DiffuseAreaLight *dl = dynamic_cast<const DiffuseAreaLight *>(l);
+        if (dl && dl->shapeSet->shapes.size() == 1)
+            spheres.push_back(dynamic_cast<const Sphere *>(dl->shapeSet->shapes[0].GetPtr()));
+        else spheres.push_back(NULL);
+    }
     for (auto &pr : bvh->primitives) {
         const GeometricPrimitive *gp = dynamic_cast<const GeometricPrimitive *>(pr.GetPtr());
         if (!gp) { fprintf(stderr, "non-geometric primitive in BVH\n"); exit(2); }
@@ -315,7 +322,7 @@ static void dumpBVH(const std::string &dir, const Scene *scene, Meta &meta,
             dp.type = 0; dp.mesh = (int32_t)mi; dp.index = (int32_t)((tri->v - m->vertexIndex) / 3);
         } else if (const Sphere *sp = dynamic_cast<const Sphere *>(sh)) {
             size_t si = std::find(spheres.begin(), spheres.end(), sp) - spheres.begin();
-            if (si == spheres.size()) spheres.push_back(sp);
+            if (si == spheres.size()) { fprintf(stderr, "sphere primitive is not a light shape\n"); exit(2); }
             dp.type = 1; dp.mesh = -1; dp.index = (int32_t)si;
         } else { fprintf(stderr, "unsupported shape in BVH\n"); exit(2); }
         prims.push_back(dp);

@@ -1,0 +1,211 @@
+"""ctypes binding of include/skin_cuda.h (libskincuda.so).  Plumbing only -- see __init__."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+# record layouts of include/skin_cuda.h
+DT_BVH_NODE = np.dtype([("pmin", "<f4", 3), ("pmax", "<f4", 3), ("offset", "<u4"), ("nPrimitives", "u1"), ("axis", "u1"), ("pad", "u1", 2)])
+DT_PRIM = np.dtype([("type", "<i4"), ("mesh", "<i4"), ("index", "<i4"), ("primitiveId", "<i4")])
+DT_LIGHT = np.dtype([("o2w", "<f4", 16), ("w2o", "<f4", 16), ("radius", "<f4"), ("zmin", "<f4"), ("zmax", "<f4"), ("phiMax", "<f4"),
+                     ("nSamples", "<f4"), ("reverseOrientation", "<f4"), ("thetaMin", "<f4"), ("thetaMax", "<f4"), ("Lemit", "<f4", 30)])
+DT_RAY = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("mint", "<f4"), ("maxt", "<f4")])
+DT_HIT = np.dtype([("hit", "<i4"), ("prim", "<i4"), ("t", "<f4"), ("rayEpsilon", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("wo", "<f4", 3), ("hasBssrdf", "<i4")])
+DT_SURFACE_POINT = np.dtype([("p", "<f4", 3), ("n", "<f4", 3), ("u", "<f4"), ("v", "<f4"), ("materialId", "<u4"), ("area", "<f4"), ("rayEpsilon", "<f4")])
+DT_IRR_POINT = np.dtype([("p", "<f4", 3), ("n", "<f4", 3), ("E", "<f4", 30), ("area", "<f4"), ("rayEpsilon", "<f4")])
+DT_LAYER = np.dtype([("ior", "<f4"), ("thickness", "<f4"), ("mua", "<f4"), ("musp", "<f4"), ("g_HG", "<f4")])
+DT_MPC_OPTIONS = np.dtype([("desiredStepSize", "<f4"), ("desiredLength", "<u4"), ("lerpOnThinSlab", "<i4")])
+assert DT_BVH_NODE.itemsize == 32 and DT_LIGHT.itemsize == 280 and DT_RAY.itemsize == 32 and DT_HIT.itemsize == 56
+assert DT_SURFACE_POINT.itemsize == 44 and DT_IRR_POINT.itemsize == 152
+
+STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6}
+
+# every symbol include/skin_cuda.h declares
+SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
+           "skc_upload_bvh", "skc_trace_any", "skc_trace_closest", "skc_upload_profile", "skc_upload_lights",
+           "skc_irradiance", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
+           "skc_li_sss", "skc_camera_pass", "skc_profile_batch"]
+
+
+class SkcError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "libskincuda.so")
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libskincuda.so and declare prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise SkcError("%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
+                       "There is no CPU fallback." % path)
+    lib = C.CDLL(path)
+    vp, u64, u32, i32, f32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_float
+    lib.skc_create.restype = vp; lib.skc_create.argtypes = [i32]
+    lib.skc_destroy.restype = None; lib.skc_destroy.argtypes = [vp]
+    lib.skc_last_error.restype = C.c_char_p; lib.skc_last_error.argtypes = [vp]
+    lib.skc_synchronize.restype = i32; lib.skc_synchronize.argtypes = [vp]
+    lib.skc_launch_count.restype = u64; lib.skc_launch_count.argtypes = [vp]
+    lib.skc_stage_ms.restype = f32; lib.skc_stage_ms.argtypes = [vp, i32]
+    lib.skc_upload_bvh.restype = i32
+    lib.skc_upload_bvh.argtypes = [vp, vp, u32, vp, u32, vp, vp, vp, u32, vp, u32, vp, i32, i32, vp, u32]
+    lib.skc_trace_any.restype = i32; lib.skc_trace_any.argtypes = [vp, vp, u64, vp]
+    lib.skc_trace_closest.restype = i32; lib.skc_trace_closest.argtypes = [vp, vp, u64, vp]
+    lib.skc_upload_profile.restype = i32; lib.skc_upload_profile.argtypes = [vp, vp, vp, u32, vp]
+    lib.skc_upload_lights.restype = i32; lib.skc_upload_lights.argtypes = [vp, vp, u32]
+    lib.skc_irradiance.restype = i32; lib.skc_irradiance.argtypes = [vp, vp, u64, u64, u64, u32, f32, vp, vp]
+    lib.skc_set_irradiance_points.restype = i32; lib.skc_set_irradiance_points.argtypes = [vp, vp, u64]
+    lib.skc_irradiance_dev.restype = i32; lib.skc_irradiance_dev.argtypes = [vp, u64, C.POINTER(vp), C.POINTER(vp)]
+    lib.skc_build_octree.restype = i32; lib.skc_build_octree.argtypes = [vp, C.POINTER(u32), vp, vp]
+    lib.skc_mo.restype = i32; lib.skc_mo.argtypes = [vp, vp, u64, f32, vp]
+    lib.skc_li_sss.restype = i32; lib.skc_li_sss.argtypes = [vp, vp, u64, f32, f32, vp, vp, vp]
+    lib.skc_camera_pass.restype = i32; lib.skc_camera_pass.argtypes = [vp, vp, u64, f32, f32, vp, vp]
+    lib.skc_profile_batch.restype = i32
+    lib.skc_profile_batch.argtypes = [vp, vp, vp, vp, u32, i32, C.POINTER(u32), vp, vp, vp, vp]
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _c(a, dtype):
+    return None if a is None else np.ascontiguousarray(a, dtype=dtype)
+
+
+class SkinDevice:
+    """One skc_ctx.  Methods mirror the C entry points one to one, with numpy arrays."""
+
+    def __init__(self, device=-1):
+        self.lib = load_library()
+        self.ctx = self.lib.skc_create(device)
+        if not self.ctx:
+            raise SkcError(self.lib.skc_last_error(None).decode())
+
+    def close(self):
+        if self.ctx:
+            self.lib.skc_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise SkcError(self.lib.skc_last_error(self.ctx).decode())
+
+    def synchronize(self):
+        self._ck(self.lib.skc_synchronize(self.ctx))
+
+    def launch_count(self):
+        return int(self.lib.skc_launch_count(self.ctx))
+
+    def stage_ms(self, name):
+        return float(self.lib.skc_stage_ms(self.ctx, STAGES[name]))
+
+    # --- BVHAccel
+    def upload_bvh(self, nodes, prims, P, N, uv, indices, mesh_o2w=None, reverse=0, swaps=0, spheres=None):
+        nodes = _c(nodes.view(DT_BVH_NODE) if nodes.dtype != DT_BVH_NODE else nodes, DT_BVH_NODE)
+        prims = _c(prims, np.int32).reshape(-1, 4)
+        P = _c(P, np.float32).reshape(-1, 3); N = _c(N, np.float32); uv = _c(uv, np.float32)
+        indices = _c(indices, np.int32).reshape(-1, 3)
+        mesh_o2w = _c(mesh_o2w, np.float32)
+        spheres = _c(spheres, np.float32)
+        ns = 0 if spheres is None else spheres.size // 70
+        self._keep = (nodes, prims, P, N, uv, indices, mesh_o2w, spheres)
+        self._ck(self.lib.skc_upload_bvh(self.ctx, _ptr(nodes), nodes.size, _ptr(prims), len(prims), _ptr(P), _ptr(N), _ptr(uv),
+                                         len(P), _ptr(indices), len(indices), _ptr(mesh_o2w), int(reverse), int(swaps), _ptr(spheres), ns))
+
+    def trace_any(self, rays):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        out = np.empty(len(rays), np.uint8)
+        self._ck(self.lib.skc_trace_any(self.ctx, _ptr(rays), len(rays), _ptr(out)))
+        return out
+
+    def trace_closest(self, rays):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        out = np.empty(len(rays), DT_HIT)
+        self._ck(self.lib.skc_trace_closest(self.ctx, _ptr(rays), len(rays), _ptr(out)))
+        return out
+
+    # --- tables, lights
+    def upload_profile(self, table=None, rcp=None, rho_hd=None):
+        table = _c(table, np.float32); rcp = _c(rcp, np.float32); rho_hd = _c(rho_hd, np.float32)
+        ln = 0 if table is None else table.shape[-1]
+        self._ck(self.lib.skc_upload_profile(self.ctx, _ptr(table), _ptr(rcp), ln, _ptr(rho_hd)))
+
+    def upload_lights(self, lights):
+        lights = _c(lights, np.float32).reshape(-1, 70)
+        self._ck(self.lib.skc_upload_lights(self.ctx, _ptr(lights), len(lights)))
+
+    # --- Preprocess
+    def irradiance(self, points, n_tasks, mix=0.5, first=0, count=None, albedo=None, want_out=True):
+        pts = points if points.dtype == DT_SURFACE_POINT else points.view(DT_SURFACE_POINT)
+        pts = np.ascontiguousarray(pts)
+        n = len(pts)
+        count = n - first if count is None else count
+        out = np.empty(count, DT_IRR_POINT) if want_out else None
+        albedo = _c(albedo, np.float32)
+        self._ck(self.lib.skc_irradiance(self.ctx, _ptr(pts), n, first, count, n_tasks, mix, _ptr(albedo), _ptr(out)))
+        return out
+
+    def set_irradiance_points(self, pts):
+        pts = np.ascontiguousarray(pts if pts.dtype == DT_IRR_POINT else pts.view(DT_IRR_POINT).reshape(-1))
+        self._ck(self.lib.skc_set_irradiance_points(self.ctx, _ptr(pts), len(pts)))
+
+    def irradiance_dev(self, n_total):
+        a, b = C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.skc_irradiance_dev(self.ctx, n_total, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def build_octree(self):
+        nn = C.c_uint32(0)
+        root = np.zeros(34, np.float32); bounds = np.zeros(6, np.float32)
+        self._ck(self.lib.skc_build_octree(self.ctx, C.byref(nn), _ptr(root), _ptr(bounds)))
+        return int(nn.value), root, bounds
+
+    # --- Li
+    def mo(self, p, max_error):
+        p = _c(p, np.float32).reshape(-1, 3)
+        out = np.empty((len(p), 30), np.float32)
+        self._ck(self.lib.skc_mo(self.ctx, _ptr(p), len(p), max_error, _ptr(out)))
+        return out
+
+    def li_sss(self, hits, max_error, mix=0.5, albedo=None):
+        hits = np.ascontiguousarray(hits if hits.dtype == DT_HIT else hits.view(DT_HIT).reshape(-1))
+        mo = np.empty((len(hits), 30), np.float32); L = np.empty((len(hits), 30), np.float32)
+        albedo = _c(albedo, np.float32)
+        self._ck(self.lib.skc_li_sss(self.ctx, _ptr(hits), len(hits), max_error, mix, _ptr(albedo), _ptr(mo), _ptr(L)))
+        return mo, L
+
+    def camera_pass(self, rays, max_error, mix=0.5, want_hits=False):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        L = np.empty((len(rays), 30), np.float32)
+        hits = np.empty(len(rays), DT_HIT) if want_hits else None
+        self._ck(self.lib.skc_camera_pass(self.ctx, _ptr(rays), len(rays), max_error, mix, _ptr(hits), _ptr(L)))
+        return (L, hits) if want_hits else L
+
+    # --- MPC
+    def profile_batch(self, specs, layers_per_set, opts, resample=True):
+        specs = np.ascontiguousarray(specs, DT_LAYER); lps = _c(layers_per_set, np.uint32); opts = np.ascontiguousarray(opts, DT_MPC_OPTIONS)
+        n = len(lps)
+        ln = C.c_uint32(0)
+        self._ck(self.lib.skc_profile_batch(self.ctx, _ptr(specs), _ptr(lps), _ptr(opts), n, int(resample), C.byref(ln), None, None, None, None))
+        L = int(ln.value)
+        d2 = np.empty((n, L), np.float32); R = np.empty((n, L), np.float32); T = np.empty((n, L), np.float32); tot = np.empty((n, 2), np.float32)
+        self._ck(self.lib.skc_profile_batch(self.ctx, _ptr(specs), _ptr(lps), _ptr(opts), n, int(resample), C.byref(ln), _ptr(d2), _ptr(R), _ptr(T), _ptr(tot)))
+        return d2, R, T, tot

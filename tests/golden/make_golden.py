@@ -1,0 +1,117 @@
+#!/usr/bin/env python3
+"""Generate the golden fixtures of tests/golden/ from the REAL reference.
+
+TEST INFRASTRUCTURE.  Runs oracle/_ref/ref_driver (the reference's own
+MultipoleSubsurfaceIntegrator / BVHAccel / LayeredSkin / MPC_* code, built by
+oracle/build_ref.sh from /root/reference) at --ncores 1 (deterministic order)
+and packs the exported streams into compressed .npz files:
+
+  skin_tiny.npz   scenes/skin_tiny.scene: flat BVH + meshes + lights, profile/rho tables,
+                  surface points, irradiance points, octree bounds/root, camera rays,
+                  closest hits, per-hit Mo, per-hit subsurface radiance, per-sample radiance
+  mpc_kat.npz     MPC_ComputeDiffusionProfile on the parameter sets of the reference's
+                  src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
+
+Only this script and the fixtures are committed; nothing at test time reads /root/reference.
+Usage:  python tests/golden/make_golden.py [skin_tiny] [mpc_kat]
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def read_meta(path):
+    meta = {}
+    for line in open(path):
+        k, v = line.split()
+        meta[k] = float(v) if ("." in v or "e" in v) else int(v)
+    return meta
+
+
+def scene_golden(name):
+    scene = os.path.join(ROOT, "scenes", name + ".scene")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        meta = read_meta(os.path.join(d, "meta.txt"))
+        f32 = lambda fn: np.fromfile(os.path.join(d, fn), np.float32)
+        i32 = lambda fn: np.fromfile(os.path.join(d, fn), np.int32)
+        raw = lambda fn: np.fromfile(os.path.join(d, fn), np.uint8)
+        arrays = dict(
+            meta_keys=np.array(list(meta.keys())), meta_vals=np.array([float(v) for v in meta.values()]),
+            bvh_nodes=raw("bvh_nodes.bin"),                      # LinearBVHNode[nNodes] 32 B
+            bvh_prims=i32("bvh_prims.bin").reshape(-1, 4),      # type, mesh, index, primitiveId
+            mesh_P=f32("mesh0_P.bin").reshape(-1, 3), mesh_N=f32("mesh0_N.bin").reshape(-1, 3),
+            mesh_uv=f32("mesh0_uv.bin").reshape(-1, 2), mesh_idx=i32("mesh0_idx.bin").reshape(-1, 3),
+            mesh_o2w=f32("mesh0_o2w.bin"),
+            lights=f32("lights.bin").reshape(-1, 70),
+            surface_points=raw("surface_points.bin"),            # SurfacePoint[n] 44 B
+            irradiance_points=f32("irradiance_points.bin").reshape(-1, 38),
+            octree_bounds=f32("octree_bounds.bin"), octree_root=f32("octree_root.bin"),
+            profile_hdr=f32("profile_hdr.bin").reshape(30, 4),
+            profile_rd=f32("profile_rd.bin").reshape(30, -1),
+            rho_hd=f32("rho_hd.bin").reshape(-1, 30),
+            skin_coeffs=f32("skin_coeffs.bin"),
+            cie_xyz30=f32("cie_xyz30.bin").reshape(3, 30),
+            camera_rays=f32("camera_rays.bin").reshape(-1, 8), camera_xy=f32("camera_xy.bin").reshape(-1, 2),
+            hits=raw("hits.bin"),                                # DrvHit[n] 56 B
+            mo=f32("mo.bin").reshape(-1, 30), L_sss=f32("L_sss.bin").reshape(-1, 30),
+            L=f32("L.bin").reshape(-1, 30),
+        )
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "bvh_nodes")})
+
+
+# (nLayers, desiredLength, lerpOnThinSlab, resample, stepSize, [(ior, thickness, mua, musp)...])
+# First three: src/multipole/test/test.cpp:84-116 at desiredLength 512 -> here 64/128 to keep
+# the fixture small; the full-size known answers are checked in the GPU-marked tests against
+# oracle/_ref directly when it is present.
+EPI = (1.4, 0.025, 0.268088, 19.4879)
+DERM = (1.4, 2.0, 0.268088, 9.74395)
+MPC_CASES = [
+    (1, 64, 1, 0, 0.0, [EPI]),
+    (1, 64, 1, 0, 0.0, [DERM]),
+    (2, 64, 1, 0, 0.0, [EPI, DERM]),
+    (2, 64, 1, 1, 0.0, [EPI, DERM]),
+    (2, 128, 1, 1, 0.0, [EPI, DERM]),
+    (2, 64, 0, 1, 0.0, [EPI, DERM]),
+    (2, 64, 1, 1, 0.0, [(1.4, 0.005, 0.5, 30.0), (1.3, 1.0, 0.1, 5.0)]),
+    (3, 64, 1, 1, 0.0, [(1.4, 0.01, 0.5, 30.0), (1.45, 0.1, 0.3, 15.0), (1.35, 3.0, 0.05, 8.0)]),
+]
+
+
+def mpc_golden():
+    with tempfile.TemporaryDirectory() as d:
+        inp, outp = os.path.join(d, "in.txt"), os.path.join(d, "out.bin")
+        with open(inp, "w") as f:
+            for nl, dl, lerp, res, step, layers in MPC_CASES:
+                f.write("%d %d %d %d %r " % (nl, dl, lerp, res, step) + " ".join("%r %r %r %r" % l for l in layers) + "\n")
+        subprocess.run([DRIVER, "mpc", inp, outp], check=True, stdout=subprocess.DEVNULL)
+        blob = open(outp, "rb").read()
+    arrays, off = {}, 0
+    for i, case in enumerate(MPC_CASES):
+        ln = int(np.frombuffer(blob, np.uint32, 1, off)[0]); off += 4
+        tot = np.frombuffer(blob, np.float32, 2, off); off += 8
+        body = np.frombuffer(blob, np.float32, 3 * ln, off).reshape(3, ln); off += 12 * ln
+        arrays["case%d_spec" % i] = np.array([case[0], case[1], case[2], case[3], case[4]] + [x for l in case[5] for x in l], np.float64)
+        arrays["case%d_totals" % i] = tot.copy()
+        arrays["case%d_d2_R_T" % i] = body.copy()
+    path = os.path.join(OUT, "mpc_kat.npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    what = sys.argv[1:] or ["skin_tiny", "mpc_kat"]
+    if not os.path.exists(DRIVER):
+        sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
+    for w in what:
+        mpc_golden() if w == "mpc_kat" else scene_golden(w)

@@ -1,0 +1,73 @@
+"""Shared helpers for the parity tests: golden-fixture loading and device set-up."""
+import os
+import types
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+DT_HIT = np.dtype([("hit", "<i4"), ("prim", "<i4"), ("t", "<f4"), ("rayEpsilon", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("wo", "<f4", 3), ("hasBssrdf", "<i4")])
+DT_SP = np.dtype([("p", "<f4", 3), ("n", "<f4", 3), ("u", "<f4"), ("v", "<f4"), ("materialId", "<u4"), ("area", "<f4"), ("rayEpsilon", "<f4")])
+DT_IP = np.dtype([("p", "<f4", 3), ("n", "<f4", 3), ("E", "<f4", 30), ("area", "<f4"), ("rayEpsilon", "<f4")])
+DT_NODE = np.dtype([("pmin", "<f4", 3), ("pmax", "<f4", 3), ("offset", "<u4"), ("nPrimitives", "u1"), ("axis", "u1"), ("pad", "u1", 2)])
+
+
+def load_scene_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    g = types.SimpleNamespace()
+    g.meta = dict(zip([str(k) for k in z["meta_keys"]], z["meta_vals"]))
+    g.bvh_nodes = z["bvh_nodes"].view(DT_NODE)
+    g.bvh_prims = z["bvh_prims"]
+    g.mesh_P, g.mesh_N, g.mesh_uv, g.mesh_idx, g.mesh_o2w = z["mesh_P"], z["mesh_N"], z["mesh_uv"], z["mesh_idx"], z["mesh_o2w"]
+    g.lights = z["lights"]
+    g.surface_points = z["surface_points"].view(DT_SP)
+    g.irradiance_points = np.ascontiguousarray(z["irradiance_points"]).view(DT_IP).reshape(-1)
+    g.octree_bounds, g.octree_root = z["octree_bounds"], z["octree_root"]
+    g.profile_hdr, g.profile_rd, g.rho_hd = z["profile_hdr"], z["profile_rd"], z["rho_hd"]
+    g.skin_coeffs, g.cie = z["skin_coeffs"], z["cie_xyz30"]
+    g.camera_rays, g.camera_xy = z["camera_rays"], z["camera_xy"]
+    g.hits = z["hits"].view(DT_HIT)
+    g.mo, g.L_sss, g.L = z["mo"], z["L_sss"], z["L"]
+    g.max_error = float(g.meta["maxError"]); g.mix = float(g.meta["mix"])
+    g.n_tasks = int(g.meta["irradiance_tasks"])
+    return g
+
+
+def setup_device(dev, g, tables=True):
+    """Upload the exported flat BVH, lights and material tables of a scene golden."""
+    dev.upload_bvh(g.bvh_nodes, g.bvh_prims, g.mesh_P, g.mesh_N, g.mesh_uv, g.mesh_idx, g.mesh_o2w,
+                   reverse=int(g.meta["mesh0_reverse"]), swaps=int(g.meta["mesh0_swaps"]), spheres=g.lights)
+    dev.upload_lights(g.lights)
+    if tables:
+        dev.upload_profile(g.profile_rd, g.profile_hdr[:, 1], g.rho_hd[:1025])
+
+
+def rel_err(a, b, floor=0.0):
+    """|a-b| / max(|b|, floor) elementwise (b = reference)."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return np.abs(a - b) / np.maximum(np.abs(b), floor if floor > 0 else np.finfo(np.float64).tiny)
+
+
+def row_rel_err(a, b):
+    """Per-row relative error: max_c |a-b| / max_c |b| (spectra compared against their own scale)."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    scale = np.abs(b).max(axis=1)
+    err = np.abs(a - b).max(axis=1)
+    return np.where(scale > 0, err / np.where(scale > 0, scale, 1), err)
+
+
+def smoke_check(pkg):
+    g = load_scene_golden("skin_tiny")
+    dev = pkg.SkinDevice(0)
+    try:
+        setup_device(dev, g)
+        irr = dev.irradiance(g.surface_points, g.n_tasks, g.mix)
+        e = row_rel_err(irr["E"], g.irradiance_points["E"])
+        assert np.mean(e < 1e-4) > 0.995, "irradiance parity: %.4f within 1e-4" % np.mean(e < 1e-4)
+        dev.build_octree()
+        L = dev.camera_pass(g.camera_rays, g.max_error, g.mix)
+        e = row_rel_err(L, g.L_sss)
+        assert np.mean(e < 1e-3) > 0.99, "camera pass parity: %.4f within 1e-3" % np.mean(e < 1e-3)
+        assert dev.launch_count() > 0
+    finally:
+        dev.close()
