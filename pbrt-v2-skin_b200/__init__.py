@@ -15,3 +15,4 @@ interfaces (host/).  There is no CPU fallback: every entry point raises if the l
 GPU is missing.
 """
 from .skc import SkinDevice, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
+from .host_api import HostScene, load_host_library  # noqa: F401

@@ -1,0 +1,127 @@
+// skin_integrator.cpp -- MultipoleSubsurfaceIntegrator on the device + the C interface the
+// Python tests/bench bind (skh_*).  Mirrors integrators/multipolesubsurface.cpp:170-304.
+#include "skin_scene.h"
+#include <cstdio>
+
+namespace skin {
+
+bool MultipoleSubsurfaceIntegrator::Preprocess(skc_ctx *ctx, const SceneDesc &sd, int nCoresForTasks, std::string *err) {
+    if (sd.lights.empty()) return true;                       // multipolesubsurface.cpp:173
+    // GetSurfacePointsThroughTessellation (renderers/surfacepoints.cpp:362-369)
+    surfacePoints.clear();
+    for (const TriangleMesh &m : sd.meshes) m.TessellateSurfacePoints(minSampleDist, m.materialId, surfacePoints, incenter);
+    int nPoints = (int)surfacePoints.size();
+    int nT = std::max(32 * nCoresForTasks, nPoints / 4096);   // :194-199
+    nTasks = RoundUpPow2((uint32_t)nT);
+    if (skc_irradiance(ctx, surfacePoints.data(), surfacePoints.size(), 0, surfacePoints.size(), nTasks, mix, nullptr, nullptr)) {
+        *err = skc_last_error(ctx); return false;
+    }
+    if (skc_build_octree(ctx, &octreeNodes, nullptr, nullptr)) { *err = skc_last_error(ctx); return false; }
+    return true;
+}
+
+bool MultipoleSubsurfaceIntegrator::LiBatch(skc_ctx *ctx, const skc_ray *rays, uint64_t n, skc_hit *hits, float *L30, std::string *err) const {
+    if (skc_camera_pass(ctx, rays, n, maxError, mix, hits, L30)) { *err = skc_last_error(ctx); return false; }
+    return true;
+}
+
+}  // namespace skin
+
+// ---------------------------------------------------------------------------------------------
+// C interface for tests / bench (plain pointers; the handle owns everything it returns)
+// ---------------------------------------------------------------------------------------------
+using namespace skin;
+
+struct skh_scene {
+    SceneDesc sd;
+    BuiltScene built;
+    std::vector<skc_surface_point> points;
+    std::vector<skc_ray> rays;
+    std::vector<float> xy;
+    std::string err;
+};
+
+extern "C" {
+
+skh_scene *skh_load(const char *path, char *errbuf, int errlen) {
+    skh_scene *s = new skh_scene();
+    std::string err;
+    if (!s->sd.Load(path) || !BuildScene(s->sd, nullptr, &s->built, &(err = s->sd.error))) {
+        if (err.empty()) err = s->sd.error;
+        if (errbuf) snprintf(errbuf, errlen, "%s", err.c_str());
+        delete s;
+        return nullptr;
+    }
+    return s;
+}
+void skh_free(skh_scene *s) { delete s; }
+
+// sizes: [0] nodes [1] prims [2] verts [3] tris [4] lights [5] hasN [6] hasUV [7] xres [8] yres [9] spp
+void skh_sizes(const skh_scene *s, int64_t *out) {
+    const TriangleMesh &m = *s->built.mesh;
+    out[0] = (int64_t)s->built.nodes.size(); out[1] = (int64_t)s->built.prims.size(); out[2] = m.nverts; out[3] = m.ntris;
+    out[4] = (int64_t)s->built.lights.size(); out[5] = !m.n.empty(); out[6] = !m.uvs.empty();
+    out[7] = s->sd.xres; out[8] = s->sd.yres; out[9] = s->sd.spp;
+}
+const void *skh_nodes(const skh_scene *s) { return s->built.nodes.data(); }
+const void *skh_prims(const skh_scene *s) { return s->built.prims.data(); }
+const void *skh_lights(const skh_scene *s) { return s->built.lights.data(); }
+const void *skh_mesh_P(const skh_scene *s) { return s->built.mesh->p.data(); }
+const void *skh_mesh_N(const skh_scene *s) { return s->built.mesh->n.empty() ? nullptr : s->built.mesh->n.data(); }
+const void *skh_mesh_uv(const skh_scene *s) { return s->built.mesh->uvs.empty() ? nullptr : s->built.mesh->uvs.data(); }
+const void *skh_mesh_idx(const skh_scene *s) { return s->built.mesh->vertexIndex.data(); }
+void skh_mesh_o2w(const skh_scene *s, float *out32, int *reverse, int *swaps) {
+    memcpy(out32, s->built.mesh->ObjectToWorld.m.m, 64); memcpy(out32 + 16, s->built.mesh->ObjectToWorld.mInv.m, 64);
+    *reverse = s->built.mesh->ReverseOrientation; *swaps = s->built.mesh->TransformSwapsHandedness;
+}
+// integrator params: maxerror, minsampledistance, mix, maxdepth
+void skh_integrator_params(const skh_scene *s, float *out4) {
+    out4[0] = s->sd.maxerror; out4[1] = s->sd.minsampledistance; out4[2] = s->sd.mix; out4[3] = (float)s->sd.maxdepth;
+}
+// skin params: roughness nmperunit f_mel f_eu f_blood f_ohg desiredlength lerp t0 ior0 t1 ior1
+void skh_skin_params(const skh_scene *s, float *out12) {
+    const SkinParams &k = s->sd.skin;
+    float v[12] = {k.roughness, k.nmperunit, k.f_mel, k.f_eu, k.f_blood, k.f_ohg, (float)k.desiredlength, (float)k.lerponthinslab,
+                   k.layerThickness[0], k.layerIor[0], k.layerThickness[1], k.layerIor[1]};
+    memcpy(out12, v, sizeof v);
+}
+// Tessellation (Preprocess' point source).  Returns the count; pointer valid until the next call.
+uint64_t skh_tessellate(skh_scene *s, float minDist, int incenter, const void **pts) {
+    s->points.clear();
+    for (const TriangleMesh &m : s->sd.meshes) m.TessellateSurfacePoints(minDist, m.materialId, s->points, incenter != 0);
+    *pts = s->points.data();
+    return s->points.size();
+}
+uint64_t skh_count_points(const skh_scene *s, float minDist) {
+    uint64_t n = 0;
+    for (const TriangleMesh &m : s->sd.meshes) n += m.CountSurfacePoints(minDist);
+    return n;
+}
+// Camera rays for given raster positions (cameras/perspective.cpp)
+void skh_camera_rays(skh_scene *s, const float *xy, uint64_t n, skc_ray *out) {
+    const float *la = s->sd.lookat;
+    Transform w2c = Transform() * LookAt(V3(la[0], la[1], la[2]), V3(la[3], la[4], la[5]), V3(la[6], la[7], la[8]));
+    PerspectiveCamera cam(InverseT(w2c), s->sd.fov, s->sd.xres, s->sd.yres);   // api.cpp:862
+    for (uint64_t i = 0; i < n; ++i) cam.GenerateRay(xy[2 * i], xy[2 * i + 1], &out[i]);
+}
+// A deterministic stratified sample pattern for benches (spp samples per pixel, row-major):
+// NOT the reference's LDSampler stream; parity tests use the exported camera_xy instead.
+uint64_t skh_bench_rays(skh_scene *s, const void **rays) {
+    int W = s->sd.xres, H = s->sd.yres, spp = std::max(1, s->sd.spp);
+    int sx = 1; while (sx * sx < spp) ++sx;
+    s->xy.resize((size_t)W * H * spp * 2);
+    size_t k = 0;
+    for (int y = 0; y < H; ++y) for (int x = 0; x < W; ++x) for (int q = 0; q < spp; ++q) {
+        s->xy[k++] = x + ((q % sx) + .5f) / sx; s->xy[k++] = y + ((q / sx) + .5f) / sx;
+    }
+    s->rays.resize((size_t)W * H * spp);
+    skh_camera_rays(s, s->xy.data(), s->rays.size(), s->rays.data());
+    *rays = s->rays.data();
+    return s->rays.size();
+}
+// nTasks of IrradianceTask (multipolesubsurface.cpp:194-199)
+uint32_t skh_irradiance_tasks(uint64_t nPoints, int nCores) {
+    return RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPoints / 4096));
+}
+
+}  // extern "C"

@@ -1,0 +1,258 @@
+// skin_scene.cpp -- transforms, scene description, camera (host mirror; see skin_scene.h).
+#include "skin_scene.h"
+#include <cstdio>
+#include <fstream>
+#include <sstream>
+#include "skin_tables.h"
+
+namespace skin {
+
+// core/transform.cpp:75-133 (Gauss-Jordan, full pivoting) -- same pivot order, same fp32 ops
+Mat4 Inverse(const Mat4 &m) {
+    int indxc[4], indxr[4];
+    int ipiv[4] = {0, 0, 0, 0};
+    float minv[4][4];
+    memcpy(minv, m.m, sizeof minv);
+    for (int i = 0; i < 4; i++) {
+        int irow = -1, icol = -1;
+        float big = 0.;
+        for (int j = 0; j < 4; j++) {
+            if (ipiv[j] != 1) {
+                for (int k = 0; k < 4; k++) {
+                    if (ipiv[k] == 0) {
+                        if (fabsf(minv[j][k]) >= big) { big = float(fabsf(minv[j][k])); irow = j; icol = k; }
+                    }
+                }
+            }
+        }
+        ++ipiv[icol];
+        if (irow != icol) for (int k = 0; k < 4; ++k) std::swap(minv[irow][k], minv[icol][k]);
+        indxr[i] = irow; indxc[i] = icol;
+        float pivinv = 1.f / minv[icol][icol];
+        minv[icol][icol] = 1.f;
+        for (int j = 0; j < 4; j++) minv[icol][j] *= pivinv;
+        for (int j = 0; j < 4; j++) {
+            if (j != icol) {
+                float save = minv[j][icol];
+                minv[j][icol] = 0;
+                for (int k = 0; k < 4; k++) minv[j][k] -= minv[icol][k] * save;
+            }
+        }
+    }
+    for (int j = 3; j >= 0; j--)
+        if (indxr[j] != indxc[j]) for (int k = 0; k < 4; k++) std::swap(minv[k][indxr[j]], minv[k][indxc[j]]);
+    Mat4 r; memcpy(r.m, minv, sizeof minv);
+    return r;
+}
+
+Transform Translate(V3 d) {
+    return Transform(Mat4(1, 0, 0, d.x, 0, 1, 0, d.y, 0, 0, 1, d.z, 0, 0, 0, 1), Mat4(1, 0, 0, -d.x, 0, 1, 0, -d.y, 0, 0, 1, -d.z, 0, 0, 0, 1));
+}
+Transform Scale(float x, float y, float z) {
+    return Transform(Mat4(x, 0, 0, 0, 0, y, 0, 0, 0, 0, z, 0, 0, 0, 0, 1), Mat4(1.f / x, 0, 0, 0, 0, 1.f / y, 0, 0, 0, 0, 1.f / z, 0, 0, 0, 0, 1));
+}
+Transform Rotate(float angle, V3 axis) {   // transform.cpp:213-241
+    V3 a = Normalize(axis);
+    float s = sinf(Radians(angle)), c = cosf(Radians(angle));
+    Mat4 m;
+    m.m[0][0] = a.x * a.x + (1.f - a.x * a.x) * c; m.m[0][1] = a.x * a.y * (1.f - c) - a.z * s; m.m[0][2] = a.x * a.z * (1.f - c) + a.y * s; m.m[0][3] = 0;
+    m.m[1][0] = a.x * a.y * (1.f - c) + a.z * s; m.m[1][1] = a.y * a.y + (1.f - a.y * a.y) * c; m.m[1][2] = a.y * a.z * (1.f - c) - a.x * s; m.m[1][3] = 0;
+    m.m[2][0] = a.x * a.z * (1.f - c) - a.y * s; m.m[2][1] = a.y * a.z * (1.f - c) + a.x * s; m.m[2][2] = a.z * a.z + (1.f - a.z * a.z) * c; m.m[2][3] = 0;
+    m.m[3][0] = 0; m.m[3][1] = 0; m.m[3][2] = 0; m.m[3][3] = 1;
+    return Transform(m, Transpose(m));
+}
+Transform LookAt(V3 pos, V3 look, V3 up) {   // transform.cpp:244-265
+    Mat4 m;
+    m.m[0][3] = pos.x; m.m[1][3] = pos.y; m.m[2][3] = pos.z; m.m[3][3] = 1;
+    V3 dir = Normalize(look - pos);
+    V3 left = Normalize(Cross(Normalize(up), dir));
+    V3 newUp = Cross(dir, left);
+    m.m[0][0] = left.x; m.m[1][0] = left.y; m.m[2][0] = left.z; m.m[3][0] = 0.;
+    m.m[0][1] = newUp.x; m.m[1][1] = newUp.y; m.m[2][1] = newUp.z; m.m[3][1] = 0.;
+    m.m[0][2] = dir.x; m.m[1][2] = dir.y; m.m[2][2] = dir.z; m.m[3][2] = 0.;
+    return Transform(Inverse(m), m);
+}
+Transform Perspective(float fov, float n, float f) {   // transform.cpp:309-319
+    Mat4 persp(1, 0, 0, 0, 0, 1, 0, 0, 0, 0, f / (f - n), -f * n / (f - n), 0, 0, 1, 0);
+    float invTanAng = 1.f / tanf(Radians(fov) / 2.f);
+    return Scale(invTanAng, invTanAng, 1) * Transform(persp);
+}
+
+// core/camera.cpp:83-102, cameras/perspective.cpp:124-155
+PerspectiveCamera::PerspectiveCamera(const Transform &cam2world, float fov, int xres, int yres) : CameraToWorld(cam2world) {
+    float frame = float(xres) / float(yres);
+    float screen[4];
+    if (frame > 1.f) { screen[0] = -frame; screen[1] = frame; screen[2] = -1.f; screen[3] = 1.f; }
+    else { screen[0] = -1.f; screen[1] = 1.f; screen[2] = -1.f / frame; screen[3] = 1.f / frame; }
+    Transform CameraToScreen = Perspective(fov, 1e-2f, 1000.f);
+    Transform ScreenToRaster = Scale(float(xres), float(yres), 1.f) *
+                               Scale(1.f / (screen[1] - screen[0]), 1.f / (screen[2] - screen[3]), 1.f) *
+                               Translate(V3(-screen[0], -screen[3], 0.f));
+    Transform RasterToScreen = InverseT(ScreenToRaster);
+    RasterToCamera = InverseT(CameraToScreen) * RasterToScreen;
+}
+
+void PerspectiveCamera::GenerateRay(float imageX, float imageY, skc_ray *ray) const {   // perspective.cpp:79-113
+    V3 Pcamera = RasterToCamera.Point(V3(imageX, imageY, 0));
+    V3 dir = Normalize(Pcamera);
+    V3 o = CameraToWorld.Point(V3(0, 0, 0));
+    V3 d = CameraToWorld.Vector(dir);
+    ray->o[0] = o.x; ray->o[1] = o.y; ray->o[2] = o.z;
+    ray->d[0] = d.x; ray->d[1] = d.y; ray->d[2] = d.z;
+    ray->mint = 0.f; ray->maxt = INFINITY;
+}
+
+// ParamSet::AddRGBSpectrum -> Spectrum::FromRGB(rgb, SPECTRUM_REFLECTANCE) (core/paramset.cpp,
+// core/spectrum.cpp).  For r == g == b the conversion reduces to rgb * rgbRefl2SpectWhite * .94;
+// the binned white table comes from skin_tables.h.  Coloured emitters are not on this path yet.
+void RGBIlluminantToSpectrum(const float rgb[3], float out30[30]) {
+    for (int i = 0; i < 30; ++i) out30[i] = rgb[0] * kGreyRGBToSpectrum30[i];
+}
+
+skc_light SphereLight::Pack(const float *Lemit30) const {
+    skc_light L;
+    memcpy(L.o2w, ObjectToWorld.m.m, 64); memcpy(L.w2o, ObjectToWorld.mInv.m, 64);
+    // Sphere ctor (shapes/sphere.cpp:40-50)
+    float zmn = std::min(std::max(std::min(zmin, zmax), -radius), radius);
+    float zmx = std::min(std::max(std::max(zmin, zmax), -radius), radius);
+    L.radius = radius; L.zmin = zmn; L.zmax = zmx;
+    L.thetaMin = acosf(std::min(std::max(zmn / radius, -1.f), 1.f));
+    L.thetaMax = acosf(std::min(std::max(zmx / radius, -1.f), 1.f));
+    L.phiMax = Radians(std::min(std::max(phiMaxDeg, 0.0f), 360.0f));
+    L.nSamples = (float)nSamples; L.reverseOrientation = ReverseOrientation ? 1.f : 0.f;
+    for (int i = 0; i < 30; ++i) L.Lemit[i] = Lemit30[i];
+    return L;
+}
+
+BBox SphereLight::WorldBound() const {
+    float zmn = std::min(std::max(std::min(zmin, zmax), -radius), radius);
+    float zmx = std::min(std::max(std::max(zmin, zmax), -radius), radius);
+    return ObjectToWorld.Box(BBox(V3(-radius, -radius, zmn), V3(radius, radius, zmx)));
+}
+
+static bool loadMesh(const std::string &file, const Transform &o2w, TriangleMesh *m, std::string *err) {
+    FILE *f = fopen(file.c_str(), "rb");
+    if (!f) { *err = "cannot open mesh " + file; return false; }
+    int32_t hdr[4];
+    bool ok = fread(hdr, 4, 4, f) == 4;
+    if (ok) {
+        m->nverts = hdr[0]; m->ntris = hdr[1];
+        std::vector<V3> P(m->nverts);
+        ok = fread(P.data(), 12, m->nverts, f) == (size_t)m->nverts;
+        if (ok && hdr[2]) { m->n.resize(m->nverts); ok = fread(m->n.data(), 12, m->nverts, f) == (size_t)m->nverts; }
+        if (ok && hdr[3]) { m->uvs.resize(2 * (size_t)m->nverts); ok = fread(m->uvs.data(), 8, m->nverts, f) == (size_t)m->nverts; }
+        if (ok) { m->vertexIndex.resize(3 * (size_t)m->ntris); ok = fread(m->vertexIndex.data(), 12, m->ntris, f) == (size_t)m->ntris; }
+        if (ok) {
+            m->p.resize(m->nverts);
+            for (int i = 0; i < m->nverts; ++i) m->p[i] = o2w.Point(P[i]);   // trianglemesh.cpp:72-73
+        }
+    }
+    fclose(f);
+    if (!ok) { *err = "short read in mesh " + file; return false; }
+    m->ObjectToWorld = o2w;
+    m->TransformSwapsHandedness = o2w.SwapsHandedness();
+    return true;
+}
+
+// Line format shared with oracle/refbuild/ref_driver.cpp ("Scene description")
+bool SceneDesc::Load(const std::string &path) {
+    std::ifstream in(path);
+    if (!in) { error = "cannot open scene " + path; return false; }
+    std::string dir = path.substr(0, path.find_last_of('/') + 1), line;
+    Transform cur;   // CTM of the next mesh (pbrtTranslate etc. post-multiply: core/api.cpp:720-756)
+    uint32_t nextMaterialId = 0;
+    while (std::getline(in, line)) {
+        std::istringstream ls(line);
+        std::string key;
+        if (!(ls >> key) || key[0] == '#') continue;
+        if (key == "film") ls >> xres >> yres;
+        else if (key == "lookat") { for (int i = 0; i < 9; ++i) ls >> lookat[i]; }
+        else if (key == "fov") ls >> fov;
+        else if (key == "spp") ls >> spp;
+        else if (key == "integrator") {
+            std::string k; float v;
+            while (ls >> k >> v) {
+                if (k == "maxdepth") maxdepth = (int)v; else if (k == "maxerror") maxerror = v;
+                else if (k == "minsampledistance") minsampledistance = v; else if (k == "mix") mix = v;
+                else if (k == "incenter") incenter = v != 0.f;
+                else { error = "unknown integrator parameter " + k; return false; }
+            }
+        } else if (key == "light") {
+            SphereLight l; float t[3];
+            ls >> t[0] >> t[1] >> t[2] >> l.radius >> l.Lrgb[0] >> l.Lrgb[1] >> l.Lrgb[2] >> l.nSamples;
+            l.zmin = -l.radius; l.zmax = l.radius;
+            l.ObjectToWorld = Transform() * Translate(V3(t[0], t[1], t[2]));
+            lights.push_back(l);
+            nextMaterialId++;   // each emitter shape gets the default matte material (api.cpp MakeMaterial)
+        } else if (key == "skin") {
+            std::string k;
+            while (ls >> k) {
+                if (k == "layers") ls >> skin.layerThickness[0] >> skin.layerIor[0] >> skin.layerThickness[1] >> skin.layerIor[1];
+                else {
+                    float v; ls >> v;
+                    if (k == "roughness") skin.roughness = v; else if (k == "nmperunit") skin.nmperunit = v;
+                    else if (k == "f_mel") skin.f_mel = v; else if (k == "f_eu") skin.f_eu = v;
+                    else if (k == "f_blood") skin.f_blood = v; else if (k == "f_ohg") skin.f_ohg = v;
+                    else if (k == "desiredlength") skin.desiredlength = (int)v; else if (k == "lerponthinslab") skin.lerponthinslab = v != 0.f;
+                    else { error = "unknown skin parameter " + k; return false; }
+                }
+            }
+        } else if (key == "xform") {
+            std::string kind; float v[4] = {0, 0, 0, 0};
+            ls >> kind;
+            int n = kind == "rotate" ? 4 : 3;
+            for (int i = 0; i < n; ++i) ls >> v[i];
+            if (kind == "translate") cur = cur * Translate(V3(v[0], v[1], v[2]));
+            else if (kind == "rotate") cur = cur * Rotate(v[0], V3(v[1], v[2], v[3]));
+            else if (kind == "scale") cur = cur * Scale(v[0], v[1], v[2]);
+            else { error = "unknown xform " + kind; return false; }
+        } else if (key == "mesh") {
+            std::string file; ls >> file;
+            if (file[0] != '/') file = dir + file;
+            TriangleMesh m;
+            if (!loadMesh(file, cur, &m, &error)) return false;
+            m.materialId = nextMaterialId++;
+            meshes.push_back(std::move(m));
+            cur = Transform();
+        } else { error = "scene: unknown key " + key; return false; }
+    }
+    return true;
+}
+
+bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *out, std::string *err) {
+    if (sd.meshes.size() != 1) { *err = "the device path takes exactly one skin mesh"; return false; }
+    const TriangleMesh &mesh = sd.meshes[0];
+    // renderOptions->primitives order: emitter spheres, then the mesh triangles (api.cpp:1066-1070)
+    std::vector<BBox> bounds;
+    std::vector<skc_prim> prims;
+    for (size_t i = 0; i < sd.lights.size(); ++i) {
+        bounds.push_back(sd.lights[i].WorldBound());
+        skc_prim p = {1, -1, (int32_t)i, (int32_t)prims.size()};
+        prims.push_back(p);
+    }
+    for (int t = 0; t < mesh.ntris; ++t) {
+        const V3 &p1 = mesh.p[mesh.vertexIndex[3 * t]], &p2 = mesh.p[mesh.vertexIndex[3 * t + 1]], &p3 = mesh.p[mesh.vertexIndex[3 * t + 2]];
+        bounds.push_back(Union(BBox(p1, p2), p3));   // trianglemesh.inl:45-51
+        skc_prim p = {0, 0, t, (int32_t)prims.size()};
+        prims.push_back(p);
+    }
+    BVHAccel bvh(bounds, 4, "sah");
+    out->nodes = bvh.nodes;
+    out->prims.clear();
+    for (uint32_t pn : bvh.orderedPrims) out->prims.push_back(prims[pn]);
+    out->lights.clear();
+    for (size_t i = 0; i < sd.lights.size(); ++i) {
+        float Le[30];
+        if (Lemit30PerLight) memcpy(Le, Lemit30PerLight + 30 * i, sizeof Le);
+        else {
+            const float *c = sd.lights[i].Lrgb;
+            if (c[0] != c[1] || c[1] != c[2]) { *err = "coloured emitters are not supported on the device path yet (grey RGB only)"; return false; }
+            RGBIlluminantToSpectrum(c, Le);
+        }
+        out->lights.push_back(sd.lights[i].Pack(Le));
+    }
+    out->mesh = &mesh;
+    return true;
+}
+
+}  // namespace skin

@@ -1,0 +1,102 @@
+"""ctypes binding of the C++ host mirror (libskinhost.so, host/skin_integrator.cpp skh_*).  Plumbing."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .skc import DT_BVH_NODE, DT_SURFACE_POINT, SkcError
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+
+
+def load_host_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = os.path.join(_HERE, "libskinhost.so")
+    if not os.path.exists(path):
+        raise SkcError("%s not built (make -C pbrt-v2-skin_b200)" % path)
+    lib = C.CDLL(path)
+    vp = C.c_void_p
+    lib.skh_load.restype = vp; lib.skh_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    lib.skh_free.restype = None; lib.skh_free.argtypes = [vp]
+    lib.skh_sizes.restype = None; lib.skh_sizes.argtypes = [vp, vp]
+    for f in ("skh_nodes", "skh_prims", "skh_lights", "skh_mesh_P", "skh_mesh_N", "skh_mesh_uv", "skh_mesh_idx"):
+        getattr(lib, f).restype = vp; getattr(lib, f).argtypes = [vp]
+    lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
+    lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
+    lib.skh_tessellate.restype = C.c_uint64; lib.skh_tessellate.argtypes = [vp, C.c_float, C.c_int, C.POINTER(vp)]
+    lib.skh_count_points.restype = C.c_uint64; lib.skh_count_points.argtypes = [vp, C.c_float]
+    lib.skh_camera_rays.restype = None; lib.skh_camera_rays.argtypes = [vp, vp, C.c_uint64, vp]
+    lib.skh_bench_rays.restype = C.c_uint64; lib.skh_bench_rays.argtypes = [vp, C.POINTER(vp)]
+    lib.skh_irradiance_tasks.restype = C.c_uint32; lib.skh_irradiance_tasks.argtypes = [C.c_uint64, C.c_int]
+    _lib = lib
+    return lib
+
+
+def _view(ptr, nbytes, dtype):
+    if not ptr or nbytes == 0:
+        return None
+    buf = (C.c_uint8 * nbytes).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype)
+
+
+class HostScene:
+    """A scene file loaded and built by the C++ host mirror (BVH, world-space mesh, lights)."""
+
+    def __init__(self, path):
+        self.lib = load_host_library()
+        err = C.create_string_buffer(512)
+        self.h = self.lib.skh_load(path.encode(), err, 512)
+        if not self.h:
+            raise SkcError(err.value.decode())
+        sz = np.zeros(10, np.int64)
+        self.lib.skh_sizes(self.h, sz.ctypes.data_as(C.c_void_p))
+        (self.n_nodes, self.n_prims, self.n_verts, self.n_tris, self.n_lights, has_n, has_uv, self.xres, self.yres, self.spp) = [int(x) for x in sz]
+        L = self.lib
+        self.nodes = _view(L.skh_nodes(self.h), 32 * self.n_nodes, DT_BVH_NODE)
+        self.prims = _view(L.skh_prims(self.h), 16 * self.n_prims, np.int32).reshape(-1, 4)
+        self.lights = _view(L.skh_lights(self.h), 280 * self.n_lights, np.float32).reshape(-1, 70)
+        self.P = _view(L.skh_mesh_P(self.h), 12 * self.n_verts, np.float32).reshape(-1, 3)
+        self.N = _view(L.skh_mesh_N(self.h), 12 * self.n_verts, np.float32).reshape(-1, 3) if has_n else None
+        self.uv = _view(L.skh_mesh_uv(self.h), 8 * self.n_verts, np.float32).reshape(-1, 2) if has_uv else None
+        self.idx = _view(L.skh_mesh_idx(self.h), 12 * self.n_tris, np.int32).reshape(-1, 3)
+        self.o2w = np.zeros(32, np.float32)
+        r, s = C.c_int(0), C.c_int(0)
+        L.skh_mesh_o2w(self.h, self.o2w.ctypes.data_as(C.c_void_p), C.byref(r), C.byref(s))
+        self.reverse, self.swaps = r.value, s.value
+        ip = np.zeros(4, np.float32); L.skh_integrator_params(self.h, ip.ctypes.data_as(C.c_void_p))
+        self.maxerror, self.minsampledistance, self.mix, self.maxdepth = float(ip[0]), float(ip[1]), float(ip[2]), int(ip[3])
+        self.skin = np.zeros(12, np.float32); L.skh_skin_params(self.h, self.skin.ctypes.data_as(C.c_void_p))
+
+    def close(self):
+        if self.h:
+            self.lib.skh_free(self.h); self.h = None
+
+    def tessellate(self, min_dist=None, incenter=False):
+        p = C.c_void_p()
+        n = self.lib.skh_tessellate(self.h, self.minsampledistance if min_dist is None else min_dist, int(incenter), C.byref(p))
+        return _view(p.value, 44 * n, DT_SURFACE_POINT) if n else np.zeros(0, DT_SURFACE_POINT)
+
+    def count_points(self, min_dist=None):
+        return int(self.lib.skh_count_points(self.h, self.minsampledistance if min_dist is None else min_dist))
+
+    def camera_rays(self, xy):
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        out = np.empty((len(xy), 8), np.float32)
+        self.lib.skh_camera_rays(self.h, xy.ctypes.data_as(C.c_void_p), len(xy), out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def bench_rays(self):
+        p = C.c_void_p()
+        n = self.lib.skh_bench_rays(self.h, C.byref(p))
+        return _view(p.value, 32 * n, np.float32).reshape(-1, 8)
+
+    def irradiance_tasks(self, n_points, n_cores=1):
+        return int(self.lib.skh_irradiance_tasks(n_points, n_cores))
+
+    def upload(self, dev):
+        dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
+        dev.upload_lights(self.lights)
