@@ -1,0 +1,300 @@
+#!/usr/bin/env python3
+"""bench.py -- the subsurface hot path of pbrt-v2-skin on B200 (contract: see DESIGN.md section 6).
+
+One "step" = one pass of the hot path over the reconstructed skin.scene (BASELINE.json configs[1]):
+    MultipoleSubsurfaceIntegrator::Preprocess  (irradiance pass over every surface point: light
+        sampling + shadow rays through the BVH; then the octree build + InitHierarchy)
+  + the subsurface part of the camera pass     (closest hit per camera sample, octree Mo, Li SSS term)
+metric  = shading points per second = (irradiance points + camera samples) / step time
+value   = inputs (surface points, camera rays) resident in HBM before the timed region
+e2e     = the same through the host-buffer C ABI calls: pinned host surface points and rays copied
+          in, per-sample radiance copied out, every step
+N > 1   = points sharded over ranks, in-place NCCL all-gather of the irradiance set, replicated
+          octree build, camera samples sharded (strong scaling: the scene is fixed).
+
+`--impl reference` times the reference's own CPU code (oracle/_ref/ref_driver bench) on a bounded
+sample of the same scene (1/16 of the points and of the film), all host threads.
+"""
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "skin.pbrt subsurface hot path: shading points/s (irradiance points + camera samples per second of Preprocess + Li)"
+UNIT = "shading points/s"
+WORKLOAD = "scenes/skin.scene (reconstructed skin.pbrt: head mesh Scale 10, 2 sphere lights x 4 samples, minsampledistance 0.0015, 1280x720x4spp, maxerror 0.1)"
+
+
+def clocks_sampler(stop, out):
+    q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    try:
+        p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "200", "-i", os.environ.get("LOCAL_RANK", "0")],
+                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+    except Exception:
+        return
+    def reader():
+        for line in p.stdout:
+            out.append(line.strip())
+    t = threading.Thread(target=reader, daemon=True); t.start()
+    stop.wait()
+    p.terminate()
+    t.join(timeout=2)
+
+
+def summarise_clocks(lines):
+    sm, mx, reasons = [], 0.0, set()
+    for l in lines:
+        f = [x.strip() for x in l.split(",")]
+        if len(f) < 7:
+            continue
+        try:
+            sm.append(float(f[0])); mx = max(mx, float(f[1]))
+        except ValueError:
+            continue
+        for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+            if v.lower().startswith("active"):
+                reasons.add(name)
+    return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def load_tables():
+    path = os.path.join(ROOT, "scenes", "_generated", "skin_tables.npz")
+    if not os.path.exists(path):
+        raise SystemExit("material tables %s missing (tools/export_material.py; device generation of the profile tables is not wired in yet)" % path)
+    z = np.load(path)
+    return z["profile_rd"], z["profile_hdr"][:, 1].copy(), z["rho_hd"][:1025].copy()
+
+
+def reference_arm(args):
+    """The reference's own CPU implementation on the host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+    if not os.path.exists(drv):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (oracle/build_ref.sh needs /root/reference)"}))
+        return
+    sample = os.path.join(ROOT, "scenes", "skin_sample16.scene")
+    cores = os.cpu_count() or 1
+    out = subprocess.run([drv, "bench", sample, "--ncores", str(cores), "--steps", str(args.steps), "--warmup", str(args.warmup)],
+                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, check=True).stdout
+    steps = [l.split() for l in out.splitlines() if l.startswith("step ") and int(l.split()[1]) >= 0]
+    units = sum(int(s[3]) + int(s[5]) for s in steps)
+    secs = sum(float(s[7]) + float(s[9]) for s in steps)
+    value = units / secs
+    desc = ("skin.scene at 1/16 scale (minsampledistance 0.006 -> %s irradiance points, 320x180x4spp -> %s camera samples), "
+            "reference Preprocess + SamplerRendererTask loop, %d steps" % (steps[0][3], steps[0][5], len(steps)))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * secs / max(1, len(steps)), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": desc},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--scene", default=os.path.join(ROOT, "scenes", "skin.scene"))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = pkg.SkinDevice(local)
+
+    # ---- workload (host side, untimed): scene, BVH, surface points, camera rays, tables
+    scene = pkg.HostScene(args.scene)
+    scene.upload(dev)
+    table, rcp, rho = load_tables()
+    dev.upload_profile(table, rcp, rho)
+    pts = scene.tessellate()
+    rays = scene.bench_rays()
+    n_pts, n_rays = len(pts), len(rays)
+    n_tasks = scene.irradiance_tasks(n_pts, 1)
+    # rank shards (contiguous, equal padded size so the all-gather can run in place)
+    shard = (n_pts + world - 1) // world
+    p_first = min(rank * shard, n_pts); p_count = min(shard, n_pts - p_first)
+    rshard = (n_rays + world - 1) // world
+    r_first = min(rank * rshard, n_rays); r_count = min(rshard, n_rays - r_first)
+    dev.set_surface_points(pts)
+    dev.set_camera_rays(rays)
+    pos_t = e_t = None
+    if world > 1:
+        import torch
+        pa_ptr, e_ptr = dev.irradiance_dev(shard * world)
+
+        class _Wrap:
+            def __init__(self, ptr, shape):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 3}
+        pos_t = torch.as_tensor(_Wrap(pa_ptr, (shard * world, 4)), device="cuda")
+        e_t = torch.as_tensor(_Wrap(e_ptr, (shard * world, 32)), device="cuda")
+
+    def exchange():
+        """in-place all-gather of the irradiance shards (posArea + E rows) over NCCL"""
+        if world == 1:
+            return
+        import torch
+        dev.synchronize()
+        dist.all_gather_into_tensor(pos_t, pos_t[rank * shard:(rank + 1) * shard])
+        dist.all_gather_into_tensor(e_t, e_t[rank * shard:(rank + 1) * shard])
+        torch.cuda.synchronize()
+        # padded tail (only when n_pts % world != 0): compact is unnecessary because shards are
+        # contiguous and only the LAST shard is short -> valid points are exactly [0, n_pts)
+        dev.set_point_count(n_pts)
+
+    def step_resident():
+        dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
+        exchange()
+        dev.build_octree()
+        dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix)
+
+    h_pts = dev.pinned((n_pts,), pkg.DT_SURFACE_POINT); h_pts[:] = pts
+    h_rays = dev.pinned((n_rays, 8), np.float32); h_rays[:] = rays
+    h_L = dev.pinned((max(r_count, 1), 30), np.float32)
+
+    def step_e2e():
+        dev.irradiance(h_pts, n_tasks, scene.mix, first=p_first, count=p_count, want_out=False)
+        exchange()
+        dev.build_octree()
+        L = dev.lib.skc_camera_pass(dev.ctx, h_rays[r_first:].ctypes.data, r_count, scene.maxerror, scene.mix, None, h_L.ctypes.data)
+        dev._ck(L)
+
+    def barrier():
+        if world > 1:
+            import torch
+            dist.barrier(); torch.cuda.synchronize()
+        dev.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        dev.timer_begin()
+        for _ in range(k):
+            fn()
+        ms = dev.timer_end_ms()
+        barrier()
+        if world > 1:
+            import torch
+            t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_resident()
+    stop, lines = threading.Event(), []
+    th = threading.Thread(target=clocks_sampler, args=(stop, lines), daemon=True); th.start()
+    launches0 = dev.launch_count()
+    stage_acc = {}
+    barrier()
+    dev.timer_begin()
+    for _ in range(args.steps):
+        step_resident()
+        for s in ("scramble", "irradiance", "octree", "closest", "mo"):
+            stage_acc[s] = stage_acc.get(s, 0.0) + dev.stage_ms(s)
+    ms_total = dev.timer_end_ms()
+    barrier()
+    launches = dev.launch_count() - launches0
+    if world > 1:
+        import torch
+        t = torch.tensor([ms_total], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms_total = float(t.item())
+    for _ in range(min(2, args.warmup)):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    stop.set(); th.join(timeout=3)
+
+    units = n_pts + n_rays
+    ms_step = ms_total / args.steps
+    value = units / (ms_step * 1e-3)
+    e2e_value = units / (ms_e2e / args.steps * 1e-3)
+    stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
+
+    # ---- roofline of the dominant kernel (one extra instrumented pass, untimed)
+    c_irr = dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix, counters=True)
+    exchange()
+    dev.build_octree()
+    c_cam = dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix, counters=True)
+    n_lights = scene.n_lights
+    # algorithmic bytes: irradiance = per point 44 in + 144 out + 12*nLights scramble
+    #   + per shadow ray 32*slab tests + 48*primitive tests ; Mo = per hit 12 in + 128 out + 48 B per node
+    #   classified + 16 B per leaf point tested + (128 B row + 240 B table pairs) per contribution
+    irr_bytes = p_count * (44 + 144 + 12 * n_lights) + 32 * int(c_irr[0]) + 48 * int(c_irr[1])
+    mo_bytes = r_count * (12 + 128) + 48 * int(c_cam[2]) + 16 * int(c_cam[3]) + 368 * (int(c_cam[4]) + int(c_cam[5]))
+    peak, peak_kind = measured_peak()
+    dom = "irradiance" if stage_ms["irradiance"] >= stage_ms["mo"] else "mo"
+    dom_bytes = irr_bytes if dom == "irradiance" else mo_bytes
+    achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_irradiance" if dom == "irradiance" else "k_mo", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, sustained copy)",
+                "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": stage_ms[dom],
+                "other": {"k_irradiance": {"GBps": irr_bytes / (stage_ms["irradiance"] * 1e-3) / 1e9, "ms": stage_ms["irradiance"],
+                                           "shadow_rays": int(c_irr[2]), "slab_tests": int(c_irr[0]), "prim_tests": int(c_irr[1])},
+                          "k_mo": {"GBps": mo_bytes / (stage_ms["mo"] * 1e-3) / 1e9, "ms": stage_ms["mo"], "nodes": int(c_cam[2]), "leaf_points": int(c_cam[3]),
+                                   "cluster_contribs": int(c_cam[4]), "point_contribs": int(c_cam[5])}}}
+
+    if rank != 0:
+        return
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "irradiance_points": n_pts, "camera_samples": n_rays, "irradiance_tasks": n_tasks,
+                   "l2": "inputs larger than L2 (surface points %.2f GB, octree + points > 4 GB)" % (n_pts * 44 / 1e9),
+                   "camera_sample_pattern": "stratified 2x2 per pixel (bench generator; parity tests use the reference's exported LD stream)",
+                   "material_tables": "exported by the reference checker (interim)"},
+        "stage_ms": stage_ms,
+        "hot_path_seconds": ms_step * 1e-3,
+        "rays_per_s": (int(c_irr[2]) * world + n_rays) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),
+        "irradiance_points_per_s": n_pts / ((stage_ms["scramble"] + stage_ms["irradiance"]) * 1e-3),
+        "mo_points_per_s": n_rays / (stage_ms["mo"] * 1e-3),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(p_count * 44 + r_count * 32), "d2h_bytes_per_step": int(r_count * 120),
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": summarise_clocks(lines),
+        "roofline": roofline,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+        if os.path.exists(drv):
+            cores = os.cpu_count() or 1
+            o = subprocess.run([drv, "bench", os.path.join(ROOT, "scenes", "skin_sample16.scene"), "--ncores", str(cores), "--steps", "2", "--warmup", "0"],
+                               stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+            st = [l.split() for l in o.splitlines() if l.startswith("step ")]
+            if st:
+                u = sum(int(s[3]) + int(s[5]) for s in st); sec = sum(float(s[7]) + float(s[9]) for s in st)
+                out["cpu_baseline"] = {"value": u / sec, "unit": UNIT, "cores": cores, "kind": "reference",
+                                       "sample": "skin.scene at 1/16 scale (%s points, %s camera samples), reference Preprocess + render loop, 2 steps, %.1f s" % (st[0][3], st[0][5], sec)}
+    print(json.dumps(out))
+    dev.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -93,6 +93,10 @@ uint64_t skc_launch_count(const skc_ctx *ctx);
  * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile */
 float skc_stage_ms(const skc_ctx *ctx, int stage);
 
+/* CUDA-event timer on the context's stream spanning any sequence of calls (bench.py). */
+int skc_timer_begin(skc_ctx *ctx);
+float skc_timer_end_ms(skc_ctx *ctx);
+
 /* ---- BVHAccel (accelerators/bvh.cpp) ------------------------------------------------ */
 /* Upload the flat tree BVHAccel::flattenBVHTree (bvh.cpp:362-380) produced, the ordered
  * primitive list, the world-space triangle meshes (shapes/trianglemesh.cpp:72-73) and the
@@ -134,6 +138,8 @@ int skc_set_irradiance_points(skc_ctx *ctx, const skc_irr_point *pts, uint64_t n
 /* Device-resident packed record (p, area, E[30]) range access for the multi-GPU exchange:
  * returns device pointers to the float4 {p,area} array and the [n][32] E array. */
 int skc_irradiance_dev(skc_ctx *ctx, uint64_t nTotal, void **posArea_dev, void **E_dev);
+/* After an exchange into arrays sized for padded shards: the number of valid points. */
+int skc_set_point_count(skc_ctx *ctx, uint64_t n);
 /* SubsurfaceOctreeNode::Insert + InitHierarchy (integrators/diffusionutil.h:94-173) over
  * the device irradiance-point set; the flat tree stays on the device.  Optional outputs:
  * node count, root {p[3], sumArea, Et[30]} (34 floats), bounds (6 floats). */
@@ -151,6 +157,25 @@ int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float maxError, fl
  * Only L30 (and optionally hits) crosses back to the host. */
 int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxError, float mix,
                     skc_hit *hitsOut, float *L30);
+
+/* ---- resident inputs --------------------------------------------------------------------- */
+/* The reference caches the surface-point set in a file ("string pointsfile",
+ * multipolesubsurface.cpp:176-181); here the cache is HBM.  The *_resident calls run the same
+ * kernels as skc_irradiance / skc_camera_pass on inputs uploaded once.  counters (optional,
+ * NULL = none; costs atomics) report the work the kernels did, for the roofline arithmetic:
+ *   skc_irradiance_resident   counters3 = {BVH slab tests, primitive tests, shadow rays}
+ *   skc_camera_pass_resident  counters7 = {slab tests, primitive tests, octree nodes
+ *                             classified, leaf points tested, cluster contributions,
+ *                             point contributions, 0} */
+int skc_set_surface_points(skc_ctx *ctx, const skc_surface_point *points, uint64_t n);
+int skc_irradiance_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32_t nTasks, float mix,
+                            uint64_t *counters3);
+int skc_set_camera_rays(skc_ctx *ctx, const skc_ray *rays, uint64_t n);
+int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix,
+                             float *L30, uint64_t *counters7);
+/* Pinned host memory for callers that want full-rate PCIe copies through the host-buffer calls. */
+void *skc_alloc_pinned(uint64_t bytes);
+void skc_free_pinned(void *p);
 
 /* ---- MPC_* profile generator (multipole/MultipoleProfileCalculator) ------------------ */
 /* MPC_ComputeDiffusionProfile (+ optional MPC_ResampleForUniformDistanceSquaredDistribution)

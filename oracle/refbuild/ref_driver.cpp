@@ -597,8 +597,67 @@ static int runMPC(int argc, char **argv) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------
+// bench mode: the reference's own hot path, timed, K times in one process (material tables
+// are built once, outside the timed steps -- they are not part of the per-frame hot path).
+//   ref_driver bench <scene.txt> --ncores N --steps K --warmup W
+// One step = MultipoleSubsurfaceIntegrator::Preprocess (tessellation + irradiance + octree)
+// followed by the reference's own SamplerRendererTask loop (Scene::Intersect + Li per sample).
+// Prints one line per step: "step i points P samples S preprocess_s a render_s b".
+// ---------------------------------------------------------------------------
+static int runBench(int argc, char **argv) {
+    if (argc < 3) { fprintf(stderr, "usage: ref_driver bench <scene.txt> [--ncores N] [--steps K] [--warmup W]\n"); return 2; }
+    std::string scenePath = argv[2];
+    int ncores = 0, steps = 1, warmup = 0;
+    for (int i = 3; i < argc; ++i) {
+        if (!strcmp(argv[i], "--ncores")) ncores = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--steps")) steps = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--warmup")) warmup = atoi(argv[++i]);
+    }
+    Options options; options.nCores = ncores; options.quiet = true;
+    pbrtInit(options);
+    SceneDesc sd = parseScene(scenePath);
+    double t0 = now_s();
+    buildScene(sd, "/dev/null");
+    Renderer *renderer = renderOptions->MakeRenderer();
+    Scene *scene = renderOptions->MakeScene();
+    printf("cores %d\nsetup_s %.4f\n", NumSystemCores(), now_s() - t0);
+    SamplerRenderer *sr = dynamic_cast<SamplerRenderer *>(renderer);
+    MultipoleSubsurfaceIntegrator *integ = dynamic_cast<MultipoleSubsurfaceIntegrator *>(sr->surfaceIntegrator);
+    Camera *camera = sr->camera;
+    for (int it = 0; it < warmup + steps; ++it) {
+        // reset what Preprocess accumulates (multipolesubsurface.cpp:146-150,218-237)
+        integ->irradiancePoints.clear();
+        integ->octreeArena.FreeAll();
+        integ->octree = NULL;
+        integ->octreeBounds = BBox();
+        t0 = now_s();
+        sr->surfaceIntegrator->Preprocess(scene, camera, sr);
+        double tPre = now_s() - t0;
+        t0 = now_s();
+        Sample *sample = new Sample(sr->sampler, sr->surfaceIntegrator, sr->volumeIntegrator, scene);
+        int nPixels = camera->film->xResolution * camera->film->yResolution;
+        int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPixels / (16 * 16)));
+        ProgressReporter reporter(nTasks, "Rendering");
+        vector<Task *> tasks;
+        for (int i = 0; i < nTasks; ++i)
+            tasks.push_back(new SamplerRendererTask(scene, sr, camera, reporter, sr->sampler, sample, false, nTasks - 1 - i, nTasks));
+        EnqueueTasks(tasks); WaitForAllTasks();
+        for (Task *t : tasks) delete t;
+        reporter.Done();
+        delete sample;
+        double tRender = now_s() - t0;
+        long nSamples = (long)nPixels * sr->sampler->samplesPerPixel;
+        printf("step %d points %zu samples %ld preprocess_s %.4f render_s %.4f\n", it - warmup, integ->irradiancePoints.size(), nSamples, tPre, tRender);
+        fflush(stdout);
+    }
+    TasksCleanup();
+    return 0;
+}
+
 int main(int argc, char **argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver scene|mpc ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver scene|mpc|bench ...\n"); return 2; }
+    if (!strcmp(argv[1], "bench")) return runBench(argc, argv);
     if (!strcmp(argv[1], "scene")) return runScene(argc, argv);
     if (!strcmp(argv[1], "mpc")) return runMPC(argc, argv);
     fprintf(stderr, "unknown mode %s\n", argv[1]);

@@ -63,6 +63,12 @@ struct skc_ctx {
     uint64_t otPoints = 0;
     float otBoundsHost[6];
 
+    // --- resident inputs (skc_set_surface_points / skc_set_camera_rays)
+    skc_surface_point *resPts = nullptr;
+    uint64_t resPtsCount = 0;
+    skc_ray *resRays = nullptr;
+    uint64_t resRaysCount = 0;
+
     // --- scratch
     void *scratch[8] = {nullptr};
     size_t scratchBytes[8] = {0};

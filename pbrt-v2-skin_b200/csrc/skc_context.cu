@@ -62,7 +62,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->bvhNodes, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->lights, ctx->ipPosArea, ctx->ipE,
-                    ctx->otGeo, ctx->otEt, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
+                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
@@ -83,4 +83,26 @@ extern "C" int skc_synchronize(skc_ctx *ctx) {
 extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
 extern "C" float skc_stage_ms(const skc_ctx *ctx, int stage) {
     return (stage >= 0 && stage < SKC_NSTAGES) ? ctx->stageMs[stage] : -1.f;
+}
+
+// whole-step timing on the context's stream (bench.py): CUDA events, not wall clock
+static cudaEvent_t g_t0 = nullptr, g_t1 = nullptr;
+extern "C" int skc_timer_begin(skc_ctx *ctx) {
+    cudaSetDevice(ctx->device);
+    if (!g_t0) { SKC_CUDA(cudaEventCreate(&g_t0)); SKC_CUDA(cudaEventCreate(&g_t1)); }
+    SKC_CUDA(cudaEventRecord(g_t0, ctx->stream));
+    return 0;
+}
+extern "C" float skc_timer_end_ms(skc_ctx *ctx) {
+    cudaSetDevice(ctx->device);
+    if (!g_t0) return -1.f;
+    if (cudaEventRecord(g_t1, ctx->stream) != cudaSuccess || cudaEventSynchronize(g_t1) != cudaSuccess) return -1.f;
+    float ms = -1.f;
+    cudaEventElapsedTime(&ms, g_t0, g_t1);
+    return ms;
+}
+extern "C" int skc_set_point_count(skc_ctx *ctx, uint64_t n) {
+    if (n > ctx->ipCap) return skc_fail(ctx, "skc_set_point_count: %llu exceeds capacity", (unsigned long long)n);
+    ctx->ipCount = n;
+    return 0;
 }

@@ -279,6 +279,7 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_
                     float u0 = vanDerCorput(s, s0), u1 = sobol2(s, s1);
                     f3 wi; float lp; DRay sh;
                     if (sampleSphereLight(L, p, eps, n, u0, u1, &wi, &lp, &sh)) {
+                        if (cnt) atomicAdd(&cnt[2], 1ull);
                         bool occ = cnt ? bvhOccluded<true>(bv, sh, cnt) : bvhOccluded<false>(bv, sh, nullptr);
                         if (!occ) { cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp; }
                     }
@@ -377,11 +378,9 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
     return 0;
 }
 
-extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal,
-                              uint64_t first, uint64_t count, uint32_t nTasks, float mix,
-                              const float *albedo30, skc_irr_point *out) {
-    if (!ctx) return 1;
-    cudaSetDevice(ctx->device);
+// device-level pass over surface points already on the device (dPts[0] = point `first`)
+static int irradianceDev(skc_ctx *ctx, const skc_surface_point *dPts, uint64_t nTotal, uint64_t first, uint64_t count,
+                         uint32_t nTasks, float mix, const float *dAlb, unsigned long long *cntDev) {
     if (!ctx->bvhNodes) return skc_fail(ctx, "skc_irradiance: no BVH uploaded");
     if (!ctx->nLights) return skc_fail(ctx, "skc_irradiance: no lights uploaded");
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_irradiance: no rho table uploaded (skc_upload_profile)");
@@ -391,20 +390,11 @@ extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uin
     if (ctx->ipCount < nTotal) ctx->ipCount = nTotal;
     if (!count) return 0;
     uint32_t wpp = 3 * ctx->nLights;
-    skc_surface_point *dPts = (skc_surface_point *)skc_scratch(ctx, 0, count * sizeof(skc_surface_point));
     uint32_t *dScr = (uint32_t *)skc_scratch(ctx, 1, count * wpp * sizeof(uint32_t));
-    if (!dPts || !dScr) return 1;
-    float *dAlb = nullptr;
-    if (albedo30) {
-        dAlb = (float *)skc_scratch(ctx, 2, count * SKC_NS * sizeof(float));
-        if (!dAlb) return 1;
-        SKC_CUDA(cudaMemcpyAsync(dAlb, albedo30, count * SKC_NS * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    }
-    SKC_CUDA(cudaMemcpyAsync(dPts, points + first, count * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
+    if (!dScr) return 1;
     // tasks overlapping [first, first+count): slice t covers [t*N/nT, (t+1)*N/nT)
     uint32_t t0 = 0, t1 = nTasks - 1;
     {
-        // smallest t whose end > first ; largest t whose start < first+count
         uint64_t lo = 0, hi = nTasks - 1;
         while (lo < hi) { uint64_t m = (lo + hi) / 2; if ((m + 1) * nTotal / nTasks > first) hi = m; else lo = m + 1; }
         t0 = (uint32_t)lo;
@@ -419,9 +409,29 @@ extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uin
     skc_stage_begin(ctx);
     uint64_t blocks = (count + IRR_BLOCK - 1) / IRR_BLOCK;
     k_irradiance<<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
-                                                                  ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, nullptr);
+                                                                  ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, cntDev);
     SKC_LAUNCHED("k_irradiance");
     skc_stage_end(ctx, 1);
+    return 0;
+}
+
+extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal,
+                              uint64_t first, uint64_t count, uint32_t nTasks, float mix,
+                              const float *albedo30, skc_irr_point *out) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (first + count > nTotal) return skc_fail(ctx, "skc_irradiance: bad range");
+    if (!count) { if (skc_ensure_points(ctx, nTotal ? nTotal : 1)) return 1; if (ctx->ipCount < nTotal) ctx->ipCount = nTotal; return 0; }
+    skc_surface_point *dPts = (skc_surface_point *)skc_scratch(ctx, 0, count * sizeof(skc_surface_point));
+    if (!dPts) return 1;
+    float *dAlb = nullptr;
+    if (albedo30) {
+        dAlb = (float *)skc_scratch(ctx, 2, count * SKC_NS * sizeof(float));
+        if (!dAlb) return 1;
+        SKC_CUDA(cudaMemcpyAsync(dAlb, albedo30, count * SKC_NS * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    SKC_CUDA(cudaMemcpyAsync(dPts, points + first, count * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
+    if (irradianceDev(ctx, dPts, nTotal, first, count, nTasks, mix, dAlb, nullptr)) return 1;
     if (out) {
         skc_irr_point *dOut = (skc_irr_point *)skc_scratch(ctx, 3, count * sizeof(skc_irr_point));
         if (!dOut) return 1;
@@ -433,6 +443,49 @@ extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uin
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
+
+// ---- resident inputs (the reference's "pointsfile" cache, kept in HBM) ----------------------
+extern "C" int skc_set_surface_points(skc_ctx *ctx, const skc_surface_point *points, uint64_t n) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (ctx->resPts) { cudaFree(ctx->resPts); ctx->resPts = nullptr; }
+    ctx->resPtsCount = 0;
+    if (!n) return 0;
+    SKC_CUDA(cudaMalloc((void **)&ctx->resPts, n * sizeof(skc_surface_point)));
+    SKC_CUDA(cudaMemcpyAsync(ctx->resPts, points, n * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->resPtsCount = n;
+    return 0;
+}
+
+extern "C" int skc_irradiance_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32_t nTasks, float mix, uint64_t *counters3) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->resPts) return skc_fail(ctx, "skc_irradiance_resident: no surface points set");
+    if (first + count > ctx->resPtsCount) return skc_fail(ctx, "skc_irradiance_resident: bad range");
+    unsigned long long *dCnt = nullptr;
+    if (counters3) {
+        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 4 * sizeof(unsigned long long));
+        if (!dCnt) return 1;
+        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    }
+    if (irradianceDev(ctx, ctx->resPts + first, ctx->resPtsCount, first, count, nTasks, mix, nullptr, dCnt)) return 1;
+    if (counters3) {
+        unsigned long long h[4];
+        SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+        counters3[0] = h[0]; counters3[1] = h[1]; counters3[2] = h[2];
+    }
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" void *skc_alloc_pinned(uint64_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void skc_free_pinned(void *p) { if (p) cudaFreeHost(p); }
 
 extern "C" int skc_set_irradiance_points(skc_ctx *ctx, const skc_irr_point *pts, uint64_t n) {
     if (!ctx) return 1;

@@ -52,8 +52,9 @@ __device__ __forceinline__ float sampleRd(const MoTables &T, int lambda, float r
     return (1.f - t) * v.x + t * v.y;
 }
 
+template <bool COUNT>
 __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float px, float py, float pz,
-                                      float maxError, uint32_t *stack, int lane, float &acc) {
+                                      float maxError, uint32_t *stack, int lane, float &acc, uint32_t *wc) {
     const float rcp = __ldg(&T.rcp[lane]);
     const int lam = lane < SKC_NS ? lane : 0;
     int sp = 0;
@@ -112,6 +113,11 @@ __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float
         sp += (int)total;
         // ---- spectral accumulation: lane = wavelength
         unsigned cm = __ballot_sync(0xffffffffu, contrib);
+        if (COUNT) {
+            unsigned pm = __ballot_sync(0xffffffffu, lane < take && (entry & MO_POINT));
+            unsigned cp = __ballot_sync(0xffffffffu, contrib && (rowIdx & MO_POINT));
+            wc[0] += take - __popc(pm); wc[1] += __popc(pm); wc[2] += __popc(cm) - __popc(cp); wc[3] += __popc(cp);
+        }
         while (cm) {
             int src = __ffs(cm) - 1; cm &= cm - 1;
             uint32_t r = __shfl_sync(0xffffffffu, rowIdx, src);
@@ -126,21 +132,28 @@ __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float
     }
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                      const int32_t *__restrict__ enable, uint64_t enableStrideInts,
-                                                     uint64_t n, float maxError, float *__restrict__ Mo) {
+                                                     uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt) {
     __shared__ uint32_t stacks[MO_WARPS][MO_STACK];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t nWarps = (uint64_t)gridDim.x * MO_WARPS;
+    uint32_t wc[4] = {0, 0, 0, 0};
     for (uint64_t h = (uint64_t)blockIdx.x * MO_WARPS + warp; h < n; h += nWarps) {
         float acc = 0.f;
         bool on = enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true;
         if (on) {
             const float *pp = p3 + h * strideFloats;
             float px = __ldg(pp), py = __ldg(pp + 1), pz = __ldg(pp + 2);
-            moOne(tr, T, px, py, pz, maxError, stacks[warp], lane, acc);
+            moOne<COUNT>(tr, T, px, py, pz, maxError, stacks[warp], lane, acc, wc);
+            if (COUNT) wc[0] += 0;
         }
         Mo[h * SKC_EPAD + lane] = lane < SKC_NS ? acc : 0.f;
+    }
+    if (COUNT && lane == 0 && cnt) {
+        // [0] nodes classified, [1] leaf points tested, [2] cluster contributions, [3] point contributions
+        for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
     }
 }
 
@@ -211,7 +224,7 @@ extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float 
 }
 
 static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride,
-                    uint64_t n, float maxError, float *MoDev) {
+                    uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr) {
     if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo: no octree built (skc_build_octree)");
     if (!ctx->profPairs) return skc_fail(ctx, "skc_mo: no profile table uploaded (skc_upload_profile)");
     if (!n) return 0;
@@ -220,7 +233,8 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     uint64_t blocks = (n + MO_WARPS - 1) / MO_WARPS;
     uint64_t maxBlocks = 148ull * 16ull;
     if (blocks > maxBlocks) blocks = maxBlocks;
-    k_mo<<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev);
+    if (cntDev) k_mo<true><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
+    else k_mo<false><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
     SKC_LAUNCHED("k_mo");
     return 0;
 }
@@ -251,7 +265,7 @@ extern "C" int skc_mo(skc_ctx *ctx, const float *p3, uint64_t n, float maxError,
 
 // hits on the device -> Mo (padded, scratch 1) -> L (scratch 2); shared by li_sss and camera_pass
 static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, const float *albedo30,
-                 float *Mo30, float *L30) {
+                 float *Mo30, float *L30, unsigned long long *cntDev = nullptr, bool computeL = false) {
     float *dMo = (float *)skc_scratch(ctx, 4, n * SKC_EPAD * sizeof(float));
     float *dL = (float *)skc_scratch(ctx, 2, n * SKC_NS * sizeof(float));
     if (!dMo || !dL) return 1;
@@ -264,13 +278,13 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
     }
     skc_stage_begin(ctx);
     // p at float offset 4, hasBssrdf at int offset 13 of the 14-word hit record
-    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, dMo)) return 1;
+    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, dMo, cntDev)) return 1;
     skc_stage_end(ctx, 4);
     uint64_t threads = n * 32;
-    if (L30) {
+    if (L30 || computeL) {
         k_li_sss<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dHits, n, dMo, ctx->rhoHd, dAlb, mix, dL);
         SKC_LAUNCHED("k_li_sss");
-        SKC_CUDA(cudaMemcpyAsync(L30, dL, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        if (L30) SKC_CUDA(cudaMemcpyAsync(L30, dL, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     }
     if (Mo30) {
         float *dOut = (float *)skc_scratch(ctx, 5, n * SKC_NS * sizeof(float));
@@ -308,4 +322,49 @@ extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, fl
     skc_stage_end(ctx, 3);
     if (hitsOut) SKC_CUDA(cudaMemcpyAsync(hitsOut, dHits, n * sizeof(skc_hit), cudaMemcpyDeviceToHost, ctx->stream));
     return liDev(ctx, dHits, n, maxError, mix, nullptr, nullptr, L30);
+}
+
+// ---- resident camera rays -----------------------------------------------------------------
+extern "C" int skc_set_camera_rays(skc_ctx *ctx, const skc_ray *rays, uint64_t n) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (ctx->resRays) { cudaFree(ctx->resRays); ctx->resRays = nullptr; }
+    ctx->resRaysCount = 0;
+    if (!n) return 0;
+    SKC_CUDA(cudaMalloc((void **)&ctx->resRays, n * sizeof(skc_ray)));
+    SKC_CUDA(cudaMemcpyAsync(ctx->resRays, rays, n * sizeof(skc_ray), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->resRaysCount = n;
+    return 0;
+}
+
+// counters7 (optional): [0] slab tests [1] primitive tests (closest hit), [2] octree nodes classified,
+// [3] leaf points tested, [4] cluster contributions, [5] point contributions, [6] rays that hit skin
+extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix,
+                                        float *L30, uint64_t *counters7) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->resRays) return skc_fail(ctx, "skc_camera_pass_resident: no camera rays set");
+    if (first + count > ctx->resRaysCount) return skc_fail(ctx, "skc_camera_pass_resident: bad range");
+    if (!count) return 0;
+    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 1, count * sizeof(skc_hit));
+    if (!dHits) return 1;
+    unsigned long long *dCnt = nullptr;
+    if (counters7) {
+        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 8 * sizeof(unsigned long long));
+        if (!dCnt) return 1;
+        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    }
+    skc_stage_begin(ctx);
+    if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, dCnt)) return 1;
+    skc_stage_end(ctx, 3);
+    if (liDev(ctx, dHits, count, maxError, mix, nullptr, nullptr, L30, dCnt ? dCnt + 2 : nullptr, true)) return 1;
+    if (counters7) {
+        unsigned long long h[8];
+        SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int k = 0; k < 6; ++k) counters7[k] = h[k];
+        counters7[6] = 0;
+    }
+    return 0;
 }

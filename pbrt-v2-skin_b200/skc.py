@@ -26,7 +26,9 @@ STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "a
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
            "skc_upload_bvh", "skc_trace_any", "skc_trace_closest", "skc_upload_profile", "skc_upload_lights",
            "skc_irradiance", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
-           "skc_li_sss", "skc_camera_pass", "skc_profile_batch"]
+           "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
+           "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
+           "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count"]
 
 
 class SkcError(RuntimeError):
@@ -72,6 +74,15 @@ def load_library():
     lib.skc_camera_pass.restype = i32; lib.skc_camera_pass.argtypes = [vp, vp, u64, f32, f32, vp, vp]
     lib.skc_profile_batch.restype = i32
     lib.skc_profile_batch.argtypes = [vp, vp, vp, vp, u32, i32, C.POINTER(u32), vp, vp, vp, vp]
+    lib.skc_set_surface_points.restype = i32; lib.skc_set_surface_points.argtypes = [vp, vp, u64]
+    lib.skc_irradiance_resident.restype = i32; lib.skc_irradiance_resident.argtypes = [vp, u64, u64, u32, f32, vp]
+    lib.skc_set_camera_rays.restype = i32; lib.skc_set_camera_rays.argtypes = [vp, vp, u64]
+    lib.skc_camera_pass_resident.restype = i32; lib.skc_camera_pass_resident.argtypes = [vp, u64, u64, f32, f32, vp, vp]
+    lib.skc_alloc_pinned.restype = vp; lib.skc_alloc_pinned.argtypes = [u64]
+    lib.skc_free_pinned.restype = None; lib.skc_free_pinned.argtypes = [vp]
+    lib.skc_timer_begin.restype = i32; lib.skc_timer_begin.argtypes = [vp]
+    lib.skc_timer_end_ms.restype = f32; lib.skc_timer_end_ms.argtypes = [vp]
+    lib.skc_set_point_count.restype = i32; lib.skc_set_point_count.argtypes = [vp, u64]
     _lib = lib
     return lib
 
@@ -95,6 +106,9 @@ class SkinDevice:
 
     def close(self):
         if self.ctx:
+            for p in getattr(self, "_pinned", []):
+                self.lib.skc_free_pinned(p)
+            self._pinned = []
             self.lib.skc_destroy(self.ctx)
             self.ctx = None
 
@@ -110,6 +124,15 @@ class SkinDevice:
 
     def synchronize(self):
         self._ck(self.lib.skc_synchronize(self.ctx))
+
+    def timer_begin(self):
+        self._ck(self.lib.skc_timer_begin(self.ctx))
+
+    def timer_end_ms(self):
+        return float(self.lib.skc_timer_end_ms(self.ctx))
+
+    def set_point_count(self, n):
+        self._ck(self.lib.skc_set_point_count(self.ctx, n))
 
     def launch_count(self):
         return int(self.lib.skc_launch_count(self.ctx))
@@ -198,6 +221,36 @@ class SkinDevice:
         hits = np.empty(len(rays), DT_HIT) if want_hits else None
         self._ck(self.lib.skc_camera_pass(self.ctx, _ptr(rays), len(rays), max_error, mix, _ptr(hits), _ptr(L)))
         return (L, hits) if want_hits else L
+
+    # --- resident inputs
+    def set_surface_points(self, points):
+        pts = np.ascontiguousarray(points if points.dtype == DT_SURFACE_POINT else points.view(DT_SURFACE_POINT))
+        self._ck(self.lib.skc_set_surface_points(self.ctx, _ptr(pts), len(pts)))
+
+    def irradiance_resident(self, first, count, n_tasks, mix=0.5, counters=False):
+        c = np.zeros(3, np.uint64) if counters else None
+        self._ck(self.lib.skc_irradiance_resident(self.ctx, first, count, n_tasks, mix, _ptr(c)))
+        return c
+
+    def set_camera_rays(self, rays):
+        rays = _c(rays, np.float32).reshape(-1, 8)
+        self._ck(self.lib.skc_set_camera_rays(self.ctx, _ptr(rays), len(rays)))
+
+    def camera_pass_resident(self, first, count, max_error, mix=0.5, out=None, counters=False):
+        c = np.zeros(7, np.uint64) if counters else None
+        self._ck(self.lib.skc_camera_pass_resident(self.ctx, first, count, max_error, mix, _ptr(out), _ptr(c)))
+        return c
+
+    def pinned(self, shape, dtype):
+        """numpy array over cudaHostAlloc'ed memory (freed with the device object)."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        p = self.lib.skc_alloc_pinned(n)
+        if not p:
+            raise SkcError("cudaHostAlloc(%d) failed" % n)
+        self._pinned = getattr(self, "_pinned", []) + [p]
+        buf = (C.c_uint8 * max(n, 1)).from_address(p)
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
     # --- MPC
     def profile_batch(self, specs, layers_per_set, opts, resample=True):
