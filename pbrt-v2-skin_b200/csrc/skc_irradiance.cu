@@ -124,7 +124,7 @@ __device__ inline f3 sphereDgNormal(const skc_light &s, f3 phit /*object space, 
 }
 
 // Sphere::Intersect restricted to what light sampling needs: thit and (optionally) dg.nn.
-__device__ inline bool sphereIntersectDg(const skc_light &s, const DRay &r, float *tHit, f3 *nn) {
+__device__ __noinline__ bool sphereIntersectDg(const skc_light &s, const DRay &r, float *tHit, f3 *nn) {
     DRay ray;
     ray.o = xformPoint(s.w2o, r.o);
     ray.d = xformVector(s.w2o, r.d);
@@ -235,17 +235,24 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
 }
 
 #define IRR_BLOCK 128
+#define IRR_WARPS (IRR_BLOCK / 32)
 #define IRR_CHUNK 8      // light samples handled per transposition pass
 
-// shared: per thread IRR_CHUNK x {costheta, pdf}
+// The spectral accumulators live in shared memory ([point of the warp][wavelength], conflict
+// free) so that the lane = wavelength loop over the warp's 32 points stays ROLLED: the first
+// version kept them in 2 x 32 registers with the loop unrolled 32x, and ncu showed the kernel
+// starved for instructions (stall_no_instruction 24 per issue, 128 registers).
+template <bool COUNT>
 __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_light *__restrict__ lights, uint32_t nLights,
         const skc_surface_point *__restrict__ pts, uint64_t count, const uint32_t *__restrict__ scr,
         const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
         float4 *__restrict__ posArea, float *__restrict__ Eout, uint64_t outBase, unsigned long long *cnt) {
     __shared__ float sCos[IRR_BLOCK][IRR_CHUNK + 1];
     __shared__ float sPdf[IRR_BLOCK][IRR_CHUNK + 1];
+    __shared__ float sE[IRR_WARPS][32][32];
+    __shared__ float sEl[IRR_WARPS][32][32];
     uint64_t i = (uint64_t)blockIdx.x * IRR_BLOCK + threadIdx.x;
-    int lane = threadIdx.x & 31, warpBase = threadIdx.x & ~31;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpBase = threadIdx.x & ~31;
     bool live = i < count;
     f3 p = mk3(0, 0, 0), n = mk3(0, 0, 1);
     float eps = 0.f, area = 0.f;
@@ -255,23 +262,21 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_
         n = mk3(__ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
         area = __ldg(sp + 9); eps = __ldg(sp + 10);
     }
-    // transposed accumulators: lane = wavelength, register k = point k of this warp
-    float E[32];
-#pragma unroll
-    for (int k = 0; k < 32; ++k) E[k] = 0.f;
+#pragma unroll 1
+    for (int k = 0; k < 32; ++k) sE[warp][k][lane] = 0.f;
     for (uint32_t j = 0; j < nLights; ++j) {
         const skc_light &L = lights[j];
         int ns = (int)L.nSamples;
         uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2
-        uint32_t s0 = 0, s1 = 0, sc = 0;
-        if (live) { const uint32_t *w = scr + (i * nLights + j) * 3; s0 = __ldg(w); s1 = __ldg(w + 1); sc = __ldg(w + 2); }
-        (void)sc;   // uComponent picks the shape of a ShapeSet; one sphere -> always shape 0
+        uint32_t s0 = 0, s1 = 0;
+        // the third scramble word (uComponent) picks the shape of a ShapeSet; one sphere -> shape 0
+        if (live) { const uint32_t *w = scr + (i * nLights + j) * 3; s0 = __ldg(w); s1 = __ldg(w + 1); }
         float Lc = lane < SKC_NS ? __ldg(&L.Lemit[lane]) : 0.f;
-        float El[32];
-#pragma unroll
-        for (int k = 0; k < 32; ++k) El[k] = 0.f;
+#pragma unroll 1
+        for (int k = 0; k < 32; ++k) sEl[warp][k][lane] = 0.f;
         for (uint32_t sBase = 0; sBase < nS; sBase += IRR_CHUNK) {
             uint32_t chunk = min((uint32_t)IRR_CHUNK, nS - sBase);
+#pragma unroll 1
             for (uint32_t c = 0; c < chunk; ++c) {
                 float cosT = 0.f, pdf = 0.f;
                 if (live) {
@@ -279,8 +284,8 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_
                     float u0 = vanDerCorput(s, s0), u1 = sobol2(s, s1);
                     f3 wi; float lp; DRay sh;
                     if (sampleSphereLight(L, p, eps, n, u0, u1, &wi, &lp, &sh)) {
-                        if (cnt) atomicAdd(&cnt[2], 1ull);
-                        bool occ = cnt ? bvhOccluded<true>(bv, sh, cnt) : bvhOccluded<false>(bv, sh, nullptr);
+                        if (COUNT) atomicAdd(&cnt[2], 1ull);
+                        bool occ = bvhOccluded<COUNT>(bv, sh, cnt);
                         if (!occ) { cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp; }
                     }
                 }
@@ -288,8 +293,9 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_
             }
             __syncwarp();
             if (lane < SKC_NS) {
-#pragma unroll
+#pragma unroll 1
                 for (int k = 0; k < 32; ++k) {
+                    float el = sEl[warp][k][lane];
                     for (uint32_t c = 0; c < chunk; ++c) {
                         float pdf = sPdf[warpBase + k][c];
                         if (pdf != 0.f) {
@@ -301,23 +307,24 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_
                             float r0 = __ldg(&rhoHd[id * SKC_EPAD + lane]), r1 = __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
                             float rho = (1.f - lerp) * r0 + lerp * r1;
                             float Ft = 1.f - rho;
-                            El[k] += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
+                            el += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
                         }
                     }
+                    sEl[warp][k][lane] = el;
                 }
             }
             __syncwarp();
         }
-#pragma unroll
-        for (int k = 0; k < 32; ++k) E[k] += El[k] / (float)(int)nS;      // :136
+#pragma unroll 1
+        for (int k = 0; k < 32; ++k) sE[warp][k][lane] += sEl[warp][k][lane] / (float)(int)nS;      // :136
     }
     // write: lane = wavelength, coalesced 128 B row per point; lanes 30,31 write the zero pad
     uint64_t warpFirst = (uint64_t)blockIdx.x * IRR_BLOCK + warpBase;
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 32; ++k) {
         uint64_t pi = warpFirst + k;
         if (pi < count) {
-            float e = lane < SKC_NS ? E[k] : 0.f;
+            float e = lane < SKC_NS ? sE[warp][k][lane] : 0.f;
             if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
             Eout[(outBase + pi) * SKC_EPAD + lane] = e;
         }
@@ -408,8 +415,12 @@ static int irradianceDev(skc_ctx *ctx, const skc_surface_point *dPts, uint64_t n
     skc_stage_end(ctx, 0);
     skc_stage_begin(ctx);
     uint64_t blocks = (count + IRR_BLOCK - 1) / IRR_BLOCK;
-    k_irradiance<<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
-                                                                  ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, cntDev);
+    if (cntDev)
+        k_irradiance<true><<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
+                                                                            ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, cntDev);
+    else
+        k_irradiance<false><<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
+                                                                             ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, nullptr);
     SKC_LAUNCHED("k_irradiance");
     skc_stage_end(ctx, 1);
     return 0;
