@@ -59,7 +59,7 @@ struct skc_ctx {
     uint32_t *otPointIdx = nullptr;// leaf-ordered permutation of irradiance points
     float4 *otLeafPosArea = nullptr; // irradiance points gathered in leaf order
     float *otLeafE = nullptr;        // [n][32] in leaf order
-    uint32_t otNodes = 0, otCap = 0;
+    uint32_t otNodes = 0, otCap = 0, otLevels = 0;
     uint64_t otPoints = 0;
     float otBoundsHost[6];
 

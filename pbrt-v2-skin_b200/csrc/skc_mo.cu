@@ -20,9 +20,14 @@
 #include <vector>
 #include "skc_internal.h"
 
-#define MO_WARPS 4
-#define MO_STACK 1024
-#define MO_HIGH 256
+// Launch shape: a CTA of MO_WARPS warps works through a CONTIGUOUS run of MO_WARPS*MO_HITS_PER_WARP
+// shading points (neighbouring camera samples walk the same nodes, rows and table sectors, so
+// they must share an SM's L1 -- with hits dealt round-robin over the grid the L1 hit rate was
+// 2.7 %).  Stack bound: below MO_HIGH entries the warp pops up to 32 entries per round
+// (<= MO_HIGH-1 + 7*32 afterwards), above it one entry (depth-first, +7 per tree level).
+#define MO_WARPS 8
+#define MO_HITS_PER_WARP 16
+#define MO_HIGH 64
 #define MO_POINT 0x80000000u
 
 struct MoTables {
@@ -52,7 +57,7 @@ __device__ __forceinline__ float sampleRd(const MoTables &T, int lambda, float r
     return (1.f - t) * v.x + t * v.y;
 }
 
-template <bool COUNT>
+template <bool COUNT, int MO_STACK>
 __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float px, float py, float pz,
                                       float maxError, uint32_t *stack, int lane, float &acc, uint32_t *wc) {
     const float rcp = __ldg(&T.rcp[lane]);
@@ -132,21 +137,23 @@ __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float
     }
 }
 
-template <bool COUNT>
+template <bool COUNT, int MO_STACK>
 __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                      const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                      uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt) {
     __shared__ uint32_t stacks[MO_WARPS][MO_STACK];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint64_t nWarps = (uint64_t)gridDim.x * MO_WARPS;
     uint32_t wc[4] = {0, 0, 0, 0};
-    for (uint64_t h = (uint64_t)blockIdx.x * MO_WARPS + warp; h < n; h += nWarps) {
+    uint64_t base = (uint64_t)blockIdx.x * (MO_WARPS * MO_HITS_PER_WARP);
+    for (int it = 0; it < MO_HITS_PER_WARP; ++it) {
+        uint64_t h = base + (uint64_t)it * MO_WARPS + warp;
+        if (h >= n) break;
         float acc = 0.f;
         bool on = enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true;
         if (on) {
             const float *pp = p3 + h * strideFloats;
             float px = __ldg(pp), py = __ldg(pp + 1), pz = __ldg(pp + 2);
-            moOne<COUNT>(tr, T, px, py, pz, maxError, stacks[warp], lane, acc, wc);
+            moOne<COUNT, MO_STACK>(tr, T, px, py, pz, maxError, stacks[warp], lane, acc, wc);
             if (COUNT) wc[0] += 0;
         }
         Mo[h * SKC_EPAD + lane] = lane < SKC_NS ? acc : 0.f;
@@ -230,11 +237,18 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (!n) return 0;
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
-    uint64_t blocks = (n + MO_WARPS - 1) / MO_WARPS;
-    uint64_t maxBlocks = 148ull * 16ull;
-    if (blocks > maxBlocks) blocks = maxBlocks;
-    if (cntDev) k_mo<true><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
-    else k_mo<false><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
+    uint64_t per = MO_WARPS * MO_HITS_PER_WARP;
+    uint64_t blocks = (n + per - 1) / per;
+    // stack need: MO_HIGH-1 + 7*32 + 7*levels
+    bool deep = 63 + 224 + 7 * (int)ctx->otLevels > 512;
+    if (63 + 224 + 7 * (int)ctx->otLevels > 1024) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the traversal stack", ctx->otLevels);
+    if (cntDev) {
+        if (deep) k_mo<true, 1024><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
+        else k_mo<true, 512><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
+    } else {
+        if (deep) k_mo<false, 1024><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
+        else k_mo<false, 512><<<(unsigned)blocks, MO_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
+    }
     SKC_LAUNCHED("k_mo");
     return 0;
 }

@@ -353,6 +353,7 @@ extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34
     }
     skc_stage_end(ctx, 2);
     ctx->otNodes = total;
+    ctx->otLevels = (uint32_t)levelStart.size() - 1;
     if (nNodesOut) *nNodesOut = total;
     if (bounds6) for (int k = 0; k < 6; ++k) bounds6[k] = hb[k];
     if (root34) {

@@ -104,16 +104,19 @@ void skh_camera_rays(skh_scene *s, const float *xy, uint64_t n, skc_ray *out) {
     PerspectiveCamera cam(InverseT(w2c), s->sd.fov, s->sd.xres, s->sd.yres);   // api.cpp:862
     for (uint64_t i = 0; i < n; ++i) cam.GenerateRay(xy[2 * i], xy[2 * i + 1], &out[i]);
 }
-// A deterministic stratified sample pattern for benches (spp samples per pixel, row-major):
-// NOT the reference's LDSampler stream; parity tests use the exported camera_xy instead.
+// A deterministic stratified sample pattern for benches: spp samples per pixel, pixels visited
+// tile by tile (16x16, the granularity of the reference's SamplerRendererTask windows,
+// renderers/samplerrenderer.cpp:206-208) and row-major inside a tile.  NOT the reference's
+// LDSampler stream; parity tests use the exported camera_xy instead.
 uint64_t skh_bench_rays(skh_scene *s, const void **rays) {
     int W = s->sd.xres, H = s->sd.yres, spp = std::max(1, s->sd.spp);
     int sx = 1; while (sx * sx < spp) ++sx;
     s->xy.resize((size_t)W * H * spp * 2);
     size_t k = 0;
-    for (int y = 0; y < H; ++y) for (int x = 0; x < W; ++x) for (int q = 0; q < spp; ++q) {
-        s->xy[k++] = x + ((q % sx) + .5f) / sx; s->xy[k++] = y + ((q / sx) + .5f) / sx;
-    }
+    const int T = 16;
+    for (int ty = 0; ty < H; ty += T) for (int tx = 0; tx < W; tx += T)
+        for (int y = ty; y < std::min(ty + T, H); ++y) for (int x = tx; x < std::min(tx + T, W); ++x)
+            for (int q = 0; q < spp; ++q) { s->xy[k++] = x + ((q % sx) + .5f) / sx; s->xy[k++] = y + ((q / sx) + .5f) / sx; }
     s->rays.resize((size_t)W * H * spp);
     skh_camera_rays(s, s->xy.data(), s->rays.size(), s->rays.data());
     *rays = s->rays.data();
