@@ -83,7 +83,7 @@ __device__ inline bool sphereIntersect(const skc_light &s, const DRay &r, float 
     f3 phit = add3(ray.o, mul3(ray.d, thit));
     if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
     float phi = atan2f(phit.y, phit.x);
-    if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+    if (phi < 0.f) phi += 2.f * SKC_PI_F;
     float zmin = s.zmin, zmax = s.zmax, phiMax = s.phiMax;
     if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) {
         if (thit == t1) return false;
@@ -92,7 +92,7 @@ __device__ inline bool sphereIntersect(const skc_light &s, const DRay &r, float 
         phit = add3(ray.o, mul3(ray.d, thit));
         if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
         phi = atan2f(phit.y, phit.x);
-        if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+        if (phi < 0.f) phi += 2.f * SKC_PI_F;
         if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax)
             return false;
     }

@@ -4,7 +4,7 @@
 // the reference is plain x86-64 SSE2 code (no FMA contraction, IEEE div/sqrt, no FTZ),
 // so the whole library is compiled with -fmad=false -prec-div=true -prec-sqrt=true and
 // every helper below spells the reference's operation order.  Where the reference
-// promotes to double (Cross: core/geometry.h:529-536; anything touching M_PI) so do we.
+// promotes to double (Cross: core/geometry.h:529-536) so do we; M_PI is a float literal there (core/pbrt.h:196).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -107,4 +107,5 @@ __host__ __device__ inline float len3(f3 a) { return sqrtf(a.x * a.x + a.y * a.y
 __host__ __device__ inline f3 normalize3(f3 a) { float inv = 1.f / len3(a); return mk3(a.x * inv, a.y * inv, a.z * inv); }
 __host__ __device__ inline float dist2(f3 a, f3 b) { f3 d = sub3(a, b); return d.x * d.x + d.y * d.y + d.z * d.z; }
 
-#define SKC_PI_D 3.14159265358979323846  /* M_PI */
+/* core/pbrt.h:193-196 redefines M_PI as a FLOAT literal: everything "times pi" is fp32 */
+#define SKC_PI_F 3.14159265358979323846f

@@ -141,7 +141,7 @@ __device__ __noinline__ bool sphereIntersectDg(const skc_light &s, const DRay &r
     f3 phit = add3(ray.o, mul3(ray.d, thit));
     if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
     float phi = atan2f(phit.y, phit.x);
-    if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+    if (phi < 0.f) phi += 2.f * SKC_PI_F;
     float zmin = s.zmin, zmax = s.zmax, phiMax = s.phiMax;
     if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) {
         if (thit == t1) return false;
@@ -150,7 +150,7 @@ __device__ __noinline__ bool sphereIntersectDg(const skc_light &s, const DRay &r
         phit = add3(ray.o, mul3(ray.d, thit));
         if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
         phi = atan2f(phit.y, phit.x);
-        if (phi < 0.f) phi = (float)((double)phi + 2.0 * SKC_PI_D);
+        if (phi < 0.f) phi += 2.f * SKC_PI_F;
         if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) return false;
     }
     *tHit = thit;
@@ -173,7 +173,7 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
         // Sphere::Sample(u1,u2,ns) (sphere.cpp:229-234): uniform over the sphere
         float z = 1.f - 2.f * u1;
         float rr = sqrtf(fmaxf(0.f, 1.f - z * z));
-        float phi = (float)((double)(2.f) * SKC_PI_D * (double)u2);
+        float phi = 2.f * SKC_PI_F * u2;
         f3 po = mk3(radius * (rr * cosf_cr(phi)), radius * (rr * sinf_cr(phi)), radius * z);
         ns = normalize3(xformNormal(L.w2o, po));
         if (reverse) ns = mul3(ns, -1.f);
@@ -187,7 +187,7 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
         // UniformSampleCone (core/montecarlo.cpp:413-420)
         float costheta = (1.f - u1) * cosThetaMax + u1 * 1.f;
         float sintheta = sqrtf(1.f - costheta * costheta);
-        float phi = (float)((double)(u2 * 2.f) * SKC_PI_D);
+        float phi = u2 * 2.f * SKC_PI_F;
         f3 dir = add3(add3(mul3(wcX, cosf_cr(phi) * sintheta), mul3(wcY, sinf_cr(phi) * sintheta)), mul3(wc, costheta));
         DRay r; r.o = p; r.d = dir; r.mint = 1e-3f; r.maxt = INFINITY;
         float thit;
@@ -218,7 +218,7 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
     } else {
         float sinThetaMax2 = radius * radius / dc2;
         float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
-        spdf = (float)(1.0 / ((double)2.f * SKC_PI_D * (double)(1.f - cosThetaMax)));   // UniformConePdf
+        spdf = 1.f / (2.f * SKC_PI_F * (1.f - cosThetaMax));   // UniformConePdf (core/montecarlo.cpp:400-402)
     }
     float pdf = 0.f + area * spdf;
     pdf = pdf / area;
