@@ -142,10 +142,8 @@ def main():
     n_pts, n_rays = len(pts), len(rays)
     n_tasks = scene.irradiance_tasks(n_pts, 1)
     # rank shards (contiguous, equal padded size so the all-gather can run in place)
-    shard = (n_pts + world - 1) // world
-    p_first = min(rank * shard, n_pts); p_count = min(shard, n_pts - p_first)
-    rshard = (n_rays + world - 1) // world
-    r_first = min(rank * rshard, n_rays); r_count = min(rshard, n_rays - r_first)
+    p_first, p_count, shard = pkg.shard_range(n_pts, rank, world)
+    r_first, r_count, _ = pkg.shard_range(n_rays, rank, world)
     dev.set_surface_points(pts)
     dev.set_camera_rays(rays)
     pos_t = e_t = None
@@ -165,8 +163,8 @@ def main():
             return
         import torch
         dev.synchronize()
-        dist.all_gather_into_tensor(pos_t, pos_t[rank * shard:(rank + 1) * shard])
-        dist.all_gather_into_tensor(e_t, e_t[rank * shard:(rank + 1) * shard])
+        pkg.allgather_inplace(dist, pos_t, rank, shard)
+        pkg.allgather_inplace(dist, e_t, rank, shard)
         torch.cuda.synchronize()
         # padded tail (only when n_pts % world != 0): compact is unnecessary because shards are
         # contiguous and only the LAST shard is short -> valid points are exactly [0, n_pts)

@@ -1,0 +1,17 @@
+"""Multi-GPU partitioning of the hot path: contiguous equal shards of the irradiance
+points and of the camera samples, and the in-place all-gather of the irradiance set.  Pure
+host logic over torch.distributed; used by bench.py (NCCL) and tested on CPU with gloo."""
+
+
+def shard_range(n, rank, world):
+    """Contiguous shard [first, first+count) of n items; every shard but the last has ceil(n/world)."""
+    per = (n + world - 1) // world
+    first = min(rank * per, n)
+    return first, min(per, n - first), per
+
+
+def allgather_inplace(dist, full, rank, per):
+    """full: tensor of world*per rows; rows [rank*per, (rank+1)*per) hold this rank's shard.
+    After the call every rank holds every shard (NCCL/gloo all_gather_into_tensor, no staging copy)."""
+    dist.all_gather_into_tensor(full, full[rank * per:(rank + 1) * per])
+    return full

@@ -69,5 +69,14 @@ def smoke_check(pkg):
         e = row_rel_err(L, g.L_sss)
         assert np.mean(e < 1e-3) > 0.99, "camera pass parity: %.4f within 1e-3" % np.mean(e < 1e-3)
         assert dev.launch_count() > 0
+        # and against the C restatement on a few hits (oracle/skin_oracle.c)
+        import oracle_api as orc
+        dev.set_irradiance_points(g.irradiance_points)
+        dev.build_octree()
+        s = np.nonzero(g.hits["hasBssrdf"] == 1)[0][:64]
+        tree = orc.Octree(g.irradiance_points, g.cie[1])
+        ref = tree.mo(g.hits["p"][s], g.profile_rd, g.profile_hdr[:, 1], g.max_error)
+        e = row_rel_err(dev.mo(g.hits["p"][s], g.max_error), ref)
+        assert e.max() < 1e-5, "Mo vs oracle: %.3g" % e.max()
     finally:
         dev.close()
