@@ -257,6 +257,18 @@ def main():
                           "k_mo": {"GBps": mo_bytes / (stage_ms["mo"] * 1e-3) / 1e9, "ms": stage_ms["mo"], "nodes": int(c_cam[2]), "leaf_points": int(c_cam[3]),
                                    "cluster_contribs": int(c_cam[4]), "point_contribs": int(c_cam[5])}}}
 
+    # ---- multi-GPU self-check (untimed): the sharded + all-gathered octree must equal the one built
+    # from a full local irradiance pass, bit for bit (root p / sumArea / Et) on every rank
+    mg_check = None
+    if world > 1:
+        import torch
+        _, root_sharded, _ = dev.build_octree()
+        dev.irradiance_resident(0, n_pts, n_tasks, scene.mix)
+        dev.set_point_count(n_pts)
+        _, root_full, _ = dev.build_octree()
+        same = bool(np.array_equal(root_sharded.view(np.uint32), root_full.view(np.uint32)))
+        t = torch.tensor([1 if same else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        mg_check = "octree root bit-exact vs single-GPU pass on all ranks" if int(t.item()) == 1 else "MISMATCH"
     if rank != 0:
         return
     out = {
@@ -277,6 +289,8 @@ def main():
         "clocks": summarise_clocks(lines),
         "roofline": roofline,
     }
+    if mg_check:
+        out["multi_gpu_check"] = mg_check
     if world == 1 and not args.no_cpu_baseline:
         drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
         if os.path.exists(drv):
