@@ -1,9 +1,439 @@
-// skc_profile.cu -- MPC_ComputeDiffusionProfile on the device (batched).  Under construction.
+// skc_profile.cu -- MPC_ComputeDiffusionProfile (+ uniform-r^2 resample) on the device, batched.
+//
+// Reference: multipole/MultipoleProfileCalculator/MultipoleProfileCalculator.cpp:151-230
+// (ComputeLayerProfile), :233-280 (To{Frequency,Time}Domain, CombineLayerProfiles), :294-346
+// (MPC_ComputeDiffusionProfile), :355-426 (resample), DipoleCalculator.cpp:38-91, numutil.h
+// (ScaleAndShift, Sum); FFT = kissfft 1.3.0 kiss_fftndr in double.
+//
+// Per parameter set (one wavelength of one layer stack):
+//   k_layer_profile   one thread per octant cell of the (2L)^2 grid: 11 dipole pairs in the
+//                     reference's fp32 arithmetic, accumulated in double in its order, thin-slab
+//                     lerp, centre delta, 8-fold mirroring -- writes z = R + iT
+//   combine           the layer grids are real and even, so their spectra are real: ONE complex
+//                     FFT of z = R + iT yields FR (real part) and FT (imaginary part).  Two
+//                     forward 2-D FFTs (4L)^2 + pointwise adding equations + one inverse replace the
+//                     reference's four real forward and two inverse transforms.
+//   k_fft_rows        one CTA per row, row in shared memory (double2), radix-2 DIT, twiddle table
+//   k_transpose       32x32 tiles through shared memory
+//   k_extract/k_resample  the reference's unique-radius list (host-built index table, it is
+//                     data independent) and its lower_bound + fp32 lerp
+#include <algorithm>
+#include <map>
+#include <vector>
+#include <math.h>
+#include <string.h>
 #include "skc_internal.h"
+
+// ---------------------------------------------------------------------------------------------
+struct DipoleSet {            // DipoleCalculator members for zi = -5..5 (DipoleCalculator.cpp:51-69)
+    float zpos[11], zneg[11];
+    float d, sigma_tr, alphap;
+    double lerp;              // thin-slab factor (MultipoleProfileCalculator.cpp:163-171)
+    double normalize;         // stepSize*stepSize
+    float step2;              // (float)(stepSize*stepSize)
+};
+
+static float FresnelDiffuseReflectance(float eta) {   // DipoleCalculator.cpp:38-45
+    if (eta >= 1.f) return -1.4399f / (eta * eta) + 0.7099f / eta + 0.6681f + 0.0636f * eta;
+    float eta2 = eta * eta;
+    return -0.4399f + 0.7099f / eta - 0.3319f / eta2 + 0.0636f / (eta2 * eta);
+}
+
+static DipoleSet makeDipoles(const skc_layer_spec &spec, float iorUpper, float iorLower, float stepSize, bool lerpOnThinSlab) {
+    DipoleSet ds;
+    float thickness = spec.thickness;
+    double mfp2 = 2. / (spec.mua + spec.musp);
+    double lerp = 1.;
+    if (lerpOnThinSlab) {
+        lerp = (thickness < mfp2) ? (1. - exp(-thickness * 2. / mfp2)) / (1. - exp(-2.)) : 1.;
+        if (thickness < 0.01 * mfp2) thickness = (float)(0.01 * mfp2);
+    }
+    ds.lerp = lerp;
+    ds.step2 = stepSize * stepSize;
+    ds.normalize = (double)ds.step2;
+    float sigma_a = spec.mua, sigmap_s = spec.musp, d = thickness;
+    float sigmap_t = sigma_a + sigmap_s;
+    ds.d = d;
+    ds.sigma_tr = sqrtf(3 * sigma_a * sigmap_t);
+    ds.alphap = sigmap_s / sigmap_t;
+    float Fdr0 = FresnelDiffuseReflectance(iorUpper), Fdrd = FresnelDiffuseReflectance(iorLower);
+    float A_0 = (1.f + Fdr0) / (1.f - Fdr0), A_d = (1.f + Fdrd) / (1.f - Fdrd);
+    float D = 1.f / (3.f * sigmap_t);
+    float zb_0 = 2.f * A_0 * D, zb_d = 2.f * A_d * D;
+    float l = 1.f / sigmap_t;
+    if (lerpOnThinSlab && l > d * .5f) l = d * .5f;
+    for (int zi = -5; zi <= 5; ++zi) {
+        float zpos = 2.f * (float)zi * (d + zb_0 + zb_d) + l;
+        ds.zpos[zi + 5] = zpos;
+        ds.zneg[zi + 5] = zpos - 2.f * (l + zb_0);
+    }
+    return ds;
+}
+
+// expf as glibc >= 2.27 computes it (sysdeps/ieee754/flt-32/e_expf.c: 32-entry 2^(i/32) table, cubic in
+// double, one rounding to float), so that the dipole sums -- which cancel heavily for thin slabs without the
+// lerp -- see the same fp32 inputs as the reference run on a glibc host.  A correctly rounded expf differs from
+// it in ~5e-4 of all arguments by one ulp, which the cancellation amplifies to ~1e-5 of the table value.
+__constant__ unsigned long long c_exp2Tab[32];
+static void uploadExpTable(cudaStream_t st) {
+    unsigned long long tab[32];
+    for (int i = 0; i < 32; ++i) {
+        double v = (double)exp2l(i / 32.0L);
+        unsigned long long u; memcpy(&u, &v, 8);
+        tab[i] = u - (((unsigned long long)i << 52) / 32);
+    }
+    cudaMemcpyToSymbolAsync(c_exp2Tab, tab, sizeof(tab), 0, cudaMemcpyHostToDevice, st);
+    cudaStreamSynchronize(st);
+}
+__device__ __forceinline__ float expf_glibc(float x, const unsigned long long *tab) {
+    if (x < -0x1.9fe368p6f) return 0.f;
+    const double N = 32, shift = 0x1.8p+52, inv = 0x1.71547652b82fep+0 * N;
+    const double C0 = 0x1.c6af84b912394p-5 / N / N / N, C1 = 0x1.ebfce50fac4f3p-3 / N / N, C2 = 0x1.62e42ff0c52d6p-1 / N;
+    double z = inv * (double)x, kd = z + shift;
+    unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd -= shift;
+    double r = z - kd;
+    double s = __longlong_as_double((long long)(tab[ki & 31] + (ki << 47)));
+    z = C0 * r + C1;
+    double r2 = r * r, y = C2 * r + 1.;
+    y = z * r2 + y;
+    return (float)(y * s);
+}
+
+#define INV_FOURPI_F (0.25f / 3.141592654f)   /* numutil.h:45-46 */
+
+// z[G][G] (double2 = {R, T}); one thread per (row<=col) cell of the [0,extent]^2 quadrant
+__global__ void k_layer_profile(DipoleSet ds, uint32_t G, double2 *__restrict__ z) {
+    uint32_t center = (G - 1) / 2, extent = center;
+    __shared__ unsigned long long sTab[32];
+    if (threadIdx.y == 0) sTab[threadIdx.x] = c_exp2Tab[threadIdx.x];
+    __syncthreads();
+    uint32_t col = blockIdx.x * blockDim.x + threadIdx.x, row = blockIdx.y * blockDim.y + threadIdx.y;
+    if (row > extent || col > extent || col < row) return;
+    double drow2 = (double)(row * row), dcol2 = (double)(col * col);
+    double r2 = (drow2 + dcol2) * (double)ds.step2;
+    float dsq = (float)r2;
+    double R = 0., T = 0.;
+    for (int k = 0; k < 11; ++k) {
+        float zpos = ds.zpos[k], zneg = ds.zneg[k], d = ds.d, str = ds.sigma_tr;
+        {   // DipoleCalculator::Rd (DipoleCalculator.cpp:71-80)
+            float dpos = sqrtf(dsq + zpos * zpos), dneg = sqrtf(dsq + zneg * zneg);
+            float dpos3 = dpos * dpos * dpos, dneg3 = dneg * dneg * dneg;
+            float rd = ds.alphap * INV_FOURPI_F * (zpos * (1 + str * dpos) * expf_glibc(-str * dpos, sTab) / dpos3 -
+                                                   zneg * (1 + str * dneg) * expf_glibc(-str * dneg, sTab) / dneg3);
+            R += (double)rd * ds.normalize;
+        }
+        {   // DipoleCalculator::Td (:82-91)
+            float dpos = sqrtf(dsq + (d - zpos) * (d - zpos)), dneg = sqrtf(dsq + (d - zneg) * (d - zneg));
+            float dpos3 = dpos * dpos * dpos, dneg3 = dneg * dneg * dneg;
+            float td = ds.alphap * INV_FOURPI_F * ((d - zpos) * (1 + str * dpos) * expf_glibc(-str * dpos, sTab) / dpos3 -
+                                                   (d - zneg) * (1 + str * dneg) * expf_glibc(-str * dneg, sTab) / dneg3);
+            T += (double)td * ds.normalize;
+        }
+    }
+    if (ds.lerp < 1.) {
+        R *= ds.lerp; T *= ds.lerp;
+        if (row == 0 && col == 0) T += 1. - ds.lerp;
+    }
+    double2 v = make_double2(R, T);
+    // symmetric fill (MultipoleProfileCalculator.cpp:210-229)
+    uint32_t rr[2] = {center + row, center - row}, cc[2] = {center + col, center - col};
+    for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+            z[(size_t)rr[a] * G + cc[b]] = v;
+            z[(size_t)cc[b] * G + rr[a]] = v;
+        }
+}
+
+// Z[N][N] <- ScaleAndShift(grid, center) (numutil.h:192-204): grid cell (i,j) -> ((i-c) mod N, (j-c) mod N)
+__global__ void k_pack(const double2 *__restrict__ z, uint32_t G, uint32_t N, double2 *__restrict__ Z) {
+    uint32_t jj = blockIdx.x * blockDim.x + threadIdx.x, ii = blockIdx.y;
+    if (jj >= N) return;
+    uint32_t c = (G - 1) / 2;
+    uint32_t i = (ii + c) % N, j = (jj + c) % N;
+    Z[(size_t)ii * N + jj] = (i < G && j < G) ? z[(size_t)i * G + j] : make_double2(0., 0.);
+}
+
+// in-place FFT of every row of Z[rows][N]; N a power of two <= 4096; sign = -1 forward, +1 inverse
+__global__ void k_fft_rows(double2 *__restrict__ Z, uint32_t N, uint32_t logN, const double2 *__restrict__ tw, int inverse) {
+    extern __shared__ double2 s[];
+    double2 *row = Z + (size_t)blockIdx.x * N;
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) s[__brev(i) >> (32 - logN)] = row[i];
+    __syncthreads();
+    for (uint32_t st = 1; st <= logN; ++st) {
+        uint32_t half = 1u << (st - 1), stride = N >> st;
+        for (uint32_t b = threadIdx.x; b < N / 2; b += blockDim.x) {
+            uint32_t pos = b & (half - 1), i0 = ((b >> (st - 1)) << st) + pos, i1 = i0 + half;
+            double2 w = tw[pos * stride];
+            if (inverse) w.y = -w.y;
+            double2 a = s[i0], c = s[i1];
+            double2 t = make_double2(w.x * c.x - w.y * c.y, w.x * c.y + w.y * c.x);
+            s[i0] = make_double2(a.x + t.x, a.y + t.y);
+            s[i1] = make_double2(a.x - t.x, a.y - t.y);
+        }
+        __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) row[i] = s[i];
+}
+
+__global__ void k_transpose(const double2 *__restrict__ in, uint32_t N, double2 *__restrict__ out) {
+    __shared__ double2 tile[32][33];
+    uint32_t x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * 32;
+    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) tile[k][threadIdx.x] = in[(size_t)(y0 + k) * N + x];
+    __syncthreads();
+    uint32_t xo = blockIdx.y * 32 + threadIdx.x, yo0 = blockIdx.x * 32;
+    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) out[(size_t)(yo0 + k) * N + xo] = tile[threadIdx.x][k];
+}
+
+// adding equations in the frequency domain (MultipoleProfileCalculator.cpp:253-280).  R and T are real, so the
+// transform of z = R + iT separates into the two Hermitian spectra FR(k) = (Z(k) + conj Z(-k))/2 and
+// FT(k) = (Z(k) - conj Z(-k))/(2i); a fresh layer grid is even (real spectra) but a combined one is not quite
+// (its last row/column has no mirror partner), so the general form is used throughout.  The result is packed
+// the same way, W = FR12 + i FT12, and one inverse transform returns R12 in the real and T12 in the imaginary part.
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ double2 cdiv(double2 a, double2 b) {
+    double d = b.x * b.x + b.y * b.y;
+    return make_double2((a.x * b.x + a.y * b.y) / d, (a.y * b.x - a.x * b.y) / d);
+}
+__device__ __forceinline__ void splitSpectra(double2 zk, double2 zm, double2 &FR, double2 &FT) {
+    // zm = Z(-k); conj(zm) = (zm.x, -zm.y)
+    FR = make_double2(0.5 * (zk.x + zm.x), 0.5 * (zk.y - zm.y));
+    double dx = zk.x - zm.x, dy = zk.y + zm.y;              // Z(k) - conj Z(-k)
+    FT = make_double2(0.5 * dy, -0.5 * dx);                // divided by 2i
+}
+__global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restrict__ Z2, uint32_t N, double2 *__restrict__ W) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, a = blockIdx.y;
+    if (b >= N) return;
+    size_t i = (size_t)a * N + b, j = (size_t)((N - a) & (N - 1)) * N + ((N - b) & (N - 1));
+    double2 R1, T1, R2, T2;
+    splitSpectra(Z1[i], Z1[j], R1, T1);
+    splitSpectra(Z2[i], Z2[j], R2, T2);
+    double2 one = cmul(R2, R1);
+    one = make_double2(1. - one.x, -one.y);
+    double2 R12 = cdiv(cmul(cmul(T1, R2), T1), one);
+    R12.x += R1.x; R12.y += R1.y;
+    double2 T12 = cdiv(cmul(T1, T2), one);
+    W[i] = make_double2(R12.x - T12.y, R12.y + T12.x);
+}
+
+// ScaleAndShiftReversed (numutil.h:205-217) of the inverse transform, scaled by 1/N^2 (:132-139)
+__global__ void k_unpack(const double2 *__restrict__ W, uint32_t N, uint32_t G, double2 *__restrict__ z) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= G) return;
+    uint32_t c = (G - 1) / 2;
+    uint32_t ii = (N - c + i) % N, jj = (N - c + j) % N;
+    double scale = (double)1 / ((double)N * (double)N);
+    double2 v = W[(size_t)ii * N + jj];
+    z[(size_t)i * G + j] = make_double2(v.x * scale, v.y * scale);
+}
+
+// block sums of R and T over the grid (totalReflectance / totalTransmittance, :338-339)
+__global__ void k_grid_sum(const double2 *__restrict__ z, size_t n, double2 *__restrict__ partial) {
+    __shared__ double2 s[256];
+    double r = 0., t = 0.;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) { r += z[i].x; t += z[i].y; }
+    s[threadIdx.x] = make_double2(r, t);
+    __syncthreads();
+    for (int st = 128; st > 0; st >>= 1) {
+        if (threadIdx.x < st) { s[threadIdx.x].x += s[threadIdx.x + st].x; s[threadIdx.x].y += s[threadIdx.x + st].y; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[blockIdx.x] = s[0];
+}
+
+// unique radii (:316-330): entry e <- grid cell idx[e] = (i, j); d2 = (float)(i*i+j*j)*step*step
+__global__ void k_extract(const double2 *__restrict__ z, uint32_t G, const uint2 *__restrict__ idx, uint32_t nEntries, float stepSize,
+                          float *__restrict__ d2, float *__restrict__ R, float *__restrict__ T) {
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nEntries) return;
+    uint32_t c = G / 2 - 1;       // center = length - 1
+    uint2 ij = idx[e];
+    float denorm = 1.f / (stepSize * stepSize);
+    double2 v = z[(size_t)(c + ij.x) * G + (c + ij.y)];
+    d2[e] = (float)(ij.x * ij.x + ij.y * ij.y) * stepSize * stepSize;
+    R[e] = (float)v.x * denorm;
+    T[e] = (float)v.y * denorm;
+}
+
+// MPC_ResampleForUniformDistanceSquaredDistribution (:404-426) with resample (:355-402)
+__global__ void k_resample(const float *__restrict__ d2, const float *__restrict__ R, const float *__restrict__ T, uint32_t len,
+                           uint32_t target, float *__restrict__ od2, float *__restrict__ oR, float *__restrict__ oT) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= target) return;
+    float extent = d2[len - 1];
+    float dsq = (float)i * extent / (float)(target - 1);
+    od2[i] = dsq;
+    float r, t;
+    if (dsq > extent) { r = t = 0.f; }
+    else {
+        uint32_t lo = 0, hi = len - 1;          // first index with d2[lo] >= dsq, capped at len-1
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (dsq > d2[mid]) lo = mid + 1; else hi = mid; }
+        if (lo) {
+            float la = (dsq - d2[lo - 1]) / (d2[lo] - d2[lo - 1]);
+            la = la <= 0.f ? 0.f : (la >= 1.f ? 1.f : la);   // Clamp (template above :348-353)
+            if (la != la) la = 0.5f;
+            r = (1.f - la) * R[lo - 1] + la * R[lo];
+            t = (1.f - la) * T[lo - 1] + la * T[lo];
+        } else { r = R[0]; t = T[0]; }
+    }
+    oR[i] = r; oT[i] = t;
+}
+
+// ---------------------------------------------------------------------------------------------
+static uint32_t roundUpPow2(uint32_t v) { v--; v |= v >> 1; v |= v >> 2; v |= v >> 4; v |= v >> 8; v |= v >> 16; return v + 1; }
+
+// the reference's std::set<OutEntry> keyed by distanceSquared: unique i*i+j*j <= extent^2 in
+// ascending order, first inserted (smallest i) wins (:316-330)
+static std::vector<uint2> uniqueRadii(uint32_t length) {
+    uint32_t extent = length - 1;
+    std::map<uint32_t, uint2> m;
+    for (uint32_t i = 0; i <= extent; i++)
+        for (uint32_t j = i; i * i + j * j <= extent * extent; j++) m.insert({i * i + j * j, make_uint2(i, j)});
+    std::vector<uint2> v;
+    v.reserve(m.size());
+    for (auto &kv : m) v.push_back(kv.second);
+    return v;
+}
+
+struct ProfileWork {
+    double2 *grid[2] = {nullptr, nullptr}, *Z[3] = {nullptr, nullptr, nullptr}, *tw = nullptr, *partial = nullptr;
+    uint2 *idx = nullptr;
+    float *raw = nullptr, *res = nullptr;
+    uint32_t G = 0, N = 0, nEntries = 0;
+    void release() {
+        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res};
+        for (void *q : p) if (q) cudaFree(q);
+        *this = ProfileWork();
+    }
+};
+
+static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t logN, int inverse) {
+    // rows of A in place, transpose into B, rows of B in place: B holds the 2-D transform (transposed layout)
+    uint32_t N = w.N, threads = std::min(N / 2, 1024u);
+    k_fft_rows<<<N, threads, N * sizeof(double2), ctx->stream>>>(A, N, logN, w.tw, inverse);
+    SKC_LAUNCHED("k_fft_rows");
+    k_transpose<<<dim3(N / 32, N / 32), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
+    SKC_LAUNCHED("k_transpose");
+    k_fft_rows<<<N, threads, N * sizeof(double2), ctx->stream>>>(B, N, logN, w.tw, inverse);
+    SKC_LAUNCHED("k_fft_rows");
+    return 0;
+}
 
 extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, const uint32_t *layersPerSet,
                                  const skc_mpc_options *opts, uint32_t nSets, int resample,
                                  uint32_t *lenOut, float *d2, float *R, float *T, float *totals) {
-    (void)specs; (void)layersPerSet; (void)opts; (void)nSets; (void)resample; (void)lenOut; (void)d2; (void)R; (void)T; (void)totals;
-    return skc_fail(ctx, "skc_profile_batch: not implemented yet");
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!nSets) { if (lenOut) *lenOut = 0; return 0; }
+    uint32_t length = roundUpPow2(opts[0].desiredLength);
+    for (uint32_t s = 0; s < nSets; ++s) {
+        if (roundUpPow2(opts[s].desiredLength) != length) return skc_fail(ctx, "skc_profile_batch: all sets of a batch must share desiredLength");
+        if (!layersPerSet[s]) return skc_fail(ctx, "skc_profile_batch: set %u has no layers", s);
+    }
+    if (length < 2 || length > 1024) return skc_fail(ctx, "skc_profile_batch: desiredLength %u out of range (2..1024)", length);
+    std::vector<uint2> radii = uniqueRadii(length);
+    uint32_t nEntries = (uint32_t)radii.size(), outLen = resample ? 2 * nEntries : nEntries;
+    if (lenOut) *lenOut = outLen;
+    if (!d2 && !R && !T && !totals) return 0;
+
+    ProfileWork w;
+    w.G = 2 * length; w.N = 2 * w.G; w.nEntries = nEntries;
+    uint32_t G = w.G, N = w.N, logN = 0;
+    while ((1u << logN) < N) ++logN;
+    if (N * sizeof(double2) > 48 * 1024)
+        SKC_CUDA(cudaFuncSetAttribute(k_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * sizeof(double2))));
+    int rc = 1;
+    do {
+        bool multi = false;
+        for (uint32_t s = 0; s < nSets; ++s) multi |= layersPerSet[s] > 1;
+        if (cudaMalloc((void **)&w.grid[0], (size_t)G * G * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.grid[1], (size_t)G * G * sizeof(double2)) != cudaSuccess) break;
+        if (multi) {
+            bool ok = true;
+            for (int k = 0; k < 3; ++k) ok &= cudaMalloc((void **)&w.Z[k], (size_t)N * N * sizeof(double2)) == cudaSuccess;
+            if (!ok) break;
+            std::vector<double2> tw(N / 2);
+            for (uint32_t k = 0; k < N / 2; ++k) { long double a = -2.0L * 3.14159265358979323846264338327950288L * k / N; tw[k] = make_double2((double)cosl(a), (double)sinl(a)); }
+            if (cudaMalloc((void **)&w.tw, tw.size() * sizeof(double2)) != cudaSuccess) break;
+            if (cudaMemcpyAsync(w.tw, tw.data(), tw.size() * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
+            if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
+        }
+        if (cudaMalloc((void **)&w.partial, 256 * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.idx, nEntries * sizeof(uint2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.raw, 3 * (size_t)nEntries * sizeof(float)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.res, 3 * (size_t)outLen * sizeof(float)) != cudaSuccess) break;
+        if (cudaMemcpyAsync(w.idx, radii.data(), nEntries * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
+        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
+        rc = 0;
+    } while (0);
+    if (rc) { w.release(); return skc_fail(ctx, "skc_profile_batch: device allocation failed (%s)", cudaGetErrorString(cudaGetLastError())); }
+
+    uploadExpTable(ctx->stream);
+    skc_stage_begin(ctx);
+    const skc_layer_spec *sp = specs;
+    std::vector<double2> hpart(256);
+    uint32_t ext = (G - 1) / 2 + 1;
+    dim3 lpBlock(32, 8), lpGrid((ext + 31) / 32, (ext + 7) / 8);
+    for (uint32_t s = 0; s < nSets && !rc; ++s) {
+        uint32_t nL = layersPerSet[s];
+        float stepSize = opts[s].desiredStepSize;
+        bool lerpThin = opts[s].lerpOnThinSlab != 0;
+        auto layer = [&](uint32_t l, double2 *dst) -> int {
+            float iorUpper = l == 0 ? sp[0].ior : sp[l].ior / sp[l - 1].ior;                     // :303-309
+            float iorLower = nL > l + 1 ? sp[l].ior / sp[l + 1].ior : sp[l].ior;
+            DipoleSet ds = makeDipoles(sp[l], iorUpper, iorLower, stepSize, lerpThin);
+            SKC_CUDA(cudaMemsetAsync(dst, 0, (size_t)G * G * sizeof(double2), ctx->stream));   // profile.Clear()
+            k_layer_profile<<<lpGrid, lpBlock, 0, ctx->stream>>>(ds, G, dst);
+            SKC_LAUNCHED("k_layer_profile");
+            return 0;
+        };
+        rc = layer(0, w.grid[0]);
+        for (uint32_t l = 1; l < nL && !rc; ++l) {
+            if ((rc = layer(l, w.grid[1]))) break;
+            dim3 pg((N + 255) / 256, N);
+            k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[0], G, N, w.Z[0]);
+            k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[1], G, N, w.Z[1]);
+            ctx->launches += 2;
+            // forward: Z0 -> Z2 (transposed spectrum of layer 1); Z1 -> Z0 (layer 2)
+            if ((rc = fft2d(ctx, w, w.Z[0], w.Z[2], logN, 0))) break;
+            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[0], logN, 0))) break;
+            k_adding<<<dim3((N + 255) / 256, N), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
+            ctx->launches++;
+            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[2], logN, 1))) break;      // back to the natural layout
+            k_unpack<<<dim3((G + 255) / 256, G), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0]);
+            ctx->launches++;
+        }
+        if (rc) break;
+        float *rawD = w.raw, *rawR = w.raw + nEntries, *rawT = w.raw + 2 * (size_t)nEntries;
+        k_extract<<<(nEntries + 255) / 256, 256, 0, ctx->stream>>>(w.grid[0], G, w.idx, nEntries, stepSize, rawD, rawR, rawT);
+        ctx->launches++;
+        const float *oD = rawD, *oR = rawR, *oT = rawT;
+        if (resample) {
+            float *rD = w.res, *rR = w.res + outLen, *rT = w.res + 2 * (size_t)outLen;
+            k_resample<<<(outLen + 255) / 256, 256, 0, ctx->stream>>>(rawD, rawR, rawT, nEntries, outLen, rD, rR, rT);
+            ctx->launches++;
+            oD = rD; oR = rR; oT = rT;
+        }
+        if (totals) {
+            k_grid_sum<<<256, 256, 0, ctx->stream>>>(w.grid[0], (size_t)G * G, w.partial);
+            ctx->launches++;
+            if (cudaMemcpyAsync(hpart.data(), w.partial, 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        }
+        if (d2 && cudaMemcpyAsync(d2 + (size_t)s * outLen, oD, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        if (R && cudaMemcpyAsync(R + (size_t)s * outLen, oR, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        if (T && cudaMemcpyAsync(T + (size_t)s * outLen, oT, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { rc = 1; break; }
+        if (totals) {
+            double r = 0., t = 0.;
+            for (int k = 0; k < 256; ++k) { r += hpart[k].x; t += hpart[k].y; }
+            totals[2 * s] = (float)r; totals[2 * s + 1] = (float)t;
+        }
+        sp += nL;
+    }
+    if (!rc) skc_stage_end(ctx, 6);
+    cudaError_t e = cudaGetLastError();
+    cudaStreamSynchronize(ctx->stream);
+    w.release();
+    if (rc || e != cudaSuccess) return skc_fail(ctx, "skc_profile_batch: %s", ctx->err.empty() ? cudaGetErrorString(e) : ctx->err.c_str());
+    return 0;
 }

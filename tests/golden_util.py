@@ -80,3 +80,25 @@ def smoke_check(pkg):
         assert e.max() < 1e-5, "Mo vs oracle: %.3g" % e.max()
     finally:
         dev.close()
+
+
+def load_mpc_cases():
+    """tests/golden/mpc_kat.npz -> list of (specs, opts, resample, totals, d2_R_T); the step size follows
+    core/multipole.cpp:262-268 (12 * mean mfp / desiredLength) in fp32, as the generating driver did."""
+    z = np.load(os.path.join(GOLDEN, "mpc_kat.npz"))
+    out = []
+    i = 0
+    while "case%d_spec" % i in z.files:
+        s = z["case%d_spec" % i]
+        nl, dl, lerp, res, step = int(s[0]), int(s[1]), int(s[2]), int(s[3]), np.float32(s[4])
+        layers = s[5:].reshape(nl, 4).astype(np.float32)
+        if not step > 0:
+            tot = np.float32(0)
+            for l in layers:
+                tot = np.float32(tot + np.float32(1) / np.float32(l[2] + l[3]))
+            mfp = np.float32(tot / np.float32(nl))
+            step = np.float32(np.float32(np.float32(12) * mfp) / np.float32(dl))
+        specs = [(l[0], l[1], l[2], l[3], 0.0) for l in layers]
+        out.append((specs, (step, dl, lerp), res, z["case%d_totals" % i], z["case%d_d2_R_T" % i]))
+        i += 1
+    return out

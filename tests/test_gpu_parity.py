@@ -233,3 +233,38 @@ def test_irradiance_dense_vs_oracle(dev, scene, pkg):
     a = len(pts) // 3
     part = dev.irradiance(pts, n_tasks, g.mix, first=a, count=len(pts) - 2 * a)
     assert np.array_equal(part["E"], irr["E"][a:len(pts) - a])
+
+
+def _profile_err(got, ref):
+    """Relative error against the table's own peak scale: the reference's fp64 FFT leaves a noise floor of
+    ~1e-16 x peak in the far tail, so entries below 1e-9 x peak are compared absolutely against that floor."""
+    got = np.asarray(got, np.float64); ref = np.asarray(ref, np.float64)
+    floor = np.abs(ref).max() * 1e-9
+    return np.abs(got - ref) / np.maximum(np.abs(ref), floor)
+
+
+@pytest.mark.gpu
+def test_profile_batch_known_answers(pkg, dev):
+    """a10: skc_profile_batch vs MPC_ComputeDiffusionProfile (+ resample) of the real reference, 1e-5 relative
+    (BASELINE.json tolerance for profile tables); d2 abscissae and lengths bit-exact."""
+    from golden_util import load_mpc_cases
+    for k, (specs, opt, res, totals, ref) in enumerate(load_mpc_cases()):
+        d2, R, T, tot = dev.profile_batch(specs, [len(specs)], [opt], resample=bool(res))
+        assert d2.shape[1] == ref.shape[1], "case %d length %d != %d" % (k, d2.shape[1], ref.shape[1])
+        assert np.array_equal(d2[0], ref[0]), "case %d: d2 abscissae differ" % k
+        eR, eT = _profile_err(R[0], ref[1]).max(), _profile_err(T[0], ref[2]).max()
+        print("mpc case %d: len %d  max rel R %.3g T %.3g  totals %s vs %s" % (k, d2.shape[1], eR, eT, tot[0], totals))
+        assert eR < 1e-5 and eT < 1e-5, "case %d: R %.3g T %.3g" % (k, eR, eT)
+        assert np.allclose(tot[0], totals, rtol=1e-5, atol=0)
+
+
+@pytest.mark.gpu
+def test_profile_batch_is_batched(pkg, dev):
+    """Several parameter sets in one call give the same tables as one call per set."""
+    from golden_util import load_mpc_cases
+    cases = [c for c in load_mpc_cases() if c[1][1] == 64 and c[2] == 1]
+    specs = [s for c in cases for s in c[0]]
+    d2, R, T, tot = dev.profile_batch(specs, [len(c[0]) for c in cases], [c[1] for c in cases], resample=True)
+    for k, c in enumerate(cases):
+        a = dev.profile_batch(c[0], [len(c[0])], [c[1]], resample=True)
+        assert np.array_equal(a[1][0], R[k]) and np.array_equal(a[2][0], T[k]) and np.array_equal(a[3][0], tot[k])
