@@ -1,7 +1,9 @@
 // skin_integrator.cpp -- MultipoleSubsurfaceIntegrator on the device + the C interface the
 // Python tests/bench bind (skh_*).  Mirrors integrators/multipolesubsurface.cpp:170-304.
 #include "skin_scene.h"
+#include "skin_material.h"
 #include <cstdio>
+#include <cstring>
 
 namespace skin {
 
@@ -125,6 +127,36 @@ uint64_t skh_bench_rays(skh_scene *s, const void **rays) {
 // nTasks of IrradianceTask (multipolesubsurface.cpp:194-199)
 uint32_t skh_irradiance_tasks(uint64_t nPoints, int nCores) {
     return RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPoints / 4096));
+}
+
+// LayeredSkin layer coefficients (a11): out124 = [layer][mua30 | musp30], eta[2], thickness[2]
+void skh_skin_coefficients(const skh_scene *s, float *out124) {
+    SkinLayerSpectra sp = ComputeSkinLayerSpectra(s->sd.skin);
+    float *o = out124;
+    for (int l = 0; l < 2; ++l) { memcpy(o, sp.mua[l], 120); o += 30; memcpy(o, sp.musp[l], 120); o += 30; }
+    o[0] = sp.eta[0]; o[1] = sp.eta[1]; o[2] = sp.thickness[0]; o[3] = sp.thickness[1];
+}
+// ComputeMultipoleProfile on the device for the scene's skin material and upload of the result together
+// with the caller's rho_hd table (skc_upload_profile).  hdr120 = [30][dsqSpacing, rcpDsqSpacing, totalR, totalT];
+// rdOut (optional) receives [30][len].  Two-phase like skc_profile_batch: rdOut == NULL only reports len.
+int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *len, float *hdr120, float *rdOut, int upload) {
+    SkinLayerSpectra sp = ComputeSkinLayerSpectra(s->sd.skin);
+    if (!hdr120 && !rdOut && !upload) {
+        std::vector<skc_layer_spec> specs; std::vector<uint32_t> lps; std::vector<skc_mpc_options> opts;
+        BuildProfileJobs(sp, s->sd.skin.desiredlength, s->sd.skin.lerponthinslab, specs, lps, opts);
+        return skc_profile_batch(ctx, specs.data(), lps.data(), opts.data(), kWavelengths, 1, len, nullptr, nullptr, nullptr, nullptr);
+    }
+    ProfileTable t;
+    int rc = ComputeMultipoleProfile(ctx, sp, s->sd.skin.desiredlength, s->sd.skin.lerponthinslab, t);
+    if (rc) return rc;
+    if (len) *len = t.len;
+    if (hdr120) for (int w = 0; w < kWavelengths; ++w) {
+        hdr120[4 * w] = t.dsqSpacing[w]; hdr120[4 * w + 1] = t.rcpDsqSpacing[w];
+        hdr120[4 * w + 2] = t.totalReflectance[w]; hdr120[4 * w + 3] = t.totalTransmittance[w];
+    }
+    if (rdOut) memcpy(rdOut, t.rd.data(), t.rd.size() * sizeof(float));
+    if (upload) return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd);
+    return 0;
 }
 
 }  // extern "C"

@@ -32,6 +32,8 @@ def load_host_library():
     lib.skh_camera_rays.restype = None; lib.skh_camera_rays.argtypes = [vp, vp, C.c_uint64, vp]
     lib.skh_bench_rays.restype = C.c_uint64; lib.skh_bench_rays.argtypes = [vp, C.POINTER(vp)]
     lib.skh_irradiance_tasks.restype = C.c_uint32; lib.skh_irradiance_tasks.argtypes = [C.c_uint64, C.c_int]
+    lib.skh_skin_coefficients.restype = None; lib.skh_skin_coefficients.argtypes = [vp, vp]
+    lib.skh_build_profile.restype = C.c_int; lib.skh_build_profile.argtypes = [vp, vp, vp, C.POINTER(C.c_uint32), vp, vp, C.c_int]
     _lib = lib
     return lib
 
@@ -100,3 +102,26 @@ class HostScene:
     def upload(self, dev):
         dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
         dev.upload_lights(self.lights)
+
+    def skin_coefficients(self):
+        """LayeredSkin layer coefficients (materials/layeredskin.cpp:49-92): dict of mua/musp [2][30], eta[2], thickness[2]."""
+        v = np.zeros(124, np.float32)
+        self.lib.skh_skin_coefficients(self.h, v.ctypes.data_as(C.c_void_p))
+        c = v[:120].reshape(2, 2, 30)
+        return {"flat": v, "mua": c[:, 0], "musp": c[:, 1], "eta": v[120:122], "thickness": v[122:124]}
+
+    def build_profile(self, dev, rho_hd=None, upload=True):
+        """ComputeMultipoleProfile for the scene's skin on the device (30 wavelengths, one batched call); uploads the
+        Rd tables (+ the given rho_hd [1025][30]) into dev's context when upload is set.  Returns (hdr [30][4], rd [30][len])."""
+        ln = C.c_uint32(0)
+        if self.lib.skh_build_profile(self.h, dev.ctx, None, C.byref(ln), None, None, 0):
+            raise SkcError(dev.lib.skc_last_error(dev.ctx).decode())
+        hdr = np.empty((30, 4), np.float32); rd = np.empty((30, int(ln.value)), np.float32)
+        rho = None if rho_hd is None else np.ascontiguousarray(rho_hd, np.float32)
+        if upload and rho is None:
+            raise SkcError("build_profile: upload needs the rho_hd table")
+        rc = self.lib.skh_build_profile(self.h, dev.ctx, None if rho is None else rho.ctypes.data_as(C.c_void_p), C.byref(ln),
+                                        hdr.ctypes.data_as(C.c_void_p), rd.ctypes.data_as(C.c_void_p), int(bool(upload)))
+        if rc:
+            raise SkcError(dev.lib.skc_last_error(dev.ctx).decode())
+        return hdr, rd

@@ -8,10 +8,14 @@ differ more: a shadow ray whose direction differs in the last ulp (sinf/cosf of 
 CUDA) can flip visibility at a silhouette (1/nSamples of one light's contribution); the tests
 state the fraction they allow.
 """
+import os
+
 import numpy as np
 import pytest
 
 import golden_util as gu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -268,3 +272,30 @@ def test_profile_batch_is_batched(pkg, dev):
     for k, c in enumerate(cases):
         a = dev.profile_batch(c[0], [len(c[0])], [c[1]], resample=True)
         assert np.array_equal(a[1][0], R[k]) and np.array_equal(a[2][0], T[k]) and np.array_equal(a[3][0], tot[k])
+
+
+@pytest.mark.gpu
+def test_skin_profile_tables_from_scene(pkg, dev, tiny):
+    """a10+a11 end to end: scene skin parameters -> layer coefficients (host) -> 30 two-layer profiles in one
+    skc_profile_batch call -> Profile tables, against the tables of the reference's LayeredSkin (1e-5 rel)."""
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tiny.scene"))
+    try:
+        hdr, rd = hs.build_profile(dev, tiny.rho_hd[:1025], upload=True)
+    finally:
+        hs.close()
+    assert rd.shape == tiny.profile_rd.shape
+    assert np.array_equal(hdr[:, :2], tiny.profile_hdr[:, :2]), "dsqSpacing / rcpDsqSpacing differ"
+    assert np.allclose(hdr[:, 2], tiny.profile_hdr[:, 2], rtol=1e-5, atol=0)
+    # total transmittance through the 0.5-unit dermis is ~1e-12 or exactly 0 (fp32 underflow of every dipole term) in the
+    # reference; the packed R + iT transform leaves fp64 rounding noise of R (~1e-19) there, hence the absolute floor
+    assert np.allclose(hdr[:, 3], tiny.profile_hdr[:, 3], rtol=1e-5, atol=1e-15)
+    worst = max(_profile_err(rd[w], tiny.profile_rd[w]).max() for w in range(30))
+    print("profile tables: max rel %.3g, bit-exact %.4f" % (worst, np.mean(rd == tiny.profile_rd)))
+    assert worst < 1e-5
+    # the uploaded tables drive Mo: same camera pass result as with the reference's tables
+    gu.setup_device(dev, tiny, tables=False)
+    dev.set_irradiance_points(tiny.irradiance_points)
+    dev.build_octree()
+    s = np.nonzero(tiny.hits["hasBssrdf"] == 1)[0][:256]
+    e = gu.row_rel_err(dev.mo(tiny.hits["p"][s], tiny.max_error), tiny.mo[s])
+    assert e.max() < 1e-4

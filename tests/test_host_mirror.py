@@ -63,3 +63,15 @@ def test_bench_rays_cover_film(host):
     rays = host.bench_rays()
     assert len(rays) == host.xres * host.yres * host.spp
     assert np.isfinite(rays[:, :7]).all()
+
+
+def test_skin_layer_coefficients_bit_exact(pkg, tiny):
+    """a11: pigment model -> 30-bin mua/musp per layer, eta, thickness (materials/layeredskin.cpp:49-92,
+    materials/skincoeffs.h:46-135) against the coefficients the reference's LayeredSkin computed."""
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tiny.scene"))
+    try:
+        c = hs.skin_coefficients()
+        assert np.array_equal(c["flat"], tiny.skin_coeffs)
+        assert c["mua"].shape == (2, 30) and np.all(c["mua"] > 0) and np.all(c["musp"] > 0)
+    finally:
+        hs.close()
