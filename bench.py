@@ -74,12 +74,22 @@ def measured_peak():
         return 6650.0, "fallback"
 
 
-def load_tables():
+def build_material(scene, dev):
+    """LayeredSkin construction on the device: 30 two-layer diffusion profiles (skc_profile_batch) and the rho_hd table
+    (skc_rho_table), uploaded into the context.  Untimed set-up (once per material, not per frame); its device time is
+    reported as material_ms.  When the checker's export of the same scene is around (container runs), compare."""
+    t0 = time.time()
+    hdr, rd = scene.build_profile(dev, None, upload=True)
+    info = {"source": "generated on the device (skc_profile_batch + skc_rho_table)", "profile_len": int(rd.shape[1]),
+            "profile_ms": round(dev.stage_ms("profile"), 3), "rho_ms": round(dev.stage_ms("rho"), 3), "wall_s": round(time.time() - t0, 3)}
     path = os.path.join(ROOT, "scenes", "_generated", "skin_tables.npz")
-    if not os.path.exists(path):
-        raise SystemExit("material tables %s missing (tools/export_material.py; device generation of the profile tables is not wired in yet)" % path)
-    z = np.load(path)
-    return z["profile_rd"], z["profile_hdr"][:, 1].copy(), z["rho_hd"][:1025].copy()
+    if os.path.exists(path) and os.path.basename(scene.path) == "skin.scene":
+        z = np.load(path)
+        if z["profile_rd"].shape == rd.shape:
+            ref = z["profile_rd"].astype(np.float64)
+            floor = np.abs(ref).max(axis=1, keepdims=True) * 1e-9
+            info["vs_reference_tables_max_rel"] = float((np.abs(rd - ref) / np.maximum(np.abs(ref), floor)).max())
+    return info
 
 
 def reference_arm(args):
@@ -135,8 +145,7 @@ def main():
     # ---- workload (host side, untimed): scene, BVH, surface points, camera rays, tables
     scene = pkg.HostScene(args.scene)
     scene.upload(dev)
-    table, rcp, rho = load_tables()
-    dev.upload_profile(table, rcp, rho)
+    material = build_material(scene, dev)
     pts = scene.tessellate()
     rays = scene.bench_rays()
     n_pts, n_rays = len(pts), len(rays)
@@ -277,7 +286,7 @@ def main():
         "config": {"workload": WORKLOAD, "irradiance_points": n_pts, "camera_samples": n_rays, "irradiance_tasks": n_tasks,
                    "l2": "inputs larger than L2 (surface points %.2f GB, octree + points > 4 GB)" % (n_pts * 44 / 1e9),
                    "camera_sample_pattern": "stratified 2x2 per pixel (bench generator; parity tests use the reference's exported LD stream)",
-                   "material_tables": "exported by the reference checker (interim)"},
+                   "material_tables": material},
         "stage_ms": stage_ms,
         "hot_path_seconds": ms_step * 1e-3,
         "rays_per_s": (int(c_irr[2]) * world + n_rays) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),

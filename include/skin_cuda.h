@@ -90,7 +90,7 @@ int skc_synchronize(skc_ctx *ctx);
 /* Counters of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t skc_launch_count(const skc_ctx *ctx);
 /* Device time of the last call of each stage in ms (CUDA events on the ctx stream).
- * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile */
+ * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table */
 float skc_stage_ms(const skc_ctx *ctx, int stage);
 
 /* CUDA-event timer on the context's stream spanning any sequence of calls (bench.py). */
@@ -185,6 +185,14 @@ void skc_free_pinned(void *p);
 int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, const uint32_t *layersPerSet,
                       const skc_mpc_options *opts, uint32_t nSets, int resample,
                       uint32_t *lenOut, float *d2, float *R, float *T, float *totals);
+
+/* ---- rho_hd table ------------------------------------------------
+ * Replaces ComputeRhoDataFromBxDF (core/multipole.cpp:518-549) for the Microfacet(Beckmann(roughness),
+ * FresnelDielectric(etaI, etaT)) lobe LayeredSkin builds (materials/layeredskin.cpp:103-109):
+ * 1025 entries, entry k = BxDF::rho(wo(cos = k/1024), 65536 stratified samples jittered by RNG(6428263*k)).
+ * fixedFresnel != 0 selects FixedFresnelDielectric ("doublerefsslf").  hd30 receives [1025][30] floats
+ * (RhoData::hd as Spectrum rows), the layout skc_upload_profile takes. */
+int skc_rho_table(skc_ctx *ctx, float roughness, float etaI, float etaT, int fixedFresnel, float *hd30);
 
 #ifdef __cplusplus
 }

@@ -137,7 +137,7 @@ void skh_skin_coefficients(const skh_scene *s, float *out124) {
     o[0] = sp.eta[0]; o[1] = sp.eta[1]; o[2] = sp.thickness[0]; o[3] = sp.thickness[1];
 }
 // ComputeMultipoleProfile on the device for the scene's skin material and upload of the result together
-// with the caller's rho_hd table (skc_upload_profile).  hdr120 = [30][dsqSpacing, rcpDsqSpacing, totalR, totalT];
+// with the caller's rho_hd table, or the device-generated one when rhoHd is NULL (skc_upload_profile).  hdr120 = [30][dsqSpacing, rcpDsqSpacing, totalR, totalT];
 // rdOut (optional) receives [30][len].  Two-phase like skc_profile_batch: rdOut == NULL only reports len.
 int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *len, float *hdr120, float *rdOut, int upload) {
     SkinLayerSpectra sp = ComputeSkinLayerSpectra(s->sd.skin);
@@ -155,7 +155,15 @@ int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *
         hdr120[4 * w + 2] = t.totalReflectance[w]; hdr120[4 * w + 3] = t.totalTransmittance[w];
     }
     if (rdOut) memcpy(rdOut, t.rd.data(), t.rd.size() * sizeof(float));
-    if (upload) return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd);
+    if (upload) {
+        std::vector<float> rho;
+        if (!rhoHd) {   // ComputeRhoDataFromBxDF for Microfacet(Beckmann(roughness), FresnelDielectric(1, ior0)), layeredskin.cpp:103-109
+            rho.resize(1025 * 30);
+            if ((rc = skc_rho_table(ctx, s->sd.skin.roughness, 1.f, s->sd.skin.layerIor[0], 0, rho.data()))) return rc;
+            rhoHd = rho.data();
+        }
+        return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd);
+    }
     return 0;
 }
 

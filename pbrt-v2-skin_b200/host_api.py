@@ -50,6 +50,7 @@ class HostScene:
 
     def __init__(self, path):
         self.lib = load_host_library()
+        self.path = path
         err = C.create_string_buffer(512)
         self.h = self.lib.skh_load(path.encode(), err, 512)
         if not self.h:
@@ -112,14 +113,12 @@ class HostScene:
 
     def build_profile(self, dev, rho_hd=None, upload=True):
         """ComputeMultipoleProfile for the scene's skin on the device (30 wavelengths, one batched call); uploads the
-        Rd tables (+ the given rho_hd [1025][30]) into dev's context when upload is set.  Returns (hdr [30][4], rd [30][len])."""
+        Rd tables and rho_hd [1025][30] (the given one, else generated on the device by skc_rho_table) into dev's context when upload is set.  Returns (hdr [30][4], rd [30][len])."""
         ln = C.c_uint32(0)
         if self.lib.skh_build_profile(self.h, dev.ctx, None, C.byref(ln), None, None, 0):
             raise SkcError(dev.lib.skc_last_error(dev.ctx).decode())
         hdr = np.empty((30, 4), np.float32); rd = np.empty((30, int(ln.value)), np.float32)
         rho = None if rho_hd is None else np.ascontiguousarray(rho_hd, np.float32)
-        if upload and rho is None:
-            raise SkcError("build_profile: upload needs the rho_hd table")
         rc = self.lib.skh_build_profile(self.h, dev.ctx, None if rho is None else rho.ctypes.data_as(C.c_void_p), C.byref(ln),
                                         hdr.ctypes.data_as(C.c_void_p), rd.ctypes.data_as(C.c_void_p), int(bool(upload)))
         if rc:

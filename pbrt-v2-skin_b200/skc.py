@@ -20,7 +20,7 @@ DT_MPC_OPTIONS = np.dtype([("desiredStepSize", "<f4"), ("desiredLength", "<u4"),
 assert DT_BVH_NODE.itemsize == 32 and DT_LIGHT.itemsize == 280 and DT_RAY.itemsize == 32 and DT_HIT.itemsize == 56
 assert DT_SURFACE_POINT.itemsize == 44 and DT_IRR_POINT.itemsize == 152
 
-STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6}
+STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6, "rho": 7}
 
 # every symbol include/skin_cuda.h declares
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
@@ -28,7 +28,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_irradiance", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
-           "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count"]
+           "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table"]
 
 
 class SkcError(RuntimeError):
@@ -72,6 +72,8 @@ def load_library():
     lib.skc_mo.restype = i32; lib.skc_mo.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_li_sss.restype = i32; lib.skc_li_sss.argtypes = [vp, vp, u64, f32, f32, vp, vp, vp]
     lib.skc_camera_pass.restype = i32; lib.skc_camera_pass.argtypes = [vp, vp, u64, f32, f32, vp, vp]
+    lib.skc_rho_table.restype = i32
+    lib.skc_rho_table.argtypes = [vp, C.c_float, C.c_float, C.c_float, i32, vp]
     lib.skc_profile_batch.restype = i32
     lib.skc_profile_batch.argtypes = [vp, vp, vp, vp, u32, i32, C.POINTER(u32), vp, vp, vp, vp]
     lib.skc_set_surface_points.restype = i32; lib.skc_set_surface_points.argtypes = [vp, vp, u64]
@@ -262,3 +264,9 @@ class SkinDevice:
         d2 = np.empty((n, L), np.float32); R = np.empty((n, L), np.float32); T = np.empty((n, L), np.float32); tot = np.empty((n, 2), np.float32)
         self._ck(self.lib.skc_profile_batch(self.ctx, _ptr(specs), _ptr(lps), _ptr(opts), n, int(resample), C.byref(ln), _ptr(d2), _ptr(R), _ptr(T), _ptr(tot)))
         return d2, R, T, tot
+
+    def rho_table(self, roughness, eta_t, eta_i=1.0, fixed_fresnel=False):
+        """rho_hd [1025][30] of Microfacet(Beckmann(roughness), FresnelDielectric(eta_i, eta_t)) (core/multipole.cpp:518-549)."""
+        hd = np.empty((1025, 30), np.float32)
+        self._ck(self.lib.skc_rho_table(self.ctx, float(roughness), float(eta_i), float(eta_t), int(fixed_fresnel), _ptr(hd)))
+        return hd
