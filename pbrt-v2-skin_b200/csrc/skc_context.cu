@@ -1,4 +1,6 @@
 // skc_context.cu -- context lifetime, error reporting, scratch memory, stage timing.
+#include <cstdlib>
+#include <cstring>
 #include <stdarg.h>
 #include "skc_common.cuh"
 
@@ -53,6 +55,7 @@ extern "C" skc_ctx *skc_create(int device) {
         delete ctx;
         return nullptr;
     }
+    if (const char *k = getenv("SKC_MO_KERNEL")) ctx->moPacket = strcmp(k, "warp") != 0;
     return ctx;
 }
 

@@ -164,6 +164,140 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Packet variant: one warp walks the octree ONCE for 32 neighbouring shading points (lane = hit).
+// A stack entry is (node, mask of lanes that still have to evaluate it); every lane applies the reference's
+// tests to the node with its own point, accepting lanes add the cluster, the others descend.  Neighbouring
+// camera samples accept the same far clusters at almost the same d2, so the warp's 32 table gathers of one
+// wavelength fall into one or two 128 B lines and the Et / E row is one broadcast load -- the warp-per-hit
+// kernel above spends 30 separate lines per contribution (one per wavelength) and is bound by L1 wavefronts.
+// Each lane keeps its 30 wavelength sums in registers; the result is transposed through shared memory.
+#define MOP_WARPS 4
+#define MOP_STACK 512          // 1 + 7 * levels entries at most (levels <= 64)
+
+template <bool COUNT>
+__device__ __forceinline__ void mopContribute(const MoTables &T, const float *sRcp, const float4 *__restrict__ row4, float d2, float scale,
+                                              bool active, float (&acc)[SKC_NS]) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        float4 e4 = __ldg(row4 + q);
+        float e[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int w = 4 * q + r;
+            if (w < SKC_NS) {
+                float f = d2 * sRcp[w];
+                if (active && f < T.lenM1) {
+                    uint32_t seg = (uint32_t)f;
+                    float t = f - (float)seg;
+                    float2 v = __ldg(&T.pairs[(size_t)w * T.len + seg]);
+                    float rd = (1.f - t) * v.x + t * v.y;
+                    acc[w] += (rd * e[r]) * scale;
+                }
+            }
+        }
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(MOP_WARPS * 32) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+                                                             const int32_t *__restrict__ enable, uint64_t enableStrideInts,
+                                                             uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt) {
+    __shared__ uint2 stacks[MOP_WARPS][MOP_STACK];
+    __shared__ float sRcp[32];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) sRcp[threadIdx.x] = __ldg(&T.rcp[threadIdx.x]);
+    __syncthreads();
+    uint2 *stack = stacks[warp];
+    uint64_t h0 = ((uint64_t)blockIdx.x * MOP_WARPS + warp) * 32, h = h0 + lane;
+    if (h0 >= n) return;
+    bool on = h < n && (enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true);
+    float px = 0.f, py = 0.f, pz = 0.f;
+    if (on) { const float *pp = p3 + h * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
+    float acc[SKC_NS];
+#pragma unroll
+    for (int w = 0; w < SKC_NS; ++w) acc[w] = 0.f;
+    uint32_t wc[4] = {0, 0, 0, 0};
+    unsigned all = __ballot_sync(0xffffffffu, on);
+    int sp = 0;
+    if (all) { if (lane == 0) stack[0] = make_uint2(0u, all); sp = 1; }
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        uint2 ent = stack[sp];
+        __syncwarp();
+        bool mine = (ent.y >> lane) & 1u;
+        const float4 *nd = tr.nodes + 3 * (size_t)ent.x;
+        float4 g = __ldg(nd), b0 = __ldg(nd + 1), b1 = __ldg(nd + 2);
+        uint32_t w0 = __float_as_uint(b1.z), w1 = __float_as_uint(b1.w);
+        if (COUNT) wc[0] += __popc(ent.y);
+        if (w1 & SKC_OT_BLACK) continue;
+        float dx = px - g.x, dy = py - g.y, dz = pz - g.z;
+        float d2 = dx * dx + dy * dy + dz * dz;
+        float dw = g.w / d2;
+        bool inside = px >= b0.x && px <= b0.w && py >= b0.y && py <= b1.x && pz >= b0.z && pz <= b1.y;
+        bool accept = mine && dw < maxError && !inside;
+        bool descend = mine && !accept;
+        bool addC = accept && d2 * T.rcpMin < T.lenM1;
+        if (descend) {      // beyond the table range nothing below contributes
+            float ex = fmaxf(fmaxf(b0.x - px, px - b0.w), 0.f);
+            float ey = fmaxf(fmaxf(b0.y - py, py - b1.x), 0.f);
+            float ez = fmaxf(fmaxf(b0.z - pz, pz - b1.y), 0.f);
+            float db2 = ex * ex + ey * ey + ez * ez;
+            descend = (db2 * 0.999f) * T.rcpMin < T.lenM1;
+        }
+        unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
+        if (am) {
+            if (COUNT) wc[2] += __popc(am);
+            mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.Et + (size_t)ent.x * SKC_EPAD), d2, 1.f, addC, acc);
+        }
+        if (dm) {
+            if (w1 & SKC_OT_LEAF) {
+                uint32_t cntP = w1 & 0xffu;
+                if (COUNT) wc[1] += cntP * __popc(dm);
+                for (uint32_t k = 0; k < cntP; ++k) {
+                    uint32_t slot = w0 + k;
+                    float4 pa = __ldg(&tr.leafPosArea[slot]);
+                    float qx = px - pa.x, qy = py - pa.y, qz = pz - pa.z;
+                    float q2 = qx * qx + qy * qy + qz * qz;
+                    bool c = descend && q2 * T.rcpMin < T.lenM1;
+                    unsigned pm = __ballot_sync(0xffffffffu, c);
+                    if (pm) {
+                        if (COUNT) wc[3] += __popc(pm);
+                        mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q2, pa.w, c, acc);
+                    }
+                }
+            } else {
+                int nc = __popc(w1 & 0xffu);
+                if (lane < nc) stack[sp + lane] = make_uint2(w0 + lane, dm);
+                sp += nc;
+                __syncwarp();
+            }
+        }
+    }
+    // transpose through the (now idle) stack memory: lane = hit -> lane = wavelength rows
+    float *tile = reinterpret_cast<float *>(stack);           // 32 x 33 floats = 4224 B > 4096: use two halves
+    __syncwarp();
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        // hits [16*half, 16*half+16): lanes of that half write their 30 sums, then all lanes stream rows out
+        if ((lane >> 4) == half) {
+#pragma unroll
+            for (int w = 0; w < SKC_NS; ++w) tile[(lane & 15) * 33 + w] = acc[w];
+            tile[(lane & 15) * 33 + 30] = 0.f; tile[(lane & 15) * 33 + 31] = 0.f;
+        }
+        __syncwarp();
+        for (int r = 0; r < 16; ++r) {
+            uint64_t hh = h0 + 16 * half + r;
+            if (hh < n) Mo[hh * SKC_EPAD + lane] = tile[r * 33 + lane];
+        }
+        __syncwarp();
+    }
+    if (COUNT && lane == 0 && cnt) {
+        for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
+    }
+}
+
 // Li subsurface term (multipolesubsurface.cpp:279-287); one warp per hit, lane = wavelength
 __global__ void k_li_sss(const skc_hit *__restrict__ hits, uint64_t n, const float *__restrict__ Mo, const float *__restrict__ rhoHd,
                          const float *__restrict__ albedo, float mix, float *__restrict__ L) {
@@ -237,6 +371,14 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (!n) return 0;
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
+    if (ctx->moPacket) {
+        if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
+        uint64_t pb = (n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32);
+        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
+        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
+        SKC_LAUNCHED("k_mo_packet");
+        return 0;
+    }
     uint64_t per = MO_WARPS * MO_HITS_PER_WARP;
     uint64_t blocks = (n + per - 1) / per;
     // stack need: MO_HIGH-1 + 7*32 + 7*levels
