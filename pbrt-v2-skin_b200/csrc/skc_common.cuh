@@ -60,6 +60,7 @@ struct skc_ctx {
     float4 *otLeafPosArea = nullptr; // irradiance points gathered in leaf order
     float *otLeafE = nullptr;        // [n][32] in leaf order
     uint32_t otNodes = 0, otCap = 0, otLevels = 0;
+    uint32_t lightNS[16] = {0};   // RoundUpPow2(nSamples) per light (host copy for launch shapes)
     int moPacket = 1;        // Mo kernel: 1 = packet (lane = hit), 0 = warp per hit (lane = wavelength); env SKC_MO_KERNEL=warp|packet
     uint64_t otPoints = 0;
     float otBoundsHost[6];

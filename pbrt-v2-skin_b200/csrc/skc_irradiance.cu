@@ -234,102 +234,127 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
     return true;
 }
 
-#define IRR_BLOCK 128
-#define IRR_WARPS (IRR_BLOCK / 32)
-#define IRR_CHUNK 8      // light samples handled per transposition pass
+// ---------------------------------------------------------------------------------------------
+// The pass runs as three kernels per batch of points (the first version did everything in one
+// thread-per-point kernel: 93 registers + 41 KB of shared accumulators held it at 20 warps/SM and
+// ncu showed it latency-bound in the BVH loop, ~50 % of the stall samples on node fetch + slab test):
+//   k_irr_sample    one thread per (point, light, sample): scrambled (0,2) sample -> Sample_L geometry ->
+//                   (cos, pdf) candidate, and the shadow segments that need a visibility test are
+//                   compacted into a ray list (one atomic per CTA)
+//   k_irr_shadow    one thread per listed shadow ray, any-hit BVH walk at full occupancy; an occluded
+//                   ray clears its sample's pdf
+//   k_irr_spectral  one warp per run of points, lane = wavelength: the reference's sum
+//                   sum_lights (1/nS) sum_s (1 - rho_hd(cos)) * Lemit * cos / pdf  in its own order,
+//                   128 B coalesced rows for rho, Lemit and E
+#define IRR_BLOCK 256
+#define IRR_MAX_LIGHTS 16
+#define IRR_SPECTRAL_POINTS 8        // points per warp in k_irr_spectral
 
-// The spectral accumulators live in shared memory ([point of the warp][wavelength], conflict
-// free) so that the lane = wavelength loop over the warp's 32 points stays ROLLED: the first
-// version kept them in 2 x 32 registers with the loop unrolled 32x, and ncu showed the kernel
-// starved for instructions (stall_no_instruction 24 per issue, 128 registers).
+struct IrrSlots { uint32_t nLights, S; uint32_t nS[IRR_MAX_LIGHTS]; };   // S = sum of RoundUpPow2(nSamples)
+
 template <bool COUNT>
-__global__ void __launch_bounds__(IRR_BLOCK) k_irradiance(BvhView bv, const skc_light *__restrict__ lights, uint32_t nLights,
-        const skc_surface_point *__restrict__ pts, uint64_t count, const uint32_t *__restrict__ scr,
-        const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
-        float4 *__restrict__ posArea, float *__restrict__ Eout, uint64_t outBase, unsigned long long *cnt) {
-    __shared__ float sCos[IRR_BLOCK][IRR_CHUNK + 1];
-    __shared__ float sPdf[IRR_BLOCK][IRR_CHUNK + 1];
-    __shared__ float sE[IRR_WARPS][32][32];
-    __shared__ float sEl[IRR_WARPS][32][32];
-    uint64_t i = (uint64_t)blockIdx.x * IRR_BLOCK + threadIdx.x;
-    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpBase = threadIdx.x & ~31;
-    bool live = i < count;
-    f3 p = mk3(0, 0, 0), n = mk3(0, 0, 1);
-    float eps = 0.f, area = 0.f;
-    if (live) {
+__global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__restrict__ lights, IrrSlots sl,
+        const skc_surface_point *__restrict__ pts, const uint32_t *__restrict__ scr, uint64_t ptBase, uint32_t nPts,
+        float2 *__restrict__ cosPdf, float4 *__restrict__ rayO, float4 *__restrict__ rayD, uint32_t *__restrict__ rayTarget,
+        uint32_t *__restrict__ nRays, float4 *__restrict__ posArea, uint64_t outBase, unsigned long long *cnt) {
+    __shared__ uint32_t sWarpCount[IRR_BLOCK / 32];
+    __shared__ uint32_t sBase;
+    uint32_t t = blockIdx.x * IRR_BLOCK + threadIdx.x;
+    uint32_t point = t / sl.S, slot = t - point * sl.S;
+    bool need = false;
+    DRay sh; sh.o = mk3(0, 0, 0); sh.d = mk3(0, 0, 1); sh.mint = 0.f; sh.maxt = 0.f;
+    if (point < nPts) {
+        uint64_t i = ptBase + point;
         const float *sp = reinterpret_cast<const float *>(pts + i);
-        p = mk3(__ldg(sp), __ldg(sp + 1), __ldg(sp + 2));
-        n = mk3(__ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
-        area = __ldg(sp + 9); eps = __ldg(sp + 10);
-    }
-#pragma unroll 1
-    for (int k = 0; k < 32; ++k) sE[warp][k][lane] = 0.f;
-    for (uint32_t j = 0; j < nLights; ++j) {
-        const skc_light &L = lights[j];
-        int ns = (int)L.nSamples;
-        uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2
-        uint32_t s0 = 0, s1 = 0;
+        f3 p = mk3(__ldg(sp), __ldg(sp + 1), __ldg(sp + 2));
+        f3 n = mk3(__ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
+        float eps = __ldg(sp + 10);
+        if (slot == 0) posArea[outBase + i] = make_float4(p.x, p.y, p.z, __ldg(sp + 9));
+        uint32_t j = 0, s = slot;
+        while (s >= sl.nS[j]) { s -= sl.nS[j]; ++j; }
         // the third scramble word (uComponent) picks the shape of a ShapeSet; one sphere -> shape 0
-        if (live) { const uint32_t *w = scr + (i * nLights + j) * 3; s0 = __ldg(w); s1 = __ldg(w + 1); }
-        float Lc = lane < SKC_NS ? __ldg(&L.Lemit[lane]) : 0.f;
-#pragma unroll 1
-        for (int k = 0; k < 32; ++k) sEl[warp][k][lane] = 0.f;
-        for (uint32_t sBase = 0; sBase < nS; sBase += IRR_CHUNK) {
-            uint32_t chunk = min((uint32_t)IRR_CHUNK, nS - sBase);
-#pragma unroll 1
-            for (uint32_t c = 0; c < chunk; ++c) {
-                float cosT = 0.f, pdf = 0.f;
-                if (live) {
-                    uint32_t s = sBase + c;
-                    float u0 = vanDerCorput(s, s0), u1 = sobol2(s, s1);
-                    f3 wi; float lp; DRay sh;
-                    if (sampleSphereLight(L, p, eps, n, u0, u1, &wi, &lp, &sh)) {
-                        if (COUNT) atomicAdd(&cnt[2], 1ull);
-                        bool occ = bvhOccluded<COUNT>(bv, sh, cnt);
-                        if (!occ) { cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp; }
-                    }
-                }
-                sCos[threadIdx.x][c] = cosT; sPdf[threadIdx.x][c] = pdf;
-            }
-            __syncwarp();
-            if (lane < SKC_NS) {
-#pragma unroll 1
-                for (int k = 0; k < 32; ++k) {
-                    float el = sEl[warp][k][lane];
-                    for (uint32_t c = 0; c < chunk; ++c) {
-                        float pdf = sPdf[warpBase + k][c];
-                        if (pdf != 0.f) {
-                            float cosT = sCos[warpBase + k][c];
-                            // MultipoleBSSRDFData::rho (core/multipole.cpp:458-463)
-                            float fid = cosT * (float)(SKC_RHO_LEN - 1);
-                            int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
-                            float lerp = fid - (float)id;
-                            float r0 = __ldg(&rhoHd[id * SKC_EPAD + lane]), r1 = __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
-                            float rho = (1.f - lerp) * r0 + lerp * r1;
-                            float Ft = 1.f - rho;
-                            el += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
-                        }
-                    }
-                    sEl[warp][k][lane] = el;
-                }
-            }
-            __syncwarp();
+        const uint32_t *w = scr + (i * sl.nLights + j) * 3;
+        float u0 = vanDerCorput(s, __ldg(w)), u1 = sobol2(s, __ldg(w + 1));
+        f3 wi; float lp;
+        float cosT = 0.f, pdf = 0.f;
+        if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
+            need = true;
+            cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
         }
-#pragma unroll 1
-        for (int k = 0; k < 32; ++k) sE[warp][k][lane] += sEl[warp][k][lane] / (float)(int)nS;      // :136
+        cosPdf[t] = make_float2(cosT, pdf);
     }
-    // write: lane = wavelength, coalesced 128 B row per point; lanes 30,31 write the zero pad
-    uint64_t warpFirst = (uint64_t)blockIdx.x * IRR_BLOCK + warpBase;
-#pragma unroll 1
-    for (int k = 0; k < 32; ++k) {
-        uint64_t pi = warpFirst + k;
-        if (pi < count) {
-            float e = lane < SKC_NS ? sE[warp][k][lane] : 0.f;
-            if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
-            Eout[(outBase + pi) * SKC_EPAD + lane] = e;
+    // compact the shadow segments: warp ballot -> CTA total -> one atomic per CTA
+    unsigned m = __ballot_sync(0xffffffffu, need);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) sWarpCount[warp] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+        for (int k = 0; k < IRR_BLOCK / 32; ++k) { uint32_t c = sWarpCount[k]; sWarpCount[k] = tot; tot += c; }
+        sBase = tot ? atomicAdd(nRays, tot) : 0u;
+        if (COUNT && tot) atomicAdd(&cnt[2], (unsigned long long)tot);
+    }
+    __syncthreads();
+    if (need) {
+        uint32_t r = sBase + sWarpCount[warp] + __popc(m & ((1u << lane) - 1u));
+        rayO[r] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.mint);
+        rayD[r] = make_float4(sh.d.x, sh.d.y, sh.d.z, sh.maxt);
+        rayTarget[r] = t;
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__restrict__ rayO, const float4 *__restrict__ rayD,
+        const uint32_t *__restrict__ rayTarget, const uint32_t *__restrict__ nRays, float2 *__restrict__ cosPdf,
+        unsigned long long *cnt) {
+    uint32_t r = blockIdx.x * 128 + threadIdx.x;
+    if (r >= __ldg(nRays)) return;
+    float4 o = __ldg(&rayO[r]), d = __ldg(&rayD[r]);
+    DRay ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.mint = o.w; ray.maxt = d.w;
+    if (bvhOccluded<COUNT>(bv, ray, cnt)) cosPdf[__ldg(&rayTarget[r])] = make_float2(0.f, 0.f);
+}
+
+__global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
+        uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
+        float *__restrict__ Eout, uint64_t outBase) {
+    int lane = threadIdx.x & 31;
+    uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
+    uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
+    const int lam = lane < SKC_NS ? lane : 0;
+    for (uint32_t k = 0; k < IRR_SPECTRAL_POINTS; ++k) {
+        uint32_t point = p0 + k;
+        if (point >= nPts) return;
+        const float2 *cp = cosPdf + (size_t)point * sl.S;
+        float E = 0.f;
+        for (uint32_t j = 0; j < sl.nLights; ++j) {
+            uint32_t nS = sl.nS[j];
+            float Lc = __ldg(&lights[j].Lemit[lam]);
+            float el = 0.f;
+            for (uint32_t sBase = 0; sBase < nS; sBase += 32) {
+                uint32_t chunk = min(32u, nS - sBase);
+                float2 mine = lane < chunk ? __ldg(&cp[sBase + lane]) : make_float2(0.f, 0.f);
+                unsigned lit = __ballot_sync(0xffffffffu, mine.y != 0.f);
+                while (lit) {                 // ascending sample order, as the reference's loop
+                    int c = __ffs(lit) - 1; lit &= lit - 1;
+                    float cosT = __shfl_sync(0xffffffffu, mine.x, c), pdf = __shfl_sync(0xffffffffu, mine.y, c);
+                    // MultipoleBSSRDFData::rho (core/multipole.cpp:458-463)
+                    float fid = cosT * (float)(SKC_RHO_LEN - 1);
+                    int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
+                    float lerp = fid - (float)id;
+                    float r0 = __ldg(&rhoHd[id * SKC_EPAD + lane]), r1 = __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
+                    float rho = (1.f - lerp) * r0 + lerp * r1;
+                    float Ft = 1.f - rho;
+                    el += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
+                }
+            }
+            cp += nS;
+            E += el / (float)(int)nS;                    // :136
         }
+        uint64_t pi = ptBase + point;
+        float e = lane < SKC_NS ? E : 0.f;            // lanes 30,31 write the zero pad of the 128 B row
+        if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
+        Eout[(outBase + pi) * SKC_EPAD + lane] = e;
     }
-    if (live) posArea[outBase + i] = make_float4(p.x, p.y, p.z, area);
 }
 
 // AoS export of the device point set (IrradiancePoint records for the host / the oracle)
@@ -382,6 +407,11 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
     SKC_CUDA(cudaMemcpyAsync(ctx->lights, lights, nLights * sizeof(skc_light), cudaMemcpyHostToDevice, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->nLights = nLights;
+    for (uint32_t j = 0; j < nLights && j < IRR_MAX_LIGHTS; ++j) {
+        int ns = (int)lights[j].nSamples;
+        uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2 (multipolesubsurface.cpp:101)
+        ctx->lightNS[j] = nS;
+    }
     return 0;
 }
 
@@ -413,15 +443,39 @@ static int irradianceDev(skc_ctx *ctx, const skc_surface_point *dPts, uint64_t n
     k_scrambles<<<t1 - t0 + 1, 256, 0, ctx->stream>>>(t0, nTasks, nTotal, first, count, wpp, dScr);
     SKC_LAUNCHED("k_scrambles");
     skc_stage_end(ctx, 0);
+    if (ctx->nLights > IRR_MAX_LIGHTS) return skc_fail(ctx, "skc_irradiance: %u lights, at most %d supported", ctx->nLights, IRR_MAX_LIGHTS);
+    IrrSlots sl; sl.nLights = ctx->nLights; sl.S = 0;
+    for (uint32_t j = 0; j < IRR_MAX_LIGHTS; ++j) { sl.nS[j] = j < ctx->nLights ? ctx->lightNS[j] : 0xffffffffu; if (j < ctx->nLights) sl.S += sl.nS[j]; }
+    // batches of at most 2^25 (point, light, sample) slots: 256 MB of (cos, pdf) + at most 1.2 GB of shadow segments
+    const uint64_t maxSlots = 1ull << 25;
+    uint64_t batchPts = maxSlots / sl.S; if (!batchPts) batchPts = 1;
+    if (batchPts > count) batchPts = count;
+    uint64_t nBatches = (count + batchPts - 1) / batchPts, slots = batchPts * sl.S;
+    float2 *dCosPdf = (float2 *)skc_scratch(ctx, 4, slots * sizeof(float2));
+    char *dRays = (char *)skc_scratch(ctx, 5, slots * 36);
+    uint32_t *dNRays = (uint32_t *)skc_scratch(ctx, 6, nBatches * sizeof(uint32_t));
+    if (!dCosPdf || !dRays || !dNRays) return 1;
+    float4 *rayO = (float4 *)dRays, *rayD = rayO + slots;
+    uint32_t *rayTarget = (uint32_t *)(rayD + slots);
     skc_stage_begin(ctx);
-    uint64_t blocks = (count + IRR_BLOCK - 1) / IRR_BLOCK;
-    if (cntDev)
-        k_irradiance<true><<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
-                                                                            ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, cntDev);
-    else
-        k_irradiance<false><<<(unsigned)blocks, IRR_BLOCK, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, ctx->nLights, dPts, count, dScr,
-                                                                             ctx->rhoHd, dAlb, mix, ctx->ipPosArea, ctx->ipE, first, nullptr);
-    SKC_LAUNCHED("k_irradiance");
+    SKC_CUDA(cudaMemsetAsync(dNRays, 0, nBatches * sizeof(uint32_t), ctx->stream));
+    for (uint64_t b = 0; b < nBatches; ++b) {
+        uint64_t pb = b * batchPts;
+        uint32_t np = (uint32_t)std::min<uint64_t>(batchPts, count - pb);
+        uint64_t ns = (uint64_t)np * sl.S;
+        unsigned gSample = (unsigned)((ns + IRR_BLOCK - 1) / IRR_BLOCK), gShadow = (unsigned)((ns + 127) / 128);
+        unsigned gSpec = (unsigned)(((uint64_t)np + IRR_SPECTRAL_POINTS * 8 - 1) / (IRR_SPECTRAL_POINTS * 8));
+        if (cntDev) {
+            k_irr_sample<true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
+            k_irr_shadow<true><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, cntDev);
+        } else {
+            k_irr_sample<false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
+            k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
+        }
+        k_irr_spectral<<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first);
+        ctx->launches += 2;
+        SKC_LAUNCHED("k_irr_spectral");
+    }
     skc_stage_end(ctx, 1);
     return 0;
 }
