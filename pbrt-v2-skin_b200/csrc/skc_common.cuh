@@ -10,6 +10,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include <vector>
 #include "../../include/skin_cuda.h"
 
 #define SKC_NS SKC_NSPECTRAL
@@ -20,6 +21,9 @@ struct skc_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute
+    std::vector<cudaEvent_t> evPool;         // untimed events ordering copyStream against stream
+    bool stageAccumulate = false;            // skc_stage_end adds to stageMs instead of overwriting (chunked passes)
     std::string err;
     uint64_t launches = 0;
     float stageMs[SKC_NSTAGES] = {0};
@@ -86,6 +90,7 @@ int skc_check(skc_ctx *ctx, cudaError_t e, const char *what);
 void *skc_scratch(skc_ctx *ctx, int slot, size_t bytes);
 void skc_stage_begin(skc_ctx *ctx);
 void skc_stage_end(skc_ctx *ctx, int stage);
+cudaEvent_t skc_event(skc_ctx *ctx, size_t i);   // pooled cudaEventDisableTiming event, nullptr on failure
 
 #define SKC_CUDA(call) do { if (skc_check(ctx, (call), #call)) return 1; } while (0)
 #define SKC_LAUNCHED(what) do { ctx->launches++; if (skc_check(ctx, cudaGetLastError(), what)) return 1; } while (0)

@@ -33,7 +33,16 @@ void skc_stage_end(skc_ctx *ctx, int stage) {
     cudaEventSynchronize(ctx->ev1);
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
-    ctx->stageMs[stage] = ms;
+    if (ctx->stageAccumulate) ctx->stageMs[stage] += ms; else ctx->stageMs[stage] = ms;
+}
+
+cudaEvent_t skc_event(skc_ctx *ctx, size_t i) {
+    while (ctx->evPool.size() <= i) {
+        cudaEvent_t e = nullptr;
+        if (skc_check(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate")) return nullptr;
+        ctx->evPool.push_back(e);
+    }
+    return ctx->evPool[i];
 }
 
 extern "C" skc_ctx *skc_create(int device) {
@@ -50,6 +59,7 @@ extern "C" skc_ctx *skc_create(int device) {
     skc_ctx *ctx = new skc_ctx();
     ctx->device = device;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         skc_fail(nullptr, "skc_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -69,6 +79,9 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
+    cudaStreamSynchronize(ctx->copyStream);
+    cudaStreamDestroy(ctx->copyStream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

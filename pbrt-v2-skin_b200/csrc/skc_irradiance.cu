@@ -416,8 +416,11 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
 }
 
 // device-level pass over surface points already on the device (dPts[0] = point `first`)
-static int irradianceDev(skc_ctx *ctx, const skc_surface_point *dPts, uint64_t nTotal, uint64_t first, uint64_t count,
-                         uint32_t nTasks, float mix, const float *dAlb, unsigned long long *cntDev) {
+// hostPts (optional): the points of [first, first+count) still in host memory -- they are uploaded batch by batch on the
+// copy stream, each batch's kernels waiting only for their own slice, so the 1 GB upload hides behind the compute
+static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal, uint64_t first, uint64_t count,
+                         uint32_t nTasks, float mix, const float *dAlb, unsigned long long *cntDev,
+                         const skc_surface_point *hostPts = nullptr) {
     if (!ctx->bvhNodes) return skc_fail(ctx, "skc_irradiance: no BVH uploaded");
     if (!ctx->nLights) return skc_fail(ctx, "skc_irradiance: no lights uploaded");
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_irradiance: no rho table uploaded (skc_upload_profile)");
@@ -457,11 +460,23 @@ static int irradianceDev(skc_ctx *ctx, const skc_surface_point *dPts, uint64_t n
     if (!dCosPdf || !dRays || !dNRays) return 1;
     float4 *rayO = (float4 *)dRays, *rayD = rayO + slots;
     uint32_t *rayTarget = (uint32_t *)(rayD + slots);
+    if (hostPts) {
+        cudaEvent_t e0 = skc_event(ctx, 0);
+        if (!e0 || !skc_event(ctx, nBatches)) return 1;
+        SKC_CUDA(cudaEventRecord(e0, ctx->stream));                 // earlier work on the scratch buffer
+        SKC_CUDA(cudaStreamWaitEvent(ctx->copyStream, e0, 0));
+        for (uint64_t b = 0; b < nBatches; ++b) {
+            uint64_t pb = b * batchPts, np = std::min<uint64_t>(batchPts, count - pb);
+            SKC_CUDA(cudaMemcpyAsync(dPts + pb, hostPts + pb, np * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->copyStream));
+            SKC_CUDA(cudaEventRecord(skc_event(ctx, 1 + b), ctx->copyStream));
+        }
+    }
     skc_stage_begin(ctx);
     SKC_CUDA(cudaMemsetAsync(dNRays, 0, nBatches * sizeof(uint32_t), ctx->stream));
     for (uint64_t b = 0; b < nBatches; ++b) {
         uint64_t pb = b * batchPts;
         uint32_t np = (uint32_t)std::min<uint64_t>(batchPts, count - pb);
+        if (hostPts) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, skc_event(ctx, 1 + b), 0));
         uint64_t ns = (uint64_t)np * sl.S;
         unsigned gSample = (unsigned)((ns + IRR_BLOCK - 1) / IRR_BLOCK), gShadow = (unsigned)((ns + 127) / 128);
         unsigned gSpec = (unsigned)(((uint64_t)np + IRR_SPECTRAL_POINTS * 8 - 1) / (IRR_SPECTRAL_POINTS * 8));
@@ -495,8 +510,7 @@ extern "C" int skc_irradiance(skc_ctx *ctx, const skc_surface_point *points, uin
         if (!dAlb) return 1;
         SKC_CUDA(cudaMemcpyAsync(dAlb, albedo30, count * SKC_NS * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     }
-    SKC_CUDA(cudaMemcpyAsync(dPts, points + first, count * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
-    if (irradianceDev(ctx, dPts, nTotal, first, count, nTasks, mix, dAlb, nullptr)) return 1;
+    if (irradianceDev(ctx, dPts, nTotal, first, count, nTasks, mix, dAlb, nullptr, points + first)) return 1;
     if (out) {
         skc_irr_point *dOut = (skc_irr_point *)skc_scratch(ctx, 3, count * sizeof(skc_irr_point));
         if (!dOut) return 1;

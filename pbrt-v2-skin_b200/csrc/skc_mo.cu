@@ -17,6 +17,7 @@
 // Exact-zero culling (not in the reference, results identical): Rd is 0 for every
 // wavelength once d2 * min(rcpDsqSpacing) >= len-1, so contributions beyond that range are
 // skipped, and so are subtrees whose box lies entirely beyond it.
+#include <algorithm>
 #include <vector>
 #include "skc_internal.h"
 
@@ -175,6 +176,11 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 #define MOP_WARPS 4
 #define MOP_STACK 512          // 1 + 7 * levels entries at most (levels <= 64)
 
+// Optional fused Li epilogue of the packet kernel (multipolesubsurface.cpp:279-287): the subsurface radiance of each
+// hit is written straight from the Mo sums -- into device memory, or into mapped pinned host memory, in which case the
+// 120 B/sample result crosses PCIe while the kernel is still running instead of in a copy after it.
+struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; };
+
 template <bool COUNT>
 __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sRcp, const float4 *__restrict__ row4, float d2, float scale,
                                               bool active, float (&acc)[SKC_NS]) {
@@ -202,7 +208,7 @@ __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sR
 template <bool COUNT>
 __global__ void __launch_bounds__(MOP_WARPS * 32) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
-                                                             uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt) {
+                                                             uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li) {
     __shared__ uint2 stacks[MOP_WARPS][MOP_STACK];
     __shared__ float sRcp[32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -289,7 +295,26 @@ __global__ void __launch_bounds__(MOP_WARPS * 32) k_mo_packet(MoTree tr, MoTable
         __syncwarp();
         for (int r = 0; r < 16; ++r) {
             uint64_t hh = h0 + 16 * half + r;
-            if (hh < n) Mo[hh * SKC_EPAD + lane] = tile[r * 33 + lane];
+            if (hh >= n) break;
+            float mo = tile[r * 33 + lane];
+            if (Mo) Mo[hh * SKC_EPAD + lane] = mo;
+            if (li.L) {
+                const float *hp = reinterpret_cast<const float *>(li.hits + hh);
+                float out = 0.f;
+                if (__float_as_int(__ldg(hp + 13)) && lane < SKC_NS) {
+                    f3 nn = mk3(__ldg(hp + 7), __ldg(hp + 8), __ldg(hp + 9)), wo = mk3(__ldg(hp + 10), __ldg(hp + 11), __ldg(hp + 12));
+                    float costheta = fminf(fabsf(dot3(wo, nn)), 1.f);
+                    float fid = costheta * (float)(SKC_RHO_LEN - 1);
+                    int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
+                    float lerp = fid - (float)id;
+                    float rho = (1.f - lerp) * __ldg(&li.rhoHd[id * SKC_EPAD + lane]) + lerp * __ldg(&li.rhoHd[(id + 1) * SKC_EPAD + lane]);
+                    float Ft = 1.f - rho;
+                    float a = 1.f;
+                    if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + lane]), (double)(1.f - li.mix));
+                    out = fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
+                }
+                if (lane < SKC_NS) li.L[hh * SKC_NS + lane] = out;
+            }
         }
         __syncwarp();
     }
@@ -365,7 +390,7 @@ extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float 
 }
 
 static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride,
-                    uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr) {
+                    uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr, const LiEpilogue *li = nullptr) {
     if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo: no octree built (skc_build_octree)");
     if (!ctx->profPairs) return skc_fail(ctx, "skc_mo: no profile table uploaded (skc_upload_profile)");
     if (!n) return 0;
@@ -374,11 +399,13 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (ctx->moPacket) {
         if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
         uint64_t pb = (n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32);
-        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev);
-        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr);
+        LiEpilogue ep = li ? *li : LiEpilogue{nullptr, nullptr, nullptr, 0.f, nullptr};
+        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep);
+        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep);
         SKC_LAUNCHED("k_mo_packet");
         return 0;
     }
+    if (li) return skc_fail(ctx, "skc_mo: the fused Li epilogue needs the packet kernel");
     uint64_t per = MO_WARPS * MO_HITS_PER_WARP;
     uint64_t blocks = (n + per - 1) / per;
     // stack need: MO_HIGH-1 + 7*32 + 7*levels
@@ -464,11 +491,15 @@ extern "C" int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float m
     return liDev(ctx, dHits, n, maxError, mix, albedo30, Mo30, L30);
 }
 
+// Host-buffer camera pass: rays up, closest hit, Mo with the fused Li epilogue.  When L30 is pinned host memory
+// (skc_alloc_pinned / cudaHostAlloc) the kernel writes the radiance rows straight into it; otherwise they are staged
+// in device memory and copied afterwards.  The hit records travel back on the copy stream while Mo runs.
 extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxError, float mix,
                                skc_hit *hitsOut, float *L30) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     if (!n) return 0;
+    if (!ctx->rhoHd) return skc_fail(ctx, "skc_camera_pass: no rho table uploaded (skc_upload_profile)");
     skc_ray *dRays = (skc_ray *)skc_scratch(ctx, 0, n * sizeof(skc_ray));
     skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 1, n * sizeof(skc_hit));
     if (!dRays || !dHits) return 1;
@@ -476,8 +507,37 @@ extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, fl
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, dRays, n, dHits, nullptr)) return 1;
     skc_stage_end(ctx, 3);
-    if (hitsOut) SKC_CUDA(cudaMemcpyAsync(hitsOut, dHits, n * sizeof(skc_hit), cudaMemcpyDeviceToHost, ctx->stream));
-    return liDev(ctx, dHits, n, maxError, mix, nullptr, nullptr, L30);
+    if (hitsOut) {
+        cudaEvent_t traced = skc_event(ctx, 0);
+        if (!traced) return 1;
+        SKC_CUDA(cudaEventRecord(traced, ctx->stream));
+        SKC_CUDA(cudaStreamWaitEvent(ctx->copyStream, traced, 0));
+        SKC_CUDA(cudaMemcpyAsync(hitsOut, dHits, n * sizeof(skc_hit), cudaMemcpyDeviceToHost, ctx->copyStream));
+    }
+    if (!ctx->moPacket || !L30) {
+        int rc = liDev(ctx, dHits, n, maxError, mix, nullptr, nullptr, L30);
+        cudaError_t e = cudaStreamSynchronize(ctx->copyStream);
+        if (rc) return rc;
+        SKC_CUDA(e);
+        return 0;
+    }
+    float *target = nullptr, *dL = nullptr;
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, L30) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer) target = (float *)attr.devicePointer;
+    else {
+        cudaGetLastError();
+        dL = (float *)skc_scratch(ctx, 2, n * SKC_NS * sizeof(float));
+        if (!dL) return 1;
+        target = dL;
+    }
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, target};
+    skc_stage_begin(ctx);
+    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep)) return 1;
+    skc_stage_end(ctx, 4);
+    if (dL) SKC_CUDA(cudaMemcpyAsync(L30, dL, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->copyStream));
+    return 0;
 }
 
 // ---- resident camera rays -----------------------------------------------------------------

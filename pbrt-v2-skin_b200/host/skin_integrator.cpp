@@ -117,8 +117,14 @@ uint64_t skh_bench_rays(skh_scene *s, const void **rays) {
     size_t k = 0;
     const int T = 16;
     for (int ty = 0; ty < H; ty += T) for (int tx = 0; tx < W; tx += T)
-        for (int y = ty; y < std::min(ty + T, H); ++y) for (int x = tx; x < std::min(tx + T, W); ++x)
+        for (int m = 0; m < T * T; ++m) {
+            int lx, ly;
+            if (getenv("SKH_MORTON")) { lx = (m & 1) | ((m >> 1) & 2) | ((m >> 2) & 4) | ((m >> 3) & 8); ly = ((m >> 1) & 1) | ((m >> 2) & 2) | ((m >> 3) & 4) | ((m >> 4) & 8); }
+            else { lx = m % T; ly = m / T; }
+            int x = tx + lx, y = ty + ly;
+            if (x >= W || y >= H) continue;
             for (int q = 0; q < spp; ++q) { s->xy[k++] = x + ((q % sx) + .5f) / sx; s->xy[k++] = y + ((q / sx) + .5f) / sx; }
+        }
     s->rays.resize((size_t)W * H * spp);
     skh_camera_rays(s, s->xy.data(), s->rays.size(), s->rays.data());
     *rays = s->rays.data();

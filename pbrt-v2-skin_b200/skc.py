@@ -217,9 +217,9 @@ class SkinDevice:
         self._ck(self.lib.skc_li_sss(self.ctx, _ptr(hits), len(hits), max_error, mix, _ptr(albedo), _ptr(mo), _ptr(L)))
         return mo, L
 
-    def camera_pass(self, rays, max_error, mix=0.5, want_hits=False):
+    def camera_pass(self, rays, max_error, mix=0.5, want_hits=False, out=None):
         rays = _c(rays, np.float32).reshape(-1, 8)
-        L = np.empty((len(rays), 30), np.float32)
+        L = np.empty((len(rays), 30), np.float32) if out is None else out
         hits = np.empty(len(rays), DT_HIT) if want_hits else None
         self._ck(self.lib.skc_camera_pass(self.ctx, _ptr(rays), len(rays), max_error, mix, _ptr(hits), _ptr(L)))
         return (L, hits) if want_hits else L

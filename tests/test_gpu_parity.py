@@ -311,3 +311,19 @@ def test_rho_table_vs_reference(dev, tiny):
     e = np.abs(hd[:, 0].astype(np.float64) - ref[:, 0]) / np.abs(ref[:, 0])
     print("rho_hd: max rel %.3g, bit-exact entries %.3f" % (e.max(), np.mean(hd[:, 0] == ref[:, 0])))
     assert e.max() < 1e-5
+
+
+def test_camera_pass_pinned_output_matches_staged(dev, scene):
+    """skc_camera_pass writes L straight into pinned host memory from the Mo kernel's epilogue; a pageable buffer goes
+    through a device staging copy.  Same bits either way, hit records included."""
+    g = scene
+    dev.set_irradiance_points(g.irradiance_points)
+    dev.build_octree()
+    L0, h0 = dev.camera_pass(g.camera_rays, g.max_error, g.mix, want_hits=True)
+    Lp = dev.pinned((len(g.camera_rays), 30), np.float32)
+    Lp[:] = -1.0
+    L1, h1 = dev.camera_pass(g.camera_rays, g.max_error, g.mix, want_hits=True, out=Lp)
+    assert np.array_equal(L0.view(np.uint32), np.asarray(L1).view(np.uint32))
+    assert h0.tobytes() == h1.tobytes()
+    e = gu.row_rel_err(L1, g.L_sss)
+    assert np.mean(e < 1e-4) > 0.99
