@@ -166,23 +166,29 @@ def main():
         pos_t = torch.as_tensor(_Wrap(pa_ptr, (shard * world, 4)), device="cuda")
         e_t = torch.as_tensor(_Wrap(e_ptr, (shard * world, 32)), device="cuda")
 
-    def exchange():
-        """in-place all-gather of the irradiance shards (posArea + E rows) over NCCL"""
+    def exchange_and_build():
+        """Irradiance exchange + octree.  N > 1: in-place NCCL all-gather of the shards; the positions (16 B/point) go
+        first, then the irradiance rows (128 B/point) travel while every rank already builds the octree topology
+        from the positions; the finalize pass (leaf gather + InitHierarchy) waits for the rows."""
         if world == 1:
+            dev.build_octree()
             return
         import torch
         dev.synchronize()
         pkg.allgather_inplace(dist, pos_t, rank, shard)
-        pkg.allgather_inplace(dist, e_t, rank, shard)
-        torch.cuda.synchronize()
-        # padded tail (only when n_pts % world != 0): compact is unnecessary because shards are
-        # contiguous and only the LAST shard is short -> valid points are exactly [0, n_pts)
+        work = pkg.allgather_inplace_async(dist, e_t, rank, shard)
+        torch.cuda.current_stream().synchronize()          # positions are in
+        # padded tail (only when n_pts % world != 0): shards are contiguous and only the LAST one is short,
+        # so the valid points are exactly [0, n_pts)
         dev.set_point_count(n_pts)
+        dev.build_octree_topology()
+        work.wait()
+        torch.cuda.synchronize()
+        dev.build_octree_finalize()
 
     def step_resident():
         dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
-        exchange()
-        dev.build_octree()
+        exchange_and_build()
         dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix)
 
     h_pts = dev.pinned((n_pts,), pkg.DT_SURFACE_POINT); h_pts[:] = pts
@@ -191,8 +197,7 @@ def main():
 
     def step_e2e():
         dev.irradiance(h_pts, n_tasks, scene.mix, first=p_first, count=p_count, want_out=False)
-        exchange()
-        dev.build_octree()
+        exchange_and_build()
         L = dev.lib.skc_camera_pass(dev.ctx, h_rays[r_first:].ctypes.data, r_count, scene.maxerror, scene.mix, None, h_L.ctypes.data)
         dev._ck(L)
 
@@ -245,8 +250,7 @@ def main():
 
     # ---- roofline of the dominant kernel (one extra instrumented pass, untimed)
     c_irr = dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix, counters=True)
-    exchange()
-    dev.build_octree()
+    exchange_and_build()
     c_cam = dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix, counters=True)
     n_lights = scene.n_lights
     # algorithmic bytes: irradiance = per point 44 in + 144 out + 12*nLights scramble

@@ -144,6 +144,12 @@ int skc_set_point_count(skc_ctx *ctx, uint64_t n);
  * the device irradiance-point set; the flat tree stays on the device.  Optional outputs:
  * node count, root {p[3], sumArea, Et[30]} (34 floats), bounds (6 floats). */
 int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6);
+/* The two halves of skc_build_octree, for callers that can overlap them with an exchange: the topology pass reads
+ * only the point positions (bounds, splitting by `p > pMid`, leaf order = insertion order; diffusionutil.h:94-132,
+ * multipolesubsurface.cpp:218-237); finalize gathers the records into leaf order and runs InitHierarchy
+ * (diffusionutil.h:133-173) and needs the irradiance rows. */
+int skc_build_octree_topology(skc_ctx *ctx);
+int skc_build_octree_finalize(skc_ctx *ctx, uint32_t *nNodes, float *root34, float *bounds6);
 
 /* ---- MultipoleSubsurfaceIntegrator::Li, subsurface term ----------------------------- */
 /* SubsurfaceOctreeNode::Mo (diffusionutil.h:175-210) for n points: Mo30[n][30]. */

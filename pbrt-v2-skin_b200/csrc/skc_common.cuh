@@ -65,6 +65,8 @@ struct skc_ctx {
     float *otLeafE = nullptr;        // [n][32] in leaf order
     uint32_t otNodes = 0, otCap = 0, otLevels = 0;
     uint32_t lightNS[16] = {0};   // RoundUpPow2(nSamples) per light (host copy for launch shapes)
+    std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize
+    bool otTopologyReady = false;
     int moPacket = 1;        // Mo kernel: 1 = packet (lane = hit), 0 = warp per hit (lane = wavelength); env SKC_MO_KERNEL=warp|packet
     uint64_t otPoints = 0;
     float otBoundsHost[6];

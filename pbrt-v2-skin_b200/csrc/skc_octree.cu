@@ -167,15 +167,15 @@ __global__ void k_sort_leaves(OtBuild b, uint32_t nNodes, uint32_t *__restrict__
     for (uint32_t k = 0; k < cnt; ++k) idx[start + k] = v[k];
 }
 
-// gather the point records into leaf order: one warp per point row
-__global__ void k_gather_points(const uint32_t *__restrict__ idx, uint64_t n, const float4 *__restrict__ posArea,
-                                const float *__restrict__ E, float4 *__restrict__ posAreaOut, float *__restrict__ Eout) {
+// gather the point records into leaf order: 8 threads per 128 B row (one float4 each), 4 rows per warp
+__global__ void __launch_bounds__(256) k_gather_points(const uint32_t *__restrict__ idx, uint64_t n, const float4 *__restrict__ posArea,
+                                const float4 *__restrict__ E4, float4 *__restrict__ posAreaOut, float4 *__restrict__ Eout4) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint64_t slot = t >> 5; int lane = t & 31;
+    uint64_t slot = t >> 3; int q = t & 7;
     if (slot >= n) return;
-    uint32_t src = idx[slot];
-    Eout[slot * SKC_EPAD + lane] = __ldg(&E[(uint64_t)src * SKC_EPAD + lane]);
-    if (lane == 0) posAreaOut[slot] = __ldg(&posArea[src]);
+    uint32_t src = __ldg(&idx[slot]);
+    Eout4[slot * (SKC_EPAD / 4) + q] = __ldg(&E4[(uint64_t)src * (SKC_EPAD / 4) + q]);
+    if (q == 0) posAreaOut[slot] = __ldg(&posArea[src]);
 }
 
 // SampledSpectrum::y() (core/spectrum.h:387-393)
@@ -266,9 +266,12 @@ static int ensureOctreeStorage(skc_ctx *ctx, uint64_t n, uint32_t cap) {
     return 0;
 }
 
-extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6) {
+// Topology: bounds, breadth-first splitting, leaf order.  Reads only the point POSITIONS, so a multi-GPU caller can run it
+// while the irradiance rows (8x the bytes) are still being gathered from the other ranks.
+extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
+    ctx->otTopologyReady = false;
     uint64_t n64 = ctx->ipCount;
     if (n64 > 0x1fffffffull) return skc_fail(ctx, "skc_build_octree: more than 2^29 irradiance points");
     uint32_t n = (uint32_t)n64;
@@ -341,8 +344,29 @@ extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34
         k_sort_leaves<<<(total + 255) / 256, 256, 0, ctx->stream>>>(b, total, idxA);
         SKC_LAUNCHED("k_sort_leaves");
         SKC_CUDA(cudaMemcpyAsync(ctx->otPointIdx, idxA, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
-        uint64_t threads = (uint64_t)n * 32;
-        k_gather_points<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(idxA, n, ctx->ipPosArea, ctx->ipE, ctx->otLeafPosArea, ctx->otLeafE);
+    }
+    skc_stage_end(ctx, 2);
+    ctx->otNodes = total;
+    ctx->otLevels = (uint32_t)levelStart.size() - 1;
+    ctx->otLevelStart = levelStart;
+    ctx->otTopologyReady = true;
+    return 0;
+}
+
+// Finalize: gather the point records into leaf order and run InitHierarchy bottom-up (needs the irradiance rows).
+extern "C" int skc_build_octree_finalize(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->otTopologyReady) return skc_fail(ctx, "skc_build_octree_finalize: no topology (skc_build_octree_topology)");
+    uint32_t n = (uint32_t)ctx->otPoints, total = ctx->otNodes;
+    const std::vector<uint32_t> &levelStart = ctx->otLevelStart;
+    const float *hb = ctx->otBoundsHost;
+    float prev = ctx->stageMs[2];
+    skc_stage_begin(ctx);
+    if (n) {
+        uint64_t threads = (uint64_t)n * 8;
+        k_gather_points<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(ctx->otPointIdx, n, ctx->ipPosArea, reinterpret_cast<const float4 *>(ctx->ipE),
+                                                                                     ctx->otLeafPosArea, reinterpret_cast<float4 *>(ctx->otLeafE));
         SKC_LAUNCHED("k_gather_points");
     }
     for (int lv = (int)levelStart.size() - 2; lv >= 0; --lv) {
@@ -352,8 +376,7 @@ extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34
         SKC_LAUNCHED("k_init_level");
     }
     skc_stage_end(ctx, 2);
-    ctx->otNodes = total;
-    ctx->otLevels = (uint32_t)levelStart.size() - 1;
+    ctx->stageMs[2] += prev;          // stage 2 = topology + finalize of one build
     if (nNodesOut) *nNodesOut = total;
     if (bounds6) for (int k = 0; k < 6; ++k) bounds6[k] = hb[k];
     if (root34) {
@@ -366,4 +389,9 @@ extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34
         for (int c = 0; c < SKC_NS; ++c) root34[4 + c] = e[c];
     }
     return 0;
+}
+
+extern "C" int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6) {
+    if (skc_build_octree_topology(ctx)) return 1;
+    return skc_build_octree_finalize(ctx, nNodesOut, root34, bounds6);
 }

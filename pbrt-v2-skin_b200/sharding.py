@@ -15,3 +15,9 @@ def allgather_inplace(dist, full, rank, per):
     After the call every rank holds every shard (NCCL/gloo all_gather_into_tensor, no staging copy)."""
     dist.all_gather_into_tensor(full, full[rank * per:(rank + 1) * per])
     return full
+
+
+def allgather_inplace_async(dist, full, rank, per):
+    """Same, returning the work handle: the caller overlaps the transfer with work that does not read `full`
+    (bench.py: octree topology from the positions while the 8x larger irradiance rows are in flight)."""
+    return dist.all_gather_into_tensor(full, full[rank * per:(rank + 1) * per], async_op=True)

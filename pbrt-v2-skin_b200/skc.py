@@ -28,7 +28,8 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_irradiance", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
-           "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table"]
+           "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
+           "skc_build_octree_topology", "skc_build_octree_finalize"]
 
 
 class SkcError(RuntimeError):
@@ -69,6 +70,8 @@ def load_library():
     lib.skc_set_irradiance_points.restype = i32; lib.skc_set_irradiance_points.argtypes = [vp, vp, u64]
     lib.skc_irradiance_dev.restype = i32; lib.skc_irradiance_dev.argtypes = [vp, u64, C.POINTER(vp), C.POINTER(vp)]
     lib.skc_build_octree.restype = i32; lib.skc_build_octree.argtypes = [vp, C.POINTER(u32), vp, vp]
+    lib.skc_build_octree_topology.restype = i32; lib.skc_build_octree_topology.argtypes = [vp]
+    lib.skc_build_octree_finalize.restype = i32; lib.skc_build_octree_finalize.argtypes = [vp, C.POINTER(u32), vp, vp]
     lib.skc_mo.restype = i32; lib.skc_mo.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_li_sss.restype = i32; lib.skc_li_sss.argtypes = [vp, vp, u64, f32, f32, vp, vp, vp]
     lib.skc_camera_pass.restype = i32; lib.skc_camera_pass.argtypes = [vp, vp, u64, f32, f32, vp, vp]
@@ -201,6 +204,15 @@ class SkinDevice:
         nn = C.c_uint32(0)
         root = np.zeros(34, np.float32); bounds = np.zeros(6, np.float32)
         self._ck(self.lib.skc_build_octree(self.ctx, C.byref(nn), _ptr(root), _ptr(bounds)))
+        return int(nn.value), root, bounds
+
+    def build_octree_topology(self):
+        self._ck(self.lib.skc_build_octree_topology(self.ctx))
+
+    def build_octree_finalize(self):
+        nn = C.c_uint32(0)
+        root = np.zeros(34, np.float32); bounds = np.zeros(6, np.float32)
+        self._ck(self.lib.skc_build_octree_finalize(self.ctx, C.byref(nn), _ptr(root), _ptr(bounds)))
         return int(nn.value), root, bounds
 
     # --- Li
