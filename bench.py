@@ -152,9 +152,12 @@ def main():
     n_tasks = scene.irradiance_tasks(n_pts, 1)
     # rank shards (contiguous, equal padded size so the all-gather can run in place)
     p_first, p_count, shard = pkg.shard_range(n_pts, rank, world)
-    r_first, r_count, _ = pkg.shard_range(n_rays, rank, world)
+    # camera samples: 16x16-pixel tiles (the generator's order) dealt round-robin over the ranks
+    tile = 256 * max(1, scene.spp)
+    my_rays = rays if world == 1 else np.ascontiguousarray(rays[pkg.tile_round_robin(n_rays, tile, rank, world)])
+    r_first, r_count = 0, len(my_rays)
     dev.set_surface_points(pts)
-    dev.set_camera_rays(rays)
+    dev.set_camera_rays(my_rays)
     pos_t = e_t = None
     if world > 1:
         import torch
@@ -192,7 +195,7 @@ def main():
         dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix)
 
     h_pts = dev.pinned((n_pts,), pkg.DT_SURFACE_POINT); h_pts[:] = pts
-    h_rays = dev.pinned((n_rays, 8), np.float32); h_rays[:] = rays
+    h_rays = dev.pinned((max(r_count, 1), 8), np.float32); h_rays[:r_count] = my_rays
     h_L = dev.pinned((max(r_count, 1), 30), np.float32)
 
     def step_e2e():

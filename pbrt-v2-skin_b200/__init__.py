@@ -16,4 +16,4 @@ GPU is missing.
 """
 from .skc import SkinDevice, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
 from .host_api import HostScene, load_host_library  # noqa: F401
-from .sharding import shard_range, allgather_inplace, allgather_inplace_async  # noqa: F401
+from .sharding import shard_range, tile_round_robin, allgather_inplace, allgather_inplace_async  # noqa: F401

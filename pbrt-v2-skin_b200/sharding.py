@@ -10,6 +10,17 @@ def shard_range(n, rank, world):
     return first, min(per, n - first), per
 
 
+def tile_round_robin(n, tile, rank, world):
+    """Indices of the camera samples of `rank` when tiles of `tile` consecutive samples are dealt round-robin
+    (the reference's own tile = one SamplerRendererTask window).  Contiguous halves of the image carry
+    very different amounts of skin; interleaved tiles balance the Mo work across ranks."""
+    import numpy as np
+    tiles = (n + tile - 1) // tile
+    mine = np.arange(rank, tiles, world, dtype=np.int64)
+    idx = (mine[:, None] * tile + np.arange(tile, dtype=np.int64)[None, :]).reshape(-1)
+    return idx[idx < n]
+
+
 def allgather_inplace(dist, full, rank, per):
     """full: tensor of world*per rows; rows [rank*per, (rank+1)*per) hold this rank's shard.
     After the call every rank holds every shard (NCCL/gloo all_gather_into_tensor, no staging copy)."""

@@ -59,3 +59,14 @@ def test_inplace_allgather_world2():
         p.join(timeout=60)
     assert [r[3] for r in res] == [True, True]
     assert res[0][1:3] == (0, 501) and res[1][1:3] == (501, 500)
+
+
+def test_tile_round_robin_partitions_all_samples(pkg):
+    n, tile = 10_000, 1024
+    for world in (1, 2, 3, 8):
+        parts = [pkg.tile_round_robin(n, tile, r, world) for r in range(world)]
+        allidx = np.sort(np.concatenate(parts))
+        assert np.array_equal(allidx, np.arange(n))
+        # whole tiles stay together and consecutive tiles go to consecutive ranks
+        for r, p in enumerate(parts):
+            assert np.all((p // tile) % world == r)
