@@ -19,6 +19,7 @@
 
 struct skc_ctx {
     int device = 0;
+    int smCount = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute

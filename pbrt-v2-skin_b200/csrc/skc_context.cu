@@ -58,6 +58,7 @@ extern "C" skc_ctx *skc_create(int device) {
     if (cudaSetDevice(device) != cudaSuccess) { skc_fail(nullptr, "skc_create: cudaSetDevice(%d) failed", device); return nullptr; }
     skc_ctx *ctx = new skc_ctx();
     ctx->device = device;
+    if (cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->smCount <= 0) ctx->smCount = 148;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {

@@ -206,24 +206,32 @@ __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sR
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(MOP_WARPS * 32) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+__global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
-                                                             uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li) {
+                                                             uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
+                                                             uint32_t *__restrict__ nextPacket) {
     __shared__ uint2 stacks[MOP_WARPS][MOP_STACK];
     __shared__ float sRcp[32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x < 32) sRcp[threadIdx.x] = __ldg(&T.rcp[threadIdx.x]);
     __syncthreads();
     uint2 *stack = stacks[warp];
-    uint64_t h0 = ((uint64_t)blockIdx.x * MOP_WARPS + warp) * 32, h = h0 + lane;
-    if (h0 >= n) return;
+    uint32_t wc[4] = {0, 0, 0, 0};
+    const uint32_t nPackets = (uint32_t)((n + 31) / 32);
+    // persistent warps: packets are handed out in order from a global counter, so the per-packet cost (none for sky,
+    // ~0.1 ms for a packet on the skin) balances across the grid and no wave of CTAs leaves a tail
+    for (;;) {
+    uint32_t packet = 0;
+    if (lane == 0) packet = atomicAdd(nextPacket, 1u);
+    packet = __shfl_sync(0xffffffffu, packet, 0);
+    if (packet >= nPackets) break;
+    uint64_t h0 = (uint64_t)packet * 32, h = h0 + lane;
     bool on = h < n && (enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true);
     float px = 0.f, py = 0.f, pz = 0.f;
     if (on) { const float *pp = p3 + h * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
     float acc[SKC_NS];
 #pragma unroll
     for (int w = 0; w < SKC_NS; ++w) acc[w] = 0.f;
-    uint32_t wc[4] = {0, 0, 0, 0};
     unsigned all = __ballot_sync(0xffffffffu, on);
     int sp = 0;
     if (all) { if (lane == 0) stack[0] = make_uint2(0u, all); sp = 1; }
@@ -318,6 +326,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32) k_mo_packet(MoTree tr, MoTable
         }
         __syncwarp();
     }
+    }   // packet loop
     if (COUNT && lane == 0 && cnt) {
         for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
     }
@@ -399,9 +408,13 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (ctx->moPacket) {
         if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
         uint64_t pb = (n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32);
+        if (pb > (uint64_t)ctx->smCount * 7) pb = (uint64_t)ctx->smCount * 7;       // persistent: at most the resident CTAs
         LiEpilogue ep = li ? *li : LiEpilogue{nullptr, nullptr, nullptr, 0.f, nullptr};
-        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep);
-        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep);
+        uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
+        if (!next) return 1;
+        SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
+        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
+        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
         SKC_LAUNCHED("k_mo_packet");
         return 0;
     }
