@@ -259,19 +259,24 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
         uint32_t *__restrict__ nRays, float4 *__restrict__ posArea, uint64_t outBase, unsigned long long *cnt) {
     __shared__ uint32_t sWarpCount[IRR_BLOCK / 32];
     __shared__ uint32_t sBase;
+    // thread order is LIGHT-major: all samples towards light 0 of the batch's points first, then light 1, ... so the
+    // shadow segments compacted from one warp point at the same emitter and walk the same BVH nodes (with the
+    // lights interleaved per point the shadow kernel ran at 14 of 32 lanes)
     uint32_t t = blockIdx.x * IRR_BLOCK + threadIdx.x;
-    uint32_t point = t / sl.S, slot = t - point * sl.S;
     bool need = false;
     DRay sh; sh.o = mk3(0, 0, 0); sh.d = mk3(0, 0, 1); sh.mint = 0.f; sh.maxt = 0.f;
-    if (point < nPts) {
+    uint32_t target = 0;
+    if (t < nPts * sl.S) {
+        uint32_t j = 0, r = t, slotBase = 0;
+        while (r >= nPts * sl.nS[j]) { r -= nPts * sl.nS[j]; slotBase += sl.nS[j]; ++j; }
+        uint32_t point = r / sl.nS[j], s = r - point * sl.nS[j];
+        target = point * sl.S + slotBase + s;
         uint64_t i = ptBase + point;
         const float *sp = reinterpret_cast<const float *>(pts + i);
         f3 p = mk3(__ldg(sp), __ldg(sp + 1), __ldg(sp + 2));
         f3 n = mk3(__ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
         float eps = __ldg(sp + 10);
-        if (slot == 0) posArea[outBase + i] = make_float4(p.x, p.y, p.z, __ldg(sp + 9));
-        uint32_t j = 0, s = slot;
-        while (s >= sl.nS[j]) { s -= sl.nS[j]; ++j; }
+        if (slotBase + s == 0) posArea[outBase + i] = make_float4(p.x, p.y, p.z, __ldg(sp + 9));
         // the third scramble word (uComponent) picks the shape of a ShapeSet; one sphere -> shape 0
         const uint32_t *w = scr + (i * sl.nLights + j) * 3;
         float u0 = vanDerCorput(s, __ldg(w)), u1 = sobol2(s, __ldg(w + 1));
@@ -281,7 +286,7 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
             need = true;
             cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
         }
-        cosPdf[t] = make_float2(cosT, pdf);
+        cosPdf[target] = make_float2(cosT, pdf);
     }
     // compact the shadow segments: warp ballot -> CTA total -> one atomic per CTA
     unsigned m = __ballot_sync(0xffffffffu, need);
@@ -299,7 +304,7 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
         uint32_t r = sBase + sWarpCount[warp] + __popc(m & ((1u << lane) - 1u));
         rayO[r] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.mint);
         rayD[r] = make_float4(sh.d.x, sh.d.y, sh.d.z, sh.maxt);
-        rayTarget[r] = t;
+        rayTarget[r] = target;
     }
 }
 
