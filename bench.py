@@ -262,6 +262,7 @@ def main():
     irr_bytes = p_count * (44 + 144 + 12 * n_lights) + 32 * int(c_irr[0]) + 48 * int(c_irr[1])
     mo_bytes = r_count * (12 + 128) + 48 * int(c_cam[2]) + 16 * int(c_cam[3]) + 368 * (int(c_cam[4]) + int(c_cam[5]))
     peak, peak_kind = measured_peak()
+    dev_sm_count = 148
     dom = "irradiance" if stage_ms["irradiance"] >= stage_ms["mo"] else "mo"
     dom_bytes = irr_bytes if dom == "irradiance" else mo_bytes
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
@@ -271,7 +272,14 @@ def main():
                 "other": {"k_irradiance": {"GBps": irr_bytes / (stage_ms["irradiance"] * 1e-3) / 1e9, "ms": stage_ms["irradiance"],
                                            "shadow_rays": int(c_irr[2]), "slab_tests": int(c_irr[0]), "prim_tests": int(c_irr[1])},
                           "k_mo": {"GBps": mo_bytes / (stage_ms["mo"] * 1e-3) / 1e9, "ms": stage_ms["mo"], "nodes": int(c_cam[2]), "leaf_points": int(c_cam[3]),
-                                   "cluster_contribs": int(c_cam[4]), "point_contribs": int(c_cam[5])}}}
+                                   "cluster_contribs": int(c_cam[4]), "point_contribs": int(c_cam[5]), "table_reads": int(c_cam[6])}}}
+    if int(c_cam[6]):
+        # what actually bounds Mo: scattered 8 B profile-table reads.  A B200 SM retires one scattered
+        # lane-gather per clock whatever the load path (tools/microbench/gather.cu, measured on this pool: 290 G/s chip-wide)
+        g_peak = 290e9 * (dev_sm_count / 148.0)
+        floor_ms = int(c_cam[6]) / g_peak * 1e3
+        roofline["l1tex_gather"] = {"kernel": "k_mo_packet", "lane_gathers": int(c_cam[6]), "peak_lane_gathers_per_s": g_peak,
+                                    "floor_ms": floor_ms, "frac": floor_ms / stage_ms["mo"]}
 
     # ---- multi-GPU self-check (untimed): the sharded + all-gathered octree must equal the one built
     # from a full local irradiance pass, bit for bit (root p / sumArea / Et) on every rank

@@ -172,7 +172,8 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  *   skc_irradiance_resident   counters3 = {BVH slab tests, primitive tests, shadow rays}
  *   skc_camera_pass_resident  counters7 = {slab tests, primitive tests, octree nodes
  *                             classified, leaf points tested, cluster contributions,
- *                             point contributions, 0} */
+ *                             point contributions, profile-table reads (one per contribution and
+ *                             wavelength inside its table's range)} */
 int skc_set_surface_points(skc_ctx *ctx, const skc_surface_point *points, uint64_t n);
 int skc_irradiance_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32_t nTasks, float mix,
                             uint64_t *counters3);

@@ -183,7 +183,7 @@ struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo
 
 template <bool COUNT>
 __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sRcp, const float4 *__restrict__ row4, float d2, float scale,
-                                              bool active, float (&acc)[SKC_NS]) {
+                                              bool active, float (&acc)[SKC_NS], uint32_t &gathers) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         float4 e4 = __ldg(row4 + q);
@@ -194,6 +194,7 @@ __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sR
             if (w < SKC_NS) {
                 float f = d2 * sRcp[w];
                 if (active && f < T.lenM1) {
+                    if (COUNT) ++gathers;
                     uint32_t seg = (uint32_t)f;
                     float t = f - (float)seg;
                     float2 v = __ldg(&T.pairs[(size_t)w * T.len + seg]);
@@ -217,6 +218,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
     __syncthreads();
     uint2 *stack = stacks[warp];
     uint32_t wc[4] = {0, 0, 0, 0};
+    uint32_t gathers = 0;          // this lane's table reads (COUNT only)
     const uint32_t nPackets = (uint32_t)((n + 31) / 32);
     // persistent warps: packets are handed out in order from a global counter, so the per-packet cost (none for sky,
     // ~0.1 ms for a packet on the skin) balances across the grid and no wave of CTAs leaves a tail
@@ -263,7 +265,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
         unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
         if (am) {
             if (COUNT) wc[2] += __popc(am);
-            mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.Et + (size_t)ent.x * SKC_EPAD), d2, 1.f, addC, acc);
+            mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.Et + (size_t)ent.x * SKC_EPAD), d2, 1.f, addC, acc, gathers);
         }
         if (dm) {
             if (w1 & SKC_OT_LEAF) {
@@ -278,7 +280,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
                     unsigned pm = __ballot_sync(0xffffffffu, c);
                     if (pm) {
                         if (COUNT) wc[3] += __popc(pm);
-                        mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q2, pa.w, c, acc);
+                        mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q2, pa.w, c, acc, gathers);
                     }
                 }
             } else {
@@ -327,8 +329,9 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
         __syncwarp();
     }
     }   // packet loop
-    if (COUNT && lane == 0 && cnt) {
-        for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
+    if (COUNT && cnt) {
+        if (lane == 0) for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
+        atomicAdd(&cnt[4], (unsigned long long)gathers);
     }
 }
 
@@ -568,7 +571,7 @@ extern "C" int skc_set_camera_rays(skc_ctx *ctx, const skc_ray *rays, uint64_t n
 }
 
 // counters7 (optional): [0] slab tests [1] primitive tests (closest hit), [2] octree nodes classified,
-// [3] leaf points tested, [4] cluster contributions, [5] point contributions, [6] rays that hit skin
+// [3] leaf points tested, [4] cluster contributions, [5] point contributions, [6] profile-table reads (packet kernel)
 extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix,
                                         float *L30, uint64_t *counters7) {
     if (!ctx) return 1;
@@ -592,8 +595,7 @@ extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t c
         unsigned long long h[8];
         SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
-        for (int k = 0; k < 6; ++k) counters7[k] = h[k];
-        counters7[6] = 0;
+        for (int k = 0; k < 7; ++k) counters7[k] = h[k];
     }
     return 0;
 }

@@ -142,6 +142,16 @@ void skh_skin_coefficients(const skh_scene *s, float *out124) {
     for (int l = 0; l < 2; ++l) { memcpy(o, sp.mua[l], 120); o += 30; memcpy(o, sp.musp[l], 120); o += 30; }
     o[0] = sp.eta[0]; o[1] = sp.eta[1]; o[2] = sp.thickness[0]; o[3] = sp.thickness[1];
 }
+// The same without a scene: params9 = f_mel f_eu f_blood f_ohg nmperunit thickness0 ior0 thickness1 ior1
+void skh_skin_spectra(const float *params9, float *out124) {
+    SkinParams k;
+    k.f_mel = params9[0]; k.f_eu = params9[1]; k.f_blood = params9[2]; k.f_ohg = params9[3]; k.nmperunit = params9[4];
+    k.layerThickness[0] = params9[5]; k.layerIor[0] = params9[6]; k.layerThickness[1] = params9[7]; k.layerIor[1] = params9[8];
+    SkinLayerSpectra sp = ComputeSkinLayerSpectra(k);
+    float *o = out124;
+    for (int l = 0; l < 2; ++l) { memcpy(o, sp.mua[l], 120); o += 30; memcpy(o, sp.musp[l], 120); o += 30; }
+    o[0] = sp.eta[0]; o[1] = sp.eta[1]; o[2] = sp.thickness[0]; o[3] = sp.thickness[1];
+}
 // ComputeMultipoleProfile on the device for the scene's skin material and upload of the result together
 // with the caller's rho_hd table, or the device-generated one when rhoHd is NULL (skc_upload_profile).  hdr120 = [30][dsqSpacing, rcpDsqSpacing, totalR, totalT];
 // rdOut (optional) receives [30][len].  Two-phase like skc_profile_batch: rdOut == NULL only reports len.

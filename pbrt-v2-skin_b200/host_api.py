@@ -33,6 +33,7 @@ def load_host_library():
     lib.skh_bench_rays.restype = C.c_uint64; lib.skh_bench_rays.argtypes = [vp, C.POINTER(vp)]
     lib.skh_irradiance_tasks.restype = C.c_uint32; lib.skh_irradiance_tasks.argtypes = [C.c_uint64, C.c_int]
     lib.skh_skin_coefficients.restype = None; lib.skh_skin_coefficients.argtypes = [vp, vp]
+    lib.skh_skin_spectra.restype = None; lib.skh_skin_spectra.argtypes = [vp, vp]
     lib.skh_build_profile.restype = C.c_int; lib.skh_build_profile.argtypes = [vp, vp, vp, C.POINTER(C.c_uint32), vp, vp, C.c_int]
     _lib = lib
     return lib
@@ -43,6 +44,17 @@ def _view(ptr, nbytes, dtype):
         return None
     buf = (C.c_uint8 * nbytes).from_address(ptr)
     return np.frombuffer(buf, dtype=dtype)
+
+
+def skin_spectra(f_mel=0.15, f_eu=1.0, f_blood=0.002, f_ohg=0.3, nmperunit=100e6, layers=((0.25e6, 1.4), (20e6, 1.4))):
+    """LayeredSkin layer coefficients from the pigment parameters alone (defaults = materials/layeredskin.cpp:234-257):
+    dict of mua/musp [2][30] in scene units, eta[2], thickness[2]."""
+    lib = load_host_library()
+    p = np.array([f_mel, f_eu, f_blood, f_ohg, nmperunit, layers[0][0], layers[0][1], layers[1][0], layers[1][1]], np.float32)
+    v = np.zeros(124, np.float32)
+    lib.skh_skin_spectra(p.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p))
+    c = v[:120].reshape(2, 2, 30)
+    return {"flat": v, "mua": c[:, 0], "musp": c[:, 1], "eta": v[120:122], "thickness": v[122:124]}
 
 
 class HostScene:

@@ -106,3 +106,19 @@ def li_sss(hits, mo, rho, mix):
     out = np.zeros((len(hits), 30), np.float32)
     lib().orc_li_sss(_p(hits), C.c_uint64(len(hits)), _p(mo), _p(rho), None, C.c_float(mix), _p(out))
     return out
+
+
+DT_ORC_LAYER = np.dtype([("ior", "<f4"), ("thickness", "<f4"), ("mua", "<f4"), ("musp", "<f4"), ("g_HG", "<f4")])
+DT_ORC_MPC_OPTIONS = np.dtype([("desiredStepSize", "<f4"), ("desiredLength", "<u4"), ("lerpOnThinSlab", "<i4")])
+
+
+def mpc_profile(specs, opt, resample=True):
+    """oracle/mpc_oracle.c orc_mpc_profile: (d2, R, T, totals) of one layer stack."""
+    L = lib()
+    L.orc_mpc_profile.restype = C.c_uint32
+    specs = np.ascontiguousarray(np.array([tuple(s) for s in specs], DT_ORC_LAYER))
+    o = np.ascontiguousarray(np.array([tuple(opt)], DT_ORC_MPC_OPTIONS))
+    n = L.orc_mpc_profile(len(specs), _p(specs), _p(o), int(resample), None, None, None, None)
+    d2 = np.empty(n, np.float32); R = np.empty(n, np.float32); T = np.empty(n, np.float32); tot = np.empty(2, np.float32)
+    L.orc_mpc_profile(len(specs), _p(specs), _p(o), int(resample), _p(d2), _p(R), _p(T), _p(tot))
+    return d2, R, T, tot

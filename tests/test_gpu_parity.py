@@ -239,11 +239,11 @@ def test_irradiance_dense_vs_oracle(dev, scene, pkg):
     assert np.array_equal(part["E"], irr["E"][a:len(pts) - a])
 
 
-def _profile_err(got, ref):
+def _profile_err(got, ref, scale=None):
     """Relative error against the table's own peak scale: the reference's fp64 FFT leaves a noise floor of
     ~1e-16 x peak in the far tail, so entries below 1e-9 x peak are compared absolutely against that floor."""
     got = np.asarray(got, np.float64); ref = np.asarray(ref, np.float64)
-    floor = np.abs(ref).max() * 1e-9
+    floor = (np.abs(ref).max() if scale is None else scale) * 1e-9
     return np.abs(got - ref) / np.maximum(np.abs(ref), floor)
 
 
@@ -327,3 +327,38 @@ def test_camera_pass_pinned_output_matches_staged(dev, scene):
     assert h0.tobytes() == h1.tobytes()
     e = gu.row_rel_err(L1, g.L_sss)
     assert np.mean(e < 1e-4) > 0.99
+
+
+def c5_parameter_sets(pkg, n_thick=256, desired_length=64):
+    """epidermis thickness swept over [0.02, 2] mean free paths (all thin: the lerp branch),
+    fixed dermis 2.0, eta 1.4/1.4, mua/musp = the 30-bin spectra of SkinCoefficients(0.15, 1, 0.002, 0.3)."""
+    sp = pkg.skin_spectra(0.15, 1.0, 0.002, 0.3)
+    specs, lps, opts = [], [], []
+    for k in range(n_thick):
+        for w in range(30):
+            mfp0 = np.float32(1) / np.float32(sp["mua"][0][w] + sp["musp"][0][w])
+            t = np.float32(0.02 + k * (2.0 - 0.02) / max(n_thick - 1, 1)) * mfp0
+            layers = [(1.4, t, sp["mua"][0][w], sp["musp"][0][w], 0.0), (1.4, 2.0, sp["mua"][1][w], sp["musp"][1][w], 0.0)]
+            mfp = np.float32((np.float32(1) / np.float32(layers[0][2] + layers[0][3]) + np.float32(1) / np.float32(layers[1][2] + layers[1][3])) / np.float32(2))
+            specs += layers; lps.append(2)
+            opts.append((np.float32(np.float32(12) * mfp) / np.float32(desired_length), desired_length, 1))
+    return specs, lps, opts
+
+
+def test_profile_batch_c5_thickness_sweep_vs_oracle(pkg, dev):
+    """C5 at desiredLength 64: 256 thicknesses x 30 wavelengths = 7680 two-layer profiles in ONE skc_profile_batch
+    call; a spread of 96 of them against the C restatement (oracle/mpc_oracle.c), 1e-5 relative with the floor of
+    the transform's own noise."""
+    specs, lps, opts = c5_parameter_sets(pkg)
+    d2, R, T, tot = dev.profile_batch(specs, lps, opts, resample=True)
+    assert R.shape[0] == 7680 and np.all(np.isfinite(R)) and np.all(np.isfinite(T))
+    print("C5 batch: %d profiles of %d entries in %.1f ms (device)" % (R.shape[0], R.shape[1], dev.stage_ms("profile")))
+    worst = 0.0
+    for s in range(0, 7680, 80):
+        od2, oR, oT, otot = orc.mpc_profile(specs[2 * s:2 * s + 2], opts[s], resample=True)
+        assert np.array_equal(d2[s], od2)
+        # T can be exactly 0 in the reference arithmetic (fp32 underflow through the 2-unit dermis): its floor is R's scale
+        worst = max(worst, _profile_err(R[s], oR).max(), _profile_err(T[s], oT, scale=max(np.abs(oR).max(), np.abs(oT).max())).max())
+        assert np.allclose(tot[s], otot, rtol=1e-5, atol=1e-12)
+    print("C5 vs oracle: max rel %.3g" % worst)
+    assert worst < 1e-5

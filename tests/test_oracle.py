@@ -50,3 +50,19 @@ def test_scrambles_stream_layout():
     assert s.shape == (1000, 2, 3) and len(np.unique(s)) > 5900
     # task 0 seeds RNG(0): first MT19937 output for seed 0
     assert s[0, 0, 0] == 2357136044
+
+
+def test_mpc_oracle_pinned_to_reference_known_answers():
+    """oracle/mpc_oracle.c against MPC_ComputeDiffusionProfile of the real reference (tests/golden/mpc_kat.npz):
+    lengths and d2 abscissae bit-exact; R, T within 1e-6 of the table's own scale (own FFT: the rounding noise of the
+    transform differs, the dipole grids do not)."""
+    from golden_util import load_mpc_cases
+    for k, (specs, opt, res, totals, ref) in enumerate(load_mpc_cases()):
+        d2, R, T, tot = orc.mpc_profile(specs, opt, resample=bool(res))
+        assert len(d2) == ref.shape[1], "case %d" % k
+        assert np.array_equal(d2, ref[0]), "case %d d2" % k
+        for got, want, name in ((R, ref[1], "R"), (T, ref[2], "T")):
+            floor = np.abs(want).max() * 1e-9
+            e = np.abs(got.astype(np.float64) - want) / np.maximum(np.abs(want), floor)
+            assert e.max() < 1e-6, "case %d %s: %.3g" % (k, name, e.max())
+        assert np.allclose(tot, totals, rtol=1e-6, atol=1e-12)
