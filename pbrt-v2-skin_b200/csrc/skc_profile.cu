@@ -154,26 +154,56 @@ __global__ void k_pack(const double2 *__restrict__ z, uint32_t G, uint32_t N, do
     Z[(size_t)ii * N + jj] = (i < G && j < G) ? z[(size_t)i * G + j] : make_double2(0., 0.);
 }
 
-// in-place FFT of every row of Z[rows][N]; N a power of two <= 4096; sign = -1 forward, +1 inverse
-__global__ void k_fft_rows(double2 *__restrict__ Z, uint32_t N, uint32_t logN, const double2 *__restrict__ tw, int inverse) {
-    extern __shared__ double2 s[];
-    double2 *row = Z + (size_t)blockIdx.x * N;
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) s[__brev(i) >> (32 - logN)] = row[i];
-    __syncthreads();
-    for (uint32_t st = 1; st <= logN; ++st) {
-        uint32_t half = 1u << (st - 1), stride = N >> st;
-        for (uint32_t b = threadIdx.x; b < N / 2; b += blockDim.x) {
-            uint32_t pos = b & (half - 1), i0 = ((b >> (st - 1)) << st) + pos, i1 = i0 + half;
-            double2 w = tw[pos * stride];
-            if (inverse) w.y = -w.y;
-            double2 a = s[i0], c = s[i1];
-            double2 t = make_double2(w.x * c.x - w.y * c.y, w.x * c.y + w.y * c.x);
-            s[i0] = make_double2(a.x + t.x, a.y + t.y);
-            s[i1] = make_double2(a.x - t.x, a.y - t.y);
+// In-place FFT of every row of Z[rows][N], N a power of two <= 4096, one CTA per row, the row in shared memory.
+// Radix-2 decimation in time on bit-reversed input; up to three consecutive radix-2 stages are done per pass on 8
+// values held in registers (same butterflies, twiddles and operation order as stage-by-stage radix-2, so the result is
+// bit-identical to it) -- 4 shared-memory round trips and barriers for N = 2048 instead of 11.
+// shared-memory index padding: one 16 B slot after every 8 and every 64 elements, so that the stride-8 (first pass),
+// 8-consecutive-then-stride-64 (second pass) and bit-reversed (load) patterns spread over the banks
+__device__ __forceinline__ uint32_t fftSlot(uint32_t i) { return i + (i >> 3) + (i >> 6); }
+
+template <int R>
+__device__ __forceinline__ void fftPass(double2 *s, uint32_t N, uint32_t st, const double2 *__restrict__ tw, int inverse) {
+    const uint32_t half = 1u << (st - 1), items = N >> R;
+    for (uint32_t item = threadIdx.x; item < items; item += blockDim.x) {
+        uint32_t pos = item & (half - 1), base = ((item >> (st - 1)) << (st - 1 + R)) + pos;
+        double2 v[1 << R];
+#pragma unroll
+        for (int k = 0; k < (1 << R); ++k) v[k] = s[fftSlot(base + k * half)];
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            const int hs = 1 << q;
+            const uint32_t stride = N >> (st + q);
+#pragma unroll
+            for (int k = 0; k < (1 << R); ++k) {
+                if (k & hs) continue;
+                double2 w = __ldg(&tw[(pos + (k & (hs - 1)) * half) * stride]);
+                if (inverse) w.y = -w.y;
+                double2 a = v[k], c = v[k + hs];
+                double2 t = make_double2(w.x * c.x - w.y * c.y, w.x * c.y + w.y * c.x);
+                v[k] = make_double2(a.x + t.x, a.y + t.y);
+                v[k + hs] = make_double2(a.x - t.x, a.y - t.y);
+            }
         }
+#pragma unroll
+        for (int k = 0; k < (1 << R); ++k) s[fftSlot(base + k * half)] = v[k];
+    }
+}
+
+__global__ void __launch_bounds__(512) k_fft_rows(double2 *__restrict__ Z, uint32_t N, uint32_t logN, const double2 *__restrict__ tw, int inverse) {
+    extern __shared__ double2 s[];
+    double2 *row = Z + ((size_t)blockIdx.y * N + blockIdx.x) * N;
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) s[fftSlot(__brev(i) >> (32 - logN))] = row[i];
+    __syncthreads();
+    uint32_t st = 1;
+    while (st <= logN) {
+        uint32_t left = logN - st + 1;
+        if (left >= 3) { fftPass<3>(s, N, st, tw, inverse); st += 3; }
+        else if (left == 2) { fftPass<2>(s, N, st, tw, inverse); st += 2; }
+        else { fftPass<1>(s, N, st, tw, inverse); st += 1; }
         __syncthreads();
     }
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) row[i] = s[i];
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) row[i] = s[fftSlot(i)];
 }
 
 __global__ void k_transpose(const double2 *__restrict__ in, uint32_t N, double2 *__restrict__ out) {
@@ -307,14 +337,16 @@ struct ProfileWork {
     }
 };
 
+static size_t fftSmemBytes(uint32_t N) { return (size_t)(N + (N >> 3) + (N >> 6) + 2) * sizeof(double2); }
+
 static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t logN, int inverse) {
     // rows of A in place, transpose into B, rows of B in place: B holds the 2-D transform (transposed layout)
-    uint32_t N = w.N, threads = std::min(N / 2, 1024u);
-    k_fft_rows<<<N, threads, N * sizeof(double2), ctx->stream>>>(A, N, logN, w.tw, inverse);
+    uint32_t N = w.N, threads = std::max(32u, std::min(N / 8, 512u));
+    k_fft_rows<<<N, threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse);
     SKC_LAUNCHED("k_fft_rows");
     k_transpose<<<dim3(N / 32, N / 32), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
     SKC_LAUNCHED("k_transpose");
-    k_fft_rows<<<N, threads, N * sizeof(double2), ctx->stream>>>(B, N, logN, w.tw, inverse);
+    k_fft_rows<<<N, threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse);
     SKC_LAUNCHED("k_fft_rows");
     return 0;
 }
@@ -340,8 +372,8 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     w.G = 2 * length; w.N = 2 * w.G; w.nEntries = nEntries;
     uint32_t G = w.G, N = w.N, logN = 0;
     while ((1u << logN) < N) ++logN;
-    if (N * sizeof(double2) > 48 * 1024)
-        SKC_CUDA(cudaFuncSetAttribute(k_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * sizeof(double2))));
+    if (fftSmemBytes(N) > 48 * 1024)
+        SKC_CUDA(cudaFuncSetAttribute(k_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fftSmemBytes(N)));
     int rc = 1;
     do {
         bool multi = false;
