@@ -18,6 +18,8 @@
 // Node record (3 x float4 = 48 B):  {p.xyz, sumArea} {min.xyz, max.x} {max.y, max.z, w0, w1}
 //   w0 = first child (interior) or first point slot (leaf)
 //   w1 = child mask | SKC_OT_LEAF | SKC_OT_BLACK ; leaf: point count in bits 0-7
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 #include "skc_internal.h"
 #include "skc_cie.h"
@@ -300,6 +302,25 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
             for (int k = 0; k < 3; ++k) { hb[k] = fminf(hb[k], hp[b * 6 + k]); hb[3 + k] = fmaxf(hb[3 + k], hp[b * 6 + 3 + k]); }
     }
     for (int k = 0; k < 6; ++k) ctx->otBoundsHost[k] = hb[k];
+    // --- sort-based topology (skc_octree_sort.cu); trees deeper than its 21-level path keys use the level passes below
+    if (n > 8 && !getenv("SKC_OCTREE_LEVELWISE")) {
+        std::vector<uint32_t> ls;
+        uint32_t totalSorted = 0;
+        int rc = skc_octree_topology_sorted(ctx, n, hb, cap, ls, &totalSorted);
+        if (rc == 1) return 1;
+        if (rc == 0) {
+            OtBuild bs; memset(&bs, 0, sizeof bs);
+            bs.nodes = ctx->otGeo;
+            k_sort_leaves<<<(totalSorted + 255) / 256, 256, 0, ctx->stream>>>(bs, totalSorted, ctx->otPointIdx);
+            SKC_LAUNCHED("k_sort_leaves");
+            skc_stage_end(ctx, 2);
+            ctx->otNodes = totalSorted;
+            ctx->otLevels = (uint32_t)ls.size() - 1;
+            ctx->otLevelStart = ls;
+            ctx->otTopologyReady = true;
+            return 0;
+        }
+    }
     // --- scratch: ping-pong permutation + slot->node maps, digit/rank, per-node ranges, counters
     size_t words = (size_t)(n ? n : 1);
     uint32_t *buf = (uint32_t *)skc_scratch(ctx, 5, (5 * words + 2 * (size_t)cap + 16) * sizeof(uint32_t));

@@ -362,3 +362,22 @@ def test_profile_batch_c5_thickness_sweep_vs_oracle(pkg, dev):
         assert np.allclose(tot[s], otot, rtol=1e-5, atol=1e-12)
     print("C5 vs oracle: max rel %.3g" % worst)
     assert worst < 1e-5
+
+
+def test_octree_sorted_topology_equals_levelwise(dev, scene):
+    """The sort-based topology builder (skc_octree_sort.cu) and the level-by-level one build the same tree: same node
+    count, bit-identical root, and bit-identical Mo (the walk visits children in digit order in both)."""
+    g = scene
+    dev.set_irradiance_points(g.irradiance_points)
+    s = np.nonzero(g.hits["hasBssrdf"] == 1)[0][:512]
+    os.environ["SKC_OCTREE_LEVELWISE"] = "1"
+    try:
+        n0, root0, b0 = dev.build_octree()
+        mo0 = dev.mo(g.hits["p"][s], g.max_error)
+    finally:
+        del os.environ["SKC_OCTREE_LEVELWISE"]
+    n1, root1, b1 = dev.build_octree()
+    mo1 = dev.mo(g.hits["p"][s], g.max_error)
+    assert n0 == n1
+    assert np.array_equal(root0.view(np.uint32), root1.view(np.uint32)) and np.array_equal(b0, b1)
+    assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
