@@ -121,7 +121,7 @@ struct OtsLevels { uint32_t start[OTS_LEVELS + 2]; };
 
 __global__ void __launch_bounds__(OTS_BLOCK) k_emit_nodes(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ info,
                                                           uint32_t n, uint32_t nBlocks, const uint32_t *__restrict__ blockBase, OtsLevels lv,
-                                                          OtsBounds root, float4 *__restrict__ nodes) {
+                                                          OtsBounds root, float4 *__restrict__ nodes, int maxLevel) {
     __shared__ uint32_t warpTot[OTS_BLOCK / 32];
     uint32_t i = blockIdx.x * OTS_BLOCK + threadIdx.x;
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(OTS_BLOCK) k_emit_nodes(const unsigned long lo
     OtsBounds b = root;
     uint32_t containing = 0;      // node of the previous level that holds this point
     uint32_t prevOwn = 0xffffffffu;  // node this thread started at the previous level (if interior: awaits its first child)
-    for (int l = 0; l <= OTS_LEVELS; ++l) {
+    for (int l = 0; l <= maxLevel; ++l) {
         bool alive = l <= depth;
         uint32_t digit = 0;
         if (l > 0 && alive) { digit = (uint32_t)(key >> (3 * (OTS_LEVELS - l))) & 7u; otsChild(b, digit); }
@@ -216,7 +216,7 @@ int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32
     levelStart.push_back(total);
     if (total > cap) return skc_fail(ctx, "skc_build_octree: node capacity %u exceeded (%u nodes)", cap, total);
     SKC_CUDA(cudaMemsetAsync(ctx->otGeo, 0, (size_t)total * 3 * sizeof(float4), ctx->stream));
-    k_emit_nodes<<<nBlocks, OTS_BLOCK, 0, ctx->stream>>>(keys, info, n, nBlocks, blockCount, lv, root, ctx->otGeo);
+    k_emit_nodes<<<nBlocks, OTS_BLOCK, 0, ctx->stream>>>(keys, info, n, nBlocks, blockCount, lv, root, ctx->otGeo, (int)levelStart.size() - 2);
     SKC_LAUNCHED("k_emit_nodes");
     SKC_CUDA(cudaMemcpyAsync(ctx->otPointIdx, idx, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     *totalOut = total;
