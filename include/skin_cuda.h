@@ -144,6 +144,14 @@ int skc_set_point_count(skc_ctx *ctx, uint64_t n);
  * the device irradiance-point set; the flat tree stays on the device.  Optional outputs:
  * node count, root {p[3], sumArea, Et[30]} (34 floats), bounds (6 floats). */
 int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6);
+/* MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) as ONE call: the irradiance pass over
+ * points [first, first+count) and, concurrently on a second stream, the octree topology of ALL nTotal points (it
+ * needs only their positions).  Follow with skc_build_octree_finalize -- directly on one GPU; after the all-gather of
+ * the other ranks' irradiance rows (skc_irradiance_dev) on several.  skc_preprocess takes host points (uploaded
+ * batch by batch behind the kernels), skc_preprocess_resident the set given to skc_set_surface_points. */
+int skc_preprocess(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal, uint64_t first, uint64_t count,
+                   uint32_t nTasks, float mix);
+int skc_preprocess_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32_t nTasks, float mix);
 /* The two halves of skc_build_octree, for callers that can overlap them with an exchange: the topology pass reads
  * only the point positions (bounds, splitting by `p > pMid`, leaf order = insertion order; diffusionutil.h:94-132,
  * multipolesubsurface.cpp:218-237); finalize gathers the records into leaf order and runs InitHierarchy

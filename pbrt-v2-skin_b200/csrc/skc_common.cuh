@@ -22,6 +22,8 @@ struct skc_ctx {
     int smCount = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t auxStream = nullptr;        // octree topology while the irradiance pass runs on `stream` (skc_preprocess*)
+    cudaEvent_t defEv0 = nullptr, defEv1 = nullptr;   // deferred stage timing of the irradiance pass
     cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute
     std::vector<cudaEvent_t> evPool;         // untimed events ordering copyStream against stream
     bool stageAccumulate = false;            // skc_stage_end adds to stageMs instead of overwriting (chunked passes)
@@ -79,8 +81,8 @@ struct skc_ctx {
     uint64_t resRaysCount = 0;
 
     // --- scratch
-    void *scratch[8] = {nullptr};
-    size_t scratchBytes[8] = {0};
+    void *scratch[12] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently)
+    size_t scratchBytes[12] = {0};
 };
 
 // topology flags word: bits 0-7 child mask (interior) or point count (leaf),

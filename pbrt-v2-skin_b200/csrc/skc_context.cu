@@ -61,6 +61,8 @@ extern "C" skc_ctx *skc_create(int device) {
     if (cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->smCount <= 0) ctx->smCount = 148;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->auxStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->defEv0) != cudaSuccess || cudaEventCreate(&ctx->defEv1) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         skc_fail(nullptr, "skc_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -78,11 +80,14 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->lights, ctx->ipPosArea, ctx->ipE,
                     ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);
-    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     cudaStreamSynchronize(ctx->copyStream);
     cudaStreamDestroy(ctx->copyStream);
+    cudaStreamSynchronize(ctx->auxStream);
+    cudaStreamDestroy(ctx->auxStream);
+    cudaEventDestroy(ctx->defEv0); cudaEventDestroy(ctx->defEv1);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

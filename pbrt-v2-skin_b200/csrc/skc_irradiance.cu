@@ -15,6 +15,9 @@
 //                through the BVH), then the warp transposes: lane = wavelength, and the
 //                30-wide spectral accumulation runs with coalesced 120 B rows of the rho
 //                table, Lemit and the output E.
+#include <algorithm>
+#include <utility>
+#include <vector>
 #include "skc_bvh.cuh"
 #include "skc_internal.h"
 
@@ -425,7 +428,7 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
 // copy stream, each batch's kernels waiting only for their own slice, so the 1 GB upload hides behind the compute
 static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal, uint64_t first, uint64_t count,
                          uint32_t nTasks, float mix, const float *dAlb, unsigned long long *cntDev,
-                         const skc_surface_point *hostPts = nullptr) {
+                         const skc_surface_point *hostPts = nullptr, bool deferTiming = false, uint64_t *batchPtsOut = nullptr) {
     if (!ctx->bvhNodes) return skc_fail(ctx, "skc_irradiance: no BVH uploaded");
     if (!ctx->nLights) return skc_fail(ctx, "skc_irradiance: no lights uploaded");
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_irradiance: no rho table uploaded (skc_upload_profile)");
@@ -447,10 +450,11 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
         while (lo < hi) { uint64_t m = (lo + hi + 1) / 2; if (m * nTotal / nTasks < first + count) lo = m; else hi = m - 1; }
         t1 = (uint32_t)lo;
     }
-    skc_stage_begin(ctx);
+    // deferTiming: no host synchronisation inside the pass (the caller overlaps other work and collects the time later)
+    if (deferTiming) SKC_CUDA(cudaEventRecord(ctx->defEv0, ctx->stream)); else skc_stage_begin(ctx);
     k_scrambles<<<t1 - t0 + 1, 256, 0, ctx->stream>>>(t0, nTasks, nTotal, first, count, wpp, dScr);
     SKC_LAUNCHED("k_scrambles");
-    skc_stage_end(ctx, 0);
+    if (!deferTiming) skc_stage_end(ctx, 0);
     if (ctx->nLights > IRR_MAX_LIGHTS) return skc_fail(ctx, "skc_irradiance: %u lights, at most %d supported", ctx->nLights, IRR_MAX_LIGHTS);
     IrrSlots sl; sl.nLights = ctx->nLights; sl.S = 0;
     for (uint32_t j = 0; j < IRR_MAX_LIGHTS; ++j) { sl.nS[j] = j < ctx->nLights ? ctx->lightNS[j] : 0xffffffffu; if (j < ctx->nLights) sl.S += sl.nS[j]; }
@@ -459,6 +463,7 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
     uint64_t batchPts = maxSlots / sl.S; if (!batchPts) batchPts = 1;
     if (batchPts > count) batchPts = count;
     uint64_t nBatches = (count + batchPts - 1) / batchPts, slots = batchPts * sl.S;
+    if (batchPtsOut) *batchPtsOut = batchPts;
     float2 *dCosPdf = (float2 *)skc_scratch(ctx, 4, slots * sizeof(float2));
     char *dRays = (char *)skc_scratch(ctx, 5, slots * 36);
     uint32_t *dNRays = (uint32_t *)skc_scratch(ctx, 6, nBatches * sizeof(uint32_t));
@@ -476,7 +481,7 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
             SKC_CUDA(cudaEventRecord(skc_event(ctx, 1 + b), ctx->copyStream));
         }
     }
-    skc_stage_begin(ctx);
+    if (!deferTiming) skc_stage_begin(ctx);
     SKC_CUDA(cudaMemsetAsync(dNRays, 0, nBatches * sizeof(uint32_t), ctx->stream));
     for (uint64_t b = 0; b < nBatches; ++b) {
         uint64_t pb = b * batchPts;
@@ -496,7 +501,112 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }
-    skc_stage_end(ctx, 1);
+    if (deferTiming) SKC_CUDA(cudaEventRecord(ctx->defEv1, ctx->stream)); else skc_stage_end(ctx, 1);
+    return 0;
+}
+
+// ---- Preprocess as one call: irradiance pass on `stream`, octree topology on `auxStream` -------------------------
+// The octree's cell decomposition depends only on the point positions, which are known before any irradiance is:
+// MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) = irradiance tasks, then Insert of every
+// point, then InitHierarchy.  Here the positions of ALL points are written first, the topology pass runs on the
+// auxiliary stream while the irradiance kernels (issue bound, little memory traffic) run on the main one, and
+// skc_build_octree_finalize (leaf gather + InitHierarchy) follows when both are done.  In a multi-GPU run every rank
+// builds the topology of the full point set this way while it computes only its own shard of irradiance.
+__global__ void __launch_bounds__(256) k_positions(const skc_surface_point *__restrict__ pts, uint64_t n, float4 *__restrict__ posArea) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *sp = reinterpret_cast<const float *>(pts + i);
+    posArea[i] = make_float4(__ldg(sp), __ldg(sp + 1), __ldg(sp + 2), __ldg(sp + 9));
+}
+
+static int topologyOnAux(skc_ctx *ctx, cudaEvent_t positionsReady) {
+    SKC_CUDA(cudaStreamWaitEvent(ctx->auxStream, positionsReady, 0));
+    std::swap(ctx->stream, ctx->auxStream);
+    int rc = skc_build_octree_topology(ctx);
+    std::swap(ctx->stream, ctx->auxStream);
+    return rc;
+}
+
+static int collectDeferred(skc_ctx *ctx) {
+    SKC_CUDA(cudaEventSynchronize(ctx->defEv1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->defEv0, ctx->defEv1);
+    ctx->stageMs[0] = 0.f; ctx->stageMs[1] = ms;     // scramble time is inside the pass here
+    return 0;
+}
+
+extern "C" int skc_preprocess_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32_t nTasks, float mix) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->resPts) return skc_fail(ctx, "skc_preprocess_resident: no surface points set");
+    uint64_t n = ctx->resPtsCount;
+    if (first + count > n) return skc_fail(ctx, "skc_preprocess_resident: bad range");
+    if (skc_ensure_points(ctx, n)) return 1;
+    ctx->ipCount = n;
+    cudaEvent_t ready = skc_event(ctx, 0);
+    if (!ready) return 1;
+    k_positions<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->resPts, n, ctx->ipPosArea);
+    SKC_LAUNCHED("k_positions");
+    SKC_CUDA(cudaEventRecord(ready, ctx->stream));
+    if (count && irradianceDev(ctx, ctx->resPts + first, n, first, count, nTasks, mix, nullptr, nullptr, nullptr, true)) return 1;
+    int rc = topologyOnAux(ctx, ready);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (rc) return rc;
+    SKC_CUDA(e);
+    if (count) return collectDeferred(ctx);
+    return 0;
+}
+
+extern "C" int skc_preprocess(skc_ctx *ctx, const skc_surface_point *points, uint64_t nTotal, uint64_t first, uint64_t count,
+                              uint32_t nTasks, float mix) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (first + count > nTotal || !nTotal) return skc_fail(ctx, "skc_preprocess: bad range");
+    if (skc_ensure_points(ctx, nTotal)) return 1;
+    ctx->ipCount = nTotal;
+    // all points go up (the topology needs every position); the irradiance pass runs on [first, first+count) and its
+    // batches wait only for their own slice of the upload
+    skc_surface_point *dAll = (skc_surface_point *)skc_scratch(ctx, 0, nTotal * sizeof(skc_surface_point));
+    if (!dAll) return 1;
+    uint64_t batchPts = count ? count : 1, nB = 0;
+    if (count) {
+        if (irradianceDev(ctx, dAll + first, nTotal, first, count, nTasks, mix, nullptr, nullptr, points + first, true, &batchPts)) return 1;
+        nB = (count + batchPts - 1) / batchPts;
+        for (uint64_t b = 0; b < nB; ++b) {       // positions of the own range, batch by batch behind the upload
+            uint64_t a = first + b * batchPts, np = std::min(batchPts, first + count - a);
+            SKC_CUDA(cudaStreamWaitEvent(ctx->auxStream, skc_event(ctx, 1 + b), 0));
+            k_positions<<<(unsigned)((np + 255) / 256), 256, 0, ctx->auxStream>>>(dAll + a, np, ctx->ipPosArea + a);
+            SKC_LAUNCHED("k_positions");
+        }
+    } else {
+        cudaEvent_t e0 = skc_event(ctx, 0);
+        if (!e0) return 1;
+        SKC_CUDA(cudaEventRecord(e0, ctx->stream));
+        SKC_CUDA(cudaStreamWaitEvent(ctx->copyStream, e0, 0));
+    }
+    // the other ranks' ranges (multi-GPU): positions only are needed, but the records are 44 B AoS, so they go up whole
+    const uint64_t chunk = 1ull << 22;
+    size_t ev = 1 + nB;
+    uint64_t ranges[2][2] = {{0, first}, {first + count, nTotal}};
+    for (int r = 0; r < 2; ++r)
+        for (uint64_t a = ranges[r][0]; a < ranges[r][1]; a += chunk) {
+            uint64_t np = std::min(chunk, ranges[r][1] - a);
+            cudaEvent_t e = skc_event(ctx, ev++);
+            if (!e) return 1;
+            SKC_CUDA(cudaMemcpyAsync(dAll + a, points + a, np * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->copyStream));
+            SKC_CUDA(cudaEventRecord(e, ctx->copyStream));
+            SKC_CUDA(cudaStreamWaitEvent(ctx->auxStream, e, 0));
+            k_positions<<<(unsigned)((np + 255) / 256), 256, 0, ctx->auxStream>>>(dAll + a, np, ctx->ipPosArea + a);
+            SKC_LAUNCHED("k_positions");
+        }
+    cudaEvent_t ready = skc_event(ctx, ev);
+    if (!ready) return 1;
+    SKC_CUDA(cudaEventRecord(ready, ctx->auxStream));
+    int rc = topologyOnAux(ctx, ready);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (rc) return rc;
+    SKC_CUDA(e);
+    if (count) return collectDeferred(ctx);
     return 0;
 }
 

@@ -291,7 +291,7 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     float hb[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
     if (n) {
         const int nb = 296;
-        float *dPart = (float *)skc_scratch(ctx, 4, nb * 6 * sizeof(float));
+        float *dPart = (float *)skc_scratch(ctx, 8, nb * 6 * sizeof(float));
         if (!dPart) return 1;
         k_bounds_partial<<<nb, 256, 0, ctx->stream>>>(ctx->ipPosArea, n, dPart);
         SKC_LAUNCHED("k_bounds_partial");
@@ -323,8 +323,8 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     }
     // --- scratch: ping-pong permutation + slot->node maps, digit/rank, per-node ranges, counters
     size_t words = (size_t)(n ? n : 1);
-    uint32_t *buf = (uint32_t *)skc_scratch(ctx, 5, (5 * words + 2 * (size_t)cap + 16) * sizeof(uint32_t));
-    uint32_t *cnt = (uint32_t *)skc_scratch(ctx, 6, ((size_t)cap * 8 + 8) * sizeof(uint32_t));
+    uint32_t *buf = (uint32_t *)skc_scratch(ctx, 9, (5 * words + 2 * (size_t)cap + 16) * sizeof(uint32_t));
+    uint32_t *cnt = (uint32_t *)skc_scratch(ctx, 10, ((size_t)cap * 8 + 8) * sizeof(uint32_t));
     if (!buf || !cnt) return 1;
     uint32_t *idxA = buf, *idxB = buf + words, *snA = buf + 2 * words, *snB = buf + 3 * words, *dr = buf + 4 * words;
     OtBuild b;

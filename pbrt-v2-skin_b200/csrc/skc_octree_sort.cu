@@ -174,7 +174,7 @@ int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32
     cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, dk, dv, (int)n, 0, 3 * OTS_LEVELS, ctx->stream);
     size_t keyBytes = ((size_t)n * 8 + 255) / 256 * 256, idxBytes = ((size_t)n * 4 + 255) / 256 * 256;
     size_t cntBytes = ((size_t)(OTS_LEVELS + 1) * nBlocks * 4 + 255) / 256 * 256;
-    char *buf = (char *)skc_scratch(ctx, 5, 2 * keyBytes + 2 * idxBytes + idxBytes + cntBytes + tempBytes + 1024);
+    char *buf = (char *)skc_scratch(ctx, 9, 2 * keyBytes + 2 * idxBytes + idxBytes + cntBytes + tempBytes + 1024);
     if (!buf) return 1;
     unsigned long long *k0 = (unsigned long long *)buf, *k1 = (unsigned long long *)(buf + keyBytes);
     uint32_t *v0 = (uint32_t *)(buf + 2 * keyBytes), *v1 = (uint32_t *)(buf + 2 * keyBytes + idxBytes);

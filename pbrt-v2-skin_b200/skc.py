@@ -29,7 +29,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
-           "skc_build_octree_topology", "skc_build_octree_finalize"]
+           "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident"]
 
 
 class SkcError(RuntimeError):
@@ -70,6 +70,8 @@ def load_library():
     lib.skc_set_irradiance_points.restype = i32; lib.skc_set_irradiance_points.argtypes = [vp, vp, u64]
     lib.skc_irradiance_dev.restype = i32; lib.skc_irradiance_dev.argtypes = [vp, u64, C.POINTER(vp), C.POINTER(vp)]
     lib.skc_build_octree.restype = i32; lib.skc_build_octree.argtypes = [vp, C.POINTER(u32), vp, vp]
+    lib.skc_preprocess.restype = i32; lib.skc_preprocess.argtypes = [vp, vp, u64, u64, u64, u32, f32]
+    lib.skc_preprocess_resident.restype = i32; lib.skc_preprocess_resident.argtypes = [vp, u64, u64, u32, f32]
     lib.skc_build_octree_topology.restype = i32; lib.skc_build_octree_topology.argtypes = [vp]
     lib.skc_build_octree_finalize.restype = i32; lib.skc_build_octree_finalize.argtypes = [vp, C.POINTER(u32), vp, vp]
     lib.skc_mo.restype = i32; lib.skc_mo.argtypes = [vp, vp, u64, f32, vp]
@@ -205,6 +207,15 @@ class SkinDevice:
         root = np.zeros(34, np.float32); bounds = np.zeros(6, np.float32)
         self._ck(self.lib.skc_build_octree(self.ctx, C.byref(nn), _ptr(root), _ptr(bounds)))
         return int(nn.value), root, bounds
+
+    def preprocess(self, points, n_tasks, mix=0.5, first=0, count=None):
+        """Irradiance pass over [first, first+count) + octree topology of all points, overlapped (skc_preprocess)."""
+        pts = np.ascontiguousarray(points if points.dtype == DT_SURFACE_POINT else points.view(DT_SURFACE_POINT))
+        count = len(pts) - first if count is None else count
+        self._ck(self.lib.skc_preprocess(self.ctx, _ptr(pts), len(pts), first, count, n_tasks, mix))
+
+    def preprocess_resident(self, first, count, n_tasks, mix=0.5):
+        self._ck(self.lib.skc_preprocess_resident(self.ctx, first, count, n_tasks, mix))
 
     def build_octree_topology(self):
         self._ck(self.lib.skc_build_octree_topology(self.ctx))

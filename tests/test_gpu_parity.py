@@ -381,3 +381,23 @@ def test_octree_sorted_topology_equals_levelwise(dev, scene):
     assert n0 == n1
     assert np.array_equal(root0.view(np.uint32), root1.view(np.uint32)) and np.array_equal(b0, b1)
     assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
+
+
+def test_preprocess_one_call_equals_staged_calls(dev, scene):
+    """skc_preprocess (irradiance pass + octree topology overlapped on two streams) followed by
+    skc_build_octree_finalize gives bit-identical irradiance rows, octree root and Mo to skc_irradiance followed by
+    skc_build_octree."""
+    g = scene
+    s = np.nonzero(g.hits["hasBssrdf"] == 1)[0][:256]
+    irr = dev.irradiance(g.surface_points, g.n_tasks, g.mix)
+    n0, root0, b0 = dev.build_octree()
+    mo0 = dev.mo(g.hits["p"][s], g.max_error)
+    dev.preprocess(g.surface_points, g.n_tasks, g.mix)
+    n1, root1, b1 = dev.build_octree_finalize()
+    mo1 = dev.mo(g.hits["p"][s], g.max_error)
+    assert n0 == n1 and np.array_equal(root0.view(np.uint32), root1.view(np.uint32)) and np.array_equal(b0, b1)
+    assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
+    dev.set_surface_points(g.surface_points)
+    dev.preprocess_resident(0, len(g.surface_points), g.n_tasks, g.mix)
+    n2, root2, _ = dev.build_octree_finalize()
+    assert n2 == n0 and np.array_equal(root0.view(np.uint32), root2.view(np.uint32))
