@@ -90,7 +90,7 @@ int skc_synchronize(skc_ctx *ctx);
 /* Counters of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t skc_launch_count(const skc_ctx *ctx);
 /* Device time of the last call of each stage in ms (CUDA events on the ctx stream).
- * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table */
+ * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table, 8 tessellation */
 float skc_stage_ms(const skc_ctx *ctx, int stage);
 
 /* CUDA-event timer on the context's stream spanning any sequence of calls (bench.py). */
@@ -144,6 +144,14 @@ int skc_set_point_count(skc_ctx *ctx, uint64_t n);
  * the device irradiance-point set; the flat tree stays on the device.  Optional outputs:
  * node count, root {p[3], sumArea, Et[30]} (34 floats), bounds (6 floats). */
 int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bounds6);
+/* Surface points on the device: GetSurfacePointsThroughTessellation (renderers/surfacepoints.cpp:362-369)
+ * -> TriangleMesh::TessellateSurfacePoints (shapes/trianglemesh.cpp:187-351) for the mesh given to skc_upload_bvh, same
+ * points in the same order as the reference (centroid or incentre of every sub-triangle of the ring tessellation with
+ * edge factors round(0.8 * edge / minSampleDist)).  The result becomes the resident surface-point set (as after
+ * skc_set_surface_points); skc_get_surface_points copies a range of it to the host. */
+int skc_tessellate_resident(skc_ctx *ctx, float minSampleDist, int incenter, uint32_t materialId, uint64_t *countOut);
+int skc_get_surface_points(skc_ctx *ctx, uint64_t first, uint64_t count, skc_surface_point *out);
+
 /* MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) as ONE call: the irradiance pass over
  * points [first, first+count) and, concurrently on a second stream, the octree topology of ALL nTotal points (it
  * needs only their positions).  Follow with skc_build_octree_finalize -- directly on one GPU; after the all-gather of

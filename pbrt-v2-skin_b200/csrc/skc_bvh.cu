@@ -18,83 +18,12 @@ __global__ void __launch_bounds__(128) k_trace_any(BvhView bv, const skc_ray *__
     out[i] = occ ? 1 : 0;
 }
 
-// core/geometry.h:564-574
-__device__ inline void coordinateSystem(f3 v1, f3 *v2, f3 *v3) {
-    if (fabsf(v1.x) > fabsf(v1.y)) {
-        float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z);
-        *v2 = mk3(-v1.z * invLen, 0.f, v1.x * invLen);
-    } else {
-        float invLen = 1.f / sqrtf(v1.y * v1.y + v1.z * v1.z);
-        *v2 = mk3(0.f, v1.z * invLen, -v1.y * invLen);
-    }
-    *v3 = cross3(v1, *v2);
-}
-
-__device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
-
-// Shading point/normal of a triangle hit: trianglemesh.inl:92-133 (dg), :224-299 (shading
-// geometry), core/diffgeom.cpp:40-55 (nn and the orientation flip).
 __device__ inline void triShading(const MeshView &mv, int prim, const DRay &ray, float t, float b1, float b2,
                                   f3 *pOut, f3 *nOut) {
     int4 vi = __ldg(&mv.primInfo[prim]);
-    f3 p1 = ld3(mv.P, vi.x), p2 = ld3(mv.P, vi.y), p3 = ld3(mv.P, vi.z);
-    f3 e1 = sub3(p2, p1), e2 = sub3(p3, p1);
-    float uvs[3][2];
-    if (mv.UV) {
-        uvs[0][0] = mv.UV[2 * vi.x]; uvs[0][1] = mv.UV[2 * vi.x + 1];
-        uvs[1][0] = mv.UV[2 * vi.y]; uvs[1][1] = mv.UV[2 * vi.y + 1];
-        uvs[2][0] = mv.UV[2 * vi.z]; uvs[2][1] = mv.UV[2 * vi.z + 1];
-    } else {
-        uvs[0][0] = 0.f; uvs[0][1] = 0.f; uvs[1][0] = 1.f; uvs[1][1] = 0.f; uvs[2][0] = 1.f; uvs[2][1] = 1.f;
-    }
-    float du1 = uvs[0][0] - uvs[2][0], du2 = uvs[1][0] - uvs[2][0];
-    float dv1 = uvs[0][1] - uvs[2][1], dv2 = uvs[1][1] - uvs[2][1];
-    f3 dp1 = sub3(p1, p3), dp2 = sub3(p2, p3);
-    f3 dpdu, dpdv;
-    float determinant = du1 * dv2 - dv1 * du2;
-    if (determinant == 0.f) {
-        coordinateSystem(normalize3(cross3(e2, e1)), &dpdu, &dpdv);
-    } else {
-        float invdet = 1.f / determinant;
-        dpdu = mul3(sub3(mul3(dp1, dv2), mul3(dp2, dv1)), invdet);
-        dpdv = mul3(add3(mul3(dp1, -du2), mul3(dp2, du1)), invdet);
-    }
-    float b0 = 1 - b1 - b2;
-    float tu = b0 * uvs[0][0] + b1 * uvs[1][0] + b2 * uvs[2][0];
-    float tv = b0 * uvs[0][1] + b1 * uvs[1][1] + b2 * uvs[2][1];
+    float b0 = 1 - b1 - b2, tu, tv;
     *pOut = add3(ray.o, mul3(ray.d, t));
-    f3 nn;
-    if (!mv.N) {
-        nn = normalize3(cross3(dpdu, dpdv));
-    } else {
-        float A00 = uvs[1][0] - uvs[0][0], A01 = uvs[2][0] - uvs[0][0];
-        float A10 = uvs[1][1] - uvs[0][1], A11 = uvs[2][1] - uvs[0][1];
-        float C0 = tu - uvs[0][0], C1 = tv - uvs[0][1];
-        float bb[3];
-        float det = A00 * A11 - A01 * A10;     // core/transform.cpp:39-49
-        bool ok = !(fabsf(det) < 1e-10f);
-        if (ok) {
-            bb[1] = (A11 * C0 - A01 * C1) / det;
-            bb[2] = (A00 * C1 - A10 * C0) / det;
-            if (isnan(bb[1]) || isnan(bb[2])) ok = false;
-        }
-        if (!ok) bb[0] = bb[1] = bb[2] = 1.f / 3.f;
-        else bb[0] = 1.f - bb[1] - bb[2];
-        f3 n0 = ld3(mv.N, vi.x), n1 = ld3(mv.N, vi.y), n2 = ld3(mv.N, vi.z);
-        f3 nsum = add3(add3(mul3(n0, bb[0]), mul3(n1, bb[1])), mul3(n2, bb[2]));
-        f3 ns = normalize3(xformNormal(mv.w2o, nsum));
-        f3 ss = normalize3(dpdu);
-        f3 ts = cross3(ss, ns);
-        if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) {
-            ts = normalize3(ts);
-            ss = cross3(ts, ns);
-        } else {
-            coordinateSystem(ns, &ss, &ts);
-        }
-        nn = normalize3(cross3(ss, ts));
-    }
-    if (mv.flip) nn = mul3(nn, -1.f);
-    *nOut = nn;
+    triShadingGeometry(mv, vi, b0, b1, b2, nOut, &tu, &tv);
 }
 
 __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, const skc_ray *__restrict__ rays,
@@ -200,6 +129,8 @@ extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t 
     if (upload(ctx, &ctx->meshP, P, 3 * (size_t)nVerts)) return 1;
     if (upload(ctx, &ctx->meshN, N, N ? 3 * (size_t)nVerts : 0)) return 1;
     if (upload(ctx, &ctx->meshUV, uv, uv ? 2 * (size_t)nVerts : 0)) return 1;
+    if (upload(ctx, &ctx->meshIdx, indices, indices ? 3 * (size_t)nTris : 0)) return 1;
+    ctx->meshTris = indices ? nTris : 0;
     if (upload(ctx, &ctx->spheres, spheres, nSpheres)) return 1;
     ctx->nNodes = nNodes; ctx->nPrims = nPrims; ctx->nVerts = nVerts; ctx->nSpheres = nSpheres;
     if (meshO2W) memcpy(ctx->meshO2W, meshO2W, 128);

@@ -15,7 +15,7 @@
 
 #define SKC_NS SKC_NSPECTRAL
 #define SKC_EPAD 32            // spectral rows are padded to 32 floats = one 128 B line
-#define SKC_NSTAGES 8
+#define SKC_NSTAGES 9
 
 struct skc_ctx {
     int device = 0;
@@ -38,6 +38,8 @@ struct skc_ctx {
     uint32_t nPrims = 0;
     int4 *primInfo = nullptr;      // per primitive: v0,v1,v2 (mesh vertex ids), type
     float *meshP = nullptr, *meshN = nullptr, *meshUV = nullptr;
+    int32_t *meshIdx = nullptr;    // vertex indices in MESH triangle order (surface-point tessellation)
+    uint32_t meshTris = 0;
     uint32_t nVerts = 0;
     float meshO2W[32];
     int meshFlip = 0;              // ReverseOrientation ^ TransformSwapsHandedness
@@ -76,7 +78,7 @@ struct skc_ctx {
 
     // --- resident inputs (skc_set_surface_points / skc_set_camera_rays)
     skc_surface_point *resPts = nullptr;
-    uint64_t resPtsCount = 0;
+    uint64_t resPtsCount = 0, resPtsCap = 0;
     skc_ray *resRays = nullptr;
     uint64_t resRaysCount = 0;
 

@@ -643,9 +643,10 @@ extern "C" int skc_set_surface_points(skc_ctx *ctx, const skc_surface_point *poi
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     if (ctx->resPts) { cudaFree(ctx->resPts); ctx->resPts = nullptr; }
-    ctx->resPtsCount = 0;
+    ctx->resPtsCount = 0; ctx->resPtsCap = 0;
     if (!n) return 0;
     SKC_CUDA(cudaMalloc((void **)&ctx->resPts, n * sizeof(skc_surface_point)));
+    ctx->resPtsCap = n;
     SKC_CUDA(cudaMemcpyAsync(ctx->resPts, points, n * sizeof(skc_surface_point), cudaMemcpyHostToDevice, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->resPtsCount = n;

@@ -20,7 +20,7 @@ DT_MPC_OPTIONS = np.dtype([("desiredStepSize", "<f4"), ("desiredLength", "<u4"),
 assert DT_BVH_NODE.itemsize == 32 and DT_LIGHT.itemsize == 280 and DT_RAY.itemsize == 32 and DT_HIT.itemsize == 56
 assert DT_SURFACE_POINT.itemsize == 44 and DT_IRR_POINT.itemsize == 152
 
-STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6, "rho": 7}
+STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6, "rho": 7, "tessellate": 8}
 
 # every symbol include/skin_cuda.h declares
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
@@ -29,7 +29,8 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
-           "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident"]
+           "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
+           "skc_tessellate_resident", "skc_get_surface_points"]
 
 
 class SkcError(RuntimeError):
@@ -70,6 +71,8 @@ def load_library():
     lib.skc_set_irradiance_points.restype = i32; lib.skc_set_irradiance_points.argtypes = [vp, vp, u64]
     lib.skc_irradiance_dev.restype = i32; lib.skc_irradiance_dev.argtypes = [vp, u64, C.POINTER(vp), C.POINTER(vp)]
     lib.skc_build_octree.restype = i32; lib.skc_build_octree.argtypes = [vp, C.POINTER(u32), vp, vp]
+    lib.skc_tessellate_resident.restype = i32; lib.skc_tessellate_resident.argtypes = [vp, f32, i32, u32, C.POINTER(u64)]
+    lib.skc_get_surface_points.restype = i32; lib.skc_get_surface_points.argtypes = [vp, u64, u64, vp]
     lib.skc_preprocess.restype = i32; lib.skc_preprocess.argtypes = [vp, vp, u64, u64, u64, u32, f32]
     lib.skc_preprocess_resident.restype = i32; lib.skc_preprocess_resident.argtypes = [vp, u64, u64, u32, f32]
     lib.skc_build_octree_topology.restype = i32; lib.skc_build_octree_topology.argtypes = [vp]
@@ -207,6 +210,17 @@ class SkinDevice:
         root = np.zeros(34, np.float32); bounds = np.zeros(6, np.float32)
         self._ck(self.lib.skc_build_octree(self.ctx, C.byref(nn), _ptr(root), _ptr(bounds)))
         return int(nn.value), root, bounds
+
+    def tessellate_resident(self, min_dist, incenter=False, material_id=0):
+        """Surface points of the uploaded mesh, generated on the device into the resident set; returns the count."""
+        n = C.c_uint64(0)
+        self._ck(self.lib.skc_tessellate_resident(self.ctx, min_dist, int(incenter), material_id, C.byref(n)))
+        return int(n.value)
+
+    def get_surface_points(self, first, count):
+        out = np.empty(count, DT_SURFACE_POINT)
+        self._ck(self.lib.skc_get_surface_points(self.ctx, first, count, _ptr(out)))
+        return out
 
     def preprocess(self, points, n_tasks, mix=0.5, first=0, count=None):
         """Irradiance pass over [first, first+count) + octree topology of all points, overlapped (skc_preprocess)."""

@@ -401,3 +401,23 @@ def test_preprocess_one_call_equals_staged_calls(dev, scene):
     dev.preprocess_resident(0, len(g.surface_points), g.n_tasks, g.mix)
     n2, root2, _ = dev.build_octree_finalize()
     assert n2 == n0 and np.array_equal(root0.view(np.uint32), root2.view(np.uint32))
+
+
+def test_device_tessellation_bit_exact(pkg, dev):
+    """N2: skc_tessellate_resident against the host tessellator (itself bit-identical to the reference's surface-point
+    export, tests/test_host_mirror.py): same points, same order, every field bit for bit; centroid and incentre
+    variants, three sampling distances (tess factors 1..~30)."""
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tiny.scene"))
+    try:
+        hs.upload(dev)
+        for min_dist, incenter in ((0.1, False), (0.037, False), (0.5, False), (0.06, True)):
+            ref = hs.tessellate(min_dist, incenter)
+            n = dev.tessellate_resident(min_dist, incenter, material_id=int(ref["materialId"][0]))
+            assert n == len(ref), "minDist %g: %d points, host %d" % (min_dist, n, len(ref))
+            got = dev.get_surface_points(0, n)
+            for f in ("p", "n", "u", "v", "area", "rayEpsilon"):
+                a, b = np.ascontiguousarray(got[f]).view(np.uint32), np.ascontiguousarray(ref[f]).view(np.uint32)
+                assert np.array_equal(a, b), "minDist %g incenter %d: field %s differs in %d entries" % (min_dist, incenter, f, int((a != b).sum()))
+            assert np.array_equal(got["materialId"], ref["materialId"])
+    finally:
+        hs.close()
