@@ -379,6 +379,53 @@ private:
     const MultipoleBSSRDF *bssrdf;
 };
 
+// The subsurface part of the camera pass alone, on the reference's own thread pool: the sample loop of
+// SamplerRendererTask::Run (renderers/samplerrenderer.cpp:60-167) with Li reduced to what
+// MultipoleSubsurfaceIntegrator::Li does for the subsurface term (multipolesubsurface.cpp:262-287): Scene::Intersect,
+// GetBSDF, GetMultipoleBSSRDF, octree->Mo, rho, clamp.  Every function called is the reference's; direct lighting and
+// film accumulation are left out so that the timed work equals the device path's camera pass.
+class SssOnlyTask : public Task {
+public:
+    SssOnlyTask(const Scene *sc, SamplerRenderer *r, Camera *c, Sampler *ms, Sample *sam, const MultipoleSubsurfaceIntegrator *in, int tn, int tc, double *sink)
+        : scene(sc), sr(r), camera(c), mainSampler(ms), origSample(sam), integ(in), taskNum(tn), taskCount(tc), sink(sink) {}
+    void Run() override {
+        Sampler *sampler = mainSampler->GetSubSampler(taskNum, taskCount);
+        if (!sampler) return;
+        MemoryArena arena; RNG rng(taskNum);
+        int maxSamples = sampler->MaximumSampleCount();
+        Sample *samples = origSample->Duplicate(maxSamples);
+        RayDifferential *rds = new RayDifferential[maxSamples];
+        int sampleCount; double acc = 0.;
+        while ((sampleCount = sampler->GetMoreSamples(samples, rng)) > 0) {
+            for (int i = 0; i < sampleCount; ++i) {
+                camera->GenerateRayDifferential(samples[i], &rds[i]);
+                rds[i].ScaleDifferentials(1.f / sqrtf(sampler->samplesPerPixel));
+                Intersection is;
+                if (scene->Intersect(rds[i], &is)) {
+                    Vector wo = -rds[i].d;
+                    BSDF *bsdf = is.GetBSDF(rds[i], arena);
+                    const Point &p = bsdf->dgShading.p; const Normal &n = bsdf->dgShading.nn;
+                    const MultipoleBSSRDF *bssrdf = is.GetMultipoleBSSRDF(rds[i], arena);
+                    if (bssrdf && integ->octree) {
+                        MultipoleReflectanceDrv mr(bssrdf);
+                        Spectrum Mo = integ->octree->Mo(integ->octreeBounds, p, n, mr, integ->maxError);
+                        float costheta = min(AbsDot(wo, n), 1.f);
+                        Spectrum Ft = Spectrum(1.f) - bssrdf->rho(costheta);
+                        Spectrum sss = ((INV_PI * Ft) * Mo * Pow(bssrdf->albedo(), 1.f - integ->mix)).Clamp(0.f);
+                        acc += sss.y();
+                    }
+                }
+                arena.FreeAll();
+            }
+        }
+        *sink = acc;      // keeps the work observable
+        delete sampler; delete[] samples; delete[] rds;
+    }
+private:
+    const Scene *scene; SamplerRenderer *sr; Camera *camera; Sampler *mainSampler; Sample *origSample;
+    const MultipoleSubsurfaceIntegrator *integ; int taskNum, taskCount; double *sink;
+};
+
 struct DrvRay { float o[3], d[3], mint, maxt; };                       // 32 B
 struct DrvHit { int32_t hit, prim; float t, rayEpsilon; float p[3], n[3], wo[3]; int32_t hasBssrdf; };  // 56 B
 
@@ -608,11 +655,12 @@ static int runMPC(int argc, char **argv) {
 static int runBench(int argc, char **argv) {
     if (argc < 3) { fprintf(stderr, "usage: ref_driver bench <scene.txt> [--ncores N] [--steps K] [--warmup W]\n"); return 2; }
     std::string scenePath = argv[2];
-    int ncores = 0, steps = 1, warmup = 0;
+    int ncores = 0, steps = 1, warmup = 0; bool sssOnly = false;
     for (int i = 3; i < argc; ++i) {
         if (!strcmp(argv[i], "--ncores")) ncores = atoi(argv[++i]);
         else if (!strcmp(argv[i], "--steps")) steps = atoi(argv[++i]);
         else if (!strcmp(argv[i], "--warmup")) warmup = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--sss-only")) sssOnly = true;
     }
     Options options; options.nCores = ncores; options.quiet = true;
     pbrtInit(options);
@@ -640,15 +688,20 @@ static int runBench(int argc, char **argv) {
         int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPixels / (16 * 16)));
         ProgressReporter reporter(nTasks, "Rendering");
         vector<Task *> tasks;
-        for (int i = 0; i < nTasks; ++i)
-            tasks.push_back(new SamplerRendererTask(scene, sr, camera, reporter, sr->sampler, sample, false, nTasks - 1 - i, nTasks));
+        std::vector<double> sinks(nTasks, 0.);
+        for (int i = 0; i < nTasks; ++i) {
+            if (sssOnly) tasks.push_back(new SssOnlyTask(scene, sr, camera, sr->sampler, sample, integ, nTasks - 1 - i, nTasks, &sinks[i]));
+            else tasks.push_back(new SamplerRendererTask(scene, sr, camera, reporter, sr->sampler, sample, false, nTasks - 1 - i, nTasks));
+        }
         EnqueueTasks(tasks); WaitForAllTasks();
         for (Task *t : tasks) delete t;
         reporter.Done();
         delete sample;
         double tRender = now_s() - t0;
         long nSamples = (long)nPixels * sr->sampler->samplesPerPixel;
-        printf("step %d points %zu samples %ld preprocess_s %.4f render_s %.4f\n", it - warmup, integ->irradiancePoints.size(), nSamples, tPre, tRender);
+        double chk = 0.; for (double v : sinks) chk += v;
+        printf("step %d points %zu samples %ld preprocess_s %.4f render_s %.4f %s checksum %.6g\n", it - warmup, integ->irradiancePoints.size(), nSamples, tPre, tRender,
+               sssOnly ? "sss_only" : "full_li", chk);
         fflush(stdout);
     }
     TasksCleanup();
