@@ -90,7 +90,8 @@ int skc_synchronize(skc_ctx *ctx);
 /* Counters of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t skc_launch_count(const skc_ctx *ctx);
 /* Device time of the last call of each stage in ms (CUDA events on the ctx stream).
- * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table, 8 tessellation */
+ * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table, 8 tessellation,
+ * 9 sampler stream + camera rays, 10 direct lighting, 11 spectral sum + film */
 float skc_stage_ms(const skc_ctx *ctx, int stage);
 
 /* CUDA-event timer on the context's stream spanning any sequence of calls (bench.py). */
@@ -216,6 +217,49 @@ int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, const uint32_t 
  * fixedFresnel != 0 selects FixedFresnelDielectric ("doublerefsslf").  hd30 receives [1025][30] floats
  * (RhoData::hd as Spectrum rows), the layout skc_upload_profile takes. */
 int skc_rho_table(skc_ctx *ctx, float roughness, float etaI, float etaT, int fixedFresnel, float *hd30);
+
+/* ---- whole frame on the device ------------------------------------------
+ * The rest of SamplerRenderer::Render (renderers/samplerrenderer.cpp:59-167,191-225) around the subsurface term:
+ *   LDSampler stream           samplers/lowdiscrepancy.cpp:58-79, core/montecarlo.cpp:200-252, core/montecarlo.h:183-331
+ *   PerspectiveCamera rays     cameras/perspective.cpp:79-113, core/camera.cpp:83-102
+ *   Li                         integrators/multipolesubsurface.cpp:253-304: Le + subsurface term + UniformSampleAllLights
+ *                              (core/integrator.cpp:47-175) with the LayeredSkin BSDF (materials/layeredskin.cpp:139-167:
+ *                              Microfacet + MicrofacetTransmission over Beckmann, core/reflection.cpp:228-296,391-470,548-581,
+ *                              675-780) and multiple importance sampling; emitter spheres carry the default matte
+ *   ImageFilm::AddSample       film/image.cpp:77-137 (filter table, XYZ accumulation)
+ * The frame description is what api.cpp / the plugin constructors derive from the scene file. */
+typedef struct {
+    int32_t xres, yres;            /* Film "image" resolution, full crop window */
+    int32_t spp;                   /* LDSampler pixelsamples, already a power of two (lowdiscrepancy.cpp:41-50) */
+    int32_t nTasks;                /* RoundUpPow2(max(32*cores, nPixels/256)), samplerrenderer.cpp:206-208 */
+    int32_t extra1D;               /* 1-sample 1-D arrays requested after the surface integrator's (EmissionIntegrator: 2) */
+    float cameraToWorld[16];       /* row-major Transform::m */
+    float rasterToCamera[16];
+    float filterXWidth, filterYWidth;
+    float filterTable[256];        /* ImageFilm::filterTable (16 x 16) */
+    float cieXYZ[3][SKC_NSPECTRAL];/* SampledSpectrum::X, Y, Z (core/spectrum.cpp Init) */
+    float xyzScale;                /* (sampledLambdaEnd - sampledLambdaStart) / (CIE_Y_integral * nSpectralSamples) */
+    float roughness, ior;          /* LayeredSkin: roughness, layers[0].ior */
+    float Kr[SKC_NSPECTRAL], Kt[SKC_NSPECTRAL];  /* LayeredSkin "color Kr" / "color Kt" as spectra; a black one drops its lobe */
+    float matteKd;                 /* MatteMaterial Kd of the emitter spheres (default 0.5) */
+} skc_frame_desc;
+/* Allocates the film and the sample stream for the frame; *nSamplesOut = samples of the whole sample extent
+ * (Film::GetSampleExtent, film/image.cpp:158-167) x spp, in SamplerRendererTask order (task nTasks-1 first). */
+int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *desc, uint64_t *nSamplesOut);
+/* Generates the LDSampler stream of every task (RNG(taskNum) regenerated per CTA) and the camera rays; they become
+ * the resident camera rays (as after skc_set_camera_rays). */
+int skc_frame_samples(skc_ctx *ctx);
+/* Test access: image positions [count][2], the 1-D/2-D arrays of each sample [count][floatsPerSample]
+ * (every 1-D array, then every 2-D array, as Sample::oneD / twoD) and the rays.  Any output may be NULL. */
+int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t count, float *xy, float *arrays, skc_ray *rays);
+uint32_t skc_frame_sample_floats(skc_ctx *ctx);
+/* Li for samples [first, first+count) and ImageFilm::AddSample of each into the device film.  L30 (optional, host)
+ * receives the per-sample radiance [count][30]. */
+int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix, float *L30);
+/* Film pixels [yres][xres]{Lxyz[3], weightSum}: clear, device pointer (for the reduce to rank 0), copy out. */
+int skc_frame_film_clear(skc_ctx *ctx);
+void *skc_frame_film_dev(skc_ctx *ctx);
+int skc_frame_film_get(skc_ctx *ctx, float *pixels4);
 
 #ifdef __cplusplus
 }

@@ -254,6 +254,10 @@ static void dumpSpectrumConsts(const std::string &dir) {
     for (int i = 0; i < nSpectralSamples; ++i) v.push_back(SampledSpectrum::Y.c[i]);
     for (int i = 0; i < nSpectralSamples; ++i) v.push_back(SampledSpectrum::Z.c[i]);
     dump(dir + "/cie_xyz30.bin", v.data(), v.size());
+    // Spectrum::FromRGB((1,1,1), SPECTRUM_REFLECTANCE): what "color Kr" [1 1 1] becomes (core/spectrum.cpp)
+    float one[3] = {1.f, 1.f, 1.f};
+    Spectrum w = Spectrum::FromRGB(one);
+    dump(dir + "/rgb_unit30.bin", w.c, nSpectralSamples);
 }
 
 static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
@@ -523,6 +527,7 @@ static int runScene(int argc, char **argv) {
         int nPixels = camera->film->xResolution * camera->film->yResolution;
         int nTasks = RoundUpPow2((uint32_t)max(32 * NumSystemCores(), nPixels / (16 * 16)));
         std::vector<DrvRay> rays; std::vector<DrvHit> hits; std::vector<float> imgxy, mo, Lout, Lsss;
+        std::vector<float> smp;   // per camera sample: every oneD array then every twoD array (Sample::oneD/twoD, core/sampler.h)
         for (int ti = 0; ti < nTasks; ++ti) {
             int taskNum = nTasks - 1 - ti;
             Sampler *sampler = sr->sampler->GetSubSampler(taskNum, nTasks);
@@ -541,6 +546,8 @@ static int runScene(int argc, char **argv) {
                     DrvRay dr = {{rds[i].o.x, rds[i].o.y, rds[i].o.z}, {rds[i].d.x, rds[i].d.y, rds[i].d.z}, rds[i].mint, rds[i].maxt};
                     rays.push_back(dr);
                     imgxy.push_back(samples[i].imageX); imgxy.push_back(samples[i].imageY);
+                    for (size_t j = 0; j < samples[i].n1D.size(); ++j) for (uint32_t k = 0; k < samples[i].n1D[j]; ++k) smp.push_back(samples[i].oneD[j][k]);
+                    for (size_t j = 0; j < samples[i].n2D.size(); ++j) for (uint32_t k = 0; k < 2 * samples[i].n2D[j]; ++k) smp.push_back(samples[i].twoD[j][k]);
                     DrvHit h; memset(&h, 0, sizeof h); h.prim = -1;
                     Spectrum Mo(0.f), sss(0.f);
                     {   // closest hit on a copy of the ray (Intersect shrinks maxt)
@@ -582,6 +589,9 @@ static int runScene(int argc, char **argv) {
         tRender = now_s() - t0;
         dump(dir + "/camera_rays.bin", rays.data(), rays.size());
         dump(dir + "/camera_xy.bin", imgxy.data(), imgxy.size());
+        dump(dir + "/camera_samples.bin", smp.data(), smp.size());
+        meta.kv("sample_arrays_1d", origSample->n1D.size()); meta.kv("sample_arrays_2d", origSample->n2D.size());
+        meta.kv("sample_floats", rays.empty() ? 0 : smp.size() / rays.size());
         dump(dir + "/hits.bin", hits.data(), hits.size());
         dump(dir + "/mo.bin", mo.data(), mo.size());
         dump(dir + "/L_sss.bin", Lsss.data(), Lsss.size());

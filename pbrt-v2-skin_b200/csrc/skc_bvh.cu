@@ -3,7 +3,7 @@
 // IntersectP :442-488), core/primitive.cpp:180-193, shapes/trianglemesh.inl:55-136,224-299.
 #include <vector>
 #include <string.h>
-#include "skc_bvh.cuh"
+#include "skc_light.cuh"
 #include "skc_internal.h"
 
 // ---- kernels --------------------------------------------------------------------------
@@ -19,15 +19,16 @@ __global__ void __launch_bounds__(128) k_trace_any(BvhView bv, const skc_ray *__
 }
 
 __device__ inline void triShading(const MeshView &mv, int prim, const DRay &ray, float t, float b1, float b2,
-                                  f3 *pOut, f3 *nOut) {
+                                  f3 *pOut, f3 *nOut, f3 *ngOut = nullptr, f3 *ssOut = nullptr) {
     int4 vi = __ldg(&mv.primInfo[prim]);
     float b0 = 1 - b1 - b2, tu, tv;
     *pOut = add3(ray.o, mul3(ray.d, t));
-    triShadingGeometry(mv, vi, b0, b1, b2, nOut, &tu, &tv);
+    triShadingGeometry(mv, vi, b0, b1, b2, nOut, &tu, &tv, ngOut, ssOut);
 }
 
 __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, const skc_ray *__restrict__ rays,
-                                                      uint64_t n, skc_hit *__restrict__ out, unsigned long long *cnt) {
+                                                      uint64_t n, skc_hit *__restrict__ out, unsigned long long *cnt,
+                                                      float4 *__restrict__ frame) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
@@ -45,8 +46,9 @@ __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, 
         h.wo[0] = -ray.d.x; h.wo[1] = -ray.d.y; h.wo[2] = -ray.d.z;
         int type = __ldg(&mv.primInfo[prim]).w;
         if (type == 0) {
-            f3 p, nn;
-            triShading(mv, prim, ray, t, b1, b2, &p, &nn);
+            f3 p, nn, ng, ss;
+            triShading(mv, prim, ray, t, b1, b2, &p, &nn, frame ? &ng : nullptr, frame ? &ss : nullptr);
+            if (frame) { frame[2 * i] = make_float4(ng.x, ng.y, ng.z, ss.x); frame[2 * i + 1] = make_float4(ss.y, ss.z, 0.f, 0.f); }
             h.p[0] = p.x; h.p[1] = p.y; h.p[2] = p.z; h.n[0] = nn.x; h.n[1] = nn.y; h.n[2] = nn.z;
             h.rayEpsilon = 1e-3f * t;        // trianglemesh.inl:134
             h.hasBssrdf = 1;
@@ -54,6 +56,16 @@ __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, 
             f3 p = add3(ray.o, mul3(ray.d, t));
             h.p[0] = p.x; h.p[1] = p.y; h.p[2] = p.z;
             h.rayEpsilon = 5e-4f * t;        // shapes/sphere.cpp:156
+            if (frame) {   // the emitter's dg (shapes/sphere.cpp:103-150): geometric = shading frame of its matte BSDF
+                const skc_light &sp = bv.spheres[__float_as_int(__ldg(&bv.prims[3 * prim + 2]).z)];
+                DRay r0; r0.o = ray.o; r0.d = ray.d; r0.mint = r1.z; r0.maxt = r1.w;
+                float ts; f3 nn, dpdu;
+                if (sphereIntersectDg(sp, r0, &ts, &nn, &dpdu)) {
+                    if (sp.reverseOrientation != 0.f) nn = mul3(nn, -1.f);
+                    h.n[0] = nn.x; h.n[1] = nn.y; h.n[2] = nn.z;
+                    frame[2 * i] = make_float4(nn.x, nn.y, nn.z, dpdu.x); frame[2 * i + 1] = make_float4(dpdu.y, dpdu.z, 0.f, 0.f);
+                }
+            }
         }
     }
     // 56 B record: write as 14 words
@@ -148,11 +160,11 @@ int skc_trace_any_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, uint8_t 
     return 0;
 }
 
-int skc_trace_closest_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, skc_hit *outDev, unsigned long long *cntDev) {
+int skc_trace_closest_dev(skc_ctx *ctx, const skc_ray *raysDev, uint64_t n, skc_hit *outDev, unsigned long long *cntDev, float4 *frameDev) {
     if (!ctx->bvhNodes) return skc_fail(ctx, "skc_trace_closest: no BVH uploaded");
     if (!n) return 0;
     uint64_t blocks = (n + 127) / 128;
-    k_trace_closest<<<(unsigned)blocks, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), raysDev, n, outDev, cntDev);
+    k_trace_closest<<<(unsigned)blocks, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), raysDev, n, outDev, cntDev, frameDev);
     SKC_LAUNCHED("k_trace_closest");
     return 0;
 }

@@ -137,7 +137,10 @@ __device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], 
 // geometry), core/diffgeom.cpp:40-55 (nn and the orientation flip).
 // Shading normal and uv at barycentric (b0, b1, b2) of the triangle with vertex ids vi.xyz: GetDifferentialGeometries
 // (shapes/trianglemesh.inl:303-345) + GetShadingGeometry (:224-299) + diffgeom.cpp:40-55
-__device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0, float b1, float b2, f3 *nOut, float *tuOut, float *tvOut) {
+// ngOut / ssOut (optional): the geometric normal dgGeom.nn and the shading dpdu that BSDF::BSDF turns into its local frame
+// (core/reflection.cpp:755-762)
+__device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0, float b1, float b2, f3 *nOut, float *tuOut, float *tvOut,
+                                          f3 *ngOut = nullptr, f3 *ssOut = nullptr) {
     f3 p1 = ld3(mv.P, vi.x), p2 = ld3(mv.P, vi.y), p3 = ld3(mv.P, vi.z);
     f3 e1 = sub3(p2, p1), e2 = sub3(p3, p1);
     float uvs[3][2];
@@ -164,8 +167,13 @@ __device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0,
     float tv = b0 * uvs[0][1] + b1 * uvs[1][1] + b2 * uvs[2][1];
     *tuOut = tu; *tvOut = tv;
     f3 nn;
+    if (ngOut) {
+        f3 ng = normalize3(cross3(dpdu, dpdv));
+        *ngOut = mv.flip ? mul3(ng, -1.f) : ng;
+    }
     if (!mv.N) {
         nn = normalize3(cross3(dpdu, dpdv));
+        if (ssOut) *ssOut = dpdu;
     } else {
         float A00 = uvs[1][0] - uvs[0][0], A01 = uvs[2][0] - uvs[0][0];
         float A10 = uvs[1][1] - uvs[0][1], A11 = uvs[2][1] - uvs[0][1];
@@ -192,6 +200,7 @@ __device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0,
             coordinateSystem(ns, &ss, &ts);
         }
         nn = normalize3(cross3(ss, ts));
+        if (ssOut) *ssOut = ss;
     }
     if (mv.flip) nn = mul3(nn, -1.f);
     *nOut = nn;

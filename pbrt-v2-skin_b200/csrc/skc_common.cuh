@@ -15,7 +15,7 @@
 
 #define SKC_NS SKC_NSPECTRAL
 #define SKC_EPAD 32            // spectral rows are padded to 32 floats = one 128 B line
-#define SKC_NSTAGES 9
+#define SKC_NSTAGES 12
 
 struct skc_ctx {
     int device = 0;
@@ -83,8 +83,11 @@ struct skc_ctx {
     uint64_t resRaysCount = 0;
 
     // --- scratch
-    void *scratch[12] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently)
-    size_t scratchBytes[12] = {0};
+    void *scratch[16] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently), 11 tessellation, 12-15 frame
+    size_t scratchBytes[16] = {0};
+
+    // --- whole-frame state (skc_frame.cu)
+    struct skc_frame_state *frame = nullptr;
 };
 
 // topology flags word: bits 0-7 child mask (interior) or point count (leaf),
@@ -97,6 +100,7 @@ int skc_check(skc_ctx *ctx, cudaError_t e, const char *what);
 void *skc_scratch(skc_ctx *ctx, int slot, size_t bytes);
 void skc_stage_begin(skc_ctx *ctx);
 void skc_stage_end(skc_ctx *ctx, int stage);
+void skc_frame_release(skc_ctx *ctx);             // frees ctx->frame (skc_frame.cu)
 cudaEvent_t skc_event(skc_ctx *ctx, size_t i);   // pooled cudaEventDisableTiming event, nullptr on failure
 
 #define SKC_CUDA(call) do { if (skc_check(ctx, (call), #call)) return 1; } while (0)

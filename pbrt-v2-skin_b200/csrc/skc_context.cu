@@ -80,7 +80,8 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->lights, ctx->ipPosArea, ctx->ipE,
                     ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);
-    for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    skc_frame_release(ctx);
+    for (int i = 0; i < 16; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     cudaStreamSynchronize(ctx->copyStream);

@@ -1,0 +1,205 @@
+// skc_light.cuh -- device helpers shared by the irradiance pass (skc_irradiance.cu) and the direct-lighting
+// pass (skc_frame.cu): MT19937 twist, (0,2)-sequence, sphere area-light sampling.
+// Reference: core/rng.cpp:84-110, core/montecarlo.h:278-301, lights/diffuse.cpp:69-85,
+// core/light.cpp:145-166, shapes/sphere.cpp:58-158,236-288, core/shape.cpp:96-109, core/light.h:87-92.
+#pragma once
+#include "skc_bvh.cuh"
+
+#define MT_N 624
+#define MT_M 397
+
+__device__ __forceinline__ uint32_t mtTwist(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+    return c ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+}
+
+// core/montecarlo.h:285-301
+__device__ __forceinline__ float vanDerCorput(uint32_t n, uint32_t scramble) {
+    n = __brev(n);
+    n ^= scramble;
+    return fminf(((n >> 8) & 0xffffff) / float(1 << 24), 0.99999994f /* OneMinusEpsilon */);
+}
+__device__ __forceinline__ float sobol2(uint32_t n, uint32_t scramble) {
+    for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+        if (n & 0x1) scramble ^= v;
+    return fminf(((scramble >> 8) & 0xffffff) / float(1 << 24), 0.99999994f);
+}
+
+__device__ inline void coordSys(f3 v1, f3 *v2, f3 *v3) {   // core/geometry.h:564-574
+    if (fabsf(v1.x) > fabsf(v1.y)) {
+        float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z);
+        *v2 = mk3(-v1.z * invLen, 0.f, v1.x * invLen);
+    } else {
+        float invLen = 1.f / sqrtf(v1.y * v1.y + v1.z * v1.z);
+        *v2 = mk3(0.f, v1.z * invLen, -v1.y * invLen);
+    }
+    *v3 = cross3(v1, *v2);
+}
+
+// glibc's sinf/cosf are correctly rounded in all but rare cases; rounding the fp64 result
+// reproduces them far more often than CUDA's 1-2 ulp fp32 versions do.
+__device__ __forceinline__ float cosf_cr(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float sinf_cr(float x) { return (float)sin((double)x); }
+
+// Sphere::Intersect's DifferentialGeometry normal (shapes/sphere.cpp:103-150 +
+// core/diffgeom.cpp:40-55), needed by ShapeSet::Sample (core/light.cpp:156).
+__device__ inline f3 sphereDgNormal(const skc_light &s, f3 phit /*object space, after phi fixups*/, float phi, f3 *dpduOut = nullptr) {
+    (void)phi;
+    float radius = s.radius;
+    float theta = acosf(fminf(fmaxf(phit.z / radius, -1.f), 1.f));
+    float zradius = sqrtf(phit.x * phit.x + phit.y * phit.y);
+    float invzradius = 1.f / zradius;
+    float cosphi = phit.x * invzradius, sinphi = phit.y * invzradius;
+    f3 dpdu = mk3(-s.phiMax * phit.y, s.phiMax * phit.x, 0.f);
+    float dth = s.thetaMax - s.thetaMin;
+    f3 dpdv = mul3(mk3(phit.z * cosphi, phit.z * sinphi, -radius * sinf(theta)), dth);
+    f3 wu = xformVector(s.o2w, dpdu), wv = xformVector(s.o2w, dpdv);
+    if (dpduOut) *dpduOut = wu;
+    return normalize3(cross3(wu, wv));   // orientation flip applied by the caller
+}
+
+// Sphere::Intersect restricted to what light sampling needs: thit and (optionally) dg.nn.
+static __device__ __noinline__ bool sphereIntersectDg(const skc_light &s, const DRay &r, float *tHit, f3 *nn, f3 *dpduOut = nullptr) {
+    DRay ray;
+    ray.o = xformPoint(s.w2o, r.o);
+    ray.d = xformVector(s.w2o, r.d);
+    ray.mint = r.mint; ray.maxt = r.maxt;
+    float radius = s.radius;
+    float A = ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z;
+    float B = 2 * (ray.d.x * ray.o.x + ray.d.y * ray.o.y + ray.d.z * ray.o.z);
+    float C = ray.o.x * ray.o.x + ray.o.y * ray.o.y + ray.o.z * ray.o.z - radius * radius;
+    float t0, t1;
+    if (!quadratic(A, B, C, &t0, &t1)) return false;
+    if (t0 > ray.maxt || t1 < ray.mint) return false;
+    float thit = t0;
+    if (t0 < ray.mint) { thit = t1; if (thit > ray.maxt) return false; }
+    f3 phit = add3(ray.o, mul3(ray.d, thit));
+    if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+    float phi = atan2f(phit.y, phit.x);
+    if (phi < 0.f) phi += 2.f * SKC_PI_F;
+    float zmin = s.zmin, zmax = s.zmax, phiMax = s.phiMax;
+    if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) {
+        if (thit == t1) return false;
+        if (t1 > ray.maxt) return false;
+        thit = t1;
+        phit = add3(ray.o, mul3(ray.d, thit));
+        if (phit.x == 0.f && phit.y == 0.f) phit.x = 1e-5f * radius;
+        phi = atan2f(phit.y, phit.x);
+        if (phi < 0.f) phi += 2.f * SKC_PI_F;
+        if ((zmin > -radius && phit.z < zmin) || (zmax < radius && phit.z > zmax) || phi > phiMax) return false;
+    }
+    *tHit = thit;
+    if (nn) *nn = sphereDgNormal(s, phit, phi, dpduOut);
+    return true;
+}
+
+// DiffuseAreaLight::Sample_L (lights/diffuse.cpp:69-81) for a one-sphere ShapeSet: wi, pdf and the
+// shadow segment; the return value says whether the returned radiance L(ps, ns, -wi) is Lemit (true)
+// or black (false).
+__device__ inline bool sampleSphereLightL(const skc_light &L, f3 p, float pEps, float u1, float u2,
+                                          f3 *wiOut, float *pdfOut, DRay *shadow) {
+    f3 Pcenter = xformPoint(L.o2w, mk3(0.f, 0.f, 0.f));
+    float radius = L.radius;
+    bool reverse = L.reverseOrientation != 0.f;
+    f3 pt, ns;
+    float dc2 = dist2(p, Pcenter);
+    bool inside = dc2 - radius * radius < 1e-4f;
+    if (inside) {
+        // Sphere::Sample(u1,u2,ns) (sphere.cpp:229-234): uniform over the sphere
+        float z = 1.f - 2.f * u1;
+        float rr = sqrtf(fmaxf(0.f, 1.f - z * z));
+        float phi = 2.f * SKC_PI_F * u2;
+        f3 po = mk3(radius * (rr * cosf_cr(phi)), radius * (rr * sinf_cr(phi)), radius * z);
+        ns = normalize3(xformNormal(L.w2o, po));
+        if (reverse) ns = mul3(ns, -1.f);
+        pt = xformPoint(L.o2w, po);
+    } else {
+        f3 wc = normalize3(sub3(Pcenter, p));
+        f3 wcX, wcY;
+        coordSys(wc, &wcX, &wcY);
+        float sinThetaMax2 = radius * radius / dc2;
+        float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+        // UniformSampleCone (core/montecarlo.cpp:413-420)
+        float costheta = (1.f - u1) * cosThetaMax + u1 * 1.f;
+        float sintheta = sqrtf(1.f - costheta * costheta);
+        float phi = u2 * 2.f * SKC_PI_F;
+        f3 dir = add3(add3(mul3(wcX, cosf_cr(phi) * sintheta), mul3(wcY, sinf_cr(phi) * sintheta)), mul3(wc, costheta));
+        DRay r; r.o = p; r.d = dir; r.mint = 1e-3f; r.maxt = INFINITY;
+        float thit;
+        if (!sphereIntersectDg(L, r, &thit, nullptr)) thit = dot3(sub3(Pcenter, p), normalize3(r.d));
+        pt = add3(r.o, mul3(r.d, thit));
+        ns = normalize3(sub3(pt, Pcenter));
+        if (reverse) ns = mul3(ns, -1.f);
+    }
+    // ShapeSet::Sample (core/light.cpp:145-158): re-intersect p -> pt with the shape set
+    DRay r2; r2.o = p; r2.d = sub3(pt, p); r2.mint = 1e-3f; r2.maxt = INFINITY;
+    float thit = 1.f, th; f3 nn;
+    if (sphereIntersectDg(L, r2, &th, &nn)) { thit = th; if (reverse) nn = mul3(nn, -1.f); ns = nn; }
+    f3 ps = add3(r2.o, mul3(r2.d, thit));
+    f3 wi = normalize3(sub3(ps, p));
+    // ShapeSet::Pdf (light.cpp:161-166) with one shape: area * pdf / sumArea
+    float area = L.phiMax * radius * (L.zmax - L.zmin);
+    float spdf;
+    if (inside) {
+        // Shape::Pdf(p, wi) (core/shape.cpp): intersect and convert the area measure
+        DRay r3; r3.o = p; r3.d = wi; r3.mint = 1e-3f; r3.maxt = INFINITY;
+        float t3; f3 n3;
+        if (!sphereIntersectDg(L, r3, &t3, &n3)) spdf = 0.f;
+        else {
+            f3 ph = add3(r3.o, mul3(r3.d, t3));
+            spdf = dist2(p, ph) / (fabsf(dot3(n3, mul3(wi, -1.f))) * area);
+            if (isinf(spdf)) spdf = 0.f;
+        }
+    } else {
+        float sinThetaMax2 = radius * radius / dc2;
+        float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+        spdf = 1.f / (2.f * SKC_PI_F * (1.f - cosThetaMax));   // UniformConePdf (core/montecarlo.cpp:400-402)
+    }
+    float pdf = 0.f + area * spdf;
+    pdf = pdf / area;
+    // VisibilityTester::SetSegment (core/light.h:87-92)
+    float dist = len3(sub3(p, ps));
+    float invd = 1.f / dist;
+    shadow->o = p; shadow->d = mul3(sub3(ps, p), invd); shadow->mint = pEps; shadow->maxt = dist * (1.f - 1e-3f);
+    // L(ps, ns, -wi): lights/diffuse.h:51-53
+    bool lit = dot3(ns, mul3(wi, -1.f)) > 0.f;
+    *wiOut = wi; *pdfOut = pdf;
+    return lit;
+}
+
+// The irradiance loop's use of Sample_L (multipolesubsurface.cpp:119-126): false when the sample
+// contributes nothing before the shadow test.
+__device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f3 spn, float u1, float u2,
+                                         f3 *wiOut, float *pdfOut, DRay *shadow) {
+    bool lit = sampleSphereLightL(L, p, pEps, u1, u2, wiOut, pdfOut, shadow);
+    if (dot3(*wiOut, spn) <= 0.f) return false;
+    if (!lit || *pdfOut == 0.f) return false;
+    return true;
+}
+
+// DiffuseAreaLight::Pdf(p, wi) -> ShapeSet::Pdf -> Sphere::Pdf (lights/diffuse.cpp:84-86, core/light.cpp:161-166,
+// shapes/sphere.cpp:276-288, core/shape.cpp:96-109)
+__device__ inline float sphereLightPdf(const skc_light &L, f3 p, f3 wi) {
+    f3 Pcenter = xformPoint(L.o2w, mk3(0.f, 0.f, 0.f));
+    float radius = L.radius;
+    float area = L.phiMax * radius * (L.zmax - L.zmin);
+    float dc2 = dist2(p, Pcenter);
+    float spdf;
+    if (dc2 - radius * radius < 1e-4f) {
+        DRay r3; r3.o = p; r3.d = wi; r3.mint = 1e-3f; r3.maxt = INFINITY;
+        float t3; f3 n3;
+        if (!sphereIntersectDg(L, r3, &t3, &n3)) spdf = 0.f;
+        else {
+            f3 ph = add3(r3.o, mul3(r3.d, t3));
+            spdf = dist2(p, ph) / (fabsf(dot3(n3, mul3(wi, -1.f))) * area);
+            if (isinf(spdf)) spdf = 0.f;
+        }
+    } else {
+        float sinThetaMax2 = radius * radius / dc2;
+        float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+        spdf = 1.f / (2.f * SKC_PI_F * (1.f - cosThetaMax));
+    }
+    float pdf = 0.f + area * spdf;
+    return pdf / area;
+}
+

@@ -496,6 +496,16 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
     return 0;
 }
 
+int skc_li_fused_dev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, float *dL) {
+    if (!ctx->rhoHd) return skc_fail(ctx, "skc_li: no rho table uploaded (skc_upload_profile)");
+    if (!ctx->moPacket) return skc_fail(ctx, "skc_li: the fused Li epilogue needs the packet kernel");
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL};
+    skc_stage_begin(ctx);
+    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep)) return 1;
+    skc_stage_end(ctx, 4);
+    return 0;
+}
+
 extern "C" int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float maxError, float mix,
                           const float *albedo30, float *Mo30, float *L30) {
     if (!ctx) return 1;

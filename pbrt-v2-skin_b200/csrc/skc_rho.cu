@@ -14,6 +14,7 @@
 // compensated fp32 sum approximates.  R = 1 and the Fresnel term is wavelength independent, so all 30
 // spectral channels of an entry are equal.
 #include "skc_internal.h"
+#include "skc_bsdf.cuh"
 
 #define MT_N 624
 #define MT_M 397
@@ -30,35 +31,6 @@ __device__ __forceinline__ float rhoRandomFloat(uint32_t y) {   // tempering + R
     y ^= (y << 15) & 0xefc60000u;
     y ^= (y >> 18);
     return (float)(y & 0xffffffu) / 16777216.f;
-}
-
-struct RhoBxdf { float rms2, rcpRMS2, etaI, etaT; int fixedFresnel; };
-
-__device__ __forceinline__ float beckmannD(const RhoBxdf &b, float whz) {
-    float costheta = fabsf(whz);
-    float c2 = costheta * costheta;
-    float d = c2 * c2 * SKC_PI_F;
-    if (d == 0.f) return 0.f;
-    float e = (c2 - 1) * b.rcpRMS2 / c2;
-    return b.rcpRMS2 * expf(e) / d;
-}
-
-__device__ __forceinline__ float fresnelDielectric(const RhoBxdf &b, float cosi) {
-    cosi = fminf(fmaxf(cosi, -1.f), 1.f);
-    bool entering = cosi > 0.;
-    float ei = entering ? b.etaI : b.etaT, et = entering ? b.etaT : b.etaI;
-    float sint = ei / et * sqrtf(fmaxf(0.f, 1.f - cosi * cosi));
-    float F;
-    if (sint >= 1.) F = 1.f;
-    else {
-        float cost = sqrtf(fmaxf(0.f, 1.f - sint * sint));
-        float ci = fabsf(cosi);
-        float Rparl = ((et * ci) - (ei * cost)) / ((et * ci) + (ei * cost));
-        float Rperp = ((ei * ci) - (et * cost)) / ((ei * ci) + (et * cost));
-        F = (Rparl * Rparl + Rperp * Rperp) / 2.f;
-    }
-    if (b.fixedFresnel) F = F + F * (1.f - F) * (1.f - F);
-    return F;
 }
 
 // one term f * |cos(wi)| / pdf of BxDF::rho(wo, ...) for the Beckmann microfacet lobe, or 0

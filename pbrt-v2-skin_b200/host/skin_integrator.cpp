@@ -2,6 +2,8 @@
 // Python tests/bench bind (skh_*).  Mirrors integrators/multipolesubsurface.cpp:170-304.
 #include "skin_scene.h"
 #include "skin_material.h"
+#include "skin_cie.h"
+#include "skin_tables.h"
 #include <cstdio>
 #include <cstring>
 
@@ -180,6 +182,60 @@ int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *
         }
         return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd);
     }
+    return 0;
+}
+
+// ---- whole frame --------------------------------------------------------------------------------
+// What api.cpp's MakeCamera / MakeFilm / MakeSampler / MakeRenderer derive from the scene file for the device frame
+// pass: perspective camera matrices (api.cpp:862, cameras/perspective.cpp:124-155), Film "image" with the default
+// box filter of half-width 0.5 (film/image.cpp:55-66, filters/box.cpp), LDSampler pixelsamples rounded up to a power
+// of two (lowdiscrepancy.cpp:41-50), the render task count (samplerrenderer.cpp:206-208), EmissionIntegrator's two
+// 1-sample arrays (integrators/emission.cpp:42-45), the XYZ matching tables.
+void skh_frame_desc(const skh_scene *s, int nCores, skc_frame_desc *d) {
+    memset(d, 0, sizeof *d);
+    const SceneDesc &sd = s->sd;
+    d->xres = sd.xres; d->yres = sd.yres;
+    d->spp = (int)RoundUpPow2((uint32_t)std::max(1, sd.spp));
+    int nPixels = sd.xres * sd.yres;
+    d->nTasks = (int)RoundUpPow2((uint32_t)std::max(32 * nCores, nPixels / (16 * 16)));
+    d->extra1D = 2;
+    const float *la = sd.lookat;
+    Transform w2c = Transform() * LookAt(V3(la[0], la[1], la[2]), V3(la[3], la[4], la[5]), V3(la[6], la[7], la[8]));
+    PerspectiveCamera cam(InverseT(w2c), sd.fov, sd.xres, sd.yres);
+    memcpy(d->cameraToWorld, cam.CameraToWorld.m.m, 64);
+    memcpy(d->rasterToCamera, cam.RasterToCamera.m.m, 64);
+    d->filterXWidth = d->filterYWidth = 0.5f;
+    for (int i = 0; i < 256; ++i) d->filterTable[i] = 1.f;                   // BoxFilter::Evaluate
+    for (int k = 0; k < 3; ++k) memcpy(d->cieXYZ[k], kCieXYZ30[k], sizeof(float) * 30);
+    d->xyzScale = float(700 - 400) / float(kCieYIntegral * 30);               // core/spectrum.h:381-382
+    d->roughness = sd.skin.roughness; d->ior = sd.skin.layerIor[0];
+    // "color Kr" / "color Kt": Spectrum::FromRGB, grey values only on this path
+    for (int i = 0; i < 30; ++i) { d->Kr[i] = sd.skin.Kr[0] * kUnitRGBToSpectrum30[i]; d->Kt[i] = sd.skin.Kt[0] * kUnitRGBToSpectrum30[i]; }
+    d->matteKd = 0.5f;                                                        // materials/matte.cpp: Kd default
+}
+// ImageFilm::WriteImage (film/image.cpp:178-213): XYZ -> RGB, divide by the weight sum, clamp at 0.  rgb = [h][w][3].
+void skh_film_to_rgb(const float *pixels4, int w, int h, float *rgb) {
+    for (int i = 0; i < w * h; ++i) {
+        const float *xyz = pixels4 + 4 * i;
+        float *o = rgb + 3 * i;
+        o[0] = 3.240479f * xyz[0] - 1.537150f * xyz[1] - 0.498535f * xyz[2];      // XYZToRGB (core/spectrum.h:51-55)
+        o[1] = -0.969256f * xyz[0] + 1.875991f * xyz[1] + 0.041556f * xyz[2];
+        o[2] = 0.055648f * xyz[0] - 0.204043f * xyz[1] + 1.057311f * xyz[2];
+        float weightSum = xyz[3];
+        if (weightSum != 0.f) {
+            float invWt = 1.f / weightSum;
+            o[0] = std::max(0.f, o[0] * invWt); o[1] = std::max(0.f, o[1] * invWt); o[2] = std::max(0.f, o[2] * invWt);
+        }
+    }
+}
+// Portable float map, little endian, bottom row first (core/imageio.cpp WriteImagePFM)
+int skh_write_pfm(const char *path, const float *rgb, int w, int h) {
+    FILE *fp = fopen(path, "wb");
+    if (!fp) return 1;
+    fprintf(fp, "PF\n%d %d\n-1.000000\n", w, h);
+    for (int y = h - 1; y >= 0; --y)
+        if (fwrite(rgb + (size_t)3 * w * y, sizeof(float), (size_t)3 * w, fp) != (size_t)3 * w) { fclose(fp); return 1; }
+    fclose(fp);
     return 0;
 }
 

@@ -188,6 +188,8 @@ bool SceneDesc::Load(const std::string &path) {
             std::string k;
             while (ls >> k) {
                 if (k == "layers") ls >> skin.layerThickness[0] >> skin.layerIor[0] >> skin.layerThickness[1] >> skin.layerIor[1];
+                else if (k == "Kr") ls >> skin.Kr[0] >> skin.Kr[1] >> skin.Kr[2];
+                else if (k == "Kt") ls >> skin.Kt[0] >> skin.Kt[1] >> skin.Kt[2];
                 else {
                     float v; ls >> v;
                     if (k == "roughness") skin.roughness = v; else if (k == "nmperunit") skin.nmperunit = v;

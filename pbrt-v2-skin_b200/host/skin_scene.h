@@ -45,6 +45,9 @@ struct SkinParams {
     float roughness = 0.3f, nmperunit = 100e6f;
     float f_mel = 0.15f, f_eu = 1.f, f_blood = 0.002f, f_ohg = 0.3f;
     int desiredlength = 512;
+    // "color Kr" / "color Kt" as the skin scenes give them (results/PigmentManips/Eum0.1_Deoxy0.5.pbrt:37-38); the scene-file
+    // format issues these two like the reference driver does.  (The material's own defaults are Spectrum(1) for both.)
+    float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};
     bool lerponthinslab = true;
     float layerThickness[2] = {0.25e6f, 20e6f}, layerIor[2] = {1.4f, 1.4f};
 };

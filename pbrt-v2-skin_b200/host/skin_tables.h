@@ -12,6 +12,18 @@ static const float kGreyRGBToSpectrum30[30] = {
     0.998574495f, 0.99752152f, 0.996186376f, 0.996272445f, 0.996561229f
 };
 
+// Spectrum::FromRGB((1,1,1), SPECTRUM_REFLECTANCE) (core/spectrum.cpp): what "color Kr" [1 1 1] becomes.  Exported
+// from the reference build (rgb_unit30 in tests/golden/skin_ld4.npz).  A grey value v converts to (v * white) * .94,
+// which equals v * k[i] up to one rounding.
+static const float kUnitRGBToSpectrum30[30] = {
+    0.997982085f, 0.998490036f, 0.998524427f, 0.99871248f, 0.998672247f,
+    0.998708844f, 0.998744309f, 0.998709857f, 0.99849236f, 0.998001933f,
+    0.997532845f, 0.997481167f, 0.997701705f, 0.997843564f, 0.998324633f,
+    0.998719871f, 0.998711884f, 0.998748541f, 0.998712003f, 0.998708963f,
+    0.998764694f, 0.998792112f, 0.998735189f, 0.998644888f, 0.998655975f,
+    0.998574495f, 0.99752152f, 0.996186376f, 0.996272445f, 0.99656117f
+};
+
 // Molar extinction of oxy-/deoxy-haemoglobin [cm^-1/(mol/L)] at 400..700 nm in 5 nm steps (61 samples;
 // Prahl's compilation, as tabulated by the reference in materials/skincoeffs.cpp:35-73).  Data, not code.
 static const int kPigmentSamples = 61;

@@ -35,6 +35,9 @@ def load_host_library():
     lib.skh_skin_coefficients.restype = None; lib.skh_skin_coefficients.argtypes = [vp, vp]
     lib.skh_skin_spectra.restype = None; lib.skh_skin_spectra.argtypes = [vp, vp]
     lib.skh_build_profile.restype = C.c_int; lib.skh_build_profile.argtypes = [vp, vp, vp, C.POINTER(C.c_uint32), vp, vp, C.c_int]
+    lib.skh_frame_desc.restype = None; lib.skh_frame_desc.argtypes = [vp, C.c_int, vp]
+    lib.skh_film_to_rgb.restype = None; lib.skh_film_to_rgb.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.skh_write_pfm.restype = C.c_int; lib.skh_write_pfm.argtypes = [C.c_char_p, vp, C.c_int, C.c_int]
     _lib = lib
     return lib
 
@@ -115,6 +118,27 @@ class HostScene:
     def upload(self, dev):
         dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
         dev.upload_lights(self.lights)
+
+    FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1)
+
+    def frame_desc(self, n_cores=1):
+        """skc_frame_desc for this scene: camera, film + box filter, LDSampler, render task count (bytes)."""
+        buf = np.zeros(self.FRAME_DESC_BYTES, np.uint8)
+        self.lib.skh_frame_desc(self.h, int(n_cores), buf.ctypes.data_as(C.c_void_p))
+        return buf
+
+    def film_to_rgb(self, pixels4):
+        """ImageFilm::WriteImage's pixel arithmetic: [h][w]{Lxyz, weightSum} -> RGB [h][w][3]."""
+        px = np.ascontiguousarray(pixels4, np.float32)
+        h, w = px.shape[:2]
+        rgb = np.empty((h, w, 3), np.float32)
+        self.lib.skh_film_to_rgb(px.ctypes.data_as(C.c_void_p), w, h, rgb.ctypes.data_as(C.c_void_p))
+        return rgb
+
+    def write_pfm(self, path, rgb):
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        if self.lib.skh_write_pfm(path.encode(), rgb.ctypes.data_as(C.c_void_p), rgb.shape[1], rgb.shape[0]):
+            raise SkcError("cannot write %s" % path)
 
     def skin_coefficients(self):
         """LayeredSkin layer coefficients (materials/layeredskin.cpp:49-92): dict of mua/musp [2][30], eta[2], thickness[2]."""

@@ -30,7 +30,9 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
-           "skc_tessellate_resident", "skc_get_surface_points"]
+           "skc_tessellate_resident", "skc_get_surface_points",
+           "skc_frame_setup", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
+           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get"]
 
 
 class SkcError(RuntimeError):
@@ -93,6 +95,14 @@ def load_library():
     lib.skc_timer_begin.restype = i32; lib.skc_timer_begin.argtypes = [vp]
     lib.skc_timer_end_ms.restype = f32; lib.skc_timer_end_ms.argtypes = [vp]
     lib.skc_set_point_count.restype = i32; lib.skc_set_point_count.argtypes = [vp, u64]
+    lib.skc_frame_setup.restype = i32; lib.skc_frame_setup.argtypes = [vp, vp, C.POINTER(u64)]
+    lib.skc_frame_samples.restype = i32; lib.skc_frame_samples.argtypes = [vp]
+    lib.skc_frame_get_samples.restype = i32; lib.skc_frame_get_samples.argtypes = [vp, u64, u64, vp, vp, vp]
+    lib.skc_frame_sample_floats.restype = u32; lib.skc_frame_sample_floats.argtypes = [vp]
+    lib.skc_frame_render.restype = i32; lib.skc_frame_render.argtypes = [vp, u64, u64, f32, f32, vp]
+    lib.skc_frame_film_clear.restype = i32; lib.skc_frame_film_clear.argtypes = [vp]
+    lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
+    lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
     _lib = lib
     return lib
 
@@ -279,6 +289,41 @@ class SkinDevice:
         c = np.zeros(7, np.uint64) if counters else None
         self._ck(self.lib.skc_camera_pass_resident(self.ctx, first, count, max_error, mix, _ptr(out), _ptr(c)))
         return c
+
+    # --- whole frame (SamplerRenderer::Render around the subsurface term)
+    def frame_setup(self, desc):
+        """desc: bytes of a skc_frame_desc (HostScene.frame_desc).  Returns the number of camera samples."""
+        self._frame_desc = np.frombuffer(bytes(desc), np.uint8).copy()
+        n = C.c_uint64(0)
+        self._ck(self.lib.skc_frame_setup(self.ctx, _ptr(self._frame_desc), C.byref(n)))
+        self._frame_res = tuple(int(v) for v in self._frame_desc[:8].view(np.int32))
+        return int(n.value)
+
+    def frame_samples(self):
+        self._ck(self.lib.skc_frame_samples(self.ctx))
+
+    def frame_get_samples(self, first, count):
+        fl = int(self.lib.skc_frame_sample_floats(self.ctx))
+        xy = np.empty((count, 2), np.float32); arr = np.empty((count, fl), np.float32); rays = np.empty((count, 8), np.float32)
+        self._ck(self.lib.skc_frame_get_samples(self.ctx, first, count, _ptr(xy), _ptr(arr), _ptr(rays)))
+        return xy, arr, rays
+
+    def frame_render(self, first, count, max_error, mix=0.5, want_L=False):
+        L = np.empty((count, 30), np.float32) if want_L else None
+        self._ck(self.lib.skc_frame_render(self.ctx, first, count, max_error, mix, _ptr(L)))
+        return L
+
+    def frame_film_clear(self):
+        self._ck(self.lib.skc_frame_film_clear(self.ctx))
+
+    def frame_film_dev(self):
+        return self.lib.skc_frame_film_dev(self.ctx)
+
+    def frame_film(self):
+        xres, yres = self._frame_res
+        px = np.empty((yres, xres, 4), np.float32)
+        self._ck(self.lib.skc_frame_film_get(self.ctx, _ptr(px)))
+        return px
 
     def pinned(self, shape, dtype):
         """numpy array over cudaHostAlloc'ed memory (freed with the device object)."""

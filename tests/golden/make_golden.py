@@ -9,6 +9,8 @@ and packs the exported streams into compressed .npz files:
   skin_tiny.npz   scenes/skin_tiny.scene: flat BVH + meshes + lights, profile/rho tables,
                   surface points, irradiance points, octree bounds/root, camera rays,
                   closest hits, per-hit Mo, per-hit subsurface radiance, per-sample radiance
+  skin_ld4.npz    scenes/skin_ld4.scene (48x27 film, 4 spp): the LDSampler stream, full Li per sample,
+                  the film's image (row N1: the rest of Li, sampler and film on the device)
   mpc_kat.npz     MPC_ComputeDiffusionProfile on the parameter sets of the reference's
                   src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
 
@@ -70,6 +72,39 @@ def scene_golden(name):
     print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "bvh_nodes")})
 
 
+def read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = map(int, f.readline().split())
+        scale = float(f.readline())
+        data = np.frombuffer(f.read(), "<f4" if scale < 0 else ">f4").reshape(h, w, 3)
+    return data[::-1].astype(np.float32)     # PFM stores the bottom row first
+
+
+def frame_golden(name):
+    """Whole-frame fixture (row N1): the LDSampler stream (image position + every 1D/2D integrator
+    sample of each camera sample, in task order), full Li per sample and the film's output image."""
+    scene = os.path.join(ROOT, "scenes", name + ".scene")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        meta = read_meta(os.path.join(d, "meta.txt"))
+        f32 = lambda fn: np.fromfile(os.path.join(d, fn), np.float32)
+        arrays = dict(
+            meta_keys=np.array(list(meta.keys())), meta_vals=np.array([float(v) for v in meta.values()]),
+            camera_xy=f32("camera_xy.bin").reshape(-1, 2),
+            camera_samples=f32("camera_samples.bin").reshape(-1, meta["sample_floats"]),
+            camera_rays=f32("camera_rays.bin").reshape(-1, 8),
+            hits=np.fromfile(os.path.join(d, "hits.bin"), np.uint8),
+            L_sss=f32("L_sss.bin").reshape(-1, 30), L=f32("L.bin").reshape(-1, 30),
+            image=read_pfm(os.path.join(d, "image.pfm")),
+            rgb_unit30=f32("rgb_unit30.bin"),
+        )
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("camera_samples", "camera_tasks", "sample_floats")})
+
+
 # (nLayers, desiredLength, lerpOnThinSlab, resample, stepSize, [(ior, thickness, mua, musp)...])
 # First three: src/multipole/test/test.cpp:84-116 at desiredLength 512 -> here 64/128 to keep
 # the fixture small; the full-size known answers are checked in the GPU-marked tests against
@@ -110,8 +145,8 @@ def mpc_golden():
 
 
 if __name__ == "__main__":
-    what = sys.argv[1:] or ["skin_tiny", "mpc_kat"]
+    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "mpc_kat"]
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else scene_golden(w)

@@ -1,0 +1,111 @@
+"""GPU parity tests of the whole-frame path: LDSampler stream, camera rays, full Li
+(emission + subsurface term + direct lighting with the LayeredSkin BSDF and MIS) and the film, against the real
+reference's export of scenes/skin_ld4.scene (tests/golden/skin_ld4.npz, made by tests/golden/make_golden.py from
+oracle/_ref/ref_driver at --ncores 1).
+
+Tolerances: the sampler stream and the camera rays are integer / exactly-rounded work -> bit-exact.  Li per sample:
+1e-4 relative to the row's scale for the bulk of the samples; a small fraction may differ more, because one shadow or
+BSDF ray whose direction differs in the last ulp (libm vs CUDA transcendental functions) can flip visibility at a
+silhouette, which changes one of the 16 direct-lighting terms of that sample.  Image: RMSE 1e-3 relative per channel
+(BASELINE.json).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ld4():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "skin_ld4.npz"))
+    meta = dict(zip([str(k) for k in z["meta_keys"]], z["meta_vals"]))
+    return z, meta
+
+
+@pytest.fixture(scope="module")
+def frame(pkg, dev, ld4):
+    """Scene loaded by the host mirror, material tables + Preprocess + sampler stream on the device."""
+    z, meta = ld4
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_ld4.scene"))
+    hs.upload(dev)
+    hs.build_profile(dev)
+    n_pts = dev.tessellate_resident(hs.minsampledistance, False, material_id=0)
+    dev.irradiance_resident(0, n_pts, hs.irradiance_tasks(n_pts, 1), hs.mix)
+    dev.build_octree()
+    n = dev.frame_setup(hs.frame_desc(n_cores=1))
+    dev.frame_samples()
+    yield hs, n
+    hs.close()
+
+
+def test_sampler_stream_and_camera_rays_bit_exact(dev, frame, ld4):
+    z, meta = ld4
+    hs, n = frame
+    assert n == int(meta["camera_samples"]) == len(z["camera_xy"])
+    xy, arrays, rays = dev.frame_get_samples(0, n)
+    assert np.array_equal(xy.view(np.uint32), z["camera_xy"].view(np.uint32)), "image positions differ"
+    assert arrays.shape == z["camera_samples"].shape
+    bad = (arrays.view(np.uint32) != z["camera_samples"].view(np.uint32))
+    assert not bad.any(), "%d of %d integrator sample values differ (first column %d)" % (bad.sum(), bad.size, np.argmax(bad.any(axis=0)))
+    assert np.array_equal(rays[:, :6].view(np.uint32), z["camera_rays"][:, :6].view(np.uint32)), "camera rays differ"
+
+
+def test_frame_radiance_vs_reference(dev, frame, ld4):
+    z, meta = ld4
+    hs, n = frame
+    dev.frame_film_clear()
+    L = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+    ref = z["L"]
+    e = gu.row_rel_err(L, ref)
+    lit = ref.max(axis=1) > 0
+    assert np.array_equal(L.max(axis=1) > 0, lit), "different sets of samples carry radiance"
+    f4, f3 = np.mean(e[lit] < 1e-4), np.mean(e[lit] < 1e-2)
+    print("full Li: %d lit samples, within 1e-4: %.4f, within 1e-2: %.4f, max %.3g" % (lit.sum(), f4, f3, e.max()))
+    assert f4 > 0.97 and f3 > 0.995
+    # direct lighting alone (L - subsurface term), where it is not negligible
+    d_ref = ref - z["L_sss"]
+    d_got = L - z["L_sss"]
+    scale = np.abs(d_ref).max(axis=1)
+    m = scale > 1e-3 * np.abs(ref).max(axis=1)
+    ed = np.abs(d_got - d_ref).max(axis=1)[m] / scale[m]
+    print("direct term: %d samples, median rel %.3g, within 1e-3: %.4f" % (m.sum(), np.median(ed), np.mean(ed < 1e-3)))
+    assert np.mean(ed < 1e-3) > 0.97
+
+
+def test_frame_image_vs_reference(dev, frame, ld4):
+    z, meta = ld4
+    hs, n = frame
+    dev.frame_film_clear()
+    half = n // 2                      # two calls: the film accumulates across ranges (tile sharding)
+    dev.frame_render(0, half, hs.maxerror, hs.mix)
+    dev.frame_render(half, n - half, hs.maxerror, hs.mix)
+    px = dev.frame_film()
+    assert px.shape == (hs.yres, hs.xres, 4)
+    assert np.all(px[..., 3] == hs.spp), "every pixel receives pixelsamples box-filter weights"
+    rgb = hs.film_to_rgb(px)
+    ref = z["image"]
+    assert rgb.shape == ref.shape
+    for c in range(3):
+        rmse = np.sqrt(np.mean((rgb[..., c] - ref[..., c]) ** 2))
+        scale = np.sqrt(np.mean(ref[..., c] ** 2))
+        print("channel %d: RMSE %.3g of RMS %.3g = %.3g" % (c, rmse, scale, rmse / scale))
+        assert rmse < 1e-3 * scale
+
+
+def test_frame_pfm_round_trip(dev, frame, tmp_path):
+    hs, n = frame
+    rgb = hs.film_to_rgb(dev.frame_film())
+    path = str(tmp_path / "frame.pfm")
+    hs.write_pfm(path, rgb)
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = map(int, f.readline().split())
+        assert float(f.readline()) < 0
+        data = np.frombuffer(f.read(), "<f4").reshape(h, w, 3)[::-1]
+    assert (w, h) == (hs.xres, hs.yres) and np.array_equal(data, rgb)
