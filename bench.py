@@ -1,20 +1,24 @@
 #!/usr/bin/env python3
 """bench.py -- the subsurface hot path of pbrt-v2-skin on B200 (contract: see DESIGN.md section 6).
 
-One "step" = one pass of the hot path over the reconstructed skin.scene (BASELINE.json configs[1]):
+One "step" = one FRAME of the reconstructed skin.scene (BASELINE.json configs[1]), i.e. SamplerRenderer::Render
+without the material construction:
     MultipoleSubsurfaceIntegrator::Preprocess  (surface points by tessellation of the mesh; irradiance pass
         over every point: light sampling + shadow rays through the BVH; octree build + InitHierarchy)
-  + the subsurface part of the camera pass     (closest hit per camera sample, octree Mo, Li SSS term)
+  + the camera pass                            (LDSampler stream, camera rays, closest hit, octree Mo + the Li
+        subsurface term, emission, direct lighting with the LayeredSkin BSDF and MIS, film accumulation)
 metric  = shading points per second = (irradiance points + camera samples) / step time
-value   = scene (mesh, BVH, lights, material tables) and camera rays resident in HBM before the timed region
-e2e     = the same with the camera rays coming from pinned host memory and the per-sample radiance written
-          back to pinned host memory every step (skc_camera_pass); the scene stays resident, as it does in
-          the reference, and the surface points are generated on the device
-N > 1   = points sharded over ranks, in-place NCCL all-gather of the irradiance set, replicated
-          octree build, camera samples sharded (strong scaling: the scene is fixed).
+value   = scene (mesh, BVH, lights, material tables) resident in HBM before the timed region
+e2e     = the same from HOST buffers: the scene (BVH nodes, primitives, mesh, lights) is uploaded from host memory
+          every step, the film comes back to the host and is converted to RGB there (ImageFilm::WriteImage's
+          arithmetic) -- what `pbrt scene.pbrt` does per frame after parsing
+N > 1   = points sharded over ranks, in-place NCCL all-gather of the irradiance set, replicated octree build,
+          render tasks (tiles) dealt round-robin over the ranks, film reduced (sum) to rank 0 over NCCL
+          (strong scaling: the scene is fixed).
 
-`--impl reference` times the reference's own CPU code (oracle/_ref/ref_driver bench) on a bounded
-sample of the same scene (1/16 of the points and of the film), all host threads.
+`--impl reference` times the reference's own CPU code (oracle/_ref/ref_driver bench: Preprocess + its
+SamplerRendererTask loop with the full Li) on a bounded sample of the same scene (1/16 of the points and of the
+film), all host threads.
 """
 import argparse
 import json
@@ -103,14 +107,14 @@ def reference_arm(args):
         return
     sample = os.path.join(ROOT, "scenes", "skin_sample16.scene")
     cores = os.cpu_count() or 1
-    out = subprocess.run([drv, "bench", sample, "--ncores", str(cores), "--steps", str(args.steps), "--warmup", str(args.warmup), "--sss-only"],
+    out = subprocess.run([drv, "bench", sample, "--ncores", str(cores), "--steps", str(args.steps), "--warmup", str(args.warmup)],
                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, check=True).stdout
     steps = [l.split() for l in out.splitlines() if l.startswith("step ") and int(l.split()[1]) >= 0]
     units = sum(int(s[3]) + int(s[5]) for s in steps)
     secs = sum(float(s[7]) + float(s[9]) for s in steps)
     value = units / secs
     desc = ("skin.scene at 1/16 scale (minsampledistance 0.006 -> %s irradiance points, 320x180x4spp -> %s camera samples), "
-            "reference Preprocess + camera pass restricted to what the device step computes (Scene::Intersect + the integrator's subsurface term: octree Mo, Fresnel, rho_dr, Ft), %d steps" % (steps[0][3], steps[0][5], len(steps)))
+            "reference Preprocess + its SamplerRendererTask loop (sampler, camera rays, Scene::Intersect, full Li, film AddSample), %d steps" % (steps[0][3], steps[0][5], len(steps)))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / max(1, len(steps)), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -148,17 +152,14 @@ def main():
     scene.upload(dev)
     material = build_material(scene, dev)
     n_pts = dev.tessellate_resident(scene.minsampledistance, material_id=0)     # also done inside every step
-    rays = scene.bench_rays()
-    n_rays = len(rays)
     n_tasks = scene.irradiance_tasks(n_pts, 1)
     # rank shards (contiguous, equal padded size so the all-gather can run in place)
     p_first, p_count, shard = pkg.shard_range(n_pts, rank, world)
-    # camera samples: 16x16-pixel tiles (the generator's order) dealt round-robin over the ranks
-    tile = 256 * max(1, scene.spp)
-    my_rays = rays if world == 1 else np.ascontiguousarray(rays[pkg.tile_round_robin(n_rays, tile, rank, world)])
-    r_first, r_count = 0, len(my_rays)
-    dev.set_camera_rays(my_rays)
-    pos_t = e_t = None
+    # camera samples: the reference's render tasks (sub-windows of the film), dealt round-robin over the ranks
+    r_count = dev.frame_setup(scene.frame_desc(n_cores=1, rank=rank, world=world))
+    r_first = 0
+    n_rays = r_count
+    pos_t = e_t = film_t = None
     if world > 1:
         import torch
         pa_ptr, e_ptr = dev.irradiance_dev(shard * world)
@@ -168,6 +169,8 @@ def main():
                 self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 3}
         pos_t = torch.as_tensor(_Wrap(pa_ptr, (shard * world, 4)), device="cuda")
         e_t = torch.as_tensor(_Wrap(e_ptr, (shard * world, 32)), device="cuda")
+        film_t = torch.as_tensor(_Wrap(dev.frame_film_dev(), (scene.yres * scene.xres, 4)), device="cuda")
+        t = torch.tensor([r_count], device="cuda", dtype=torch.int64); dist.all_reduce(t); n_rays = int(t.item())
 
     def exchange_and_build():
         """Irradiance exchange + octree.  N > 1: in-place NCCL all-gather of the shards; the positions (16 B/point) go
@@ -193,17 +196,25 @@ def main():
         dev.tessellate_resident(scene.minsampledistance, material_id=0)
         dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
         exchange_and_build()
-        dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix)
+        dev.frame_samples()
+        dev.frame_film_clear()
+        dev.frame_render(r_first, r_count, scene.maxerror, scene.mix)
+        if world > 1:
+            import torch
+            dev.synchronize()
+            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+            torch.cuda.current_stream().synchronize()
 
-    h_rays = dev.pinned((max(r_count, 1), 8), np.float32); h_rays[:r_count] = my_rays
-    h_L = dev.pinned((max(r_count, 1), 30), np.float32)
+    h2d_bytes = sum(a.nbytes for a in (scene.nodes, scene.prims, scene.P, scene.idx, scene.lights, scene.lights) if a is not None) \
+        + sum(a.nbytes for a in (scene.N, scene.uv) if a is not None)
+    d2h_bytes = scene.xres * scene.yres * 16 if rank == 0 else 0
+    e2e_image = {}
 
     def step_e2e():
-        dev.tessellate_resident(scene.minsampledistance, material_id=0)     # the scene (mesh, BVH, lights) is resident; points are made on the device
-        dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
-        exchange_and_build()
-        L = dev.lib.skc_camera_pass(dev.ctx, h_rays[r_first:].ctypes.data, r_count, scene.maxerror, scene.mix, None, h_L.ctypes.data)
-        dev._ck(L)
+        scene.upload(dev)                       # BVH nodes, primitives, mesh, lights from host memory
+        step_resident()
+        if rank == 0:
+            e2e_image["rgb"] = scene.film_to_rgb(dev.frame_film())      # film D2H + ImageFilm::WriteImage's pixel arithmetic
 
     def barrier():
         if world > 1:
@@ -233,7 +244,7 @@ def main():
     dev.timer_begin()
     for _ in range(args.steps):
         step_resident()
-        for s in ("tessellate", "scramble", "irradiance", "octree", "closest", "mo"):
+        for s in ("tessellate", "scramble", "irradiance", "octree", "samples", "closest", "mo", "direct", "film"):
             stage_acc[s] = stage_acc.get(s, 0.0) + dev.stage_ms(s)
     ms_total = dev.timer_end_ms()
     barrier()
@@ -301,15 +312,17 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "irradiance_points": n_pts, "camera_samples": n_rays, "irradiance_tasks": n_tasks,
                    "l2": "working set larger than L2 (surface points %.2f GB generated per step, octree + points > 4 GB)" % (n_pts * 44 / 1e9),
-                   "camera_sample_pattern": "stratified 2x2 per pixel (bench generator; parity tests use the reference's exported LD stream)",
+                   "camera_sample_pattern": "the reference's LDSampler stream, regenerated on the device every step (render tasks for 1 host core: %d)" % int(scene.frame_desc(1)[12:16].view(np.int32)[0]),
+                   "li": "full Li: emission + subsurface term + direct lighting (2 lights x 4 samples, MIS) + film",
                    "material_tables": material},
         "stage_ms": stage_ms,
         "hot_path_seconds": ms_step * 1e-3,
         "rays_per_s": (int(c_irr[2]) * world + n_rays) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),
         "irradiance_points_per_s": n_pts / ((stage_ms["scramble"] + stage_ms["irradiance"]) * 1e-3),
         "mo_points_per_s": n_rays / (stage_ms["mo"] * 1e-3),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(r_count * 32), "d2h_bytes_per_step": int(r_count * 120),
-                "ms_per_step": ms_e2e / args.steps},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
+                "ms_per_step": ms_e2e / args.steps, "render_seconds": ms_e2e / args.steps * 1e-3,
+                "what": "scene upload from host + Preprocess + camera pass + film to host + RGB conversion"},
         "gpu_launches": int(launches),
         "clocks": summarise_clocks(lines),
         "roofline": roofline,
@@ -320,13 +333,13 @@ def main():
         drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
         if os.path.exists(drv):
             cores = os.cpu_count() or 1
-            o = subprocess.run([drv, "bench", os.path.join(ROOT, "scenes", "skin_sample16.scene"), "--ncores", str(cores), "--steps", "2", "--warmup", "0", "--sss-only"],
+            o = subprocess.run([drv, "bench", os.path.join(ROOT, "scenes", "skin_sample16.scene"), "--ncores", str(cores), "--steps", "2", "--warmup", "0"],
                                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
             st = [l.split() for l in o.splitlines() if l.startswith("step ")]
             if st:
                 u = sum(int(s[3]) + int(s[5]) for s in st); sec = sum(float(s[7]) + float(s[9]) for s in st)
                 out["cpu_baseline"] = {"value": u / sec, "unit": UNIT, "cores": cores, "kind": "reference",
-                                       "sample": "skin.scene at 1/16 scale (%s points, %s camera samples), reference Preprocess + camera pass restricted to the subsurface term the device step computes, 2 steps, %.1f s" % (st[0][3], st[0][5], sec)}
+                                       "sample": "skin.scene at 1/16 scale (%s points, %s camera samples), reference Preprocess + its SamplerRendererTask loop with the full Li, 2 steps, %.1f s" % (st[0][3], st[0][5], sec)}
     print(json.dumps(out))
     dev.close()
     if world > 1:

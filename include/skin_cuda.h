@@ -242,6 +242,8 @@ typedef struct {
     float roughness, ior;          /* LayeredSkin: roughness, layers[0].ior */
     float Kr[SKC_NSPECTRAL], Kt[SKC_NSPECTRAL];  /* LayeredSkin "color Kr" / "color Kt" as spectra; a black one drops its lobe */
     float matteKd;                 /* MatteMaterial Kd of the emitter spheres (default 0.5) */
+    int32_t taskRank, taskWorld;   /* several GPUs: this context renders the tasks whose emission index % taskWorld == taskRank
+                                    * (round-robin tiles); taskWorld <= 1 = all tasks */
 } skc_frame_desc;
 /* Allocates the film and the sample stream for the frame; *nSamplesOut = samples of the whole sample extent
  * (Film::GetSampleExtent, film/image.cpp:158-167) x spp, in SamplerRendererTask order (task nTasks-1 first). */
@@ -253,8 +255,11 @@ int skc_frame_samples(skc_ctx *ctx);
  * (every 1-D array, then every 2-D array, as Sample::oneD / twoD) and the rays.  Any output may be NULL. */
 int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t count, float *xy, float *arrays, skc_ray *rays);
 uint32_t skc_frame_sample_floats(skc_ctx *ctx);
-/* Li for samples [first, first+count) and ImageFilm::AddSample of each into the device film.  L30 (optional, host)
- * receives the per-sample radiance [count][30]. */
+/* Li for samples [first, first+count) of the RENDER ORDER and ImageFilm::AddSample of each into the device film.
+ * The render order visits the pixels of every task window along a Z-curve (compact Mo packets); skc_frame_get_order
+ * gives, for render-order positions [first, first+count), the index of that sample in the sampler stream.  L30
+ * (optional, host) receives the per-sample radiance [count][30] in render order. */
+int skc_frame_get_order(skc_ctx *ctx, uint64_t first, uint64_t count, uint64_t *streamIndex);
 int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix, float *L30);
 /* Film pixels [yres][xres]{Lxyz[3], weightSum}: clear, device pointer (for the reduce to rank 0), copy out. */
 int skc_frame_film_clear(skc_ctx *ctx);

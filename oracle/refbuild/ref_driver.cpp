@@ -708,7 +708,8 @@ static int runBench(int argc, char **argv) {
         reporter.Done();
         delete sample;
         double tRender = now_s() - t0;
-        long nSamples = (long)nPixels * sr->sampler->samplesPerPixel;
+        // every sample of the sampler's extent is generated, traced and shaded (Film::GetSampleExtent adds a row and a column)
+        long nSamples = (long)(sr->sampler->xPixelEnd - sr->sampler->xPixelStart) * (sr->sampler->yPixelEnd - sr->sampler->yPixelStart) * sr->sampler->samplesPerPixel;
         double chk = 0.; for (double v : sinks) chk += v;
         printf("step %d points %zu samples %ld preprocess_s %.4f render_s %.4f %s checksum %.6g\n", it - warmup, integ->irradiancePoints.size(), nSamples, tPre, tRender,
                sssOnly ? "sss_only" : "full_li", chk);

@@ -63,6 +63,7 @@ struct skc_frame_state {
     uint64_t nPixels = 0, nSamples = 0;
     int4 *dWin = nullptr; uint32_t *dSeed = nullptr, *dPixBase = nullptr;
     float2 *dXY = nullptr; float *dArrays = nullptr; float4 *dFilm = nullptr;
+    uint32_t *dOrder = nullptr;   // render order: pixel slot -> pixel of the sampler stream (Z-order inside each task window)
     FrameConsts *dConsts = nullptr;
     bool samplesReady = false;
 };
@@ -70,7 +71,7 @@ struct skc_frame_state {
 void skc_frame_release(skc_ctx *ctx) {
     skc_frame_state *f = ctx->frame;
     if (!f) return;
-    void *ptrs[] = {f->dWin, f->dSeed, f->dPixBase, f->dXY, f->dArrays, f->dFilm, f->dConsts};
+    void *ptrs[] = {f->dWin, f->dSeed, f->dPixBase, f->dXY, f->dArrays, f->dFilm, f->dConsts, f->dOrder};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete f;
     ctx->frame = nullptr;
@@ -189,50 +190,85 @@ __device__ __forceinline__ DRay cameraRay(const FrameConsts *__restrict__ C, flo
     r.mint = 0.f; r.maxt = INFINITY;
     return r;
 }
+// Render order.  The kernels after the sampler work on camera samples in an order of their own choosing: within each
+// task window the pixels are visited along a Z-curve, so that the 32 consecutive samples of one Mo packet cover a
+// compact 4x2-pixel block (at 4 spp) instead of a strip -- neighbouring hit points share their octree walk.  Sample j
+// of the render order is sample renderToStream(j) of the reference's stream; the film does not depend on the order.
+__device__ __forceinline__ uint64_t renderToStream(const uint32_t *__restrict__ order, uint32_t spp, uint64_t j) {
+    return order ? (uint64_t)__ldg(&order[j / spp]) * spp + (j % spp) : j;
+}
 __global__ void __launch_bounds__(256) k_camera_rays(const FrameConsts *__restrict__ C, const float2 *__restrict__ xy, uint64_t n,
-                                                    skc_ray *__restrict__ rays) {
+                                                    const uint32_t *__restrict__ order, uint32_t spp, skc_ray *__restrict__ rays) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    DRay r = cameraRay(C, xy[i]);
+    DRay r = cameraRay(C, xy[renderToStream(order, spp, i)]);
     float4 *dst = reinterpret_cast<float4 *>(rays + i);
     dst[0] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
     dst[1] = make_float4(r.d.y, r.d.z, 0.f, INFINITY);
 }
 
-// Start of every pixel's words in its task's stream.  One warp per task; lane i < spp traces sample i of the pixel.
-#define LC_WARPS 4
-__global__ void __launch_bounds__(LC_WARPS * 32) k_ld_chain(BvhView bv, const FrameConsts *__restrict__ C, FrameLayout lay,
-                                                           const int4 *__restrict__ win, const uint32_t *__restrict__ pixBase, uint32_t nTasks,
-                                                           uint32_t cap, const uint32_t *__restrict__ words, uint64_t *__restrict__ pixOff) {
-    __shared__ float sxy[LC_WARPS][2 * FR_MAX_VALUES];
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t t = blockIdx.x * LC_WARPS + warp;
-    if (t >= nTasks) return;
+// Start of every pixel's words in its task's stream: off[k] = k*K + 6 * (camera rays of pixels < k that hit).
+// Pixel k's own hit count depends on off[k] (through its image samples), so this is a chain -- but an almost
+// data-independent one: whether a pixel's rays hit is decided by where the pixel is, and only at silhouettes by where
+// exactly its samples fall.  One CTA per task iterates to the fixed point instead of walking the pixels one by one:
+// every round computes all pixels' samples from the current offsets, traces all camera rays in parallel, and rescans
+// the hit counts; pixel k is final after at most k+1 rounds (induction over k), in practice after 2-4 rounds.
+#define LC_THREADS 256
+__global__ void __launch_bounds__(LC_THREADS) k_ld_chain(BvhView bv, const FrameConsts *__restrict__ C, FrameLayout lay,
+                                                        const int4 *__restrict__ win, const uint32_t *__restrict__ pixBase,
+                                                        uint32_t cap, const uint32_t *__restrict__ words,
+                                                        uint64_t *__restrict__ pixOff, float2 *__restrict__ xy) {
+    extern __shared__ uint32_t sm[];                 // [nPix] hit counts, then [nPix] relative offsets
+    __shared__ int changed;
+    uint32_t t = blockIdx.x;
     int4 w = win[t];
     uint32_t p0 = pixBase[t], nPix = pixBase[t + 1] - p0, wx = (uint32_t)(w.y - w.x);
-    uint64_t off = (uint64_t)p0 * cap;              // the task's words start here (k_mt_words)
-    float *buf = sxy[warp];
-    for (uint32_t k = 0; k < nPix; ++k) {
-        if (lane == 0) {
-            pixOff[p0 + k] = off;
+    uint32_t *hits = sm, *rel = sm + nPix;
+    const uint32_t *tw = words + (uint64_t)p0 * cap; // the task's words start here (k_mt_words)
+    const uint32_t spp = lay.spp;
+    int tid = threadIdx.x;
+    for (uint32_t k = tid; k < nPix; k += LC_THREADS) rel[k] = k * lay.draws;
+    __syncthreads();
+    for (uint32_t round = 0; round <= nPix; ++round) {
+        // image samples of every pixel at its current offset (LDPixelSample's first array)
+        for (uint32_t k = tid; k < nPix; k += LC_THREADS) {
+            float buf[2 * FR_MAX_VALUES];
             uint32_t ri = 0;
-            ldScrambled2D(1, lay.spp, buf, words + off, ri);
+            ldScrambled2D(1, spp, buf, tw + rel[k], ri);
+            int xPos = w.x + (int)(k % wx), yPos = w.z + (int)(k / wx);
+            for (uint32_t i = 0; i < spp; ++i) xy[(uint64_t)(p0 + k) * spp + i] = make_float2((float)xPos + buf[2 * i], (float)yPos + buf[2 * i + 1]);
+            hits[k] = 0;
         }
-        __syncwarp();
-        int xPos = w.x + (int)(k % wx), yPos = w.z + (int)(k / wx);
-        uint32_t hits = 0;
-        for (uint32_t i0 = 0; i0 < lay.spp; i0 += 32) {
-            uint32_t i = i0 + lane;
-            bool hit = false;
-            if (i < lay.spp) {
-                DRay r = cameraRay(C, make_float2((float)xPos + buf[2 * i], (float)yPos + buf[2 * i + 1]));
-                hit = bvhOccluded<false>(bv, r, nullptr);       // Scene::Intersect is true iff anything lies on the ray
+        if (tid == 0) changed = 0;
+        __syncthreads();
+        // Scene::Intersect is true iff anything lies on the camera ray
+        for (uint32_t j = tid; j < nPix * spp; j += LC_THREADS) {
+            DRay r = cameraRay(C, xy[(uint64_t)p0 * spp + j]);
+            if (bvhOccluded<false>(bv, r, nullptr)) atomicAdd(&hits[j / spp], 1u);
+        }
+        __syncthreads();
+        // exclusive scan of the hit counts (warp 0, 32 pixels at a time)
+        if (tid < 32) {
+            uint32_t running = 0;
+            bool ch = false;
+            for (uint32_t b = 0; b < nPix; b += 32) {
+                uint32_t k = b + tid;
+                uint32_t h = k < nPix ? hits[k] : 0, incl = h;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += v; }
+                if (k < nPix) {
+                    uint32_t nr = k * lay.draws + 6 * (running + incl - h);
+                    ch |= nr != rel[k];
+                    rel[k] = nr;
+                }
+                running += __shfl_sync(0xffffffffu, incl, 31);
             }
-            hits += __popc(__ballot_sync(0xffffffffu, hit));
+            if (__any_sync(0xffffffffu, ch) && tid == 0) changed = 1;
         }
-        off += lay.draws + 6 * hits;
-        __syncwarp();
+        __syncthreads();
+        if (!changed) break;
+        __syncthreads();
     }
+    for (uint32_t k = tid; k < nPix; k += LC_THREADS) pixOff[p0 + k] = (uint64_t)p0 * cap + rel[k];
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -311,7 +347,8 @@ __device__ __forceinline__ float powerHeuristic(float fPdf, float gPdf) {   // c
 __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_light *__restrict__ lights, FrameLayout lay,
                                                      RhoBxdf mf, float ior, float kd, int hasR, int hasT,
                                                      const skc_hit *__restrict__ hits, const float4 *__restrict__ frame,
-                                                     const float *__restrict__ arrays, uint64_t n, float4 *__restrict__ terms) {
+                                                     const float *__restrict__ arrays, const uint32_t *__restrict__ order, uint64_t first,
+                                                     uint64_t n, float4 *__restrict__ terms) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * lay.slots) return;
     uint64_t s = t / lay.slots;
@@ -331,7 +368,7 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
         B.tn = cross3(B.nn, B.sn);
         B.matte = __float_as_int(__ldg(hp + 13)) == 0;
         B.mf = mf; B.ior = ior; B.lambert = kd * FR_INV_PI; B.hasR = hasR != 0; B.hasT = hasT != 0;
-        const float *A = arrays + s * lay.floats;
+        const float *A = arrays + renderToStream(order, lay.spp, first + s) * lay.floats;
         float lu0 = __ldg(A + lay.off2L[li] + 2 * j), lu1 = __ldg(A + lay.off2L[li] + 2 * j + 1);
         float bc = __ldg(A + lay.off1B[li] + j), bu0 = __ldg(A + lay.off2B[li] + 2 * j), bu1 = __ldg(A + lay.off2B[li] + 2 * j + 1);
         const skc_light &L = lights[li];
@@ -390,6 +427,7 @@ __device__ __forceinline__ float lobeValue(float4 c, float Kr, float Kt) {
 __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const skc_light *__restrict__ lights, FrameLayout lay,
                                                             const FrameConsts *__restrict__ C, const skc_hit *__restrict__ hits,
                                                             const float4 *__restrict__ terms, const float2 *__restrict__ xy,
+                                                            const uint32_t *__restrict__ order, uint64_t first,
                                                             uint64_t n, float *__restrict__ Lrows, float4 *__restrict__ film) {
     __shared__ float sL[FS_WARPS][32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -441,7 +479,7 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
     }
     float X = __shfl_sync(0xffffffffu, xyzc, 0), Y = __shfl_sync(0xffffffffu, xyzc, 1), Z = __shfl_sync(0xffffffffu, xyzc, 2);
     if (lane == 0) {
-        float2 p = xy[s];
+        float2 p = xy[renderToStream(order, lay.spp, first + s)];
         float dimageX = p.x - 0.5f, dimageY = p.y - 0.5f;
         int x0 = (int)ceilf(dimageX - C->filterXWidth), x1 = (int)floorf(dimageX + C->filterXWidth);
         int y0 = (int)ceilf(dimageY - C->filterYWidth), y1 = (int)floorf(dimageY + C->filterYWidth);
@@ -507,6 +545,7 @@ extern "C" int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *d, uint64_t *
     int dx = xe - xs, dy = ye - ys, nx = count, ny = 1;
     while ((nx & 0x1) == 0 && 2 * dx * ny < dy * nx) { nx >>= 1; ny <<= 1; }
     f->pixBase.push_back(0);
+    int emitted = 0;
     for (int i = 0; i < count; ++i) {
         int num = count - 1 - i;
         int xo = num % nx, yo = num / nx;
@@ -515,17 +554,36 @@ extern "C" int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *d, uint64_t *
         int x0 = floor2Int(lerpf(tx0, (float)xs, (float)xe)), x1 = floor2Int(lerpf(tx1, (float)xs, (float)xe));
         int y0 = floor2Int(lerpf(ty0, (float)ys, (float)ye)), y1 = floor2Int(lerpf(ty1, (float)ys, (float)ye));
         if (x0 == x1 || y0 == y1) continue;                   // GetSubSampler returns NULL
+        if (d->taskWorld > 1 && (emitted++ % d->taskWorld) != d->taskRank) continue;     // another rank's tile
         f->win.push_back(make_int4(x0, x1, y0, y1));
         f->seed.push_back((uint32_t)num);                     // RNG rng(taskNum), samplerrenderer.cpp:73
         f->pixBase.push_back(f->pixBase.back() + (uint32_t)((x1 - x0) * (y1 - y0)));
     }
     f->nPixels = f->pixBase.back();
+    std::vector<uint32_t> order(f->nPixels);
+    {   // Z-curve over the film (not per window: task windows are not multiples of the 4x2 block)
+        auto part1by1 = [](uint32_t v) { v &= 0xffff; v = (v | (v << 8)) & 0x00ff00ffu; v = (v | (v << 4)) & 0x0f0f0f0fu; v = (v | (v << 2)) & 0x33333333u; v = (v | (v << 1)) & 0x55555555u; return v; };
+        std::vector<std::pair<uint32_t, uint32_t>> keyed(f->nPixels);
+        for (size_t t = 0; t < f->win.size(); ++t) {
+            int4 w = f->win[t];
+            uint32_t wx = (uint32_t)(w.y - w.x), np = f->pixBase[t + 1] - f->pixBase[t];
+            for (uint32_t k = 0; k < np; ++k) {
+                uint32_t x = (uint32_t)(w.x - xs) + k % wx, y = (uint32_t)(w.z - ys) + k / wx;
+                keyed[f->pixBase[t] + k] = std::make_pair(part1by1(x) | (part1by1(y) << 1), f->pixBase[t] + k);
+            }
+        }
+        std::sort(keyed.begin(), keyed.end());
+        for (size_t k = 0; k < keyed.size(); ++k) order[k] = keyed[k].second;
+    }
     f->nSamples = f->nPixels * L.spp;
     if (!f->nPixels) return skc_fail(ctx, "skc_frame_setup: empty sample extent");
     size_t nT = f->win.size();
     SKC_CUDA(cudaMalloc((void **)&f->dWin, nT * sizeof(int4)));
     SKC_CUDA(cudaMalloc((void **)&f->dSeed, nT * sizeof(uint32_t)));
     SKC_CUDA(cudaMalloc((void **)&f->dPixBase, (nT + 1) * sizeof(uint32_t)));
+    SKC_CUDA(cudaMalloc((void **)&f->dOrder, f->nPixels * sizeof(uint32_t)));
+    SKC_CUDA(cudaMemcpyAsync(f->dOrder, order.data(), f->nPixels * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     SKC_CUDA(cudaMalloc((void **)&f->dXY, f->nSamples * sizeof(float2)));
     SKC_CUDA(cudaMalloc((void **)&f->dArrays, f->nSamples * L.floats * sizeof(float)));
     SKC_CUDA(cudaMalloc((void **)&f->dFilm, (size_t)d->xres * d->yres * sizeof(float4)));
@@ -571,11 +629,16 @@ extern "C" int skc_frame_samples(skc_ctx *ctx) {
     skc_stage_begin(ctx);
     k_mt_words<<<nT, 256, 0, ctx->stream>>>(f->dSeed, f->dPixBase, cap, dWords);
     SKC_LAUNCHED("k_mt_words");
-    k_ld_chain<<<(nT + LC_WARPS - 1) / LC_WARPS, LC_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), f->dConsts, f->lay, f->dWin, f->dPixBase, nT, cap, dWords, dPixOff);
+    uint32_t maxPix = 0;
+    for (size_t t = 0; t < f->win.size(); ++t) maxPix = std::max(maxPix, f->pixBase[t + 1] - f->pixBase[t]);
+    size_t chainSmem = (size_t)maxPix * 2 * sizeof(uint32_t);
+    if (chainSmem > 200 * 1024) return skc_fail(ctx, "skc_frame_samples: a render task of %u pixels exceeds the sampler kernel's shared memory", maxPix);
+    if (chainSmem > 48 * 1024) SKC_CUDA(cudaFuncSetAttribute(k_ld_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)chainSmem));
+    k_ld_chain<<<nT, LC_THREADS, chainSmem, ctx->stream>>>(skc_bvh_view(ctx), f->dConsts, f->lay, f->dWin, f->dPixBase, cap, dWords, dPixOff, f->dXY);
     SKC_LAUNCHED("k_ld_chain");
     k_ld_pixel<<<(unsigned)((f->nPixels + 127) / 128), 128, 0, ctx->stream>>>(f->lay, f->dWin, f->dPixBase, nT, dWords, dPixOff, f->dXY, f->dArrays);
     SKC_LAUNCHED("k_ld_pixel");
-    k_camera_rays<<<(unsigned)((f->nSamples + 255) / 256), 256, 0, ctx->stream>>>(f->dConsts, f->dXY, f->nSamples, ctx->resRays);
+    k_camera_rays<<<(unsigned)((f->nSamples + 255) / 256), 256, 0, ctx->stream>>>(f->dConsts, f->dXY, f->nSamples, f->dOrder, f->lay.spp, ctx->resRays);
     SKC_LAUNCHED("k_camera_rays");
     skc_stage_end(ctx, 9);
     f->samplesReady = true;
@@ -591,7 +654,13 @@ extern "C" int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t coun
     if (!count) return 0;
     if (xy) SKC_CUDA(cudaMemcpyAsync(xy, f->dXY + first, count * sizeof(float2), cudaMemcpyDeviceToHost, ctx->stream));
     if (arrays) SKC_CUDA(cudaMemcpyAsync(arrays, f->dArrays + first * f->lay.floats, count * f->lay.floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-    if (rays) SKC_CUDA(cudaMemcpyAsync(rays, ctx->resRays + first, count * sizeof(skc_ray), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rays) {   // stream order (the resident rays are in render order)
+        skc_ray *tmp = (skc_ray *)skc_scratch(ctx, 0, count * sizeof(skc_ray));
+        if (!tmp) return 1;
+        k_camera_rays<<<(unsigned)((count + 255) / 256), 256, 0, ctx->stream>>>(f->dConsts, f->dXY + first, count, nullptr, f->lay.spp, tmp);
+        SKC_LAUNCHED("k_camera_rays");
+        SKC_CUDA(cudaMemcpyAsync(rays, tmp, count * sizeof(skc_ray), cudaMemcpyDeviceToHost, ctx->stream));
+    }
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -625,12 +694,12 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     skc_stage_begin(ctx);
     uint64_t nThreads = count * lay.slots;
     k_direct_terms<<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
-                                                                                dHits, dFrame, f->dArrays + first * lay.floats, count, dTerms);
+                                                                                dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms);
     SKC_LAUNCHED("k_direct_terms");
     skc_stage_end(ctx, 10);
     skc_stage_begin(ctx);
     k_frame_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, f->dConsts, dHits, dTerms,
-                                                                                                 f->dXY + first, count, dL, f->dFilm);
+                                                                                                 f->dXY, f->dOrder, first, count, dL, f->dFilm);
     SKC_LAUNCHED("k_frame_sum");
     skc_stage_end(ctx, 11);
     if (L30) {
@@ -656,5 +725,18 @@ extern "C" int skc_frame_film_get(skc_ctx *ctx, float *pixels4) {
     if (!f) return skc_fail(ctx, "skc_frame_film_get: skc_frame_setup first");
     SKC_CUDA(cudaMemcpyAsync(pixels4, f->dFilm, (size_t)f->desc.xres * f->desc.yres * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int skc_frame_get_order(skc_ctx *ctx, uint64_t first, uint64_t count, uint64_t *streamIndex) {
+    if (!ctx) return 1;
+    skc_frame_state *f = ctx->frame;
+    if (!f) return skc_fail(ctx, "skc_frame_get_order: skc_frame_setup first");
+    if (first + count > f->nSamples) return skc_fail(ctx, "skc_frame_get_order: bad range");
+    std::vector<uint32_t> order(f->nPixels);
+    cudaSetDevice(ctx->device);
+    SKC_CUDA(cudaMemcpy(order.data(), f->dOrder, f->nPixels * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    uint32_t spp = f->lay.spp;
+    for (uint64_t j = 0; j < count; ++j) streamIndex[j] = (uint64_t)order[(first + j) / spp] * spp + (first + j) % spp;
     return 0;
 }

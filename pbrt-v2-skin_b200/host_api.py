@@ -119,12 +119,14 @@ class HostScene:
         dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
         dev.upload_lights(self.lights)
 
-    FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1)
+    FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1 + 2)
 
-    def frame_desc(self, n_cores=1):
-        """skc_frame_desc for this scene: camera, film + box filter, LDSampler, render task count (bytes)."""
+    def frame_desc(self, n_cores=1, rank=0, world=1):
+        """skc_frame_desc for this scene: camera, film + box filter, LDSampler, render task count (bytes).
+        rank / world: this context renders every world-th render task (round-robin tiles)."""
         buf = np.zeros(self.FRAME_DESC_BYTES, np.uint8)
         self.lib.skh_frame_desc(self.h, int(n_cores), buf.ctypes.data_as(C.c_void_p))
+        buf[-8:].view(np.int32)[:] = (rank, world)
         return buf
 
     def film_to_rgb(self, pixels4):

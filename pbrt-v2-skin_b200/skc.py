@@ -20,7 +20,8 @@ DT_MPC_OPTIONS = np.dtype([("desiredStepSize", "<f4"), ("desiredLength", "<u4"),
 assert DT_BVH_NODE.itemsize == 32 and DT_LIGHT.itemsize == 280 and DT_RAY.itemsize == 32 and DT_HIT.itemsize == 56
 assert DT_SURFACE_POINT.itemsize == 44 and DT_IRR_POINT.itemsize == 152
 
-STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6, "rho": 7, "tessellate": 8}
+STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "any": 5, "profile": 6, "rho": 7, "tessellate": 8,
+          "samples": 9, "direct": 10, "film": 11}
 
 # every symbol include/skin_cuda.h declares
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
@@ -32,7 +33,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
            "skc_tessellate_resident", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
-           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get"]
+           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_get_order"]
 
 
 class SkcError(RuntimeError):
@@ -100,6 +101,7 @@ def load_library():
     lib.skc_frame_get_samples.restype = i32; lib.skc_frame_get_samples.argtypes = [vp, u64, u64, vp, vp, vp]
     lib.skc_frame_sample_floats.restype = u32; lib.skc_frame_sample_floats.argtypes = [vp]
     lib.skc_frame_render.restype = i32; lib.skc_frame_render.argtypes = [vp, u64, u64, f32, f32, vp]
+    lib.skc_frame_get_order.restype = i32; lib.skc_frame_get_order.argtypes = [vp, u64, u64, vp]
     lib.skc_frame_film_clear.restype = i32; lib.skc_frame_film_clear.argtypes = [vp]
     lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
     lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
@@ -309,9 +311,16 @@ class SkinDevice:
         return xy, arr, rays
 
     def frame_render(self, first, count, max_error, mix=0.5, want_L=False):
+        """Samples [first, first+count) of the render order; L rows (optional) come back in render order."""
         L = np.empty((count, 30), np.float32) if want_L else None
         self._ck(self.lib.skc_frame_render(self.ctx, first, count, max_error, mix, _ptr(L)))
         return L
+
+    def frame_order(self, first, count):
+        """Sampler-stream index of each render-order position in [first, first+count)."""
+        idx = np.empty(count, np.uint64)
+        self._ck(self.lib.skc_frame_get_order(self.ctx, first, count, _ptr(idx)))
+        return idx.astype(np.int64)
 
     def frame_film_clear(self):
         self._ck(self.lib.skc_frame_film_clear(self.ctx))

@@ -60,7 +60,10 @@ def test_frame_radiance_vs_reference(dev, frame, ld4):
     z, meta = ld4
     hs, n = frame
     dev.frame_film_clear()
-    L = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+    Lr = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+    order = dev.frame_order(0, n)
+    assert np.array_equal(np.sort(order), np.arange(n)), "the render order is a permutation of the sampler stream"
+    L = np.empty_like(Lr); L[order] = Lr
     ref = z["L"]
     e = gu.row_rel_err(L, ref)
     lit = ref.max(axis=1) > 0
@@ -109,3 +112,32 @@ def test_frame_pfm_round_trip(dev, frame, tmp_path):
         assert float(f.readline()) < 0
         data = np.frombuffer(f.read(), "<f4").reshape(h, w, 3)[::-1]
     assert (w, h) == (hs.xres, hs.yres) and np.array_equal(data, rgb)
+
+
+def test_round_robin_tasks_partition_the_frame(pkg, dev, frame, ld4):
+    """Multi-GPU sharding of the camera pass: the render tasks dealt round-robin over `world` contexts produce every
+    sample of the single-context frame exactly once, and the films add up to the single-context film."""
+    z, meta = ld4
+    hs, n = frame
+    dev.frame_film_clear()
+    dev.frame_render(0, n, hs.maxerror, hs.mix)
+    full = dev.frame_film()
+    world = 3
+    got_xy, film = [], np.zeros_like(full)
+    try:
+        for rank in range(world):
+            m = dev.frame_setup(hs.frame_desc(n_cores=1, rank=rank, world=world))
+            dev.frame_samples()
+            xy, _, _ = dev.frame_get_samples(0, m)
+            got_xy.append(xy)
+            dev.frame_render(0, m, hs.maxerror, hs.mix)
+            film += dev.frame_film()
+    finally:
+        assert dev.frame_setup(hs.frame_desc(n_cores=1)) == n      # leave the module fixture's frame in place
+        dev.frame_samples()
+    allxy = np.concatenate(got_xy)
+    assert len(allxy) == n
+    key = lambda a: np.sort(np.ascontiguousarray(a).view(np.uint64).ravel())
+    assert np.array_equal(key(allxy), key(z["camera_xy"]))
+    assert np.array_equal(film[..., 3], full[..., 3])
+    assert np.allclose(film[..., :3], full[..., :3], rtol=1e-5, atol=1e-6 * np.abs(full[..., :3]).max())

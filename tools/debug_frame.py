@@ -29,9 +29,13 @@ hs.build_profile(dev)
 n_pts = dev.tessellate_resident(hs.minsampledistance, False, material_id=0)
 dev.irradiance_resident(0, n_pts, hs.irradiance_tasks(n_pts, 1), hs.mix)
 dev.build_octree()
-L = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
-Ls = np.empty((n, 30), np.float32)
-dev.camera_pass_resident(0, n, hs.maxerror, hs.mix, out=Ls)
+Lr = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+order = dev.frame_order(0, n)
+L = np.empty_like(Lr); L[order] = Lr
+Lsr = np.empty((n, 30), np.float32)
+dev.camera_pass_resident(0, n, hs.maxerror, hs.mix, out=Lsr)
+dev.synchronize()
+Ls = np.empty_like(Lsr); Ls[order] = Lsr
 dev.synchronize()
 ref, ref_s = z["L"], z["L_sss"]
 d_ref, d_got = ref - ref_s, L - Ls
