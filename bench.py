@@ -144,6 +144,7 @@ def main():
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = pkg.SkinDevice(local)
 

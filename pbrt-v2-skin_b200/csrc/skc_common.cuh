@@ -72,6 +72,7 @@ struct skc_ctx {
     uint32_t lightNS[16] = {0};   // RoundUpPow2(nSamples) per light (host copy for launch shapes)
     std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize
     bool otTopologyReady = false;
+    int moSplit = 0;         // warps per Mo packet (each sums 1/moSplit of the spectrum): 0 = by launch size; env SKC_MO_SPLIT=1|2
     int moPacket = 1;        // Mo kernel: 1 = packet (lane = hit), 0 = warp per hit (lane = wavelength); env SKC_MO_KERNEL=warp|packet
     uint64_t otPoints = 0;
     float otBoundsHost[6];

@@ -69,6 +69,7 @@ extern "C" skc_ctx *skc_create(int device) {
         return nullptr;
     }
     if (const char *k = getenv("SKC_MO_KERNEL")) ctx->moPacket = strcmp(k, "warp") != 0;
+    if (const char *k = getenv("SKC_MO_SPLIT")) ctx->moSplit = atoi(k) == 1 ? 1 : atoi(k) == 2 ? 2 : 0;
     return ctx;
 }
 

@@ -181,16 +181,18 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 // 120 B/sample result crosses PCIe while the kernel is still running instead of in a copy after it.
 struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; };
 
-template <bool COUNT>
-__device__ __forceinline__ void mopContribute(const MoTables &T, const float *sRcp, const float4 *__restrict__ row4, float d2, float scale,
-                                              bool active, float (&acc)[SKC_NS], uint32_t &gathers) {
+// NQ float4 groups of the 32-float row starting at group q0: 8 = the whole spectrum, 4 = half of it (a packet shared
+// by two warps, see k_mo_packet)
+template <bool COUNT, int NQ>
+__device__ __forceinline__ void mopContribute(const MoTables &T, const float *sRcp, const float4 *__restrict__ row4, int q0, float d2, float scale,
+                                              bool active, float (&acc)[4 * NQ], uint32_t &gathers) {
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-        float4 e4 = __ldg(row4 + q);
+    for (int qq = 0; qq < NQ; ++qq) {
+        float4 e4 = __ldg(row4 + q0 + qq);
         float e[4] = {e4.x, e4.y, e4.z, e4.w};
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const int w = 4 * q + r;
+            const int w = 4 * (NQ == 8 ? qq : q0 + qq) + r;
             if (w < SKC_NS) {
                 float f = d2 * sRcp[w];
                 if (active && f < T.lenM1) {
@@ -199,15 +201,37 @@ __device__ __forceinline__ void mopContribute(const MoTables &T, const float *sR
                     float t = f - (float)seg;
                     float2 v = __ldg(&T.pairs[(size_t)w * T.len + seg]);
                     float rd = (1.f - t) * v.x + t * v.y;
-                    acc[w] += (rd * e[r]) * scale;
+                    acc[4 * qq + r] += (rd * e[r]) * scale;
                 }
             }
         }
     }
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+// Li subsurface term of one (hit, wavelength) (multipolesubsurface.cpp:279-287)
+__device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, int wl, float mo) {
+    const float *hp = reinterpret_cast<const float *>(li.hits + hh);
+    if (!__float_as_int(__ldg(hp + 13)) || wl >= SKC_NS) return 0.f;
+    f3 nn = mk3(__ldg(hp + 7), __ldg(hp + 8), __ldg(hp + 9)), wo = mk3(__ldg(hp + 10), __ldg(hp + 11), __ldg(hp + 12));
+    float costheta = fminf(fabsf(dot3(wo, nn)), 1.f);
+    float fid = costheta * (float)(SKC_RHO_LEN - 1);
+    int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
+    float lerp = fid - (float)id;
+    float rho = (1.f - lerp) * __ldg(&li.rhoHd[id * SKC_EPAD + wl]) + lerp * __ldg(&li.rhoHd[(id + 1) * SKC_EPAD + wl]);
+    float Ft = 1.f - rho;
+    float a = 1.f;
+    if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + wl]), (double)(1.f - li.mix));
+    return fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
+}
+
+// SPLIT = 1: one warp per packet sums all 30 wavelengths.  SPLIT = 2: two warps share a packet, each walks the octree
+// for the same 32 hit points (identical decisions, no communication) and sums one half of the spectrum (wavelengths 0-15 /
+// 16-29).  The walk's tests are a few per cent of the work and get done twice; in return a packet finishes in half the
+// time -- the heaviest packets of a frame otherwise run 15-25 ms (each warp owns 1/28 of its SM's gather pipe) and
+// set the length of every launch that has few packets per warp (multi-GPU shards) -- and 16 accumulators instead of
+// 30 leave room for more resident warps.
+template <bool COUNT, int SPLIT>
+__global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                              uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
                                                              uint32_t *__restrict__ nextPacket) {
@@ -219,21 +243,24 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
     uint2 *stack = stacks[warp];
     uint32_t wc[4] = {0, 0, 0, 0};
     uint32_t gathers = 0;          // this lane's table reads (COUNT only)
-    const uint32_t nPackets = (uint32_t)((n + 31) / 32);
+    const uint32_t nPackets = (uint32_t)((n + 31) / 32), nTickets = nPackets * SPLIT;
+    constexpr int NQ = 8 / SPLIT;
     // persistent warps: packets are handed out in order from a global counter, so the per-packet cost (none for sky,
     // ~0.1 ms for a packet on the skin) balances across the grid and no wave of CTAs leaves a tail
     for (;;) {
     uint32_t packet = 0;
     if (lane == 0) packet = atomicAdd(nextPacket, 1u);
     packet = __shfl_sync(0xffffffffu, packet, 0);
-    if (packet >= nPackets) break;
+    if (packet >= nTickets) break;
+    const int part = SPLIT == 1 ? 0 : (int)(packet % SPLIT), q0 = part * NQ;
+    packet /= SPLIT;
     uint64_t h0 = (uint64_t)packet * 32, h = h0 + lane;
     bool on = h < n && (enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true);
     float px = 0.f, py = 0.f, pz = 0.f;
     if (on) { const float *pp = p3 + h * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
-    float acc[SKC_NS];
+    float acc[4 * NQ];
 #pragma unroll
-    for (int w = 0; w < SKC_NS; ++w) acc[w] = 0.f;
+    for (int w = 0; w < 4 * NQ; ++w) acc[w] = 0.f;
     unsigned all = __ballot_sync(0xffffffffu, on);
     int sp = 0;
     if (all) { if (lane == 0) stack[0] = make_uint2(0u, all); sp = 1; }
@@ -246,7 +273,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
         const float4 *nd = tr.nodes + 3 * (size_t)ent.x;
         float4 g = __ldg(nd), b0 = __ldg(nd + 1), b1 = __ldg(nd + 2);
         uint32_t w0 = __float_as_uint(b1.z), w1 = __float_as_uint(b1.w);
-        if (COUNT) wc[0] += __popc(ent.y);
+        if (COUNT && part == 0) wc[0] += __popc(ent.y);
         if (w1 & SKC_OT_BLACK) continue;
         float dx = px - g.x, dy = py - g.y, dz = pz - g.z;
         float d2 = dx * dx + dy * dy + dz * dz;
@@ -264,13 +291,13 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
         }
         unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
         if (am) {
-            if (COUNT) wc[2] += __popc(am);
-            mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.Et + (size_t)ent.x * SKC_EPAD), d2, 1.f, addC, acc, gathers);
+            if (COUNT && part == 0) wc[2] += __popc(am);
+            mopContribute<COUNT, NQ>(T, sRcp, reinterpret_cast<const float4 *>(tr.Et + (size_t)ent.x * SKC_EPAD), q0, d2, 1.f, addC, acc, gathers);
         }
         if (dm) {
             if (w1 & SKC_OT_LEAF) {
                 uint32_t cntP = w1 & 0xffu;
-                if (COUNT) wc[1] += cntP * __popc(dm);
+                if (COUNT && part == 0) wc[1] += cntP * __popc(dm);
                 for (uint32_t k = 0; k < cntP; ++k) {
                     uint32_t slot = w0 + k;
                     float4 pa = __ldg(&tr.leafPosArea[slot]);
@@ -279,8 +306,8 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
                     bool c = descend && q2 * T.rcpMin < T.lenM1;
                     unsigned pm = __ballot_sync(0xffffffffu, c);
                     if (pm) {
-                        if (COUNT) wc[3] += __popc(pm);
-                        mopContribute<COUNT>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q2, pa.w, c, acc, gathers);
+                        if (COUNT && part == 0) wc[3] += __popc(pm);
+                        mopContribute<COUNT, NQ>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q0, q2, pa.w, c, acc, gathers);
                     }
                 }
             } else {
@@ -294,6 +321,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
     // transpose through the (now idle) stack memory: lane = hit -> lane = wavelength rows
     float *tile = reinterpret_cast<float *>(stack);           // 32 x 33 floats = 4224 B > 4096: use two halves
     __syncwarp();
+    if constexpr (SPLIT == 1) {
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         // hits [16*half, 16*half+16): lanes of that half write their 30 sums, then all lanes stream rows out
@@ -309,21 +337,29 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, 7) k_mo_packet(MoTree tr, MoTa
             float mo = tile[r * 33 + lane];
             if (Mo) Mo[hh * SKC_EPAD + lane] = mo;
             if (li.L) {
-                const float *hp = reinterpret_cast<const float *>(li.hits + hh);
-                float out = 0.f;
-                if (__float_as_int(__ldg(hp + 13)) && lane < SKC_NS) {
-                    f3 nn = mk3(__ldg(hp + 7), __ldg(hp + 8), __ldg(hp + 9)), wo = mk3(__ldg(hp + 10), __ldg(hp + 11), __ldg(hp + 12));
-                    float costheta = fminf(fabsf(dot3(wo, nn)), 1.f);
-                    float fid = costheta * (float)(SKC_RHO_LEN - 1);
-                    int id = min(max((int)fid, 0), SKC_RHO_LEN - 2);
-                    float lerp = fid - (float)id;
-                    float rho = (1.f - lerp) * __ldg(&li.rhoHd[id * SKC_EPAD + lane]) + lerp * __ldg(&li.rhoHd[(id + 1) * SKC_EPAD + lane]);
-                    float Ft = 1.f - rho;
-                    float a = 1.f;
-                    if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + lane]), (double)(1.f - li.mix));
-                    out = fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
-                }
+                float out = liSssValue(li, hh, lane, mo);
                 if (lane < SKC_NS) li.L[hh * SKC_NS + lane] = out;
+            }
+        }
+        __syncwarp();
+    }
+    } else {
+        // this warp's 4*NQ wavelengths of all 32 hits: 32 x (4*NQ+1) floats, then 32/(4*NQ) hits per pass
+#pragma unroll
+        for (int w = 0; w < 4 * NQ; ++w) tile[lane * (4 * NQ + 1) + w] = acc[w];
+        __syncwarp();
+        constexpr int NW = 4 * NQ;                     // wavelengths of this warp; 32 / NW hits per pass
+        const int wl = 4 * q0 + (lane % NW);
+        for (int r = 0; r < 32; r += 32 / NW) {
+            int rr = r + lane / NW;
+            uint64_t hh = h0 + rr;
+            if (hh < n) {
+                float mo = tile[rr * (NW + 1) + (lane % NW)];
+                if (Mo) Mo[hh * SKC_EPAD + wl] = mo;
+                if (li.L) {
+                    float out = liSssValue(li, hh, wl, mo);
+                    if (wl < SKC_NS) li.L[hh * SKC_NS + wl] = out;
+                }
             }
         }
         __syncwarp();
@@ -416,8 +452,18 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
         if (!next) return 1;
         SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
-        if (cntDev) k_mo_packet<true><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
-        else k_mo_packet<false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
+        // one warp per packet when there are plenty of packets per resident warp; two warps per packet (half the spectrum each)
+        // when a launch is short (multi-GPU shards), where the heaviest packets' run time is what the launch waits for.
+        // Measured on skin.scene: 28 packets/warp 60.4 vs 61.9 ms, 14 packets/warp 38.1 vs 35.7 ms, 3.5 packets/warp 23.0 vs 17.5 ms
+        int split = ctx->moSplit ? ctx->moSplit : ((n + 31) / 32 >= 20ull * ctx->smCount * 7 * MOP_WARPS ? 1 : 2);
+        if (split == 2) {
+            pb = std::min<uint64_t>(2 * ((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32)), (uint64_t)ctx->smCount * 8);
+            if (cntDev) k_mo_packet<true, 2><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
+            else k_mo_packet<false, 2><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
+        } else {
+            if (cntDev) k_mo_packet<true, 1><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
+            else k_mo_packet<false, 1><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
+        }
         SKC_LAUNCHED("k_mo_packet");
         return 0;
     }

@@ -421,3 +421,26 @@ def test_device_tessellation_bit_exact(pkg, dev):
             assert np.array_equal(got["materialId"], ref["materialId"])
     finally:
         hs.close()
+
+
+def test_mo_packet_one_and_two_warps_per_packet_agree(pkg, tiny):
+    """The packet kernel with one warp per packet (all 30 wavelengths) and with two warps per packet (half the spectrum
+    each, the variant short launches use) performs the same arithmetic per wavelength: bit-identical rows."""
+    g = tiny
+    out = []
+    for split in ("1", "2"):
+        os.environ["SKC_MO_SPLIT"] = split
+        try:
+            d = pkg.SkinDevice(0)
+        finally:
+            del os.environ["SKC_MO_SPLIT"]
+        try:
+            gu.setup_device(d, g)
+            d.set_irradiance_points(g.irradiance_points)
+            d.build_octree()
+            L, _ = d.camera_pass(g.camera_rays, g.max_error, g.mix, want_hits=True)
+            out.append(L.copy())
+        finally:
+            d.close()
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+    assert out[0].max() > 0
