@@ -545,7 +545,6 @@ extern "C" int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *d, uint64_t *
     int dx = xe - xs, dy = ye - ys, nx = count, ny = 1;
     while ((nx & 0x1) == 0 && 2 * dx * ny < dy * nx) { nx >>= 1; ny <<= 1; }
     f->pixBase.push_back(0);
-    int emitted = 0;
     for (int i = 0; i < count; ++i) {
         int num = count - 1 - i;
         int xo = num % nx, yo = num / nx;
@@ -554,7 +553,9 @@ extern "C" int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *d, uint64_t *
         int x0 = floor2Int(lerpf(tx0, (float)xs, (float)xe)), x1 = floor2Int(lerpf(tx1, (float)xs, (float)xe));
         int y0 = floor2Int(lerpf(ty0, (float)ys, (float)ye)), y1 = floor2Int(lerpf(ty1, (float)ys, (float)ye));
         if (x0 == x1 || y0 == y1) continue;                   // GetSubSampler returns NULL
-        if (d->taskWorld > 1 && (emitted++ % d->taskWorld) != d->taskRank) continue;     // another rank's tile
+        // several GPUs: windows dealt round-robin along each row of windows, every row shifted by 3 against the one above
+        // (plain emission order would give each rank whole columns of the film whenever nx is a multiple of the world size)
+        if (d->taskWorld > 1 && (xo + 3 * yo) % d->taskWorld != d->taskRank) continue;
         f->win.push_back(make_int4(x0, x1, y0, y1));
         f->seed.push_back((uint32_t)num);                     // RNG rng(taskNum), samplerrenderer.cpp:73
         f->pixBase.push_back(f->pixBase.back() + (uint32_t)((x1 - x0) * (y1 - y0)));
