@@ -5,6 +5,7 @@ import types
 import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 DT_HIT = np.dtype([("hit", "<i4"), ("prim", "<i4"), ("t", "<f4"), ("rayEpsilon", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("wo", "<f4", 3), ("hasBssrdf", "<i4")])
 DT_SP = np.dtype([("p", "<f4", 3), ("n", "<f4", 3), ("u", "<f4"), ("v", "<f4"), ("materialId", "<u4"), ("area", "<f4"), ("rayEpsilon", "<f4")])
@@ -79,6 +80,26 @@ def smoke_check(pkg):
         e = row_rel_err(dev.mo(g.hits["p"][s], g.max_error), ref)
         assert e.max() < 1e-5, "Mo vs oracle: %.3g" % e.max()
     finally:
+        dev.close()
+    # one whole frame from the scene file (device tessellation, sampler stream, full Li, film) against the reference's image
+    z = np.load(os.path.join(GOLDEN, "skin_ld4.npz"))
+    dev = pkg.SkinDevice(0)
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_ld4.scene"))
+    try:
+        hs.upload(dev)
+        hs.build_profile(dev)
+        n_pts = dev.tessellate_resident(hs.minsampledistance, False, material_id=0)
+        dev.irradiance_resident(0, n_pts, hs.irradiance_tasks(n_pts, 1), hs.mix)
+        dev.build_octree()
+        n = dev.frame_setup(hs.frame_desc(n_cores=1))
+        dev.frame_samples()
+        dev.frame_render(0, n, hs.maxerror, hs.mix)
+        rgb = hs.film_to_rgb(dev.frame_film())
+        ref = z["image"]
+        rmse = np.sqrt(np.mean((rgb - ref) ** 2)) / np.sqrt(np.mean(ref ** 2))
+        assert rmse < 1e-3, "frame RMSE %.3g relative" % rmse
+    finally:
+        hs.close()
         dev.close()
 
 
