@@ -194,7 +194,10 @@ def main():
         dev.build_octree_finalize()
 
     def step_resident():
-        dev.tessellate_resident(scene.minsampledistance, material_id=0)
+        if world == 1:
+            dev.tessellate_resident(scene.minsampledistance, material_id=0)
+        else:
+            dev.tessellate_range(scene.minsampledistance, p_first, p_count, material_id=0)      # this rank's shard of the points
         dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
         exchange_and_build()
         dev.frame_samples()

@@ -151,6 +151,10 @@ int skc_build_octree(skc_ctx *ctx, uint32_t *nNodesOut, float *root34, float *bo
  * edge factors round(0.8 * edge / minSampleDist)).  The result becomes the resident surface-point set (as after
  * skc_set_surface_points); skc_get_surface_points copies a range of it to the host. */
 int skc_tessellate_resident(skc_ctx *ctx, float minSampleDist, int incenter, uint32_t materialId, uint64_t *countOut);
+/* The same for one shard of the set (several GPUs): only the points [first, first+count) -- rounded out to whole
+ * triangles -- are written; *countOut is still the size of the whole set.  The rest of the resident array is left as it is. */
+int skc_tessellate_range(skc_ctx *ctx, float minSampleDist, int incenter, uint32_t materialId, uint64_t first, uint64_t count,
+                         uint64_t *countOut);
 int skc_get_surface_points(skc_ctx *ctx, uint64_t first, uint64_t count, skc_surface_point *out);
 
 /* MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) as ONE call: the irradiance pass over

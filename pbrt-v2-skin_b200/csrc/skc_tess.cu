@@ -13,6 +13,7 @@
 //   k_tess_emit   one CTA per triangle, one thread per (ring, side) walk; each step evaluates the sub-triangle's
 //                 centroid (or incentre), area, shading normal and uv with the reference's fp32 arithmetic
 #include <cub/device/device_scan.cuh>
+#include <algorithm>
 #include "skc_internal.h"
 
 struct TessBC { float b0, b1, b2; };
@@ -106,9 +107,11 @@ __device__ void tessMatching(const TessEmit &e, TessBC b0Inner, TessBC b1Inner, 
 }
 
 __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *__restrict__ idx, uint32_t nTris, float minDist, int incenter,
-                                                   uint32_t materialId, const uint32_t *__restrict__ offsets, skc_surface_point *__restrict__ out) {
+                                                   uint32_t materialId, const uint32_t *__restrict__ offsets, skc_surface_point *__restrict__ out,
+                                                   uint32_t rangeLo, uint32_t rangeHi) {
     uint32_t tri = blockIdx.x;
     if (tri >= nTris) return;
+    if (offsets[tri + 1] <= rangeLo || offsets[tri] >= rangeHi) return;      // none of this triangle's points is wanted (a shard of the set)
     TessEmit e;
     e.mv = mv; e.vi = make_int4(idx[3 * tri], idx[3 * tri + 1], idx[3 * tri + 2], 0);
     e.v0 = ld3(mv.P, e.vi.x); e.v1 = ld3(mv.P, e.vi.y); e.v2 = ld3(mv.P, e.vi.z);
@@ -155,7 +158,7 @@ __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *_
 }
 
 // GetSurfacePointsThroughTessellation for the uploaded mesh, written into the resident surface-point set
-extern "C" int skc_tessellate_resident(skc_ctx *ctx, float minDist, int incenter, uint32_t materialId, uint64_t *countOut) {
+static int tessellate(skc_ctx *ctx, float minDist, int incenter, uint32_t materialId, uint64_t first, uint64_t count, bool ranged, uint64_t *countOut) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     if (!ctx->meshIdx || !ctx->meshTris || !ctx->meshP) return skc_fail(ctx, "skc_tessellate_resident: no mesh uploaded (skc_upload_bvh)");
@@ -185,13 +188,22 @@ extern "C" int skc_tessellate_resident(skc_ctx *ctx, float minDist, int incenter
         ctx->resPtsCap = total;
     }
     if (total) {
-        k_tess_emit<<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts);
+        uint32_t lo = ranged ? (uint32_t)std::min<uint64_t>(first, total) : 0u, hi = ranged ? (uint32_t)std::min<uint64_t>(first + count, total) : total;
+        k_tess_emit<<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi);
         SKC_LAUNCHED("k_tess_emit");
     }
     skc_stage_end(ctx, 8);
     ctx->resPtsCount = total;
     if (countOut) *countOut = total;
     return 0;
+}
+
+extern "C" int skc_tessellate_resident(skc_ctx *ctx, float minDist, int incenter, uint32_t materialId, uint64_t *countOut) {
+    return tessellate(ctx, minDist, incenter, materialId, 0, 0, false, countOut);
+}
+extern "C" int skc_tessellate_range(skc_ctx *ctx, float minDist, int incenter, uint32_t materialId, uint64_t first, uint64_t count,
+                                    uint64_t *countOut) {
+    return tessellate(ctx, minDist, incenter, materialId, first, count, true, countOut);
 }
 
 // copy of resident surface points [first, first+count) for the host (tests, "pointsfile" export)

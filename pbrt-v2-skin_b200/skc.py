@@ -31,7 +31,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
-           "skc_tessellate_resident", "skc_get_surface_points",
+           "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_get_order"]
 
@@ -96,6 +96,7 @@ def load_library():
     lib.skc_timer_begin.restype = i32; lib.skc_timer_begin.argtypes = [vp]
     lib.skc_timer_end_ms.restype = f32; lib.skc_timer_end_ms.argtypes = [vp]
     lib.skc_set_point_count.restype = i32; lib.skc_set_point_count.argtypes = [vp, u64]
+    lib.skc_tessellate_range.restype = i32; lib.skc_tessellate_range.argtypes = [vp, f32, i32, u32, u64, u64, C.POINTER(u64)]
     lib.skc_frame_setup.restype = i32; lib.skc_frame_setup.argtypes = [vp, vp, C.POINTER(u64)]
     lib.skc_frame_samples.restype = i32; lib.skc_frame_samples.argtypes = [vp]
     lib.skc_frame_get_samples.restype = i32; lib.skc_frame_get_samples.argtypes = [vp, u64, u64, vp, vp, vp]
@@ -227,6 +228,12 @@ class SkinDevice:
         """Surface points of the uploaded mesh, generated on the device into the resident set; returns the count."""
         n = C.c_uint64(0)
         self._ck(self.lib.skc_tessellate_resident(self.ctx, min_dist, int(incenter), material_id, C.byref(n)))
+        return int(n.value)
+
+    def tessellate_range(self, min_dist, first, count, incenter=False, material_id=0):
+        """Surface points [first, first+count) of the tessellated set only (a rank's shard); returns the size of the whole set."""
+        n = C.c_uint64(0)
+        self._ck(self.lib.skc_tessellate_range(self.ctx, float(min_dist), int(incenter), int(material_id), int(first), int(count), C.byref(n)))
         return int(n.value)
 
     def get_surface_points(self, first, count):

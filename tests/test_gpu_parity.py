@@ -444,3 +444,24 @@ def test_mo_packet_one_and_two_warps_per_packet_agree(pkg, tiny):
             d.close()
     assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
     assert out[0].max() > 0
+
+
+def test_device_tessellation_of_a_shard(pkg, dev):
+    """skc_tessellate_range: a rank's shard of the surface points, rounded out to whole triangles, nothing else written."""
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tiny.scene"))
+    try:
+        hs.upload(dev)
+        ref = hs.tessellate(0.1, False)
+        n = len(ref)
+        dev.set_surface_points(np.zeros(n, ref.dtype))
+        first, count = n // 3, n // 5
+        assert dev.tessellate_range(0.1, first, count, material_id=int(ref["materialId"][0])) == n
+        got = dev.get_surface_points(0, n)
+        sl = slice(first, first + count)
+        assert np.array_equal(np.ascontiguousarray(got[sl]).view(np.uint8), np.ascontiguousarray(ref[sl]).view(np.uint8))
+        written = got["area"] != 0
+        assert written[sl].all()
+        # whole triangles only: at most one triangle's worth of extra points on either side
+        assert written.sum() < count + 2000 and not written[: first - 1000].any() and not written[first + count + 1000:].any()
+    finally:
+        hs.close()
