@@ -15,5 +15,5 @@ interfaces (host/).  There is no CPU fallback: every entry point raises if the l
 GPU is missing.
 """
 from .skc import SkinDevice, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
-from .host_api import HostScene, load_host_library, skin_spectra  # noqa: F401
+from .host_api import HostScene, load_host_library, skin_spectra, pbrt_render  # noqa: F401
 from .sharding import shard_range, tile_round_robin, allgather_inplace, allgather_inplace_async  # noqa: F401

@@ -58,7 +58,30 @@ skh_scene *skh_load(const char *path, char *errbuf, int errlen) {
     }
     return s;
 }
+// The same with the command-line options that reach the plugin factories (--quick, --outfile): main/pbrt.cpp:76-93
+skh_scene *skh_load_opts(const char *path, int quick, const char *outfile, char *errbuf, int errlen) {
+    skh_scene *s = new skh_scene();
+    LoadOptions opt;
+    opt.quickRender = quick != 0;
+    if (outfile) opt.imageFile = outfile;
+    std::string err;
+    if (!s->sd.Load(path, &opt) || !BuildScene(s->sd, nullptr, &s->built, &(err = s->sd.error))) {
+        if (err.empty()) err = s->sd.error;
+        if (errbuf) snprintf(errbuf, errlen, "%s", err.c_str());
+        delete s;
+        return nullptr;
+    }
+    return s;
+}
 void skh_free(skh_scene *s) { delete s; }
+int skh_warning_count(const skh_scene *s) { return (int)s->sd.warnings.size(); }
+const char *skh_warning(const skh_scene *s, int i) { return s->sd.warnings[i].c_str(); }
+const char *skh_film_filename(const skh_scene *s) { return s->sd.filmFilename.c_str(); }
+// Pixel filter: out = {xwidth, ywidth}, table256 = ImageFilm::filterTable
+void skh_filter(const skh_scene *s, float *out2, float *table256) { out2[0] = s->sd.filter.xwidth; out2[1] = s->sd.filter.ywidth; s->sd.filter.Table(table256); }
+// BVH build parameters: returns maxnodeprims, split method name copied into buf
+int skh_accelerator(const skh_scene *s, char *buf, int len) { snprintf(buf, len, "%s", s->sd.splitMethod.c_str()); return s->sd.maxNodePrims; }
+void skh_light_samples(const skh_scene *s, int *out) { for (size_t i = 0; i < s->sd.lights.size(); ++i) out[i] = s->sd.lights[i].nSamples; }
 
 // sizes: [0] nodes [1] prims [2] verts [3] tris [4] lights [5] hasN [6] hasUV [7] xres [8] yres [9] spp
 void skh_sizes(const skh_scene *s, int64_t *out) {
@@ -103,9 +126,8 @@ uint64_t skh_count_points(const skh_scene *s, float minDist) {
 }
 // Camera rays for given raster positions (cameras/perspective.cpp)
 void skh_camera_rays(skh_scene *s, const float *xy, uint64_t n, skc_ray *out) {
-    const float *la = s->sd.lookat;
-    Transform w2c = Transform() * LookAt(V3(la[0], la[1], la[2]), V3(la[3], la[4], la[5]), V3(la[6], la[7], la[8]));
-    PerspectiveCamera cam(InverseT(w2c), s->sd.fov, s->sd.xres, s->sd.yres);   // api.cpp:862
+    PerspectiveCamera cam(InverseT(s->sd.WorldToCamera), s->sd.fov, s->sd.xres, s->sd.yres, s->sd.frameAspect,
+                          s->sd.haveScreenWindow ? s->sd.screenWindow : nullptr);   // api.cpp:862
     for (uint64_t i = 0; i < n; ++i) cam.GenerateRay(xy[2 * i], xy[2 * i + 1], &out[i]);
 }
 // A deterministic stratified sample pattern for benches: spp samples per pixel, pixels visited
@@ -191,28 +213,7 @@ int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *
 // box filter of half-width 0.5 (film/image.cpp:55-66, filters/box.cpp), LDSampler pixelsamples rounded up to a power
 // of two (lowdiscrepancy.cpp:41-50), the render task count (samplerrenderer.cpp:206-208), EmissionIntegrator's two
 // 1-sample arrays (integrators/emission.cpp:42-45), the XYZ matching tables.
-void skh_frame_desc(const skh_scene *s, int nCores, skc_frame_desc *d) {
-    memset(d, 0, sizeof *d);
-    const SceneDesc &sd = s->sd;
-    d->xres = sd.xres; d->yres = sd.yres;
-    d->spp = (int)RoundUpPow2((uint32_t)std::max(1, sd.spp));
-    int nPixels = sd.xres * sd.yres;
-    d->nTasks = (int)RoundUpPow2((uint32_t)std::max(32 * nCores, nPixels / (16 * 16)));
-    d->extra1D = 2;
-    const float *la = sd.lookat;
-    Transform w2c = Transform() * LookAt(V3(la[0], la[1], la[2]), V3(la[3], la[4], la[5]), V3(la[6], la[7], la[8]));
-    PerspectiveCamera cam(InverseT(w2c), sd.fov, sd.xres, sd.yres);
-    memcpy(d->cameraToWorld, cam.CameraToWorld.m.m, 64);
-    memcpy(d->rasterToCamera, cam.RasterToCamera.m.m, 64);
-    d->filterXWidth = d->filterYWidth = 0.5f;
-    for (int i = 0; i < 256; ++i) d->filterTable[i] = 1.f;                   // BoxFilter::Evaluate
-    for (int k = 0; k < 3; ++k) memcpy(d->cieXYZ[k], kCieXYZ30[k], sizeof(float) * 30);
-    d->xyzScale = float(700 - 400) / float(kCieYIntegral * 30);               // core/spectrum.h:381-382
-    d->roughness = sd.skin.roughness; d->ior = sd.skin.layerIor[0];
-    // "color Kr" / "color Kt": Spectrum::FromRGB, grey values only on this path
-    for (int i = 0; i < 30; ++i) { d->Kr[i] = sd.skin.Kr[0] * kUnitRGBToSpectrum30[i]; d->Kt[i] = sd.skin.Kt[0] * kUnitRGBToSpectrum30[i]; }
-    d->matteKd = 0.5f;                                                        // materials/matte.cpp: Kd default
-}
+void skh_frame_desc(const skh_scene *s, int nCores, skc_frame_desc *d) { MakeFrameDesc(s->sd, nCores, d); }
 // ImageFilm::WriteImage (film/image.cpp:178-213): XYZ -> RGB, divide by the weight sum, clamp at 0.  rgb = [h][w][3].
 void skh_film_to_rgb(const float *pixels4, int w, int h, float *rgb) {
     for (int i = 0; i < w * h; ++i) {

@@ -1,0 +1,172 @@
+// skin_render.cpp -- SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) for a parsed scene, every stage on
+// the device through include/skin_cuda.h:
+//   LayeredSkin construction   materials/layeredskin.cpp:39-123   -> skc_profile_batch, skc_rho_table, skc_upload_profile
+//   RenderOptions::MakeScene   core/api.cpp:1190-1225             -> BuildScene (host BVH build) + skc_upload_bvh / skc_upload_lights
+//   integrator Preprocess      multipolesubsurface.cpp:170-238    -> skc_tessellate_resident, skc_irradiance_resident, skc_build_octree
+//   SamplerRendererTask loop   samplerrenderer.cpp:59-167         -> skc_frame_setup / _samples / _render
+//   ImageFilm::WriteImage      film/image.cpp:178-213             -> skc_frame_film_get + skh_film_to_rgb + the image writers below
+#include "skin_scene.h"
+#include "skin_material.h"
+#include "skin_cie.h"
+#include "skin_tables.h"
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+
+extern "C" void skh_film_to_rgb(const float *pixels4, int w, int h, float *rgb);
+extern "C" int skh_write_pfm(const char *path, const float *rgb, int w, int h);
+
+namespace skin {
+
+void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d) {
+    memset(d, 0, sizeof *d);
+    d->xres = sd.xres; d->yres = sd.yres;
+    d->spp = (int)RoundUpPow2((uint32_t)std::max(1, sd.spp));                // lowdiscrepancy.cpp:41-50
+    int nPixels = sd.xres * sd.yres;
+    d->nTasks = (int)RoundUpPow2((uint32_t)std::max(32 * nCores, nPixels / (16 * 16)));   // samplerrenderer.cpp:206-208
+    d->extra1D = 2;                                                           // EmissionIntegrator::RequestSamples
+    PerspectiveCameraDesc cam = sd.Camera();
+    memcpy(d->cameraToWorld, cam.CameraToWorld.m.m, 64);
+    memcpy(d->rasterToCamera, cam.RasterToCamera.m.m, 64);
+    d->filterXWidth = sd.filter.xwidth; d->filterYWidth = sd.filter.ywidth;
+    sd.filter.Table(d->filterTable);                                          // film/image.cpp:55-68
+    for (int k = 0; k < 3; ++k) memcpy(d->cieXYZ[k], kCieXYZ30[k], sizeof(float) * 30);
+    d->xyzScale = float(700 - 400) / float(kCieYIntegral * 30);               // core/spectrum.h:381-382
+    d->roughness = sd.skin.roughness; d->ior = sd.skin.layerIor[0];
+    // "color Kr" / "color Kt": Spectrum::FromRGB, grey values only on this path
+    for (int i = 0; i < 30; ++i) { d->Kr[i] = sd.skin.Kr[0] * kUnitRGBToSpectrum30[i]; d->Kt[i] = sd.skin.Kt[0] * kUnitRGBToSpectrum30[i]; }
+    d->matteKd = 0.5f;                                                        // materials/matte.cpp: Kd default
+}
+
+// LayeredSkin::LayeredSkin (materials/layeredskin.cpp:39-123): layer spectra -> 30 diffusion profiles -> rho_hd, all
+// generated on the device and installed as the context's material tables.
+int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin) {
+    SkinLayerSpectra sp = ComputeSkinLayerSpectra(skin);
+    ProfileTable t;
+    int rc = ComputeMultipoleProfile(ctx, sp, skin.desiredlength, skin.lerponthinslab, t);
+    if (rc) return rc;
+    std::vector<float> rho(1025 * 30);
+    if ((rc = skc_rho_table(ctx, skin.roughness, 1.f, skin.layerIor[0], 0, rho.data()))) return rc;
+    return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rho.data());
+}
+
+int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
+    const TriangleMesh &m = *b.mesh;
+    float o2w[32];
+    memcpy(o2w, m.ObjectToWorld.m.m, 64); memcpy(o2w + 16, m.ObjectToWorld.mInv.m, 64);
+    int rc = skc_upload_bvh(ctx, b.nodes.data(), (uint32_t)b.nodes.size(), b.prims.data(), (uint32_t)b.prims.size(),
+                            &m.p[0].x, m.n.empty() ? nullptr : &m.n[0].x, m.uvs.empty() ? nullptr : m.uvs.data(), (uint32_t)m.nverts,
+                            m.vertexIndex.data(), (uint32_t)m.ntris, o2w, m.ReverseOrientation, m.TransformSwapsHandedness,
+                            b.lights.data(), (uint32_t)b.lights.size());
+    if (rc) return rc;
+    return skc_upload_lights(ctx, b.lights.data(), (uint32_t)b.lights.size());
+}
+
+static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// rgb: [yres][xres][3] as ImageFilm::WriteImage hands to ::WriteImage
+bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err) {
+    auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
+    double t0 = now();
+    BuiltScene built;
+    if (!BuildScene(sd, nullptr, &built, err)) return false;
+    if (!dev(UploadScene(ctx, built))) return false;
+    double t1 = now();
+    if (!dev(BuildSkinMaterial(ctx, sd.skin)) || !dev(skc_synchronize(ctx))) return false;
+    double t2 = now();
+    // Preprocess
+    uint64_t nPts = 0;
+    if (!sd.lights.empty()) {                                                // multipolesubsurface.cpp:173
+        if (!dev(skc_tessellate_resident(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, &nPts))) return false;
+        st->irradianceTasks = RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPts / 4096));   // :194-199
+        if (!dev(skc_irradiance_resident(ctx, 0, nPts, st->irradianceTasks, sd.mix, nullptr))) return false;
+        if (!dev(skc_build_octree(ctx, &st->octreeNodes, nullptr, nullptr))) return false;
+    } else { *err = "no light sources in the scene: the subsurface integrator has nothing to render"; return false; }
+    if (!dev(skc_synchronize(ctx))) return false;
+    double t3 = now();
+    // the camera pass
+    skc_frame_desc fd;
+    MakeFrameDesc(sd, nCores, &fd);
+    uint64_t nSamples = 0;
+    if (!dev(skc_frame_setup(ctx, &fd, &nSamples)) || !dev(skc_frame_samples(ctx)) || !dev(skc_frame_film_clear(ctx)) ||
+        !dev(skc_frame_render(ctx, 0, nSamples, sd.maxerror, sd.mix, nullptr))) return false;
+    std::vector<float> film((size_t)sd.xres * sd.yres * 4);
+    if (!dev(skc_frame_film_get(ctx, film.data()))) return false;
+    rgb->resize((size_t)sd.xres * sd.yres * 3);
+    skh_film_to_rgb(film.data(), sd.xres, sd.yres, rgb->data());
+    double t4 = now();
+    st->buildSec = t1 - t0; st->materialSec = t2 - t1; st->preprocessSec = t3 - t2; st->renderSec = t4 - t3;
+    st->nPoints = nPts; st->nSamples = nSamples; st->renderTasks = (uint32_t)fd.nTasks;
+    return true;
+}
+
+// WriteImageTGA (core/imageio.cpp:185-215): 24-bit BGR, gamma 2.2, top row first
+static bool writeTGA(const std::string &name, const float *rgb, int w, int h) {
+    FILE *f = fopen(name.c_str(), "wb");
+    if (!f) return false;
+    unsigned char hdr[18] = {0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, (unsigned char)(w & 255), (unsigned char)(w >> 8), (unsigned char)(h & 255),
+                             (unsigned char)(h >> 8), 24, 0x20};
+    bool ok = fwrite(hdr, 1, 18, f) == 18;
+    std::vector<unsigned char> row(3 * (size_t)w);
+    auto toByte = [](float v) { float x = 255.f * powf(v, 1.f / 2.2f); return (unsigned char)(x < 0.f ? 0.f : x > 255.f ? 255.f : x); };
+    for (int y = 0; y < h && ok; ++y) {
+        for (int x = 0; x < w; ++x) {
+            const float *p = rgb + 3 * ((size_t)y * w + x);
+            row[3 * x] = toByte(p[2]); row[3 * x + 1] = toByte(p[1]); row[3 * x + 2] = toByte(p[0]);
+        }
+        ok = fwrite(row.data(), 1, row.size(), f) == row.size();
+    }
+    fclose(f);
+    return ok;
+}
+
+// ::WriteImage (core/imageio.cpp:78-104) without OpenEXR
+bool WriteImage(const std::string &name, const float *rgb, int w, int h, std::string *err) {
+    auto ends = [&](const char *a, const char *b) { return name.size() >= 5 && (!name.compare(name.size() - 4, 4, a) || !name.compare(name.size() - 4, 4, b)); };
+    if (ends(".pfm", ".PFM")) { if (skh_write_pfm(name.c_str(), rgb, w, h)) { *err = "Unable to open output PFM file \"" + name + "\""; return false; } return true; }
+    if (ends(".tga", ".TGA")) { if (!writeTGA(name, rgb, w, h)) { *err = "Unable to write image file \"" + name + "\""; return false; } return true; }
+    if (ends(".exr", ".EXR")) { *err = "OpenEXR is not available in this build (as in a reference build without PBRT_HAS_OPENEXR): use a .pfm or .tga filename"; return false; }
+    *err = "Can't determine image file type from suffix of filename \"" + name + "\"";
+    return false;
+}
+
+}  // namespace skin
+
+// ---- C interface (tests, bench, the pbrt executable) ------------------------------------------------------------------
+using namespace skin;
+
+extern "C" {
+
+// `pbrt [--ncores n] [--outfile f] [--quick] scene` in one call: parse, build, render on `device`, write the image (when
+// the film has a filename or outfile is given; "" -> pbrt.tga) and/or return the RGB pixels.  rgbOut may be NULL; when
+// not, it must hold xres*yres*3 floats -- call with rgbOut == NULL and dims != NULL first to learn the size (no render).
+// stats (optional) = {build s, material s, preprocess s, render s, points, samples, octree nodes}.
+int skh_pbrt_render(const char *scenePath, int device, int nCores, int quick, const char *outfile, int writeImage, int *dims2, float *rgbOut,
+                    double *stats7, char *errbuf, int errlen) {
+    auto fail = [&](const std::string &e) { if (errbuf) snprintf(errbuf, errlen, "%s", e.c_str()); return 1; };
+    SceneDesc sd;
+    LoadOptions opt;
+    opt.quickRender = quick != 0;
+    if (outfile) opt.imageFile = outfile;
+    if (!sd.Load(scenePath, &opt)) return fail(sd.error);
+    if (dims2) { dims2[0] = sd.xres; dims2[1] = sd.yres; }
+    if (!rgbOut && !writeImage) return 0;
+    skc_ctx *ctx = skc_create(device);
+    if (!ctx) return fail(std::string("skc_create: ") + skc_last_error(nullptr));
+    std::vector<float> rgb;
+    RenderStats st;
+    std::string err;
+    bool ok = RenderScene(ctx, sd, nCores, &rgb, &st, &err);
+    skc_destroy(ctx);
+    if (!ok) return fail(err);
+    if (rgbOut) memcpy(rgbOut, rgb.data(), rgb.size() * sizeof(float));
+    if (stats7) { stats7[0] = st.buildSec; stats7[1] = st.materialSec; stats7[2] = st.preprocessSec; stats7[3] = st.renderSec;
+                  stats7[4] = (double)st.nPoints; stats7[5] = (double)st.nSamples; stats7[6] = (double)st.octreeNodes; }
+    if (writeImage) {
+        std::string name = sd.filmFilename.empty() ? "pbrt.tga" : sd.filmFilename;
+        if (!WriteImage(name, rgb.data(), sd.xres, sd.yres, &err)) return fail(err);
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -79,11 +79,13 @@ Transform Perspective(float fov, float n, float f) {   // transform.cpp:309-319
 }
 
 // core/camera.cpp:83-102, cameras/perspective.cpp:124-155
-PerspectiveCamera::PerspectiveCamera(const Transform &cam2world, float fov, int xres, int yres) : CameraToWorld(cam2world) {
-    float frame = float(xres) / float(yres);
+PerspectiveCamera::PerspectiveCamera(const Transform &cam2world, float fov, int xres, int yres, float frameAspect, const float *screenWindow)
+    : CameraToWorld(cam2world) {
+    float frame = frameAspect > 0.f ? frameAspect : float(xres) / float(yres);
     float screen[4];
     if (frame > 1.f) { screen[0] = -frame; screen[1] = frame; screen[2] = -1.f; screen[3] = 1.f; }
     else { screen[0] = -1.f; screen[1] = 1.f; screen[2] = -1.f / frame; screen[3] = 1.f / frame; }
+    if (screenWindow) memcpy(screen, screenWindow, sizeof screen);
     Transform CameraToScreen = Perspective(fov, 1e-2f, 1000.f);
     Transform ScreenToRaster = Scale(float(xres), float(yres), 1.f) *
                                Scale(1.f / (screen[1] - screen[0]), 1.f / (screen[2] - screen[3]), 1.f) *
@@ -130,32 +132,94 @@ BBox SphereLight::WorldBound() const {
     return ObjectToWorld.Box(BBox(V3(-radius, -radius, zmn), V3(radius, radius, zmx)));
 }
 
+void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, int nverts, const float *P, const float *N, const float *uv,
+              int ntris, const int *indices) {
+    m->nverts = nverts; m->ntris = ntris;
+    m->p.resize(nverts);
+    for (int i = 0; i < nverts; ++i) m->p[i] = o2w.Point(V3(P[3 * i], P[3 * i + 1], P[3 * i + 2]));   // trianglemesh.cpp:72-73
+    m->n.clear(); m->uvs.clear();
+    if (N) { m->n.resize(nverts); memcpy((void *)m->n.data(), N, 12 * (size_t)nverts); }
+    if (uv) m->uvs.assign(uv, uv + 2 * (size_t)nverts);
+    m->vertexIndex.assign(indices, indices + 3 * (size_t)ntris);
+    m->ObjectToWorld = o2w;
+    m->ReverseOrientation = reverseOrientation;
+    m->TransformSwapsHandedness = o2w.SwapsHandedness();
+}
+
 static bool loadMesh(const std::string &file, const Transform &o2w, TriangleMesh *m, std::string *err) {
     FILE *f = fopen(file.c_str(), "rb");
     if (!f) { *err = "cannot open mesh " + file; return false; }
     int32_t hdr[4];
     bool ok = fread(hdr, 4, 4, f) == 4;
     if (ok) {
-        m->nverts = hdr[0]; m->ntris = hdr[1];
-        std::vector<V3> P(m->nverts);
-        ok = fread(P.data(), 12, m->nverts, f) == (size_t)m->nverts;
-        if (ok && hdr[2]) { m->n.resize(m->nverts); ok = fread(m->n.data(), 12, m->nverts, f) == (size_t)m->nverts; }
-        if (ok && hdr[3]) { m->uvs.resize(2 * (size_t)m->nverts); ok = fread(m->uvs.data(), 8, m->nverts, f) == (size_t)m->nverts; }
-        if (ok) { m->vertexIndex.resize(3 * (size_t)m->ntris); ok = fread(m->vertexIndex.data(), 12, m->ntris, f) == (size_t)m->ntris; }
-        if (ok) {
-            m->p.resize(m->nverts);
-            for (int i = 0; i < m->nverts; ++i) m->p[i] = o2w.Point(P[i]);   // trianglemesh.cpp:72-73
-        }
+        int nv = hdr[0], nt = hdr[1];
+        std::vector<float> P(3 * (size_t)nv), N, uv;
+        std::vector<int> idx;
+        ok = fread(P.data(), 12, nv, f) == (size_t)nv;
+        if (ok && hdr[2]) { N.resize(3 * (size_t)nv); ok = fread(N.data(), 12, nv, f) == (size_t)nv; }
+        if (ok && hdr[3]) { uv.resize(2 * (size_t)nv); ok = fread(uv.data(), 8, nv, f) == (size_t)nv; }
+        if (ok) { idx.resize(3 * (size_t)nt); ok = fread(idx.data(), 12, nt, f) == (size_t)nt; }
+        if (ok) InitMesh(m, o2w, false, nv, P.data(), N.empty() ? nullptr : N.data(), uv.empty() ? nullptr : uv.data(), nt, idx.data());
     }
     fclose(f);
     if (!ok) { *err = "short read in mesh " + file; return false; }
-    m->ObjectToWorld = o2w;
-    m->TransformSwapsHandedness = o2w.SwapsHandedness();
     return true;
 }
 
+// ---- pixel filters (filters/*.cpp) ----------------------------------------------------------------------------------
+float PixelFilter::Evaluate(float x, float y) const {
+    const float invX = 1.f / xwidth, invY = 1.f / ywidth;     // core/filter.h:50-52
+    if (name == "box") return 1.f;
+    if (name == "triangle") return std::max(0.f, xwidth - fabsf(x)) * std::max(0.f, ywidth - fabsf(y));
+    if (name == "gaussian") {                                  // filters/gaussian.{h,cpp}
+        float expX = expf(-alpha * xwidth * xwidth), expY = expf(-alpha * ywidth * ywidth);
+        float gx = std::max(0.f, float(expf(-alpha * x * x) - expX)), gy = std::max(0.f, float(expf(-alpha * y * y) - expY));
+        return gx * gy;
+    }
+    if (name == "mitchell") {                                  // filters/mitchell.h:49-58
+        auto m1 = [&](float v) {
+            v = fabsf(2.f * v);
+            if (v > 1.f) return ((-B - 6 * C) * v * v * v + (6 * B + 30 * C) * v * v + (-12 * B - 48 * C) * v + (8 * B + 24 * C)) * (1.f / 6.f);
+            return ((12 - 9 * B - 6 * C) * v * v * v + (-18 + 12 * B + 6 * C) * v * v + (6 - 2 * B)) * (1.f / 6.f);
+        };
+        return m1(x * invX) * m1(y * invY);
+    }
+    // "sinc": filters/sinc.h:49-57 (M_PI is the float literal of core/pbrt.h:193-196)
+    auto s1 = [&](float v) {
+        v = fabsf(v);
+        if (v < 1e-5) return 1.f;
+        if (v > 1.) return 0.f;
+        v *= 3.14159265358979323846f;
+        float sinc = sinf(v) / v;
+        float lanczos = sinf(v * tau) / (v * tau);
+        return sinc * lanczos;
+    };
+    return s1(x * invX) * s1(y * invY);
+}
+void PixelFilter::Table(float out[256]) const {
+    float *ftp = out;
+    for (int y = 0; y < 16; ++y) {
+        float fy = ((float)y + .5f) * ywidth / 16;
+        for (int x = 0; x < 16; ++x) {
+            float fx = ((float)x + .5f) * xwidth / 16;
+            *ftp++ = Evaluate(fx, fy);
+        }
+    }
+}
+
+PerspectiveCameraDesc SceneDesc::Camera() const {
+    PerspectiveCamera cam(InverseT(WorldToCamera), fov, xres, yres, frameAspect, haveScreenWindow ? screenWindow : nullptr);   // api.cpp:862
+    PerspectiveCameraDesc d; d.CameraToWorld = cam.CameraToWorld; d.RasterToCamera = cam.RasterToCamera;
+    return d;
+}
+
+bool SceneDesc::Load(const std::string &path, const LoadOptions *opt) {
+    bool pbrt = path.size() >= 5 && path.compare(path.size() - 5, 5, ".pbrt") == 0;
+    return pbrt ? LoadPbrt(path, opt) : LoadLines(path);
+}
+
 // Line format shared with oracle/refbuild/ref_driver.cpp ("Scene description")
-bool SceneDesc::Load(const std::string &path) {
+bool SceneDesc::LoadLines(const std::string &path) {
     std::ifstream in(path);
     if (!in) { error = "cannot open scene " + path; return false; }
     std::string dir = path.substr(0, path.find_last_of('/') + 1), line;
@@ -218,6 +282,7 @@ bool SceneDesc::Load(const std::string &path) {
             cur = Transform();
         } else { error = "scene: unknown key " + key; return false; }
     }
+    WorldToCamera = Transform() * LookAt(V3(lookat[0], lookat[1], lookat[2]), V3(lookat[3], lookat[4], lookat[5]), V3(lookat[6], lookat[7], lookat[8]));
     return true;
 }
 
@@ -225,20 +290,27 @@ bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *o
     if (sd.meshes.size() != 1) { *err = "the device path takes exactly one skin mesh"; return false; }
     const TriangleMesh &mesh = sd.meshes[0];
     // renderOptions->primitives order: emitter spheres, then the mesh triangles (api.cpp:1066-1070)
+    // (a .pbrt file fixes the order itself: primOrder)
     std::vector<BBox> bounds;
     std::vector<skc_prim> prims;
-    for (size_t i = 0; i < sd.lights.size(); ++i) {
-        bounds.push_back(sd.lights[i].WorldBound());
-        skc_prim p = {1, -1, (int32_t)i, (int32_t)prims.size()};
-        prims.push_back(p);
+    std::vector<PrimRef> order = sd.primOrder;
+    if (order.empty()) {
+        for (size_t i = 0; i < sd.lights.size(); ++i) order.push_back(PrimRef{1, (int)i});
+        order.push_back(PrimRef{0, 0});
     }
-    for (int t = 0; t < mesh.ntris; ++t) {
-        const V3 &p1 = mesh.p[mesh.vertexIndex[3 * t]], &p2 = mesh.p[mesh.vertexIndex[3 * t + 1]], &p3 = mesh.p[mesh.vertexIndex[3 * t + 2]];
-        bounds.push_back(Union(BBox(p1, p2), p3));   // trianglemesh.inl:45-51
-        skc_prim p = {0, 0, t, (int32_t)prims.size()};
-        prims.push_back(p);
+    for (const PrimRef &r : order) {
+        if (r.kind == 1) {
+            bounds.push_back(sd.lights[r.index].WorldBound());
+            skc_prim p = {1, -1, (int32_t)r.index, (int32_t)prims.size()};
+            prims.push_back(p);
+        } else for (int t = 0; t < mesh.ntris; ++t) {
+            const V3 &p1 = mesh.p[mesh.vertexIndex[3 * t]], &p2 = mesh.p[mesh.vertexIndex[3 * t + 1]], &p3 = mesh.p[mesh.vertexIndex[3 * t + 2]];
+            bounds.push_back(Union(BBox(p1, p2), p3));   // trianglemesh.inl:45-51
+            skc_prim p = {0, 0, t, (int32_t)prims.size()};
+            prims.push_back(p);
+        }
     }
-    BVHAccel bvh(bounds, 4, "sah");
+    BVHAccel bvh(bounds, (uint32_t)sd.maxNodePrims, sd.splitMethod);
     out->nodes = bvh.nodes;
     out->prims.clear();
     for (uint32_t pn : bvh.orderedPrims) out->prims.push_back(prims[pn]);

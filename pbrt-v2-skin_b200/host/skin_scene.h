@@ -52,10 +52,41 @@ struct SkinParams {
     float layerThickness[2] = {0.25e6f, 20e6f}, layerIor[2] = {1.4f, 1.4f};
 };
 
+// Pixel filter of Film "image" (filters/{box,gaussian,mitchell,sinc,triangle}.cpp; api.cpp:648-672 default "box")
+struct PixelFilter {
+    std::string name = "box";
+    float xwidth = .5f, ywidth = .5f;
+    float alpha = 2.f, B = 1.f / 3.f, C = 1.f / 3.f, tau = 3.f;
+    float Evaluate(float x, float y) const;
+    void Table(float out256[256]) const;      // ImageFilm ctor, film/image.cpp:55-68
+};
+
+// Command-line options that reach the plugin factories (core/pbrt.h Options, main/pbrt.cpp:76-93)
+struct LoadOptions {
+    bool quickRender = false;       // --quick
+    std::string imageFile;          // --outfile
+};
+
+struct PrimRef { int kind; int index; };      // kind 0 = meshes[index], 1 = lights[index]; order of renderOptions->primitives
+
+struct PerspectiveCameraDesc { Transform CameraToWorld, RasterToCamera; };
+
 struct SceneDesc {
     int xres = 320, yres = 180, spp = 4;
     float lookat[9] = {0, -5, 0, 0, 0, 0, 0, 0, 1};
     float fov = 30.f;
+    // Camera "perspective": world-to-camera = the CTM at the Camera directive (api.cpp:858-864); screen window
+    // (cameras/perspective.cpp:128-147).  The .scene line format sets it from `lookat`.
+    Transform WorldToCamera;
+    bool haveScreenWindow = false;
+    float screenWindow[4] = {-1, 1, -1, 1};
+    float frameAspect = 0.f;        // 0: xres / yres
+    PixelFilter filter;
+    std::string filmFilename;       // Film "image" "string filename" / --outfile; "" -> pbrt.tga (film/image.cpp:222-238 without OpenEXR)
+    std::string splitMethod = "sah";  // Accelerator "bvh" (accelerators/bvh.cpp:549-550)
+    int maxNodePrims = 4;
+    std::vector<PrimRef> primOrder;   // empty: emitters first, then the meshes (the .scene format's order)
+    std::vector<std::string> warnings;
     // SurfaceIntegrator "multipolesubsurface" (multipolesubsurface.cpp:309-316)
     int maxdepth = 5;
     float maxerror = .05f, minsampledistance = .25f, mix = .5f;
@@ -64,7 +95,12 @@ struct SceneDesc {
     SkinParams skin;
     std::vector<TriangleMesh> meshes;
     std::string error;
-    bool Load(const std::string &path);
+    // Load: `.pbrt` files go through the pbrt scene-description front end (skin_pbrt.cpp: the directives and
+    // parameter lists of core/pbrtlex.ll + pbrtparse.yy + api.cpp), anything else is the line format of scenes/*.scene.
+    bool Load(const std::string &path, const LoadOptions *opt = nullptr);
+    bool LoadPbrt(const std::string &path, const LoadOptions *opt);
+    bool LoadLines(const std::string &path);
+    PerspectiveCameraDesc Camera() const;
 };
 
 // accelerators/bvh.{h,cpp}
@@ -86,7 +122,7 @@ private:
 // cameras/perspective.cpp + core/camera.cpp:83-102
 class PerspectiveCamera {
 public:
-    PerspectiveCamera(const Transform &cam2world, float fov, int xres, int yres);
+    PerspectiveCamera(const Transform &cam2world, float fov, int xres, int yres, float frameAspect = 0.f, const float *screenWindow = nullptr);
     void GenerateRay(float imageX, float imageY, skc_ray *ray) const;
     Transform CameraToWorld, RasterToCamera;
 };
@@ -99,6 +135,25 @@ struct BuiltScene {
     const TriangleMesh *mesh = nullptr;       // single skin mesh supported on the device path
 };
 bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *out, std::string *err);
+// TriangleMesh from object-space arrays the way CreateTriangleMeshShape + the TriangleMesh ctor do (shapes/trianglemesh.cpp:55-80,360-420)
+void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, int nverts, const float *P, const float *N, const float *uv,
+              int ntris, const int *indices);
+
+// What api.cpp's MakeCamera / MakeFilm / MakeSampler / MakeRenderer derive from the scene for the device frame pass
+void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d);
+int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin);
+int UploadScene(skc_ctx *ctx, const BuiltScene &b);
+
+// SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,
+// camera pass, film -> RGB [yres][xres][3].  nCores only fixes the task counts that seed the random streams.
+struct RenderStats {
+    double buildSec = 0, materialSec = 0, preprocessSec = 0, renderSec = 0;
+    uint64_t nPoints = 0, nSamples = 0;
+    uint32_t octreeNodes = 0, irradianceTasks = 0, renderTasks = 0;
+};
+bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err);
+// ::WriteImage (core/imageio.cpp:78-104): .pfm / .tga by suffix (no OpenEXR in this build)
+bool WriteImage(const std::string &name, const float *rgb, int w, int h, std::string *err);
 
 // RGB -> SampledSpectrum for an illuminant (core/spectrum.cpp FromRGB, SpectrumType illuminant)
 void RGBIlluminantToSpectrum(const float rgb[3], float out30[30]);

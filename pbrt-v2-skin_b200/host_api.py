@@ -20,7 +20,16 @@ def load_host_library():
     lib = C.CDLL(path)
     vp = C.c_void_p
     lib.skh_load.restype = vp; lib.skh_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    lib.skh_load_opts.restype = vp; lib.skh_load_opts.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_char_p, C.c_int]
     lib.skh_free.restype = None; lib.skh_free.argtypes = [vp]
+    lib.skh_warning_count.restype = C.c_int; lib.skh_warning_count.argtypes = [vp]
+    lib.skh_warning.restype = C.c_char_p; lib.skh_warning.argtypes = [vp, C.c_int]
+    lib.skh_film_filename.restype = C.c_char_p; lib.skh_film_filename.argtypes = [vp]
+    lib.skh_filter.restype = None; lib.skh_filter.argtypes = [vp, vp, vp]
+    lib.skh_accelerator.restype = C.c_int; lib.skh_accelerator.argtypes = [vp, C.c_char_p, C.c_int]
+    lib.skh_light_samples.restype = None; lib.skh_light_samples.argtypes = [vp, vp]
+    lib.skh_pbrt_render.restype = C.c_int
+    lib.skh_pbrt_render.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, vp, vp, vp, C.c_char_p, C.c_int]
     lib.skh_sizes.restype = None; lib.skh_sizes.argtypes = [vp, vp]
     for f in ("skh_nodes", "skh_prims", "skh_lights", "skh_mesh_P", "skh_mesh_N", "skh_mesh_uv", "skh_mesh_idx"):
         getattr(lib, f).restype = vp; getattr(lib, f).argtypes = [vp]
@@ -63,13 +72,17 @@ def skin_spectra(f_mel=0.15, f_eu=1.0, f_blood=0.002, f_ohg=0.3, nmperunit=100e6
 class HostScene:
     """A scene file loaded and built by the C++ host mirror (BVH, world-space mesh, lights)."""
 
-    def __init__(self, path):
+    def __init__(self, path, quick=False, outfile=None):
+        """path: a `.pbrt` scene description (host/skin_pbrt.cpp) or the line format of scenes/*.scene.  quick / outfile are
+        the reference's --quick / --outfile command-line options (they reach the Film, Sampler and light factories)."""
         self.lib = load_host_library()
         self.path = path
-        err = C.create_string_buffer(512)
-        self.h = self.lib.skh_load(path.encode(), err, 512)
+        err = C.create_string_buffer(1024)
+        self.h = self.lib.skh_load_opts(path.encode(), int(bool(quick)), None if outfile is None else outfile.encode(), err, 1024)
         if not self.h:
             raise SkcError(err.value.decode())
+        self.warnings = [self.lib.skh_warning(self.h, i).decode() for i in range(self.lib.skh_warning_count(self.h))]
+        self.film_filename = self.lib.skh_film_filename(self.h).decode()
         sz = np.zeros(10, np.int64)
         self.lib.skh_sizes(self.h, sz.ctypes.data_as(C.c_void_p))
         (self.n_nodes, self.n_prims, self.n_verts, self.n_tris, self.n_lights, has_n, has_uv, self.xres, self.yres, self.spp) = [int(x) for x in sz]
@@ -88,6 +101,22 @@ class HostScene:
         ip = np.zeros(4, np.float32); L.skh_integrator_params(self.h, ip.ctypes.data_as(C.c_void_p))
         self.maxerror, self.minsampledistance, self.mix, self.maxdepth = float(ip[0]), float(ip[1]), float(ip[2]), int(ip[3])
         self.skin = np.zeros(12, np.float32); L.skh_skin_params(self.h, self.skin.ctypes.data_as(C.c_void_p))
+
+    def pixel_filter(self):
+        """(xwidth, ywidth, ImageFilm::filterTable [16][16])"""
+        w = np.zeros(2, np.float32); t = np.zeros(256, np.float32)
+        self.lib.skh_filter(self.h, w.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p))
+        return float(w[0]), float(w[1]), t.reshape(16, 16)
+
+    def accelerator(self):
+        buf = C.create_string_buffer(64)
+        n = self.lib.skh_accelerator(self.h, buf, 64)
+        return buf.value.decode(), int(n)
+
+    def light_samples(self):
+        out = np.zeros(max(1, self.n_lights), np.int32)
+        self.lib.skh_light_samples(self.h, out.ctypes.data_as(C.c_void_p))
+        return out[:self.n_lights]
 
     def close(self):
         if self.h:
@@ -162,3 +191,21 @@ class HostScene:
         if rc:
             raise SkcError(dev.lib.skc_last_error(dev.ctx).decode())
         return hdr, rd
+
+
+def pbrt_render(scene_path, device=0, n_cores=1, quick=False, outfile=None, write_image=False):
+    """`pbrt [--ncores n] [--quick] [--outfile f] scene` through the C++ host (host/skin_render.cpp RenderScene): returns
+    (rgb [yres][xres][3], stats dict).  The image file is written only when write_image is set."""
+    lib = load_host_library()
+    err = C.create_string_buffer(1024)
+    dims = (C.c_int * 2)()
+    of = None if outfile is None else outfile.encode()
+    if lib.skh_pbrt_render(scene_path.encode(), device, n_cores, int(bool(quick)), of, 0, dims, None, None, err, 1024):
+        raise SkcError(err.value.decode())
+    rgb = np.empty((dims[1], dims[0], 3), np.float32)
+    st = np.zeros(7, np.float64)
+    if lib.skh_pbrt_render(scene_path.encode(), device, n_cores, int(bool(quick)), of, int(bool(write_image)), dims,
+                           rgb.ctypes.data_as(C.c_void_p), st.ctypes.data_as(C.c_void_p), err, 1024):
+        raise SkcError(err.value.decode())
+    keys = ("build_s", "material_s", "preprocess_s", "render_s", "points", "samples", "octree_nodes")
+    return rgb, dict(zip(keys, st.tolist()))
