@@ -111,6 +111,7 @@ struct SceneDesc {
     std::vector<Light> lights;
     std::map<std::string, float> skin;
     float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
+    float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};     // "color Kr" / "color Kt" as the skin scenes give them
     struct Xf { std::string kind; float v[4]; };
     struct Mesh { std::vector<Xf> xf; std::string file; };
     std::vector<Mesh> meshes;
@@ -141,6 +142,8 @@ static SceneDesc parseScene(const std::string &path) {
             std::string k;
             while (ls >> k) {
                 if (k == "layers") { for (int i = 0; i < 4; ++i) ls >> sd.layers[i]; }
+                else if (k == "Kr") { for (int i = 0; i < 3; ++i) ls >> sd.Kr[i]; }
+                else if (k == "Kt") { for (int i = 0; i < 3; ++i) ls >> sd.Kt[i]; }
                 else { float v; ls >> v; sd.skin[k] = v; }
             }
         }
@@ -204,8 +207,7 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
                 if (kv.first == "desiredlength") addI(ps, "desiredlength", (int)kv.second);
                 else addF(ps, kv.first.c_str(), kv.second);
             }
-            float one[3] = {1, 1, 1}, zero[3] = {0, 0, 0};
-            ps.AddRGBSpectrum("Kr", one, 3); ps.AddRGBSpectrum("Kt", zero, 3);
+            ps.AddRGBSpectrum("Kr", sd.Kr, 3); ps.AddRGBSpectrum("Kt", sd.Kt, 3);
             SkinLayer sl[2]; sl[0].thickness = sd.layers[0]; sl[0].ior = sd.layers[1];
             sl[1].thickness = sd.layers[2]; sl[1].ior = sd.layers[3];
             ps.AddSkinLayer("layers", sl, 2);

@@ -11,6 +11,8 @@ and packs the exported streams into compressed .npz files:
                   closest hits, per-hit Mo, per-hit subsurface radiance, per-sample radiance
   skin_ld4.npz    scenes/skin_ld4.scene (48x27 film, 4 spp): the LDSampler stream, full Li per sample,
                   the film's image (row N1: the rest of Li, sampler and film on the device)
+  tissue.npz      scenes/tissue.scene (BASELINE.json configs[0] stand-in: 160x90 film, LayeredSkin slab at the material's
+                  defaults): image, octree root, strided irradiance points and per-sample radiance
   mpc_kat.npz     MPC_ComputeDiffusionProfile on the parameter sets of the reference's
                   src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
 
@@ -105,6 +107,34 @@ def frame_golden(name):
     print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("camera_samples", "camera_tasks", "sample_floats")})
 
 
+def tissue_golden(name="tissue"):
+    """BASELINE.json configs[0] stand-in (scenes/tissue.scene = scenes/tissue.pbrt: LayeredSkin slab at the material's
+    defaults incl. the transmission lobe, mesh without normals / uvs): image, octree root and bounds, and every 37th
+    irradiance point / every 29th camera sample's radiance, to keep the fixture small."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import make_slab_mesh
+    g = os.path.join(ROOT, "scenes", "geometry")
+    make_slab_mesh.write(os.path.join(g, "slab.mesh.bin"), os.path.join(g, "slab.pbrt"))
+    scene = os.path.join(ROOT, "scenes", name + ".scene")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        meta = read_meta(os.path.join(d, "meta.txt"))
+        f32 = lambda fn: np.fromfile(os.path.join(d, fn), np.float32)
+        irr = f32("irradiance_points.bin").reshape(-1, 38)
+        L = f32("L.bin").reshape(-1, 30)
+        arrays = dict(
+            meta_keys=np.array(list(meta.keys())), meta_vals=np.array([float(v) for v in meta.values()]),
+            irradiance_stride=np.int64(37), irradiance_points=irr[::37].copy(),
+            octree_bounds=f32("octree_bounds.bin"), octree_root=f32("octree_root.bin"),
+            L_stride=np.int64(29), L=L[::29].copy(), L_sss=f32("L_sss.bin").reshape(-1, 30)[::29].copy(),
+            camera_xy=f32("camera_xy.bin").reshape(-1, 2)[::29].copy(),
+            image=read_pfm(os.path.join(d, "image.pfm")),
+        )
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "bvh_nodes")})
+
+
 # (nLayers, desiredLength, lerpOnThinSlab, resample, stepSize, [(ior, thickness, mua, musp)...])
 # First three: src/multipole/test/test.cpp:84-116 at desiredLength 512 -> here 64/128 to keep
 # the fixture small; the full-size known answers are checked in the GPU-marked tests against
@@ -145,8 +175,8 @@ def mpc_golden():
 
 
 if __name__ == "__main__":
-    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "mpc_kat"]
+    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "mpc_kat"]
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else scene_golden(w)
