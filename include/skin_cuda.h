@@ -201,6 +201,10 @@ int skc_irradiance_resident(skc_ctx *ctx, uint64_t first, uint64_t count, uint32
 int skc_set_camera_rays(skc_ctx *ctx, const skc_ray *rays, uint64_t n);
 int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix,
                              float *L30, uint64_t *counters7);
+/* Scene::Intersect (anyHit = 0; hitsOut = count skc_hit records or NULL) / Scene::IntersectP (anyHit = 1; hitsOut = count
+ * bytes or NULL) over the resident rays [first, first+count): core/scene.h:51-68 -> accelerators/bvh.cpp:388-488.
+ * counters2 (optional) = {slab tests, primitive tests}. */
+int skc_trace_resident(skc_ctx *ctx, uint64_t first, uint64_t count, int anyHit, void *hitsOut, uint64_t *counters2);
 /* Pinned host memory for callers that want full-rate PCIe copies through the host-buffer calls. */
 void *skc_alloc_pinned(uint64_t bytes);
 void skc_free_pinned(void *p);

@@ -626,6 +626,40 @@ extern "C" int skc_set_camera_rays(skc_ctx *ctx, const skc_ray *rays, uint64_t n
     return 0;
 }
 
+// Scene::Intersect / IntersectP alone over the resident rays (BVH microbenchmark of SURVEY.md 8d): anyHit = 0 closest hit
+// (hitsOut: host, count skc_hit records, or NULL), 1 = any hit (hitsOut: host, count bytes, or NULL).  counters2
+// (optional) = {slab tests, primitive tests}.  Device time lands in stage "closest" / "any".
+extern "C" int skc_trace_resident(skc_ctx *ctx, uint64_t first, uint64_t count, int anyHit, void *hitsOut, uint64_t *counters2) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!ctx->resRays) return skc_fail(ctx, "skc_trace_resident: no camera rays set");
+    if (first + count > ctx->resRaysCount) return skc_fail(ctx, "skc_trace_resident: bad range");
+    if (!count) return 0;
+    size_t outBytes = anyHit ? count : count * sizeof(skc_hit);
+    void *dOut = skc_scratch(ctx, 1, outBytes);
+    if (!dOut) return 1;
+    unsigned long long *dCnt = nullptr;
+    if (counters2) {
+        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 8 * sizeof(unsigned long long));
+        if (!dCnt) return 1;
+        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    }
+    skc_stage_begin(ctx);
+    int rc = anyHit ? skc_trace_any_dev(ctx, ctx->resRays + first, count, (uint8_t *)dOut, dCnt)
+                    : skc_trace_closest_dev(ctx, ctx->resRays + first, count, (skc_hit *)dOut, dCnt);
+    if (rc) return 1;
+    skc_stage_end(ctx, anyHit ? 5 : 3);
+    if (hitsOut) SKC_CUDA(cudaMemcpyAsync(hitsOut, dOut, outBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (counters2) {
+        unsigned long long h[2];
+        SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+        counters2[0] = h[0]; counters2[1] = h[1];
+    }
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
 // counters7 (optional): [0] slab tests [1] primitive tests (closest hit), [2] octree nodes classified,
 // [3] leaf points tested, [4] cluster contributions, [5] point contributions, [6] profile-table reads (packet kernel)
 extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix,

@@ -26,7 +26,7 @@ STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "a
 # every symbol include/skin_cuda.h declares
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
            "skc_upload_bvh", "skc_trace_any", "skc_trace_closest", "skc_upload_profile", "skc_upload_lights",
-           "skc_irradiance", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
+           "skc_irradiance", "skc_trace_resident", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
@@ -71,6 +71,7 @@ def load_library():
     lib.skc_upload_profile.restype = i32; lib.skc_upload_profile.argtypes = [vp, vp, vp, u32, vp]
     lib.skc_upload_lights.restype = i32; lib.skc_upload_lights.argtypes = [vp, vp, u32]
     lib.skc_irradiance.restype = i32; lib.skc_irradiance.argtypes = [vp, vp, u64, u64, u64, u32, f32, vp, vp]
+    lib.skc_trace_resident.restype = i32; lib.skc_trace_resident.argtypes = [vp, u64, u64, i32, vp, vp]
     lib.skc_set_irradiance_points.restype = i32; lib.skc_set_irradiance_points.argtypes = [vp, vp, u64]
     lib.skc_irradiance_dev.restype = i32; lib.skc_irradiance_dev.argtypes = [vp, u64, C.POINTER(vp), C.POINTER(vp)]
     lib.skc_build_octree.restype = i32; lib.skc_build_octree.argtypes = [vp, C.POINTER(u32), vp, vp]
@@ -293,6 +294,13 @@ class SkinDevice:
     def set_camera_rays(self, rays):
         rays = _c(rays, np.float32).reshape(-1, 8)
         self._ck(self.lib.skc_set_camera_rays(self.ctx, _ptr(rays), len(rays)))
+
+    def trace_resident(self, first, count, any_hit=False, want_out=False, counters=False):
+        """BVH traversal alone over the resident rays; returns (out or None, counters2 or None)."""
+        out = (np.empty(count, np.uint8) if any_hit else np.empty(count, DT_HIT)) if want_out else None
+        c = np.zeros(2, np.uint64) if counters else None
+        self._ck(self.lib.skc_trace_resident(self.ctx, first, count, int(bool(any_hit)), _ptr(out), _ptr(c)))
+        return out, c
 
     def camera_pass_resident(self, first, count, max_error, mix=0.5, out=None, counters=False):
         c = np.zeros(7, np.uint64) if counters else None
