@@ -41,6 +41,13 @@ int main(int argc, char *argv[]) {
         std::vector<float> rgb;
         skin::RenderStats st = {};
         std::string err;
+        if (sd.rendererName == "tessellatesurfacepoints") {
+            uint64_t n = 0;
+            if (!skin::TessellateSurfacePointsToFile(ctx, sd, &n, &err)) { fprintf(stderr, "Error: %s: %s\n", f.c_str(), err.c_str()); rc = 1; continue; }
+            if (!quiet) printf("Obtained %llu surface points%s%s\n", (unsigned long long)n, sd.rendererFilename.empty() ? ". (Not writing to file)" : ", writing to file ",
+                               sd.rendererFilename.c_str());
+            continue;
+        }
         if (!skin::RenderScene(ctx, sd, nCores, &rgb, &st, &err)) { fprintf(stderr, "Error: %s: %s\n", f.c_str(), err.c_str()); rc = 1; continue; }
         std::string name = sd.filmFilename.empty() ? "pbrt.tga" : sd.filmFilename;
         if (!skin::WriteImage(name, rgb.data(), sd.xres, sd.yres, &err)) { fprintf(stderr, "Error: %s\n", err.c_str()); rc = 1; continue; }

@@ -108,6 +108,7 @@ private:
     bool numArray(std::vector<float> *v, const char *what);
     void reportUnused(const ParamSet &ps, const char *what);
     bool include(const std::string &name);
+    std::string resolve(const std::string &name) const;       // ParamSet::FindOneFilename -> AbsolutePath(ResolveFilename()), core/fileutil.cpp:51-73
     bool statement(const std::string &id);
     void shape(const std::string &name, const ParamSet &ps);
     bool skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, SkinParams *out);
@@ -308,12 +309,17 @@ void Front::reportUnused(const ParamSet &ps, const char *what) {   // ParamSet::
         if (!p.lookedUp) Warn("Parameter \"%s\" not used (%s)", p.name.c_str(), what);
 }
 
-bool Front::include(const std::string &name) {
-    if (stack.size() > 32) { Error("Only 32 levels of nested Include allowed in scene files."); return false; }
+std::string Front::resolve(const std::string &name) const {
     // ResolveFilename (core/fileutil.cpp:61-73): relative names live beside the scene file given on the command line
     std::string f = name;
     for (char &c : f) if (c == '\\') c = '/';
     if (!isAbsolute(f)) f = searchDirectory + f;
+    return f;
+}
+
+bool Front::include(const std::string &name) {
+    if (stack.size() > 32) { Error("Only 32 levels of nested Include allowed in scene files."); return false; }
+    std::string f = resolve(name);
     Source s;
     s.file = f;
     if (!readFile(f, &s.text)) { Error("Unable to open included scene file \"%s\"", f.c_str()); return false; }
@@ -534,7 +540,8 @@ bool Front::statement(const std::string &id) {
         sd->minsampledistance = ps.FindOneFloat("minsampledistance", .25f);
         sd->mix = ps.FindOneFloat("mix", .5f);
         sd->incenter = ps.FindOneBool("incenter", false);
-        if (!ps.FindOneString("pointsfile", "").empty()) { Error("multipolesubsurface \"pointsfile\" is not supported on the device path (points come from the tessellator)"); return false; }
+        sd->pointsFile = ps.FindOneString("pointsfile", "");
+        if (!sd->pointsFile.empty()) sd->pointsFile = resolve(sd->pointsFile);
         if (ps.FindOneBool("showirradiancepoints", false)) { Error("multipolesubsurface \"showirradiancepoints\" is not supported on the device path"); return false; }
         if (ps.FindOneBool("usepoissonpointfinder", false)) { Error("multipolesubsurface \"usepoissonpointfinder\" is not supported on the device path (tessellated surface points only)"); return false; }
         if (options.quickRender) { /* the reference's integrator has no quick-render branch */ }
@@ -549,8 +556,19 @@ bool Front::statement(const std::string &id) {
     }
     if (id == "Renderer") {
         if (!named("Renderer") || !needOptions("Renderer")) return false;
-        if (name != "sampler") { Error("Renderer \"%s\": only \"sampler\" is supported on the device path", name.c_str()); return false; }
+        if (name == "tessellatesurfacepoints") {              // CreateTessellateSurfacePointsRenderer, renderers/surfacepoints.cpp:381-388
+            sd->rendererName = name;
+            sd->rendererMinDist = ps.FindOneFloat("minsampledistance", .25f);
+            sd->rendererFilename = ps.FindOneString("filename", "");
+            if (!sd->rendererFilename.empty()) sd->rendererFilename = resolve(sd->rendererFilename);
+            if (options.quickRender) sd->rendererMinDist *= 4.f;
+            haveIntegrator = true;                            // this renderer never calls the surface integrator
+            reportUnused(ps, "Renderer");
+            return true;
+        }
+        if (name != "sampler") { Error("Renderer \"%s\": only \"sampler\" and \"tessellatesurfacepoints\" are supported on the device path", name.c_str()); return false; }
         if (ps.FindOneBool("visualizeobjectids", false)) { Error("Renderer \"visualizeobjectids\" is not supported on the device path"); return false; }
+        sd->rendererName = name;
         return true;
     }
     if (id == "Accelerator") {

@@ -77,6 +77,21 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
     // Preprocess
     uint64_t nPts = 0;
     if (!sd.lights.empty()) {                                                // multipolesubsurface.cpp:173
+        std::vector<skc_surface_point> filePts;
+        if (!sd.pointsFile.empty()) {                                        // :176-181, ReadBinaryFile (core/floatfile.h:45-63)
+            FILE *f = fopen(sd.pointsFile.c_str(), "rb");
+            if (!f) fprintf(stderr, "Error: Unable to open file \"%s\"\n", sd.pointsFile.c_str());
+            else {
+                fseek(f, 0, SEEK_END); long size = ftell(f); fseek(f, 0, SEEK_SET);
+                filePts.resize((size_t)size / sizeof(skc_surface_point));
+                if (!filePts.empty() && fread(filePts.data(), sizeof(skc_surface_point), filePts.size(), f) != filePts.size()) filePts.clear();
+                fclose(f);
+            }
+        }
+        if (!filePts.empty()) {
+            nPts = filePts.size();
+            if (!dev(skc_set_surface_points(ctx, filePts.data(), nPts))) return false;
+        } else                                                               // pts.size() == 0 -> tessellate (:182-190)
         if (!dev(skc_tessellate_resident(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, &nPts))) return false;
         st->irradianceTasks = RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPts / 4096));   // :194-199
         if (!dev(skc_irradiance_resident(ctx, 0, nPts, st->irradianceTasks, sd.mix, nullptr))) return false;
@@ -98,6 +113,23 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
     st->buildSec = t1 - t0; st->materialSec = t2 - t1; st->preprocessSec = t3 - t2; st->renderSec = t4 - t3;
     st->nPoints = nPts; st->nSamples = nSamples; st->renderTasks = (uint32_t)fd.nTasks;
     return true;
+}
+
+bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *nPoints, std::string *err) {
+    BuiltScene built;
+    if (!BuildScene(sd, nullptr, &built, err)) return false;
+    uint64_t n = 0;
+    if (UploadScene(ctx, built) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
+    *nPoints = n;
+    if (sd.rendererFilename.empty()) return true;                            // "(Not writing to file)"
+    std::vector<skc_surface_point> pts(n);
+    if (n && skc_get_surface_points(ctx, 0, n, pts.data())) { *err = skc_last_error(ctx); return false; }
+    FILE *f = fopen(sd.rendererFilename.c_str(), "wb");
+    if (!f) { *err = "Unable to open output file \"" + sd.rendererFilename + "\""; return false; }
+    bool ok = fwrite(pts.data(), sizeof(skc_surface_point), pts.size(), f) == pts.size();
+    fclose(f);
+    if (!ok) *err = "short write to \"" + sd.rendererFilename + "\"";
+    return ok;
 }
 
 // WriteImageTGA (core/imageio.cpp:185-215): 24-bit BGR, gamma 2.2, top row first
@@ -153,6 +185,14 @@ int skh_pbrt_render(const char *scenePath, int device, int nCores, int quick, co
     if (!rgbOut && !writeImage) return 0;
     skc_ctx *ctx = skc_create(device);
     if (!ctx) return fail(std::string("skc_create: ") + skc_last_error(nullptr));
+    if (sd.rendererName == "tessellatesurfacepoints") {
+        uint64_t n = 0;
+        std::string e;
+        bool ok = TessellateSurfacePointsToFile(ctx, sd, &n, &e);
+        skc_destroy(ctx);
+        if (stats7) stats7[4] = (double)n;
+        return ok ? 0 : fail(e);
+    }
     std::vector<float> rgb;
     RenderStats st;
     std::string err;

@@ -91,6 +91,12 @@ struct SceneDesc {
     int maxdepth = 5;
     float maxerror = .05f, minsampledistance = .25f, mix = .5f;
     bool incenter = false;
+    std::string pointsFile;           // "string pointsfile": raw SurfacePoint[44 B] records (multipolesubsurface.cpp:176-181, core/floatfile.h:45-63)
+    // Renderer: "sampler" renders the frame; "tessellatesurfacepoints" only writes the surface points of the scene's
+    // translucent meshes to "string filename" (renderers/surfacepoints.cpp:335-347,381-388) -- the file `pointsfile` reads
+    std::string rendererName = "sampler";
+    float rendererMinDist = .25f;
+    std::string rendererFilename;
     std::vector<SphereLight> lights;
     SkinParams skin;
     std::vector<TriangleMesh> meshes;
@@ -152,6 +158,8 @@ struct RenderStats {
     uint32_t octreeNodes = 0, irradianceTasks = 0, renderTasks = 0;
 };
 bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err);
+// Renderer "tessellatesurfacepoints" (renderers/surfacepoints.cpp:300-347): device tessellation -> raw SurfacePoint file
+bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *nPoints, std::string *err);
 // ::WriteImage (core/imageio.cpp:78-104): .pfm / .tga by suffix (no OpenEXR in this build)
 bool WriteImage(const std::string &name, const float *rgb, int w, int h, std::string *err);
 

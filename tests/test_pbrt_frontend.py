@@ -148,6 +148,8 @@ def test_shape_parameters_override_material_parameters(pkg, tmp_path):
     (scene_text(""), "multipolesubsurface"),
     (scene_text(world='LightSource "point"\n' + TRI % ("", "")), 'LightSource "point"'),
     (scene_text(mat='"texture albedo" "tex"'), "texture albedo"),
+    (scene_text('SurfaceIntegrator "multipolesubsurface" "bool usepoissonpointfinder" "true"'), "usepoissonpointfinder"),
+    (scene_text('Renderer "metropolis"\nSurfaceIntegrator "multipolesubsurface"'), 'Renderer "metropolis"'),
     (scene_text(world=LIGHT + 'Shape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]'), 'Material "matte"'),
     (scene_text(world=LIGHT + 'Material "layeredskin"\nShape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]'), "No layers"),
     (scene_text(world=LIGHT + TRI % ("", "") + 'Shape "cylinder"'), 'Shape "cylinder"'),
@@ -217,3 +219,31 @@ def _no_filename(tmp_path):
     p = tmp_path / "nofile.pbrt"
     p.write_text(src)
     return p
+
+
+@pytest.mark.gpu
+def test_tessellatesurfacepoints_renderer_and_pointsfile(pkg, head_pbrt, tmp_path):
+    """`Renderer "tessellatesurfacepoints" "string filename"` writes the raw SurfacePoint[44 B] file the reference writes
+    (renderers/surfacepoints.cpp:335-347) -- byte for byte the reference's own points (tests/golden/skin_tiny.npz, same mesh and
+    minsampledistance) -- and `"string pointsfile"` renders from it (multipolesubsurface.cpp:176-181) to the same image."""
+    exe = os.path.join(ROOT, "pbrt-v2-skin_b200", "pbrt")
+    src = open(os.path.join(ROOT, "scenes", "skin_ld4.pbrt")).read()
+    src = src.replace('Include "geometry/head.pbrt"', 'Include "%s"' % head_pbrt)
+    a = src.replace('SurfaceIntegrator "multipolesubsurface"', 'Renderer "tessellatesurfacepoints" "float minsampledistance" 0.1 "string filename" "pts.bin"\nSurfaceIntegrator "multipolesubsurface"')
+    (tmp_path / "points.pbrt").write_text(a)
+    r = subprocess.run([exe, str(tmp_path / "points.pbrt")], cwd=str(tmp_path), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    raw = np.fromfile(tmp_path / "pts.bin", np.uint8)       # "filename" resolves beside the scene file (core/fileutil.cpp:61-73)
+    ref = np.load(os.path.join(ROOT, "tests", "golden", "skin_tiny.npz"))["surface_points"]
+    assert "Obtained %d surface points" % (len(ref) // 44) in r.stdout
+    assert np.array_equal(raw, ref)
+    b = src.replace('"float minsampledistance" 0.1', '"float minsampledistance" 0.1 "string pointsfile" "pts.bin"').replace("skin_ld4.pfm", "from_file.pfm")
+    (tmp_path / "fromfile.pbrt").write_text(b)
+    img_file, st = pkg.pbrt_render(str(tmp_path / "fromfile.pbrt"), n_cores=1)
+    img_tess, _ = pkg.pbrt_render(os.path.join(ROOT, "scenes", "skin_ld4.pbrt"), n_cores=1)
+    assert st["points"] == len(ref) // 44
+    assert np.allclose(img_file, img_tess, rtol=1e-5, atol=1e-6 * img_tess.max())
+    # a missing points file falls back to the tessellator, as pts.size() == 0 does in the reference (:182-190)
+    (tmp_path / "missing.pbrt").write_text(b.replace('"pts.bin"', '"nothere.bin"'))
+    img_missing, _ = pkg.pbrt_render(str(tmp_path / "missing.pbrt"), n_cores=1)
+    assert np.allclose(img_missing, img_tess, rtol=1e-5, atol=1e-6 * img_tess.max())
