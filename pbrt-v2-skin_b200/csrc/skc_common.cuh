@@ -73,6 +73,7 @@ struct skc_ctx {
     std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize
     bool otTopologyReady = false;
     int moSplit = 0;         // warps per Mo packet (each sums 1/moSplit of the spectrum): 0 = by launch size; env SKC_MO_SPLIT=1|2
+    int moSort = -1;         // spatial sort of the hit points before the packet kernel: -1 = where the caller fixes the order (skc_mo, skc_li_sss, skc_camera_pass*), 0 never, 1 also in the frame path; env SKC_MO_SORT
     int moPacket = 1;        // Mo kernel: 1 = packet (lane = hit), 0 = warp per hit (lane = wavelength); env SKC_MO_KERNEL=warp|packet
     uint64_t otPoints = 0;
     float otBoundsHost[6];
@@ -84,8 +85,8 @@ struct skc_ctx {
     uint64_t resRaysCount = 0;
 
     // --- scratch
-    void *scratch[16] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently), 11 tessellation, 12-15 frame
-    size_t scratchBytes[16] = {0};
+    void *scratch[20] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently), 11 tessellation, 12-15 frame, 16 Mo hit sort
+    size_t scratchBytes[20] = {0};
 
     // --- whole-frame state (skc_frame.cu)
     struct skc_frame_state *frame = nullptr;

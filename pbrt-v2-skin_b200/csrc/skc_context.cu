@@ -69,6 +69,7 @@ extern "C" skc_ctx *skc_create(int device) {
         return nullptr;
     }
     if (const char *k = getenv("SKC_MO_KERNEL")) ctx->moPacket = strcmp(k, "warp") != 0;
+    if (const char *k = getenv("SKC_MO_SORT")) ctx->moSort = atoi(k);
     if (const char *k = getenv("SKC_MO_SPLIT")) ctx->moSplit = atoi(k) == 1 ? 1 : atoi(k) == 2 ? 2 : 0;
     return ctx;
 }
@@ -82,7 +83,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
                     ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
-    for (int i = 0; i < 16; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (int i = 0; i < 20; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     cudaStreamSynchronize(ctx->copyStream);

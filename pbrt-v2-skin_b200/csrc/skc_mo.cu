@@ -19,6 +19,7 @@
 // skipped, and so are subtrees whose box lies entirely beyond it.
 #include <algorithm>
 #include <vector>
+#include <cub/cub.cuh>
 #include "skc_internal.h"
 
 // Launch shape: a CTA of MO_WARPS warps works through a CONTIGUOUS run of MO_WARPS*MO_HITS_PER_WARP
@@ -230,11 +231,11 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
 // time -- the heaviest packets of a frame otherwise run 15-25 ms (each warp owns 1/28 of its SM's gather pipe) and
 // set the length of every launch that has few packets per warp (multi-GPU shards) -- and 16 accumulators instead of
 // 30 leave room for more resident warps.
-template <bool COUNT, int SPLIT>
+template <bool COUNT, int SPLIT, bool PERM>
 __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                              uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
-                                                             uint32_t *__restrict__ nextPacket) {
+                                                             uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm) {
     __shared__ uint2 stacks[MOP_WARPS][MOP_STACK];
     __shared__ float sRcp[32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -254,10 +255,12 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packe
     if (packet >= nTickets) break;
     const int part = SPLIT == 1 ? 0 : (int)(packet % SPLIT), q0 = part * NQ;
     packet /= SPLIT;
+    // perm (optional): packet position -> index of the hit in the caller's arrays (hits sorted along a space-filling curve, moLaunch)
     uint64_t h0 = (uint64_t)packet * 32, h = h0 + lane;
-    bool on = h < n && (enable ? (__ldg(&enable[h * enableStrideInts]) != 0) : true);
+    const uint32_t src = (PERM && h < n) ? __ldg(&perm[h]) : (uint32_t)h;      // n < 2^32 (checked at launch)
+    bool on = h < n && (enable ? (__ldg(&enable[(uint64_t)src * enableStrideInts]) != 0) : true);
     float px = 0.f, py = 0.f, pz = 0.f;
-    if (on) { const float *pp = p3 + h * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
+    if (on) { const float *pp = p3 + (uint64_t)src * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
     float acc[4 * NQ];
 #pragma unroll
     for (int w = 0; w < 4 * NQ; ++w) acc[w] = 0.f;
@@ -334,6 +337,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packe
         for (int r = 0; r < 16; ++r) {
             uint64_t hh = h0 + 16 * half + r;
             if (hh >= n) break;
+            if (PERM) hh = (uint64_t)__shfl_sync(0xffffffffu, src, 16 * half + r);
             float mo = tile[r * 33 + lane];
             if (Mo) Mo[hh * SKC_EPAD + lane] = mo;
             if (li.L) {
@@ -352,8 +356,8 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packe
         const int wl = 4 * q0 + (lane % NW);
         for (int r = 0; r < 32; r += 32 / NW) {
             int rr = r + lane / NW;
-            uint64_t hh = h0 + rr;
-            if (hh < n) {
+            uint64_t hh = PERM ? (uint64_t)__shfl_sync(0xffffffffu, src, rr) : h0 + rr;
+            if (h0 + rr < n) {
                 float mo = tile[rr * (NW + 1) + (lane % NW)];
                 if (Mo) Mo[hh * SKC_EPAD + wl] = mo;
                 if (li.L) {
@@ -437,14 +441,56 @@ extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float 
     return 0;
 }
 
+// Hit points -> 30-bit Morton keys over the octree's bounds (10 bits per axis); hits that carry no BSSRDF sort last.
+__global__ void __launch_bounds__(256) k_mo_sort_keys(const float *__restrict__ p3, uint64_t strideFloats, const int32_t *__restrict__ enable,
+                                                      uint64_t enableStrideInts, uint32_t n, float3 bmin, float3 scale,
+                                                      uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    uint32_t key = 0x40000000u;
+    if (!enable || __ldg(&enable[(uint64_t)i * enableStrideInts]) != 0) {
+        const float *pp = p3 + (uint64_t)i * strideFloats;
+        auto cell = [](float v) { return (uint32_t)fminf(fmaxf(v, 0.f), 1023.f); };
+        auto spread = [](uint32_t x) { x = (x | (x << 16)) & 0x030000FFu; x = (x | (x << 8)) & 0x0300F00Fu; x = (x | (x << 4)) & 0x030C30C3u; return (x | (x << 2)) & 0x09249249u; };
+        key = spread(cell((__ldg(pp) - bmin.x) * scale.x)) | (spread(cell((__ldg(pp + 1) - bmin.y) * scale.y)) << 1) | (spread(cell((__ldg(pp + 2) - bmin.z) * scale.z)) << 2);
+    }
+    keys[i] = key; vals[i] = i;
+}
+
+// The packet kernel walks the octree once for 32 hit points, so it wants neighbouring points in a packet.  The frame path
+// renders its samples along a Z-curve over the film; callers of skc_mo / skc_li_sss / skc_camera_pass* own the order of
+// their points, so those are sorted here along a Morton curve through the octree's bounds (one 32-bit radix sort) and the
+// kernel reads and writes through the permutation -- results land at the caller's indices, bit-identical to the unsorted run.
+static const uint32_t *moSortHits(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride, uint64_t n) {
+    if (n < 64 || n >= (1ull << 31)) return nullptr;
+    size_t tempBytes = 0;
+    cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, dk, dv, (int)n, 0, 31, ctx->stream);
+    size_t arr = ((size_t)n * 4 + 255) & ~(size_t)255;
+    char *buf = (char *)skc_scratch(ctx, 16, 4 * arr + tempBytes);
+    if (!buf) return nullptr;
+    dk = cub::DoubleBuffer<uint32_t>((uint32_t *)buf, (uint32_t *)(buf + arr));
+    dv = cub::DoubleBuffer<uint32_t>((uint32_t *)(buf + 2 * arr), (uint32_t *)(buf + 3 * arr));
+    const float *b = ctx->otBoundsHost;
+    float3 bmin = make_float3(b[0], b[1], b[2]);
+    auto sc = [](float lo, float hi) { return hi > lo ? 1024.f / (hi - lo) : 0.f; };
+    float3 scale = make_float3(sc(b[0], b[3]), sc(b[1], b[4]), sc(b[2], b[5]));
+    k_mo_sort_keys<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(p3Dev, strideFloats, enableDev, enableStride, (uint32_t)n, bmin, scale, dk.Current(), dv.Current());
+    ctx->launches += 2;
+    if (cudaGetLastError() != cudaSuccess || cub::DeviceRadixSort::SortPairs(buf + 4 * arr, tempBytes, dk, dv, (int)n, 0, 31, ctx->stream) != cudaSuccess) return nullptr;
+    return dv.Current();
+}
+
 static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride,
-                    uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr, const LiEpilogue *li = nullptr) {
+                    uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr, const LiEpilogue *li = nullptr,
+                    bool callerOrder = true) {
     if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo: no octree built (skc_build_octree)");
     if (!ctx->profPairs) return skc_fail(ctx, "skc_mo: no profile table uploaded (skc_upload_profile)");
     if (!n) return 0;
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
     if (ctx->moPacket) {
+        if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
         if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
         uint64_t pb = (n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32);
         if (pb > (uint64_t)ctx->smCount * 7) pb = (uint64_t)ctx->smCount * 7;       // persistent: at most the resident CTAs
@@ -452,18 +498,16 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
         if (!next) return 1;
         SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
+        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n) : nullptr;
         // one warp per packet when there are plenty of packets per resident warp; two warps per packet (half the spectrum each)
         // when a launch is short (multi-GPU shards), where the heaviest packets' run time is what the launch waits for.
         // Measured on skin.scene: 28 packets/warp 60.4 vs 61.9 ms, 14 packets/warp 38.1 vs 35.7 ms, 3.5 packets/warp 23.0 vs 17.5 ms
         int split = ctx->moSplit ? ctx->moSplit : ((n + 31) / 32 >= 20ull * ctx->smCount * 7 * MOP_WARPS ? 1 : 2);
-        if (split == 2) {
-            pb = std::min<uint64_t>(2 * ((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32)), (uint64_t)ctx->smCount * 8);
-            if (cntDev) k_mo_packet<true, 2><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
-            else k_mo_packet<false, 2><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
-        } else {
-            if (cntDev) k_mo_packet<true, 1><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next);
-            else k_mo_packet<false, 1><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, nullptr, ep, next);
-        }
+        if (split == 2) pb = std::min<uint64_t>(2 * ((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32)), (uint64_t)ctx->smCount * 8);
+#define MOP_GO(C, S, P) k_mo_packet<C, S, P><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm)
+        if (split == 2) { if (cntDev) { if (perm) MOP_GO(true, 2, true); else MOP_GO(true, 2, false); } else { if (perm) MOP_GO(false, 2, true); else MOP_GO(false, 2, false); } }
+        else            { if (cntDev) { if (perm) MOP_GO(true, 1, true); else MOP_GO(true, 1, false); } else { if (perm) MOP_GO(false, 1, true); else MOP_GO(false, 1, false); } }
+#undef MOP_GO
         SKC_LAUNCHED("k_mo_packet");
         return 0;
     }
@@ -542,12 +586,13 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
     return 0;
 }
 
+// (the frame path: its samples already follow a Z-curve over the film)
 int skc_li_fused_dev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, float *dL) {
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_li: no rho table uploaded (skc_upload_profile)");
     if (!ctx->moPacket) return skc_fail(ctx, "skc_li: the fused Li epilogue needs the packet kernel");
     LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL};
     skc_stage_begin(ctx);
-    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep)) return 1;
+    if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep, false)) return 1;
     skc_stage_end(ctx, 4);
     return 0;
 }

@@ -446,6 +446,38 @@ def test_mo_packet_one_and_two_warps_per_packet_agree(pkg, tiny):
     assert out[0].max() > 0
 
 
+def test_mo_hit_sort_is_invisible_to_the_caller(pkg, tiny):
+    """skc_mo / skc_camera_pass sort the caller's hit points along a Morton curve before forming packets (incoherent point
+    sets otherwise walk the union of 32 unrelated paths per packet).  The kernel reads and writes through the permutation:
+    every row lands at the caller's index, bit-identical to the unsorted run, for shuffled points and for camera rays with
+    misses among them; the frame path (SKC_MO_SORT=1 forces the sort there too) is unchanged as well."""
+    g = tiny
+    rng = np.random.RandomState(3)
+    pts = g.hits["p"][g.hits["hasBssrdf"] == 1]
+    pts = np.ascontiguousarray(pts[rng.permutation(len(pts))])
+    rays = np.ascontiguousarray(g.camera_rays[rng.permutation(len(g.camera_rays))])
+    out = []
+    for mode in ("0", "-1", "1"):
+        os.environ["SKC_MO_SORT"] = mode
+        try:
+            d = pkg.SkinDevice(0)
+        finally:
+            del os.environ["SKC_MO_SORT"]
+        try:
+            gu.setup_device(d, g)
+            d.set_irradiance_points(g.irradiance_points)
+            d.build_octree()
+            mo = d.mo(pts, g.max_error)
+            L, hits = d.camera_pass(rays, g.max_error, g.mix, want_hits=True)
+            out.append((mo.copy(), L.copy()))
+        finally:
+            d.close()
+    assert out[0][0].max() > 0 and (hits["hit"] == 0).any() and (hits["hasBssrdf"] == 1).any()
+    for k in (1, 2):
+        assert np.array_equal(out[0][0].view(np.uint32), out[k][0].view(np.uint32))
+        assert np.array_equal(out[0][1].view(np.uint32), out[k][1].view(np.uint32))
+
+
 def test_device_tessellation_of_a_shard(pkg, dev):
     """skc_tessellate_range: a rank's shard of the surface points, rounded out to whole triangles, nothing else written."""
     hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tiny.scene"))
