@@ -47,6 +47,9 @@
 #include "shapes/trianglemesh.h"
 #include "shapes/sphere.h"
 #include "lights/diffuse.h"
+#include "lights/point.h"
+#include "lights/spot.h"
+#include "lights/distant.h"
 #include "core/multipole.h"
 #include "core/reflection.h"
 #include "core/film.h"
@@ -107,7 +110,7 @@ struct SceneDesc {
     float lookat[9] = {0, -5, 0, 0, 0, 0, 0, 0, 1};
     float fov = 30.f;
     std::map<std::string, float> integ;
-    struct Light { float t[3], radius, L[3]; int ns; };
+    struct Light { float t[3], radius, L[3]; int ns; int kind = 0; float to[3] = {0, 0, 1}, cone = 30.f, delta = 5.f; };   // kind 0 sphere area, 1 point, 2 spot, 3 distant
     std::vector<Light> lights;
     std::map<std::string, float> skin;
     float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
@@ -136,6 +139,16 @@ static SceneDesc parseScene(const std::string &path) {
         else if (key == "light") {
             SceneDesc::Light l;
             ls >> l.t[0] >> l.t[1] >> l.t[2] >> l.radius >> l.L[0] >> l.L[1] >> l.L[2] >> l.ns;
+            sd.lights.push_back(l);
+        }
+        else if (key == "pointlight" || key == "spotlight" || key == "distantlight") {
+            // pointlight fx fy fz r g b | spotlight fx fy fz tx ty tz r g b coneangle conedeltaangle | distantlight fx fy fz tx ty tz r g b
+            SceneDesc::Light l; l.radius = 0.f; l.ns = 1;
+            l.kind = key == "pointlight" ? 1 : key == "spotlight" ? 2 : 3;
+            ls >> l.t[0] >> l.t[1] >> l.t[2];
+            if (l.kind != 1) ls >> l.to[0] >> l.to[1] >> l.to[2];
+            ls >> l.L[0] >> l.L[1] >> l.L[2];
+            if (l.kind == 2) ls >> l.cone >> l.delta;
             sd.lights.push_back(l);
         }
         else if (key == "skin") {
@@ -189,6 +202,17 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
     pbrtWorldBegin();
     for (auto &l : sd.lights) {
         pbrtAttributeBegin();
+        if (l.kind != 0) {
+            ParamSet ps;
+            Point from(l.t[0], l.t[1], l.t[2]), to(l.to[0], l.to[1], l.to[2]);
+            ps.AddRGBSpectrum(l.kind == 3 ? "L" : "I", l.L, 3);
+            ps.AddPoint("from", &from, 1);
+            if (l.kind != 1) ps.AddPoint("to", &to, 1);
+            if (l.kind == 2) { addF(ps, "coneangle", l.cone); addF(ps, "conedeltaangle", l.delta); }
+            pbrtLightSource(l.kind == 1 ? "point" : l.kind == 2 ? "spot" : "distant", ps);
+            pbrtAttributeEnd();
+            continue;
+        }
         { ParamSet ps; ps.AddRGBSpectrum("L", l.L, 3); addI(ps, "nsamples", l.ns); pbrtAreaLightSource("area", ps); }
         pbrtTranslate(l.t[0], l.t[1], l.t[2]);
         { ParamSet ps; addF(ps, "radius", l.radius); pbrtShape("sphere", ps); }
@@ -260,6 +284,14 @@ static void dumpSpectrumConsts(const std::string &dir) {
     float one[3] = {1.f, 1.f, 1.f};
     Spectrum w = Spectrum::FromRGB(one);
     dump(dir + "/rgb_unit30.bin", w.c, nSpectralSamples);
+    // the binned basis spectra FromRGB(.., SPECTRUM_REFLECTANCE) mixes (SampledSpectrum::Init, core/spectrum.cpp): data for
+    // pbrt-v2-skin_b200/host/skin_tables.h kRGBRefl2Spect30 (white, cyan, magenta, yellow, red, green, blue)
+    std::vector<float> bases;
+    const SampledSpectrum *bs[7] = {&SampledSpectrum::rgbRefl2SpectWhite, &SampledSpectrum::rgbRefl2SpectCyan, &SampledSpectrum::rgbRefl2SpectMagenta,
+                                    &SampledSpectrum::rgbRefl2SpectYellow, &SampledSpectrum::rgbRefl2SpectRed, &SampledSpectrum::rgbRefl2SpectGreen,
+                                    &SampledSpectrum::rgbRefl2SpectBlue};
+    for (int k = 0; k < 7; ++k) for (int i = 0; i < nSpectralSamples; ++i) bases.push_back(bs[k]->c[i]);
+    dump(dir + "/rgb_refl_bases30.bin", bases.data(), bases.size());
 }
 
 static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
@@ -362,6 +394,25 @@ static void dumpLights(const std::string &dir, const Scene *scene, Meta &meta) {
     // Per light: o2w(16) w2o(16) radius zmin zmax phiMax nSamples reverse Lemit[30]
     std::vector<float> out;
     for (const Light *l : scene->lights) {
+        // delta lights in the record convention of include/skin_cuda.h: radius -1 / -2 / -3, LightToWorld, cone cosines or direction
+        if (const PointLight *pl = dynamic_cast<const PointLight *>(l)) {
+            dumpTransform(out, pl->LightToWorld);
+            float r[8] = {-1.f, 0, 0, 0, 1.f, 0, 0, 0}; out.insert(out.end(), r, r + 8);
+            for (int i = 0; i < nSpectralSamples; ++i) out.push_back(pl->Intensity.c[i]);
+            continue;
+        }
+        if (const SpotLight *sl = dynamic_cast<const SpotLight *>(l)) {
+            dumpTransform(out, sl->LightToWorld);
+            float r[8] = {-2.f, sl->cosTotalWidth, sl->cosFalloffStart, 0, 1.f, 0, 0, 0}; out.insert(out.end(), r, r + 8);
+            for (int i = 0; i < nSpectralSamples; ++i) out.push_back(sl->Intensity.c[i]);
+            continue;
+        }
+        if (const DistantLight *dd = dynamic_cast<const DistantLight *>(l)) {
+            dumpTransform(out, dd->LightToWorld);
+            float r[8] = {-3.f, dd->lightDir.x, dd->lightDir.y, dd->lightDir.z, 1.f, 0, 0, 0}; out.insert(out.end(), r, r + 8);
+            for (int i = 0; i < nSpectralSamples; ++i) out.push_back(dd->L.c[i]);
+            continue;
+        }
         const DiffuseAreaLight *dl = dynamic_cast<const DiffuseAreaLight *>(l);
         if (!dl || dl->shapeSet->shapes.size() != 1) { fprintf(stderr, "unsupported light\n"); exit(2); }
         const Sphere *sp = dynamic_cast<const Sphere *>(dl->shapeSet->shapes[0].GetPtr());

@@ -372,6 +372,19 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
         float lu0 = __ldg(A + lay.off2L[li] + 2 * j), lu1 = __ldg(A + lay.off2L[li] + 2 * j + 1);
         float bc = __ldg(A + lay.off1B[li] + j), bu0 = __ldg(A + lay.off2B[li] + 2 * j), bu1 = __ldg(A + lay.off2B[li] + 2 * j + 1);
         const skc_light &L = lights[li];
+        const int kind = lightKind(L);
+        if (kind != 0) {
+            // delta light (integrator.cpp:114-126): Ld += f * Li * (AbsDot(wi, n) / lightPdf), lightPdf = 1, and no BSDF-sampling
+            // term (:134).  T1.y / T1.z carry DistanceSquared and the spot falloff: Li = (I * falloff) / d2 in k_frame_sum.
+            f3 wi; float d2, fall; DRay sh;
+            if (sampleDeltaLight(L, kind, p, eps, &wi, &d2, &fall, &sh) && d2 != 0.f) {
+                float4 comp;
+                float f = bsdfF(B, wo, wi, &comp);
+                if (f != 0.f && !bvhOccluded<false>(bv, sh, nullptr)) { T0 = comp; T1.x = fabsf(dot3(wi, B.nn)) / 1.f; T1.y = d2; T1.z = fall; }
+            }
+            terms[3 * t] = T0; terms[3 * t + 1] = T1; terms[3 * t + 2] = T2;
+            return;
+        }
         // ---- sample the light (integrator.cpp:114-131)
         f3 wi; float lightPdf; DRay sh;
         bool lit = sampleSphereLightL(L, p, eps, lu0, lu1, &wi, &lightPdf, &sh);
@@ -448,10 +461,16 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
         uint64_t t = s * lay.slots;
         for (uint32_t i = 0; i < lay.nLights; ++i) {
             float Le = __ldg(&lights[i].Lemit[lane]);
+            const bool delta = lights[i].radius < 0.f;
             float Ld = 0.f;
             for (uint32_t j = 0; j < lay.nS[i]; ++j, ++t) {
                 float4 T0 = __ldg(&terms[3 * t]), T1 = __ldg(&terms[3 * t + 1]), T2 = __ldg(&terms[3 * t + 2]);
                 float est = 0.f;
+                if (delta) {                                                   // Li = Intensity * Falloff / DistanceSquared (lights/point.cpp:55, spot.cpp:58)
+                    if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * ((Le * T1.z) / T1.y)) * T1.x;
+                    Ld += est;
+                    continue;
+                }
                 if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * Le) * T1.x;
                 if (T2.w != 0.f) est += (((lobeValue(T2, Kr, Kt) * Le) * T1.y) * T1.z) / T1.w;
                 Ld += est;

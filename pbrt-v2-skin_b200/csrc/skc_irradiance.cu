@@ -122,9 +122,19 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
         float u0 = vanDerCorput(s, __ldg(w)), u1 = sobol2(s, __ldg(w + 1));
         f3 wi; float lp;
         float cosT = 0.f, pdf = 0.f;
-        if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
-            need = true;
-            cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
+        const int kind = lightKind(lights[j]);
+        if (kind == 0) {
+            if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
+                need = true;
+                cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
+            }
+        } else {      // delta light: lightPdf = 1; the pdf slot carries DistanceSquared(lightPos, p) for k_irr_spectral's Li
+            float d2, fall;
+            bool lit = sampleDeltaLight(lights[j], kind, p, eps, &wi, &d2, &fall, &sh);
+            if (dot3(wi, n) > 0.f && lit && d2 != 0.f) {
+                need = true;
+                cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = d2;
+            }
         }
         cosPdf[target] = make_float2(cosT, pdf);
     }
@@ -161,7 +171,7 @@ __global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__
 
 __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
         uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
-        float *__restrict__ Eout, uint64_t outBase) {
+        float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea) {
     int lane = threadIdx.x & 31;
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
@@ -175,6 +185,14 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
             uint32_t nS = sl.nS[j];
             float Lc = __ldg(&lights[j].Lemit[lam]);
             float el = 0.f;
+            const int kind = lightKind(lights[j]);
+            float fall = 1.f;
+            if (kind == 2) {      // SpotLight::Sample_L's Falloff(-wi), recomputed from the point (k_irr_sample keeps {cos, d2})
+                float4 pa = __ldg(&posArea[outBase + ptBase + point]);
+                f3 pp = mk3(pa.x, pa.y, pa.z);
+                f3 lightPos = xformPoint(lights[j].o2w, mk3(0.f, 0.f, 0.f));
+                fall = spotFalloff(lights[j], mul3(normalize3(sub3(lightPos, pp)), -1.f));
+            }
             for (uint32_t sBase = 0; sBase < nS; sBase += 32) {
                 uint32_t chunk = min(32u, nS - sBase);
                 float2 mine = lane < chunk ? __ldg(&cp[sBase + lane]) : make_float2(0.f, 0.f);
@@ -189,7 +207,9 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
                     float r0 = __ldg(&rhoHd[id * SKC_EPAD + lane]), r1 = __ldg(&rhoHd[(id + 1) * SKC_EPAD + lane]);
                     float rho = (1.f - lerp) * r0 + lerp * r1;
                     float Ft = 1.f - rho;
-                    el += ((Ft * Lc) * cosT) / pdf;      // multipolesubsurface.cpp:133
+                    float Li = Lc;
+                    if (kind != 0) { Li = (Lc * fall) / pdf; pdf = 1.f; }      // Intensity * Falloff / DistanceSquared; lightPdf = 1
+                    el += ((Ft * Li) * cosT) / pdf;      // multipolesubsurface.cpp:133
                 }
             }
             cp += nS;
@@ -334,7 +354,7 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
             k_irr_sample<false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
             k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
         }
-        k_irr_spectral<<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first);
+        k_irr_spectral<<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }

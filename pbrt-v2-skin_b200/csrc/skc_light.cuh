@@ -177,6 +177,45 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
     return true;
 }
 
+// ---- delta lights: lights/point.cpp:49-56, lights/spot.cpp:52-72, lights/distant.cpp:49-56 -------------
+// They reuse the 70-float record (include/skin_cuda.h): radius = -1 point, -2 spot, -3 distant; o2w / w2o = LightToWorld and
+// its inverse; spot: zmin = cosTotalWidth, zmax = cosFalloffStart; distant: (zmin, zmax, phiMax) = lightDir; Lemit = the
+// intensity I (point, spot) or the radiance L (distant); nSamples = 1.
+__device__ __forceinline__ int lightKind(const skc_light &L) { return L.radius < 0.f ? (int)(-L.radius) : 0; }
+
+__device__ inline float spotFalloff(const skc_light &L, f3 w) {          // SpotLight::Falloff (lights/spot.cpp:62-72)
+    f3 wl = normalize3(xformVector(L.w2o, w));
+    float costheta = wl.z;
+    if (costheta < L.zmin) return 0.f;
+    if (costheta > L.zmax) return 1.f;
+    float delta = (costheta - L.zmin) / (L.zmax - L.zmin);
+    return delta * delta * delta * delta;
+}
+
+// Sample_L of a delta light: wi, the shadow ray of its VisibilityTester (core/light.h:87-99 SetSegment / SetRay), and the two
+// scalars that turn the stored spectrum into Li: Li = (Lemit * falloff) / d2 (d2 = 1 for a distant light, falloff = 1
+// unless spot; x * 1 and x / 1 are exact, so one expression serves the three).  Returns false when Li is black.
+__device__ inline bool sampleDeltaLight(const skc_light &L, int kind, f3 p, float pEps, f3 *wiOut, float *d2Out, float *falloffOut, DRay *shadow) {
+    *d2Out = 1.f; *falloffOut = 1.f;
+    if (kind == 3) {
+        f3 wi = mk3(L.zmin, L.zmax, L.phiMax);
+        *wiOut = wi;
+        shadow->o = p; shadow->d = wi; shadow->mint = pEps; shadow->maxt = INFINITY;
+        return true;
+    }
+    f3 lightPos = xformPoint(L.o2w, mk3(0.f, 0.f, 0.f));
+    f3 wi = normalize3(sub3(lightPos, p));
+    *wiOut = wi;
+    *d2Out = dist2(lightPos, p);
+    if (kind == 2) {
+        float f = spotFalloff(L, mul3(wi, -1.f));
+        *falloffOut = f;
+        if (f == 0.f) return false;
+    }
+    shadow->o = p; shadow->d = sub3(lightPos, p); shadow->mint = pEps; shadow->maxt = 1.f - 0.f;
+    return true;
+}
+
 // DiffuseAreaLight::Pdf(p, wi) -> ShapeSet::Pdf -> Sphere::Pdf (lights/diffuse.cpp:84-86, core/light.cpp:161-166,
 // shapes/sphere.cpp:276-288, core/shape.cpp:96-109)
 __device__ inline float sphereLightPdf(const skc_light &L, f3 p, f3 wi) {

@@ -354,8 +354,6 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
     k.Kt[0] = k.Kt[1] = k.Kt[2] = 1.f;
     if (!greyColor(mp, "Kr", k.Kr, "layeredskin") || !greyColor(shapeParams, "Kr", k.Kr, "layeredskin")) return false;
     if (!greyColor(mp, "Kt", k.Kt, "layeredskin") || !greyColor(shapeParams, "Kt", k.Kt, "layeredskin")) return false;
-    for (const float *c : {k.Kr, k.Kt})
-        if (c[0] != c[1] || c[1] != c[2]) { Error("layeredskin: coloured Kr / Kt are not supported on the device path (grey RGB only)"); return false; }
     for (const char *tex : {"albedo", "bumpmap", "Kr", "Kt"}) {
         std::string t = shapeParams.FindTexture(tex);
         if (t.empty()) t = mp.FindTexture(tex);
@@ -613,8 +611,21 @@ bool Front::statement(const std::string &id) {
     }
     if (id == "LightSource") {
         if (!named("LightSource") || !needWorld("LightSource")) return false;
-        Error("LightSource \"%s\": only sphere AreaLightSource emitters are supported on the device path", name.c_str());
-        return false;
+        // MakeLight (core/api.cpp:470-500) -> CreatePointLight / CreateSpotLight / CreateDistantLight
+        if (name != "point" && name != "spot" && name != "distant") {
+            Error("LightSource \"%s\": the device path has sphere AreaLightSource emitters and point / spot / distant lights", name.c_str());
+            return false;
+        }
+        float rgb[3] = {1, 1, 1}, sc[3] = {1, 1, 1};
+        if (!greyColor(ps, name == "distant" ? "L" : "I", rgb, "LightSource") || !greyColor(ps, "scale", sc, "LightSource")) return false;
+        if (sc[0] != 1.f || sc[1] != 1.f || sc[2] != 1.f) { Error("LightSource \"scale\" is not supported on the device path; fold it into the intensity"); return false; }
+        auto pt = [&](const char *n, V3 d) { const std::vector<float> *v = ps.FindFloats(n, "point"); return v && v->size() == 3 ? V3((*v)[0], (*v)[1], (*v)[2]) : d; };
+        V3 from = pt("from", V3(0, 0, 0)), to = pt("to", V3(0, 0, 1));
+        if (name == "point") sd->lights.push_back(MakePointLight(ctm, from, rgb));
+        else if (name == "spot") sd->lights.push_back(MakeSpotLight(ctm, from, to, rgb, ps.FindOneFloat("coneangle", 30.f), ps.FindOneFloat("conedeltaangle", 5.f)));
+        else sd->lights.push_back(MakeDistantLight(ctm, from, to, rgb));
+        reportUnused(ps, "LightSource");
+        return true;
     }
     if (id == "Material") {
         if (!named("Material") || !needWorld("Material")) return false;

@@ -33,8 +33,8 @@ void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d) {
     for (int k = 0; k < 3; ++k) memcpy(d->cieXYZ[k], kCieXYZ30[k], sizeof(float) * 30);
     d->xyzScale = float(700 - 400) / float(kCieYIntegral * 30);               // core/spectrum.h:381-382
     d->roughness = sd.skin.roughness; d->ior = sd.skin.layerIor[0];
-    // "color Kr" / "color Kt": Spectrum::FromRGB, grey values only on this path
-    for (int i = 0; i < 30; ++i) { d->Kr[i] = sd.skin.Kr[0] * kUnitRGBToSpectrum30[i]; d->Kt[i] = sd.skin.Kt[0] * kUnitRGBToSpectrum30[i]; }
+    RGBToSpectrum(sd.skin.Kr, d->Kr);                                         // "color Kr" / "color Kt": Spectrum::FromRGB
+    RGBToSpectrum(sd.skin.Kt, d->Kt);
     d->matteKd = 0.5f;                                                        // materials/matte.cpp: Kd default
 }
 

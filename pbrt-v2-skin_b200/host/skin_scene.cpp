@@ -104,16 +104,78 @@ void PerspectiveCamera::GenerateRay(float imageX, float imageY, skc_ray *ray) co
     ray->mint = 0.f; ray->maxt = INFINITY;
 }
 
-// ParamSet::AddRGBSpectrum -> Spectrum::FromRGB(rgb, SPECTRUM_REFLECTANCE) (core/paramset.cpp,
-// core/spectrum.cpp).  For r == g == b the conversion reduces to rgb * rgbRefl2SpectWhite * .94;
-// the binned white table comes from skin_tables.h.  Coloured emitters are not on this path yet.
-void RGBIlluminantToSpectrum(const float rgb[3], float out30[30]) {
-    for (int i = 0; i < 30; ++i) out30[i] = rgb[0] * kGreyRGBToSpectrum30[i];
+// ParamSet::AddRGBSpectrum -> Spectrum::FromRGB(rgb, SPECTRUM_REFLECTANCE) (core/paramset.cpp, core/spectrum.cpp:103-145,185):
+// the smallest component's share of the white basis plus the two remaining differences on the cyan/magenta/yellow and
+// red/green/blue bases, times .94, clamped at 0 -- same operation order (0 + a, then += b, += c; the .94 last).
+void RGBToSpectrum(const float rgb[3], float out30[30]) {
+    enum { W, C, M, Y, R, G, B };
+    float a, b, c; int ib, ic;
+    if (rgb[0] <= rgb[1] && rgb[0] <= rgb[2]) {
+        a = rgb[0];
+        if (rgb[1] <= rgb[2]) { b = rgb[1] - rgb[0]; ib = C; c = rgb[2] - rgb[1]; ic = B; }
+        else { b = rgb[2] - rgb[0]; ib = C; c = rgb[1] - rgb[2]; ic = G; }
+    } else if (rgb[1] <= rgb[0] && rgb[1] <= rgb[2]) {
+        a = rgb[1];
+        if (rgb[0] <= rgb[2]) { b = rgb[0] - rgb[1]; ib = M; c = rgb[2] - rgb[0]; ic = B; }
+        else { b = rgb[2] - rgb[1]; ib = M; c = rgb[0] - rgb[2]; ic = R; }
+    } else {
+        a = rgb[2];
+        if (rgb[0] <= rgb[1]) { b = rgb[0] - rgb[2]; ib = Y; c = rgb[1] - rgb[0]; ic = G; }
+        else { b = rgb[1] - rgb[2]; ib = Y; c = rgb[0] - rgb[1]; ic = R; }
+    }
+    for (int i = 0; i < 30; ++i) {
+        float r = 0.f;
+        r += kRGBRefl2Spect30[W][i] * a;
+        r += kRGBRefl2Spect30[ib][i] * b;
+        r += kRGBRefl2Spect30[ic][i] * c;
+        r *= .94f;
+        out30[i] = r < 0.f ? 0.f : r;       // Clamp(0, INFINITY)
+    }
+}
+void RGBIlluminantToSpectrum(const float rgb[3], float out30[30]) { RGBToSpectrum(rgb, out30); }
+
+static void CoordinateSystemV(V3 v1, V3 *v2, V3 *v3) {      // core/geometry.h:564-574
+    if (fabsf(v1.x) > fabsf(v1.y)) { float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z); *v2 = V3(-v1.z * invLen, 0.f, v1.x * invLen); }
+    else { float invLen = 1.f / sqrtf(v1.y * v1.y + v1.z * v1.z); *v2 = V3(0.f, v1.z * invLen, -v1.y * invLen); }
+    *v3 = Cross(v1, *v2);
+}
+
+SphereLight MakePointLight(const Transform &l2w, V3 from, const float rgb[3]) {
+    SphereLight l; l.kind = 1; l.nSamples = 1; l.radius = 0.f;
+    l.ObjectToWorld = Translate(from) * l2w;                  // lights/point.cpp:68 (this order)
+    memcpy(l.Lrgb, rgb, 12);
+    return l;
+}
+SphereLight MakeSpotLight(const Transform &l2w, V3 from, V3 to, const float rgb[3], float coneangle, float conedelta) {
+    SphereLight l; l.kind = 2; l.nSamples = 1; l.radius = 0.f;
+    V3 dir = Normalize(to - from), du, dv;
+    CoordinateSystemV(dir, &du, &dv);
+    Transform dirToZ(Mat4(du.x, du.y, du.z, 0.f, dv.x, dv.y, dv.z, 0.f, dir.x, dir.y, dir.z, 0.f, 0.f, 0.f, 0.f, 1.f));
+    l.ObjectToWorld = l2w * Translate(from) * InverseT(dirToZ);          // lights/spot.cpp:97-98
+    l.cosTotalWidth = cosf(Radians(coneangle));                           // SpotLight ctor, width = coneangle, fall = coneangle - conedelta
+    l.cosFalloffStart = cosf(Radians(coneangle - conedelta));
+    memcpy(l.Lrgb, rgb, 12);
+    return l;
+}
+SphereLight MakeDistantLight(const Transform &l2w, V3 from, V3 to, const float rgb[3]) {
+    SphereLight l; l.kind = 3; l.nSamples = 1; l.radius = 0.f;
+    l.ObjectToWorld = l2w;
+    l.lightDir = Normalize(l2w.Vector(from - to));
+    memcpy(l.Lrgb, rgb, 12);
+    return l;
 }
 
 skc_light SphereLight::Pack(const float *Lemit30) const {
     skc_light L;
     memcpy(L.o2w, ObjectToWorld.m.m, 64); memcpy(L.w2o, ObjectToWorld.mInv.m, 64);
+    if (kind != 0) {      // delta lights in the sphere record (include/skin_cuda.h)
+        L.radius = -(float)kind; L.zmin = L.zmax = L.phiMax = 0.f;
+        if (kind == 2) { L.zmin = cosTotalWidth; L.zmax = cosFalloffStart; }
+        if (kind == 3) { L.zmin = lightDir.x; L.zmax = lightDir.y; L.phiMax = lightDir.z; }
+        L.nSamples = 1.f; L.reverseOrientation = 0.f; L.thetaMin = L.thetaMax = 0.f;
+        for (int i = 0; i < 30; ++i) L.Lemit[i] = Lemit30[i];
+        return L;
+    }
     // Sphere ctor (shapes/sphere.cpp:40-50)
     float zmn = std::min(std::max(std::min(zmin, zmax), -radius), radius);
     float zmx = std::min(std::max(std::max(zmin, zmax), -radius), radius);
@@ -248,6 +310,16 @@ bool SceneDesc::LoadLines(const std::string &path) {
             l.ObjectToWorld = Transform() * Translate(V3(t[0], t[1], t[2]));
             lights.push_back(l);
             nextMaterialId++;   // each emitter shape gets the default matte material (api.cpp MakeMaterial)
+        } else if (key == "pointlight" || key == "spotlight" || key == "distantlight") {
+            // pointlight fx fy fz r g b | spotlight fx fy fz tx ty tz r g b coneangle conedeltaangle | distantlight fx fy fz tx ty tz r g b
+            float f[3], t[3] = {0, 0, 1}, c[3], cone = 30.f, delta = 5.f;
+            ls >> f[0] >> f[1] >> f[2];
+            if (key != "pointlight") ls >> t[0] >> t[1] >> t[2];
+            ls >> c[0] >> c[1] >> c[2];
+            if (key == "spotlight") ls >> cone >> delta;
+            V3 from(f[0], f[1], f[2]), to(t[0], t[1], t[2]);
+            lights.push_back(key == "pointlight" ? MakePointLight(Transform(), from, c) : key == "spotlight" ? MakeSpotLight(Transform(), from, to, c, cone, delta)
+                                                 : MakeDistantLight(Transform(), from, to, c));
         } else if (key == "skin") {
             std::string k;
             while (ls >> k) {
@@ -295,7 +367,7 @@ bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *o
     std::vector<skc_prim> prims;
     std::vector<PrimRef> order = sd.primOrder;
     if (order.empty()) {
-        for (size_t i = 0; i < sd.lights.size(); ++i) order.push_back(PrimRef{1, (int)i});
+        for (size_t i = 0; i < sd.lights.size(); ++i) if (sd.lights[i].kind == 0) order.push_back(PrimRef{1, (int)i});
         order.push_back(PrimRef{0, 0});
     }
     for (const PrimRef &r : order) {
@@ -319,9 +391,7 @@ bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *o
         float Le[30];
         if (Lemit30PerLight) memcpy(Le, Lemit30PerLight + 30 * i, sizeof Le);
         else {
-            const float *c = sd.lights[i].Lrgb;
-            if (c[0] != c[1] || c[1] != c[2]) { *err = "coloured emitters are not supported on the device path yet (grey RGB only)"; return false; }
-            RGBIlluminantToSpectrum(c, Le);
+            RGBToSpectrum(sd.lights[i].Lrgb, Le);
         }
         out->lights.push_back(sd.lights[i].Pack(Le));
     }

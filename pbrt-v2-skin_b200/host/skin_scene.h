@@ -30,7 +30,13 @@ struct TriangleMesh {
     uint64_t CountSurfacePoints(float minDist) const;
 };
 
-struct SphereLight {      // Shape "sphere" + AreaLightSource "area" (shapes/sphere.cpp, lights/diffuse.cpp)
+// A light of scene->lights, in scene order.  kind 0: Shape "sphere" + AreaLightSource "area" (shapes/sphere.cpp,
+// lights/diffuse.cpp); kind 1 / 2 / 3: LightSource "point" / "spot" / "distant" (lights/point.cpp, spot.cpp, distant.cpp) --
+// delta lights, no shape in the BVH.  ObjectToWorld is the shape's / the light's LightToWorld.
+struct SphereLight {
+    int kind = 0;
+    float cosTotalWidth = 0.f, cosFalloffStart = 0.f;    // spot (lights/spot.cpp:42-50)
+    V3 lightDir;                                        // distant: Normalize(LightToWorld(from - to)) (lights/distant.cpp:42-47)
     Transform ObjectToWorld;
     float radius = 1.f, zmin = -1.f, zmax = 1.f, phiMaxDeg = 360.f;
     float Lrgb[3] = {1, 1, 1};
@@ -140,6 +146,11 @@ struct BuiltScene {
     std::vector<skc_light> lights;
     const TriangleMesh *mesh = nullptr;       // single skin mesh supported on the device path
 };
+// CreatePointLight / CreateSpotLight / CreateDistantLight (lights/point.cpp:63-70, spot.cpp:81-101, distant.cpp:67-75): l2w is
+// the CTM at the LightSource directive
+SphereLight MakePointLight(const Transform &l2w, V3 from, const float rgb[3]);
+SphereLight MakeSpotLight(const Transform &l2w, V3 from, V3 to, const float rgb[3], float coneangle, float conedelta);
+SphereLight MakeDistantLight(const Transform &l2w, V3 from, V3 to, const float rgb[3]);
 bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *out, std::string *err);
 // TriangleMesh from object-space arrays the way CreateTriangleMeshShape + the TriangleMesh ctor do (shapes/trianglemesh.cpp:55-80,360-420)
 void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, int nverts, const float *P, const float *N, const float *uv,
@@ -165,6 +176,8 @@ bool WriteImage(const std::string &name, const float *rgb, int w, int h, std::st
 
 // RGB -> SampledSpectrum for an illuminant (core/spectrum.cpp FromRGB, SpectrumType illuminant)
 void RGBIlluminantToSpectrum(const float rgb[3], float out30[30]);
+// Spectrum::FromRGB(rgb, SPECTRUM_REFLECTANCE) (core/spectrum.cpp:103-145): what ParamSet turns every "color" parameter into
+void RGBToSpectrum(const float rgb[3], float out30[30]);
 
 // integrators/multipolesubsurface.{h,cpp}
 class MultipoleSubsurfaceIntegrator {

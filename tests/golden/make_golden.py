@@ -13,6 +13,8 @@ and packs the exported streams into compressed .npz files:
                   the film's image (row N1: the rest of Li, sampler and film on the device)
   tissue.npz      scenes/tissue.scene (BASELINE.json configs[0] stand-in: 160x90 film, LayeredSkin slab at the material's
                   defaults): image, octree root, strided irradiance points and per-sample radiance
+  skin_lights.npz scenes/skin_lights.scene (point, sphere area, spot and distant light): light records, irradiance,
+                  per-sample radiance, image
   mpc_kat.npz     MPC_ComputeDiffusionProfile on the parameter sets of the reference's
                   src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
 
@@ -107,6 +109,28 @@ def frame_golden(name):
     print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("camera_samples", "camera_tasks", "sample_floats")})
 
 
+def lights_golden(name="skin_lights"):
+    """SURVEY.md 8f N4 (scenes/skin_lights.scene = .pbrt: point + sphere area + spot + distant light on the head): the
+    lights as the reference built them (records in the convention of include/skin_cuda.h), every irradiance point, the full
+    Li of every camera sample and the image."""
+    scene = os.path.join(ROOT, "scenes", name + ".scene")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        meta = read_meta(os.path.join(d, "meta.txt"))
+        f32 = lambda fn: np.fromfile(os.path.join(d, fn), np.float32)
+        arrays = dict(
+            meta_keys=np.array(list(meta.keys())), meta_vals=np.array([float(v) for v in meta.values()]),
+            lights=f32("lights.bin").reshape(-1, 70),
+            irradiance_E=f32("irradiance_points.bin").reshape(-1, 38)[:, 6:36].copy(),
+            octree_root=f32("octree_root.bin"),
+            camera_xy=f32("camera_xy.bin").reshape(-1, 2), L=f32("L.bin").reshape(-1, 30), L_sss=f32("L_sss.bin").reshape(-1, 30),
+            image=read_pfm(os.path.join(d, "image.pfm")),
+        )
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "lights")})
+
+
 def tissue_golden(name="tissue"):
     """BASELINE.json configs[0] stand-in (scenes/tissue.scene = scenes/tissue.pbrt: LayeredSkin slab at the material's
     defaults incl. the transmission lobe, mesh without normals / uvs): image, octree root and bounds, and every 37th
@@ -175,8 +199,8 @@ def mpc_golden():
 
 
 if __name__ == "__main__":
-    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "mpc_kat"]
+    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "skin_lights", "mpc_kat"]
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)

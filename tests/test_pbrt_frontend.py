@@ -146,7 +146,7 @@ def test_shape_parameters_override_material_parameters(pkg, tmp_path):
 @pytest.mark.parametrize("text,needle", [
     (scene_text('SurfaceIntegrator "path"'), 'SurfaceIntegrator "path"'),
     (scene_text(""), "multipolesubsurface"),
-    (scene_text(world='LightSource "point"\n' + TRI % ("", "")), 'LightSource "point"'),
+    (scene_text(world='LightSource "infinite"\n' + TRI % ("", "")), 'LightSource "infinite"'),
     (scene_text(mat='"texture albedo" "tex"'), "texture albedo"),
     (scene_text('SurfaceIntegrator "multipolesubsurface" "bool usepoissonpointfinder" "true"'), "usepoissonpointfinder"),
     (scene_text('Renderer "metropolis"\nSurfaceIntegrator "multipolesubsurface"'), 'Renderer "metropolis"'),
