@@ -212,7 +212,10 @@ __device__ inline bool sampleDeltaLight(const skc_light &L, int kind, f3 p, floa
         *falloffOut = f;
         if (f == 0.f) return false;
     }
-    shadow->o = p; shadow->d = sub3(lightPos, p); shadow->mint = pEps; shadow->maxt = 1.f - 0.f;
+    // VisibilityTester::SetSegment(p, pEpsilon, lightPos, 0.) (core/light.h:87-92)
+    float dist = len3(sub3(p, lightPos));
+    float invd = 1.f / dist;
+    shadow->o = p; shadow->d = mul3(sub3(lightPos, p), invd); shadow->mint = pEps; shadow->maxt = dist * (1.f - 0.f);
     return true;
 }
 
