@@ -145,6 +145,16 @@ extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t 
     ctx->meshTris = indices ? nTris : 0;
     if (upload(ctx, &ctx->spheres, spheres, nSpheres)) return 1;
     ctx->nNodes = nNodes; ctx->nPrims = nPrims; ctx->nVerts = nVerts; ctx->nSpheres = nSpheres;
+    {   // longest root-to-leaf path of the depth-first array: the most entries a traversal stack can hold
+        std::vector<std::pair<uint32_t, uint32_t>> st; st.push_back({0u, 1u});
+        uint32_t depth = 0;
+        while (!st.empty()) {
+            auto [n, d] = st.back(); st.pop_back();
+            depth = std::max(depth, d);
+            if (n < nNodes && nodes[n].nPrimitives == 0) { st.push_back({n + 1, d + 1}); if (nodes[n].offset < nNodes) st.push_back({nodes[n].offset, d + 1}); }
+        }
+        ctx->bvhDepth = depth;
+    }
     if (meshO2W) memcpy(ctx->meshO2W, meshO2W, 128);
     else { float id[32] = {1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1, 1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1}; memcpy(ctx->meshO2W, id, 128); }
     ctx->meshFlip = (reverseOrientation != 0) ^ (transformSwapsHandedness != 0);

@@ -207,11 +207,12 @@ __device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0,
 }
 
 
-struct SlabSetup { f3 invDir; int neg[3]; };
+struct SlabSetup { f3 invDir; int neg[3]; int negMask; };   // negMask: the three signs as bits, for the child order by split axis (no dynamically indexed array -> no local memory)
 __device__ __forceinline__ SlabSetup slabSetup(const DRay &r) {
     SlabSetup s;
     s.invDir = mk3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
     s.neg[0] = s.invDir.x < 0; s.neg[1] = s.invDir.y < 0; s.neg[2] = s.invDir.z < 0;
+    s.negMask = s.neg[0] | (s.neg[1] << 1) | (s.neg[2] << 2);
     return s;
 }
 // accelerators/bvh.cpp:126-148
@@ -267,7 +268,7 @@ __device__ inline bool bvhOccluded(const BvhView &bv, const DRay &ray, unsigned 
                 nodeNum = todo[--todoOffset];
             } else {
                 uint32_t axis = (meta >> 8) & 3;
-                if (ss.neg[axis]) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
+                if ((ss.negMask >> axis) & 1) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
                 else              { todo[todoOffset++] = offset; nodeNum = nodeNum + 1; }
             }
         } else {
@@ -312,7 +313,7 @@ __device__ inline int bvhClosest(const BvhView &bv, DRay &ray, float *b1Hit, flo
                 nodeNum = todo[--todoOffset];
             } else {
                 uint32_t axis = (meta >> 8) & 3;
-                if (ss.neg[axis]) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
+                if ((ss.negMask >> axis) & 1) { todo[todoOffset++] = nodeNum + 1; nodeNum = offset; }
                 else              { todo[todoOffset++] = offset; nodeNum = nodeNum + 1; }
             }
         } else {

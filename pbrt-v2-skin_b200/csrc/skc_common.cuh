@@ -73,6 +73,8 @@ struct skc_ctx {
     std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize
     bool otTopologyReady = false;
     int moSplit = 0;         // warps per Mo packet (each sums 1/moSplit of the spectrum): 0 = by launch size; env SKC_MO_SPLIT=1|2
+    bool hasDeltaLights = false;   // any point / spot / distant light among the uploaded lights (selects the DELTA kernel instances)
+    uint32_t bvhDepth = 0;      // depth of the uploaded BVH (longest root-to-leaf path), bounds the traversal stacks
     int moSort = -1;         // spatial sort of the hit points before the packet kernel: -1 = where the caller fixes the order (skc_mo, skc_li_sss, skc_camera_pass*), 0 never, 1 also in the frame path; env SKC_MO_SORT
     int moPacket = 1;        // Mo kernel: 1 = packet (lane = hit), 0 = warp per hit (lane = wavelength); env SKC_MO_KERNEL=warp|packet
     uint64_t otPoints = 0;

@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(256) k_scrambles(uint32_t taskFirst, uint32_t 
 
 struct IrrSlots { uint32_t nLights, S; uint32_t nS[IRR_MAX_LIGHTS]; };   // S = sum of RoundUpPow2(nSamples)
 
-template <bool COUNT>
+// DELTA: the scene has point / spot / distant lights (row N4); without them the instance is the sphere-emitter code alone
+template <bool COUNT, bool DELTA>
 __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__restrict__ lights, IrrSlots sl,
         const skc_surface_point *__restrict__ pts, const uint32_t *__restrict__ scr, uint64_t ptBase, uint32_t nPts,
         float2 *__restrict__ cosPdf, float4 *__restrict__ rayO, float4 *__restrict__ rayD, uint32_t *__restrict__ rayTarget,
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
         float u0 = vanDerCorput(s, __ldg(w)), u1 = sobol2(s, __ldg(w + 1));
         f3 wi; float lp;
         float cosT = 0.f, pdf = 0.f;
-        const int kind = lightKind(lights[j]);
+        const int kind = DELTA ? lightKind(lights[j]) : 0;
         if (kind == 0) {
             if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
                 need = true;
@@ -169,6 +170,7 @@ __global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__
     if (bvhOccluded<COUNT>(bv, ray, cnt)) cosPdf[__ldg(&rayTarget[r])] = make_float2(0.f, 0.f);
 }
 
+template <bool DELTA>
 __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
         uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
         float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea) {
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
             uint32_t nS = sl.nS[j];
             float Lc = __ldg(&lights[j].Lemit[lam]);
             float el = 0.f;
-            const int kind = lightKind(lights[j]);
+            const int kind = DELTA ? lightKind(lights[j]) : 0;
             float fall = 1.f;
             if (kind == 2) {      // SpotLight::Sample_L's Falloff(-wi), recomputed from the point (k_irr_sample keeps {cos, d2})
                 float4 pa = __ldg(&posArea[outBase + ptBase + point]);
@@ -208,7 +210,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
                     float rho = (1.f - lerp) * r0 + lerp * r1;
                     float Ft = 1.f - rho;
                     float Li = Lc;
-                    if (kind != 0) { Li = (Lc * fall) / pdf; pdf = 1.f; }      // Intensity * Falloff / DistanceSquared; lightPdf = 1
+                    if (DELTA && kind != 0) { Li = (Lc * fall) / pdf; pdf = 1.f; }      // Intensity * Falloff / DistanceSquared; lightPdf = 1
                     el += ((Ft * Li) * cosT) / pdf;      // multipolesubsurface.cpp:133
                 }
             }
@@ -277,6 +279,8 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
         uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2 (multipolesubsurface.cpp:101)
         ctx->lightNS[j] = nS;
     }
+    ctx->hasDeltaLights = false;
+    for (uint32_t j = 0; j < nLights; ++j) ctx->hasDeltaLights |= lights[j].radius < 0.f;
     return 0;
 }
 
@@ -340,6 +344,7 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
     }
     if (!deferTiming) skc_stage_begin(ctx);
     SKC_CUDA(cudaMemsetAsync(dNRays, 0, nBatches * sizeof(uint32_t), ctx->stream));
+
     for (uint64_t b = 0; b < nBatches; ++b) {
         uint64_t pb = b * batchPts;
         uint32_t np = (uint32_t)std::min<uint64_t>(batchPts, count - pb);
@@ -348,13 +353,16 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
         unsigned gSample = (unsigned)((ns + IRR_BLOCK - 1) / IRR_BLOCK), gShadow = (unsigned)((ns + 127) / 128);
         unsigned gSpec = (unsigned)(((uint64_t)np + IRR_SPECTRAL_POINTS * 8 - 1) / (IRR_SPECTRAL_POINTS * 8));
         if (cntDev) {
-            k_irr_sample<true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
+            if (ctx->hasDeltaLights) k_irr_sample<true, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
+            else k_irr_sample<true, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
             k_irr_shadow<true><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, cntDev);
         } else {
-            k_irr_sample<false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
+            if (ctx->hasDeltaLights) k_irr_sample<false, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
+            else k_irr_sample<false, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
             k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
         }
-        k_irr_spectral<<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
+        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
+        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }
