@@ -282,8 +282,15 @@ def main():
     dom = "irradiance" if stage_ms["irradiance"] >= stage_ms["mo"] else "mo"
     dom_bytes = irr_bytes if dom == "irradiance" else mo_bytes
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_irradiance" if dom == "irradiance" else "k_mo", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, sustained copy)",
+    # DRAM traffic of the dominant kernel per launch, from the committed ncu --set full capture of this same step
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_dram_traffic.json"))).get("k_mo_packet" if dom == "mo" else None)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "k_irr_sample + k_irr_shadow + k_irr_spectral" if dom == "irradiance" else "k_mo_packet", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r1_frame_kernels_full.txt): far below the algorithmic bytes because the octree top, the profile tables and the rows neighbouring samples share are served by L1/L2", "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, sustained copy)",
                 "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": stage_ms[dom],
                 "other": {"k_irradiance": {"GBps": irr_bytes / (stage_ms["irradiance"] * 1e-3) / 1e9, "ms": stage_ms["irradiance"],
                                            "shadow_rays": int(c_irr[2]), "slab_tests": int(c_irr[0]), "prim_tests": int(c_irr[1])},
