@@ -103,7 +103,7 @@ def reference_arm(args):
         return
     drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
     if not os.path.exists(drv):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (oracle/build_ref.sh needs /root/reference)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (oracle/build_ref.sh needs /root/reference)"})
         return
     sample = os.path.join(ROOT, "scenes", "skin_sample16.scene")
     cores = os.cpu_count() or 1
@@ -115,16 +115,35 @@ def reference_arm(args):
     value = units / secs
     desc = ("skin.scene at 1/16 scale (minsampledistance 0.006 -> %s irradiance points, 320x180x4spp -> %s camera samples), "
             "reference Preprocess + its SamplerRendererTask loop (sampler, camera rays, Scene::Intersect, full Li, film AddSample), %d steps" % (steps[0][3], steps[0][5], len(steps)))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / max(1, len(steps)), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": desc},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries loaded later write there too (NCCL prints its version line to
+    stdout when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at stderr for the run and the JSON line goes
+    to the saved descriptor."""
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    _OUT.write(json.dumps(obj) + "\n")
+    _OUT.flush()
+
+
+_OUT = sys.stdout
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -132,6 +151,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scene", default=os.path.join(ROOT, "scenes", "skin.scene"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefetch", action="store_true", help="staged flow: sampler stream, closest hits and direct lighting after Preprocess instead of beside it")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -194,13 +214,16 @@ def main():
         dev.build_octree_finalize()
 
     def step_resident():
+        if not args.no_prefetch:
+            dev.frame_prefetch()                # sampler stream, camera rays, closest hits, direct-lighting terms: second stream, beside Preprocess
         if world == 1:
             dev.tessellate_resident(scene.minsampledistance, material_id=0)
         else:
             dev.tessellate_range(scene.minsampledistance, p_first, p_count, material_id=0)      # this rank's shard of the points
         dev.irradiance_resident(p_first, p_count, n_tasks, scene.mix)
         exchange_and_build()
-        dev.frame_samples()
+        if args.no_prefetch:
+            dev.frame_samples()
         dev.frame_film_clear()
         dev.frame_render(r_first, r_count, scene.maxerror, scene.mix)
         if world > 1:
@@ -351,7 +374,7 @@ def main():
                 u = sum(int(s[3]) + int(s[5]) for s in st); sec = sum(float(s[7]) + float(s[9]) for s in st)
                 out["cpu_baseline"] = {"value": u / sec, "unit": UNIT, "cores": cores, "kind": "reference",
                                        "sample": "skin.scene at 1/16 scale (%s points, %s camera samples), reference Preprocess + its SamplerRendererTask loop with the full Li, 2 steps, %.1f s" % (st[0][3], st[0][5], sec)}
-    print(json.dumps(out))
+    emit(out)
     dev.close()
     if world > 1:
         dist.destroy_process_group()

@@ -259,6 +259,11 @@ int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *desc, uint64_t *nSamples
 /* Generates the LDSampler stream of every task (RNG(taskNum) regenerated per CTA) and the camera rays; they become
  * the resident camera rays (as after skc_set_camera_rays). */
 int skc_frame_samples(skc_ctx *ctx);
+/* The part of the frame that does not depend on Preprocess -- skc_frame_samples, Scene::Intersect of every camera ray and
+ * EstimateDirect's terms (core/integrator.cpp:108-155) -- enqueued on the context's second stream; returns without
+ * waiting.  Call it before the Preprocess calls; skc_frame_render(ctx, 0, nSamples, ...) then picks the results up on
+ * the device.  Replaces skc_frame_samples in that flow; results are bit-identical to the staged calls. */
+int skc_frame_prefetch(skc_ctx *ctx);
 /* Test access: image positions [count][2], the 1-D/2-D arrays of each sample [count][floatsPerSample]
  * (every 1-D array, then every 2-D array, as Sample::oneD / twoD) and the rays.  Any output may be NULL. */
 int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t count, float *xy, float *arrays, skc_ray *rays);

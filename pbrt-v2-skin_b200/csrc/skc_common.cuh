@@ -26,6 +26,7 @@ struct skc_ctx {
     cudaEvent_t defEv0 = nullptr, defEv1 = nullptr;   // deferred stage timing of the irradiance pass
     cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute
     std::vector<cudaEvent_t> evPool;         // untimed events ordering copyStream against stream
+    bool stageOff = false;                   // skc_stage_begin/end are no-ops (work enqueued on auxStream without host synchronisation: skc_frame_prefetch)
     bool stageAccumulate = false;            // skc_stage_end adds to stageMs instead of overwriting (chunked passes)
     std::string err;
     uint64_t launches = 0;

@@ -27,8 +27,9 @@ void *skc_scratch(skc_ctx *ctx, int slot, size_t bytes) {
     return ctx->scratch[slot];
 }
 
-void skc_stage_begin(skc_ctx *ctx) { cudaEventRecord(ctx->ev0, ctx->stream); }
+void skc_stage_begin(skc_ctx *ctx) { if (!ctx->stageOff) cudaEventRecord(ctx->ev0, ctx->stream); }
 void skc_stage_end(skc_ctx *ctx, int stage) {
+    if (ctx->stageOff) return;
     cudaEventRecord(ctx->ev1, ctx->stream);
     cudaEventSynchronize(ctx->ev1);
     float ms = 0.f;
@@ -59,9 +60,16 @@ extern "C" skc_ctx *skc_create(int device) {
     skc_ctx *ctx = new skc_ctx();
     ctx->device = device;
     if (cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->smCount <= 0) ctx->smCount = 148;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    // Stream priorities (lower number = served first).  The main stream carries the critical path (Preprocess, Mo, film) and
+    // gets the highest priority; the second stream (skc_frame_prefetch, the octree topology of skc_preprocess) the lowest,
+    // so that its blocks only fill what the main stream's kernels leave free.  Measured on skin.scene, frame with prefetch:
+    // equal priorities 123.7 ms, second stream first 123.8 ms, main stream first 121.7 ms (staged flow: 126.5 ms).
+    int prioLeast = 0, prioGreatest = 0;
+    cudaDeviceGetStreamPriorityRange(&prioLeast, &prioGreatest);
+    int prioMain = getenv("SKC_MAIN_PRIO") ? atoi(getenv("SKC_MAIN_PRIO")) : prioGreatest, prioAux = getenv("SKC_AUX_PRIO") ? atoi(getenv("SKC_AUX_PRIO")) : prioLeast;
+    if (cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prioMain) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&ctx->auxStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&ctx->auxStream, cudaStreamNonBlocking, prioAux) != cudaSuccess ||
         cudaEventCreate(&ctx->defEv0) != cudaSuccess || cudaEventCreate(&ctx->defEv1) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         skc_fail(nullptr, "skc_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));

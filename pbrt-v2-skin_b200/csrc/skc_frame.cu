@@ -66,6 +66,9 @@ struct skc_frame_state {
     uint32_t *dOrder = nullptr;   // render order: pixel slot -> pixel of the sampler stream (Z-order inside each task window)
     FrameConsts *dConsts = nullptr;
     bool samplesReady = false;
+    // skc_frame_prefetch: the part of the frame that does not depend on Preprocess, enqueued on auxStream
+    bool prefetched = false;
+    cudaEvent_t evP0 = nullptr, evP1 = nullptr, evDone = nullptr;
 };
 
 void skc_frame_release(skc_ctx *ctx) {
@@ -73,6 +76,7 @@ void skc_frame_release(skc_ctx *ctx) {
     if (!f) return;
     void *ptrs[] = {f->dWin, f->dSeed, f->dPixBase, f->dXY, f->dArrays, f->dFilm, f->dConsts, f->dOrder};
     for (void *p : ptrs) if (p) cudaFree(p);
+    for (cudaEvent_t e : {f->evP0, f->evP1, f->evDone}) if (e) cudaEventDestroy(e);
     delete f;
     ctx->frame = nullptr;
 }
@@ -685,27 +689,12 @@ extern "C" int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t coun
     return 0;
 }
 
-extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix, float *L30) {
-    if (!ctx) return 1;
-    cudaSetDevice(ctx->device);
-    skc_frame_state *f = ctx->frame;
-    if (!f || !f->samplesReady) return skc_fail(ctx, "skc_frame_render: skc_frame_samples first");
-    if (first + count > f->nSamples) return skc_fail(ctx, "skc_frame_render: bad range");
-    if (!count) return 0;
+// Scene::Intersect for the camera rays and EstimateDirect's terms (everything of Li that does not need the octree)
+static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, uint64_t count, skc_hit *dHits, float4 *dFrame, float4 *dTerms) {
     const FrameLayout &lay = f->lay;
-    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 1, count * sizeof(skc_hit));
-    float *dL = (float *)skc_scratch(ctx, 2, count * SKC_NS * sizeof(float));
-    float4 *dFrame = (float4 *)skc_scratch(ctx, 13, count * 2 * sizeof(float4));
-    float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * lay.slots * 3 * sizeof(float4));
-    if (!dHits || !dL || !dFrame || !dTerms) return 1;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
     skc_stage_end(ctx, 3);
-    if (ctx->otGeo && ctx->otNodes) {
-        if (skc_li_fused_dev(ctx, dHits, count, maxError, mix, dL)) return 1;
-    } else {
-        SKC_CUDA(cudaMemsetAsync(dL, 0, count * SKC_NS * sizeof(float), ctx->stream));    // no octree: `if (bssrdf && octree)` (multipolesubsurface.cpp:267)
-    }
     RhoBxdf mf;
     float rms = f->desc.roughness < 1e-3f ? 1e-3f : f->desc.roughness;      // Beckmann::Beckmann (reflection.h:509-514)
     mf.rms2 = rms * rms; mf.rcpRMS2 = 1 / mf.rms2; mf.etaI = 1.f; mf.etaT = f->desc.ior; mf.fixedFresnel = 0;
@@ -717,11 +706,74 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
                                                                                 dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms);
     SKC_LAUNCHED("k_direct_terms");
     skc_stage_end(ctx, 10);
+    return 0;
+}
+
+// The sampler stream, the camera rays, their closest hits and the direct-lighting terms depend on the scene and the film
+// only -- not on Preprocess.  skc_frame_prefetch enqueues them for the whole frame on the context's second stream and
+// returns at once; the caller then runs Preprocess (tessellation, irradiance pass, octree) on the main stream, and
+// skc_frame_render(0, nSamples, ...) waits for the prefetched part on the device and goes on with Mo and the film.  The
+// latency-bound sampler kernels and the BVH walks of direct lighting fill issue slots the irradiance kernels leave empty.
+// Same kernels, same inputs: bit-identical results.  Stage times of the prefetched part: "samples" = the whole prefetch as
+// timed on its own stream (it overlaps the other stages), "closest" and "direct" = 0.
+extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    skc_frame_state *f = ctx->frame;
+    if (!f) return skc_fail(ctx, "skc_frame_prefetch: skc_frame_setup first");
+    if (!f->evP0) { SKC_CUDA(cudaEventCreate(&f->evP0)); SKC_CUDA(cudaEventCreate(&f->evP1)); SKC_CUDA(cudaEventCreateWithFlags(&f->evDone, cudaEventDisableTiming)); }
+    const uint64_t count = f->nSamples;
+    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 17, count * sizeof(skc_hit));
+    float4 *dFrame = (float4 *)skc_scratch(ctx, 13, count * 2 * sizeof(float4));
+    float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * f->lay.slots * 3 * sizeof(float4));
+    if (!dHits || !dFrame || !dTerms) return 1;
+    SKC_CUDA(cudaEventRecord(f->evDone, ctx->stream));                       // earlier consumers of these buffers
+    SKC_CUDA(cudaStreamWaitEvent(ctx->auxStream, f->evDone, 0));
+    cudaStream_t mainStream = ctx->stream;
+    ctx->stream = ctx->auxStream; ctx->stageOff = true;
+    cudaEventRecord(f->evP0, ctx->stream);
+    int rc = skc_frame_samples(ctx);
+    if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms);
+    cudaEventRecord(f->evP1, ctx->stream);
+    ctx->stream = mainStream; ctx->stageOff = false;
+    if (rc) return 1;
+    f->prefetched = true;
+    return 0;
+}
+
+extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, float maxError, float mix, float *L30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    skc_frame_state *f = ctx->frame;
+    if (!f || !f->samplesReady) return skc_fail(ctx, "skc_frame_render: skc_frame_samples first");
+    if (first + count > f->nSamples) return skc_fail(ctx, "skc_frame_render: bad range");
+    if (!count) return 0;
+    const FrameLayout &lay = f->lay;
+    skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 17, count * sizeof(skc_hit));
+    float *dL = (float *)skc_scratch(ctx, 2, count * SKC_NS * sizeof(float));
+    float4 *dFrame = (float4 *)skc_scratch(ctx, 13, count * 2 * sizeof(float4));
+    float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * lay.slots * 3 * sizeof(float4));
+    if (!dHits || !dL || !dFrame || !dTerms) return 1;
+    const bool usePrefetch = f->prefetched && first == 0 && count == f->nSamples;
+    if (f->prefetched) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, f->evP1, 0));    // hits, frames and direct-lighting terms are (being) made on auxStream
+    f->prefetched = false;
+    if (!usePrefetch) if (frameHitsAndDirect(ctx, f, first, count, dHits, dFrame, dTerms)) return 1;
+    if (ctx->otGeo && ctx->otNodes) {
+        if (skc_li_fused_dev(ctx, dHits, count, maxError, mix, dL)) return 1;
+    } else {
+        SKC_CUDA(cudaMemsetAsync(dL, 0, count * SKC_NS * sizeof(float), ctx->stream));    // no octree: `if (bssrdf && octree)` (multipolesubsurface.cpp:267)
+    }
     skc_stage_begin(ctx);
     k_frame_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, f->dConsts, dHits, dTerms,
                                                                                                  f->dXY, f->dOrder, first, count, dL, f->dFilm);
     SKC_LAUNCHED("k_frame_sum");
     skc_stage_end(ctx, 11);
+    if (usePrefetch) {      // the prefetched part, as timed on its own stream
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, f->evP0, f->evP1);
+        if (ctx->stageAccumulate) ctx->stageMs[9] += ms; else ctx->stageMs[9] = ms;
+        if (!ctx->stageAccumulate) ctx->stageMs[3] = ctx->stageMs[10] = 0.f;
+    }
     if (L30) {
         SKC_CUDA(cudaMemcpyAsync(L30, dL, count * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));

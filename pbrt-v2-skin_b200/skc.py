@@ -32,7 +32,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
            "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
-           "skc_frame_setup", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
+           "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_get_order"]
 
 
@@ -100,6 +100,7 @@ def load_library():
     lib.skc_tessellate_range.restype = i32; lib.skc_tessellate_range.argtypes = [vp, f32, i32, u32, u64, u64, C.POINTER(u64)]
     lib.skc_frame_setup.restype = i32; lib.skc_frame_setup.argtypes = [vp, vp, C.POINTER(u64)]
     lib.skc_frame_samples.restype = i32; lib.skc_frame_samples.argtypes = [vp]
+    lib.skc_frame_prefetch.restype = i32; lib.skc_frame_prefetch.argtypes = [vp]
     lib.skc_frame_get_samples.restype = i32; lib.skc_frame_get_samples.argtypes = [vp, u64, u64, vp, vp, vp]
     lib.skc_frame_sample_floats.restype = u32; lib.skc_frame_sample_floats.argtypes = [vp]
     lib.skc_frame_render.restype = i32; lib.skc_frame_render.argtypes = [vp, u64, u64, f32, f32, vp]
@@ -315,6 +316,10 @@ class SkinDevice:
         self._ck(self.lib.skc_frame_setup(self.ctx, _ptr(self._frame_desc), C.byref(n)))
         self._frame_res = tuple(int(v) for v in self._frame_desc[:8].view(np.int32))
         return int(n.value)
+
+    def frame_prefetch(self):
+        """Sampler stream + camera rays + closest hits + direct-lighting terms on the second stream (no wait)."""
+        self._ck(self.lib.skc_frame_prefetch(self.ctx))
 
     def frame_samples(self):
         self._ck(self.lib.skc_frame_samples(self.ctx))

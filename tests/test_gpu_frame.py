@@ -141,3 +141,22 @@ def test_round_robin_tasks_partition_the_frame(pkg, dev, frame, ld4):
     assert np.array_equal(key(allxy), key(z["camera_xy"]))
     assert np.array_equal(film[..., 3], full[..., 3])
     assert np.allclose(film[..., :3], full[..., :3], rtol=1e-5, atol=1e-6 * np.abs(full[..., :3]).max())
+
+
+def test_prefetch_flow_is_bit_identical(dev, frame):
+    """skc_frame_prefetch (sampler stream, closest hits and direct-lighting terms on the second stream, beside Preprocess)
+    followed by skc_frame_render gives the per-sample radiance of the staged calls bit for bit -- also when the render
+    call does not cover the whole frame and therefore redoes its range itself."""
+    hs, n = frame
+    dev.frame_film_clear()
+    L0 = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True).copy()
+    dev.frame_prefetch()
+    dev.frame_film_clear()
+    L1 = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True).copy()
+    assert np.array_equal(L0.view(np.uint32), L1.view(np.uint32)) and L0.max() > 0
+    assert dev.stage_ms("samples") > 0 and dev.stage_ms("direct") == 0
+    dev.frame_prefetch()
+    half = n // 2
+    La = dev.frame_render(0, half, hs.maxerror, hs.mix, want_L=True).copy()
+    Lb = dev.frame_render(half, n - half, hs.maxerror, hs.mix, want_L=True).copy()
+    assert np.array_equal(np.concatenate([La, Lb]).view(np.uint32), L0.view(np.uint32))
