@@ -74,9 +74,16 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
     double t1 = now();
     if (!dev(BuildSkinMaterial(ctx, sd.skin)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
-    // Preprocess
+    // the camera pass's Preprocess-independent part (sampler stream, camera rays, closest hits, direct lighting) goes to the
+    // second stream first and runs beside Preprocess
+    skc_frame_desc fd;
+    MakeFrameDesc(sd, nCores, &fd);
+    uint64_t nSamples = 0;
+    if (sd.lights.empty()) { *err = "no light sources in the scene: the subsurface integrator has nothing to render"; return false; }
+    if (!dev(skc_frame_setup(ctx, &fd, &nSamples)) || !dev(skc_frame_prefetch(ctx))) return false;
+    // Preprocess (multipolesubsurface.cpp:170-238)
     uint64_t nPts = 0;
-    if (!sd.lights.empty()) {                                                // multipolesubsurface.cpp:173
+    {
         std::vector<skc_surface_point> filePts;
         if (!sd.pointsFile.empty()) {                                        // :176-181, ReadBinaryFile (core/floatfile.h:45-63)
             FILE *f = fopen(sd.pointsFile.c_str(), "rb");
@@ -96,15 +103,11 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
         st->irradianceTasks = RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPts / 4096));   // :194-199
         if (!dev(skc_irradiance_resident(ctx, 0, nPts, st->irradianceTasks, sd.mix, nullptr))) return false;
         if (!dev(skc_build_octree(ctx, &st->octreeNodes, nullptr, nullptr))) return false;
-    } else { *err = "no light sources in the scene: the subsurface integrator has nothing to render"; return false; }
+    }
     if (!dev(skc_synchronize(ctx))) return false;
     double t3 = now();
-    // the camera pass
-    skc_frame_desc fd;
-    MakeFrameDesc(sd, nCores, &fd);
-    uint64_t nSamples = 0;
-    if (!dev(skc_frame_setup(ctx, &fd, &nSamples)) || !dev(skc_frame_samples(ctx)) || !dev(skc_frame_film_clear(ctx)) ||
-        !dev(skc_frame_render(ctx, 0, nSamples, sd.maxerror, sd.mix, nullptr))) return false;
+    // Mo + the subsurface term, the spectral sum and the film
+    if (!dev(skc_frame_film_clear(ctx)) || !dev(skc_frame_render(ctx, 0, nSamples, sd.maxerror, sd.mix, nullptr))) return false;
     std::vector<float> film((size_t)sd.xres * sd.yres * 4);
     if (!dev(skc_frame_film_get(ctx, film.data()))) return false;
     rgb->resize((size_t)sd.xres * sd.yres * 3);
