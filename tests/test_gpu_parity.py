@@ -9,6 +9,7 @@ CUDA) can flip visibility at a silhouette (1/nSamples of one light's contributio
 state the fraction they allow.
 """
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -330,19 +331,10 @@ def test_camera_pass_pinned_output_matches_staged(dev, scene):
 
 
 def c5_parameter_sets(pkg, n_thick=256, desired_length=64):
-    """epidermis thickness swept over [0.02, 2] mean free paths (all thin: the lerp branch),
-    fixed dermis 2.0, eta 1.4/1.4, mua/musp = the 30-bin spectra of SkinCoefficients(0.15, 1, 0.002, 0.3)."""
-    sp = pkg.skin_spectra(0.15, 1.0, 0.002, 0.3)
-    specs, lps, opts = [], [], []
-    for k in range(n_thick):
-        for w in range(30):
-            mfp0 = np.float32(1) / np.float32(sp["mua"][0][w] + sp["musp"][0][w])
-            t = np.float32(0.02 + k * (2.0 - 0.02) / max(n_thick - 1, 1)) * mfp0
-            layers = [(1.4, t, sp["mua"][0][w], sp["musp"][0][w], 0.0), (1.4, 2.0, sp["mua"][1][w], sp["musp"][1][w], 0.0)]
-            mfp = np.float32((np.float32(1) / np.float32(layers[0][2] + layers[0][3]) + np.float32(1) / np.float32(layers[1][2] + layers[1][3])) / np.float32(2))
-            specs += layers; lps.append(2)
-            opts.append((np.float32(np.float32(12) * mfp) / np.float32(desired_length), desired_length, 1))
-    return specs, lps, opts
+    """SURVEY.md 8d config C5 (tools/profile_batch_bench.py holds the generator; the bench runs it at desiredLength 512)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import profile_batch_bench
+    return profile_batch_bench.c5_parameter_sets(pkg, n_thick, desired_length)
 
 
 def test_profile_batch_c5_thickness_sweep_vs_oracle(pkg, dev):
