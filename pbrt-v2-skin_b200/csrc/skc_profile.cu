@@ -103,7 +103,10 @@ __device__ __forceinline__ float expf_glibc(float x, const unsigned long long *t
 #define INV_FOURPI_F (0.25f / 3.141592654f)   /* numutil.h:45-46 */
 
 // z[G][G] (double2 = {R, T}); one thread per (row<=col) cell of the [0,extent]^2 quadrant
-__global__ void k_layer_profile(DipoleSet ds, uint32_t G, double2 *__restrict__ z) {
+// blockIdx.z = set of the batch (its DipoleSet and its grid)
+__global__ void k_layer_profile(const DipoleSet *__restrict__ dsAll, uint32_t G, double2 *__restrict__ z) {
+    const DipoleSet ds = dsAll[blockIdx.z];
+    z += (size_t)blockIdx.z * G * G;
     uint32_t center = (G - 1) / 2, extent = center;
     __shared__ unsigned long long sTab[32];
     if (threadIdx.y == 0) sTab[threadIdx.x] = c_exp2Tab[threadIdx.x];
@@ -149,6 +152,7 @@ __global__ void k_layer_profile(DipoleSet ds, uint32_t G, double2 *__restrict__ 
 __global__ void k_pack(const double2 *__restrict__ z, uint32_t G, uint32_t N, double2 *__restrict__ Z) {
     uint32_t jj = blockIdx.x * blockDim.x + threadIdx.x, ii = blockIdx.y;
     if (jj >= N) return;
+    z += (size_t)blockIdx.z * G * G; Z += (size_t)blockIdx.z * N * N;
     uint32_t c = (G - 1) / 2;
     uint32_t i = (ii + c) % N, j = (jj + c) % N;
     Z[(size_t)ii * N + jj] = (i < G && j < G) ? z[(size_t)i * G + j] : make_double2(0., 0.);
@@ -208,6 +212,7 @@ __global__ void __launch_bounds__(512) k_fft_rows(double2 *__restrict__ Z, uint3
 
 __global__ void k_transpose(const double2 *__restrict__ in, uint32_t N, double2 *__restrict__ out) {
     __shared__ double2 tile[32][33];
+    in += (size_t)blockIdx.z * N * N; out += (size_t)blockIdx.z * N * N;
     uint32_t x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * 32;
     for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) tile[k][threadIdx.x] = in[(size_t)(y0 + k) * N + x];
     __syncthreads();
@@ -234,6 +239,7 @@ __device__ __forceinline__ void splitSpectra(double2 zk, double2 zm, double2 &FR
 __global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restrict__ Z2, uint32_t N, double2 *__restrict__ W) {
     uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, a = blockIdx.y;
     if (b >= N) return;
+    Z1 += (size_t)blockIdx.z * N * N; Z2 += (size_t)blockIdx.z * N * N; W += (size_t)blockIdx.z * N * N;
     size_t i = (size_t)a * N + b, j = (size_t)((N - a) & (N - 1)) * N + ((N - b) & (N - 1));
     double2 R1, T1, R2, T2;
     splitSpectra(Z1[i], Z1[j], R1, T1);
@@ -250,6 +256,7 @@ __global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restri
 __global__ void k_unpack(const double2 *__restrict__ W, uint32_t N, uint32_t G, double2 *__restrict__ z) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
     if (j >= G) return;
+    W += (size_t)blockIdx.z * N * N; z += (size_t)blockIdx.z * G * G;
     uint32_t c = (G - 1) / 2;
     uint32_t ii = (N - c + i) % N, jj = (N - c + j) % N;
     double scale = (double)1 / ((double)N * (double)N);
@@ -260,6 +267,7 @@ __global__ void k_unpack(const double2 *__restrict__ W, uint32_t N, uint32_t G, 
 // block sums of R and T over the grid (totalReflectance / totalTransmittance, :338-339)
 __global__ void k_grid_sum(const double2 *__restrict__ z, size_t n, double2 *__restrict__ partial) {
     __shared__ double2 s[256];
+    z += (size_t)blockIdx.y * n; partial += (size_t)blockIdx.y * gridDim.x;      // blockIdx.y = set
     double r = 0., t = 0.;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) { r += z[i].x; t += z[i].y; }
     s[threadIdx.x] = make_double2(r, t);
@@ -272,10 +280,14 @@ __global__ void k_grid_sum(const double2 *__restrict__ z, size_t n, double2 *__r
 }
 
 // unique radii (:316-330): entry e <- grid cell idx[e] = (i, j); d2 = (float)(i*i+j*j)*step*step
-__global__ void k_extract(const double2 *__restrict__ z, uint32_t G, const uint2 *__restrict__ idx, uint32_t nEntries, float stepSize,
-                          float *__restrict__ d2, float *__restrict__ R, float *__restrict__ T) {
+// blockIdx.y = set: its grid, its step size, its [d2 | R | T] rows of nEntries floats each
+__global__ void k_extract(const double2 *__restrict__ z, uint32_t G, const uint2 *__restrict__ idx, uint32_t nEntries, const float *__restrict__ stepSizes,
+                          float *__restrict__ raw) {
     uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nEntries) return;
+    z += (size_t)blockIdx.y * G * G;
+    const float stepSize = stepSizes[blockIdx.y];
+    float *d2 = raw + (size_t)blockIdx.y * 3 * nEntries, *R = d2 + nEntries, *T = R + nEntries;
     uint32_t c = G / 2 - 1;       // center = length - 1
     uint2 ij = idx[e];
     float denorm = 1.f / (stepSize * stepSize);
@@ -286,10 +298,11 @@ __global__ void k_extract(const double2 *__restrict__ z, uint32_t G, const uint2
 }
 
 // MPC_ResampleForUniformDistanceSquaredDistribution (:404-426) with resample (:355-402)
-__global__ void k_resample(const float *__restrict__ d2, const float *__restrict__ R, const float *__restrict__ T, uint32_t len,
-                           uint32_t target, float *__restrict__ od2, float *__restrict__ oR, float *__restrict__ oT) {
+__global__ void k_resample(const float *__restrict__ raw, uint32_t len, uint32_t target, float *__restrict__ res) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= target) return;
+    const float *d2 = raw + (size_t)blockIdx.y * 3 * len, *R = d2 + len, *T = R + len;      // blockIdx.y = set
+    float *od2 = res + (size_t)blockIdx.y * 3 * target, *oR = od2 + target, *oT = oR + target;
     float extent = d2[len - 1];
     float dsq = (float)i * extent / (float)(target - 1);
     od2[i] = dsq;
@@ -325,13 +338,16 @@ static std::vector<uint2> uniqueRadii(uint32_t length) {
     return v;
 }
 
+// Work areas of one GROUP of K sets: every array holds K consecutive per-set blocks and every kernel takes the set from
+// its grid (blockIdx.z, or .y where noted), so a group's profiles go through each stage in one launch.
 struct ProfileWork {
     double2 *grid[2] = {nullptr, nullptr}, *Z[3] = {nullptr, nullptr, nullptr}, *tw = nullptr, *partial = nullptr;
     uint2 *idx = nullptr;
-    float *raw = nullptr, *res = nullptr;
-    uint32_t G = 0, N = 0, nEntries = 0;
+    float *raw = nullptr, *res = nullptr, *steps = nullptr;
+    DipoleSet *ds = nullptr;
+    uint32_t G = 0, N = 0, nEntries = 0, K = 1;
     void release() {
-        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res};
+        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res, steps, ds};
         for (void *q : p) if (q) cudaFree(q);
         *this = ProfileWork();
     }
@@ -339,14 +355,14 @@ struct ProfileWork {
 
 static size_t fftSmemBytes(uint32_t N) { return (size_t)(N + (N >> 3) + (N >> 6) + 2) * sizeof(double2); }
 
-static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t logN, int inverse) {
+static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t logN, int inverse, uint32_t k) {
     // rows of A in place, transpose into B, rows of B in place: B holds the 2-D transform (transposed layout)
     uint32_t N = w.N, threads = std::max(32u, std::min(N / 8, 512u));
-    k_fft_rows<<<N, threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse);
+    k_fft_rows<<<dim3(N, k), threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse);
     SKC_LAUNCHED("k_fft_rows");
-    k_transpose<<<dim3(N / 32, N / 32), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
+    k_transpose<<<dim3(N / 32, N / 32, k), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
     SKC_LAUNCHED("k_transpose");
-    k_fft_rows<<<N, threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse);
+    k_fft_rows<<<dim3(N, k), threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse);
     SKC_LAUNCHED("k_fft_rows");
     return 0;
 }
@@ -374,15 +390,22 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     while ((1u << logN) < N) ++logN;
     if (fftSmemBytes(N) > 48 * 1024)
         SKC_CUDA(cudaFuncSetAttribute(k_fft_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fftSmemBytes(N)));
+    // group size: as many sets per launch as fit a quarter of the free memory, at most 32
+    bool multi = false;
+    for (uint32_t s = 0; s < nSets; ++s) multi |= layersPerSet[s] > 1;
+    size_t perSet = 2 * (size_t)G * G * sizeof(double2) + (multi ? 3 * (size_t)N * N * sizeof(double2) : 0) + 3 * (size_t)(nEntries + outLen) * sizeof(float);
+    size_t freeB = 0, totalB = 0;
+    cudaMemGetInfo(&freeB, &totalB);
+    uint32_t K = (uint32_t)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(nSets, 32), freeB / 4 / perSet));
+    if (const char *e = getenv("SKC_PROFILE_GROUP")) K = (uint32_t)std::max(1, std::min(atoi(e), (int)nSets));
+    w.K = K;
     int rc = 1;
     do {
-        bool multi = false;
-        for (uint32_t s = 0; s < nSets; ++s) multi |= layersPerSet[s] > 1;
-        if (cudaMalloc((void **)&w.grid[0], (size_t)G * G * sizeof(double2)) != cudaSuccess) break;
-        if (cudaMalloc((void **)&w.grid[1], (size_t)G * G * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.grid[0], (size_t)K * G * G * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.grid[1], (size_t)K * G * G * sizeof(double2)) != cudaSuccess) break;
         if (multi) {
             bool ok = true;
-            for (int k = 0; k < 3; ++k) ok &= cudaMalloc((void **)&w.Z[k], (size_t)N * N * sizeof(double2)) == cudaSuccess;
+            for (int k = 0; k < 3; ++k) ok &= cudaMalloc((void **)&w.Z[k], (size_t)K * N * N * sizeof(double2)) == cudaSuccess;
             if (!ok) break;
             std::vector<double2> tw(N / 2);
             for (uint32_t k = 0; k < N / 2; ++k) { long double a = -2.0L * 3.14159265358979323846264338327950288L * k / N; tw[k] = make_double2((double)cosl(a), (double)sinl(a)); }
@@ -390,10 +413,12 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
             if (cudaMemcpyAsync(w.tw, tw.data(), tw.size() * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
             if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
         }
-        if (cudaMalloc((void **)&w.partial, 256 * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.partial, (size_t)K * 256 * sizeof(double2)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.idx, nEntries * sizeof(uint2)) != cudaSuccess) break;
-        if (cudaMalloc((void **)&w.raw, 3 * (size_t)nEntries * sizeof(float)) != cudaSuccess) break;
-        if (cudaMalloc((void **)&w.res, 3 * (size_t)outLen * sizeof(float)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.raw, (size_t)K * 3 * nEntries * sizeof(float)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.res, (size_t)K * 3 * outLen * sizeof(float)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.steps, (size_t)K * sizeof(float)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.ds, (size_t)K * sizeof(DipoleSet)) != cudaSuccess) break;
         if (cudaMemcpyAsync(w.idx, radii.data(), nEntries * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
         rc = 0;
@@ -402,65 +427,77 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
 
     uploadExpTable(ctx->stream);
     skc_stage_begin(ctx);
-    const skc_layer_spec *sp = specs;
-    std::vector<double2> hpart(256);
+    std::vector<size_t> specOffset(nSets + 1, 0);
+    for (uint32_t s = 0; s < nSets; ++s) specOffset[s + 1] = specOffset[s] + layersPerSet[s];
+    std::vector<double2> hpart((size_t)K * 256);
+    std::vector<DipoleSet> hds(K);
+    std::vector<float> hsteps(K);
     uint32_t ext = (G - 1) / 2 + 1;
-    dim3 lpBlock(32, 8), lpGrid((ext + 31) / 32, (ext + 7) / 8);
-    for (uint32_t s = 0; s < nSets && !rc; ++s) {
-        uint32_t nL = layersPerSet[s];
-        float stepSize = opts[s].desiredStepSize;
-        bool lerpThin = opts[s].lerpOnThinSlab != 0;
+    dim3 lpBlock(32, 8);
+    // a group = up to K consecutive sets with the same number of layers: layer l of all of them goes through each stage at once
+    for (uint32_t s0 = 0; s0 < nSets && !rc;) {
+        const uint32_t nL = layersPerSet[s0];
+        uint32_t k = 1;
+        while (k < K && s0 + k < nSets && layersPerSet[s0 + k] == nL) ++k;
         auto layer = [&](uint32_t l, double2 *dst) -> int {
-            float iorUpper = l == 0 ? sp[0].ior : sp[l].ior / sp[l - 1].ior;                     // :303-309
-            float iorLower = nL > l + 1 ? sp[l].ior / sp[l + 1].ior : sp[l].ior;
-            DipoleSet ds = makeDipoles(sp[l], iorUpper, iorLower, stepSize, lerpThin);
-            SKC_CUDA(cudaMemsetAsync(dst, 0, (size_t)G * G * sizeof(double2), ctx->stream));   // profile.Clear()
-            k_layer_profile<<<lpGrid, lpBlock, 0, ctx->stream>>>(ds, G, dst);
+            for (uint32_t q = 0; q < k; ++q) {
+                const skc_layer_spec *sp = specs + specOffset[s0 + q];
+                float iorUpper = l == 0 ? sp[0].ior : sp[l].ior / sp[l - 1].ior;                     // :303-309
+                float iorLower = nL > l + 1 ? sp[l].ior / sp[l + 1].ior : sp[l].ior;
+                hds[q] = makeDipoles(sp[l], iorUpper, iorLower, opts[s0 + q].desiredStepSize, opts[s0 + q].lerpOnThinSlab != 0);
+            }
+            SKC_CUDA(cudaMemcpyAsync(w.ds, hds.data(), k * sizeof(DipoleSet), cudaMemcpyHostToDevice, ctx->stream));      // pageable source: staged before the call returns
+            SKC_CUDA(cudaMemsetAsync(dst, 0, (size_t)k * G * G * sizeof(double2), ctx->stream));   // profile.Clear()
+            k_layer_profile<<<dim3((ext + 31) / 32, (ext + 7) / 8, k), lpBlock, 0, ctx->stream>>>(w.ds, G, dst);
             SKC_LAUNCHED("k_layer_profile");
             return 0;
         };
         rc = layer(0, w.grid[0]);
         for (uint32_t l = 1; l < nL && !rc; ++l) {
             if ((rc = layer(l, w.grid[1]))) break;
-            dim3 pg((N + 255) / 256, N);
+            dim3 pg((N + 255) / 256, N, k);
             k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[0], G, N, w.Z[0]);
             k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[1], G, N, w.Z[1]);
             ctx->launches += 2;
             // forward: Z0 -> Z2 (transposed spectrum of layer 1); Z1 -> Z0 (layer 2)
-            if ((rc = fft2d(ctx, w, w.Z[0], w.Z[2], logN, 0))) break;
-            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[0], logN, 0))) break;
-            k_adding<<<dim3((N + 255) / 256, N), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
+            if ((rc = fft2d(ctx, w, w.Z[0], w.Z[2], logN, 0, k))) break;
+            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[0], logN, 0, k))) break;
+            k_adding<<<dim3((N + 255) / 256, N, k), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
             ctx->launches++;
-            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[2], logN, 1))) break;      // back to the natural layout
-            k_unpack<<<dim3((G + 255) / 256, G), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0]);
+            if ((rc = fft2d(ctx, w, w.Z[1], w.Z[2], logN, 1, k))) break;      // back to the natural layout
+            k_unpack<<<dim3((G + 255) / 256, G, k), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0]);
             ctx->launches++;
         }
         if (rc) break;
-        float *rawD = w.raw, *rawR = w.raw + nEntries, *rawT = w.raw + 2 * (size_t)nEntries;
-        k_extract<<<(nEntries + 255) / 256, 256, 0, ctx->stream>>>(w.grid[0], G, w.idx, nEntries, stepSize, rawD, rawR, rawT);
+        for (uint32_t q = 0; q < k; ++q) hsteps[q] = opts[s0 + q].desiredStepSize;
+        if (cudaMemcpyAsync(w.steps, hsteps.data(), k * sizeof(float), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        k_extract<<<dim3((nEntries + 255) / 256, k), 256, 0, ctx->stream>>>(w.grid[0], G, w.idx, nEntries, w.steps, w.raw);
         ctx->launches++;
-        const float *oD = rawD, *oR = rawR, *oT = rawT;
+        const float *o = w.raw;
         if (resample) {
-            float *rD = w.res, *rR = w.res + outLen, *rT = w.res + 2 * (size_t)outLen;
-            k_resample<<<(outLen + 255) / 256, 256, 0, ctx->stream>>>(rawD, rawR, rawT, nEntries, outLen, rD, rR, rT);
+            k_resample<<<dim3((outLen + 255) / 256, k), 256, 0, ctx->stream>>>(w.raw, nEntries, outLen, w.res);
             ctx->launches++;
-            oD = rD; oR = rR; oT = rT;
+            o = w.res;
         }
         if (totals) {
-            k_grid_sum<<<256, 256, 0, ctx->stream>>>(w.grid[0], (size_t)G * G, w.partial);
+            k_grid_sum<<<dim3(256, k), 256, 0, ctx->stream>>>(w.grid[0], (size_t)G * G, w.partial);
             ctx->launches++;
-            if (cudaMemcpyAsync(hpart.data(), w.partial, 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+            if (cudaMemcpyAsync(hpart.data(), w.partial, (size_t)k * 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
         }
-        if (d2 && cudaMemcpyAsync(d2 + (size_t)s * outLen, oD, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
-        if (R && cudaMemcpyAsync(R + (size_t)s * outLen, oR, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
-        if (T && cudaMemcpyAsync(T + (size_t)s * outLen, oT, outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+        // rows [set][d2 | R | T][outLen] -> the caller's three [set][outLen] arrays
+        const size_t rowB = (size_t)outLen * sizeof(float);
+        float *dsts[3] = {d2, R, T};
+        for (int a = 0; a < 3 && !rc; ++a)
+            if (dsts[a] && cudaMemcpy2DAsync(dsts[a] + (size_t)s0 * outLen, rowB, o + (size_t)a * outLen, 3 * rowB, rowB, k, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = 1;
+        if (rc) break;
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { rc = 1; break; }
-        if (totals) {
-            double r = 0., t = 0.;
-            for (int k = 0; k < 256; ++k) { r += hpart[k].x; t += hpart[k].y; }
-            totals[2 * s] = (float)r; totals[2 * s + 1] = (float)t;
-        }
-        sp += nL;
+        if (totals)
+            for (uint32_t q = 0; q < k; ++q) {
+                double r = 0., t = 0.;
+                for (int j = 0; j < 256; ++j) { r += hpart[(size_t)q * 256 + j].x; t += hpart[(size_t)q * 256 + j].y; }
+                totals[2 * (s0 + q)] = (float)r; totals[2 * (s0 + q) + 1] = (float)t;
+            }
+        s0 += k;
     }
     if (!rc) skc_stage_end(ctx, 6);
     cudaError_t e = cudaGetLastError();
