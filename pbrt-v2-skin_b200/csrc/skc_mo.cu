@@ -175,6 +175,9 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 // kernel above spends 30 separate lines per contribution (one per wavelength) and is bound by L1 wavefronts.
 // Each lane keeps its 30 wavelength sums in registers; the result is transposed through shared memory.
 #define MOP_WARPS 4
+#ifndef MOP_CTAS1
+#define MOP_CTAS1 7          // resident CTAs per SM of the one-warp-per-packet instance (72 registers)
+#endif
 #define MOP_STACK 512          // 1 + 7 * levels entries at most (levels <= 64)
 
 // Optional fused Li epilogue of the packet kernel (multipolesubsurface.cpp:279-287): the subsurface radiance of each
@@ -232,7 +235,7 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
 // set the length of every launch that has few packets per warp (multi-GPU shards) -- and 16 accumulators instead of
 // 30 leave room for more resident warps.
 template <bool COUNT, int SPLIT, bool PERM>
-__global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? 7 : 8) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+__global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : 8) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                              uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
                                                              uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm) {
@@ -493,7 +496,7 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
         if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
         uint64_t pb = (n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32);
-        if (pb > (uint64_t)ctx->smCount * 7) pb = (uint64_t)ctx->smCount * 7;       // persistent: at most the resident CTAs
+        if (pb > (uint64_t)ctx->smCount * MOP_CTAS1) pb = (uint64_t)ctx->smCount * MOP_CTAS1;       // persistent: at most the resident CTAs
         LiEpilogue ep = li ? *li : LiEpilogue{nullptr, nullptr, nullptr, 0.f, nullptr};
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
         if (!next) return 1;
