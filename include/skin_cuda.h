@@ -278,6 +278,9 @@ int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, float maxErro
 int skc_frame_film_clear(skc_ctx *ctx);
 void *skc_frame_film_dev(skc_ctx *ctx);
 int skc_frame_film_get(skc_ctx *ctx, float *pixels4);
+/* The image ImageFilm::WriteImage hands to ::WriteImage (film/image.cpp:178-213): XYZ -> RGB, divided by the weight sum,
+ * clamped at 0; rgb3 = [yres][xres][3] on the host. */
+int skc_frame_film_rgb(skc_ctx *ctx, float *rgb3);
 
 #ifdef __cplusplus
 }

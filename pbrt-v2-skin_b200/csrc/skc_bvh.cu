@@ -85,12 +85,22 @@ MeshView skc_mesh_view(const skc_ctx *ctx) {
     return mv;
 }
 
+// A scene is uploaded once per frame in the host-buffer flow: the device arrays are kept and reused while they are large
+// enough (cudaFree / cudaMalloc synchronise the device), the copies are stream-ordered and the caller synchronises once.
 template <class T> static int upload(skc_ctx *ctx, T **dst, const T *src, size_t n) {
-    if (*dst) { cudaFree(*dst); *dst = nullptr; }
-    if (!n || !src) return 0;
-    SKC_CUDA(cudaMalloc((void **)dst, n * sizeof(T)));
-    SKC_CUDA(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
-    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    size_t &cap = ctx->uploadCap[(void *)dst];
+    if (!n || !src) {
+        if (*dst) { cudaFree(*dst); *dst = nullptr; }
+        cap = 0;
+        return 0;
+    }
+    if (!*dst || cap < n * sizeof(T)) {
+        if (*dst) { cudaFree(*dst); *dst = nullptr; }
+        cap = 0;
+        SKC_CUDA(cudaMalloc((void **)dst, n * sizeof(T)));
+        cap = n * sizeof(T);
+    }
+    SKC_CUDA(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));     // pageable source: staged before the call returns
     return 0;
 }
 
@@ -158,6 +168,7 @@ extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t 
     if (meshO2W) memcpy(ctx->meshO2W, meshO2W, 128);
     else { float id[32] = {1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1, 1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1}; memcpy(ctx->meshO2W, id, 128); }
     ctx->meshFlip = (reverseOrientation != 0) ^ (transformSwapsHandedness != 0);
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 

@@ -11,6 +11,7 @@
 #include <stdio.h>
 #include <string>
 #include <vector>
+#include <map>
 #include "../../include/skin_cuda.h"
 
 #define SKC_NS SKC_NSPECTRAL
@@ -26,6 +27,7 @@ struct skc_ctx {
     cudaEvent_t defEv0 = nullptr, defEv1 = nullptr;   // deferred stage timing of the irradiance pass
     cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute
     std::vector<cudaEvent_t> evPool;         // untimed events ordering copyStream against stream
+    std::map<void *, size_t> uploadCap;      // bytes allocated behind each uploaded scene array (skc_upload_bvh reuses them)
     bool stageOff = false;                   // skc_stage_begin/end are no-ops (work enqueued on auxStream without host synchronisation: skc_frame_prefetch)
     bool stageAccumulate = false;            // skc_stage_end adds to stageMs instead of overwriting (chunked passes)
     std::string err;

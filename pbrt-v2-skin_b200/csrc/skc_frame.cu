@@ -800,6 +800,37 @@ extern "C" int skc_frame_film_get(skc_ctx *ctx, float *pixels4) {
     return 0;
 }
 
+// ImageFilm::WriteImage's pixel arithmetic (film/image.cpp:178-213): XYZ -> RGB (core/spectrum.h:51-55), divide by the weight
+// sum, clamp at 0.  fp32, no contraction: the same values as host/skin_integrator.cpp skh_film_to_rgb.
+__global__ void __launch_bounds__(256) k_film_to_rgb(const float4 *__restrict__ film, uint32_t n, float *__restrict__ rgb) {
+    uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    float4 p = __ldg(&film[i]);
+    float r = 3.240479f * p.x - 1.537150f * p.y - 0.498535f * p.z;
+    float g = -0.969256f * p.x + 1.875991f * p.y + 0.041556f * p.z;
+    float b = 0.055648f * p.x - 0.204043f * p.y + 1.057311f * p.z;
+    if (p.w != 0.f) {
+        float invWt = 1.f / p.w;
+        r = fmaxf(0.f, r * invWt); g = fmaxf(0.f, g * invWt); b = fmaxf(0.f, b * invWt);
+    }
+    rgb[3 * i] = r; rgb[3 * i + 1] = g; rgb[3 * i + 2] = b;
+}
+
+extern "C" int skc_frame_film_rgb(skc_ctx *ctx, float *rgb3) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    skc_frame_state *f = ctx->frame;
+    if (!f) return skc_fail(ctx, "skc_frame_film_rgb: skc_frame_setup first");
+    uint32_t n = (uint32_t)f->desc.xres * (uint32_t)f->desc.yres;
+    float *d = (float *)skc_scratch(ctx, 18, (size_t)n * 3 * sizeof(float));
+    if (!d) return 1;
+    k_film_to_rgb<<<(n + 255) / 256, 256, 0, ctx->stream>>>(f->dFilm, n, d);
+    SKC_LAUNCHED("k_film_to_rgb");
+    SKC_CUDA(cudaMemcpyAsync(rgb3, d, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
 extern "C" int skc_frame_get_order(skc_ctx *ctx, uint64_t first, uint64_t count, uint64_t *streamIndex) {
     if (!ctx) return 1;
     skc_frame_state *f = ctx->frame;

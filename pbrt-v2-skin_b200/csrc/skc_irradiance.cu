@@ -267,10 +267,10 @@ int skc_ensure_points(skc_ctx *ctx, uint64_t n) {
 extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t nLights) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
-    if (ctx->lights) { cudaFree(ctx->lights); ctx->lights = nullptr; }
+    if (ctx->lights && ctx->nLights != nLights) { cudaFree(ctx->lights); ctx->lights = nullptr; }      // same count: the array is reused
     ctx->nLights = 0;
-    if (!nLights) return 0;
-    SKC_CUDA(cudaMalloc((void **)&ctx->lights, nLights * sizeof(skc_light)));
+    if (!nLights) { if (ctx->lights) { cudaFree(ctx->lights); ctx->lights = nullptr; } return 0; }
+    if (!ctx->lights) SKC_CUDA(cudaMalloc((void **)&ctx->lights, nLights * sizeof(skc_light)));
     SKC_CUDA(cudaMemcpyAsync(ctx->lights, lights, nLights * sizeof(skc_light), cudaMemcpyHostToDevice, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->nLights = nLights;

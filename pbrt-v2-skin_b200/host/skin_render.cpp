@@ -108,10 +108,8 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
     double t3 = now();
     // Mo + the subsurface term, the spectral sum and the film
     if (!dev(skc_frame_film_clear(ctx)) || !dev(skc_frame_render(ctx, 0, nSamples, sd.maxerror, sd.mix, nullptr))) return false;
-    std::vector<float> film((size_t)sd.xres * sd.yres * 4);
-    if (!dev(skc_frame_film_get(ctx, film.data()))) return false;
     rgb->resize((size_t)sd.xres * sd.yres * 3);
-    skh_film_to_rgb(film.data(), sd.xres, sd.yres, rgb->data());
+    if (!dev(skc_frame_film_rgb(ctx, rgb->data()))) return false;           // ImageFilm::WriteImage's XYZ -> RGB / weight on the device
     double t4 = now();
     st->buildSec = t1 - t0; st->materialSec = t2 - t1; st->preprocessSec = t3 - t2; st->renderSec = t4 - t3;
     st->nPoints = nPts; st->nSamples = nSamples; st->renderTasks = (uint32_t)fd.nTasks;

@@ -33,7 +33,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
            "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
-           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_get_order"]
+           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order"]
 
 
 class SkcError(RuntimeError):
@@ -108,6 +108,7 @@ def load_library():
     lib.skc_frame_film_clear.restype = i32; lib.skc_frame_film_clear.argtypes = [vp]
     lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
     lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
+    lib.skc_frame_film_rgb.restype = i32; lib.skc_frame_film_rgb.argtypes = [vp, vp]
     _lib = lib
     return lib
 
@@ -348,11 +349,19 @@ class SkinDevice:
     def frame_film_dev(self):
         return self.lib.skc_frame_film_dev(self.ctx)
 
-    def frame_film(self):
+    def frame_film(self, out=None):
+        """Film pixels [yres][xres]{Lxyz, weightSum}; out: a preallocated (e.g. pinned) array to copy into."""
         xres, yres = self._frame_res
-        px = np.empty((yres, xres, 4), np.float32)
+        px = np.empty((yres, xres, 4), np.float32) if out is None else out
         self._ck(self.lib.skc_frame_film_get(self.ctx, _ptr(px)))
         return px
+
+    def frame_rgb(self, out=None):
+        """The frame as ImageFilm::WriteImage computes it, converted on the device: RGB [yres][xres][3]."""
+        xres, yres = self._frame_res
+        rgb = np.empty((yres, xres, 3), np.float32) if out is None else out
+        self._ck(self.lib.skc_frame_film_rgb(self.ctx, _ptr(rgb)))
+        return rgb
 
     def pinned(self, shape, dtype):
         """numpy array over cudaHostAlloc'ed memory (freed with the device object)."""

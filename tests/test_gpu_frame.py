@@ -160,3 +160,12 @@ def test_prefetch_flow_is_bit_identical(dev, frame):
     La = dev.frame_render(0, half, hs.maxerror, hs.mix, want_L=True).copy()
     Lb = dev.frame_render(half, n - half, hs.maxerror, hs.mix, want_L=True).copy()
     assert np.array_equal(np.concatenate([La, Lb]).view(np.uint32), L0.view(np.uint32))
+
+
+def test_device_rgb_equals_host_conversion(dev, frame):
+    """skc_frame_film_rgb (XYZ -> RGB, / weight sum, clamp on the device) = skh_film_to_rgb of the downloaded film, bit for bit."""
+    hs, n = frame
+    dev.frame_film_clear()
+    dev.frame_render(0, n, hs.maxerror, hs.mix)
+    host = hs.film_to_rgb(dev.frame_film())
+    assert np.array_equal(dev.frame_rgb().view(np.uint32), host.view(np.uint32)) and host.max() > 0
