@@ -45,23 +45,43 @@ def main():
     args = ap.parse_args()
     import __graft_entry__ as ge
     pkg = ge.load_package()
-    dev = pkg.SkinDevice(0)
+    # several GPUs (first row): the parameter sets are independent, so the chunks are dealt round-robin over the
+    # ranks of a torchrun launch and nothing is exchanged but the timing (max over ranks) and the checksum
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = pkg.SkinDevice(local)
     specs, lps, opts = c5_parameter_sets(pkg, args.thicknesses, args.length)
     n = len(lps)
     ms, entries, wall0 = 0.0, 0, time.time()
     checksum = 0.0
-    for c0 in range(0, args.thicknesses, args.chunk):
+    for ci, c0 in enumerate(range(0, args.thicknesses, args.chunk)):
+        if ci % world != rank:
+            continue
         a, b = 30 * c0, 30 * min(c0 + args.chunk, args.thicknesses)
         d2, R, T, tot = dev.profile_batch(specs[2 * a:2 * b], lps[a:b], opts[a:b], resample=True)
         ms += dev.stage_ms("profile")
         entries = R.shape[1]
         checksum += float(tot.sum())
         assert np.all(np.isfinite(R)) and np.all(np.isfinite(T))
+    if world > 1:
+        import torch
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        c = torch.tensor([checksum, float(entries)], device="cuda", dtype=torch.float64); dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        checksum, entries = float(c[0].item()), int(round(float(c[1].item()) / world))
+        dist.destroy_process_group()
+        if rank != 0:
+            dev.close()
+            return
     grid = 2 * (2 * args.length)                      # transform size per side (zero-padded 2 x desiredLength x 2)
     fft_bytes = 3 * 2 * 2 * grid * grid * 16          # 3 transforms x 2 passes x (read + write) x complex double
     layer_bytes = 2 * 2 * (grid // 2) ** 2 * 8         # two layers, R and T grids, fp64
     bytes_per_profile = fft_bytes + layer_bytes + 3 * entries * 4
-    out = {"profiles": n, "desiredLength": args.length, "table_entries": entries, "device_ms": ms, "ms_per_profile": ms / n,
+    out = {"n_gpus": world, "profiles": n, "desiredLength": args.length, "table_entries": entries, "device_ms": ms, "ms_per_profile": ms / n,
            "profiles_per_s": n / (ms * 1e-3), "algorithmic_GB_per_profile": bytes_per_profile / 1e9,
            "algorithmic_GBps": bytes_per_profile * n / (ms * 1e-3) / 1e9, "wall_s_incl_host_copies": time.time() - wall0,
            "sum_of_totals": checksum}
