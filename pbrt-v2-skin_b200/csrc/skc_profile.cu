@@ -327,7 +327,10 @@ static uint32_t roundUpPow2(uint32_t v) { v--; v |= v >> 1; v |= v >> 2; v |= v 
 
 // the reference's std::set<OutEntry> keyed by distanceSquared: unique i*i+j*j <= extent^2 in
 // ascending order, first inserted (smallest i) wins (:316-330)
-static std::vector<uint2> uniqueRadii(uint32_t length) {
+static const std::vector<uint2> &uniqueRadii(uint32_t length) {
+    static std::map<uint32_t, std::vector<uint2>> cache;      // the list depends on the length only
+    auto it = cache.find(length);
+    if (it != cache.end()) return it->second;
     uint32_t extent = length - 1;
     std::map<uint32_t, uint2> m;
     for (uint32_t i = 0; i <= extent; i++)
@@ -335,7 +338,7 @@ static std::vector<uint2> uniqueRadii(uint32_t length) {
     std::vector<uint2> v;
     v.reserve(m.size());
     for (auto &kv : m) v.push_back(kv.second);
-    return v;
+    return cache[length] = std::move(v);
 }
 
 // Work areas of one GROUP of K sets: every array holds K consecutive per-set blocks and every kernel takes the set from
@@ -379,7 +382,7 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
         if (!layersPerSet[s]) return skc_fail(ctx, "skc_profile_batch: set %u has no layers", s);
     }
     if (length < 2 || length > 1024) return skc_fail(ctx, "skc_profile_batch: desiredLength %u out of range (2..1024)", length);
-    std::vector<uint2> radii = uniqueRadii(length);
+    const std::vector<uint2> &radii = uniqueRadii(length);
     uint32_t nEntries = (uint32_t)radii.size(), outLen = resample ? 2 * nEntries : nEntries;
     if (lenOut) *lenOut = outLen;
     if (!d2 && !R && !T && !totals) return 0;
