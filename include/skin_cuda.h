@@ -40,7 +40,12 @@ typedef struct {
     int32_t type, mesh, index, primitiveId;
 } skc_prim;
 
-/* shapes/sphere.h Sphere + lights/diffuse.h DiffuseAreaLight, as one 70-float record. */
+/* One light of scene->lights as a 70-float record.
+ *   radius > 0: shapes/sphere.h Sphere + lights/diffuse.h DiffuseAreaLight (the emitter sphere is also a BVH primitive).
+ *   radius < 0: a delta light without a shape -- radius = -1 PointLight (lights/point.cpp), -2 SpotLight
+ *     (lights/spot.cpp), -3 DistantLight (lights/distant.cpp); o2w / w2o = LightToWorld / WorldToLight; spot: zmin =
+ *     cosTotalWidth, zmax = cosFalloffStart; distant: (zmin, zmax, phiMax) = lightDir (world space, normalised); Lemit =
+ *     Intensity (point, spot) or L (distant); nSamples = 1; the other fields 0. */
 typedef struct {
     float o2w[16], w2o[16];            /* ObjectToWorld matrix and its inverse, row-major */
     float radius, zmin, zmax, phiMax;
