@@ -359,8 +359,34 @@ bool SceneDesc::LoadLines(const std::string &path) {
 }
 
 bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *out, std::string *err) {
-    if (sd.meshes.size() != 1) { *err = "the device path takes exactly one skin mesh"; return false; }
-    const TriangleMesh &mesh = sd.meshes[0];
+    if (sd.meshes.empty()) { *err = "no layeredskin trianglemesh in the scene"; return false; }
+    // The device holds ONE mesh.  Several Shape "trianglemesh" directives under the same layeredskin material are joined into
+    // one (vertices are already in world space, indices are offset); this is exact as long as the per-mesh state the device
+    // keeps once -- orientation flags, and ObjectToWorld when there are vertex normals to transform -- agrees.
+    std::vector<int> triOffset(sd.meshes.size(), 0);
+    if (sd.meshes.size() > 1) {
+        TriangleMesh &m = out->merged;
+        m = TriangleMesh();
+        const TriangleMesh &m0 = sd.meshes[0];
+        m.ObjectToWorld = m0.ObjectToWorld; m.ReverseOrientation = m0.ReverseOrientation; m.TransformSwapsHandedness = m0.TransformSwapsHandedness;
+        m.materialId = m0.materialId;
+        for (size_t k = 0; k < sd.meshes.size(); ++k) {
+            const TriangleMesh &mk = sd.meshes[k];
+            if (mk.ReverseOrientation != m0.ReverseOrientation || mk.TransformSwapsHandedness != m0.TransformSwapsHandedness || mk.n.empty() != m0.n.empty() ||
+                mk.uvs.empty() != m0.uvs.empty() ||
+                (!m0.n.empty() && memcmp(&mk.ObjectToWorld, &m0.ObjectToWorld, sizeof(Transform)) != 0)) {
+                *err = "several skin meshes that differ in orientation, in having normals / uvs, or (with normals) in their transform cannot be joined into the one mesh the device path holds";
+                return false;
+            }
+            triOffset[k] = m.ntris;
+            for (int v : mk.vertexIndex) m.vertexIndex.push_back(v + m.nverts);
+            m.p.insert(m.p.end(), mk.p.begin(), mk.p.end());
+            m.n.insert(m.n.end(), mk.n.begin(), mk.n.end());
+            m.uvs.insert(m.uvs.end(), mk.uvs.begin(), mk.uvs.end());
+            m.nverts += mk.nverts; m.ntris += mk.ntris;
+        }
+    }
+    const TriangleMesh &mesh = sd.meshes.size() > 1 ? out->merged : sd.meshes[0];
     // renderOptions->primitives order: emitter spheres, then the mesh triangles (api.cpp:1066-1070)
     // (a .pbrt file fixes the order itself: primOrder)
     std::vector<BBox> bounds;
@@ -368,14 +394,14 @@ bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *o
     std::vector<PrimRef> order = sd.primOrder;
     if (order.empty()) {
         for (size_t i = 0; i < sd.lights.size(); ++i) if (sd.lights[i].kind == 0) order.push_back(PrimRef{1, (int)i});
-        order.push_back(PrimRef{0, 0});
+        for (size_t k = 0; k < sd.meshes.size(); ++k) order.push_back(PrimRef{0, (int)k});
     }
     for (const PrimRef &r : order) {
         if (r.kind == 1) {
             bounds.push_back(sd.lights[r.index].WorldBound());
             skc_prim p = {1, -1, (int32_t)r.index, (int32_t)prims.size()};
             prims.push_back(p);
-        } else for (int t = 0; t < mesh.ntris; ++t) {
+        } else for (int t = triOffset[r.index], tEnd = triOffset[r.index] + sd.meshes[r.index].ntris; t < tEnd; ++t) {
             const V3 &p1 = mesh.p[mesh.vertexIndex[3 * t]], &p2 = mesh.p[mesh.vertexIndex[3 * t + 1]], &p3 = mesh.p[mesh.vertexIndex[3 * t + 2]];
             bounds.push_back(Union(BBox(p1, p2), p3));   // trianglemesh.inl:45-51
             skc_prim p = {0, 0, t, (int32_t)prims.size()};

@@ -144,7 +144,8 @@ struct BuiltScene {
     std::vector<skc_prim> prims;              // BVH leaf order
     std::vector<skc_bvh_node> nodes;
     std::vector<skc_light> lights;
-    const TriangleMesh *mesh = nullptr;       // single skin mesh supported on the device path
+    TriangleMesh merged;                      // several skin meshes joined into one (BuildScene)
+    const TriangleMesh *mesh = nullptr;       // the one mesh the device holds: the scene's only mesh, or `merged`
 };
 // CreatePointLight / CreateSpotLight / CreateDistantLight (lights/point.cpp:63-70, spot.cpp:81-101, distant.cpp:67-75): l2w is
 // the CTM at the LightSource directive

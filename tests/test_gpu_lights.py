@@ -41,7 +41,7 @@ def test_light_records_bit_exact(pkg, golden, ext):
 def test_coloured_rgb_to_spectrum(pkg, tmp_path):
     """Spectrum::FromRGB for non-grey values (core/spectrum.cpp:103-145): the three branches pick the right basis pair, the
     result is non-negative, and a grey value reduces to the white basis."""
-    src = open(os.path.join(ROOT, "scenes", "skin_lights.scene")).read().replace("pointlight 1.5 -3 1.5 40 40 40", "pointlight 1.5 -3 1.5 40 10 25")
+    src = open(os.path.join(ROOT, "scenes", "skin_lights.scene")).read().replace("pointlight 1.5 -3 1.5 30 40 55", "pointlight 1.5 -3 1.5 40 10 25")
     src = src.replace("mesh head.mesh.bin", "mesh %s" % os.path.join(ROOT, "scenes", "head.mesh.bin"))
     (tmp_path / "c.scene").write_text(src)
     hs = pkg.HostScene(str(tmp_path / "c.scene"))

@@ -247,3 +247,30 @@ def test_tessellatesurfacepoints_renderer_and_pointsfile(pkg, head_pbrt, tmp_pat
     (tmp_path / "missing.pbrt").write_text(b.replace('"pts.bin"', '"nothere.bin"'))
     img_missing, _ = pkg.pbrt_render(str(tmp_path / "missing.pbrt"), n_cores=1)
     assert np.allclose(img_missing, img_tess, rtol=1e-5, atol=1e-6 * img_tess.max())
+
+
+def test_several_skin_shapes_join_into_the_device_mesh(pkg, tmp_path):
+    """Two Shape "trianglemesh" directives under one layeredskin material (the slab's top and bottom quad given separately)
+    build the same device scene as the one-mesh file: vertices, indices, primitive list and BVH byte for byte."""
+    import make_slab_mesh
+    n = 12
+    P, idx = make_slab_mesh.slab(n)
+    nv = (n + 1) ** 2
+    fmt = lambda a: " ".join("%.9g" % float(v) for v in a.ravel())
+    head = ('SurfaceIntegrator "multipolesubsurface" "float minsampledistance" 0.02\nWorldBegin\n' + LIGHT +
+            'Material "layeredskin" "skinlayer layers" [0.25e6 1.4 20e6 1.4]\n')
+    one = head + 'Shape "trianglemesh" "point P" [%s] "integer indices" [%s]\nWorldEnd\n' % (fmt(P), " ".join(map(str, idx.ravel())))
+    top, bot = idx[:len(idx) // 2], idx[len(idx) // 2:] - nv
+    two = head + 'Shape "trianglemesh" "point P" [%s] "integer indices" [%s]\n' % (fmt(P[:nv]), " ".join(map(str, top.ravel()))) + \
+        'Shape "trianglemesh" "point P" [%s] "integer indices" [%s]\nWorldEnd\n' % (fmt(P[nv:]), " ".join(map(str, bot.ravel())))
+    (tmp_path / "one.pbrt").write_text(one); (tmp_path / "two.pbrt").write_text(two)
+    a, b = pkg.HostScene(str(tmp_path / "one.pbrt")), pkg.HostScene(str(tmp_path / "two.pbrt"))
+    assert b.n_tris == 4 * n * n and b.n_verts == 2 * nv
+    for k in ("nodes", "prims", "P", "idx", "lights"):
+        assert np.array_equal(bytes_of(getattr(a, k)), bytes_of(getattr(b, k))), k
+    # meshes that cannot share the device's one transform / orientation are refused
+    bad = two.replace('Shape "trianglemesh" "point P" [%s]' % fmt(P[nv:]), 'ReverseOrientation\nShape "trianglemesh" "point P" [%s]' % fmt(P[nv:]))
+    (tmp_path / "bad.pbrt").write_text(bad)
+    with pytest.raises(pkg.SkcError) as e:
+        pkg.HostScene(str(tmp_path / "bad.pbrt"))
+    assert "cannot be joined" in str(e.value)
