@@ -68,7 +68,7 @@ struct skc_frame_state {
     bool samplesReady = false;
     // skc_frame_prefetch: the part of the frame that does not depend on Preprocess, enqueued on auxStream
     bool prefetched = false;
-    cudaEvent_t evP0 = nullptr, evP1 = nullptr, evDone = nullptr;
+    cudaEvent_t evP0 = nullptr, evP1 = nullptr, evDone = nullptr, evHits = nullptr;   // evHits: closest hits done (what Mo needs); evP1: direct terms done (what the spectral sum needs)
 };
 
 void skc_frame_release(skc_ctx *ctx) {
@@ -76,7 +76,7 @@ void skc_frame_release(skc_ctx *ctx) {
     if (!f) return;
     void *ptrs[] = {f->dWin, f->dSeed, f->dPixBase, f->dXY, f->dArrays, f->dFilm, f->dConsts, f->dOrder};
     for (void *p : ptrs) if (p) cudaFree(p);
-    for (cudaEvent_t e : {f->evP0, f->evP1, f->evDone}) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : {f->evP0, f->evP1, f->evDone, f->evHits}) if (e) cudaEventDestroy(e);
     delete f;
     ctx->frame = nullptr;
 }
@@ -690,11 +690,13 @@ extern "C" int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t coun
 }
 
 // Scene::Intersect for the camera rays and EstimateDirect's terms (everything of Li that does not need the octree)
-static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, uint64_t count, skc_hit *dHits, float4 *dFrame, float4 *dTerms) {
+static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, uint64_t count, skc_hit *dHits, float4 *dFrame, float4 *dTerms,
+                              cudaEvent_t hitsDone = nullptr) {
     const FrameLayout &lay = f->lay;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
     skc_stage_end(ctx, 3);
+    if (hitsDone) SKC_CUDA(cudaEventRecord(hitsDone, ctx->stream));
     RhoBxdf mf;
     float rms = f->desc.roughness < 1e-3f ? 1e-3f : f->desc.roughness;      // Beckmann::Beckmann (reflection.h:509-514)
     mf.rms2 = rms * rms; mf.rcpRMS2 = 1 / mf.rms2; mf.etaI = 1.f; mf.etaT = f->desc.ior; mf.fixedFresnel = 0;
@@ -721,7 +723,8 @@ extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
     cudaSetDevice(ctx->device);
     skc_frame_state *f = ctx->frame;
     if (!f) return skc_fail(ctx, "skc_frame_prefetch: skc_frame_setup first");
-    if (!f->evP0) { SKC_CUDA(cudaEventCreate(&f->evP0)); SKC_CUDA(cudaEventCreate(&f->evP1)); SKC_CUDA(cudaEventCreateWithFlags(&f->evDone, cudaEventDisableTiming)); }
+    if (!f->evP0) { SKC_CUDA(cudaEventCreate(&f->evP0)); SKC_CUDA(cudaEventCreate(&f->evP1)); SKC_CUDA(cudaEventCreateWithFlags(&f->evDone, cudaEventDisableTiming));
+                     SKC_CUDA(cudaEventCreateWithFlags(&f->evHits, cudaEventDisableTiming)); }
     const uint64_t count = f->nSamples;
     skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 17, count * sizeof(skc_hit));
     float4 *dFrame = (float4 *)skc_scratch(ctx, 13, count * 2 * sizeof(float4));
@@ -733,7 +736,7 @@ extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
     ctx->stream = ctx->auxStream; ctx->stageOff = true;
     cudaEventRecord(f->evP0, ctx->stream);
     int rc = skc_frame_samples(ctx);
-    if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms);
+    if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms, f->evHits);
     cudaEventRecord(f->evP1, ctx->stream);
     ctx->stream = mainStream; ctx->stageOff = false;
     if (rc) return 1;
@@ -755,7 +758,8 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * lay.slots * 3 * sizeof(float4));
     if (!dHits || !dL || !dFrame || !dTerms) return 1;
     const bool usePrefetch = f->prefetched && first == 0 && count == f->nSamples;
-    if (f->prefetched) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, f->evP1, 0));    // hits, frames and direct-lighting terms are (being) made on auxStream
+    // hits, frames and direct-lighting terms are (being) made on auxStream: Mo needs the hits only, the spectral sum the terms too
+    if (f->prefetched) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, usePrefetch ? f->evHits : f->evP1, 0));
     f->prefetched = false;
     if (!usePrefetch) if (frameHitsAndDirect(ctx, f, first, count, dHits, dFrame, dTerms)) return 1;
     if (ctx->otGeo && ctx->otNodes) {
@@ -763,6 +767,7 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     } else {
         SKC_CUDA(cudaMemsetAsync(dL, 0, count * SKC_NS * sizeof(float), ctx->stream));    // no octree: `if (bssrdf && octree)` (multipolesubsurface.cpp:267)
     }
+    if (usePrefetch) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, f->evP1, 0));
     skc_stage_begin(ctx);
     k_frame_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, f->dConsts, dHits, dTerms,
                                                                                                  f->dXY, f->dOrder, first, count, dL, f->dFilm);
