@@ -113,7 +113,7 @@ extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t 
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     if (!nodes || !nNodes || !prims || !nPrims) return skc_fail(ctx, "skc_upload_bvh: empty tree");
-    cudaStreamSynchronize(ctx->auxStream);          // a prefetch still walking the old tree (skc_frame_prefetch) finishes first
+    cudaStreamSynchronize(ctx->prefetchStream);     // a prefetch still walking the old tree (skc_frame_prefetch) finishes first
     std::vector<float4> dn(2 * (size_t)nNodes), dp(3 * (size_t)nPrims);
     std::vector<int4> info(nPrims);
     for (uint32_t i = 0; i < nNodes; ++i) {

@@ -23,6 +23,7 @@ struct skc_ctx {
     int smCount = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t prefetchStream = nullptr;   // skc_frame_prefetch: sampler stream, closest hits, direct-lighting terms beside Preprocess (lowest priority)
     cudaStream_t auxStream = nullptr;        // octree topology while the irradiance pass runs on `stream` (skc_preprocess*)
     cudaEvent_t defEv0 = nullptr, defEv1 = nullptr;   // deferred stage timing of the irradiance pass
     cudaStream_t copyStream = nullptr;       // host<->device copies of the host-buffer entry points, overlapped with compute

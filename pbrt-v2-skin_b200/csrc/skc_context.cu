@@ -70,6 +70,7 @@ extern "C" skc_ctx *skc_create(int device) {
     if (cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prioMain) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithPriority(&ctx->auxStream, cudaStreamNonBlocking, prioAux) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&ctx->prefetchStream, cudaStreamNonBlocking, prioAux) != cudaSuccess ||
         cudaEventCreate(&ctx->defEv0) != cudaSuccess || cudaEventCreate(&ctx->defEv1) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         skc_fail(nullptr, "skc_create: stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -98,6 +99,8 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamDestroy(ctx->copyStream);
     cudaStreamSynchronize(ctx->auxStream);
     cudaStreamDestroy(ctx->auxStream);
+    cudaStreamSynchronize(ctx->prefetchStream);
+    cudaStreamDestroy(ctx->prefetchStream);
     cudaEventDestroy(ctx->defEv0); cudaEventDestroy(ctx->defEv1);
     cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -66,7 +66,7 @@ struct skc_frame_state {
     uint32_t *dOrder = nullptr;   // render order: pixel slot -> pixel of the sampler stream (Z-order inside each task window)
     FrameConsts *dConsts = nullptr;
     bool samplesReady = false;
-    // skc_frame_prefetch: the part of the frame that does not depend on Preprocess, enqueued on auxStream
+    // skc_frame_prefetch: the part of the frame that does not depend on Preprocess, enqueued on prefetchStream
     bool prefetched = false;
     cudaEvent_t evP0 = nullptr, evP1 = nullptr, evDone = nullptr, evHits = nullptr;   // evHits: closest hits done (what Mo needs); evP1: direct terms done (what the spectral sum needs)
 };
@@ -731,9 +731,9 @@ extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
     float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * f->lay.slots * 3 * sizeof(float4));
     if (!dHits || !dFrame || !dTerms) return 1;
     SKC_CUDA(cudaEventRecord(f->evDone, ctx->stream));                       // earlier consumers of these buffers
-    SKC_CUDA(cudaStreamWaitEvent(ctx->auxStream, f->evDone, 0));
+    SKC_CUDA(cudaStreamWaitEvent(ctx->prefetchStream, f->evDone, 0));
     cudaStream_t mainStream = ctx->stream;
-    ctx->stream = ctx->auxStream; ctx->stageOff = true;
+    ctx->stream = ctx->prefetchStream; ctx->stageOff = true;
     cudaEventRecord(f->evP0, ctx->stream);
     int rc = skc_frame_samples(ctx);
     if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms, f->evHits);
@@ -758,7 +758,7 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * lay.slots * 3 * sizeof(float4));
     if (!dHits || !dL || !dFrame || !dTerms) return 1;
     const bool usePrefetch = f->prefetched && first == 0 && count == f->nSamples;
-    // hits, frames and direct-lighting terms are (being) made on auxStream: Mo needs the hits only, the spectral sum the terms too
+    // hits, frames and direct-lighting terms are (being) made on prefetchStream: Mo needs the hits only, the spectral sum the terms too
     if (f->prefetched) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, usePrefetch ? f->evHits : f->evP1, 0));
     f->prefetched = false;
     if (!usePrefetch) if (frameHitsAndDirect(ctx, f, first, count, dHits, dFrame, dTerms)) return 1;
