@@ -79,7 +79,7 @@ extern "C" skc_ctx *skc_create(int device) {
     }
     if (const char *k = getenv("SKC_MO_KERNEL")) ctx->moPacket = strcmp(k, "warp") != 0;
     if (const char *k = getenv("SKC_MO_SORT")) ctx->moSort = atoi(k);
-    if (const char *k = getenv("SKC_MO_SPLIT")) ctx->moSplit = atoi(k) == 1 ? 1 : atoi(k) == 2 ? 2 : 0;
+    if (const char *k = getenv("SKC_MO_SPLIT")) ctx->moSplit = atoi(k) == 1 ? 1 : atoi(k) == 2 ? 2 : atoi(k) == 4 ? 4 : 0;
     return ctx;
 }
 

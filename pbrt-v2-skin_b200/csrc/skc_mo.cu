@@ -175,6 +175,9 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 // kernel above spends 30 separate lines per contribution (one per wavelength) and is bound by L1 wavefronts.
 // Each lane keeps its 30 wavelength sums in registers; the result is transposed through shared memory.
 #define MOP_WARPS 4
+#ifndef MOP_CTAS4
+#define MOP_CTAS4 8          // resident CTAs per SM of the four-warps-per-packet instance (12 at 40 registers spills: 19.1 vs 13.6 ms on a 1/8 frame)
+#endif
 #ifndef MOP_CTAS1
 #define MOP_CTAS1 7          // resident CTAs per SM of the one-warp-per-packet instance (72 registers)
 #endif
@@ -235,7 +238,7 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
 // set the length of every launch that has few packets per warp (multi-GPU shards) -- and 16 accumulators instead of
 // 30 leave room for more resident warps.
 template <bool COUNT, int SPLIT, bool PERM>
-__global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : 8) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
+__global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : (SPLIT == 2 ? 8 : MOP_CTAS4)) k_mo_packet(MoTree tr, MoTables T, const float *__restrict__ p3, uint64_t strideFloats,
                                                              const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                              uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
                                                              uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm) {
@@ -505,10 +508,13 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         // one warp per packet when there are plenty of packets per resident warp; two warps per packet (half the spectrum each)
         // when a launch is short (multi-GPU shards), where the heaviest packets' run time is what the launch waits for.
         // Measured on skin.scene: 28 packets/warp 60.4 vs 61.9 ms, 14 packets/warp 38.1 vs 35.7 ms, 3.5 packets/warp 23.0 vs 17.5 ms
-        int split = ctx->moSplit ? ctx->moSplit : ((n + 31) / 32 >= 20ull * ctx->smCount * 7 * MOP_WARPS ? 1 : 2);
-        if (split == 2) pb = std::min<uint64_t>(2 * ((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32)), (uint64_t)ctx->smCount * 8);
+        // ... and four warps per packet (a quarter of the spectrum each) below 5 packets per resident warp: 1/8 frame 15.5 -> 13.6 ms, 1/4 frame 22.7 vs 22.5 ms
+        const uint64_t nPk = (n + 31) / 32, resident = (uint64_t)ctx->smCount * 8 * MOP_WARPS;
+        int split = ctx->moSplit ? ctx->moSplit : (nPk >= 20ull * ctx->smCount * 7 * MOP_WARPS ? 1 : (nPk < 5 * resident ? 4 : 2));
+        if (split >= 2) pb = std::min<uint64_t>((uint64_t)split * ((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32)), (uint64_t)ctx->smCount * (split == 4 ? MOP_CTAS4 : 8));
 #define MOP_GO(C, S, P) k_mo_packet<C, S, P><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm)
-        if (split == 2) { if (cntDev) { if (perm) MOP_GO(true, 2, true); else MOP_GO(true, 2, false); } else { if (perm) MOP_GO(false, 2, true); else MOP_GO(false, 2, false); } }
+        if (split == 4) { if (cntDev) { if (perm) MOP_GO(true, 4, true); else MOP_GO(true, 4, false); } else { if (perm) MOP_GO(false, 4, true); else MOP_GO(false, 4, false); } }
+        else if (split == 2) { if (cntDev) { if (perm) MOP_GO(true, 2, true); else MOP_GO(true, 2, false); } else { if (perm) MOP_GO(false, 2, true); else MOP_GO(false, 2, false); } }
         else            { if (cntDev) { if (perm) MOP_GO(true, 1, true); else MOP_GO(true, 1, false); } else { if (perm) MOP_GO(false, 1, true); else MOP_GO(false, 1, false); } }
 #undef MOP_GO
         SKC_LAUNCHED("k_mo_packet");

@@ -420,7 +420,7 @@ def test_mo_packet_one_and_two_warps_per_packet_agree(pkg, tiny):
     each, the variant short launches use) performs the same arithmetic per wavelength: bit-identical rows."""
     g = tiny
     out = []
-    for split in ("1", "2"):
+    for split in ("1", "2", "4"):
         os.environ["SKC_MO_SPLIT"] = split
         try:
             d = pkg.SkinDevice(0)
@@ -434,7 +434,7 @@ def test_mo_packet_one_and_two_warps_per_packet_agree(pkg, tiny):
             out.append(L.copy())
         finally:
             d.close()
-    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32)) and np.array_equal(out[0].view(np.uint32), out[2].view(np.uint32))
     assert out[0].max() > 0
 
 
