@@ -169,3 +169,33 @@ def test_device_rgb_equals_host_conversion(dev, frame):
     dev.frame_render(0, n, hs.maxerror, hs.mix)
     host = hs.film_to_rgb(dev.frame_film())
     assert np.array_equal(dev.frame_rgb().view(np.uint32), host.view(np.uint32)) and host.max() > 0
+
+
+def test_frame_edge_cases_through_the_pbrt_entry(pkg, tmp_path):
+    """Edge cases of a whole frame through `pbrt scene.pbrt` (parser + RenderScene): a camera that sees nothing (every sample
+    misses: black image, all weights present), a camera inside the emitter's glow only (emitter hit, no skin), --quick
+    (film / 4, one sample per pixel, light samples / 4), and a one-pixel film."""
+    src = open(os.path.join(ROOT, "scenes", "skin_ld4.pbrt")).read()
+    src = src.replace('Include "geometry/head.pbrt"', 'Include "%s"' % os.path.join(ROOT, "scenes", "geometry", "head.pbrt"))
+    if not os.path.exists(os.path.join(ROOT, "scenes", "geometry", "head.pbrt")):
+        import sys
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import mesh_bin_to_pbrt
+        mesh_bin_to_pbrt.convert(os.path.join(ROOT, "scenes", "head.mesh.bin"), os.path.join(ROOT, "scenes", "geometry", "head.pbrt"))
+
+    def render(text, name, **kw):
+        p = tmp_path / name
+        p.write_text(text)
+        return pkg.pbrt_render(str(p), n_cores=1, **kw)
+
+    away = src.replace("LookAt 0.491171 -4.4848 0.897406 0 0 0 0 0 1", "LookAt 0.491171 -4.4848 0.897406 0.5 -20 0.9 0 0 1")
+    rgb, st = render(away, "away.pbrt")
+    assert rgb.shape == (27, 48, 3) and np.all(rgb == 0) and st["points"] > 0
+    at_light = src.replace("LookAt 0.491171 -4.4848 0.897406 0 0 0 0 0 1", "LookAt 0.5 -4.5 0.9 -0.0859535 -4.92443 5.00725 0 1 0")
+    rgb, _ = render(at_light, "light.pbrt")
+    assert rgb.max() > 100 and np.isfinite(rgb).all(), "the emitter's radiance reaches the film"
+    rgb, st = render(src, "quick.pbrt", quick=True)
+    assert rgb.shape == (6, 12, 3) and st["samples"] == 13 * 7 * 1 and rgb.max() > 0
+    one = src.replace('"integer xresolution" [48] "integer yresolution" [27]', '"integer xresolution" [1] "integer yresolution" [1]')
+    rgb, st = render(one, "one.pbrt")
+    assert rgb.shape == (1, 1, 3) and np.isfinite(rgb).all() and st["samples"] == 2 * 2 * 4
