@@ -20,6 +20,7 @@
 #include "skc_internal.h"
 
 #define OTS_LEVELS 21
+#define OTS_FAST_LEVELS 16      // levels the first, shorter sort covers
 #define OTS_BLOCK 256
 
 struct OtsBounds { float mnx, mny, mnz, mxx, mxy, mxz; };
@@ -62,8 +63,10 @@ __device__ __forceinline__ int otsCommonLevels(unsigned long long a, unsigned lo
 
 // info[i] = depth | lo << 8 | leafCount << 16 ; depth = level of the leaf holding sorted point i, lo = first level at
 // which i's path differs from i-1's (0 for i = 0), leafCount = points in that leaf (valid where lo <= depth)
+// sortedLevels: the keys are sorted on their first sortedLevels levels only (see skc_octree_topology_sorted); cells of deeper
+// levels are then not contiguous, so a leaf deeper than that cannot be recognised here and is reported through `overflow`.
 __global__ void __launch_bounds__(256) k_leaf_depth(const unsigned long long *__restrict__ keys, uint32_t n,
-                                                    uint32_t *__restrict__ info, uint32_t *__restrict__ overflow) {
+                                                    uint32_t *__restrict__ info, uint32_t *__restrict__ overflow, int sortedLevels) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     unsigned long long k = keys[i];
@@ -74,7 +77,7 @@ __global__ void __launch_bounds__(256) k_leaf_depth(const unsigned long long *__
         cr[t] = i + t + 1 < n ? otsCommonLevels(k, keys[i + t + 1]) : -1;
     }
     int depth = -1, count = 0;
-    for (int l = 0; l <= OTS_LEVELS; ++l) {
+    for (int l = 0; l <= sortedLevels; ++l) {
         int c = 1;
 #pragma unroll
         for (int t = 0; t < 8; ++t) c += (cl[t] >= l) + (cr[t] >= l);
@@ -186,24 +189,34 @@ int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32
     OtsBounds root = {hb[0], hb[1], hb[2], hb[3], hb[4], hb[5]};
     unsigned grid = (n + 255) / 256;
     SKC_CUDA(cudaMemsetAsync(small, 0, (OTS_LEVELS + 4) * sizeof(uint32_t), ctx->stream));
-    k_path_keys<<<grid, 256, 0, ctx->stream>>>(ctx->ipPosArea, n, root, k0, v0);
-    SKC_LAUNCHED("k_path_keys");
-    dk = cub::DoubleBuffer<unsigned long long>(k0, k1);
-    dv = cub::DoubleBuffer<uint32_t>(v0, v1);
-    SKC_CUDA(cub::DeviceRadixSort::SortPairs(temp, tempBytes, dk, dv, (int)n, 0, 3 * OTS_LEVELS, ctx->stream));
-    ctx->launches += 8;
-    const unsigned long long *keys = dk.Current();
-    const uint32_t *idx = dv.Current();
-    k_leaf_depth<<<grid, 256, 0, ctx->stream>>>(keys, n, info, small);
-    SKC_LAUNCHED("k_leaf_depth");
-    k_level_counts<<<nBlocks, OTS_BLOCK, 0, ctx->stream>>>(info, n, nBlocks, blockCount);
-    SKC_LAUNCHED("k_level_counts");
-    k_level_scan<<<OTS_LEVELS + 1, 1024, 0, ctx->stream>>>(blockCount, nBlocks, small + 1);
-    SKC_LAUNCHED("k_level_scan");
+    // First try: sort on the first OTS_FAST_LEVELS levels only (48 of the 63 key bits: 6 radix passes instead of 8).  Every
+    // cell down to that level is a contiguous run, which is all k_leaf_depth needs when no leaf lies deeper -- the usual case
+    // (skin.scene: 15 levels); a deeper tree raises the overflow flag and the keys are sorted again in full.
+    const unsigned long long *keys = nullptr;
+    const uint32_t *idx = nullptr;
     uint32_t h[OTS_LEVELS + 2];
-    SKC_CUDA(cudaMemcpyAsync(h, small, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
-    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (h[0]) return 2;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const int sortedLevels = attempt == 0 ? OTS_FAST_LEVELS : OTS_LEVELS;
+        SKC_CUDA(cudaMemsetAsync(small, 0, (OTS_LEVELS + 4) * sizeof(uint32_t), ctx->stream));
+        k_path_keys<<<grid, 256, 0, ctx->stream>>>(ctx->ipPosArea, n, root, k0, v0);
+        SKC_LAUNCHED("k_path_keys");
+        dk = cub::DoubleBuffer<unsigned long long>(k0, k1);
+        dv = cub::DoubleBuffer<uint32_t>(v0, v1);
+        SKC_CUDA(cub::DeviceRadixSort::SortPairs(temp, tempBytes, dk, dv, (int)n, 3 * (OTS_LEVELS - sortedLevels), 3 * OTS_LEVELS, ctx->stream));
+        ctx->launches += 8;
+        keys = dk.Current();
+        idx = dv.Current();
+        k_leaf_depth<<<grid, 256, 0, ctx->stream>>>(keys, n, info, small, sortedLevels);
+        SKC_LAUNCHED("k_leaf_depth");
+        k_level_counts<<<nBlocks, OTS_BLOCK, 0, ctx->stream>>>(info, n, nBlocks, blockCount);
+        SKC_LAUNCHED("k_level_counts");
+        k_level_scan<<<OTS_LEVELS + 1, 1024, 0, ctx->stream>>>(blockCount, nBlocks, small + 1);
+        SKC_LAUNCHED("k_level_scan");
+        SKC_CUDA(cudaMemcpyAsync(h, small, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (!h[0]) break;
+        if (attempt == 1) return 2;
+    }
     OtsLevels lv;
     levelStart.clear();
     uint32_t total = 0;

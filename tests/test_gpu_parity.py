@@ -375,6 +375,32 @@ def test_octree_sorted_topology_equals_levelwise(dev, scene):
     assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
 
 
+def test_octree_deep_clusters_take_the_full_sort(dev, scene):
+    """The sorted builder first orders the points on their 16-level path prefix only; a tree with leaves deeper than that
+    (here: 12 points inside a ball of 3e-6 of the bounds -> a chain of 17-19 levels) must notice and sort the full 21-level
+    keys; a cluster tighter than 2^-21 of the bounds falls through to the level-by-level builder.  All three agree with the
+    level-by-level builder in node count, root and Mo."""
+    g = scene
+    rng = np.random.RandomState(11)
+    for radius in (3e-6, 1e-8):
+        pts = g.irradiance_points[:4000].copy()
+        c = pts["p"][100].copy()
+        ext = float((pts["p"].max(0) - pts["p"].min(0)).max())
+        pts["p"][200:212] = c + (rng.rand(12, 3).astype(np.float32) - 0.5) * np.float32(radius * ext)
+        dev.set_irradiance_points(pts)
+        q = np.ascontiguousarray(pts["p"][190:260])
+        os.environ["SKC_OCTREE_LEVELWISE"] = "1"
+        try:
+            n0, root0, _ = dev.build_octree()
+            mo0 = dev.mo(q, g.max_error)
+        finally:
+            del os.environ["SKC_OCTREE_LEVELWISE"]
+        n1, root1, _ = dev.build_octree()
+        mo1 = dev.mo(q, g.max_error)
+        assert n0 == n1 and np.array_equal(root0.view(np.uint32), root1.view(np.uint32))
+        assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
+
+
 def test_preprocess_one_call_equals_staged_calls(dev, scene):
     """skc_preprocess (irradiance pass + octree topology overlapped on two streams) followed by
     skc_build_octree_finalize gives bit-identical irradiance rows, octree root and Mo to skc_irradiance followed by
