@@ -441,11 +441,51 @@ __device__ __forceinline__ float lobeValue(float4 c, float Kr, float Kt) {
     if (c.z == -2.f) return c.x;                       // Lambertian::f
     return ((Kr * c.x) * c.y) * c.z / c.w;             // Microfacet::f: R * D * G * F / (4 cos cos)
 }
+// UniformSampleAllLights (integrator.cpp:47-75) of one camera sample in one spectral channel, from k_direct_terms' factors
+__device__ __forceinline__ float directSum(const skc_light *__restrict__ lights, const FrameLayout &lay, const float4 *__restrict__ terms,
+                                           uint64_t s, int lane, float Kr, float Kt) {
+    float Ldir = 0.f;
+    uint64_t t = s * lay.slots;
+    for (uint32_t i = 0; i < lay.nLights; ++i) {
+        float Le = __ldg(&lights[i].Lemit[lane]);
+        const bool delta = lights[i].radius < 0.f;
+        float Ld = 0.f;
+        for (uint32_t j = 0; j < lay.nS[i]; ++j, ++t) {
+            float4 T0 = __ldg(&terms[3 * t]), T1 = __ldg(&terms[3 * t + 1]), T2 = __ldg(&terms[3 * t + 2]);
+            float est = 0.f;
+            if (delta) {                                                   // Li = Intensity * Falloff / DistanceSquared (lights/point.cpp:55, spot.cpp:58)
+                if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * ((Le * T1.z) / T1.y)) * T1.x;
+                Ld += est;
+                continue;
+            }
+            if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * Le) * T1.x;
+            if (T2.w != 0.f) est += (((lobeValue(T2, Kr, Kt) * Le) * T1.y) * T1.z) / T1.w;
+            Ld += est;
+        }
+        Ldir += Ld / (float)lay.nS[i];
+    }
+    return Ldir;
+}
+
+// The direct-lighting sum of every sample as its own pass (prefetch flow: it runs on the prefetch stream beside Mo, and
+// k_frame_sum then only adds the row): Ldir[s][lane], zero for samples that hit nothing.
+__global__ void __launch_bounds__(FS_WARPS * 32) k_direct_sum(const skc_light *__restrict__ lights, FrameLayout lay, const FrameConsts *__restrict__ C,
+                                                             const skc_hit *__restrict__ hits, const float4 *__restrict__ terms, uint64_t n,
+                                                             float *__restrict__ Ldir) {
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint64_t s = (uint64_t)blockIdx.x * FS_WARPS + warp;
+    if (s >= n || lane >= SKC_NS) return;
+    float v = 0.f;
+    if (__float_as_int(__ldg(reinterpret_cast<const float *>(hits + s)))) v = directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane]);
+    Ldir[s * SKC_NS + lane] = v;
+}
+
 __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const skc_light *__restrict__ lights, FrameLayout lay,
                                                             const FrameConsts *__restrict__ C, const skc_hit *__restrict__ hits,
                                                             const float4 *__restrict__ terms, const float2 *__restrict__ xy,
                                                             const uint32_t *__restrict__ order, uint64_t first,
-                                                            uint64_t n, float *__restrict__ Lrows, float4 *__restrict__ film) {
+                                                            uint64_t n, float *__restrict__ Lrows, float4 *__restrict__ film,
+                                                            const float *__restrict__ LdirRows) {
     __shared__ float sL[FS_WARPS][32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t s = (uint64_t)blockIdx.x * FS_WARPS + warp;
@@ -460,27 +500,8 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
             if (dot3(nn, wo) > 0.f) Lc += bv.spheres[__float_as_int(c.z)].Lemit[lane];
         }
         Lc += Lrows[s * SKC_NS + lane];       // subsurface term (0 for non-subsurface hits)
-        // UniformSampleAllLights (integrator.cpp:47-75)
-        float Ldir = 0.f, Kr = C->Kr[lane], Kt = C->Kt[lane];
-        uint64_t t = s * lay.slots;
-        for (uint32_t i = 0; i < lay.nLights; ++i) {
-            float Le = __ldg(&lights[i].Lemit[lane]);
-            const bool delta = lights[i].radius < 0.f;
-            float Ld = 0.f;
-            for (uint32_t j = 0; j < lay.nS[i]; ++j, ++t) {
-                float4 T0 = __ldg(&terms[3 * t]), T1 = __ldg(&terms[3 * t + 1]), T2 = __ldg(&terms[3 * t + 2]);
-                float est = 0.f;
-                if (delta) {                                                   // Li = Intensity * Falloff / DistanceSquared (lights/point.cpp:55, spot.cpp:58)
-                    if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * ((Le * T1.z) / T1.y)) * T1.x;
-                    Ld += est;
-                    continue;
-                }
-                if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * Le) * T1.x;
-                if (T2.w != 0.f) est += (((lobeValue(T2, Kr, Kt) * Le) * T1.y) * T1.z) / T1.w;
-                Ld += est;
-            }
-            Ldir += Ld / (float)lay.nS[i];
-        }
+        // UniformSampleAllLights (integrator.cpp:47-75): summed here, or already by k_direct_sum (same arithmetic, same order)
+        float Ldir = LdirRows ? __ldg(&LdirRows[s * SKC_NS + lane]) : directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane]);
         Lc += Ldir;
     }
     sL[warp][lane] = lane < SKC_NS ? Lc : 0.f;
@@ -691,7 +712,7 @@ extern "C" int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t coun
 
 // Scene::Intersect for the camera rays and EstimateDirect's terms (everything of Li that does not need the octree)
 static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, uint64_t count, skc_hit *dHits, float4 *dFrame, float4 *dTerms,
-                              cudaEvent_t hitsDone = nullptr) {
+                              cudaEvent_t hitsDone = nullptr, float *dLdir = nullptr) {
     const FrameLayout &lay = f->lay;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
@@ -707,6 +728,10 @@ static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, 
     k_direct_terms<<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
                                                                                 dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms);
     SKC_LAUNCHED("k_direct_terms");
+    if (dLdir) {
+        k_direct_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(ctx->lights, lay, f->dConsts, dHits, dTerms, count, dLdir);
+        SKC_LAUNCHED("k_direct_sum");
+    }
     skc_stage_end(ctx, 10);
     return 0;
 }
@@ -729,14 +754,15 @@ extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
     skc_hit *dHits = (skc_hit *)skc_scratch(ctx, 17, count * sizeof(skc_hit));
     float4 *dFrame = (float4 *)skc_scratch(ctx, 13, count * 2 * sizeof(float4));
     float4 *dTerms = (float4 *)skc_scratch(ctx, 14, count * f->lay.slots * 3 * sizeof(float4));
-    if (!dHits || !dFrame || !dTerms) return 1;
+    float *dLdir = (float *)skc_scratch(ctx, 19, count * SKC_NS * sizeof(float));
+    if (!dHits || !dFrame || !dTerms || !dLdir) return 1;
     SKC_CUDA(cudaEventRecord(f->evDone, ctx->stream));                       // earlier consumers of these buffers
     SKC_CUDA(cudaStreamWaitEvent(ctx->prefetchStream, f->evDone, 0));
     cudaStream_t mainStream = ctx->stream;
     ctx->stream = ctx->prefetchStream; ctx->stageOff = true;
     cudaEventRecord(f->evP0, ctx->stream);
     int rc = skc_frame_samples(ctx);
-    if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms, f->evHits);
+    if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms, f->evHits, dLdir);
     cudaEventRecord(f->evP1, ctx->stream);
     ctx->stream = mainStream; ctx->stageOff = false;
     if (rc) return 1;
@@ -770,7 +796,8 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     if (usePrefetch) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, f->evP1, 0));
     skc_stage_begin(ctx);
     k_frame_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, f->dConsts, dHits, dTerms,
-                                                                                                 f->dXY, f->dOrder, first, count, dL, f->dFilm);
+                                                                                                 f->dXY, f->dOrder, first, count, dL, f->dFilm,
+                                                                                                 usePrefetch ? (const float *)skc_scratch(ctx, 19, count * SKC_NS * sizeof(float)) : nullptr);
     SKC_LAUNCHED("k_frame_sum");
     skc_stage_end(ctx, 11);
     if (usePrefetch) {      // the prefetched part, as timed on its own stream
