@@ -352,7 +352,8 @@ def main():
                    "material_tables": material},
         "stage_ms": stage_ms,
         "hot_path_seconds": ms_step * 1e-3,
-        "rays_per_s": (int(c_irr[2]) * world + n_rays) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),
+        # shadow rays of the irradiance pass (+ the camera rays where their closest-hit stage is timed on its own, i.e. --no-prefetch)
+        "rays_per_s": (int(c_irr[2]) * world + (n_rays if stage_ms["closest"] > 0 else 0)) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),
         "irradiance_points_per_s": n_pts / ((stage_ms["scramble"] + stage_ms["irradiance"]) * 1e-3),
         "mo_points_per_s": n_rays / (stage_ms["mo"] * 1e-3),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
