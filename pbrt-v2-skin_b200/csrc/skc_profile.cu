@@ -194,9 +194,12 @@ __device__ __forceinline__ void fftPass(double2 *s, uint32_t N, uint32_t st, con
     }
 }
 
-__global__ void __launch_bounds__(512) k_fft_rows(double2 *__restrict__ Z, uint32_t N, uint32_t logN, const double2 *__restrict__ tw, int inverse) {
+// rows (rowStart + blockIdx.x) mod N of every set (blockIdx.y): the whole matrix, or the band of rows that is not all zero
+// (first pass of a forward transform of the zero-padded grid) / that anything reads afterwards (last pass of the inverse)
+__global__ void __launch_bounds__(512) k_fft_rows(double2 *__restrict__ Z, uint32_t N, uint32_t logN, const double2 *__restrict__ tw, int inverse,
+                                                  uint32_t rowStart) {
     extern __shared__ double2 s[];
-    double2 *row = Z + ((size_t)blockIdx.y * N + blockIdx.x) * N;
+    double2 *row = Z + ((size_t)blockIdx.y * N + ((rowStart + blockIdx.x) & (N - 1))) * N;
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) s[fftSlot(__brev(i) >> (32 - logN))] = row[i];
     __syncthreads();
     uint32_t st = 1;
@@ -360,12 +363,15 @@ static size_t fftSmemBytes(uint32_t N) { return (size_t)(N + (N >> 3) + (N >> 6)
 
 static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t logN, int inverse, uint32_t k) {
     // rows of A in place, transpose into B, rows of B in place: B holds the 2-D transform (transposed layout)
-    uint32_t N = w.N, threads = std::max(32u, std::min(N / 8, 512u));
-    k_fft_rows<<<dim3(N, k), threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse);
+    // The G x G grid sits zero-padded in the N x N matrix, on the rows and columns (i - c) mod N, i < G, c = (G-1)/2 (k_pack):
+    // a forward transform's first pass meets N - G rows of zeros (whose transform is zeros, already in place), and of the
+    // inverse's last pass only that band of rows is ever read (k_unpack) -- both passes run on the G-row band alone.
+    uint32_t N = w.N, G = w.G, threads = std::max(32u, std::min(N / 8, 512u)), band = N - (G - 1) / 2;
+    k_fft_rows<<<dim3(inverse ? N : G, k), threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse, inverse ? 0u : band);
     SKC_LAUNCHED("k_fft_rows");
     k_transpose<<<dim3(N / 32, N / 32, k), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
     SKC_LAUNCHED("k_transpose");
-    k_fft_rows<<<dim3(N, k), threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse);
+    k_fft_rows<<<dim3(inverse ? G : N, k), threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse, inverse ? band : 0u);
     SKC_LAUNCHED("k_fft_rows");
     return 0;
 }
