@@ -350,11 +350,20 @@ struct ProfileWork {
     double2 *grid[2] = {nullptr, nullptr}, *Z[3] = {nullptr, nullptr, nullptr}, *tw = nullptr, *partial = nullptr;
     uint2 *idx = nullptr;
     float *raw = nullptr, *res = nullptr, *steps = nullptr;
+    float *out[2] = {nullptr, nullptr}, *hostOut[2] = {nullptr, nullptr};      // a group's [set][d2 | R | T][len] rows: device, and pinned host
+    double2 *hostPart[2] = {nullptr, nullptr};
+    cudaEvent_t computed[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
     DipoleSet *ds = nullptr;
     uint32_t G = 0, N = 0, nEntries = 0, K = 1;
     void release() {
-        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res, steps, ds};
+        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res, steps, ds, out[0], out[1]};
         for (void *q : p) if (q) cudaFree(q);
+        for (int b = 0; b < 2; ++b) {
+            if (hostOut[b]) cudaFreeHost(hostOut[b]);
+            if (hostPart[b]) cudaFreeHost(hostPart[b]);
+            if (computed[b]) cudaEventDestroy(computed[b]);
+            if (copied[b]) cudaEventDestroy(copied[b]);
+        }
         *this = ProfileWork();
     }
 };
@@ -408,6 +417,9 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     uint32_t K = (uint32_t)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(nSets, 32), freeB / 4 / perSet));
     if (const char *e = getenv("SKC_PROFILE_GROUP")) K = (uint32_t)std::max(1, std::min(atoi(e), (int)nSets));
     w.K = K;
+    // more than one group: the groups' outputs are staged through pinned memory and delivered while the next group computes;
+    // a single group (a material's 30 wavelengths) copies straight into the caller's arrays
+    const bool pipelined = nSets > K;
     int rc = 1;
     do {
         if (cudaMalloc((void **)&w.grid[0], (size_t)K * G * G * sizeof(double2)) != cudaSuccess) break;
@@ -422,10 +434,20 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
             if (cudaMemcpyAsync(w.tw, tw.data(), tw.size() * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
             if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
         }
-        if (cudaMalloc((void **)&w.partial, (size_t)K * 256 * sizeof(double2)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.partial, 2 * (size_t)K * 256 * sizeof(double2)) != cudaSuccess) break;
+        {
+            bool ok = true;
+            for (int b = 0; b < (pipelined ? 2 : 1); ++b) {
+                ok &= cudaMalloc((void **)&w.out[b], (size_t)K * 3 * outLen * sizeof(float)) == cudaSuccess;
+                if (pipelined) ok &= cudaMallocHost((void **)&w.hostOut[b], (size_t)K * 3 * outLen * sizeof(float)) == cudaSuccess;
+                if (pipelined) ok &= cudaMallocHost((void **)&w.hostPart[b], (size_t)K * 256 * sizeof(double2)) == cudaSuccess;
+                ok &= cudaEventCreateWithFlags(&w.computed[b], cudaEventDisableTiming) == cudaSuccess;
+                ok &= cudaEventCreateWithFlags(&w.copied[b], cudaEventDisableTiming) == cudaSuccess;
+            }
+            if (!ok) break;
+        }
         if (cudaMalloc((void **)&w.idx, nEntries * sizeof(uint2)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.raw, (size_t)K * 3 * nEntries * sizeof(float)) != cudaSuccess) break;
-        if (cudaMalloc((void **)&w.res, (size_t)K * 3 * outLen * sizeof(float)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.steps, (size_t)K * sizeof(float)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.ds, (size_t)K * sizeof(DipoleSet)) != cudaSuccess) break;
         if (cudaMemcpyAsync(w.idx, radii.data(), nEntries * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
@@ -444,6 +466,9 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     uint32_t ext = (G - 1) / 2 + 1;
     dim3 lpBlock(32, 8);
     // a group = up to K consecutive sets with the same number of layers: layer l of all of them goes through each stage at once
+    uint32_t groupIndex = 0, prevS0 = 0, prevK = 0;
+    int prevB = 0;
+    bool havePrev = false;
     for (uint32_t s0 = 0; s0 < nSets && !rc;) {
         const uint32_t nL = layersPerSet[s0];
         uint32_t k = 1;
@@ -482,31 +507,64 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
         if (cudaMemcpyAsync(w.steps, hsteps.data(), k * sizeof(float), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) { rc = 1; break; }
         k_extract<<<dim3((nEntries + 255) / 256, k), 256, 0, ctx->stream>>>(w.grid[0], G, w.idx, nEntries, w.steps, w.raw);
         ctx->launches++;
-        const float *o = w.raw;
+        // Output of the group: double-buffered on the device (out[gi & 1]) and in pinned host memory; the copy runs on the copy
+        // stream and the scatter into the caller's (pageable) arrays on the host while the next group is being computed.
+        const int bsel = pipelined ? (int)(groupIndex & 1) : 0;
+        float *o = w.out[bsel];
+        double2 *part = w.partial + (size_t)bsel * K * 256;
+        if (pipelined && groupIndex >= 2) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, w.copied[bsel], 0));      // the copy that last read this buffer
         if (resample) {
-            k_resample<<<dim3((outLen + 255) / 256, k), 256, 0, ctx->stream>>>(w.raw, nEntries, outLen, w.res);
+            k_resample<<<dim3((outLen + 255) / 256, k), 256, 0, ctx->stream>>>(w.raw, nEntries, outLen, o);
             ctx->launches++;
-            o = w.res;
-        }
+        } else SKC_CUDA(cudaMemcpyAsync(o, w.raw, (size_t)k * 3 * nEntries * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
         if (totals) {
-            k_grid_sum<<<dim3(256, k), 256, 0, ctx->stream>>>(w.grid[0], (size_t)G * G, w.partial);
+            k_grid_sum<<<dim3(256, k), 256, 0, ctx->stream>>>(w.grid[0], (size_t)G * G, part);
             ctx->launches++;
-            if (cudaMemcpyAsync(hpart.data(), w.partial, (size_t)k * 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
         }
-        // rows [set][d2 | R | T][outLen] -> the caller's three [set][outLen] arrays
-        const size_t rowB = (size_t)outLen * sizeof(float);
-        float *dsts[3] = {d2, R, T};
-        for (int a = 0; a < 3 && !rc; ++a)
-            if (dsts[a] && cudaMemcpy2DAsync(dsts[a] + (size_t)s0 * outLen, rowB, o + (size_t)a * outLen, 3 * rowB, rowB, k, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = 1;
-        if (rc) break;
-        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { rc = 1; break; }
-        if (totals)
-            for (uint32_t q = 0; q < k; ++q) {
-                double r = 0., t = 0.;
-                for (int j = 0; j < 256; ++j) { r += hpart[(size_t)q * 256 + j].x; t += hpart[(size_t)q * 256 + j].y; }
-                totals[2 * (s0 + q)] = (float)r; totals[2 * (s0 + q) + 1] = (float)t;
-            }
+        if (!pipelined) {
+            if (totals && cudaMemcpyAsync(hpart.data(), part, (size_t)k * 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = 1; break; }
+            const size_t rowB = (size_t)outLen * sizeof(float);
+            float *dsts[3] = {d2, R, T};
+            for (int a = 0; a < 3 && !rc; ++a)
+                if (dsts[a] && cudaMemcpy2DAsync(dsts[a] + (size_t)s0 * outLen, rowB, o + (size_t)a * outLen, 3 * rowB, rowB, k, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = 1;
+            if (rc) break;
+            if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { rc = 1; break; }
+            if (totals)
+                for (uint32_t q = 0; q < k; ++q) {
+                    double r = 0., t = 0.;
+                    for (int j = 0; j < 256; ++j) { r += hpart[(size_t)q * 256 + j].x; t += hpart[(size_t)q * 256 + j].y; }
+                    totals[2 * (s0 + q)] = (float)r; totals[2 * (s0 + q) + 1] = (float)t;
+                }
+            s0 += k;
+            ++groupIndex;
+            continue;
+        }
+        SKC_CUDA(cudaEventRecord(w.computed[bsel], ctx->stream));
+        SKC_CUDA(cudaStreamWaitEvent(ctx->copyStream, w.computed[bsel], 0));
+        SKC_CUDA(cudaMemcpyAsync(w.hostOut[bsel], o, (size_t)k * 3 * outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->copyStream));
+        if (totals) SKC_CUDA(cudaMemcpyAsync(w.hostPart[bsel], part, (size_t)k * 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->copyStream));
+        SKC_CUDA(cudaEventRecord(w.copied[bsel], ctx->copyStream));
+        // rows [set][d2 | R | T][outLen] of a finished group -> the caller's three [set][outLen] arrays
+        auto deliver = [&](int bb, uint32_t gs0, uint32_t gk) -> int {
+            if (cudaEventSynchronize(w.copied[bb]) != cudaSuccess) return 1;
+            const float *h = w.hostOut[bb];
+            float *dsts[3] = {d2, R, T};
+            for (uint32_t q = 0; q < gk; ++q)
+                for (int a = 0; a < 3; ++a)
+                    if (dsts[a]) memcpy(dsts[a] + (size_t)(gs0 + q) * outLen, h + ((size_t)q * 3 + a) * outLen, (size_t)outLen * sizeof(float));
+            if (totals)
+                for (uint32_t q = 0; q < gk; ++q) {
+                    double r = 0., t = 0.;
+                    for (int j = 0; j < 256; ++j) { r += w.hostPart[bb][(size_t)q * 256 + j].x; t += w.hostPart[bb][(size_t)q * 256 + j].y; }
+                    totals[2 * (gs0 + q)] = (float)r; totals[2 * (gs0 + q) + 1] = (float)t;
+                }
+            return 0;
+        };
+        if (havePrev && deliver(prevB, prevS0, prevK)) { rc = 1; break; }
+        havePrev = true; prevB = bsel; prevS0 = s0; prevK = k;
+        if (s0 + k >= nSets && deliver(prevB, prevS0, prevK)) { rc = 1; break; }
         s0 += k;
+        ++groupIndex;
     }
     if (!rc) skc_stage_end(ctx, 6);
     cudaError_t e = cudaGetLastError();
