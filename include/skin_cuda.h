@@ -190,6 +190,20 @@ int skc_li_sss(skc_ctx *ctx, const skc_hit *hits, uint64_t n, float maxError, fl
 int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxError, float mix,
                     skc_hit *hitsOut, float *L30);
 
+/* The Mo kernel keeps a compact form of the Rd tables in shared memory (csrc/skc_mo_table.h: one abscissa for all
+ * wavelengths, cubic interpolation, per-wavelength windows verified against sampleProfile at upload time; outside
+ * a window the lookup is the reference's exact one).  SKC_MO_TABLE=exact in the environment keeps the exact tables
+ * only.  stats8 = {rows, shared-memory bytes, coverage, largest verified relative error inside the windows, and
+ * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
+ * global tables, 0}. */
+int skc_mo_table_stats(skc_ctx *ctx, double *stats8);
+/* Host-only (no GPU, no context): the builder and evaluator behind skc_upload_profile, for the error-bound test
+ * (tests/test_mo_table.py).  skc_moc_build returns NULL when no wavelength gets a window. */
+void *skc_moc_build(const float *table, const float *rcpDsqSpacing, uint32_t len, float tol, int K, int M, uint32_t headCapFloats);
+double skc_moc_info(void *handle, float *info4x30 /* {fLo, fHi, headLen, maxErr} */, uint32_t *rowsOut, uint32_t *headFloatsOut);
+void skc_moc_eval(void *handle, int lambda, const float *d2, uint64_t n, float *out, float *exactOut);
+void skc_moc_free(void *handle);
+
 /* ---- resident inputs --------------------------------------------------------------------- */
 /* The reference caches the surface-point set in a file ("string pointsfile",
  * multipolesubsurface.cpp:176-181); here the cache is HBM.  The *_resident calls run the same

@@ -56,6 +56,20 @@ struct skc_ctx {
     float profMaxD2 = 0.f;         // beyond this d^2 every wavelength returns 0
     uint32_t profLen = 0;
     float *rhoHd = nullptr;        // [1025][32]
+    // compact shared-abscissa form of the profile tables, copied into shared memory by k_mo_lambda (skc_mo_table.h)
+    float *mocRows = nullptr;      // [mocRowCount][32]
+    float *mocHeads = nullptr;     // table heads of the wavelengths whose compact window starts above 0
+    float4 *mocLam = nullptr;      // [32] {rcp, fLo, fHi, headLen} per wavelength
+    uint32_t *mocHeadOff = nullptr;// [32]
+    uint32_t mocRowCount = 0, mocHeadFloats = 0;
+    float mocInvA = 0.f, mocM = 0.f;
+    int moTable = 1;               // 1 = compact table in shared memory + exact fallback (k_mo_lambda), 0 = exact tables only (k_mo_packet); env SKC_MO_TABLE=exact|compact
+    float mocCoverage = 0.f, mocMaxErr = 0.f;
+    uint64_t moLookups[3] = {0, 0, 0};   // last counted pass: profile lookups in range / from shared-memory heads / from global tables
+    int smemOptin = 0;             // cudaDevAttrMaxSharedMemoryPerBlockOptin
+    int moGroup = 4;               // contributions per round of k_mo_lambda's summation loop; env SKC_MO_GROUP=2|4|8
+    int moWarps = 0;               // cap on warps per CTA of k_mo_lambda; env SKC_MO_WARPS
+    float mocTol = 1e-5f;          // window tolerance of the compact table; env SKC_MO_TOL
 
     // --- lights (skc_irradiance.cu)
     skc_light *lights = nullptr;

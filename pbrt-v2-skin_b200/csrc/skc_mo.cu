@@ -21,12 +21,17 @@
 #include <vector>
 #include <cub/cub.cuh>
 #include "skc_internal.h"
+#include "skc_mo_table.h"
 
 // Launch shape: a CTA of MO_WARPS warps works through a CONTIGUOUS run of MO_WARPS*MO_HITS_PER_WARP
 // shading points (neighbouring camera samples walk the same nodes, rows and table sectors, so
 // they must share an SM's L1 -- with hits dealt round-robin over the grid the L1 hit rate was
 // 2.7 %).  Stack bound: below MO_HIGH entries the warp pops up to 32 entries per round
 // (<= MO_HIGH-1 + 7*32 afterwards), above it one entry (depth-first, +7 per tree level).
+// compact profile table (skc_mo_table.h): abscissae, cells per binade, shared-memory floats for the table heads
+#define MOC_K 256
+#define MOC_M 16
+#define MOC_HEAD_CAP 0
 #define MO_WARPS 8
 #define MO_HITS_PER_WARP 16
 #define MO_HIGH 64
@@ -381,6 +386,213 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : (SPLI
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// k_mo_lambda: the packet walk of k_mo_packet (lane = hit for the node tests), but the contributions are summed with
+// lane = WAVELENGTH and the profile values come from shared memory (skc_mo_table.h): every accepting lane leaves a
+// record {d2, scale, abscissa cell, the four Lagrange weights} in shared memory, then the warp goes through the
+// accepting hits one by one -- the Et / E row is one coalesced 128 B load for the whole loop, a profile value is four
+// conflict-free LDS (row[k..k+3][lane]) and three FMAs, and the hit's sum is a read-modify-write of its own row of a
+// per-warp 32 x 32 accumulator tile in shared memory.  Outside a wavelength's verified window the lane does the
+// reference's exact lookup instead: from the table head held in shared memory, or from the global table (the far,
+// noisy part of the tables: ~1 in 8 lookups).  No transposition at the end: lane = wavelength is the output layout.
+#define MOL_STACK 256          // (node, mask) entries: 1 + 7 * levels, levels <= 36
+#define MOL_WARP_BYTES (32 * 32 * 4 + 32 * 16 + MOL_STACK * 8)
+#define MOL_MAX_WARPS 28
+
+struct MoCompactDev {
+    const float *rows, *heads;
+    const float4 *lam;            // {rcp, fLo, fHi, headLen}
+    const uint32_t *headOff;
+    uint32_t rowFloats, headFloats;   // headFloats padded to a multiple of 4
+    MoCompactParams P;
+};
+
+// G records at once: the records first, then every lane's global-table reads of the group (predicated, independent -- the
+// L2 round trip of the exact tail lookups is what a one-at-a-time loop waits for), then the shared-memory work, then the sums.
+template <bool COUNT, bool HEADS, int G>
+__device__ __forceinline__ void molGroup(const float4 *rec, float e, float *acc, const float *sRows, const float *sHeads,
+                                         const float2 *myPairs, int lane, const float4 &lp, uint32_t hoff, float lenM1L, uint32_t (&gc)[3]) {
+    float4 a[G];          // {d2, scale, t, cell row offset | accumulator row offset << 16}: one 16-byte broadcast read per record
+#pragma unroll
+    for (int g = 0; g < G; ++g) a[g] = rec[g];
+    float f[G]; bool inC[G], ex[G], gl[G]; float2 v[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        f[g] = a[g].x * lp.x;
+        inC[g] = f[g] >= lp.y && f[g] < lp.z;                       // the verified window of this wavelength (fHi <= len-2)
+        ex[g] = !inC[g] && f[g] < lenM1L;
+        gl[g] = HEADS ? (ex[g] && f[g] >= lp.w) : ex[g];
+        v[g] = make_float2(0.f, 0.f);
+        if (gl[g]) v[g] = __ldg(myPairs + (uint32_t)f[g]);
+    }
+    if (HEADS)
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+        if (ex[g] && !gl[g]) { const uint32_t seg = (uint32_t)f[g]; v[g].x = sHeads[hoff + seg]; v[g].y = sHeads[hoff + seg + 1]; }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const int bits = __float_as_int(a[g].w);
+        const float *r = sRows + (bits & 0xffff) + lane;
+        float w[4];
+        mocWeights(a[g].z, w);
+        const float rdC = mocCubic(w, r[0], r[32], r[64], r[96]);
+        const float t = f[g] - (float)(uint32_t)f[g];
+        const float rdE = (1.f - t) * v[g].x + t * v[g].y;          // sampleProfile's own arithmetic (core/multipole.cpp:60-73)
+        const float rd = inC[g] ? rdC : rdE;                        // rdE is 0 when neither path applies
+        if (COUNT) { gc[0] += (inC[g] || ex[g]); gc[1] += (ex[g] && !gl[g]); gc[2] += gl[g]; }
+        float *ap = acc + (bits >> 16) + lane;
+        *ap += (rd * e) * a[g].y;
+    }
+}
+
+// sums `e * Rd(d2) * scale` into the accumulator rows of the cnt hits whose records lie densely in rec[0 .. cnt)
+template <bool COUNT, bool HEADS>
+__device__ __forceinline__ void molContribute(int cnt, float e, const float4 *rec, float *acc, const float *sRows, const float *sHeads,
+                                              const MoTables &T, int lane, const float4 &lp, uint32_t hoff, float lenM1L, uint32_t (&gc)[3]) {
+    const float2 *myPairs = T.pairs + (size_t)lane * T.len;
+    int i = 0;
+    for (; i + 4 <= cnt; i += 4) molGroup<COUNT, HEADS, 4>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
+    if (cnt & 2) { molGroup<COUNT, HEADS, 2>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc); i += 2; }
+    if (cnt & 1) molGroup<COUNT, HEADS, 1>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
+}
+
+template <bool COUNT, bool PERM, bool HEADS, int MAXW>
+__global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables T, MoCompactDev C, const float *__restrict__ p3, uint64_t strideFloats,
+                                                                     const int32_t *__restrict__ enable, uint64_t enableStrideInts,
+                                                                     uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
+                                                                     uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm) {
+    extern __shared__ float4 molSmem[];
+    float *sRows = reinterpret_cast<float *>(molSmem);
+    float *sHeads = sRows + C.rowFloats;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    char *wb = reinterpret_cast<char *>(sHeads + C.headFloats) + (size_t)warp * MOL_WARP_BYTES;
+    float *acc = reinterpret_cast<float *>(wb);                          // [32 hits][32 wavelengths]
+    float4 *rec = reinterpret_cast<float4 *>(wb + 32 * 32 * 4);          // [32 records]
+    uint2 *stack = reinterpret_cast<uint2 *>(wb + 32 * 32 * 4 + 32 * 16);
+    {   // the compact rows and the table heads -> shared memory (float4 copies; both sizes are multiples of 4 floats)
+        const float4 *src = reinterpret_cast<const float4 *>(C.rows);
+        for (uint32_t i = threadIdx.x; i < C.rowFloats / 4; i += blockDim.x) molSmem[i] = __ldg(src + i);
+        const float4 *hs = reinterpret_cast<const float4 *>(C.heads);
+        float4 *hd = reinterpret_cast<float4 *>(sHeads);
+        for (uint32_t i = threadIdx.x; i < C.headFloats / 4; i += blockDim.x) hd[i] = __ldg(hs + i);
+    }
+    const float4 lp = __ldg(&C.lam[lane]);
+    const uint32_t hoff = __ldg(&C.headOff[lane]);
+    const float lenM1L = lane < SKC_NS ? T.lenM1 : -1.f;
+    const int kMax32 = (C.P.K - 2) * 32;
+    const unsigned lanesBelow = (1u << lane) - 1u;
+    __syncthreads();
+    uint32_t wc[4] = {0, 0, 0, 0};
+    uint32_t gc[3] = {0, 0, 0};        // this lane's profile lookups: all in range / from the shared-memory heads / from the global tables
+    const uint32_t nPackets = (uint32_t)((n + 31) / 32);
+    for (;;) {
+        uint32_t packet = 0;
+        if (lane == 0) packet = atomicAdd(nextPacket, 1u);
+        packet = __shfl_sync(0xffffffffu, packet, 0);
+        if (packet >= nPackets) break;
+        uint64_t h0 = (uint64_t)packet * 32, h = h0 + lane;
+        const uint32_t src = (PERM && h < n) ? __ldg(&perm[h]) : (uint32_t)h;
+        bool on = h < n && (enable ? (__ldg(&enable[(uint64_t)src * enableStrideInts]) != 0) : true);
+        float px = 0.f, py = 0.f, pz = 0.f;
+        if (on) { const float *pp = p3 + (uint64_t)src * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
+#pragma unroll
+        for (int r = 0; r < 32; ++r) acc[r * 32 + lane] = 0.f;
+        unsigned all = __ballot_sync(0xffffffffu, on);
+        int sp = 0;
+        if (all) { if (lane == 0) stack[0] = make_uint2(0u, all); sp = 1; }
+        __syncwarp();
+        while (sp > 0) {
+            --sp;
+            uint2 ent = stack[sp];
+            __syncwarp();
+            bool mine = (ent.y >> lane) & 1u;
+            const float4 *nd = tr.nodes + 3 * (size_t)ent.x;
+            float4 g = __ldg(nd), b0 = __ldg(nd + 1), b1 = __ldg(nd + 2);
+            uint32_t w0 = __float_as_uint(b1.z), w1 = __float_as_uint(b1.w);
+            if (COUNT) wc[0] += __popc(ent.y);
+            if (w1 & SKC_OT_BLACK) continue;
+            float dx = px - g.x, dy = py - g.y, dz = pz - g.z;
+            float d2 = dx * dx + dy * dy + dz * dz;
+            float dw = g.w / d2;
+            bool inside = px >= b0.x && px <= b0.w && py >= b0.y && py <= b1.x && pz >= b0.z && pz <= b1.y;
+            bool accept = mine && dw < maxError && !inside;
+            bool descend = mine && !accept;
+            bool addC = accept && d2 * T.rcpMin < T.lenM1;
+            if (descend) {      // beyond the table range nothing below contributes
+                float ex = fmaxf(fmaxf(b0.x - px, px - b0.w), 0.f);
+                float ey = fmaxf(fmaxf(b0.y - py, py - b1.x), 0.f);
+                float ez = fmaxf(fmaxf(b0.z - pz, pz - b1.y), 0.f);
+                float db2 = ex * ex + ey * ey + ez * ez;
+                descend = (db2 * 0.999f) * T.rcpMin < T.lenM1;
+            }
+            unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
+            if (am) {
+                if (COUNT) wc[2] += __popc(am);
+                const float e = __ldg(tr.Et + (size_t)ent.x * SKC_EPAD + lane);
+                if (addC) {     // records densely, in hit order
+                    int k; float t;
+                    mocCell(C.P, d2, k, t);
+                    rec[__popc(am & lanesBelow)] = make_float4(d2, 1.f, t, __int_as_float(min(k * 32, kMax32) | (lane << 21)));
+                }
+                __syncwarp();
+                molContribute<COUNT, HEADS>(__popc(am), e, rec, acc, sRows, sHeads, T, lane, lp, hoff, lenM1L, gc);
+                __syncwarp();
+            }
+            if (dm) {
+                if (w1 & SKC_OT_LEAF) {
+                    uint32_t cntP = w1 & 0xffu;
+                    if (COUNT) wc[1] += cntP * __popc(dm);
+                    for (uint32_t kp = 0; kp < cntP; ++kp) {
+                        uint32_t slot = w0 + kp;
+                        float4 pa = __ldg(&tr.leafPosArea[slot]);
+                        float qx = px - pa.x, qy = py - pa.y, qz = pz - pa.z;
+                        float q2 = qx * qx + qy * qy + qz * qz;
+                        bool c = descend && q2 * T.rcpMin < T.lenM1;
+                        unsigned pm = __ballot_sync(0xffffffffu, c);
+                        if (pm) {
+                            if (COUNT) wc[3] += __popc(pm);
+                            const float e = __ldg(tr.leafE + (size_t)slot * SKC_EPAD + lane);
+                            if (c) {
+                                int k; float t;
+                                mocCell(C.P, q2, k, t);
+                                rec[__popc(pm & lanesBelow)] = make_float4(q2, pa.w, t, __int_as_float(min(k * 32, kMax32) | (lane << 21)));
+                            }
+                            __syncwarp();
+                            molContribute<COUNT, HEADS>(__popc(pm), e, rec, acc, sRows, sHeads, T, lane, lp, hoff, lenM1L, gc);
+                            __syncwarp();
+                        }
+                    }
+                } else {
+                    int nc = __popc(w1 & 0xffu);
+                    if (lane < nc) stack[sp + lane] = make_uint2(w0 + lane, dm);
+                    sp += nc;
+                    __syncwarp();
+                }
+            }
+        }
+        // lane = wavelength already: stream the 32 rows out
+        for (int r = 0; r < 32; ++r) {
+            uint64_t hh = h0 + r;
+            if (hh >= n) break;
+            if (PERM) hh = (uint64_t)__shfl_sync(0xffffffffu, src, r);
+            float mo = lane < SKC_NS ? acc[r * 32 + lane] : 0.f;
+            if (Mo) Mo[hh * SKC_EPAD + lane] = mo;
+            if (li.L) {
+                float out = liSssValue(li, hh, lane, mo);
+                if (lane < SKC_NS) li.L[hh * SKC_NS + lane] = out;
+            }
+        }
+        __syncwarp();
+    }
+    if (COUNT && cnt) {
+        if (lane == 0) for (int k = 0; k < 4; ++k) atomicAdd(&cnt[k], (unsigned long long)wc[k]);
+        atomicAdd(&cnt[4], (unsigned long long)gc[0]);
+        atomicAdd(&cnt[5], (unsigned long long)gc[1]);
+        atomicAdd(&cnt[6], (unsigned long long)gc[2]);
+    }
+}
+
 // Li subsurface term (multipolesubsurface.cpp:279-287); one warp per hit, lane = wavelength
 __global__ void k_li_sss(const skc_hit *__restrict__ hits, uint64_t n, const float *__restrict__ Mo, const float *__restrict__ rhoHd,
                          const float *__restrict__ albedo, float mix, float *__restrict__ L) {
@@ -433,6 +645,32 @@ extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float 
         SKC_CUDA(cudaMemcpyAsync(ctx->profRcp, rcp, sizeof rcp, cudaMemcpyHostToDevice, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->profLen = len; ctx->profMaxD2 = rmin;   // rmin kept here: smallest rcpDsqSpacing
+        // the compact shared-memory form (skc_mo_table.h); tables too short to be worth it stay on the exact kernel
+        for (void *q : {(void *)ctx->mocRows, (void *)ctx->mocHeads, (void *)ctx->mocLam, (void *)ctx->mocHeadOff}) if (q) cudaFree(q);
+        ctx->mocRows = nullptr; ctx->mocHeads = nullptr; ctx->mocLam = nullptr; ctx->mocHeadOff = nullptr; ctx->mocRowCount = 0;
+        MoCompactTable C;
+        if (ctx->moTable && len >= 4096 && mocBuild(table, rcpDsqSpacing, len, ctx->mocTol, MOC_K, MOC_M, getenv("SKC_MO_HEADCAP") ? (uint32_t)atoi(getenv("SKC_MO_HEADCAP")) : MOC_HEAD_CAP, C)) {
+            float4 lam[32]; uint32_t hoff[32];
+            for (int l = 0; l < 32; ++l) {
+                lam[l] = l < SKC_NS ? make_float4(rcpDsqSpacing[l], C.fLo[l], C.fHi[l], (float)C.headLen[l]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                hoff[l] = C.headOff[l];
+            }
+            while (C.heads.size() % 4) C.heads.push_back(0.f);
+            SKC_CUDA(cudaMalloc((void **)&ctx->mocRows, C.rows.size() * sizeof(float)));
+            SKC_CUDA(cudaMalloc((void **)&ctx->mocHeads, C.heads.size() * sizeof(float)));
+            SKC_CUDA(cudaMalloc((void **)&ctx->mocLam, sizeof lam));
+            SKC_CUDA(cudaMalloc((void **)&ctx->mocHeadOff, sizeof hoff));
+            SKC_CUDA(cudaMemcpyAsync(ctx->mocRows, C.rows.data(), C.rows.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+            SKC_CUDA(cudaMemcpyAsync(ctx->mocHeads, C.heads.data(), C.heads.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+            SKC_CUDA(cudaMemcpyAsync(ctx->mocLam, lam, sizeof lam, cudaMemcpyHostToDevice, ctx->stream));
+            SKC_CUDA(cudaMemcpyAsync(ctx->mocHeadOff, hoff, sizeof hoff, cudaMemcpyHostToDevice, ctx->stream));
+            SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+            ctx->mocRowCount = (uint32_t)C.P.K + 3; ctx->mocHeadFloats = (uint32_t)C.heads.size();
+            ctx->mocInvA = C.P.invA; ctx->mocM = C.P.cellsPerBinade;
+            ctx->mocCoverage = (float)C.coverage;
+            float me = 0.f; for (int l = 0; l < SKC_NS; ++l) me = fmaxf(me, C.maxErr[l]);
+            ctx->mocMaxErr = me;
+        }
     }
     if (rhoHd) {
         std::vector<float> pad((size_t)SKC_RHO_LEN * SKC_EPAD, 0.f);
@@ -495,6 +733,33 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (!n) return 0;
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
+    if (ctx->moPacket && ctx->moTable && ctx->mocRows && 7 * (int)ctx->otLevels + 1 <= MOL_STACK) {
+        if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
+        MoCompactDev C; C.rows = ctx->mocRows; C.heads = ctx->mocHeads; C.lam = ctx->mocLam; C.headOff = ctx->mocHeadOff;
+        C.rowFloats = ctx->mocRowCount * 32; C.headFloats = ctx->mocHeadFloats;
+        C.P.invA = ctx->mocInvA; C.P.cellsPerBinade = ctx->mocM; C.P.K = (int)ctx->mocRowCount - 3;
+        const size_t tableBytes = ((size_t)C.rowFloats + C.headFloats) * sizeof(float);
+        int warps = (int)std::min<size_t>(MOL_MAX_WARPS, ((size_t)ctx->smemOptin - 1024 - tableBytes) / MOL_WARP_BYTES);
+        if (ctx->moWarps > 0) warps = std::min(warps, ctx->moWarps);
+        if (warps < 4) return skc_fail(ctx, "skc_mo: the compact profile table (%zu B) leaves no room for the traversal state in shared memory", tableBytes);
+        const size_t smem = tableBytes + (size_t)warps * MOL_WARP_BYTES;
+        const uint64_t nPk = (n + 31) / 32;
+        const unsigned grid = (unsigned)std::min<uint64_t>((nPk + warps - 1) / warps, (uint64_t)ctx->smCount);
+        LiEpilogue ep = li ? *li : LiEpilogue{nullptr, nullptr, nullptr, 0.f, nullptr};
+        uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
+        if (!next) return 1;
+        SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
+        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n) : nullptr;
+#define MOL_GO2(CNT, P, H, W) do { \
+            SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<CNT, P, H, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            k_mo_lambda<CNT, P, H, W><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm); } while (0)
+#define MOL_GO(CNT, P) do { if (C.headFloats <= 4) { if (warps > 20) MOL_GO2(CNT, P, false, 28); else MOL_GO2(CNT, P, false, 20); } else { if (warps > 20) MOL_GO2(CNT, P, true, 28); else MOL_GO2(CNT, P, true, 20); } } while (0)
+        if (cntDev) { if (perm) MOL_GO(true, true); else MOL_GO(true, false); } else { if (perm) MOL_GO(false, true); else MOL_GO(false, false); }
+#undef MOL_GO2
+#undef MOL_GO
+        SKC_LAUNCHED("k_mo_lambda");
+        return 0;
+    }
     if (ctx->moPacket) {
         if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
         if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
@@ -727,19 +992,31 @@ extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t c
     if (!dHits) return 1;
     unsigned long long *dCnt = nullptr;
     if (counters7) {
-        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 8 * sizeof(unsigned long long));
+        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 16 * sizeof(unsigned long long));
         if (!dCnt) return 1;
-        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 8 * sizeof(unsigned long long), ctx->stream));
+        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 16 * sizeof(unsigned long long), ctx->stream));
     }
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, dCnt)) return 1;
     skc_stage_end(ctx, 3);
     if (liDev(ctx, dHits, count, maxError, mix, nullptr, nullptr, L30, dCnt ? dCnt + 2 : nullptr, true)) return 1;
     if (counters7) {
-        unsigned long long h[8];
+        unsigned long long h[16];
         SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
         for (int k = 0; k < 7; ++k) counters7[k] = h[k];
+        ctx->moLookups[0] = h[6]; ctx->moLookups[1] = h[7]; ctx->moLookups[2] = h[8];
     }
+    return 0;
+}
+
+// Compact profile table of the Mo kernel (skc_mo_table.h): stats8 = {rows, shared-memory bytes (rows + heads), coverage (log-weighted
+// share of table segments served from shared memory), largest verified relative error, and from the last counted camera pass:
+// profile lookups in range, of those from the shared-memory heads, of those from the global tables, 0}.  rows = 0: exact tables only.
+extern "C" int skc_mo_table_stats(skc_ctx *ctx, double *stats8) {
+    if (!ctx) return 1;
+    stats8[0] = ctx->mocRows ? ctx->mocRowCount : 0; stats8[1] = ctx->mocRows ? ((double)ctx->mocRowCount * 32 + ctx->mocHeadFloats) * 4 : 0;
+    stats8[2] = ctx->mocRows ? ctx->mocCoverage : 0; stats8[3] = ctx->mocRows ? ctx->mocMaxErr : 0;
+    stats8[4] = (double)ctx->moLookups[0]; stats8[5] = (double)ctx->moLookups[1]; stats8[6] = (double)ctx->moLookups[2]; stats8[7] = 0;
     return 0;
 }

@@ -33,7 +33,8 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
            "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
-           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order"]
+           "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
+           "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -109,6 +110,11 @@ def load_library():
     lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
     lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
     lib.skc_frame_film_rgb.restype = i32; lib.skc_frame_film_rgb.argtypes = [vp, vp]
+    lib.skc_mo_table_stats.restype = i32; lib.skc_mo_table_stats.argtypes = [vp, vp]
+    lib.skc_moc_build.restype = vp; lib.skc_moc_build.argtypes = [vp, vp, u32, f32, i32, i32, u32]
+    lib.skc_moc_info.restype = C.c_double; lib.skc_moc_info.argtypes = [vp, vp, C.POINTER(u32), C.POINTER(u32)]
+    lib.skc_moc_eval.restype = None; lib.skc_moc_eval.argtypes = [vp, i32, vp, u64, vp, vp]
+    lib.skc_moc_free.restype = None; lib.skc_moc_free.argtypes = [vp]
     _lib = lib
     return lib
 
@@ -269,6 +275,13 @@ class SkinDevice:
         self._ck(self.lib.skc_mo(self.ctx, _ptr(p), len(p), max_error, _ptr(out)))
         return out
 
+    def mo_table_stats(self):
+        """Compact profile table of the Mo kernel: dict(rows, smem_bytes, coverage, max_err, lookups, from_heads, from_global)."""
+        st = np.zeros(8, np.float64)
+        self._ck(self.lib.skc_mo_table_stats(self.ctx, _ptr(st)))
+        return dict(rows=int(st[0]), smem_bytes=int(st[1]), coverage=float(st[2]), max_err=float(st[3]),
+                    lookups=int(st[4]), from_heads=int(st[5]), from_global=int(st[6]))
+
     def li_sss(self, hits, max_error, mix=0.5, albedo=None):
         hits = np.ascontiguousarray(hits if hits.dtype == DT_HIT else hits.view(DT_HIT).reshape(-1))
         mo = np.empty((len(hits), 30), np.float32); L = np.empty((len(hits), 30), np.float32)
@@ -390,3 +403,28 @@ class SkinDevice:
         hd = np.empty((1025, 30), np.float32)
         self._ck(self.lib.skc_rho_table(self.ctx, float(roughness), float(eta_i), float(eta_t), int(fixed_fresnel), _ptr(hd)))
         return hd
+
+
+class CompactProfile:
+    """Host-only view of the compact Rd table skc_upload_profile builds (csrc/skc_mo_table.h); no GPU needed."""
+
+    def __init__(self, table, rcp, tol=1e-5, K=256, M=16, head_cap=16384):
+        self.lib = load_library()
+        self.table = np.ascontiguousarray(table, np.float32); self.rcp = np.ascontiguousarray(rcp, np.float32)
+        self.h = self.lib.skc_moc_build(_ptr(self.table), _ptr(self.rcp), self.table.shape[1], tol, K, M, head_cap)
+        if self.h:
+            info = np.zeros((30, 4), np.float32); rows = C.c_uint32(0); hf = C.c_uint32(0)
+            self.coverage = float(self.lib.skc_moc_info(self.h, _ptr(info), C.byref(rows), C.byref(hf)))
+            self.f_lo, self.f_hi, self.head_len, self.max_err = info[:, 0].copy(), info[:, 1].copy(), info[:, 2].astype(int), info[:, 3].copy()
+            self.rows, self.head_floats = int(rows.value), int(hf.value)
+
+    def eval(self, lam, d2):
+        """(kernel value, sampleProfile value) of wavelength lam at the fp32 distances d2."""
+        d2 = np.ascontiguousarray(d2, np.float32)
+        out = np.empty(len(d2), np.float32); ex = np.empty(len(d2), np.float32)
+        self.lib.skc_moc_eval(self.h, int(lam), _ptr(d2), len(d2), _ptr(out), _ptr(ex))
+        return out, ex
+
+    def close(self):
+        if self.h:
+            self.lib.skc_moc_free(self.h); self.h = None
