@@ -18,6 +18,9 @@ and packs the exported streams into compressed .npz files:
   mpc_kat.npz     MPC_ComputeDiffusionProfile on the parameter sets of the reference's
                   src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
 
+  skin_full.npz   scenes/skin.scene at FULL size (the benchmarked configuration): image, strided points / samples / tables
+  mpc_kat512.npz  four two-layer thin-slab sets at desiredLength 512 (strided tables + both ends)
+
 Only this script and the fixtures are committed; nothing at test time reads /root/reference.
 Usage:  python tests/golden/make_golden.py [skin_tiny] [mpc_kat]
 """
@@ -198,9 +201,80 @@ def mpc_golden():
     print(path, os.path.getsize(path) // 1024, "KiB")
 
 
+def strided_table(a, stride=16, edge=2048):
+    """A long table row(s) [..., len] kept as: every stride-th entry, the first `edge` and the last `edge` entries."""
+    a = np.asarray(a)
+    return dict(strided=a[..., ::stride].copy(), head=a[..., :edge].copy(), tail=a[..., -edge:].copy())
+
+
+def skin_full_golden(name="skin_full"):
+    """BASELINE.json configs[1] at FULL size (scenes/skin.scene: 24.6 M irradiance points, 1280x720x4 spp, desiredLength 512):
+    the reference's image, octree root and bounds, every 4099th irradiance point, every 997th camera sample (hit, Mo,
+    subsurface radiance, full Li) and the 30 profile tables (every 16th entry + both ends) with their headers.
+    The run takes ~22 min at --ncores 1 and ~9 GB of scratch; SKIN_FULL_DIR=<dir> reuses an existing export."""
+    d = os.environ.get("SKIN_FULL_DIR")
+    tmp = None
+    if not d:
+        tmp = tempfile.TemporaryDirectory(); d = tmp.name
+        subprocess.run([DRIVER, "scene", os.path.join(ROOT, "scenes", "skin.scene"), d, "--ncores", "1"], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    meta = read_meta(os.path.join(d, "meta.txt"))
+    mm = lambda fn, dt, cols: np.memmap(os.path.join(d, fn), dt, "r").reshape(-1, cols)
+    irr = mm("irradiance_points.bin", np.float32, 38)
+    si, sc = 4099, 997
+    hits = np.memmap(os.path.join(d, "hits.bin"), np.uint8, "r").reshape(-1, 56)
+    rd = mm("profile_rd.bin", np.float32, meta["profile_len"])
+    tab = strided_table(rd)
+    arrays = dict(
+        meta_keys=np.array(list(meta.keys())), meta_vals=np.array([float(v) for v in meta.values()]),
+        irradiance_stride=np.int64(si), irradiance_points=np.array(irr[::si]),
+        octree_bounds=np.fromfile(os.path.join(d, "octree_bounds.bin"), np.float32), octree_root=np.fromfile(os.path.join(d, "octree_root.bin"), np.float32),
+        sample_stride=np.int64(sc), camera_xy=np.array(mm("camera_xy.bin", np.float32, 2)[::sc]), camera_rays=np.array(mm("camera_rays.bin", np.float32, 8)[::sc]),
+        hits=np.array(hits[::sc]), mo=np.array(mm("mo.bin", np.float32, 30)[::sc]), L_sss=np.array(mm("L_sss.bin", np.float32, 30)[::sc]),
+        L=np.array(mm("L.bin", np.float32, 30)[::sc]),
+        profile_hdr=np.fromfile(os.path.join(d, "profile_hdr.bin"), np.float32).reshape(30, 4),
+        profile_stride=np.int64(16), profile_rd_strided=tab["strided"], profile_rd_head=tab["head"], profile_rd_tail=tab["tail"],
+        rho_hd=np.fromfile(os.path.join(d, "rho_hd.bin"), np.float32).reshape(-1, 30)[:1025],
+        image=read_pfm(os.path.join(d, "image.pfm")),
+    )
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "profile_len")})
+    if tmp:
+        tmp.cleanup()
+
+
+# BASELINE.json configs[4] (SURVEY.md 8d C5) at the size that is benchmarked: two-layer thin-epidermis sets at desiredLength 512
+# (2048^2 transforms, 119 766-entry tables).  Epidermis thickness as a multiple of its mean free path: 0.02, 0.5, 1.2, 2.0.
+C5_EPI_MFP = 1.0 / (0.268088 + 19.4879)
+MPC512_CASES = [(2, 512, 1, 1, 0.0, [(1.4, t * C5_EPI_MFP, 0.268088, 19.4879), (1.4, 2.0, 0.268088, 9.74395)]) for t in (0.02, 0.5, 1.2, 2.0)]
+
+
+def mpc512_golden():
+    with tempfile.TemporaryDirectory() as d:
+        inp, outp = os.path.join(d, "in.txt"), os.path.join(d, "out.bin")
+        with open(inp, "w") as f:
+            for nl, dl, lerp, res, step, layers in MPC512_CASES:
+                f.write("%d %d %d %d %r " % (nl, dl, lerp, res, step) + " ".join("%r %r %r %r" % l for l in layers) + "\n")
+        subprocess.run([DRIVER, "mpc", inp, outp], check=True, stdout=subprocess.DEVNULL)
+        blob = open(outp, "rb").read()
+    arrays, off = {}, 0
+    for i, case in enumerate(MPC512_CASES):
+        ln = int(np.frombuffer(blob, np.uint32, 1, off)[0]); off += 4
+        tot = np.frombuffer(blob, np.float32, 2, off); off += 8
+        body = np.frombuffer(blob, np.float32, 3 * ln, off).reshape(3, ln); off += 12 * ln
+        arrays["case%d_spec" % i] = np.array([case[0], case[1], case[2], case[3], case[4]] + [x for l in case[5] for x in l], np.float64)
+        arrays["case%d_totals" % i] = tot.copy(); arrays["case%d_len" % i] = np.int64(ln)
+        for k, v in strided_table(body).items():
+            arrays["case%d_d2_R_T_%s" % (i, k)] = v
+    path = os.path.join(OUT, "mpc_kat512.npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "skin_lights", "mpc_kat"]
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)
