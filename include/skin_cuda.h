@@ -204,6 +204,18 @@ double skc_moc_info(void *handle, float *info4x30 /* {fLo, fHi, headLen, maxErr}
 void skc_moc_eval(void *handle, int lambda, const float *d2, uint64_t n, float *out, float *exactOut);
 void skc_moc_free(void *handle);
 
+/* skc_mo for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same kernels and results as
+ * skc_mo, but all scratch (ticket counter, staged points, padded rows, output staging) lives in one file-scope
+ * `static __device__` array of csrc/skc_mo.cu: 4 260 096 bytes, held by every GPU that loads the library until exit.  The
+ * call makes no cudaMalloc / cudaFree and uses no allocating library routine; it needs the octree and the profile tables
+ * already set up in ctx.  p3 [n][3] and Mo30 [n][30] may be host or device memory.  Limit: n <= SKC_MO_STATIC_MAX_HITS
+ * points per call; a larger n is rejected with an error (split the call, or use skc_mo).  All calls share the array and it
+ * keeps the last call's contents (what must start at zero is cleared per call); calls that overlap on the GPU -- two
+ * contexts or two host threads on one device -- race on it. */
+#define SKC_MO_STATIC_MAX_HITS 16384u
+int skc_mo_static(skc_ctx *ctx, const float *p3, uint64_t n, float maxError, float *Mo30);
+
 /* ---- resident inputs --------------------------------------------------------------------- */
 /* The reference caches the surface-point set in a file ("string pointsfile",
  * multipolesubsurface.cpp:176-181); here the cache is HBM.  The *_resident calls run the same

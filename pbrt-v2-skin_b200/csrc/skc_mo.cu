@@ -1020,3 +1020,83 @@ extern "C" int skc_mo_table_stats(skc_ctx *ctx, double *stats8) {
     stats8[4] = (double)ctx->moLookups[0]; stats8[5] = (double)ctx->moLookups[1]; stats8[6] = (double)ctx->moLookups[2]; stats8[7] = 0;
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// skc_mo_static: SubsurfaceOctreeNode::Mo for callers that must not allocate (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels as skc_mo, but every byte of scratch -- the packet ticket counter, the staged points, the padded [n][32]
+// rows and the [n][30] output staging -- lives in ONE file-scope device array of fixed size, so the call makes no
+// cudaMalloc / cudaFree and uses no allocating library routine (no hit sort either: the points are walked in the
+// caller's order, which changes packet coherence, not results).  Every GPU that loads the library holds the array until
+// exit.  All calls share it and it keeps the last call's contents: the ticket counter is cleared per call, everything
+// else is fully overwritten before it is read; two calls that overlap on the GPU (two contexts or host threads on one
+// device) race on it.
+#define MOS_OFF_P3 256u                                                     // after the counter's 256 B
+#define MOS_OFF_PAD (MOS_OFF_P3 + SKC_MO_STATIC_MAX_HITS * 12u)              // 12 B per point
+#define MOS_OFF_OUT (MOS_OFF_PAD + SKC_MO_STATIC_MAX_HITS * SKC_EPAD * 4u)    // 128 B per padded row
+#define MOS_BYTES (MOS_OFF_OUT + SKC_MO_STATIC_MAX_HITS * SKC_NS * 4u)        // 120 B per output row: 4 260 096 B in all
+static __device__ __align__(256) unsigned char g_moStaticScratch[MOS_BYTES];
+
+// In host code `g_moStaticScratch` is a host-side stand-in, not a device address: resolve it once per device, with that
+// device current, and hand the kernels the resolved pointer.
+static unsigned char *moStaticBase(skc_ctx *ctx) {
+    static unsigned char *base[64] = {nullptr};
+    const int d = ctx->device;
+    if (d < 0 || d >= 64) { skc_fail(ctx, "skc_mo_static: device %d out of range", d); return nullptr; }
+    if (!base[d]) {
+        unsigned char *p = nullptr;
+        if (skc_check(ctx, cudaGetSymbolAddress((void **)&p, g_moStaticScratch), "cudaGetSymbolAddress(g_moStaticScratch)")) return nullptr;
+        base[d] = p;
+    }
+    return base[d];
+}
+
+extern "C" int skc_mo_static(skc_ctx *ctx, const float *p3, uint64_t n, float maxError, float *Mo30) {
+    if (!ctx) return 1;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return skc_fail(ctx, "skc_mo_static: cudaSetDevice(%d) failed", ctx->device);
+    if (n > SKC_MO_STATIC_MAX_HITS)
+        return skc_fail(ctx, "skc_mo_static: %llu points exceed the static scratch capacity of %u points per call (split the call, or use skc_mo)",
+                        (unsigned long long)n, SKC_MO_STATIC_MAX_HITS);
+    if (!n) return 0;
+    if (!p3 || !Mo30) return skc_fail(ctx, "skc_mo_static: null input or output");
+    if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo_static: no octree built (skc_build_octree)");
+    if (!ctx->profPairs) return skc_fail(ctx, "skc_mo_static: no profile table uploaded (skc_upload_profile)");
+    unsigned char *base = moStaticBase(ctx);
+    if (!base) return 1;
+    uint32_t *next = reinterpret_cast<uint32_t *>(base);
+    float *dP = reinterpret_cast<float *>(base + MOS_OFF_P3), *dPad = reinterpret_cast<float *>(base + MOS_OFF_PAD), *dOut = reinterpret_cast<float *>(base + MOS_OFF_OUT);
+    // p3 / Mo30 may be host or device memory (unified addressing picks the direction)
+    SKC_CUDA(cudaMemcpyAsync(dP, p3, n * 3 * sizeof(float), cudaMemcpyDefault, ctx->stream));
+    SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
+    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
+    MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
+    const LiEpilogue ep{nullptr, nullptr, nullptr, 0.f, nullptr};
+    if (ctx->moTable && ctx->mocRows && 7 * (int)ctx->otLevels + 1 <= MOL_STACK) {
+        MoCompactDev C; C.rows = ctx->mocRows; C.heads = ctx->mocHeads; C.lam = ctx->mocLam; C.headOff = ctx->mocHeadOff;
+        C.rowFloats = ctx->mocRowCount * 32; C.headFloats = ctx->mocHeadFloats;
+        C.P.invA = ctx->mocInvA; C.P.cellsPerBinade = ctx->mocM; C.P.K = (int)ctx->mocRowCount - 3;
+        const size_t tableBytes = ((size_t)C.rowFloats + C.headFloats) * sizeof(float);
+        const int warps = (int)std::min<size_t>(20, ((size_t)ctx->smemOptin - 1024 - tableBytes) / MOL_WARP_BYTES);
+        if (warps < 4) return skc_fail(ctx, "skc_mo_static: the compact profile table (%zu B) leaves no room for the traversal state in shared memory", tableBytes);
+        const size_t smem = tableBytes + (size_t)warps * MOL_WARP_BYTES;
+        const unsigned grid = (unsigned)std::min<uint64_t>(((n + 31) / 32 + warps - 1) / warps, (uint64_t)ctx->smCount);
+        if (C.headFloats <= 4) {
+            SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<false, false, false, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_mo_lambda<false, false, false, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr);
+        } else {
+            SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<false, false, true, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_mo_lambda<false, false, true, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr);
+        }
+        SKC_LAUNCHED("k_mo_lambda (static scratch)");
+    } else {
+        if (7 * (int)ctx->otLevels + 1 > MOP_STACK) return skc_fail(ctx, "skc_mo_static: octree with %u levels exceeds the packet traversal stack", ctx->otLevels);
+        const uint64_t pb = std::min<uint64_t>((n + MOP_WARPS * 32 - 1) / (MOP_WARPS * 32), (uint64_t)ctx->smCount * MOP_CTAS1);
+        k_mo_packet<false, 1, false><<<(unsigned)pb, MOP_WARPS * 32, 0, ctx->stream>>>(tr, T, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr);
+        SKC_LAUNCHED("k_mo_packet (static scratch)");
+    }
+    k_unpad<<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>(dPad, n, dOut);
+    SKC_LAUNCHED("k_unpad (static scratch)");
+    SKC_CUDA(cudaMemcpyAsync(Mo30, dOut, n * SKC_NS * sizeof(float), cudaMemcpyDefault, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}

@@ -34,7 +34,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
-           "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_mo_static", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -110,6 +110,7 @@ def load_library():
     lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
     lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
     lib.skc_frame_film_rgb.restype = i32; lib.skc_frame_film_rgb.argtypes = [vp, vp]
+    lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_mo_table_stats.restype = i32; lib.skc_mo_table_stats.argtypes = [vp, vp]
     lib.skc_moc_build.restype = vp; lib.skc_moc_build.argtypes = [vp, vp, u32, f32, i32, i32, u32]
     lib.skc_moc_info.restype = C.c_double; lib.skc_moc_info.argtypes = [vp, vp, C.POINTER(u32), C.POINTER(u32)]
@@ -273,6 +274,15 @@ class SkinDevice:
         p = _c(p, np.float32).reshape(-1, 3)
         out = np.empty((len(p), 30), np.float32)
         self._ck(self.lib.skc_mo(self.ctx, _ptr(p), len(p), max_error, _ptr(out)))
+        return out
+
+    MO_STATIC_MAX_HITS = 16384
+
+    def mo_static(self, p, max_error):
+        """skc_mo_static: Mo through the file-scope device scratch (no allocation inside the call); at most MO_STATIC_MAX_HITS points."""
+        p = _c(p, np.float32).reshape(-1, 3)
+        out = np.empty((len(p), 30), np.float32)
+        self._ck(self.lib.skc_mo_static(self.ctx, _ptr(p), len(p), max_error, _ptr(out)))
         return out
 
     def mo_table_stats(self):
