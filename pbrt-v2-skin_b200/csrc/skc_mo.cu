@@ -484,6 +484,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
     const unsigned lanesBelow = (1u << lane) - 1u;
     __syncthreads();
     uint32_t wc[4] = {0, 0, 0, 0};
+    uint32_t grp[2] = {0, 0};          // accept events of this warp: (cluster, packet) and (leaf point, packet) groups (COUNT only)
     uint32_t gc[3] = {0, 0, 0};        // this lane's profile lookups: all in range / from the shared-memory heads / from the global tables
     const uint32_t nPackets = (uint32_t)((n + 31) / 32);
     for (;;) {
@@ -528,7 +529,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
             }
             unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
             if (am) {
-                if (COUNT) wc[2] += __popc(am);
+                if (COUNT) { wc[2] += __popc(am); ++grp[0]; }
                 const float e = __ldg(tr.Et + (size_t)ent.x * SKC_EPAD + lane);
                 if (addC) {     // records densely, in hit order
                     int k; float t;
@@ -551,7 +552,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
                         bool c = descend && q2 * T.rcpMin < T.lenM1;
                         unsigned pm = __ballot_sync(0xffffffffu, c);
                         if (pm) {
-                            if (COUNT) wc[3] += __popc(pm);
+                            if (COUNT) { wc[3] += __popc(pm); ++grp[1]; }
                             const float e = __ldg(tr.leafE + (size_t)slot * SKC_EPAD + lane);
                             if (c) {
                                 int k; float t;
@@ -590,6 +591,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
         atomicAdd(&cnt[4], (unsigned long long)gc[0]);
         atomicAdd(&cnt[5], (unsigned long long)gc[1]);
         atomicAdd(&cnt[6], (unsigned long long)gc[2]);
+        if (lane == 0) { atomicAdd(&cnt[7], (unsigned long long)grp[0]); atomicAdd(&cnt[8], (unsigned long long)grp[1]); }
     }
 }
 
@@ -1005,7 +1007,7 @@ extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t c
         SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
         for (int k = 0; k < 7; ++k) counters7[k] = h[k];
-        ctx->moLookups[0] = h[6]; ctx->moLookups[1] = h[7]; ctx->moLookups[2] = h[8];
+        ctx->moLookups[0] = h[6]; ctx->moLookups[1] = h[7]; ctx->moLookups[2] = h[8]; ctx->moGroups[0] = h[9]; ctx->moGroups[1] = h[10];
     }
     return 0;
 }
@@ -1017,7 +1019,7 @@ extern "C" int skc_mo_table_stats(skc_ctx *ctx, double *stats8) {
     if (!ctx) return 1;
     stats8[0] = ctx->mocRows ? ctx->mocRowCount : 0; stats8[1] = ctx->mocRows ? ((double)ctx->mocRowCount * 32 + ctx->mocHeadFloats) * 4 : 0;
     stats8[2] = ctx->mocRows ? ctx->mocCoverage : 0; stats8[3] = ctx->mocRows ? ctx->mocMaxErr : 0;
-    stats8[4] = (double)ctx->moLookups[0]; stats8[5] = (double)ctx->moLookups[1]; stats8[6] = (double)ctx->moLookups[2]; stats8[7] = 0;
+    stats8[4] = (double)ctx->moLookups[0]; stats8[5] = (double)ctx->moLookups[1]; stats8[6] = (double)ctx->moLookups[2]; stats8[7] = (double)ctx->moGroups[0] + (double)ctx->moGroups[1];
     return 0;
 }
 

@@ -290,7 +290,7 @@ class SkinDevice:
         st = np.zeros(8, np.float64)
         self._ck(self.lib.skc_mo_table_stats(self.ctx, _ptr(st)))
         return dict(rows=int(st[0]), smem_bytes=int(st[1]), coverage=float(st[2]), max_err=float(st[3]),
-                    lookups=int(st[4]), from_heads=int(st[5]), from_global=int(st[6]))
+                    lookups=int(st[4]), from_heads=int(st[5]), from_global=int(st[6]), accept_groups=int(st[7]))
 
     def li_sss(self, hits, max_error, mix=0.5, albedo=None):
         hits = np.ascontiguousarray(hits if hits.dtype == DT_HIT else hits.view(DT_HIT).reshape(-1))

@@ -61,7 +61,7 @@ def main():
            "L_row_rel_err_max": float(err.max()), "L_row_rel_err_p999": float(np.quantile(err, 0.999)), "L_row_rel_err_mean": float(err.mean()),
            "image_rmse_rel": rmse, "stats_exact": a["stats"], "stats_compact": b["stats"]}
     out["variants"] = {}
-    for name, env in (("headcap16384", {"SKC_MO_HEADCAP": "16384"}), ("warps24", {"SKC_MO_WARPS": "24"}), ("warps20", {"SKC_MO_WARPS": "20"})):
+    for name, env in (("tol3e-5", {"SKC_MO_TOL": "3e-5"}), ("tol5e-5", {"SKC_MO_TOL": "5e-5"}), ("tol8e-5", {"SKC_MO_TOL": "8e-5"})):
         if os.environ.get("MO_AB_VARIANTS", "1") == "0":
             break
         c = frame(pkg, scene, "compact", counters=True, env=env)
