@@ -23,6 +23,7 @@ struct skc_ctx {
     int smCount = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t timer0 = nullptr, timer1 = nullptr;   // skc_timer_begin / skc_timer_end_ms
     cudaStream_t prefetchStream = nullptr;   // skc_frame_prefetch: sampler stream, closest hits, direct-lighting terms beside Preprocess (lowest priority)
     cudaStream_t auxStream = nullptr;        // octree topology while the irradiance pass runs on `stream` (skc_preprocess*)
     cudaEvent_t defEv0 = nullptr, defEv1 = nullptr;   // deferred stage timing of the irradiance pass

@@ -99,6 +99,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     skc_frame_release(ctx);
     for (int i = 0; i < 20; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    if (ctx->timer0) { cudaEventDestroy(ctx->timer0); cudaEventDestroy(ctx->timer1); }
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     cudaStreamSynchronize(ctx->copyStream);
     cudaStreamDestroy(ctx->copyStream);
@@ -127,19 +128,19 @@ extern "C" float skc_stage_ms(const skc_ctx *ctx, int stage) {
 }
 
 // whole-step timing on the context's stream (bench.py): CUDA events, not wall clock
-static cudaEvent_t g_t0 = nullptr, g_t1 = nullptr;
+// (the events belong to the context: a second context on another GPU of the same process must not record events of a foreign device)
 extern "C" int skc_timer_begin(skc_ctx *ctx) {
     cudaSetDevice(ctx->device);
-    if (!g_t0) { SKC_CUDA(cudaEventCreate(&g_t0)); SKC_CUDA(cudaEventCreate(&g_t1)); }
-    SKC_CUDA(cudaEventRecord(g_t0, ctx->stream));
+    if (!ctx->timer0) { SKC_CUDA(cudaEventCreate(&ctx->timer0)); SKC_CUDA(cudaEventCreate(&ctx->timer1)); }
+    SKC_CUDA(cudaEventRecord(ctx->timer0, ctx->stream));
     return 0;
 }
 extern "C" float skc_timer_end_ms(skc_ctx *ctx) {
     cudaSetDevice(ctx->device);
-    if (!g_t0) return -1.f;
-    if (cudaEventRecord(g_t1, ctx->stream) != cudaSuccess || cudaEventSynchronize(g_t1) != cudaSuccess) return -1.f;
+    if (!ctx->timer0) return -1.f;
+    if (cudaEventRecord(ctx->timer1, ctx->stream) != cudaSuccess || cudaEventSynchronize(ctx->timer1) != cudaSuccess) return -1.f;
     float ms = -1.f;
-    cudaEventElapsedTime(&ms, g_t0, g_t1);
+    cudaEventElapsedTime(&ms, ctx->timer0, ctx->timer1);
     return ms;
 }
 extern "C" int skc_set_point_count(skc_ctx *ctx, uint64_t n) {

@@ -21,6 +21,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <algorithm>
 #include "skc_internal.h"
 #include "skc_cie.h"
 
@@ -270,6 +271,8 @@ static int ensureOctreeStorage(skc_ctx *ctx, uint64_t n, uint32_t cap) {
 
 // Topology: bounds, breadth-first splitting, leaf order.  Reads only the point POSITIONS, so a multi-GPU caller can run it
 // while the irradiance rows (8x the bytes) are still being gathered from the other ranks.
+static int topologyWithCapacity(skc_ctx *ctx, uint32_t n, uint32_t cap, uint32_t *needOut);
+
 extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
@@ -277,14 +280,27 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     uint64_t n64 = ctx->ipCount;
     if (n64 > 0x1fffffffull) return skc_fail(ctx, "skc_build_octree: more than 2^29 irradiance points");
     uint32_t n = (uint32_t)n64;
-    static bool cieUp = false;
     {
         float y[32] = {0};
         for (int i = 0; i < SKC_NS; ++i) y[i] = SKC_CIE_Y30[i];
         SKC_CUDA(cudaMemcpyToSymbolAsync(c_cieY, y, sizeof y, 0, cudaMemcpyHostToDevice, ctx->stream));
-        cieUp = true; (void)cieUp;
     }
-    uint32_t cap = n + n / 2 + 4096;
+    // n + n/2 nodes hold every surface-like point set; tight clusters of 9+ near-coincident points grow chains of
+    // single-child interior nodes (the reference's Insert has no depth limit) and can need more: grow and retry
+    uint32_t cap = std::max(ctx->otCap, n + n / 2 + 4096);
+    for (int attempt = 0; attempt < 6; ++attempt) {
+        uint32_t need = 0;
+        int rc = topologyWithCapacity(ctx, n, cap, &need);
+        if (rc != 3) return rc;
+        uint64_t grown = std::max<uint64_t>((uint64_t)need + need / 8 + 4096, (uint64_t)cap * 2);
+        if (grown > 0xfffffff0ull) break;
+        cap = (uint32_t)grown;
+    }
+    return skc_fail(ctx, "skc_build_octree: the tree needs more than %u nodes", cap);
+}
+
+// 0 = done, 1 = error, 3 = node capacity exceeded (*needOut = nodes needed where known, else 0)
+static int topologyWithCapacity(skc_ctx *ctx, uint32_t n, uint32_t cap, uint32_t *needOut) {
     if (ensureOctreeStorage(ctx, n, cap)) return 1;
     skc_stage_begin(ctx);
     // --- bounds (multipolesubsurface.cpp:223-225): union of the point positions
@@ -308,6 +324,7 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
         uint32_t totalSorted = 0;
         int rc = skc_octree_topology_sorted(ctx, n, hb, cap, ls, &totalSorted);
         if (rc == 1) return 1;
+        if (rc == 3) { *needOut = totalSorted; return 3; }
         if (rc == 0) {
             OtBuild bs; memset(&bs, 0, sizeof bs);
             bs.nodes = ctx->otGeo;
@@ -355,7 +372,7 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
         uint32_t hc[3];
         SKC_CUDA(cudaMemcpyAsync(hc, b.counters, sizeof hc, cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (hc[1]) return skc_fail(ctx, "skc_build_octree: node capacity %u exceeded", cap);
+        if (hc[1]) { *needOut = 0; return 3; }
         std::swap(idxA, idxB); std::swap(snA, snB);
         curStart = total; curCount = hc[0] - total; total = hc[0]; active = hc[2];
         levelStart.push_back(curStart);

@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(OTS_BLOCK) k_emit_nodes(const unsigned long lo
 }
 
 // Returns 0 and fills levelStart (first node of each level + sentinel) and total; 2 = tree deeper than OTS_LEVELS
-// (caller falls back to the level-by-level builder); 1 = error.  ctx->otGeo must hold `cap` nodes, ctx->otPointIdx n ids.
+// (caller falls back to the level-by-level builder); 3 = the tree has *totalOut > cap nodes (caller grows otGeo and retries); 1 = error.  ctx->otGeo must hold `cap` nodes, ctx->otPointIdx n ids.
 int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32_t cap, std::vector<uint32_t> &levelStart, uint32_t *totalOut) {
     uint32_t nBlocks = (n + OTS_BLOCK - 1) / OTS_BLOCK;
     size_t tempBytes = 0;
@@ -227,7 +227,7 @@ int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32
     }
     lv.start[OTS_LEVELS + 1] = total;
     levelStart.push_back(total);
-    if (total > cap) return skc_fail(ctx, "skc_build_octree: node capacity %u exceeded (%u nodes)", cap, total);
+    if (total > cap) { *totalOut = total; return 3; }      // the exact node count is known before anything is emitted: the caller grows the storage and retries
     SKC_CUDA(cudaMemsetAsync(ctx->otGeo, 0, (size_t)total * 3 * sizeof(float4), ctx->stream));
     k_emit_nodes<<<nBlocks, OTS_BLOCK, 0, ctx->stream>>>(keys, info, n, nBlocks, blockCount, lv, root, ctx->otGeo, (int)levelStart.size() - 2);
     SKC_LAUNCHED("k_emit_nodes");

@@ -345,7 +345,7 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
     if (layers->size() != 4) { Error("LayeredSkin: exactly two skin layers (epidermis, dermis) are supported on the device path; %d given", (int)layers->size() / 2); return false; }
     SkinParams k;
     k.layerThickness[0] = (*layers)[0]; k.layerIor[0] = (*layers)[1]; k.layerThickness[1] = (*layers)[2]; k.layerIor[1] = (*layers)[3];
-    k.roughness = F("roughness", 0.3f);
+    k.roughness = F("roughness", 0.4f);                      // materials/layeredskin.cpp:234
     k.nmperunit = F("nmperunit", 100e6f);
     k.f_mel = F("f_mel", 0.15f); k.f_eu = F("f_eu", 1.f); k.f_blood = F("f_blood", 0.002f); k.f_ohg = F("f_ohg", 0.3f);
     k.desiredlength = shapeParams.FindOneInt("desiredlength", mp.FindOneInt("desiredlength", 512));
@@ -359,6 +359,20 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
         if (t.empty()) t = mp.FindTexture(tex);
         if (!t.empty()) { Error("layeredskin \"texture %s\" \"%s\": textures on the skin are not supported on the device path (constant albedo, no bump map)", tex, t.c_str()); return false; }
     }
+    // Parameters the device path cannot honour are refused by name, not dropped: "color albedo" scales E by albedo^mix and
+    // Li by albedo^(1-mix) (multipolesubsurface.cpp:139-140,287), "doublerefsslf" swaps in FixedFresnelDielectric
+    // (layeredskin.cpp:103-109), "genprofile false" / "usemontecarlo true" select other profile sources (:97-101).
+    auto B = [&](const char *n, bool d) { return shapeParams.FindOneBool(n, mp.FindOneBool(n, d)); };
+    if (mp.FindFloats("albedo", "color", "spectrum") || shapeParams.FindFloats("albedo", "color", "spectrum")) {
+        Error("layeredskin \"color albedo\": a constant albedo other than the default Spectrum(1) is not supported on the device path"); return false; }
+    if (B("doublerefsslf", false)) { Error("layeredskin \"bool doublerefsslf\" \"true\" is not supported on the device path"); return false; }
+    if (!B("genprofile", true)) { Error("layeredskin \"bool genprofile\" \"false\" is not supported on the device path (the multipole profile is always generated)"); return false; }
+    if (B("usemontecarlo", false)) { Error("layeredskin \"bool usemontecarlo\" \"true\" is not supported on the device path (multipole profiles only)"); return false; }
+    // read by the reference's factory but without effect on this path: Henyey-Greenstein g / b of the LayeredIntegrator's random
+    // walk (layeredskin.cpp:53-60), photon count of the Monte-Carlo profile, the irradiance-point display of the material
+    for (const char *n : {"ga_epi", "ga_derm", "b_derm", "irradiancepointsize"}) { mp.FindOneFloat(n, 0.f); shapeParams.FindOneFloat(n, 0.f); }
+    mp.FindOneString("photons", ""); shapeParams.FindOneString("photons", "");
+    if (B("showirradiancepoints", false)) Warn("layeredskin \"bool showirradiancepoints\" is ignored on the device path");
     if (mp.Has("rgbprofile") || shapeParams.Has("rgbprofile"))
         if (shapeParams.FindOneBool("rgbprofile", mp.FindOneBool("rgbprofile", false))) { Error("layeredskin \"bool rgbprofile\" \"true\" is not supported on the device path (30-bin spectral profiles only)"); return false; }
     *out = k;
@@ -431,6 +445,7 @@ void Front::shape(const std::string &name, const ParamSet &ps) {
     if (!ps.FindTexture("alpha").empty() || ps.FindOneFloat("alpha", 1.f) == 0.f) { Error("trianglemesh \"alpha\" is not supported on the device path"); return; }
     SkinParams k;
     if (!skinFromParams(*matParams, ps, &k)) return;
+    reportUnused(*matParams, "Material \"layeredskin\"");
     if (haveSkin && !sameSkin(k, skinOfScene)) { Error("more than one distinct layeredskin material in the scene: the device path holds one profile table"); return; }
     haveSkin = true; skinOfScene = k; sd->skin = k;
     TriangleMesh m;

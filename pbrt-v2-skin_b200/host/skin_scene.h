@@ -48,7 +48,7 @@ struct SphereLight {
 
 // LayeredSkin parameters (materials/layeredskin.cpp:222-262)
 struct SkinParams {
-    float roughness = 0.3f, nmperunit = 100e6f;
+    float roughness = 0.4f, nmperunit = 100e6f;      // materials/layeredskin.cpp:234-235
     float f_mel = 0.15f, f_eu = 1.f, f_blood = 0.002f, f_ohg = 0.3f;
     int desiredlength = 512;
     // "color Kr" / "color Kt" as the skin scenes give them (results/PigmentManips/Eum0.1_Deoxy0.5.pbrt:37-38); the scene-file

@@ -401,6 +401,40 @@ def test_octree_deep_clusters_take_the_full_sort(dev, scene):
         assert np.array_equal(mo0.view(np.uint32), mo1.view(np.uint32))
 
 
+def test_octree_grows_its_node_storage_for_clustered_points(pkg, scene):
+    """2 000 clusters of 10 near-coincident points: every cluster hangs on a chain of single-child interior nodes, so the
+    tree has far more than the n + n/2 nodes that surface-like point sets need.  The reference's Insert handles this
+    (diffusionutil.h:94-132 has no depth or node limit); the device builders must grow their storage and retry, and agree
+    with the C restatement of Insert / InitHierarchy in node count and root."""
+    g = scene
+    rng = np.random.RandomState(3)
+    pts = g.irradiance_points[:20000].copy()
+    ext = float((pts["p"].max(0) - pts["p"].min(0)).max())
+    centres = pts["p"][::10].copy()
+    pts["p"] = np.repeat(centres, 10, axis=0)[:len(pts)] + (rng.rand(len(pts), 3).astype(np.float32) - 0.5) * np.float32(2e-6 * ext)
+    tree = orc.Octree(pts, g.cie[1])
+    n_ref, root_ref, _ = tree.info()
+    assert n_ref > len(pts) + len(pts) // 2 + 4096, n_ref          # beyond the first-guess capacity
+    d = pkg.SkinDevice(0)                                            # a fresh context: no storage left over from larger scenes
+    try:
+        gu.setup_device(d, g)
+        d.set_irradiance_points(pts)
+        for levelwise in (False, True):
+            if levelwise:
+                os.environ["SKC_OCTREE_LEVELWISE"] = "1"
+            try:
+                n_dev, root_dev, _ = d.build_octree()
+            finally:
+                os.environ.pop("SKC_OCTREE_LEVELWISE", None)
+            assert n_dev == n_ref
+            assert np.array_equal(root_dev.view(np.uint32), root_ref.view(np.uint32))
+        q = np.ascontiguousarray(pts["p"][:64])
+        e = gu.row_rel_err(d.mo(q, g.max_error), tree.mo(q, g.profile_rd, g.profile_hdr[:, 1], g.max_error))
+        assert e.max() < 1e-5, e.max()
+    finally:
+        d.close(); tree.close()
+
+
 def test_preprocess_one_call_equals_staged_calls(dev, scene):
     """skc_preprocess (irradiance pass + octree topology overlapped on two streams) followed by
     skc_build_octree_finalize gives bit-identical irradiance rows, octree root and Mo to skc_irradiance followed by

@@ -68,7 +68,7 @@ def test_defaults_follow_the_reference_factories(pkg, tmp_path):
     assert (s.maxdepth, s.maxerror, s.minsampledistance, s.mix) == (5, np.float32(.05), .25, .5)   # multipolesubsurface.cpp:309-316
     assert s.accelerator() == ("sah", 4)                                  # accelerators/bvh.cpp:549-550
     k = s.skin      # roughness nmperunit f_mel f_eu f_blood f_ohg desiredlength lerp (layeredskin.cpp:234-257)
-    assert np.allclose(k[:8], [0.3, 100e6, 0.15, 1.0, 0.002, 0.3, 512, 1])
+    assert np.allclose(k[:8], [0.4, 100e6, 0.15, 1.0, 0.002, 0.3, 512, 1])     # roughness 0.4: layeredskin.cpp:234
     xw, yw, table = s.pixel_filter()
     assert (xw, yw) == (.5, .5) and np.all(table == 1)                    # box, api.cpp default
     assert list(s.light_samples()) == [8]
@@ -148,6 +148,10 @@ def test_shape_parameters_override_material_parameters(pkg, tmp_path):
     (scene_text(""), "multipolesubsurface"),
     (scene_text(world='LightSource "infinite"\n' + TRI % ("", "")), 'LightSource "infinite"'),
     (scene_text(mat='"texture albedo" "tex"'), "texture albedo"),
+    (scene_text(mat='"color albedo" [0.8 0.6 0.5]'), "color albedo"),
+    (scene_text(mat='"bool doublerefsslf" "true"'), "doublerefsslf"),
+    (scene_text(mat='"bool usemontecarlo" "true"'), "usemontecarlo"),
+    (scene_text(mat='"bool genprofile" "false"'), "genprofile"),
     (scene_text('SurfaceIntegrator "multipolesubsurface" "bool usepoissonpointfinder" "true"'), "usepoissonpointfinder"),
     (scene_text('Renderer "metropolis"\nSurfaceIntegrator "multipolesubsurface"'), 'Renderer "metropolis"'),
     (scene_text(world=LIGHT + 'Shape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]'), 'Material "matte"'),
@@ -174,6 +178,9 @@ def test_refusals_name_the_directive(pkg, tmp_path, text, needle):
 def test_unused_parameters_are_reported(pkg, tmp_path):
     s = load(pkg, tmp_path, scene_text('SurfaceIntegrator "multipolesubsurface" "float maxeror" 0.2'))
     assert any('"maxeror" not used' in w for w in s.warnings)             # ParamSet::ReportUnused
+    s = load(pkg, tmp_path, scene_text(mat='"float rougness" 0.2 "float ga_epi" 0.9 "string photons" "100"'))
+    assert any('"rougness" not used (Material' in w for w in s.warnings)  # the Material's own parameter list is checked too
+    assert not any("ga_epi" in w or "photons" in w for w in s.warnings)    # read by CreateLayeredSkinMaterial (layeredskin.cpp:240-249)
 
 
 def test_pbrt_executable_usage_and_errors(pkg, tmp_path):
