@@ -103,6 +103,13 @@ float skc_stage_ms(const skc_ctx *ctx, int stage);
 int skc_timer_begin(skc_ctx *ctx);
 float skc_timer_end_ms(skc_ctx *ctx);
 
+/* Test hook: the device's sinf / cosf on n host floats.  The reference calls libm's sinf/cosf in UniformSampleCone
+ * (core/montecarlo.cpp) and Beckmann::Sample_f (core/reflection.cpp); the device restates glibc's algorithm so that the results
+ * agree bit for bit (csrc/skc_common.cuh). */
+int skc_test_sincosf(skc_ctx *ctx, const float *x, uint64_t n, float *sinOut, float *cosOut);
+/* ... and any one of them: fn 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf (Beckmann::Sample_f / D, core/reflection.cpp:548-569). */
+int skc_test_libmf(skc_ctx *ctx, int fn, const float *x, uint64_t n, float *out);
+
 /* ---- BVHAccel (accelerators/bvh.cpp) ------------------------------------------------ */
 /* Upload the flat tree BVHAccel::flattenBVHTree (bvh.cpp:362-380) produced, the ordered
  * primitive list, the world-space triangle meshes (shapes/trianglemesh.cpp:72-73) and the
@@ -144,6 +151,12 @@ int skc_set_irradiance_points(skc_ctx *ctx, const skc_irr_point *pts, uint64_t n
 /* Device-resident packed record (p, area, E[30]) range access for the multi-GPU exchange:
  * returns device pointers to the float4 {p,area} array and the [n][32] E array. */
 int skc_irradiance_dev(skc_ctx *ctx, uint64_t nTotal, void **posArea_dev, void **E_dev);
+/* Rows first, first+stride, ... (count of them) of the device irradiance-point set back to the host: posArea4 [count][4]
+ * = IrradiancePoint::p, area and E30 [count][30] = IrradiancePoint::E (integrators/irradiancepoint.h:36-45); either may be
+ * NULL.  For parity checks of point sets too large to copy out whole. */
+int skc_get_irradiance_rows(skc_ctx *ctx, uint64_t first, uint64_t count, uint64_t stride, float *posArea4, float *E30);
+/* ... and the other way: overwrite E30 [count][30] (and posArea4 [count][4] unless NULL) of device points first .. first+count-1. */
+int skc_set_irradiance_rows(skc_ctx *ctx, uint64_t first, uint64_t count, const float *posArea4, const float *E30);
 /* After an exchange into arrays sized for padded shards: the number of valid points. */
 int skc_set_point_count(skc_ctx *ctx, uint64_t n);
 /* SubsurfaceOctreeNode::Insert + InitHierarchy (integrators/diffusionutil.h:94-173) over

@@ -15,7 +15,7 @@ __device__ __forceinline__ float beckmannD(const RhoBxdf &b, float whz) {
     float d = c2 * c2 * SKC_PI_F;
     if (d == 0.f) return 0.f;
     float e = (c2 - 1) * b.rcpRMS2 / c2;
-    return b.rcpRMS2 * expf(e) / d;
+    return b.rcpRMS2 * skc_expf(e) / d;        // libm's expf, bit for bit (skc_common.cuh)
 }
 
 __device__ __forceinline__ float fresnelDielectric(const RhoBxdf &b, float cosi) {
@@ -39,12 +39,12 @@ __device__ __forceinline__ float fresnelDielectric(const RhoBxdf &b, float cosi)
 
 // ---- local-frame helpers (core/reflection.h:49-75) ---------------------------------------------------------------
 __device__ __forceinline__ bool sameHemisphere(f3 w, f3 wp) { return w.z * wp.z > 0.f; }
-// libm's float functions are correctly rounded in all but rare cases; rounding the fp64 result reproduces them more
-// often than CUDA's 1-2 ulp fp32 versions do
-__device__ __forceinline__ float cr_cosf(float x) { return (float)cos((double)x); }
-__device__ __forceinline__ float cr_sinf(float x) { return (float)sin((double)x); }
-__device__ __forceinline__ float cr_logf(float x) { return (float)log((double)x); }
-__device__ __forceinline__ float cr_atanf(float x) { return (float)atan((double)x); }
+// libm's float functions as glibc computes them (restated in skc_common.cuh; they are not correctly rounded, and the
+// reference's results depend on their last bit)
+__device__ __forceinline__ float cr_cosf(float x) { return skc_cosf(x); }     // libm's cosf / sinf bit for bit (skc_common.cuh)
+__device__ __forceinline__ float cr_sinf(float x) { return skc_sinf(x); }
+__device__ __forceinline__ float cr_logf(float x) { return skc_logf(x); }
+__device__ __forceinline__ float cr_atanf(float x) { return skc_atanf(x); }
 
 // Beckmann::Sample_f (core/reflection.cpp:548-569)
 __device__ inline void beckmannSample(const RhoBxdf &b, f3 wo, float u1, float u2, f3 *wi, float *pdf) {

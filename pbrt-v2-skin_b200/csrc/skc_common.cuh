@@ -151,3 +151,138 @@ __host__ __device__ inline float dist2(f3 a, f3 b) { f3 d = sub3(a, b); return d
 
 /* core/pbrt.h:193-196 redefines M_PI as a FLOAT literal: everything "times pi" is fp32 */
 #define SKC_PI_F 3.14159265358979323846f
+
+// ------------------------------------------------------------------------------------
+// sinf / cosf exactly as the reference's libm computes them.  The reference calls glibc's float sinf/cosf (UniformSampleCone,
+// core/montecarlo.cpp; Beckmann::Sample_f, core/reflection.cpp), which are NOT correctly rounded (0.56 ULP): against the rounded
+// fp64 result they differ in 0.09 % (sin) / 0.04 % (cos) of the arguments in [0, 2pi] -- with 16 evaluations per irradiance point
+// that made 6 % of the irradiance rows differ from the reference's in the last bit, and at 24.6 M points such one-ulp
+// differences flip enough accept/refine decisions of the hierarchical Mo to move 1 % of the hit points by 1e-4..3e-3.  So the
+// device evaluates glibc's own algorithm (sysdeps/ieee754/flt-32/s_sincosf.h: fp64 range reduction by pi/2 and two fp64
+// polynomials, one rounding to float), operation for operation, without contraction.  Verified against libm's sinf/cosf on
+// every one of the 1 086 918 620 floats in [0, 2pi] (tests/test_sincosf.py restates the check on a sample).  |x| >= 120 (never
+// reached by the callers: phi in [0, 2pi], theta in [0, pi/2]) falls back to the rounded fp64 result.
+__device__ __forceinline__ float skcSinCosPoly(double x, double x2, bool negate, int n) {
+    const double sg = negate ? -1.0 : 1.0;
+    if ((n & 1) == 0) {
+        const double s1c = -0x1.555545995a603p-3, s2c = 0x1.1107605230bc4p-7, s3c = -0x1.994eb3774cf24p-13;
+        double x3 = __dmul_rn(x, x2);
+        double s1 = __dadd_rn(s2c, __dmul_rn(x2, s3c));
+        double x7 = __dmul_rn(x3, x2);
+        double s = __dadd_rn(x, __dmul_rn(x3, s1c));
+        return (float)__dadd_rn(s, __dmul_rn(x7, s1));
+    }
+    const double c0 = sg * 0x1p0, c1c = sg * -0x1.ffffffd0c621cp-2, c2c = sg * 0x1.55553e1068f19p-5, c3c = sg * -0x1.6c087e89a359dp-10, c4c = sg * 0x1.99343027bf8c3p-16;
+    double x4 = __dmul_rn(x2, x2);
+    double c2 = __dadd_rn(c3c, __dmul_rn(x2, c4c));
+    double c1 = __dadd_rn(c0, __dmul_rn(x2, c1c));
+    double x6 = __dmul_rn(x4, x2);
+    double c = __dadd_rn(c1, __dmul_rn(x4, c2c));
+    return (float)__dadd_rn(c, __dmul_rn(x6, c2));
+}
+template <bool COS>
+__device__ __forceinline__ float skcSinCosGlibc(float y) {
+    const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ffu;
+    double x = (double)y;
+    if (top < ((0x3f490fdbu >> 20) & 0x7ffu)) {                     // |y| < pi/4 (abstop12 compare)
+        if (top < ((0x39800000u >> 20) & 0x7ffu)) return COS ? 1.0f : y;   // |y| < 2^-12
+        return skcSinCosPoly(x, __dmul_rn(x, x), false, COS ? 1 : 0);
+    }
+    if (top < ((0x42f00000u >> 20) & 0x7ffu)) {                     // |y| < 120: reduce_fast
+        double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+        int n = (__double2int_rz(r) + 0x800000) >> 24;
+        x = __dsub_rn(x, __dmul_rn((double)n, 0x1.921FB54442D18p0));
+        const double sign = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+        return skcSinCosPoly(__dmul_rn(x, sign), __dmul_rn(x, x), (n & 2) != 0, COS ? (n ^ 1) : n);
+    }
+    return COS ? (float)cos(x) : (float)sin(x);
+}
+__device__ __forceinline__ float skc_sinf(float x) { return skcSinCosGlibc<false>(x); }
+__device__ __forceinline__ float skc_cosf(float x) { return skcSinCosGlibc<true>(x); }
+
+// ---- logf, expf, atanf of the reference's libm (glibc 2.39 on x86-64), restated the same way and verified against libm on
+// every float of (0, 1] (logf), [-100, 0] (expf) and [0, inf] (atanf).  They feed Beckmann::Sample_f / D (core/reflection.cpp
+// :548-569, reflection.h:516-523), i.e. the rho_hd table (core/multipole.cpp:488-549) and the BSDF sampling of direct lighting.
+// A rho_hd table that differs from the reference's in the last bit of some entries makes 6 % of the irradiance rows differ in
+// their last bit, which at 24.6 M points is enough to flip accept/refine decisions of Mo (see the note at skc_sinf).
+__device__ __forceinline__ float skc_logf(float x) {       // sysdeps/ieee754/flt-32/e_logf.c (N = 16 table, cubic in fp64)
+    const double invc[16] = {0x1.661ec79f8f3bep+0, 0x1.571ed4aaf883dp+0, 0x1.49539f0f010bp+0, 0x1.3c995b0b80385p+0, 0x1.30d190c8864a5p+0, 0x1.25e227b0b8eap+0,
+                             0x1.1bb4a4a1a343fp+0, 0x1.12358f08ae5bap+0, 0x1.0953f419900a7p+0, 0x1p+0, 0x1.e608cfd9a47acp-1, 0x1.ca4b31f026aap-1,
+                             0x1.b2036576afce6p-1, 0x1.9c2d163a1aa2dp-1, 0x1.886e6037841edp-1, 0x1.767dcf5534862p-1};
+    const double logc[16] = {-0x1.57bf7808caadep-2, -0x1.2bef0a7c06ddbp-2, -0x1.01eae7f513a67p-2, -0x1.b31d8a68224e9p-3, -0x1.6574f0ac07758p-3, -0x1.1aa2bc79c81p-3,
+                             -0x1.a4e76ce8c0e5ep-4, -0x1.1973c5a611cccp-4, -0x1.252f438e10c1ep-5, 0x0p+0, 0x1.aa5aa5df25984p-5, 0x1.c5e53aa362eb4p-4,
+                             0x1.526e57720db08p-3, 0x1.bc2860d22477p-3, 0x1.1058bc8a07ee1p-2, 0x1.4043057b6ee09p-2};
+    uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return -INFINITY;
+        if (ix == 0x7f800000u) return x;
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return NAN;
+        ix = __float_as_uint(__fmul_rn(x, 0x1p23f)); ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (tmp >> 19) & 15, k = (int32_t)tmp >> 23;
+    const double z = (double)__uint_as_float(ix - (tmp & 0xff800000u));
+    const double r = __dsub_rn(__dmul_rn(z, invc[i]), 1.0);
+    const double y0 = __dadd_rn(logc[i], __dmul_rn((double)k, 0x1.62e42fefa39efp-1));
+    const double r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(0x1.5575b0be00b6ap-2, r), -0x1.ffffef20a4123p-2);
+    y = __dadd_rn(__dmul_rn(-0x1.00ea348b88334p-2, r2), y);
+    y = __dadd_rn(__dmul_rn(y, r2), __dadd_rn(y0, r));
+    return (float)y;
+}
+static __device__ const unsigned long long skcExp2Tab[32] = {0x3ff0000000000000ull, 0x3fefd9b0d3158574ull, 0x3fefb5586cf9890full, 0x3fef9301d0125b51ull, 0x3fef72b83c7d517bull, 0x3fef54873168b9aaull, 0x3fef387a6e756238ull, 0x3fef1e9df51fdee1ull, 0x3fef06fe0a31b715ull, 0x3feef1a7373aa9cbull, 0x3feedea64c123422ull, 0x3feece086061892dull, 0x3feebfdad5362a27ull, 0x3feeb42b569d4f82ull, 0x3feeab07dd485429ull, 0x3feea47eb03a5585ull, 0x3feea09e667f3bcdull, 0x3fee9f75e8ec5f74ull, 0x3feea11473eb0187ull, 0x3feea589994cce13ull, 0x3feeace5422aa0dbull, 0x3feeb737b0cdc5e5ull, 0x3feec49182a3f090ull, 0x3feed503b23e255dull, 0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull, 0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull};   // asuint64(2^(i/32)) - (i << 52) / 32
+// sysdeps/ieee754/flt-32/e_expf.c; libm selects its FMA build on this CPU family (sysdeps/x86_64/fpu/multiarch/e_expf.c): the
+// scaled argument enters the rounding-to-integer step and the remainder through fused multiply-adds
+__device__ __forceinline__ float skc_expf(float x) {
+    const uint32_t abstop = (__float_as_uint(x) >> 20) & 0x7ffu;
+    if (abstop >= 0x42bu) {                       // |x| >= 88
+        if (__float_as_uint(x) == 0xff800000u) return 0.f;
+        if (abstop >= 0x7f8u) return x + x;
+        if (x > 0x1.62e42ep6f) return INFINITY;
+        if (x < -0x1.9fe368p6f) return 0.f;
+    }
+    const double inv = 0x1.71547652b82fep+0 * 32, shift = 0x1.8p52, xd = (double)x;
+    const double z = __dmul_rn(inv, xd);
+    double kd = __fma_rn(inv, xd, shift);
+    const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd = __dsub_rn(kd, shift);
+    const double r = __fma_rn(inv, xd, -kd);
+    (void)z;
+    const double s = __longlong_as_double((long long)(skcExp2Tab[ki & 31] + (ki << 47)));
+    const double C0 = 0x1.c6af84b912394p-5 / 32 / 32 / 32, C1 = 0x1.ebfce50fac4f3p-3 / 32 / 32, C2 = 0x1.62e42ff0c52d6p-1 / 32;
+    const double zz = __dadd_rn(__dmul_rn(C0, r), C1), r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(C2, r), 1.0);
+    y = __dadd_rn(__dmul_rn(zz, r2), y);
+    return (float)__dmul_rn(y, s);
+}
+__device__ __forceinline__ float skc_atanf(float x) {      // sysdeps/ieee754/flt-32/s_atanf.c (fdlibm, fp32 arithmetic, no contraction)
+    const float atanhi[4] = {4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f};
+    const float atanlo[4] = {5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f, 7.5497894159e-08f};
+    const float aT[11] = {3.3333334327e-01f, -2.0000000298e-01f, 1.4285714924e-01f, -1.1111110449e-01f, 9.0908870101e-02f, -7.6918758452e-02f,
+                          6.6610731184e-02f, -5.8335702866e-02f, 4.9768779427e-02f, -3.6531571299e-02f, 1.6285819933e-02f};
+    const int32_t hx = __float_as_int(x), ix = hx & 0x7fffffff;
+    int id;
+    if (ix >= 0x4c000000) { if (ix > 0x7f800000) return x + x; return hx > 0 ? __fadd_rn(atanhi[3], atanlo[3]) : __fsub_rn(-atanhi[3], atanlo[3]); }
+    if (ix < 0x3ee00000) { if (ix < 0x31000000) return x; id = -1; }
+    else {
+        x = fabsf(x);
+        if (ix < 0x3f980000) {
+            if (ix < 0x3f300000) { id = 0; x = __fdiv_rn(__fsub_rn(__fmul_rn(2.0f, x), 1.0f), __fadd_rn(2.0f, x)); }
+            else { id = 1; x = __fdiv_rn(__fsub_rn(x, 1.0f), __fadd_rn(x, 1.0f)); }
+        } else {
+            if (ix < 0x401c0000) { id = 2; x = __fdiv_rn(__fsub_rn(x, 1.5f), __fadd_rn(1.0f, __fmul_rn(1.5f, x))); }
+            else { id = 3; x = __fdiv_rn(-1.0f, x); }
+        }
+    }
+    const float z = __fmul_rn(x, x), w = __fmul_rn(z, z);
+    float a = __fmul_rn(w, aT[10]);
+    a = __fmul_rn(w, __fadd_rn(aT[8], a)); a = __fmul_rn(w, __fadd_rn(aT[6], a)); a = __fmul_rn(w, __fadd_rn(aT[4], a)); a = __fmul_rn(w, __fadd_rn(aT[2], a));
+    const float s1 = __fmul_rn(z, __fadd_rn(aT[0], a));
+    float b = __fmul_rn(w, aT[9]);
+    b = __fmul_rn(w, __fadd_rn(aT[7], b)); b = __fmul_rn(w, __fadd_rn(aT[5], b)); b = __fmul_rn(w, __fadd_rn(aT[3], b));
+    const float s2 = __fmul_rn(w, __fadd_rn(aT[1], b));
+    if (id < 0) return __fsub_rn(x, __fmul_rn(x, __fadd_rn(s1, s2)));
+    const float zr = __fsub_rn(atanhi[id], __fsub_rn(__fsub_rn(__fmul_rn(x, __fadd_rn(s1, s2)), atanlo[id]), x));
+    return hx < 0 ? -zr : zr;
+}

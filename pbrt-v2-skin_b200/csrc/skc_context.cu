@@ -148,3 +148,67 @@ extern "C" int skc_set_point_count(skc_ctx *ctx, uint64_t n) {
     ctx->ipCount = n;
     return 0;
 }
+
+// Rows first, first+stride, ... (count of them) of the device irradiance-point set: {p, area} and E[30] (IrradiancePoint::p / area / E,
+// integrators/irradiancepoint.h:36-45).  For parity checks of sets too large to copy out whole.  Either output may be NULL.
+extern "C" int skc_get_irradiance_rows(skc_ctx *ctx, uint64_t first, uint64_t count, uint64_t stride, float *posArea4, float *E30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!count) return 0;
+    if (!stride || first + (count - 1) * stride >= ctx->ipCount) return skc_fail(ctx, "skc_get_irradiance_rows: range beyond the %llu device points", (unsigned long long)ctx->ipCount);
+    if (posArea4) SKC_CUDA(cudaMemcpy2DAsync(posArea4, sizeof(float4), ctx->ipPosArea + first, stride * sizeof(float4), sizeof(float4), count, cudaMemcpyDeviceToHost, ctx->stream));
+    if (E30) SKC_CUDA(cudaMemcpy2DAsync(E30, SKC_NS * sizeof(float), ctx->ipE + first * SKC_EPAD, stride * SKC_EPAD * sizeof(float), SKC_NS * sizeof(float), count, cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// The counterpart of skc_get_irradiance_rows: overwrite E (and, if given, {p, area}) of `count` device points starting at `first`.
+// For parity checks that need one or two rows replaced by the reference's (a shadow-ray visibility flip in a set of millions).
+extern "C" int skc_set_irradiance_rows(skc_ctx *ctx, uint64_t first, uint64_t count, const float *posArea4, const float *E30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!count) return 0;
+    if (first + count > ctx->ipCount) return skc_fail(ctx, "skc_set_irradiance_rows: range beyond the %llu device points", (unsigned long long)ctx->ipCount);
+    if (posArea4) SKC_CUDA(cudaMemcpyAsync(ctx->ipPosArea + first, posArea4, count * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    if (E30) SKC_CUDA(cudaMemcpy2DAsync(ctx->ipE + first * SKC_EPAD, SKC_EPAD * sizeof(float), E30, SKC_NS * sizeof(float), SKC_NS * sizeof(float), count, cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// Test hook: the device's sinf / cosf (skc_common.cuh: glibc's algorithm restated) on n host floats.
+__global__ void k_test_sincosf(const float *__restrict__ x, uint64_t n, float *__restrict__ s, float *__restrict__ c) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { s[i] = skc_sinf(x[i]); c[i] = skc_cosf(x[i]); }
+}
+__global__ void k_test_libmf(int fn, const float *__restrict__ x, uint64_t n, float *__restrict__ out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = fn == 2 ? skc_logf(x[i]) : fn == 3 ? skc_expf(x[i]) : fn == 4 ? skc_atanf(x[i]) : fn == 1 ? skc_cosf(x[i]) : skc_sinf(x[i]);
+}
+// fn: 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf
+extern "C" int skc_test_libmf(skc_ctx *ctx, int fn, const float *x, uint64_t n, float *out) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    float *d = (float *)skc_scratch(ctx, 0, 2 * n * sizeof(float));
+    if (!d) return 1;
+    SKC_CUDA(cudaMemcpyAsync(d, x, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_test_libmf<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(fn, d, n, d + n);
+    SKC_LAUNCHED("k_test_libmf");
+    SKC_CUDA(cudaMemcpyAsync(out, d + n, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+extern "C" int skc_test_sincosf(skc_ctx *ctx, const float *x, uint64_t n, float *sinOut, float *cosOut) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!n) return 0;
+    float *d = (float *)skc_scratch(ctx, 0, 3 * n * sizeof(float));
+    if (!d) return 1;
+    SKC_CUDA(cudaMemcpyAsync(d, x, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_test_sincosf<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d, n, d + n, d + 2 * n);
+    SKC_LAUNCHED("k_test_sincosf");
+    SKC_CUDA(cudaMemcpyAsync(sinOut, d + n, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(cosOut, d + 2 * n, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}

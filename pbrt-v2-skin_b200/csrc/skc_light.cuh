@@ -36,10 +36,9 @@ __device__ inline void coordSys(f3 v1, f3 *v2, f3 *v3) {   // core/geometry.h:56
     *v3 = cross3(v1, *v2);
 }
 
-// glibc's sinf/cosf are correctly rounded in all but rare cases; rounding the fp64 result
-// reproduces them far more often than CUDA's 1-2 ulp fp32 versions do.
-__device__ __forceinline__ float cosf_cr(float x) { return (float)cos((double)x); }
-__device__ __forceinline__ float sinf_cr(float x) { return (float)sin((double)x); }
+// the reference's libm sinf / cosf, bit for bit (skc_common.cuh)
+__device__ __forceinline__ float cosf_cr(float x) { return skc_cosf(x); }
+__device__ __forceinline__ float sinf_cr(float x) { return skc_sinf(x); }
 
 // Sphere::Intersect's DifferentialGeometry normal (shapes/sphere.cpp:103-150 +
 // core/diffgeom.cpp:40-55), needed by ShapeSet::Sample (core/light.cpp:156).

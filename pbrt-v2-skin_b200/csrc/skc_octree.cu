@@ -288,6 +288,7 @@ extern "C" int skc_build_octree_topology(skc_ctx *ctx) {
     // n + n/2 nodes hold every surface-like point set; tight clusters of 9+ near-coincident points grow chains of
     // single-child interior nodes (the reference's Insert has no depth limit) and can need more: grow and retry
     uint32_t cap = std::max(ctx->otCap, n + n / 2 + 4096);
+    if (const char *e = getenv("SKC_OCTREE_CAP")) cap = std::max(ctx->otCap, (uint32_t)std::max(16, atoi(e)));     // tests: force the growth path
     for (int attempt = 0; attempt < 6; ++attempt) {
         uint32_t need = 0;
         int rc = topologyWithCapacity(ctx, n, cap, &need);

@@ -89,10 +89,11 @@ __device__ __forceinline__ float expf_glibc(float x, const unsigned long long *t
     if (x < -0x1.9fe368p6f) return 0.f;
     const double N = 32, shift = 0x1.8p+52, inv = 0x1.71547652b82fep+0 * N;
     const double C0 = 0x1.c6af84b912394p-5 / N / N / N, C1 = 0x1.ebfce50fac4f3p-3 / N / N, C2 = 0x1.62e42ff0c52d6p-1 / N;
-    double z = inv * (double)x, kd = z + shift;
+    // libm's FMA build (the one selected on the reference host's CPU family): the scaled argument enters both steps fused
+    double z, kd = __fma_rn(inv, (double)x, shift);
     unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
     kd -= shift;
-    double r = z - kd;
+    double r = __fma_rn(inv, (double)x, -kd);
     double s = __longlong_as_double((long long)(tab[ki & 31] + (ki << 47)));
     z = C0 * r + C1;
     double r2 = r * r, y = C2 * r + 1.;

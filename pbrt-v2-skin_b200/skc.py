@@ -34,7 +34,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
-           "skc_mo_static", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -110,6 +110,10 @@ def load_library():
     lib.skc_frame_film_dev.restype = vp; lib.skc_frame_film_dev.argtypes = [vp]
     lib.skc_frame_film_get.restype = i32; lib.skc_frame_film_get.argtypes = [vp, vp]
     lib.skc_frame_film_rgb.restype = i32; lib.skc_frame_film_rgb.argtypes = [vp, vp]
+    lib.skc_get_irradiance_rows.restype = i32; lib.skc_get_irradiance_rows.argtypes = [vp, u64, u64, u64, vp, vp]
+    lib.skc_set_irradiance_rows.restype = i32; lib.skc_set_irradiance_rows.argtypes = [vp, u64, u64, vp, vp]
+    lib.skc_test_libmf.restype = i32; lib.skc_test_libmf.argtypes = [vp, i32, vp, u64, vp]
+    lib.skc_test_sincosf.restype = i32; lib.skc_test_sincosf.argtypes = [vp, vp, u64, vp, vp]
     lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_mo_table_stats.restype = i32; lib.skc_mo_table_stats.argtypes = [vp, vp]
     lib.skc_moc_build.restype = vp; lib.skc_moc_build.argtypes = [vp, vp, u32, f32, i32, i32, u32]
@@ -222,6 +226,29 @@ class SkinDevice:
     def set_irradiance_points(self, pts):
         pts = np.ascontiguousarray(pts if pts.dtype == DT_IRR_POINT else pts.view(DT_IRR_POINT).reshape(-1))
         self._ck(self.lib.skc_set_irradiance_points(self.ctx, _ptr(pts), len(pts)))
+
+    def irradiance_rows(self, first, count, stride=1):
+        """({p, area} [count][4], E [count][30]) of device irradiance points first, first+stride, ..."""
+        pa = np.empty((count, 4), np.float32); E = np.empty((count, 30), np.float32)
+        self._ck(self.lib.skc_get_irradiance_rows(self.ctx, first, count, stride, _ptr(pa), _ptr(E)))
+        return pa, E
+
+    def test_libmf(self, fn, x):
+        """The device's restatement of libm's float function fn (0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf) on x."""
+        x = _c(x, np.float32).reshape(-1)
+        out = np.empty_like(x)
+        self._ck(self.lib.skc_test_libmf(self.ctx, int(fn), _ptr(x), len(x), _ptr(out)))
+        return out
+
+    def test_sincosf(self, x):
+        x = _c(x, np.float32).reshape(-1)
+        s = np.empty_like(x); c = np.empty_like(x)
+        self._ck(self.lib.skc_test_sincosf(self.ctx, _ptr(x), len(x), _ptr(s), _ptr(c)))
+        return s, c
+
+    def set_irradiance_rows(self, first, E, pos_area=None):
+        E = _c(E, np.float32).reshape(-1, 30); pos_area = _c(pos_area, np.float32)
+        self._ck(self.lib.skc_set_irradiance_rows(self.ctx, first, len(E), _ptr(pos_area), _ptr(E)))
 
     def irradiance_dev(self, n_total):
         a, b = C.c_void_p(), C.c_void_p()

@@ -64,11 +64,11 @@ def smoke_check(pkg):
         setup_device(dev, g)
         irr = dev.irradiance(g.surface_points, g.n_tasks, g.mix)
         e = row_rel_err(irr["E"], g.irradiance_points["E"])
-        assert np.mean(e < 1e-4) > 0.995, "irradiance parity: %.4f within 1e-4" % np.mean(e < 1e-4)
+        assert e.max() < 1e-6, "irradiance parity: max rel %.3g" % e.max()
         dev.build_octree()
         L = dev.camera_pass(g.camera_rays, g.max_error, g.mix)
         e = row_rel_err(L, g.L_sss)
-        assert np.mean(e < 1e-3) > 0.99, "camera pass parity: %.4f within 1e-3" % np.mean(e < 1e-3)
+        assert e.max() < 1e-5, "camera pass parity: max rel %.3g" % e.max()
         assert dev.launch_count() > 0
         # and against the C restatement on a few hits (oracle/skin_oracle.c)
         import oracle_api as orc

@@ -4,9 +4,9 @@ reference's export of scenes/skin_ld4.scene (tests/golden/skin_ld4.npz, made by 
 oracle/_ref/ref_driver at --ncores 1).
 
 Tolerances: the sampler stream and the camera rays are integer / exactly-rounded work -> bit-exact.  Li per sample:
-1e-4 relative to the row's scale for the bulk of the samples; a small fraction may differ more, because one shadow or
-BSDF ray whose direction differs in the last ulp (libm vs CUDA transcendental functions) can flip visibility at a
-silhouette, which changes one of the 16 direct-lighting terms of that sample.  Image: RMSE 1e-3 relative per channel
+1e-5 relative to the row's scale on EVERY sample (north_star allows 1e-4): the device restates libm's float functions bit
+for bit (csrc/skc_common.cuh), so shadow and BSDF rays do not differ from the reference's in their last ulp and no
+visibility flips occur at silhouettes.  Image: RMSE 1e-3 relative per channel
 (BASELINE.json).
 """
 import os
@@ -70,7 +70,7 @@ def test_frame_radiance_vs_reference(dev, frame, ld4):
     assert np.array_equal(L.max(axis=1) > 0, lit), "different sets of samples carry radiance"
     f4, f3 = np.mean(e[lit] < 1e-4), np.mean(e[lit] < 1e-2)
     print("full Li: %d lit samples, within 1e-4: %.4f, within 1e-2: %.4f, max %.3g" % (lit.sum(), f4, f3, e.max()))
-    assert f4 > 0.97 and f3 > 0.995
+    assert e.max() < 1e-5, "every sample: measured 5.5e-7 (north_star allows 1e-4)"
     # direct lighting alone (L - subsurface term), where it is not negligible
     d_ref = ref - z["L_sss"]
     d_got = L - z["L_sss"]
@@ -78,7 +78,7 @@ def test_frame_radiance_vs_reference(dev, frame, ld4):
     m = scale > 1e-3 * np.abs(ref).max(axis=1)
     ed = np.abs(d_got - d_ref).max(axis=1)[m] / scale[m]
     print("direct term: %d samples, median rel %.3g, within 1e-3: %.4f" % (m.sum(), np.median(ed), np.mean(ed < 1e-3)))
-    assert np.mean(ed < 1e-3) > 0.97
+    assert ed.max() < 1e-3     # a difference of two nearly equal rows: rounding of the sum is amplified by the cancellation
 
 
 def test_frame_image_vs_reference(dev, frame, ld4):

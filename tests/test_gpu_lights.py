@@ -66,7 +66,7 @@ def test_irradiance_and_frame_under_delta_lights(pkg, dev, golden):
         lit = ref.max(axis=1) > 0
         print("irradiance under 4 lights: %d points (%d lit), within 1e-6: %.4f, max rel %.3g" % (len(ref), lit.sum(), np.mean(e < 1e-6), e.max()))
         assert np.array_equal(irr["E"].max(axis=1) > 0, lit)
-        assert np.mean(e < 1e-4) > 0.999, "a shadow ray that differs in the last ulp may flip one of a point's 7 samples"
+        assert e.max() < 1e-6, e.max()
         _, root, _ = dev.build_octree()
         er = np.abs(root - z["octree_root"]) / np.maximum(np.abs(z["octree_root"]), 1e-30)
         assert er.max() < 1e-4
@@ -84,13 +84,13 @@ def test_irradiance_and_frame_under_delta_lights(pkg, dev, golden):
         assert np.array_equal(L.max(axis=1) > 0, lit)
         e = gu.row_rel_err(L, ref)[lit]
         print("full Li: %d lit samples, within 1e-4: %.4f, within 1e-2: %.4f, max %.3g" % (lit.sum(), np.mean(e < 1e-4), np.mean(e < 1e-2), e.max()))
-        assert np.mean(e < 1e-4) > 0.97 and np.mean(e < 1e-2) > 0.995
+        assert e.max() < 1e-5, e.max()
         d_ref = ref - z["L_sss"]; d_got = L - z["L_sss"]
         scale = np.abs(d_ref).max(axis=1)
         m = scale > 1e-3 * np.abs(ref).max(axis=1)
         ed = np.abs(d_got - d_ref).max(axis=1)[m] / scale[m]
         print("direct term alone: %d samples, median rel %.3g, within 1e-3: %.4f" % (m.sum(), np.median(ed), np.mean(ed < 1e-3)))
-        assert np.mean(ed < 1e-3) > 0.97
+        assert ed.max() < 1e-3, ed.max()     # a difference of two nearly equal rows amplifies the rounding of the sum
         rgb = hs.film_to_rgb(dev.frame_film())
         for c in range(3):
             rmse = np.sqrt(np.mean((rgb[..., c] - z["image"][..., c]) ** 2)); s = np.sqrt(np.mean(z["image"][..., c] ** 2))

@@ -98,9 +98,9 @@ def test_irradiance(dev, scene):
     e = gu.row_rel_err(irr["E"], ref["E"])
     frac = np.mean(e < 1e-4)
     print("irradiance: within 1e-4: %.5f  max %.3g  bit-exact rows %.4f" % (frac, e.max(), np.mean((irr["E"] == ref["E"]).all(1))))
-    assert frac >= 0.999, "only %.5f of points within 1e-4 relative" % frac
+    assert e.max() < 1e-6, "irradiance rows: max rel %.3g (measured: bit-exact)" % e.max()
     # black/non-black pattern identical except at the flipped shadow rays
-    assert np.mean((irr["E"].max(1) > 0) == (ref["E"].max(1) > 0)) > 0.9995
+    assert np.array_equal(irr["E"].max(1) > 0, ref["E"].max(1) > 0)
 
 
 def test_octree_root_bit_exact(dev, scene):
@@ -139,7 +139,7 @@ def test_full_device_pipeline(dev, scene):
     e = gu.row_rel_err(L, g.L_sss)
     frac = np.mean(e < 1e-4)
     print("pipeline L_sss: within 1e-4: %.5f  max %.3g" % (frac, e.max()))
-    assert frac > 0.98 and np.mean(e < 1e-3) > 0.995
+    assert e.max() < 1e-5, e.max()
 
 
 def test_empty_inputs(dev, scene):
@@ -233,7 +233,7 @@ def test_irradiance_dense_vs_oracle(dev, scene, pkg):
     e = gu.row_rel_err(irr["E"], ref["E"])
     frac = np.mean(e < 1e-5)
     print("dense irradiance (%d pts): within 1e-5 %.5f, max %.3g, bit-exact %.4f" % (len(pts), frac, e.max(), np.mean((irr["E"] == ref["E"]).all(1))))
-    assert frac > 0.999
+    assert e.max() < 1e-6, e.max()
     # sharded call (multi-GPU slices) gives the same rows as the full call
     a = len(pts) // 3
     part = dev.irradiance(pts, n_tasks, g.mix, first=a, count=len(pts) - 2 * a)
@@ -302,16 +302,22 @@ def test_skin_profile_tables_from_scene(pkg, dev, tiny):
     assert e.max() < 1e-4
 
 
-def test_rho_table_vs_reference(dev, tiny):
+def test_rho_table_vs_reference(dev, tiny, pkg):
     """a8 / N3: the 1025-entry rho_hd table (65 536 stratified samples per entry, same MT19937 jitter streams) against
-    ComputeRhoDataFromBxDF of the reference.  The sample directions go through atanf/logf/sinf/cosf, which differ
-    from glibc's in the last ulp; the per-entry Monte Carlo mean of 65 536 terms keeps that below 1e-5 relative."""
+    ComputeRhoDataFromBxDF of the reference (core/multipole.cpp:488-549), BIT FOR BIT: the sample directions go through libm's
+    atanf / logf / sinf / cosf / expf, which the device restates exactly, and the terms are added in the reference's order with
+    its compensated fp32 sum.  (A table that is merely within 1e-7 makes 6 % of the irradiance rows of a scene differ in their
+    last bit, and at 24.6 M points that moves 1 % of the Mo values by 1e-4 .. 3e-3: tests/test_gpu_full.py.)"""
     hd = dev.rho_table(0.3, 1.4)
     ref = tiny.rho_hd[:1025]
     assert np.all(hd == hd[:, :1]), "spectral channels of an entry must be equal"
+    same = hd[:, 0].view(np.uint32) == ref[:, 0].view(np.uint32)
     e = np.abs(hd[:, 0].astype(np.float64) - ref[:, 0]) / np.abs(ref[:, 0])
-    print("rho_hd: max rel %.3g, bit-exact entries %.3f" % (e.max(), np.mean(hd[:, 0] == ref[:, 0])))
-    assert e.max() < 1e-5
+    print("rho_hd: max rel %.3g, bit-exact entries %d of 1025" % (e.max(), same.sum()))
+    assert same.all(), "entries that differ: %s" % np.nonzero(~same)[0][:20]
+    # the tissue scene's lobe (roughness 0.4, the material's default) as well
+    z = np.load(os.path.join(gu.ROOT, "tests", "golden", "skin_full.npz"))
+    assert np.array_equal(dev.rho_table(0.3, 1.4)[:, :30].view(np.uint32), z["rho_hd"][:1025].view(np.uint32))
 
 
 def test_camera_pass_pinned_output_matches_staged(dev, scene):
@@ -327,7 +333,7 @@ def test_camera_pass_pinned_output_matches_staged(dev, scene):
     assert np.array_equal(L0.view(np.uint32), np.asarray(L1).view(np.uint32))
     assert h0.tobytes() == h1.tobytes()
     e = gu.row_rel_err(L1, g.L_sss)
-    assert np.mean(e < 1e-4) > 0.99
+    assert e.max() < 1e-5, e.max()
 
 
 def c5_parameter_sets(pkg, n_thick=256, desired_length=64):
@@ -402,37 +408,40 @@ def test_octree_deep_clusters_take_the_full_sort(dev, scene):
 
 
 def test_octree_grows_its_node_storage_for_clustered_points(pkg, scene):
-    """2 000 clusters of 10 near-coincident points: every cluster hangs on a chain of single-child interior nodes, so the
-    tree has far more than the n + n/2 nodes that surface-like point sets need.  The reference's Insert handles this
-    (diffusionutil.h:94-132 has no depth or node limit); the device builders must grow their storage and retry, and agree
-    with the C restatement of Insert / InitHierarchy in node count and root."""
+    """Clusters of 10 near-coincident points hang on chains of single-child interior nodes, so such a tree can need more than
+    the n + n/2 nodes that surface-like point sets do.  The reference's Insert handles that (diffusionutil.h:94-132 has no
+    depth or node limit); the device builders grow their storage and retry.  SKC_OCTREE_CAP forces a small first guess so
+    that both builders take the growth path (several times); node count, root and Mo must equal the C restatement's."""
     g = scene
     rng = np.random.RandomState(3)
-    pts = g.irradiance_points[:20000].copy()
+    pts = g.irradiance_points.copy()
     ext = float((pts["p"].max(0) - pts["p"].min(0)).max())
-    centres = pts["p"][::10].copy()
-    pts["p"] = np.repeat(centres, 10, axis=0)[:len(pts)] + (rng.rand(len(pts), 3).astype(np.float32) - 0.5) * np.float32(2e-6 * ext)
+    pts["p"] = np.repeat(pts["p"][::10], 10, axis=0)[:len(pts)] + (rng.rand(len(pts), 3).astype(np.float32) - 0.5) * np.float32(2e-6 * ext)
     tree = orc.Octree(pts, g.cie[1])
     n_ref, root_ref, _ = tree.info()
-    assert n_ref > len(pts) + len(pts) // 2 + 4096, n_ref          # beyond the first-guess capacity
-    d = pkg.SkinDevice(0)                                            # a fresh context: no storage left over from larger scenes
+    assert n_ref > 1.4 * len(pts)
+    q = np.ascontiguousarray(pts["p"][:64])
+    mo_ref = tree.mo(q, g.profile_rd, g.profile_hdr[:, 1], g.max_error)
+    os.environ["SKC_OCTREE_CAP"] = "1000"
     try:
-        gu.setup_device(d, g)
-        d.set_irradiance_points(pts)
         for levelwise in (False, True):
-            if levelwise:
-                os.environ["SKC_OCTREE_LEVELWISE"] = "1"
+            d = pkg.SkinDevice(0)                                    # a fresh context: no node storage left over from larger scenes
             try:
+                gu.setup_device(d, g)
+                d.set_irradiance_points(pts)
+                if levelwise:
+                    os.environ["SKC_OCTREE_LEVELWISE"] = "1"
                 n_dev, root_dev, _ = d.build_octree()
+                assert n_dev == n_ref
+                assert np.array_equal(root_dev.view(np.uint32), root_ref.view(np.uint32))
+                e = gu.row_rel_err(d.mo(q, g.max_error), mo_ref)
+                assert e.max() < 1e-5, e.max()
             finally:
                 os.environ.pop("SKC_OCTREE_LEVELWISE", None)
-            assert n_dev == n_ref
-            assert np.array_equal(root_dev.view(np.uint32), root_ref.view(np.uint32))
-        q = np.ascontiguousarray(pts["p"][:64])
-        e = gu.row_rel_err(d.mo(q, g.max_error), tree.mo(q, g.profile_rd, g.profile_hdr[:, 1], g.max_error))
-        assert e.max() < 1e-5, e.max()
+                d.close()
     finally:
-        d.close(); tree.close()
+        del os.environ["SKC_OCTREE_CAP"]
+        tree.close()
 
 
 def test_preprocess_one_call_equals_staged_calls(dev, scene):
@@ -549,3 +558,31 @@ def test_device_tessellation_of_a_shard(pkg, dev):
         assert written.sum() < count + 2000 and not written[: first - 1000].any() and not written[first + count + 1000:].any()
     finally:
         hs.close()
+
+
+def test_device_libm_functions_equal_libm_bit_for_bit(dev):
+    """The reference's irradiance and BSDF sampling call libm's float sinf / cosf / logf / expf / atanf, which are not
+    correctly rounded; the device restates glibc's algorithms (csrc/skc_common.cuh; checked exhaustively on the CPU when they
+    were written).  Against the host's libm (the image's glibc, the one the reference was built with), identical bits on
+    samples of the domains the callers use, incl. quadrant / branch boundaries and tiny values."""
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")
+    rng = np.random.default_rng(9)
+    phi = np.concatenate([rng.uniform(0, 2 * np.pi, 180000), np.float32(np.pi / 4) * np.arange(0, 9), rng.uniform(0, 1e-3, 10000),
+                          np.float32(6.2831855) * (rng.random(9991) ** 8), [0.0, 2.0 ** -13, 2.0 ** -12, 6.2831855]])
+    cases = {
+        0: ("sinf", phi), 1: ("cosf", phi),
+        2: ("logf", np.concatenate([rng.random(150000), 1.0 - rng.random(40000) ** 6, rng.random(10000) ** 12 + 1e-30, [1.0, 5.9604645e-08, 0.5]])),
+        3: ("expf", np.concatenate([-rng.uniform(0, 104, 150000), -(rng.random(50000) ** 10) * 1e-2, [0.0, -87.9, -88.0, -103.97, -104.5]])),
+        4: ("atanf", np.concatenate([rng.random(60000) * 3, rng.random(60000) ** 4 * 100, np.exp(rng.uniform(-70, 60, 60000)),
+                                     [0.4375, 0.6875, 1.1875, 2.4375, 0.0, 3.4e38]])),
+    }
+    for fn, (name, x) in cases.items():
+        x = x.astype(np.float32)
+        f = getattr(libm, name); f.restype = ctypes.c_float; f.argtypes = [ctypes.c_float]
+        host = np.array([f(float(v)) for v in x], np.float32)
+        got = dev.test_libmf(fn, x)
+        bad = got.view(np.uint32) != host.view(np.uint32)
+        assert not bad.any(), "%s differs at %d of %d arguments, e.g. x = %r" % (name, bad.sum(), len(x), x[bad][:4])
+    s, c = dev.test_sincosf(phi.astype(np.float32))
+    assert np.array_equal(s.view(np.uint32), dev.test_libmf(0, phi).view(np.uint32)) and np.array_equal(c.view(np.uint32), dev.test_libmf(1, phi).view(np.uint32))

@@ -78,10 +78,10 @@ def test_tissue_preprocess_and_frame(pkg, dev, slab, golden):
         assert np.array_equal(xy[::st].view(np.uint32), z["camera_xy"].view(np.uint32))
         got, ref = L[::st], z["L"]
         lit = ref.max(axis=1) > 0
-        assert np.mean((got.max(axis=1) > 0) == lit) > 0.999
+        assert np.array_equal(got.max(axis=1) > 0, lit)
         e = gu.row_rel_err(got, ref)[lit]
         print("full Li with the transmission lobe: %d lit samples, within 1e-4: %.4f, within 1e-2: %.4f, max %.3g" % (lit.sum(), np.mean(e < 1e-4), np.mean(e < 1e-2), e.max()))
-        assert np.mean(e < 1e-4) > 0.97 and np.mean(e < 1e-2) > 0.995
+        assert e.max() < 1e-5, e.max()
         rgb = hs.film_to_rgb(dev.frame_film())
         _check_image(rgb, z["image"])
     finally:
