@@ -36,6 +36,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "skin.pbrt subsurface hot path: shading points/s (irradiance points + camera samples per second of Preprocess [surface points + irradiance + octree] + Li)"
 UNIT = "shading points/s"
+DATA = "scene file: the reference's own head mesh (scenes/geometry/head.pbrt) in the reconstructed skin.pbrt (SURVEY.md F1/F2); no external dataset, material tables generated at set-up"
 WORKLOAD = "scenes/skin.scene (reconstructed skin.pbrt: head mesh Scale 10, 2 sphere lights x 4 samples, minsampledistance 0.0015, 1280x720x4spp, maxerror 0.1)"
 
 
@@ -105,7 +106,10 @@ def reference_arm(args):
     if not os.path.exists(drv):
         emit({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (oracle/build_ref.sh needs /root/reference)"})
         return
-    sample = os.path.join(ROOT, "scenes", "skin_sample16.scene")
+    # A full-scale step of the reference costs ~2 minutes on 16 cores (octree build ~55 s of it single-threaded, render loop
+    # ~1000 core-seconds), so the timed arm runs a bounded 1/16-scale sample of the same scene; --full-scale times whole
+    # frames of scenes/skin.scene instead (one such step is committed as profiles/r2_reference_full_step.json).
+    sample = os.path.join(ROOT, "scenes", "skin.scene" if args.full_scale else "skin_sample16.scene")
     cores = os.cpu_count() or 1
     out = subprocess.run([drv, "bench", sample, "--ncores", str(cores), "--steps", str(args.steps), "--warmup", str(args.warmup)],
                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, check=True).stdout
@@ -113,12 +117,16 @@ def reference_arm(args):
     units = sum(int(s[3]) + int(s[5]) for s in steps)
     secs = sum(float(s[7]) + float(s[9]) for s in steps)
     value = units / secs
-    desc = ("skin.scene at 1/16 scale (minsampledistance 0.006 -> %s irradiance points, 320x180x4spp -> %s camera samples), "
-            "reference Preprocess + its SamplerRendererTask loop (sampler, camera rays, Scene::Intersect, full Li, film AddSample), %d steps" % (steps[0][3], steps[0][5], len(steps)))
+    what = "reference Preprocess + its SamplerRendererTask loop (sampler, camera rays, Scene::Intersect, full Li, film AddSample), %d steps" % len(steps)
+    if args.full_scale:
+        desc = "skin.scene at FULL scale (%s irradiance points, 1280x720x4spp -> %s camera samples; preprocess %.1f s + render %.1f s per step), %s" % (
+            steps[0][3], steps[0][5], sum(float(s[7]) for s in steps) / len(steps), sum(float(s[9]) for s in steps) / len(steps), what)
+    else:
+        desc = "skin.scene at 1/16 scale (minsampledistance 0.006 -> %s irradiance points, 320x180x4spp -> %s camera samples), %s" % (steps[0][3], steps[0][5], what)
     emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / max(1, len(steps)), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": desc},
+        "dtype": "f32", "data": DATA, "config": {"workload": WORKLOAD, "sample": desc},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
@@ -151,6 +159,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scene", default=os.path.join(ROOT, "scenes", "skin.scene"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--full-scale", action="store_true", help="--impl reference: time whole frames of scenes/skin.scene (minutes per step) instead of the 1/16-scale sample")
     ap.add_argument("--no-prefetch", action="store_true", help="staged flow: sampler stream, closest hits and direct lighting after Preprocess instead of beside it")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -296,37 +305,50 @@ def main():
     exchange_and_build()
     c_cam = dev.camera_pass_resident(r_first, r_count, scene.maxerror, scene.mix, counters=True)
     n_lights = scene.n_lights
-    # algorithmic bytes: irradiance = per point 44 in + 144 out + 12*nLights scramble
-    #   + per shadow ray 32*slab tests + 48*primitive tests ; Mo = per hit 12 in + 128 out + 48 B per node
-    #   classified + 16 B per leaf point tested + (128 B row + 240 B table pairs) per contribution
-    irr_bytes = p_count * (44 + 144 + 12 * n_lights) + 32 * int(c_irr[0]) + 48 * int(c_irr[1])
-    mo_bytes = r_count * (12 + 128) + 48 * int(c_cam[2]) + 16 * int(c_cam[3]) + 368 * (int(c_cam[4]) + int(c_cam[5]))
+    mo_stats = dev.mo_table_stats()
+    mo_kernel = "k_mo_lambda" if mo_stats["rows"] else "k_mo_packet"
+    # ALGORITHMIC bytes, SURVEY.md 8(d): Mo per hit 12 (p in) + 120 (Mo out) + 16 per node visited + 120 per accepted cluster (Et)
+    #   + 136 per contributing leaf point (p, area, E) + 240 per contribution (30 wavelengths x 2 table floats);
+    #   irradiance per point 44 in + 136 out + 12*nLights scramble + per shadow ray 40 + 32 per slab test + 48 per primitive test + 1 out
+    V, leaf_pts, C_int, C_pt = int(c_cam[2]), int(c_cam[3]), int(c_cam[4]), int(c_cam[5])
+    mo_bytes = r_count * (12 + 120) + 16 * V + 120 * C_int + 136 * C_pt + 240 * (C_int + C_pt)
+    irr_bytes = p_count * (44 + 136 + 12 * n_lights) + 41 * int(c_irr[2]) + 32 * int(c_irr[0]) + 48 * int(c_irr[1])
+    # the same in this repo's own layout: 48 B per node visit, 16 B per leaf point tested, 128 B rows,
+    # and 8 B per profile lookup that leaves shared memory (the compact table serves the rest)
+    mo_layout_bytes = r_count * (12 + 128) + 48 * V + 16 * leaf_pts + 128 * (C_int + C_pt) + 8 * (mo_stats["from_global"] if mo_stats["rows"] else int(c_cam[6]))
     peak, peak_kind = measured_peak()
-    dev_sm_count = 148
     dom = "irradiance" if stage_ms["irradiance"] >= stage_ms["mo"] else "mo"
     dom_bytes = irr_bytes if dom == "irradiance" else mo_bytes
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9
-    # DRAM traffic of the dominant kernel per launch, from the committed ncu --set full capture of this same step
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_dram_traffic.json"))).get("k_mo_packet" if dom == "mo" else None)
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "kernel": "k_irr_sample + k_irr_shadow + k_irr_spectral" if dom == "irradiance" else "k_mo_packet", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r1_frame_kernels_full.txt): far below the algorithmic bytes because the octree top, the profile tables and the rows neighbouring samples share are served by L1/L2", "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, sustained copy)",
-                "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": stage_ms[dom],
+    # DRAM traffic of the dominant kernel per launch: from the ncu --set full capture of this same single-GPU step that is
+    # committed under profiles/ (a profiler cannot run inside the timed run); a shard of the launch at N > 1 has no capture: null
+    traffic, traffic_src = None, None
+    if world == 1 and dom == "mo":
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r2_dram_traffic.json")))
+            traffic, traffic_src = tj.get(mo_kernel), tj.get("source")
+        except Exception:
+            pass
+    roofline = {"bound": "hbm", "kernel": "k_irr_sample + k_irr_shadow + k_irr_spectral" if dom == "irradiance" else mo_kernel, "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)" if peak_kind == "measured" else "fallback 6650 GB/s (B200_PROFILING.md)",
+                "algorithmic_bytes_per_launch": dom_bytes, "formula": "SURVEY.md 8(d)", "launch_ms": stage_ms[dom],
+                "note": "algorithmic bytes give no credit for cache reuse: the octree top, rows shared by neighbouring samples and the profile tables (shared memory) never reach DRAM, so achieved/peak describes work rate, not DRAM load",
                 "other": {"k_irradiance": {"GBps": irr_bytes / (stage_ms["irradiance"] * 1e-3) / 1e9, "ms": stage_ms["irradiance"],
                                            "shadow_rays": int(c_irr[2]), "slab_tests": int(c_irr[0]), "prim_tests": int(c_irr[1])},
-                          "k_mo": {"GBps": mo_bytes / (stage_ms["mo"] * 1e-3) / 1e9, "ms": stage_ms["mo"], "nodes": int(c_cam[2]), "leaf_points": int(c_cam[3]),
-                                   "cluster_contribs": int(c_cam[4]), "point_contribs": int(c_cam[5]), "table_reads": int(c_cam[6])}}}
-    if int(c_cam[6]):
-        # what actually bounds Mo: scattered 8 B profile-table reads.  A B200 SM retires one scattered
-        # lane-gather per clock whatever the load path (tools/microbench/gather.cu, measured on this pool: 290 G/s chip-wide)
-        g_peak = 290e9 * (dev_sm_count / 148.0)
-        floor_ms = int(c_cam[6]) / g_peak * 1e3
-        roofline["l1tex_gather"] = {"kernel": "k_mo_packet", "lane_gathers": int(c_cam[6]), "peak_lane_gathers_per_s": g_peak,
-                                    "floor_ms": floor_ms, "frac": floor_ms / stage_ms["mo"]}
+                          "k_mo": {"GBps": mo_bytes / (stage_ms["mo"] * 1e-3) / 1e9, "ms": stage_ms["mo"], "nodes_visited": V, "leaf_points_tested": leaf_pts,
+                                   "cluster_contribs": C_int, "point_contribs": C_pt, "profile_lookups": int(c_cam[6]),
+                                   "layout_bytes_per_launch": mo_layout_bytes, "layout_GBps": mo_layout_bytes / (stage_ms["mo"] * 1e-3) / 1e9,
+                                   "compact_table": mo_stats}}}
+    # Scene::IntersectP / Scene::Intersect alone over the frame's camera rays (untimed extra passes; SURVEY.md 8d asks for both)
+    rays = {"irradiance_pass_shadow_rays_any_hit": int(c_irr[2]) * world / (stage_ms["irradiance"] * 1e-3)}
+    try:
+        dev.trace_resident(0, r_count, any_hit=True); t_any = dev.stage_ms("any")
+        dev.trace_resident(0, r_count, any_hit=False); t_cl = dev.stage_ms("closest")
+        rays["camera_rays_any_hit"] = r_count / (t_any * 1e-3); rays["camera_rays_closest_hit"] = r_count / (t_cl * 1e-3)
+        rays["camera_rays"] = int(r_count)
+    except Exception as ex:       # resident camera rays are a by-product of the frame path; never fatal for the line
+        rays["error"] = str(ex)
 
     # ---- multi-GPU self-check (untimed): the sharded + all-gathered octree must equal the one built
     # from a full local irradiance pass, bit for bit (root p / sumArea / Et) on every rank
@@ -340,11 +362,26 @@ def main():
         same = bool(np.array_equal(root_sharded.view(np.uint32), root_full.view(np.uint32)))
         t = torch.tensor([1 if same else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
         mg_check = "octree root bit-exact vs single-GPU pass on all ranks" if int(t.item()) == 1 else "MISMATCH"
+        # ... and the film: the N films reduced to rank 0 against rank 0 rendering the whole frame alone (same octree)
+        dev.frame_film_clear()
+        dev.frame_render(r_first, r_count, scene.maxerror, scene.mix)
+        dev.synchronize()
+        dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+        torch.cuda.synchronize()
+        if rank == 0:
+            film_n = dev.frame_film().copy()
+            n_all = dev.frame_setup(scene.frame_desc(n_cores=1, rank=0, world=1))
+            dev.frame_samples()
+            dev.frame_film_clear()
+            dev.frame_render(0, n_all, scene.maxerror, scene.mix)
+            film_1 = dev.frame_film()
+            err = float(np.abs(film_n - film_1).max() / np.abs(film_1).max())
+            mg_check += "; film of %d ranks vs single-rank film: max |diff| / max = %.3g (%s)" % (world, err, "ok" if err < 1e-5 else "MISMATCH")
     if rank != 0:
         return
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": DATA,
         "config": {"workload": WORKLOAD, "irradiance_points": n_pts, "camera_samples": n_rays, "irradiance_tasks": n_tasks,
                    "l2": "working set larger than L2 (surface points %.2f GB generated per step, octree + points > 4 GB)" % (n_pts * 44 / 1e9),
                    "camera_sample_pattern": "the reference's LDSampler stream, regenerated on the device every step (render tasks for 1 host core: %d)" % int(scene.frame_desc(1)[12:16].view(np.int32)[0]),
@@ -353,7 +390,7 @@ def main():
         "stage_ms": stage_ms,
         "hot_path_seconds": ms_step * 1e-3,
         # shadow rays of the irradiance pass (+ the camera rays where their closest-hit stage is timed on its own, i.e. --no-prefetch)
-        "rays_per_s": (int(c_irr[2]) * world + (n_rays if stage_ms["closest"] > 0 else 0)) / ((stage_ms["irradiance"] + stage_ms["closest"]) * 1e-3),
+        "rays_per_s": rays,
         "irradiance_points_per_s": n_pts / ((stage_ms["scramble"] + stage_ms["irradiance"]) * 1e-3),
         "mo_points_per_s": n_rays / (stage_ms["mo"] * 1e-3),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
@@ -376,6 +413,10 @@ def main():
                 u = sum(int(s[3]) + int(s[5]) for s in st); sec = sum(float(s[7]) + float(s[9]) for s in st)
                 out["cpu_baseline"] = {"value": u / sec, "unit": UNIT, "cores": cores, "kind": "reference",
                                        "sample": "skin.scene at 1/16 scale (%s points, %s camera samples), reference Preprocess + its SamplerRendererTask loop with the full Li, 2 steps, %.1f s" % (st[0][3], st[0][5], sec)}
+                try:     # one whole frame of the full scene through the reference, measured once on a GPU box's host (committed)
+                    out["cpu_baseline"]["full_scale_step"] = json.load(open(os.path.join(ROOT, "profiles", "r2_reference_full_step.json")))
+                except Exception:
+                    pass
     emit(out)
     dev.close()
     if world > 1:

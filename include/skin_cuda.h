@@ -94,6 +94,8 @@ const char *skc_last_error(const skc_ctx *ctx);   /* ctx may be NULL: last creat
 int skc_synchronize(skc_ctx *ctx);
 /* Counters of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t skc_launch_count(const skc_ctx *ctx);
+/* Streaming multiprocessors of the context's device (launch shapes are multiples of it). */
+int skc_sm_count(const skc_ctx *ctx);
 /* Device time of the last call of each stage in ms (CUDA events on the ctx stream).
  * stage: 0 scramble, 1 irradiance, 2 octree build, 3 closest hit, 4 Mo, 5 any-hit, 6 profile, 7 rho table, 8 tessellation,
  * 9 sampler stream + camera rays, 10 direct lighting, 11 spectral sum + film */

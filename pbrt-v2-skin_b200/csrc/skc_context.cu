@@ -123,6 +123,7 @@ extern "C" int skc_synchronize(skc_ctx *ctx) {
 }
 
 extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
+extern "C" int skc_sm_count(const skc_ctx *ctx) { return ctx ? ctx->smCount : 0; }
 extern "C" float skc_stage_ms(const skc_ctx *ctx, int stage) {
     return (stage >= 0 && stage < SKC_NSTAGES) ? ctx->stageMs[stage] : -1.f;
 }

@@ -24,7 +24,7 @@ STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "a
           "samples": 9, "direct": 10, "film": 11}
 
 # every symbol include/skin_cuda.h declares
-SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_stage_ms",
+SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_sm_count", "skc_stage_ms",
            "skc_upload_bvh", "skc_trace_any", "skc_trace_closest", "skc_upload_profile", "skc_upload_lights",
            "skc_irradiance", "skc_trace_resident", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
            "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
@@ -64,6 +64,7 @@ def load_library():
     lib.skc_last_error.restype = C.c_char_p; lib.skc_last_error.argtypes = [vp]
     lib.skc_synchronize.restype = i32; lib.skc_synchronize.argtypes = [vp]
     lib.skc_launch_count.restype = u64; lib.skc_launch_count.argtypes = [vp]
+    lib.skc_sm_count.restype = i32; lib.skc_sm_count.argtypes = [vp]
     lib.skc_stage_ms.restype = f32; lib.skc_stage_ms.argtypes = [vp, i32]
     lib.skc_upload_bvh.restype = i32
     lib.skc_upload_bvh.argtypes = [vp, vp, u32, vp, u32, vp, vp, vp, u32, vp, u32, vp, i32, i32, vp, u32]
@@ -173,6 +174,9 @@ class SkinDevice:
 
     def launch_count(self):
         return int(self.lib.skc_launch_count(self.ctx))
+
+    def sm_count(self):
+        return int(self.lib.skc_sm_count(self.ctx))
 
     def stage_ms(self, name):
         return float(self.lib.skc_stage_ms(self.ctx, STAGES[name]))
