@@ -176,6 +176,14 @@ int skc_tessellate_resident(skc_ctx *ctx, float minSampleDist, int incenter, uin
 int skc_tessellate_range(skc_ctx *ctx, float minSampleDist, int incenter, uint32_t materialId, uint64_t first, uint64_t count,
                          uint64_t *countOut);
 int skc_get_surface_points(skc_ctx *ctx, uint64_t first, uint64_t count, skc_surface_point *out);
+/* The tessellator's job functions evaluated on the HOST (no context, no GPU): what the host mirror's
+ * TriangleMesh::TessellateSurfacePoints / CountSurfacePoints call, so host and device share ONE implementation (and the CPU
+ * tests that pin the host mirror to the reference's points pin the device kernel's logic too).  Not a fallback: the render
+ * path tessellates with the kernel.  P world-space points, N object-space normals or NULL, UV or NULL, idx [nTris][3],
+ * o2w32 = {ObjectToWorld.m, .mInv} row-major (NULL = identity), flip = ReverseOrientation ^ TransformSwapsHandedness.
+ * out == NULL counts only; returns non-zero when cap is too small or an argument is missing. */
+int skc_tessellate_host(const float *P, const float *N, const float *UV, const int32_t *idx, uint32_t nTris, const float *o2w32, int flip,
+                        float minDist, int incenter, uint32_t materialId, skc_surface_point *out, uint64_t cap, uint64_t *countOut);
 
 /* MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) as ONE call: the irradiance pass over
  * points [first, first+count) and, concurrently on a second stream, the octree topology of ALL nTotal points (it

@@ -42,7 +42,7 @@ __device__ __forceinline__ f3 xformVector(const float *m, f3 v) {
                m[8] * v.x + m[9] * v.y + m[10] * v.z);
 }
 // Transform::operator()(Normal): transpose of the inverse (core/transform.h:232-237)
-__device__ __forceinline__ f3 xformNormal(const float *mInv, f3 n) {
+__host__ __device__ __forceinline__ f3 xformNormal(const float *mInv, f3 n) {
     return mk3(mInv[0] * n.x + mInv[4] * n.y + mInv[8] * n.z,
                mInv[1] * n.x + mInv[5] * n.y + mInv[9] * n.z,
                mInv[2] * n.x + mInv[6] * n.y + mInv[10] * n.z);
@@ -120,7 +120,7 @@ __device__ __forceinline__ bool triIntersect(f3 p1, f3 e1, f3 e2, const DRay &ra
 }
 
 // core/geometry.h:564-574
-__device__ inline void coordinateSystem(f3 v1, f3 *v2, f3 *v3) {
+__host__ __device__ inline void coordinateSystem(f3 v1, f3 *v2, f3 *v3) {
     if (fabsf(v1.x) > fabsf(v1.y)) {
         float invLen = 1.f / sqrtf(v1.x * v1.x + v1.z * v1.z);
         *v2 = mk3(-v1.z * invLen, 0.f, v1.x * invLen);
@@ -131,7 +131,7 @@ __device__ inline void coordinateSystem(f3 v1, f3 *v2, f3 *v3) {
     *v3 = cross3(v1, *v2);
 }
 
-__device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
+__host__ __device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
 
 // Shading point/normal of a triangle hit: trianglemesh.inl:92-133 (dg), :224-299 (shading
 // geometry), core/diffgeom.cpp:40-55 (nn and the orientation flip).
@@ -139,7 +139,7 @@ __device__ __forceinline__ f3 ld3(const float *a, int i) { return mk3(a[3 * i], 
 // (shapes/trianglemesh.inl:303-345) + GetShadingGeometry (:224-299) + diffgeom.cpp:40-55
 // ngOut / ssOut (optional): the geometric normal dgGeom.nn and the shading dpdu that BSDF::BSDF turns into its local frame
 // (core/reflection.cpp:755-762)
-__device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0, float b1, float b2, f3 *nOut, float *tuOut, float *tvOut,
+__host__ __device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, float b0, float b1, float b2, f3 *nOut, float *tuOut, float *tvOut,
                                           f3 *ngOut = nullptr, f3 *ssOut = nullptr) {
     f3 p1 = ld3(mv.P, vi.x), p2 = ld3(mv.P, vi.y), p3 = ld3(mv.P, vi.z);
     f3 e1 = sub3(p2, p1), e2 = sub3(p3, p1);

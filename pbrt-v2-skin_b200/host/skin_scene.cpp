@@ -7,75 +7,92 @@
 
 namespace skin {
 
-// core/transform.cpp:75-133 (Gauss-Jordan, full pivoting) -- same pivot order, same fp32 ops
+// Matrix inverse.  The camera and mesh matrices must equal the reference's bit for bit (camera rays and world-space vertices
+// are compared exactly), and in fp32 that pins the elimination: in-place Gauss-Jordan with FULL pivoting, the pivot of each
+// round being the LAST largest |entry| among rows and columns not used yet, the pivot row scaled by the reciprocal, every other
+// row reduced by (row entry) x (scaled pivot row) -- core/transform.cpp:75-133 performs the same rounds.  Written over a flat
+// array with a used-column mask and the list of pivot moves, which are undone in reverse at the end.
 Mat4 Inverse(const Mat4 &m) {
-    int indxc[4], indxr[4];
-    int ipiv[4] = {0, 0, 0, 0};
-    float minv[4][4];
-    memcpy(minv, m.m, sizeof minv);
-    for (int i = 0; i < 4; i++) {
-        int irow = -1, icol = -1;
-        float big = 0.;
-        for (int j = 0; j < 4; j++) {
-            if (ipiv[j] != 1) {
-                for (int k = 0; k < 4; k++) {
-                    if (ipiv[k] == 0) {
-                        if (fabsf(minv[j][k]) >= big) { big = float(fabsf(minv[j][k])); irow = j; icol = k; }
-                    }
-                }
-            }
+    float a[16];
+    memcpy(a, m.m, sizeof a);
+    auto at = [&a](int r, int c) -> float & { return a[4 * r + c]; };
+    struct Move { int from, to; } moves[4];
+    unsigned pivoted = 0;                                    // bit c: column (= row, after the swap) c holds a finished pivot
+    for (int round = 0; round < 4; ++round) {
+        Move mv = {-1, -1};
+        float largest = 0.f;
+        for (int r = 0; r < 4; ++r) {
+            if (pivoted >> r & 1u) continue;
+            for (int c = 0; c < 4; ++c)
+                if (!(pivoted >> c & 1u) && fabsf(at(r, c)) >= largest) { largest = fabsf(at(r, c)); mv.from = r; mv.to = c; }
         }
-        ++ipiv[icol];
-        if (irow != icol) for (int k = 0; k < 4; ++k) std::swap(minv[irow][k], minv[icol][k]);
-        indxr[i] = irow; indxc[i] = icol;
-        float pivinv = 1.f / minv[icol][icol];
-        minv[icol][icol] = 1.f;
-        for (int j = 0; j < 4; j++) minv[icol][j] *= pivinv;
-        for (int j = 0; j < 4; j++) {
-            if (j != icol) {
-                float save = minv[j][icol];
-                minv[j][icol] = 0;
-                for (int k = 0; k < 4; k++) minv[j][k] -= minv[icol][k] * save;
-            }
+        pivoted |= 1u << mv.to;
+        if (mv.from != mv.to) for (int c = 0; c < 4; ++c) std::swap(at(mv.from, c), at(mv.to, c));
+        moves[round] = mv;
+        const int p = mv.to;
+        const float scale = 1.f / at(p, p);
+        at(p, p) = 1.f;
+        for (int c = 0; c < 4; ++c) at(p, c) *= scale;
+        for (int r = 0; r < 4; ++r) {
+            if (r == p) continue;
+            const float factor = at(r, p);
+            at(r, p) = 0.f;
+            for (int c = 0; c < 4; ++c) at(r, c) -= at(p, c) * factor;
         }
     }
-    for (int j = 3; j >= 0; j--)
-        if (indxr[j] != indxc[j]) for (int k = 0; k < 4; k++) std::swap(minv[k][indxr[j]], minv[k][indxc[j]]);
-    Mat4 r; memcpy(r.m, minv, sizeof minv);
-    return r;
+    for (int round = 3; round >= 0; --round)
+        if (moves[round].from != moves[round].to) for (int r = 0; r < 4; ++r) std::swap(at(r, moves[round].from), at(r, moves[round].to));
+    Mat4 out;
+    memcpy(out.m, a, sizeof a);
+    return out;
 }
 
-Transform Translate(V3 d) {
-    return Transform(Mat4(1, 0, 0, d.x, 0, 1, 0, d.y, 0, 0, 1, d.z, 0, 0, 0, 1), Mat4(1, 0, 0, -d.x, 0, 1, 0, -d.y, 0, 0, 1, -d.z, 0, 0, 0, 1));
+// scale on the diagonal, offset in the last column
+static Mat4 scaleOffset(float sx, float sy, float sz, V3 t) {
+    Mat4 r;
+    r.m[0][0] = sx; r.m[1][1] = sy; r.m[2][2] = sz;
+    r.m[0][3] = t.x; r.m[1][3] = t.y; r.m[2][3] = t.z;
+    return r;
 }
-Transform Scale(float x, float y, float z) {
-    return Transform(Mat4(x, 0, 0, 0, 0, y, 0, 0, 0, 0, z, 0, 0, 0, 0, 1), Mat4(1.f / x, 0, 0, 0, 0, 1.f / y, 0, 0, 0, 0, 1.f / z, 0, 0, 0, 0, 1));
+Transform Translate(V3 d) { return Transform(scaleOffset(1, 1, 1, d), scaleOffset(1, 1, 1, V3(-d.x, -d.y, -d.z))); }
+Transform Scale(float x, float y, float z) { return Transform(scaleOffset(x, y, z, V3(0, 0, 0)), scaleOffset(1.f / x, 1.f / y, 1.f / z, V3(0, 0, 0))); }
+// Rotation by `angle` degrees about `axis` (core/transform.cpp:213-241): u u^T (1 - cos) + cos on the diagonal, -/+ the third
+// axis component times sin off it; the inverse is the transpose.
+Transform Rotate(float angle, V3 axis) {
+    const V3 unit = Normalize(axis);
+    const float u[3] = {unit.x, unit.y, unit.z};
+    const float sine = sinf(Radians(angle)), cosine = cosf(Radians(angle));
+    Mat4 r;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            if (i == j) { r.m[i][i] = u[i] * u[i] + (1.f - u[i] * u[i]) * cosine; continue; }
+            const int lo = i < j ? i : j, hi = i < j ? j : i, third = 3 - i - j;
+            const float sym = u[lo] * u[hi] * (1.f - cosine), skew = u[third] * sine;
+            r.m[i][j] = (j - i + 3) % 3 == 1 ? sym - skew : sym + skew;
+        }
+    return Transform(r, Transpose(r));
 }
-Transform Rotate(float angle, V3 axis) {   // transform.cpp:213-241
-    V3 a = Normalize(axis);
-    float s = sinf(Radians(angle)), c = cosf(Radians(angle));
-    Mat4 m;
-    m.m[0][0] = a.x * a.x + (1.f - a.x * a.x) * c; m.m[0][1] = a.x * a.y * (1.f - c) - a.z * s; m.m[0][2] = a.x * a.z * (1.f - c) + a.y * s; m.m[0][3] = 0;
-    m.m[1][0] = a.x * a.y * (1.f - c) + a.z * s; m.m[1][1] = a.y * a.y + (1.f - a.y * a.y) * c; m.m[1][2] = a.y * a.z * (1.f - c) - a.x * s; m.m[1][3] = 0;
-    m.m[2][0] = a.x * a.z * (1.f - c) - a.y * s; m.m[2][1] = a.y * a.z * (1.f - c) + a.x * s; m.m[2][2] = a.z * a.z + (1.f - a.z * a.z) * c; m.m[2][3] = 0;
-    m.m[3][0] = 0; m.m[3][1] = 0; m.m[3][2] = 0; m.m[3][3] = 1;
-    return Transform(m, Transpose(m));
+// Camera-to-world frame from an eye point, a target and an up hint (core/transform.cpp:244-265): columns = left, up', view
+// direction, eye; the Transform returned is world-to-camera, i.e. (inverse, frame).
+Transform LookAt(V3 pos, V3 look, V3 up) {
+    const V3 view = Normalize(look - pos);
+    const V3 left = Normalize(Cross(Normalize(up), view));
+    const V3 upOrtho = Cross(view, left);
+    const V3 col[4] = {left, upOrtho, view, pos};
+    Mat4 frame;
+    for (int c = 0; c < 4; ++c) {
+        frame.m[0][c] = col[c].x; frame.m[1][c] = col[c].y; frame.m[2][c] = col[c].z;
+        frame.m[3][c] = c == 3 ? 1.f : 0.f;
+    }
+    return Transform(Inverse(frame), frame);
 }
-Transform LookAt(V3 pos, V3 look, V3 up) {   // transform.cpp:244-265
-    Mat4 m;
-    m.m[0][3] = pos.x; m.m[1][3] = pos.y; m.m[2][3] = pos.z; m.m[3][3] = 1;
-    V3 dir = Normalize(look - pos);
-    V3 left = Normalize(Cross(Normalize(up), dir));
-    V3 newUp = Cross(dir, left);
-    m.m[0][0] = left.x; m.m[1][0] = left.y; m.m[2][0] = left.z; m.m[3][0] = 0.;
-    m.m[0][1] = newUp.x; m.m[1][1] = newUp.y; m.m[2][1] = newUp.z; m.m[3][1] = 0.;
-    m.m[0][2] = dir.x; m.m[1][2] = dir.y; m.m[2][2] = dir.z; m.m[3][2] = 0.;
-    return Transform(Inverse(m), m);
-}
-Transform Perspective(float fov, float n, float f) {   // transform.cpp:309-319
-    Mat4 persp(1, 0, 0, 0, 0, 1, 0, 0, 0, 0, f / (f - n), -f * n / (f - n), 0, 0, 1, 0);
-    float invTanAng = 1.f / tanf(Radians(fov) / 2.f);
-    return Scale(invTanAng, invTanAng, 1) * Transform(persp);
+// Perspective projection onto z in [0, 1] between the planes n and f, x/y scaled by cot(fov / 2) (core/transform.cpp:309-319)
+Transform Perspective(float fov, float n, float f) {
+    Mat4 proj;                                               // identity, then the two rows that matter
+    proj.m[2][2] = f / (f - n); proj.m[2][3] = -f * n / (f - n);
+    proj.m[3][2] = 1.f;         proj.m[3][3] = 0.f;
+    const float cot = 1.f / tanf(Radians(fov) / 2.f);
+    return Scale(cot, cot, 1) * Transform(proj);
 }
 
 // core/camera.cpp:83-102, cameras/perspective.cpp:124-155

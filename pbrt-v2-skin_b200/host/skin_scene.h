@@ -2,7 +2,8 @@
 //
 //   Scene description  -> what core/api.cpp builds from `pbrt scene.pbrt` for the skin scenes
 //   TriangleMesh       -> shapes/trianglemesh.{h,cpp}: world-space vertices + the tessellator
-//   BVHAccel           -> accelerators/bvh.{h,cpp}: SAH build, flat LinearBVHNode array
+//   BVHAccel           -> accelerators/bvh.{h,cpp}: the same flat LinearBVHNode array and leaf order, built by an iterative
+//                         builder of this repo's own (host/skin_geom.cpp)
 //   PerspectiveCamera  -> cameras/perspective.cpp
 //   MultipoleSubsurfaceIntegrator -> integrators/multipolesubsurface.{h,cpp}: Preprocess / Li,
 //                         both running on the device through include/skin_cuda.h
@@ -122,13 +123,8 @@ public:
     std::vector<skc_bvh_node> nodes;          // depth-first flat tree (bvh.cpp:362-380)
     std::vector<uint32_t> orderedPrims;       // primitive numbers in leaf order
 private:
-    struct BuildNode;
-    struct PrimInfo { uint32_t primitiveNumber; V3 centroid; BBox bounds; };
-    BuildNode *recursiveBuild(std::vector<PrimInfo> &buildData, uint32_t start, uint32_t end, uint32_t *totalNodes);
-    uint32_t flatten(BuildNode *node, uint32_t *offset);
     uint32_t maxPrimsInNode;
-    int splitMethod;
-    std::vector<BuildNode *> arena;
+    int splitMethod;                          // 0 middle, 1 equal counts, 2 surface-area heuristic
 };
 
 // cameras/perspective.cpp + core/camera.cpp:83-102

@@ -31,7 +31,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",
-           "skc_tessellate_resident", "skc_tessellate_range", "skc_get_surface_points",
+           "skc_tessellate_resident", "skc_tessellate_host", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
            "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
