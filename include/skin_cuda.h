@@ -272,6 +272,12 @@ int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, const uint32_t 
                       const skc_mpc_options *opts, uint32_t nSets, int resample,
                       uint32_t *lenOut, float *d2, float *R, float *T, float *totals);
 
+/* `resample` of the profile calculator (MultipoleProfileCalculator.cpp:355-402) at arbitrary squared distances: what
+ * MPC_ResampleForUniformDistanceSquaredDistribution (:404-426) with any target length and MPC_ResampleDistribution (:428-448)
+ * both reduce to.  d2 / R / T [len] host arrays of one profile (d2 ascending), queryDsq [nQueries]; Rout / Tout [nQueries]. */
+int skc_profile_resample(skc_ctx *ctx, const float *d2, const float *R, const float *T, uint32_t len,
+                         const float *queryDsq, uint32_t nQueries, float *Rout, float *Tout);
+
 /* ---- rho_hd table ------------------------------------------------
  * Replaces ComputeRhoDataFromBxDF (core/multipole.cpp:518-549) for the Microfacet(Beckmann(roughness),
  * FresnelDielectric(etaI, etaT)) lobe LayeredSkin builds (materials/layeredskin.cpp:103-109):

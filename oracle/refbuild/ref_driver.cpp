@@ -692,7 +692,16 @@ static int runMPC(int argc, char **argv) {
         double t0 = now_s();
         MPC_Output *o = NULL;
         MPC_ComputeDiffusionProfile(nLayers, specs.data(), &opt, &o);
-        if (resample) MPC_ResampleForUniformDistanceSquaredDistribution(o);
+        // resample: 0 raw, 1 MPC_ResampleForUniformDistanceSquaredDistribution (default target), 3 the same with target length 1000,
+        // 2 MPC_ResampleDistribution at 777 radii r_i = i * 1.05 * sqrt(extent) / 776 (the last ones lie beyond the table: zeros)
+        if (resample == 1) MPC_ResampleForUniformDistanceSquaredDistribution(o);
+        else if (resample == 3) MPC_ResampleForUniformDistanceSquaredDistribution(o, 1000);
+        else if (resample == 2) {
+            std::vector<float> r(777);
+            float rmax = 1.05f * sqrtf(o->pDistanceSquared[o->length - 1]);
+            for (int i = 0; i < 777; ++i) r[i] = (float)i * rmax / 776.f;
+            MPC_ResampleDistribution(o, 777, r.data());
+        }
         total += now_s() - t0;
         uint32_t len = o->length;
         fwrite(&len, 4, 1, out);

@@ -574,3 +574,50 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     if (rc || e != cudaSuccess) return skc_fail(ctx, "skc_profile_batch: %s", ctx->err.empty() ? cudaGetErrorString(e) : ctx->err.c_str());
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// resample (MultipoleProfileCalculator.cpp:355-402) at arbitrary query points: what both MPC_ResampleForUniformDistanceSquared-
+// Distribution (:404-426, any target length) and MPC_ResampleDistribution (:428-448) reduce to.  One thread per query: first
+// entry with d2 >= query (the reference's interpolation + linear search finds the same entry; d2 is strictly increasing), fp32
+// lerp with the reference's clamp and NaN rule, 0 beyond the table.
+__global__ void k_resample_at(const float *__restrict__ d2, const float *__restrict__ R, const float *__restrict__ T, uint32_t len,
+                              const float *__restrict__ q, uint32_t nq, float *__restrict__ oR, float *__restrict__ oT) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const float dsq = q[i], extent = d2[len - 1];
+    float r, t;
+    if (dsq > extent) { r = t = 0.f; }
+    else {
+        uint32_t lo = 0, hi = len - 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (dsq > d2[mid]) lo = mid + 1; else hi = mid; }
+        if (lo) {
+            float la = (dsq - d2[lo - 1]) / (d2[lo] - d2[lo - 1]);
+            la = la < 0.f ? 0.f : (la > 1.f ? 1.f : la);
+            if (la != la) la = 0.5f;
+            r = (1.f - la) * R[lo - 1] + la * R[lo];
+            t = (1.f - la) * T[lo - 1] + la * T[lo];
+        } else { r = R[0]; t = T[0]; }
+    }
+    oR[i] = r; oT[i] = t;
+}
+
+extern "C" int skc_profile_resample(skc_ctx *ctx, const float *d2, const float *R, const float *T, uint32_t len,
+                                    const float *queryDsq, uint32_t nQueries, float *Rout, float *Tout) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!nQueries) return 0;
+    if (!len || !d2 || !R || !T || !queryDsq || !Rout || !Tout) return skc_fail(ctx, "skc_profile_resample: empty table or null argument");
+    float *buf = (float *)skc_scratch(ctx, 0, ((size_t)3 * len + (size_t)3 * nQueries) * sizeof(float));
+    if (!buf) return 1;
+    float *dD = buf, *dR = dD + len, *dT = dR + len, *dQ = dT + len, *dOR = dQ + nQueries, *dOT = dOR + nQueries;
+    SKC_CUDA(cudaMemcpyAsync(dD, d2, len * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(dR, R, len * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(dT, T, len * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(dQ, queryDsq, nQueries * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_resample_at<<<(nQueries + 255) / 256, 256, 0, ctx->stream>>>(dD, dR, dT, len, dQ, nQueries, dOR, dOT);
+    SKC_LAUNCHED("k_resample_at");
+    SKC_CUDA(cudaMemcpyAsync(Rout, dOR, nQueries * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(Tout, dOT, nQueries * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}

@@ -27,7 +27,7 @@ STAGES = {"scramble": 0, "irradiance": 1, "octree": 2, "closest": 3, "mo": 4, "a
 SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "skc_launch_count", "skc_sm_count", "skc_stage_ms",
            "skc_upload_bvh", "skc_trace_any", "skc_trace_closest", "skc_upload_profile", "skc_upload_lights",
            "skc_irradiance", "skc_trace_resident", "skc_set_irradiance_points", "skc_irradiance_dev", "skc_build_octree", "skc_mo",
-           "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_set_surface_points", "skc_irradiance_resident",
+           "skc_li_sss", "skc_camera_pass", "skc_profile_batch", "skc_profile_resample", "skc_set_surface_points", "skc_irradiance_resident",
            "skc_set_camera_rays", "skc_camera_pass_resident", "skc_alloc_pinned", "skc_free_pinned",
            "skc_timer_begin", "skc_timer_end_ms", "skc_set_point_count", "skc_rho_table",
            "skc_build_octree_topology", "skc_build_octree_finalize", "skc_preprocess", "skc_preprocess_resident",

@@ -19,6 +19,7 @@ and packs the exported streams into compressed .npz files:
                   src/multipole/test/test.cpp:84-116 (+ thin-slab cases), raw and resampled
 
   skin_full.npz   scenes/skin.scene at FULL size (the benchmarked configuration): image, strided points / samples / tables
+  mpc_api.npz     the MPC_* API's resample variants (default / explicit target length, arbitrary radii)
   mpc_kat512.npz  four two-layer thin-slab sets at desiredLength 512 (strided tables + both ends)
 
 Only this script and the fixtures are committed; nothing at test time reads /root/reference.
@@ -256,6 +257,39 @@ C5_EPI_MFP = 1.0 / (0.268088 + 19.4879)
 MPC512_CASES = [(2, 512, 1, 1, 0.0, [(1.4, t * C5_EPI_MFP, 0.268088, 19.4879), (1.4, 2.0, 0.268088, 9.74395)]) for t in (0.02, 0.5, 1.2, 2.0)]
 
 
+# The MPC_* DLL API as its three call sites use it (core/multipole.cpp:268-291, renderers/mcprofile.cpp:402-423,
+# renderers/profilefit.cpp:190-196): default-target and explicit-target uniform resampling, and MPC_ResampleDistribution at
+# arbitrary radii (ref_driver mpc resample codes 1, 3, 2).
+MPC_API_CASES = [
+    (2, 64, 1, 1, 0.0, [EPI, DERM]),
+    (2, 64, 1, 3, 0.0, [EPI, DERM]),
+    (2, 64, 1, 2, 0.0, [EPI, DERM]),
+    (1, 128, 0, 2, 0.0, [DERM]),
+    (3, 64, 1, 0, 0.0, [(1.4, 0.01, 0.5, 30.0), (1.45, 0.1, 0.3, 15.0), (1.35, 3.0, 0.05, 8.0)]),
+]
+
+
+def mpc_api_golden():
+    with tempfile.TemporaryDirectory() as d:
+        inp, outp = os.path.join(d, "in.txt"), os.path.join(d, "out.bin")
+        with open(inp, "w") as f:
+            for nl, dl, lerp, res, step, layers in MPC_API_CASES:
+                f.write("%d %d %d %d %r " % (nl, dl, lerp, res, step) + " ".join("%r %r %r %r" % l for l in layers) + "\n")
+        subprocess.run([DRIVER, "mpc", inp, outp], check=True, stdout=subprocess.DEVNULL)
+        blob = open(outp, "rb").read()
+    arrays, off = {}, 0
+    for i, case in enumerate(MPC_API_CASES):
+        ln = int(np.frombuffer(blob, np.uint32, 1, off)[0]); off += 4
+        tot = np.frombuffer(blob, np.float32, 2, off); off += 8
+        body = np.frombuffer(blob, np.float32, 3 * ln, off).reshape(3, ln); off += 12 * ln
+        arrays["case%d_spec" % i] = np.array([case[0], case[1], case[2], case[3], case[4]] + [x for l in case[5] for x in l], np.float64)
+        arrays["case%d_totals" % i] = tot.copy()
+        arrays["case%d_d2_R_T" % i] = body.copy()
+    path = os.path.join(OUT, "mpc_api.npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB")
+
+
 def mpc512_golden():
     with tempfile.TemporaryDirectory() as d:
         inp, outp = os.path.join(d, "in.txt"), os.path.join(d, "out.bin")
@@ -283,4 +317,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)
