@@ -13,8 +13,9 @@ e2e     = the same from HOST buffers: the scene (BVH nodes, primitives, mesh, li
           every step, the film comes back to the host and is converted to RGB there (ImageFilm::WriteImage's
           arithmetic) -- what `pbrt scene.pbrt` does per frame after parsing
 N > 1   = points sharded over ranks, in-place NCCL all-gather of the irradiance set, replicated octree build,
-          render tasks (tiles) dealt round-robin over the ranks, film reduced (sum) to rank 0 over NCCL
-          (strong scaling: the scene is fixed).
+          render tasks (tiles) dealt round-robin over the ranks, film reduced (sum) to rank 0 over NCCL -- both
+          collectives are C-ABI calls into libskincuda.so (skc_comm_*); torch.distributed (gloo) only carries the
+          communicator id at start-up (strong scaling: the scene is fixed).
 
 `--impl reference` times the reference's own CPU code (oracle/_ref/ref_driver bench: Preprocess + its
 SamplerRendererTask loop with the full Li) on a bounded sample of the same scene (1/16 of the points and of the
@@ -168,14 +169,15 @@ def main():
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     import __graft_entry__ as ge
     pkg = ge.load_package()
-    dist = None
+    dist = comm = None
     if world > 1:
-        import torch
+        # the launcher's rendezvous (torchrun env) on a CPU backend: it carries the 128-byte NCCL id of rank 0 to the other ranks
+        # and nothing else -- every exchange of the data path is an NCCL call inside libskincuda.so (csrc/skc_comm.cu)
         import torch.distributed as dist
-        torch.cuda.set_device(local)
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("gloo")
     dev = pkg.SkinDevice(local)
+    if world > 1:
+        comm = pkg.SkinComm(dev, rank, world, pkg.exchange_unique_id(dist, rank, pkg.SkinComm.unique_id))
 
     # ---- workload (host side, untimed): scene, BVH, surface points, camera rays, tables
     scene = pkg.HostScene(args.scene)
@@ -189,37 +191,25 @@ def main():
     r_count = dev.frame_setup(scene.frame_desc(n_cores=1, rank=rank, world=world))
     r_first = 0
     n_rays = r_count
-    pos_t = e_t = film_t = None
     if world > 1:
+        dev.irradiance_dev(shard * world)          # the point arrays sized for the padded exchange
         import torch
-        pa_ptr, e_ptr = dev.irradiance_dev(shard * world)
-
-        class _Wrap:
-            def __init__(self, ptr, shape):
-                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 3}
-        pos_t = torch.as_tensor(_Wrap(pa_ptr, (shard * world, 4)), device="cuda")
-        e_t = torch.as_tensor(_Wrap(e_ptr, (shard * world, 32)), device="cuda")
-        film_t = torch.as_tensor(_Wrap(dev.frame_film_dev(), (scene.yres * scene.xres, 4)), device="cuda")
-        t = torch.tensor([r_count], device="cuda", dtype=torch.int64); dist.all_reduce(t); n_rays = int(t.item())
+        t = torch.tensor([r_count], dtype=torch.int64); dist.all_reduce(t); n_rays = int(t.item())      # (a count for the report)
 
     def exchange_and_build():
-        """Irradiance exchange + octree.  N > 1: in-place NCCL all-gather of the shards; the positions (16 B/point) go
-        first, then the irradiance rows (128 B/point) travel while every rank already builds the octree topology
-        from the positions; the finalize pass (leaf gather + InitHierarchy) waits for the rows."""
+        """Irradiance exchange + octree.  N > 1: in-place ncclAllGather of the shards; the positions (16 B/point) go first on the
+        main stream, then the irradiance rows (128 B/point) travel on the copy stream while every rank already builds the octree
+        topology from the positions; the finalize pass (leaf gather + InitHierarchy) waits for the rows on the device."""
         if world == 1:
             dev.build_octree()
             return
-        import torch
-        dev.synchronize()
-        pkg.allgather_inplace(dist, pos_t, rank, shard)
-        work = pkg.allgather_inplace_async(dist, e_t, rank, shard)
-        torch.cuda.current_stream().synchronize()          # positions are in
+        comm.allgather_positions(shard)
+        comm.allgather_rows_begin(shard)
         # padded tail (only when n_pts % world != 0): shards are contiguous and only the LAST one is short,
         # so the valid points are exactly [0, n_pts)
         dev.set_point_count(n_pts)
         dev.build_octree_topology()
-        work.wait()
-        torch.cuda.synchronize()
+        comm.allgather_rows_wait()
         dev.build_octree_finalize()
 
     def step_resident():
@@ -236,10 +226,7 @@ def main():
         dev.frame_film_clear()
         dev.frame_render(r_first, r_count, scene.maxerror, scene.mix)
         if world > 1:
-            import torch
-            dev.synchronize()
-            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
-            torch.cuda.current_stream().synchronize()
+            comm.reduce_film(0)
 
     h2d_bytes = sum(a.nbytes for a in (scene.nodes, scene.prims, scene.P, scene.idx, scene.lights, scene.lights) if a is not None) \
         + sum(a.nbytes for a in (scene.N, scene.uv) if a is not None)
@@ -254,10 +241,9 @@ def main():
             e2e_image["rgb"] = dev.frame_rgb(out=rgb_host)      # ImageFilm::WriteImage's pixel arithmetic on the device, RGB image to the host
 
     def barrier():
-        if world > 1:
-            import torch
-            dist.barrier(); torch.cuda.synchronize()
         dev.synchronize()
+        if world > 1:
+            comm.barrier()
 
     def timed(fn, k):
         barrier()
@@ -266,10 +252,7 @@ def main():
             fn()
         ms = dev.timer_end_ms()
         barrier()
-        if world > 1:
-            import torch
-            t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
-        return ms
+        return comm.max_f32(ms) if world > 1 else ms
 
     for _ in range(args.warmup):
         step_resident()
@@ -287,8 +270,7 @@ def main():
     barrier()
     launches = dev.launch_count() - launches0
     if world > 1:
-        import torch
-        t = torch.tensor([ms_total], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms_total = float(t.item())
+        ms_total = comm.max_f32(ms_total)
     for _ in range(min(2, args.warmup)):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
@@ -360,14 +342,13 @@ def main():
         dev.set_point_count(n_pts)
         _, root_full, _ = dev.build_octree()
         same = bool(np.array_equal(root_sharded.view(np.uint32), root_full.view(np.uint32)))
-        t = torch.tensor([1 if same else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        t = torch.tensor([1 if same else 0]); dist.all_reduce(t, op=dist.ReduceOp.MIN)
         mg_check = "octree root bit-exact vs single-GPU pass on all ranks" if int(t.item()) == 1 else "MISMATCH"
         # ... and the film: the N films reduced to rank 0 against rank 0 rendering the whole frame alone (same octree)
         dev.frame_film_clear()
         dev.frame_render(r_first, r_count, scene.maxerror, scene.mix)
+        comm.reduce_film(0)
         dev.synchronize()
-        dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
-        torch.cuda.synchronize()
         if rank == 0:
             film_n = dev.frame_film().copy()
             n_all = dev.frame_setup(scene.frame_desc(n_cores=1, rank=0, world=1))
@@ -376,7 +357,8 @@ def main():
             dev.frame_render(0, n_all, scene.maxerror, scene.mix)
             film_1 = dev.frame_film()
             err = float(np.abs(film_n - film_1).max() / np.abs(film_1).max())
-            mg_check += "; film of %d ranks vs single-rank film: max |diff| / max = %.3g (%s)" % (world, err, "ok" if err < 1e-5 else "MISMATCH")
+            mg_check += "; film of %d ranks (ncclReduce) vs single-rank film: max |diff| / max = %.3g (%s)" % (world, err, "ok" if err < 1e-5 else "MISMATCH")
+        comm.barrier()
     if rank != 0:
         return
     out = {
@@ -418,6 +400,8 @@ def main():
                 except Exception:
                     pass
     emit(out)
+    if comm:
+        comm.close()
     dev.close()
     if world > 1:
         dist.destroy_process_group()

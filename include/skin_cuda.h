@@ -342,6 +342,37 @@ int skc_frame_film_get(skc_ctx *ctx, float *pixels4);
  * clamped at 0; rgb3 = [yres][xres][3] on the host. */
 int skc_frame_film_rgb(skc_ctx *ctx, float *rgb3);
 
+/* ---- several GPUs (no counterpart in the single-process reference, core/parallel.cpp:722-748) ----------------
+ * The path shards in two places and each has one exchange step, both NCCL collectives over NVLink inside this library:
+ *   irradiance points  every rank computes a contiguous range (skc_tessellate_range + skc_irradiance_resident(first, count)) of
+ *                      arrays sized for world x shard points; ncclAllGather in place; every rank then builds the same octree
+ *   camera tiles       every rank renders its render tasks (skc_frame_desc.taskRank / taskWorld) into its own film; ncclReduce
+ *                      (sum) to the root, because the reconstruction filter spreads samples across tile borders
+ * One communicator per context.  Bootstrap: one process per GPU -- rank 0 calls skc_comm_unique_id, the 128 bytes reach the
+ * other ranks by whatever the launcher offers, every rank calls skc_comm_create; or one process with several contexts --
+ * skc_comm_create_local, then one host thread per context.  All calls are enqueued on the context's streams. */
+typedef struct skc_comm skc_comm;
+int skc_comm_unique_id(uint8_t *id128);
+skc_comm *skc_comm_create(skc_ctx *ctx, int rank, int world, const uint8_t *id128);
+int skc_comm_create_local(skc_ctx **ctxs, int n, skc_comm **comms);
+void skc_comm_destroy(skc_comm *comm);
+int skc_comm_rank(const skc_comm *comm);
+int skc_comm_world(const skc_comm *comm);
+/* {p, area} of all shards, in place, on the main stream (the octree topology pass that follows needs only these). */
+int skc_comm_allgather_positions(skc_comm *comm, uint64_t shardPoints);
+/* Irradiance rows of all shards (8x the bytes), in place, on the copy stream behind the work enqueued so far; returns at once.
+ * skc_comm_allgather_rows_wait makes the main stream wait for them on the device -- call it before skc_build_octree_finalize. */
+int skc_comm_allgather_rows_begin(skc_comm *comm, uint64_t shardPoints);
+int skc_comm_allgather_rows_wait(skc_comm *comm);
+/* Sum of all ranks' films into the root's, on the main stream after the rank's skc_frame_render. */
+int skc_comm_reduce_film(skc_comm *comm, int root);
+/* max over ranks of a host float (device timings are reported as the max over ranks); a barrier of the main streams. */
+int skc_comm_max_f32(skc_comm *comm, float *value);
+int skc_comm_barrier(skc_comm *comm);
+/* bytesPerRank host bytes from every rank to every rank (buf holds world x bytesPerRank; rank r's block at r x bytesPerRank):
+ * material tables computed wavelength by wavelength across the ranks. */
+int skc_comm_allgather_host(skc_comm *comm, void *buf, uint64_t bytesPerRank);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,6 +14,6 @@ is libskincuda.so (csrc/*.cu, sm_100a) and the C++ host mirror of the reference'
 interfaces (host/).  There is no CPU fallback: every entry point raises if the library or a
 GPU is missing.
 """
-from .skc import SkinDevice, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
+from .skc import SkinDevice, SkinComm, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
 from .host_api import HostScene, load_host_library, skin_spectra, pbrt_render  # noqa: F401
-from .sharding import shard_range, tile_round_robin, allgather_inplace, allgather_inplace_async  # noqa: F401
+from .multigpu import shard_range, exchange_unique_id  # noqa: F401

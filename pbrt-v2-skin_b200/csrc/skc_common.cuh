@@ -107,8 +107,8 @@ struct skc_ctx {
     uint64_t resRaysCount = 0;
 
     // --- scratch
-    void *scratch[20] = {nullptr};     // 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently), 11 tessellation, 12-15 frame, 16 Mo hit sort
-    size_t scratchBytes[20] = {0};
+    void *scratch[24] = {nullptr};     // 20 skc_comm host all-gather; 0-7 irradiance / camera pass, 8-10 octree build (the two may run concurrently), 11 tessellation, 12-15 frame, 16 Mo hit sort
+    size_t scratchBytes[24] = {0};
 
     // --- whole-frame state (skc_frame.cu)
     struct skc_frame_state *frame = nullptr;

@@ -97,7 +97,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
                     ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
-    for (int i = 0; i < 20; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (int i = 0; i < 24; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     if (ctx->timer0) { cudaEventDestroy(ctx->timer0); cudaEventDestroy(ctx->timer1); }
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);

@@ -822,6 +822,12 @@ extern "C" int skc_frame_film_clear(skc_ctx *ctx) {
     return 0;
 }
 extern "C" void *skc_frame_film_dev(skc_ctx *ctx) { return ctx && ctx->frame ? ctx->frame->dFilm : nullptr; }
+// the film as floats, for the reduce of skc_comm.cu
+void *skc_frame_film_floats(skc_ctx *ctx, uint64_t *floats) {
+    if (!ctx || !ctx->frame || !ctx->frame->dFilm) return nullptr;
+    *floats = (uint64_t)ctx->frame->desc.xres * ctx->frame->desc.yres * 4;
+    return ctx->frame->dFilm;
+}
 extern "C" int skc_frame_film_get(skc_ctx *ctx, float *pixels4) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);

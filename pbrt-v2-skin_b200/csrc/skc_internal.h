@@ -13,3 +13,5 @@ int skc_ensure_points(skc_ctx *ctx, uint64_t n);
 int skc_octree_topology_sorted(skc_ctx *ctx, uint32_t n, const float *hb, uint32_t cap, std::vector<uint32_t> &levelStart, uint32_t *totalOut);
 // fused Mo + Li subsurface term for device hits: L rows [n][30] into dL (skc_mo.cu)
 int skc_li_fused_dev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, float *dL);
+// device film {Lxyz, weightSum} per pixel as a flat float array (skc_frame.cu), nullptr before skc_frame_setup
+void *skc_frame_film_floats(skc_ctx *ctx, uint64_t *floats);

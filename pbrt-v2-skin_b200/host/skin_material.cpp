@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include "skin_material.h"
+#include <cstring>
 #include "skin_tables.h"
 
 namespace skin {
@@ -102,25 +103,58 @@ void BuildProfileJobs(const SkinLayerSpectra &s, int desiredLength, bool lerpOnT
 }
 
 int ComputeMultipoleProfile(skc_ctx *ctx, const SkinLayerSpectra &s, int desiredLength, bool lerpOnThinSlab,
-                            ProfileTable &out) {
+                            ProfileTable &out, skc_comm *comm) {
     std::vector<skc_layer_spec> specs;
     std::vector<uint32_t> lps;
     std::vector<skc_mpc_options> opts;
     BuildProfileJobs(s, desiredLength, lerpOnThinSlab, specs, lps, opts);
-    uint32_t len = 0;
-    int rc = skc_profile_batch(ctx, specs.data(), lps.data(), opts.data(), kWavelengths, 1, &len, nullptr, nullptr, nullptr, nullptr);
+    // Several GPUs (first row): the wavelengths are independent, so rank r computes wavelengths r, r + world, ...
+    // and the finished tables (+ the last d2 and the totals of each) are all-gathered; a rank's block holds `per` table slots.
+    const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
+    const int per = (kWavelengths + world - 1) / world;
+    std::vector<skc_layer_spec> mySpecs;
+    std::vector<uint32_t> myLps;
+    std::vector<skc_mpc_options> myOpts;
+    std::vector<int> mine;
+    {
+        size_t at = 0;
+        for (int w = 0; w < kWavelengths; ++w) {
+            if (w % world == rank) {
+                mine.push_back(w);
+                mySpecs.insert(mySpecs.end(), specs.begin() + at, specs.begin() + at + lps[w]);
+                myLps.push_back(lps[w]); myOpts.push_back(opts[w]);
+            }
+            at += lps[w];
+        }
+    }
+    uint32_t len = 0;      // the same for every wavelength: it depends on desiredLength only
+    int rc = skc_profile_batch(ctx, specs.data(), lps.data(), opts.data(), 1, 1, &len, nullptr, nullptr, nullptr, nullptr);
     if (rc) return rc;
-    std::vector<float> d2((size_t)kWavelengths * len), totals(2 * kWavelengths);
+    const size_t slot = (size_t)len + 3;                              // table, last d2, total R, total T
+    std::vector<float> blocks((size_t)world * per * slot, 0.f);
+    float *myBlock = blocks.data() + (size_t)rank * per * slot;
+    if (!mine.empty()) {
+        const uint32_t n = (uint32_t)mine.size();
+        std::vector<float> d2((size_t)n * len), rd((size_t)n * len), totals(2 * (size_t)n);
+        rc = skc_profile_batch(ctx, mySpecs.data(), myLps.data(), myOpts.data(), n, 1, &len, d2.data(), rd.data(), nullptr, totals.data());
+        if (rc) return rc;
+        for (uint32_t k = 0; k < n; ++k) {
+            float *dst = myBlock + (size_t)k * slot;
+            memcpy(dst, rd.data() + (size_t)k * len, len * sizeof(float));
+            dst[len] = d2[(size_t)k * len + len - 1]; dst[len + 1] = totals[2 * k]; dst[len + 2] = totals[2 * k + 1];
+        }
+    }
+    if (comm && (rc = skc_comm_allgather_host(comm, blocks.data(), (uint64_t)per * slot * sizeof(float)))) return rc;
     out.len = len;
     out.rd.resize((size_t)kWavelengths * len);
-    rc = skc_profile_batch(ctx, specs.data(), lps.data(), opts.data(), kWavelengths, 1, &len, d2.data(), out.rd.data(), nullptr, totals.data());
-    if (rc) return rc;
     for (int w = 0; w < kWavelengths; ++w) {      // core/multipole.cpp:275-280
-        float last = d2[(size_t)w * len + len - 1];
+        const float *src = blocks.data() + ((size_t)(w % world) * per + (size_t)(w / world)) * slot;
+        memcpy(out.rd.data() + (size_t)w * len, src, len * sizeof(float));
+        const float last = src[len];
         out.dsqSpacing[w] = last / (float)(len - 1);
         out.rcpDsqSpacing[w] = (float)(len - 1) / last;
-        out.totalReflectance[w] = totals[2 * w];
-        out.totalTransmittance[w] = totals[2 * w + 1];
+        out.totalReflectance[w] = src[len + 1];
+        out.totalTransmittance[w] = src[len + 2];
     }
     return 0;
 }

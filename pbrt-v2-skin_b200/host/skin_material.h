@@ -33,9 +33,10 @@ void BuildProfileJobs(const SkinLayerSpectra &s, int desiredLength, bool lerpOnT
                       std::vector<skc_layer_spec> &specs, std::vector<uint32_t> &layersPerSet,
                       std::vector<skc_mpc_options> &opts);
 
-// ComputeMultipoleProfile (core/multipole.cpp:396-420): one skc_profile_batch call for the 30 wavelengths.
+// ComputeMultipoleProfile (core/multipole.cpp:396-420): one skc_profile_batch call for the 30 wavelengths -- or, with a
+// communicator, for this rank's share of them (wavelength w on rank w % world), the finished tables all-gathered.
 // Returns 0 or the device error code (skc_last_error(ctx) has the text).
 int ComputeMultipoleProfile(skc_ctx *ctx, const SkinLayerSpectra &s, int desiredLength, bool lerpOnThinSlab,
-                            ProfileTable &out);
+                            ProfileTable &out, skc_comm *comm = nullptr);
 
 }  // namespace skin

@@ -12,6 +12,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <thread>
 
 extern "C" void skh_film_to_rgb(const float *pixels4, int w, int h, float *rgb);
 extern "C" int skh_write_pfm(const char *path, const float *rgb, int w, int h);
@@ -40,10 +41,10 @@ void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d) {
 
 // LayeredSkin::LayeredSkin (materials/layeredskin.cpp:39-123): layer spectra -> 30 diffusion profiles -> rho_hd, all
 // generated on the device and installed as the context's material tables.
-int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin) {
+int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm) {
     SkinLayerSpectra sp = ComputeSkinLayerSpectra(skin);
     ProfileTable t;
-    int rc = ComputeMultipoleProfile(ctx, sp, skin.desiredlength, skin.lerponthinslab, t);
+    int rc = ComputeMultipoleProfile(ctx, sp, skin.desiredlength, skin.lerponthinslab, t, comm);
     if (rc) return rc;
     std::vector<float> rho(1025 * 30);
     if ((rc = skc_rho_table(ctx, skin.roughness, 1.f, skin.layerIor[0], 0, rho.data()))) return rc;
@@ -64,20 +65,23 @@ int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
 
 static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-// rgb: [yres][xres][3] as ImageFilm::WriteImage hands to ::WriteImage
-bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err) {
+// One rank's share of SamplerRenderer::Render.  comm == nullptr: the whole frame on one GPU.  With a communicator:
+// the material's wavelengths, the irradiance points and the render tasks are dealt over the ranks; the points are all-gathered
+// (positions first, the rows behind the octree topology pass), every rank builds the same octree, and the films are summed into
+// rank 0's, which alone gets the image.  rgb: [yres][xres][3] as ImageFilm::WriteImage hands to ::WriteImage (rank 0).
+bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const BuiltScene &built, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err) {
     auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
+    const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
     double t0 = now();
-    BuiltScene built;
-    if (!BuildScene(sd, nullptr, &built, err)) return false;
     if (!dev(UploadScene(ctx, built))) return false;
     double t1 = now();
-    if (!dev(BuildSkinMaterial(ctx, sd.skin)) || !dev(skc_synchronize(ctx))) return false;
+    if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
     // the camera pass's Preprocess-independent part (sampler stream, camera rays, closest hits, direct lighting) goes to the
     // second stream first and runs beside Preprocess
     skc_frame_desc fd;
     MakeFrameDesc(sd, nCores, &fd);
+    fd.taskRank = rank; fd.taskWorld = world;
     uint64_t nSamples = 0;
     if (sd.lights.empty()) { *err = "no light sources in the scene: the subsurface integrator has nothing to render"; return false; }
     if (!dev(skc_frame_setup(ctx, &fd, &nSamples)) || !dev(skc_frame_prefetch(ctx))) return false;
@@ -95,25 +99,85 @@ bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<floa
                 fclose(f);
             }
         }
-        if (!filePts.empty()) {
+        const bool fromFile = !filePts.empty();
+        if (fromFile) {
             nPts = filePts.size();
             if (!dev(skc_set_surface_points(ctx, filePts.data(), nPts))) return false;
-        } else                                                               // pts.size() == 0 -> tessellate (:182-190)
-        if (!dev(skc_tessellate_resident(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, &nPts))) return false;
+        } else if (world == 1) {                                             // pts.size() == 0 -> tessellate (:182-190)
+            if (!dev(skc_tessellate_resident(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, &nPts))) return false;
+        } else if (!dev(skc_tessellate_range(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, 0, 0, &nPts))) return false;   // the count
         st->irradianceTasks = RoundUpPow2((uint32_t)std::max(32 * nCores, (int)nPts / 4096));   // :194-199
-        if (!dev(skc_irradiance_resident(ctx, 0, nPts, st->irradianceTasks, sd.mix, nullptr))) return false;
-        if (!dev(skc_build_octree(ctx, &st->octreeNodes, nullptr, nullptr))) return false;
+        if (world == 1) {
+            if (!dev(skc_irradiance_resident(ctx, 0, nPts, st->irradianceTasks, sd.mix, nullptr))) return false;
+            if (!dev(skc_build_octree(ctx, &st->octreeNodes, nullptr, nullptr))) return false;
+        } else {
+            // contiguous equal shards (the scramble stream of a point depends on its task and its place in it, both functions
+            // of the point index alone, so any range can be computed anywhere); the last shard may be short
+            const uint64_t shard = (nPts + world - 1) / world, first = std::min<uint64_t>((uint64_t)rank * shard, nPts), count = std::min<uint64_t>(shard, nPts - first);
+            void *pa = nullptr, *rows = nullptr;
+            if (!dev(skc_irradiance_dev(ctx, shard * world, &pa, &rows))) return false;             // arrays sized for the padded exchange
+            if (!fromFile && count && !dev(skc_tessellate_range(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, first, count, &nPts))) return false;
+            if (!dev(skc_irradiance_resident(ctx, first, count, st->irradianceTasks, sd.mix, nullptr))) return false;
+            if (!dev(skc_comm_allgather_positions(comm, shard)) || !dev(skc_comm_allgather_rows_begin(comm, shard))) return false;
+            if (!dev(skc_set_point_count(ctx, nPts)) || !dev(skc_build_octree_topology(ctx))) return false;
+            if (!dev(skc_comm_allgather_rows_wait(comm)) || !dev(skc_build_octree_finalize(ctx, &st->octreeNodes, nullptr, nullptr))) return false;
+        }
     }
     if (!dev(skc_synchronize(ctx))) return false;
     double t3 = now();
     // Mo + the subsurface term, the spectral sum and the film
     if (!dev(skc_frame_film_clear(ctx)) || !dev(skc_frame_render(ctx, 0, nSamples, sd.maxerror, sd.mix, nullptr))) return false;
-    rgb->resize((size_t)sd.xres * sd.yres * 3);
-    if (!dev(skc_frame_film_rgb(ctx, rgb->data()))) return false;           // ImageFilm::WriteImage's XYZ -> RGB / weight on the device
+    if (comm && !dev(skc_comm_reduce_film(comm, 0))) return false;
+    if (rank == 0) {
+        rgb->resize((size_t)sd.xres * sd.yres * 3);
+        if (!dev(skc_frame_film_rgb(ctx, rgb->data()))) return false;       // ImageFilm::WriteImage's XYZ -> RGB / weight on the device
+    } else if (!dev(skc_synchronize(ctx))) return false;
     double t4 = now();
     st->buildSec = t1 - t0; st->materialSec = t2 - t1; st->preprocessSec = t3 - t2; st->renderSec = t4 - t3;
     st->nPoints = nPts; st->nSamples = nSamples; st->renderTasks = (uint32_t)fd.nTasks;
     return true;
+}
+
+bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err) {
+    double t0 = now();
+    BuiltScene built;
+    if (!BuildScene(sd, nullptr, &built, err)) return false;
+    double tBuild = now() - t0;
+    if (!RenderSceneRank(ctx, nullptr, sd, built, nCores, rgb, st, err)) return false;
+    st->buildSec += tBuild;
+    return true;
+}
+
+// `pbrt --gpus N scene.pbrt`: one process, N contexts on devices firstDevice .. firstDevice + N - 1, one host thread per context,
+// the exchanges through NCCL (skc_comm_create_local).  The image and the statistics are rank 0's.
+bool RenderSceneMultiGPU(int firstDevice, int nGpus, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err) {
+    double t0 = now();
+    BuiltScene built;
+    if (!BuildScene(sd, nullptr, &built, err)) return false;
+    double tBuild = now() - t0;
+    std::vector<skc_ctx *> ctxs(nGpus, nullptr);
+    std::vector<skc_comm *> comms(nGpus, nullptr);
+    bool ok = true;
+    for (int i = 0; i < nGpus && ok; ++i) {
+        ctxs[i] = skc_create(firstDevice + i);
+        if (!ctxs[i]) { *err = std::string("skc_create: ") + skc_last_error(nullptr); ok = false; }
+    }
+    if (ok && nGpus > 1 && skc_comm_create_local(ctxs.data(), nGpus, comms.data())) { *err = skc_last_error(ctxs[0]); ok = false; }
+    if (ok) {
+        std::vector<std::string> errs(nGpus);
+        std::vector<RenderStats> stats(nGpus);
+        std::vector<char> good(nGpus, 0);
+        std::vector<std::vector<float>> images(nGpus);
+        std::vector<std::thread> threads;
+        for (int i = 0; i < nGpus; ++i)
+            threads.emplace_back([&, i]() { good[i] = RenderSceneRank(ctxs[i], comms[i], sd, built, nCores, &images[i], &stats[i], &errs[i]) ? 1 : 0; });
+        for (std::thread &t : threads) t.join();
+        for (int i = 0; i < nGpus; ++i) if (!good[i]) { if (ok) *err = "GPU " + std::to_string(firstDevice + i) + ": " + errs[i]; ok = false; }
+        if (ok) { *rgb = std::move(images[0]); *st = stats[0]; st->buildSec += tBuild; }
+    }
+    for (skc_comm *c : comms) if (c) skc_comm_destroy(c);
+    for (skc_ctx *c : ctxs) if (c) skc_destroy(c);
+    return ok;
 }
 
 bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *nPoints, std::string *err) {

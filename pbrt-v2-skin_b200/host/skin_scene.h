@@ -155,7 +155,7 @@ void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, in
 
 // What api.cpp's MakeCamera / MakeFilm / MakeSampler / MakeRenderer derive from the scene for the device frame pass
 void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d);
-int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin);
+int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nullptr);   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,
@@ -166,6 +166,10 @@ struct RenderStats {
     uint32_t octreeNodes = 0, irradianceTasks = 0, renderTasks = 0;
 };
 bool RenderScene(skc_ctx *ctx, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err);
+// one rank's share of the frame (comm == nullptr: all of it); the image goes to rank 0 (host/skin_render.cpp)
+bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const BuiltScene &built, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err);
+// one process driving nGpus devices (`pbrt --gpus N`): a host thread and a context per device, NCCL between them
+bool RenderSceneMultiGPU(int firstDevice, int nGpus, const SceneDesc &sd, int nCores, std::vector<float> *rgb, RenderStats *st, std::string *err);
 // Renderer "tessellatesurfacepoints" (renderers/surfacepoints.cpp:300-347): device tessellation -> raw SurfacePoint file
 bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *nPoints, std::string *err);
 // ::WriteImage (core/imageio.cpp:78-104): .pfm / .tga by suffix (no OpenEXR in this build)

@@ -34,7 +34,9 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_tessellate_resident", "skc_tessellate_host", "skc_tessellate_range", "skc_get_surface_points",
            "skc_frame_setup", "skc_frame_prefetch", "skc_frame_samples", "skc_frame_get_samples", "skc_frame_sample_floats", "skc_frame_render",
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
-           "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_comm_unique_id", "skc_comm_create", "skc_comm_create_local", "skc_comm_destroy", "skc_comm_rank", "skc_comm_world",
+           "skc_comm_allgather_positions", "skc_comm_allgather_rows_begin", "skc_comm_allgather_rows_wait", "skc_comm_reduce_film",
+           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -115,6 +117,18 @@ def load_library():
     lib.skc_set_irradiance_rows.restype = i32; lib.skc_set_irradiance_rows.argtypes = [vp, u64, u64, vp, vp]
     lib.skc_test_libmf.restype = i32; lib.skc_test_libmf.argtypes = [vp, i32, vp, u64, vp]
     lib.skc_test_sincosf.restype = i32; lib.skc_test_sincosf.argtypes = [vp, vp, u64, vp, vp]
+    lib.skc_comm_unique_id.restype = i32; lib.skc_comm_unique_id.argtypes = [vp]
+    lib.skc_comm_create.restype = vp; lib.skc_comm_create.argtypes = [vp, i32, i32, vp]
+    lib.skc_comm_destroy.restype = None; lib.skc_comm_destroy.argtypes = [vp]
+    lib.skc_comm_rank.restype = i32; lib.skc_comm_rank.argtypes = [vp]
+    lib.skc_comm_world.restype = i32; lib.skc_comm_world.argtypes = [vp]
+    for f in ("skc_comm_allgather_positions", "skc_comm_allgather_rows_begin"):
+        getattr(lib, f).restype = i32; getattr(lib, f).argtypes = [vp, u64]
+    lib.skc_comm_allgather_rows_wait.restype = i32; lib.skc_comm_allgather_rows_wait.argtypes = [vp]
+    lib.skc_comm_reduce_film.restype = i32; lib.skc_comm_reduce_film.argtypes = [vp, i32]
+    lib.skc_comm_max_f32.restype = i32; lib.skc_comm_max_f32.argtypes = [vp, C.POINTER(f32)]
+    lib.skc_comm_barrier.restype = i32; lib.skc_comm_barrier.argtypes = [vp]
+    lib.skc_comm_allgather_host.restype = i32; lib.skc_comm_allgather_host.argtypes = [vp, vp, u64]
     lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_mo_table_stats.restype = i32; lib.skc_mo_table_stats.argtypes = [vp, vp]
     lib.skc_moc_build.restype = vp; lib.skc_moc_build.argtypes = [vp, vp, u32, f32, i32, i32, u32]
@@ -444,6 +458,54 @@ class SkinDevice:
         hd = np.empty((1025, 30), np.float32)
         self._ck(self.lib.skc_rho_table(self.ctx, float(roughness), float(eta_i), float(eta_t), int(fixed_fresnel), _ptr(hd)))
         return hd
+
+
+class SkinComm:
+    """One skc_comm: the NCCL communicator of a SkinDevice among `world` ranks (csrc/skc_comm.cu)."""
+
+    @staticmethod
+    def unique_id():
+        lib = load_library()
+        buf = (C.c_uint8 * 128)()
+        if lib.skc_comm_unique_id(buf):
+            raise SkcError("ncclGetUniqueId failed")
+        return bytes(buf)
+
+    def __init__(self, dev, rank, world, id128):
+        self.dev, self.lib = dev, dev.lib
+        self._id = (C.c_uint8 * 128).from_buffer_copy(id128)
+        self.h = self.lib.skc_comm_create(dev.ctx, rank, world, self._id)
+        if not self.h:
+            raise SkcError(self.lib.skc_last_error(dev.ctx).decode())
+        self.rank, self.world = rank, world
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise SkcError(self.lib.skc_last_error(self.dev.ctx).decode())
+
+    def allgather_positions(self, shard):
+        self._ck(self.lib.skc_comm_allgather_positions(self.h, shard))
+
+    def allgather_rows_begin(self, shard):
+        self._ck(self.lib.skc_comm_allgather_rows_begin(self.h, shard))
+
+    def allgather_rows_wait(self):
+        self._ck(self.lib.skc_comm_allgather_rows_wait(self.h))
+
+    def reduce_film(self, root=0):
+        self._ck(self.lib.skc_comm_reduce_film(self.h, root))
+
+    def max_f32(self, value):
+        v = C.c_float(value)
+        self._ck(self.lib.skc_comm_max_f32(self.h, C.byref(v)))
+        return float(v.value)
+
+    def barrier(self):
+        self._ck(self.lib.skc_comm_barrier(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.skc_comm_destroy(self.h); self.h = None
 
 
 class CompactProfile:

@@ -1,9 +1,10 @@
-"""world_size-2 gloo test (CPU) of the multi-GPU host logic: shard ranges cover the work exactly
-once and the in-place all-gather reassembles the irradiance arrays on every rank."""
+"""world_size-2 gloo test (CPU) of the multi-GPU host logic (pbrt-v2-skin_b200/multigpu.py): the shard ranges cover the points
+exactly once; rank 0's communicator id reaches every rank; and an in-place all-gather over arrays laid out as
+skc_comm_allgather_positions / _rows expect them (world x padded shard, rank r's block at r x shard) reassembles the set on
+every rank -- gloo's all_gather_into_tensor standing in for the ncclAllGather of csrc/skc_comm.cu, same layout, same call shape."""
 import os
 import sys
 
-import numpy as np
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -17,16 +18,18 @@ def _worker(rank, world, port, n, q):
     pkg = ge.load_package()
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
+    ident = pkg.exchange_unique_id(dist, rank, lambda: bytes((7 * i + 3) % 256 for i in range(128)))
     first, count, per = pkg.shard_range(n, rank, world)
     pos = torch.zeros(world * per, 4); E = torch.zeros(world * per, 32)
     idx = torch.arange(first, first + count, dtype=torch.float32)
     pos[first:first + count] = idx[:, None] * torch.tensor([1.0, 2.0, 3.0, 0.5])        # this rank's "irradiance pass"
     E[first:first + count] = idx[:, None] + torch.arange(32, dtype=torch.float32)[None] / 64
-    pkg.allgather_inplace(dist, pos, rank, per); pkg.allgather_inplace(dist, E, rank, per)
+    dist.all_gather_into_tensor(pos, pos[rank * per:(rank + 1) * per])                  # in place: send = own block of recv
+    dist.all_gather_into_tensor(E, E[rank * per:(rank + 1) * per])
     full = torch.arange(n, dtype=torch.float32)
     ok = torch.equal(pos[:n], full[:, None] * torch.tensor([1.0, 2.0, 3.0, 0.5])) and torch.equal(E[:n], full[:, None] + torch.arange(32, dtype=torch.float32)[None] / 64)
     ok = ok and bool((pos[n:] == 0).all())
-    q.put((rank, first, count, ok))
+    q.put((rank, first, count, ok, ident))
     dist.destroy_process_group()
 
 
@@ -47,7 +50,7 @@ def test_shard_ranges():
                 assert sum(c for _, c in cover) == n and all(cover[i][0] + cover[i][1] == cover[i + 1][0] for i in range(world - 1))
 
 
-def test_inplace_allgather_world2():
+def test_id_exchange_and_inplace_allgather_world2():
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     n, world, port = 1001, 2, 29731 + os.getpid() % 200
@@ -59,14 +62,11 @@ def test_inplace_allgather_world2():
         p.join(timeout=60)
     assert [r[3] for r in res] == [True, True]
     assert res[0][1:3] == (0, 501) and res[1][1:3] == (501, 500)
+    assert res[0][4] == res[1][4] == bytes((7 * i + 3) % 256 for i in range(128))
 
 
-def test_tile_round_robin_partitions_all_samples(pkg):
-    n, tile = 10_000, 1024
-    for world in (1, 2, 3, 8):
-        parts = [pkg.tile_round_robin(n, tile, r, world) for r in range(world)]
-        allidx = np.sort(np.concatenate(parts))
-        assert np.array_equal(allidx, np.arange(n))
-        # whole tiles stay together and consecutive tiles go to consecutive ranks
-        for r, p in enumerate(parts):
-            assert np.all((p // tile) % world == r)
+def test_library_exports_the_comm_entry_points(pkg):
+    lib = pkg.load_library()
+    for s in ("skc_comm_unique_id", "skc_comm_create", "skc_comm_create_local", "skc_comm_allgather_positions", "skc_comm_allgather_rows_begin",
+              "skc_comm_allgather_rows_wait", "skc_comm_reduce_film", "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_comm_destroy"):
+        assert hasattr(lib, s), s
