@@ -14,7 +14,7 @@ __global__ void __launch_bounds__(128) k_trace_any(BvhView bv, const skc_ray *__
     const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
     float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
     DRay ray; ray.o = mk3(r0.x, r0.y, r0.z); ray.d = mk3(r0.w, r1.x, r1.y); ray.mint = r1.z; ray.maxt = r1.w;
-    bool occ = cnt ? bvhOccluded<true>(bv, ray, cnt) : bvhOccluded<false>(bv, ray, nullptr);
+    bool occ = cnt ? bvhOccluded<true>(bv, ray, cnt) : bvhOccludedFast(bv, ray);
     out[i] = occ ? 1 : 0;
 }
 
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, 
 
 // ---- host side --------------------------------------------------------------------------
 BvhView skc_bvh_view(const skc_ctx *ctx) {
-    BvhView bv; bv.nodes = ctx->bvhNodes; bv.prims = ctx->bvhPrims; bv.spheres = ctx->spheres; return bv;
+    BvhView bv; bv.nodes = ctx->bvhNodes; bv.prims = ctx->bvhPrims; bv.spheres = ctx->spheres; bv.wide = ctx->bvhWideOn ? ctx->bvhWide : nullptr; return bv;
 }
 MeshView skc_mesh_view(const skc_ctx *ctx) {
     MeshView mv; mv.primInfo = ctx->primInfo; mv.P = ctx->meshP; mv.N = ctx->meshN; mv.UV = ctx->meshUV;
@@ -102,6 +102,59 @@ template <class T> static int upload(skc_ctx *ctx, T **dst, const T *src, size_t
     }
     SKC_CUDA(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));     // pageable source: staged before the call returns
     return 0;
+}
+
+// The 4-wide form of the binary tree for any-hit rays (skc_bvh.cuh bvhOccludedWide): every wide node gathers up to four
+// descendants of one binary node -- its two children, then, while fewer than four, the interior child with the largest surface
+// area is replaced by its own two children -- and stores THEIR boxes (the reference's boxes, unchanged).  Returns false when a
+// leaf does not fit the child word (more than 127 primitives or 2^24 primitives in all): the binary walk is used then.
+static bool buildWide(const skc_bvh_node *nodes, uint32_t nNodes, uint32_t nPrims, std::vector<float4> &out) {
+    if (nPrims >= (1u << 24)) return false;
+    struct Item { uint32_t bin, wide; };
+    std::vector<Item> todo;
+    auto area = [&](uint32_t b) { const skc_bvh_node &n = nodes[b]; float dx = n.pmax[0] - n.pmin[0], dy = n.pmax[1] - n.pmin[1], dz = n.pmax[2] - n.pmin[2]; return dx * dy + dx * dz + dy * dz; };
+    out.clear();
+    out.resize(8);
+    todo.push_back({0u, 0u});
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        uint32_t kids[4]; int nk = 0;
+        if (nodes[it.bin].nPrimitives) kids[nk++] = it.bin;                     // a tree that is one leaf
+        else {
+            kids[nk++] = it.bin + 1; kids[nk++] = nodes[it.bin].offset;
+            while (nk < 4) {
+                int best = -1; float bestArea = -1.f;
+                for (int k = 0; k < nk; ++k) if (!nodes[kids[k]].nPrimitives && area(kids[k]) > bestArea) { bestArea = area(kids[k]); best = k; }
+                if (best < 0) break;
+                const uint32_t b = kids[best];
+                kids[best] = b + 1; kids[nk++] = nodes[b].offset;
+            }
+        }
+        float box[6][4]; uint32_t word[4];
+        for (int k = 0; k < 4; ++k) {
+            if (k >= nk) { for (int a = 0; a < 3; ++a) { box[a][k] = INFINITY; box[3 + a][k] = -INFINITY; } word[k] = SKC_WIDE_EMPTY; continue; }
+            const skc_bvh_node &n = nodes[kids[k]];
+            for (int a = 0; a < 3; ++a) { box[a][k] = n.pmin[a]; box[3 + a][k] = n.pmax[a]; }
+            if (n.nPrimitives) {
+                if (n.nPrimitives > 127) return false;
+                word[k] = SKC_WIDE_LEAF | ((uint32_t)n.nPrimitives << 24) | n.offset;
+            } else {
+                const uint32_t w = (uint32_t)(out.size() / 8);
+                if (w >= SKC_WIDE_LEAF) return false;
+                out.resize(out.size() + 8);
+                word[k] = w;
+                todo.push_back({kids[k], w});
+            }
+        }
+        float4 *q = out.data() + 8 * (size_t)it.wide;
+        for (int a = 0; a < 6; ++a) q[a] = make_float4(box[a][0], box[a][1], box[a][2], box[a][3]);
+        float f[4]; memcpy(f, word, 16);
+        q[6] = make_float4(f[0], f[1], f[2], f[3]);
+        q[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    (void)nNodes;
+    return true;
 }
 
 extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t nNodes,
@@ -145,6 +198,11 @@ extern "C" int skc_upload_bvh(skc_ctx *ctx, const skc_bvh_node *nodes, uint32_t 
             dp[3 * i + 2] = make_float4(0.f, ft, fi, 0.f);
             info[i] = make_int4(0, 0, 0, 1);
         } else return skc_fail(ctx, "skc_upload_bvh: unsupported primitive type %d", pr.type);
+    }
+    {
+        std::vector<float4> wide;
+        if (buildWide(nodes, nNodes, nPrims, wide)) { if (upload(ctx, &ctx->bvhWide, wide.data(), wide.size())) return 1; ctx->nWideNodes = (uint32_t)(wide.size() / 8); }
+        else { if (upload(ctx, &ctx->bvhWide, (const float4 *)nullptr, 0)) return 1; ctx->nWideNodes = 0; }
     }
     if (upload(ctx, &ctx->bvhNodes, dn.data(), dn.size())) return 1;
     if (upload(ctx, &ctx->bvhPrims, dp.data(), dp.size())) return 1;

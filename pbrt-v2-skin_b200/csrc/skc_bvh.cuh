@@ -18,6 +18,7 @@ struct BvhView {
     const float4 *nodes;
     const float4 *prims;
     const skc_light *spheres;
+    const float4 *wide;        // 4-wide form of the same tree for any-hit rays (8 float4 per node, see bvhOccludedWide), or nullptr
 };
 
 // What closest-hit shading needs of the triangle mesh (shapes/trianglemesh.inl:224-299).
@@ -278,6 +279,77 @@ __device__ inline bool bvhOccluded(const BvhView &bv, const DRay &ray, unsigned 
     }
     if (COUNT && cnt) { atomicAdd(&cnt[0], (unsigned long long)nNode); atomicAdd(&cnt[1], (unsigned long long)nPrim); }
     return occluded;
+}
+
+// ---- any-hit over the 4-wide form of the same tree --------------------------------------------------------------------
+// IntersectP's ANSWER does not depend on the order in which nodes are visited, only on which leaves are reached: a leaf is
+// reached iff the ray passes the slab test of the leaf's box and of every ancestor's box.  A child's box lies inside its
+// parent's, and the slab test is monotonic in the box (a larger box gives a wider [tmin, tmax] in the same fp32 operations), so
+// a ray that passes a node's box passes all of its ancestors' boxes: testing the boxes of SOME ancestors only -- every second
+// level -- reaches exactly the same leaves.  So the binary tree is collapsed at upload time (skc_bvh.cu buildWide): a wide node
+// holds the boxes of up to four descendants of one binary node (its children, with the larger interior ones replaced by their
+// own children), as one 128 B line:
+//   q0..q5 = min.x[4] min.y[4] min.z[4] max.x[4] max.y[4] max.z[4]      q6 = child[4] (uint bits)      q7 = unused
+//   child: 0xffffffff empty | 0x80000000 + (nPrims << 24) + first primitive (leaf) | index of a wide node
+// The four slab tests of a node are independent (the binary walk is one dependent fetch-test-branch chain per box), leaves are
+// tested as they are met, interior hits go to a short stack.  The slab arithmetic is the reference's (bvh.cpp:126-148), the
+// boxes are the reference's, the primitive tests are the same functions: hit / no-hit is identical to bvhOccluded for every
+// ray (tests/test_gpu_parity.py::test_wide_any_hit_equals_binary).  Visit counts differ, so the counting instances stay binary.
+#define SKC_WIDE_EMPTY 0xffffffffu
+#define SKC_WIDE_LEAF 0x80000000u
+__device__ __forceinline__ bool slabTestSoA(float minx, float miny, float minz, float maxx, float maxy, float maxz, const DRay &ray, const SlabSetup &s) {
+    float tmin = ((s.neg[0] ? maxx : minx) - ray.o.x) * s.invDir.x;
+    float tmax = ((s.neg[0] ? minx : maxx) - ray.o.x) * s.invDir.x;
+    float tymin = ((s.neg[1] ? maxy : miny) - ray.o.y) * s.invDir.y;
+    float tymax = ((s.neg[1] ? miny : maxy) - ray.o.y) * s.invDir.y;
+    if ((tmin > tymax) || (tymin > tmax)) return false;
+    if (tymin > tmin) tmin = tymin;
+    if (tymax < tmax) tmax = tymax;
+    float tzmin = ((s.neg[2] ? maxz : minz) - ray.o.z) * s.invDir.z;
+    float tzmax = ((s.neg[2] ? minz : maxz) - ray.o.z) * s.invDir.z;
+    if ((tmin > tzmax) || (tzmin > tmax)) return false;
+    if (tzmin > tmin) tmin = tzmin;
+    if (tzmax < tmax) tmax = tzmax;
+    return (tmin < ray.maxt) && (tmax > ray.mint);
+}
+__device__ __forceinline__ bool leafOccluded(const BvhView &bv, uint32_t first, uint32_t count, const DRay &ray) {
+    for (uint32_t i = 0; i < count; ++i) {
+        const float4 *pp = &bv.prims[3 * (first + i)];
+        float4 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2);
+        float t, b1, b2;
+        bool h;
+        if (__float_as_int(c.y) == 0) h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
+        else h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
+        if (h) return true;
+    }
+    return false;
+}
+#define SKC_WIDE_STACK 48
+__device__ inline bool bvhOccludedWide(const BvhView &bv, const DRay &ray) {
+    const SlabSetup ss = slabSetup(ray);
+    uint32_t todo[SKC_WIDE_STACK];
+    int top = 0;
+    uint32_t node = 0;
+    for (;;) {
+        const float4 *q = bv.wide + 8 * (size_t)node;
+        const float4 mnx = __ldg(q), mny = __ldg(q + 1), mnz = __ldg(q + 2), mxx = __ldg(q + 3), mxy = __ldg(q + 4), mxz = __ldg(q + 5), ch = __ldg(q + 6);
+        const uint32_t c[4] = {__float_as_uint(ch.x), __float_as_uint(ch.y), __float_as_uint(ch.z), __float_as_uint(ch.w)};
+        const bool h[4] = {c[0] != SKC_WIDE_EMPTY && slabTestSoA(mnx.x, mny.x, mnz.x, mxx.x, mxy.x, mxz.x, ray, ss),
+                           c[1] != SKC_WIDE_EMPTY && slabTestSoA(mnx.y, mny.y, mnz.y, mxx.y, mxy.y, mxz.y, ray, ss),
+                           c[2] != SKC_WIDE_EMPTY && slabTestSoA(mnx.z, mny.z, mnz.z, mxx.z, mxy.z, mxz.z, ray, ss),
+                           c[3] != SKC_WIDE_EMPTY && slabTestSoA(mnx.w, mny.w, mnz.w, mxx.w, mxy.w, mxz.w, ray, ss)};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (!h[k]) continue;
+            if (c[k] & SKC_WIDE_LEAF) { if (leafOccluded(bv, c[k] & 0x00ffffffu, (c[k] >> 24) & 0x7fu, ray)) return true; }
+            else todo[top++] = c[k];
+        }
+        if (top == 0) return false;
+        node = todo[--top];
+    }
+}
+__device__ __forceinline__ bool bvhOccludedFast(const BvhView &bv, const DRay &ray) {
+    return bv.wide ? bvhOccludedWide(bv, ray) : bvhOccluded<false>(bv, ray, nullptr);
 }
 
 // BVHAccel::Intersect (bvh.cpp:388-439): closest hit; ray.maxt shrinks (primitive.cpp:191).

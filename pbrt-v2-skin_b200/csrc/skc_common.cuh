@@ -39,6 +39,9 @@ struct skc_ctx {
     // --- BVH (skc_bvh.cu)
     float4 *bvhNodes = nullptr;    // 2 x float4 per node
     uint32_t nNodes = 0;
+    float4 *bvhWide = nullptr;     // 4-wide form for any-hit rays, 8 x float4 per node (skc_bvh.cuh bvhOccludedWide), or nullptr
+    uint32_t nWideNodes = 0;
+    bool bvhWideOn = true;         // env SKC_BVH_WIDE=0 keeps the binary walk for any-hit rays too
     float4 *bvhPrims = nullptr;    // 3 x float4 per primitive (triangle: p1,e1,e2 | sphere tag)
     uint32_t nPrims = 0;
     int4 *primInfo = nullptr;      // per primitive: v0,v1,v2 (mesh vertex ids), type

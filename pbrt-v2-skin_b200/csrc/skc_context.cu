@@ -81,6 +81,7 @@ extern "C" skc_ctx *skc_create(int device) {
     if (cudaDeviceGetAttribute(&ctx->smemOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess) ctx->smemOptin = 48 * 1024;
     if (const char *k = getenv("SKC_MO_GROUP")) ctx->moGroup = atoi(k);
     if (const char *k = getenv("SKC_MO_WARPS")) ctx->moWarps = atoi(k);
+    if (const char *k = getenv("SKC_BVH_WIDE")) ctx->bvhWideOn = atoi(k) != 0;
     if (const char *k = getenv("SKC_MO_TABLE")) ctx->moTable = strcmp(k, "exact") != 0;
     if (const char *k = getenv("SKC_MO_TOL")) { float t = (float)atof(k); if (t > 0.f) ctx->mocTol = t; }
     if (const char *k = getenv("SKC_MO_SORT")) ctx->moSort = atoi(k);
@@ -92,7 +93,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
+    void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhWide, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->mocRows, ctx->mocHeads, ctx->mocLam, ctx->mocHeadOff, ctx->lights, ctx->ipPosArea, ctx->ipE,
                     ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->otLeafE};
     for (void *p : ptrs) if (p) cudaFree(p);

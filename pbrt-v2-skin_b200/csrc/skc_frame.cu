@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(LC_THREADS) k_ld_chain(BvhView bv, const Frame
         // Scene::Intersect is true iff anything lies on the camera ray
         for (uint32_t j = tid; j < nPix * spp; j += LC_THREADS) {
             DRay r = cameraRay(C, xy[(uint64_t)p0 * spp + j]);
-            if (bvhOccluded<false>(bv, r, nullptr)) atomicAdd(&hits[j / spp], 1u);
+            if (bvhOccludedFast(bv, r)) atomicAdd(&hits[j / spp], 1u);
         }
         __syncthreads();
         // exclusive scan of the hit counts (warp 0, 32 pixels at a time)
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
             if (sampleDeltaLight(L, kind, p, eps, &wi, &d2, &fall, &sh) && d2 != 0.f) {
                 float4 comp;
                 float f = bsdfF(B, wo, wi, &comp);
-                if (f != 0.f && !bvhOccluded<false>(bv, sh, nullptr)) { T0 = comp; T1.x = fabsf(dot3(wi, B.nn)) / 1.f; T1.y = d2; T1.z = fall; }
+                if (f != 0.f && !bvhOccludedFast(bv, sh)) { T0 = comp; T1.x = fabsf(dot3(wi, B.nn)) / 1.f; T1.y = d2; T1.z = fall; }
             }
             terms[3 * t] = T0; terms[3 * t + 1] = T1; terms[3 * t + 2] = T2;
             return;
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
         if (lightPdf > 0. && lit) {
             float4 comp;
             float f = bsdfF(B, wo, wi, &comp);
-            if (f != 0.f && !bvhOccluded<false>(bv, sh, nullptr)) {
+            if (f != 0.f && !bvhOccludedFast(bv, sh)) {
                 float bp = bsdfPdf(B, wo, wi);
                 float weight = powerHeuristic(lightPdf, bp);
                 T0 = comp; T1.x = fabsf(dot3(wi, B.nn)) * weight / lightPdf;

@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__
     if (r >= __ldg(nRays)) return;
     float4 o = __ldg(&rayO[r]), d = __ldg(&rayD[r]);
     DRay ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.mint = o.w; ray.maxt = d.w;
-    if (bvhOccluded<COUNT>(bv, ray, cnt)) cosPdf[__ldg(&rayTarget[r])] = make_float2(0.f, 0.f);
+    if (COUNT ? bvhOccluded<true>(bv, ray, cnt) : bvhOccludedFast(bv, ray)) cosPdf[__ldg(&rayTarget[r])] = make_float2(0.f, 0.f);
 }
 
 template <bool DELTA>

@@ -586,3 +586,36 @@ def test_device_libm_functions_equal_libm_bit_for_bit(dev):
         assert not bad.any(), "%s differs at %d of %d arguments, e.g. x = %r" % (name, bad.sum(), len(x), x[bad][:4])
     s, c = dev.test_sincosf(phi.astype(np.float32))
     assert np.array_equal(s.view(np.uint32), dev.test_libmf(0, phi).view(np.uint32)) and np.array_equal(c.view(np.uint32), dev.test_libmf(1, phi).view(np.uint32))
+
+
+def test_wide_any_hit_equals_binary(pkg, scene):
+    """The 4-wide any-hit traversal (csrc/skc_bvh.cuh bvhOccludedWide: the same boxes, slab arithmetic and primitive tests, another
+    visiting order) against the binary IntersectP walk and against the C restatement of the reference's IntersectP: identical
+    answers on every ray of (a) the AggregateTest distribution, (b) rays through the mesh, (c) short shadow-like segments that
+    start on the surface."""
+    g = scene
+    rng = np.random.RandomState(17)
+    lo, hi = g.mesh_P.min(0), g.mesh_P.max(0)
+    n = 60000
+    o = (lo + (hi - lo) * (rng.rand(n, 3) * 3 - 1)).astype(np.float32)
+    t = (lo + (hi - lo) * rng.rand(n, 3)).astype(np.float32)
+    rays_a = np.concatenate([o, t - o, np.full((n, 1), 1e-3, np.float32), np.full((n, 1), np.inf, np.float32)], axis=1).astype(np.float32)
+    sp = g.surface_points[rng.randint(0, len(g.surface_points), n)]
+    d = rng.randn(n, 3).astype(np.float32); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays_c = np.concatenate([sp["p"], d, sp["rayEpsilon"][:, None], (rng.rand(n, 1) * 0.5).astype(np.float32)], axis=1).astype(np.float32)
+    rays = np.ascontiguousarray(np.concatenate([rays_a, rays_c]))
+    out = {}
+    for mode in ("0", "1"):
+        os.environ["SKC_BVH_WIDE"] = mode
+        try:
+            d_ = pkg.SkinDevice(0)
+            try:
+                gu.setup_device(d_, g, tables=False)
+                out[mode] = d_.trace_any(rays)
+            finally:
+                d_.close()
+        finally:
+            del os.environ["SKC_BVH_WIDE"]
+    assert 0.02 < out["0"].mean() < 0.98
+    assert np.array_equal(out["0"], out["1"]), "%d rays differ" % (out["0"] != out["1"]).sum()
+    assert np.array_equal(out["1"], orc.trace_any(g, rays))
