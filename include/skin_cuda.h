@@ -220,6 +220,9 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
  * global tables, 0}. */
 int skc_mo_table_stats(skc_ctx *ctx, double *stats8);
+/* Contributions of the last counted skc_camera_pass_resident by the number of hits of their packet that accepted the same
+ * cluster / leaf point together: clusters {<8, 8-15, 16-27, 28-32}, then leaf points {same four bins}. */
+int skc_mo_group_histogram(skc_ctx *ctx, uint64_t *hist8);
 /* Host-only (no GPU, no context): the builder and evaluator behind skc_upload_profile, for the error-bound test
  * (tests/test_mo_table.py).  skc_moc_build returns NULL when no wavelength gets a window. */
 void *skc_moc_build(const float *table, const float *rcpDsqSpacing, uint32_t len, float tol, int K, int M, uint32_t headCapFloats);

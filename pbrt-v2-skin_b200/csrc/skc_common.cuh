@@ -69,6 +69,7 @@ struct skc_ctx {
     float mocInvA = 0.f, mocM = 0.f;
     int moTable = 1;               // 1 = compact table in shared memory + exact fallback (k_mo_lambda), 0 = exact tables only (k_mo_packet); env SKC_MO_TABLE=exact|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
+    uint64_t moHist[8] = {0};
     uint64_t moGroups[2] = {0, 0};       // last counted pass: (cluster, packet) and (leaf point, packet) accept groups
     uint64_t moLookups[3] = {0, 0, 0};   // last counted pass: profile lookups in range / from shared-memory heads / from global tables
     int smemOptin = 0;             // cudaDevAttrMaxSharedMemoryPerBlockOptin

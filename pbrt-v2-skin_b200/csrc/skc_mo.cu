@@ -484,6 +484,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
     const unsigned lanesBelow = (1u << lane) - 1u;
     __syncthreads();
     uint32_t wc[4] = {0, 0, 0, 0};
+    uint32_t hist[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // contributions by size of their accept group (<8, 8-15, 16-27, 28-32): clusters, then leaf points (COUNT only)
     uint32_t grp[2] = {0, 0};          // accept events of this warp: (cluster, packet) and (leaf point, packet) groups (COUNT only)
     uint32_t gc[3] = {0, 0, 0};        // this lane's profile lookups: all in range / from the shared-memory heads / from the global tables
     const uint32_t nPackets = (uint32_t)((n + 31) / 32);
@@ -529,7 +530,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
             }
             unsigned am = __ballot_sync(0xffffffffu, addC), dm = __ballot_sync(0xffffffffu, descend);
             if (am) {
-                if (COUNT) { wc[2] += __popc(am); ++grp[0]; }
+                if (COUNT) { wc[2] += __popc(am); ++grp[0]; const int A = __popc(am); hist[A >= 28 ? 3 : A >= 16 ? 2 : A >= 8 ? 1 : 0] += A; }
                 const float e = __ldg(tr.Et + (size_t)ent.x * SKC_EPAD + lane);
                 if (addC) {     // records densely, in hit order
                     int k; float t;
@@ -552,7 +553,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
                         bool c = descend && q2 * T.rcpMin < T.lenM1;
                         unsigned pm = __ballot_sync(0xffffffffu, c);
                         if (pm) {
-                            if (COUNT) { wc[3] += __popc(pm); ++grp[1]; }
+                            if (COUNT) { wc[3] += __popc(pm); ++grp[1]; const int A = __popc(pm); hist[4 + (A >= 28 ? 3 : A >= 16 ? 2 : A >= 8 ? 1 : 0)] += A; }
                             const float e = __ldg(tr.leafE + (size_t)slot * SKC_EPAD + lane);
                             if (c) {
                                 int k; float t;
@@ -591,7 +592,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
         atomicAdd(&cnt[4], (unsigned long long)gc[0]);
         atomicAdd(&cnt[5], (unsigned long long)gc[1]);
         atomicAdd(&cnt[6], (unsigned long long)gc[2]);
-        if (lane == 0) { atomicAdd(&cnt[7], (unsigned long long)grp[0]); atomicAdd(&cnt[8], (unsigned long long)grp[1]); }
+        if (lane == 0) { atomicAdd(&cnt[7], (unsigned long long)grp[0]); atomicAdd(&cnt[8], (unsigned long long)grp[1]); for (int k = 0; k < 8; ++k) atomicAdd(&cnt[9 + k], (unsigned long long)hist[k]); }
     }
 }
 
@@ -994,20 +995,20 @@ extern "C" int skc_camera_pass_resident(skc_ctx *ctx, uint64_t first, uint64_t c
     if (!dHits) return 1;
     unsigned long long *dCnt = nullptr;
     if (counters7) {
-        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 16 * sizeof(unsigned long long));
+        dCnt = (unsigned long long *)skc_scratch(ctx, 7, 32 * sizeof(unsigned long long));
         if (!dCnt) return 1;
-        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 16 * sizeof(unsigned long long), ctx->stream));
+        SKC_CUDA(cudaMemsetAsync(dCnt, 0, 32 * sizeof(unsigned long long), ctx->stream));
     }
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, dCnt)) return 1;
     skc_stage_end(ctx, 3);
     if (liDev(ctx, dHits, count, maxError, mix, nullptr, nullptr, L30, dCnt ? dCnt + 2 : nullptr, true)) return 1;
     if (counters7) {
-        unsigned long long h[16];
+        unsigned long long h[32];
         SKC_CUDA(cudaMemcpyAsync(h, dCnt, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
         for (int k = 0; k < 7; ++k) counters7[k] = h[k];
-        ctx->moLookups[0] = h[6]; ctx->moLookups[1] = h[7]; ctx->moLookups[2] = h[8]; ctx->moGroups[0] = h[9]; ctx->moGroups[1] = h[10];
+        ctx->moLookups[0] = h[6]; ctx->moLookups[1] = h[7]; ctx->moLookups[2] = h[8]; ctx->moGroups[0] = h[9]; ctx->moGroups[1] = h[10]; for (int k = 0; k < 8; ++k) ctx->moHist[k] = h[11 + k];
     }
     return 0;
 }
@@ -1022,6 +1023,8 @@ extern "C" int skc_mo_table_stats(skc_ctx *ctx, double *stats8) {
     stats8[4] = (double)ctx->moLookups[0]; stats8[5] = (double)ctx->moLookups[1]; stats8[6] = (double)ctx->moLookups[2]; stats8[7] = (double)ctx->moGroups[0] + (double)ctx->moGroups[1];
     return 0;
 }
+// contributions of the last counted camera pass by the size of their accept group: clusters {<8, 8-15, 16-27, 28-32}, leaf points {same}
+extern "C" int skc_mo_group_histogram(skc_ctx *ctx, uint64_t *hist8) { if (!ctx) return 1; for (int k = 0; k < 8; ++k) hist8[k] = ctx->moHist[k]; return 0; }
 
 // ---------------------------------------------------------------------------------------------
 // skc_mo_static: SubsurfaceOctreeNode::Mo for callers that must not allocate (code under CUDA graph capture, tight serving

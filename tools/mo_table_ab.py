@@ -15,7 +15,7 @@ import __graft_entry__ as ge  # noqa: E402
 
 def frame(pkg, scene_path, mode, reps=3, counters=True, env=None):
     os.environ["SKC_MO_TABLE"] = mode
-    for k in ("SKC_MO_GROUP", "SKC_MO_WARPS", "SKC_MO_TOL", "SKC_MO_HEADCAP"):
+    for k in ("SKC_MO_GROUP", "SKC_MO_WARPS", "SKC_MO_TOL", "SKC_MO_HEADCAP", "SKC_MO_WIDE"):
         os.environ.pop(k, None)
     os.environ.update(env or {})
     dev = pkg.SkinDevice(0)
@@ -40,6 +40,7 @@ def frame(pkg, scene_path, mode, reps=3, counters=True, env=None):
             c = dev.camera_pass_resident(0, n, hs.maxerror, hs.mix, counters=True)
             st = dev.mo_table_stats()
             st["counters7"] = [int(x) for x in c]
+            st["group_hist"] = dev.mo_group_histogram()
         return dict(ms=ms, L=L, rgb=rgb, stats=st, n_pts=n_pts, n=n)
     finally:
         hs.close()
@@ -61,12 +62,14 @@ def main():
            "L_row_rel_err_max": float(err.max()), "L_row_rel_err_p999": float(np.quantile(err, 0.999)), "L_row_rel_err_mean": float(err.mean()),
            "image_rmse_rel": rmse, "stats_exact": a["stats"], "stats_compact": b["stats"]}
     out["variants"] = {}
-    for name, env in (("tol3e-5", {"SKC_MO_TOL": "3e-5"}), ("tol5e-5", {"SKC_MO_TOL": "5e-5"}), ("tol8e-5", {"SKC_MO_TOL": "8e-5"})):
+    variants = [("tol3e-5", {"SKC_MO_TOL": "3e-5"}), ("tol5e-5", {"SKC_MO_TOL": "5e-5"}), ("tol8e-5", {"SKC_MO_TOL": "8e-5"})]
+    for name, env in variants:
         if os.environ.get("MO_AB_VARIANTS", "1") == "0":
             break
         c = frame(pkg, scene, "compact", counters=True, env=env)
         e2 = np.abs(La - c["L"].astype(np.float64)).max(axis=1)[lit] / scale[lit]
-        out["variants"][name] = {"mo_ms": c["ms"], "L_row_rel_err_max": float(e2.max()), "stats": c["stats"]}
+        out["variants"][name] = {"mo_ms": c["ms"], "L_row_rel_err_max": float(e2.max()), "stats": c["stats"],
+                                 "identical_to_default": bool(np.array_equal(c["L"].view(np.uint32), b["L"].view(np.uint32)))}
     print(json.dumps(out, indent=1))
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(out, open(os.path.join(ROOT, "gpurun_out", "mo_table_ab.json"), "w"), indent=1)
