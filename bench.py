@@ -107,9 +107,10 @@ def reference_arm(args):
     if not os.path.exists(drv):
         emit({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (oracle/build_ref.sh needs /root/reference)"})
         return
-    # A full-scale step of the reference costs ~2 minutes on 16 cores (octree build ~55 s of it single-threaded, render loop
-    # ~1000 core-seconds), so the timed arm runs a bounded 1/16-scale sample of the same scene; --full-scale times whole
-    # frames of scenes/skin.scene instead (one such step is committed as profiles/r2_reference_full_step.json).
+    # A full-scale step of the reference costs 24.5 s on the B200 box's 16 host cores (preprocess 14.8 s, render 9.6 s:
+    # profiles/r2_reference_full_step.json) -- 10 minutes for the driver's 25 steps -- so the timed arm runs a bounded
+    # 1/16-scale sample of the same scene (its points/s is 14 % HIGHER than at full scale: the comparison errs in the
+    # reference's favour); --full-scale times whole frames of scenes/skin.scene instead.
     sample = os.path.join(ROOT, "scenes", "skin.scene" if args.full_scale else "skin_sample16.scene")
     cores = os.cpu_count() or 1
     out = subprocess.run([drv, "bench", sample, "--ncores", str(cores), "--steps", str(args.steps), "--warmup", str(args.warmup)],

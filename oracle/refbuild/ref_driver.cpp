@@ -781,11 +781,72 @@ static int runBench(int argc, char **argv) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------
+// trace mode: the reference's BVHAccel::Intersect / IntersectP (accelerators/bvh.cpp:383-502) on a file of rays, timed.
+//   ref_driver trace <scene.txt> <rays.bin> [--any] [--ncores N] [--reps R]
+// rays.bin: DrvRay records (o[3], d[3], mint, maxt).  The rays are cut into 4096-ray tasks for the reference's own task
+// system.  Prints "rays N hits H seconds s" per repetition.
+// ---------------------------------------------------------------------------
+class TraceTask : public Task {
+public:
+    TraceTask(const Scene *sc, const DrvRay *r, size_t n, bool any, long *hits) : scene(sc), rays(r), n(n), any(any), hits(hits) {}
+    void Run() override {
+        long h = 0;
+        for (size_t i = 0; i < n; ++i) {
+            const DrvRay &d = rays[i];
+            Ray ray(Point(d.o[0], d.o[1], d.o[2]), Vector(d.d[0], d.d[1], d.d[2]), d.mint, d.maxt);
+            if (any) h += scene->IntersectP(ray) ? 1 : 0;
+            else { Intersection is; h += scene->Intersect(ray, &is) ? 1 : 0; }
+        }
+        *hits = h;
+    }
+private:
+    const Scene *scene; const DrvRay *rays; size_t n; bool any; long *hits;
+};
+
+static int runTrace(int argc, char **argv) {
+    if (argc < 4) { fprintf(stderr, "usage: ref_driver trace <scene.txt> <rays.bin> [--any] [--ncores N] [--reps R]\n"); return 2; }
+    int ncores = 0, reps = 1; bool any = false;
+    for (int i = 4; i < argc; ++i) {
+        if (!strcmp(argv[i], "--ncores")) ncores = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--reps")) reps = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--any")) any = true;
+    }
+    Options options; options.nCores = ncores; options.quiet = true;
+    pbrtInit(options);
+    SceneDesc sd = parseScene(argv[2]);
+    buildScene(sd, "/dev/null");
+    renderOptions->MakeRenderer();
+    Scene *scene = renderOptions->MakeScene();
+    std::ifstream f(argv[3], std::ios::binary | std::ios::ate);
+    if (!f) { fprintf(stderr, "cannot read %s\n", argv[3]); return 1; }
+    const size_t n = (size_t)f.tellg() / sizeof(DrvRay);
+    std::vector<DrvRay> rays(n);
+    f.seekg(0); f.read((char *)rays.data(), n * sizeof(DrvRay));
+    printf("cores %d\n", NumSystemCores());
+    const size_t chunk = 4096, nTasks = (n + chunk - 1) / chunk;
+    for (int r = 0; r < reps; ++r) {
+        std::vector<long> hits(nTasks, 0);
+        vector<Task *> tasks;
+        for (size_t t = 0; t < nTasks; ++t) tasks.push_back(new TraceTask(scene, rays.data() + t * chunk, std::min(chunk, n - t * chunk), any, &hits[t]));
+        double t0 = now_s();
+        EnqueueTasks(tasks); WaitForAllTasks();
+        double dt = now_s() - t0;
+        for (Task *t : tasks) delete t;
+        long h = 0; for (long v : hits) h += v;
+        printf("rays %zu hits %ld seconds %.4f %s\n", n, h, dt, any ? "any" : "closest");
+        fflush(stdout);
+    }
+    TasksCleanup();
+    return 0;
+}
+
 int main(int argc, char **argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver scene|mpc|bench ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver scene|mpc|bench|trace ...\n"); return 2; }
     if (!strcmp(argv[1], "bench")) return runBench(argc, argv);
     if (!strcmp(argv[1], "scene")) return runScene(argc, argv);
     if (!strcmp(argv[1], "mpc")) return runMPC(argc, argv);
+    if (!strcmp(argv[1], "trace")) return runTrace(argc, argv);
     fprintf(stderr, "unknown mode %s\n", argv[1]);
     return 2;
 }

@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : (SPLI
 // reference's exact lookup instead: from the table head held in shared memory, or from the global table (the far,
 // noisy part of the tables: ~1 in 8 lookups).  No transposition at the end: lane = wavelength is the output layout.
 #define MOL_STACK 256          // (node, mask) entries: 1 + 7 * levels, levels <= 36
-#define MOL_WARP_BYTES (32 * 32 * 4 + 32 * 16 + MOL_STACK * 8)
+#define MOL_WARP_BYTES (32 * 32 * 4 + 32 * 32 + MOL_STACK * 8)
 #define MOL_MAX_WARPS 28
 
 struct MoCompactDev {
@@ -413,9 +413,9 @@ struct MoCompactDev {
 template <bool COUNT, bool HEADS, int G>
 __device__ __forceinline__ void molGroup(const float4 *rec, float e, float *acc, const float *sRows, const float *sHeads,
                                          const float2 *myPairs, int lane, const float4 &lp, uint32_t hoff, float lenM1L, uint32_t (&gc)[3]) {
-    float4 a[G];          // {d2, scale, t, cell row offset | accumulator row offset << 16}: one 16-byte broadcast read per record
+    float4 a[G], w[G];    // {d2, scale, cell row offset, accumulator row offset} and the four Lagrange weights: two 16-byte broadcast reads per record
 #pragma unroll
-    for (int g = 0; g < G; ++g) a[g] = rec[g];
+    for (int g = 0; g < G; ++g) { a[g] = rec[2 * g]; w[g] = rec[2 * g + 1]; }
     float f[G]; bool inC[G], ex[G], gl[G]; float2 v[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
@@ -432,18 +432,26 @@ __device__ __forceinline__ void molGroup(const float4 *rec, float e, float *acc,
         if (ex[g] && !gl[g]) { const uint32_t seg = (uint32_t)f[g]; v[g].x = sHeads[hoff + seg]; v[g].y = sHeads[hoff + seg + 1]; }
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-        const int bits = __float_as_int(a[g].w);
-        const float *r = sRows + (bits & 0xffff) + lane;
-        float w[4];
-        mocWeights(a[g].z, w);
-        const float rdC = mocCubic(w, r[0], r[32], r[64], r[96]);
+        const float *r = sRows + __float_as_int(a[g].z) + lane;
+        const float ww[4] = {w[g].x, w[g].y, w[g].z, w[g].w};
+        const float rdC = mocCubic(ww, r[0], r[32], r[64], r[96]);
         const float t = f[g] - (float)(uint32_t)f[g];
         const float rdE = (1.f - t) * v[g].x + t * v[g].y;          // sampleProfile's own arithmetic (core/multipole.cpp:60-73)
         const float rd = inC[g] ? rdC : rdE;                        // rdE is 0 when neither path applies
         if (COUNT) { gc[0] += (inC[g] || ex[g]); gc[1] += (ex[g] && !gl[g]); gc[2] += gl[g]; }
-        float *ap = acc + (bits >> 16) + lane;
+        float *ap = acc + __float_as_int(a[g].w) + lane;
         *ap += (rd * e) * a[g].y;
     }
+}
+
+// an accepting lane's record: everything about (hit, cluster) that does not depend on the wavelength, computed once by the hit's lane
+__device__ __forceinline__ void molRecord(float4 *rec, int slot, const MoCompactParams &P, int kMax32, float d2, float scale, int lane) {
+    int k; float t;
+    mocCell(P, d2, k, t);
+    float w[4];
+    mocWeights(t, w);
+    rec[2 * slot] = make_float4(d2, scale, __int_as_float(min(k * 32, kMax32)), __int_as_float(lane * 32));
+    rec[2 * slot + 1] = make_float4(w[0], w[1], w[2], w[3]);
 }
 
 // sums `e * Rd(d2) * scale` into the accumulator rows of the cnt hits whose records lie densely in rec[0 .. cnt)
@@ -452,9 +460,9 @@ __device__ __forceinline__ void molContribute(int cnt, float e, const float4 *re
                                               const MoTables &T, int lane, const float4 &lp, uint32_t hoff, float lenM1L, uint32_t (&gc)[3]) {
     const float2 *myPairs = T.pairs + (size_t)lane * T.len;
     int i = 0;
-    for (; i + 4 <= cnt; i += 4) molGroup<COUNT, HEADS, 4>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
-    if (cnt & 2) { molGroup<COUNT, HEADS, 2>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc); i += 2; }
-    if (cnt & 1) molGroup<COUNT, HEADS, 1>(rec + i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
+    for (; i + 4 <= cnt; i += 4) molGroup<COUNT, HEADS, 4>(rec + 2 * i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
+    if (cnt & 2) { molGroup<COUNT, HEADS, 2>(rec + 2 * i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc); i += 2; }
+    if (cnt & 1) molGroup<COUNT, HEADS, 1>(rec + 2 * i, e, acc, sRows, sHeads, myPairs, lane, lp, hoff, lenM1L, gc);
 }
 
 template <bool COUNT, bool PERM, bool HEADS, int MAXW>
@@ -468,8 +476,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     char *wb = reinterpret_cast<char *>(sHeads + C.headFloats) + (size_t)warp * MOL_WARP_BYTES;
     float *acc = reinterpret_cast<float *>(wb);                          // [32 hits][32 wavelengths]
-    float4 *rec = reinterpret_cast<float4 *>(wb + 32 * 32 * 4);          // [32 records]
-    uint2 *stack = reinterpret_cast<uint2 *>(wb + 32 * 32 * 4 + 32 * 16);
+    float4 *rec = reinterpret_cast<float4 *>(wb + 32 * 32 * 4);          // [32 records] of two float4
+    uint2 *stack = reinterpret_cast<uint2 *>(wb + 32 * 32 * 4 + 32 * 32);
     {   // the compact rows and the table heads -> shared memory (float4 copies; both sizes are multiples of 4 floats)
         const float4 *src = reinterpret_cast<const float4 *>(C.rows);
         for (uint32_t i = threadIdx.x; i < C.rowFloats / 4; i += blockDim.x) molSmem[i] = __ldg(src + i);
@@ -532,11 +540,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
             if (am) {
                 if (COUNT) { wc[2] += __popc(am); ++grp[0]; const int A = __popc(am); hist[A >= 28 ? 3 : A >= 16 ? 2 : A >= 8 ? 1 : 0] += A; }
                 const float e = __ldg(tr.Et + (size_t)ent.x * SKC_EPAD + lane);
-                if (addC) {     // records densely, in hit order
-                    int k; float t;
-                    mocCell(C.P, d2, k, t);
-                    rec[__popc(am & lanesBelow)] = make_float4(d2, 1.f, t, __int_as_float(min(k * 32, kMax32) | (lane << 21)));
-                }
+                if (addC) molRecord(rec, __popc(am & lanesBelow), C.P, kMax32, d2, 1.f, lane);     // records densely, in hit order
                 __syncwarp();
                 molContribute<COUNT, HEADS>(__popc(am), e, rec, acc, sRows, sHeads, T, lane, lp, hoff, lenM1L, gc);
                 __syncwarp();
@@ -555,11 +559,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
                         if (pm) {
                             if (COUNT) { wc[3] += __popc(pm); ++grp[1]; const int A = __popc(pm); hist[4 + (A >= 28 ? 3 : A >= 16 ? 2 : A >= 8 ? 1 : 0)] += A; }
                             const float e = __ldg(tr.leafE + (size_t)slot * SKC_EPAD + lane);
-                            if (c) {
-                                int k; float t;
-                                mocCell(C.P, q2, k, t);
-                                rec[__popc(pm & lanesBelow)] = make_float4(q2, pa.w, t, __int_as_float(min(k * 32, kMax32) | (lane << 21)));
-                            }
+                            if (c) molRecord(rec, __popc(pm & lanesBelow), C.P, kMax32, q2, pa.w, lane);
                             __syncwarp();
                             molContribute<COUNT, HEADS>(__popc(pm), e, rec, acc, sRows, sHeads, T, lane, lp, hoff, lenM1L, gc);
                             __syncwarp();

@@ -103,8 +103,23 @@ def main():
             t0 = time.time()
             subprocess.run([drv, "mpc", inp, outp], check=True, stdout=subprocess.DEVNULL)
             sec = time.time() - t0
+            # the same sets again on the device, table against table (north_star: 1e-5 of each entry)
+            sel_specs = [specs[2 * s + j] for s in pick for j in (0, 1)]
+            d2, R, T, tot = dev.profile_batch(sel_specs, [2] * len(pick), [opts[s] for s in pick], resample=True)
+            raw = np.fromfile(outp, np.uint8)
+            worst, off, d2_equal = 0.0, 0, True
+            for i in range(len(pick)):
+                ln = int(raw[off:off + 4].view(np.uint32)[0]); tt = raw[off + 4:off + 12].view(np.float32); off += 12
+                body = raw[off:off + 12 * ln].view(np.float32).reshape(3, ln); off += 12 * ln
+                assert ln == R.shape[1]
+                d2_equal = d2_equal and bool(np.array_equal(body[0], d2[i]))
+                for got, ref in ((R[i], body[1]), (T[i], body[2])):
+                    ref64 = ref.astype(np.float64)
+                    worst = max(worst, float((np.abs(got - ref64) / np.maximum(np.abs(ref64), np.abs(ref64).max() * 1e-30)).max()))
+                worst = max(worst, float(np.abs(tot[i] - tt).max() / np.abs(tt).max()))
         out["reference_cpu"] = {"profiles": int(args.reference), "seconds": sec, "s_per_profile_one_core": sec / args.reference,
-                                "speedup_vs_one_core": (sec / args.reference) / (ms / n * 1e-3)}
+                                "speedup_vs_one_core": (sec / args.reference) / (ms / n * 1e-3),
+                                "tables_max_rel_err_vs_device": worst, "d2_grids_bit_equal": d2_equal, "within_1e-5": bool(worst < 1e-5)}
     print(json.dumps(out, indent=1))
     dev.close()
 

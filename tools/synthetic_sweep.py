@@ -58,7 +58,32 @@ def timed(dev, fn, stage, reps=3):
     return float(np.median(ms))
 
 
-def bvh_bench(pkg, dev, scene, name, n_rays, reps):
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+
+
+def ref_trace(scene_path, rays, any_hit, tmp):
+    """The reference's own Scene::Intersect / IntersectP on the same rays, all host cores (oracle/_ref/ref_driver trace)."""
+    import subprocess
+    rp = os.path.join(tmp, "rays.bin")
+    np.ascontiguousarray(rays, np.float32).tofile(rp)
+    out = subprocess.run([REF_DRIVER, "trace", scene_path, rp, "--reps", "2"] + (["--any"] if any_hit else []), capture_output=True, text=True).stdout
+    cores = int([l for l in out.splitlines() if l.startswith("cores")][0].split()[1])
+    rows = [l.split() for l in out.splitlines() if l.startswith("rays")]
+    sec = min(float(r[5]) for r in rows)
+    return {"cores": cores, "rays": int(rows[0][1]), "hits": int(rows[0][3]), "seconds": sec, "Mrays_per_s": int(rows[0][1]) / sec / 1e6}
+
+
+def ref_mo(scene_path):
+    """The reference's Preprocess + a camera pass that evaluates only the subsurface term (ref_driver bench --sss-only), all host cores."""
+    import subprocess
+    out = subprocess.run([REF_DRIVER, "bench", scene_path, "--sss-only", "--steps", "1", "--warmup", "0"], capture_output=True, text=True).stdout
+    cores = int([l for l in out.splitlines() if l.startswith("cores")][0].split()[1])
+    w = [l for l in out.splitlines() if l.startswith("step")][0].split()
+    return {"cores": cores, "points": int(w[3]), "samples": int(w[5]), "preprocess_s": float(w[7]), "camera_pass_sss_only_s": float(w[9]),
+            "Mhits_per_s_incl_camera_rays": int(w[5]) / float(w[9]) / 1e6}
+
+
+def bvh_bench(pkg, dev, scene, name, n_rays, reps, ref_scene=None, tmp=None):
     PEAK = peak()
     out = {"mesh": name, "triangles": scene.n_tris, "bvh_nodes": scene.n_nodes, "bvh_bytes": int(scene.n_nodes * 32 + scene.n_prims * 48)}
     bmin = scene.P.min(axis=0); bmax = scene.P.max(axis=0)          # the mesh's bound (the emitters sit far outside it)
@@ -71,6 +96,12 @@ def bvh_bench(pkg, dev, scene, name, n_rays, reps):
             byts = n_rays * per_ray + 32 * int(c[0]) + 48 * int(c[1])
             out[dist + "_" + mode] = {"rays": n_rays, "hit_fraction": frac_hit, "ms": ms, "Mrays_per_s": n_rays / ms / 1e3, "slab_tests_per_ray": int(c[0]) / n_rays,
                                       "prim_tests_per_ray": int(c[1]) / n_rays, "algorithmic_GBps": byts / ms / 1e6, "frac_of_hbm_peak": byts / ms / 1e6 / PEAK}
+            if ref_scene:       # the same rays (the first 4 M of them) through the reference on the host cores; the hit counts must agree
+                m = min(n_rays, 4 << 20)
+                cpu = ref_trace(ref_scene, rays[:m], any_hit, tmp)
+                got = int(np.count_nonzero(hits[:m] != 0)) if any_hit else int(np.count_nonzero(hits["hit"][:m] != 0))
+                cpu["hit_count_equals_device"] = bool(cpu["hits"] == got)
+                out[dist + "_" + mode]["cpu_reference"] = cpu
     return out
 
 
@@ -83,7 +114,10 @@ def main():
     ap.add_argument("--hits", type=int, default=4 << 20)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--reference", action="store_true", help="time the reference (oracle/_ref/ref_driver) beside the device: the first Mo sweep size and every BVH case")
     args = ap.parse_args()
+    if args.reference and not os.path.exists(REF_DRIVER):
+        sys.exit("--reference: oracle/_ref/ref_driver is not built")
     if args.quick:
         args.targets, args.level, args.bvh_levels, args.rays, args.hits = "2e5", 5, "5", 1 << 18, 1 << 16
     import __graft_entry__ as ge
@@ -139,6 +173,11 @@ def main():
                                 "algorithmic_GBps": byts / ms / 1e6, "frac_of_hbm_peak": byts / ms / 1e6 / PEAK,
                                 "table_gathers_per_s_G": int(cnt[6]) / ms / 1e6})
                 row["runs"].append(run)
+        if args.reference and not result["mo_sweep"]:
+            # the same icosphere, point set and camera through the reference; its irradiance comes from the scene's two lights
+            # instead of the analytic field (the octree walk depends on positions and areas only, not on E)
+            rp = syn.write_scene(os.path.join(tmp, "ref"), args.level, min_dist=md, film=film, spp=1)
+            row["cpu_reference_maxError_0.1_spp1"] = ref_mo(rp)
         result["mo_sweep"].append(row)
         print("mo sweep: %d points done (%.0f s)" % (n_pts, time.time() - t0), file=sys.stderr)
 
@@ -157,14 +196,20 @@ def main():
     # ---------------------------------------------------------------- BVH: AggregateTest rays on meshes of growing size
     head = pkg.HostScene(os.path.join(ROOT, "scenes", "skin.scene"))
     head.upload(dev)
-    result["bvh"].append(bvh_bench(pkg, dev, head, "head (scenes/skin.scene)", args.rays, args.reps))
+    head_ref = None
+    if args.reference:      # skin.scene with a short profile: only the mesh matters to the ray loop
+        head_ref = os.path.join(tmp, "head_ref.scene")
+        src = open(os.path.join(ROOT, "scenes", "skin.scene")).read().replace(" layers ", " desiredlength 32 layers ").replace("\nmesh ", "\nmesh " + os.path.join(ROOT, "scenes") + "/")
+        open(head_ref, "w").write(src)
+    result["bvh"].append(bvh_bench(pkg, dev, head, "head (scenes/skin.scene)", args.rays, args.reps, head_ref, tmp))
     head.close()
     for lvl in [int(x) for x in args.bvh_levels.split(",")]:
         t1 = time.time()
-        sc = pkg.HostScene(syn.write_scene(tmp, lvl, film=64))
+        sp_path = syn.write_scene(tmp, lvl, film=64, desired_length=32 if args.reference else 512)
+        sc = pkg.HostScene(sp_path)
         build_s = time.time() - t1
         sc.upload(dev)
-        r = bvh_bench(pkg, dev, sc, "icosphere level %d" % lvl, args.rays, args.reps)
+        r = bvh_bench(pkg, dev, sc, "icosphere level %d" % lvl, args.rays, args.reps, sp_path if args.reference else None, tmp)
         r["host_bvh_build_s"] = round(build_s, 2)
         result["bvh"].append(r)
         sc.close()
