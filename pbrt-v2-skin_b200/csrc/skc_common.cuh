@@ -67,7 +67,7 @@ struct skc_ctx {
     uint32_t *mocHeadOff = nullptr;// [32]
     uint32_t mocRowCount = 0, mocHeadFloats = 0;
     float mocInvA = 0.f, mocM = 0.f;
-    int moTable = 1;               // 1 = compact table in shared memory + exact fallback (k_mo_lambda), 0 = exact tables only (k_mo_packet); env SKC_MO_TABLE=exact|compact
+    int moTable = 1;               // 1 = k_mo_lambda (compact table in shared memory + exact fallback) when the table's windows cover enough of the tables (MOC_MIN_COVERAGE), else k_mo_packet; 0 = always k_mo_packet, 2 = always k_mo_lambda; env SKC_MO_TABLE=exact|auto|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
     uint64_t moHist[8] = {0};
     uint64_t moGroups[2] = {0, 0};       // last counted pass: (cluster, packet) and (leaf point, packet) accept groups

@@ -82,7 +82,7 @@ extern "C" skc_ctx *skc_create(int device) {
     if (const char *k = getenv("SKC_MO_GROUP")) ctx->moGroup = atoi(k);
     if (const char *k = getenv("SKC_MO_WARPS")) ctx->moWarps = atoi(k);
     if (const char *k = getenv("SKC_BVH_WIDE")) ctx->bvhWideOn = atoi(k) != 0;
-    if (const char *k = getenv("SKC_MO_TABLE")) ctx->moTable = strcmp(k, "exact") != 0;
+    if (const char *k = getenv("SKC_MO_TABLE")) ctx->moTable = !strcmp(k, "exact") ? 0 : !strcmp(k, "compact") ? 2 : 1;
     if (const char *k = getenv("SKC_MO_TOL")) { float t = (float)atof(k); if (t > 0.f) ctx->mocTol = t; }
     if (const char *k = getenv("SKC_MO_SORT")) ctx->moSort = atoi(k);
     if (const char *k = getenv("SKC_MO_SPLIT")) ctx->moSplit = atoi(k) == 1 ? 1 : atoi(k) == 2 ? 2 : atoi(k) == 4 ? 4 : 0;

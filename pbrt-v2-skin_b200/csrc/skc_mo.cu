@@ -728,6 +728,16 @@ static const uint32_t *moSortHits(skc_ctx *ctx, const float *p3Dev, uint64_t str
     return dv.Current();
 }
 
+// k_mo_lambda or k_mo_packet?  The compact table pays when most lookups fall inside its verified windows.  Where the windows are
+// short -- profiles whose near range is sampled too coarsely by the reference's own table to be smooth at 1e-5, e.g. LayeredSkin
+// at its defaults on a unit sphere: coverage 0.11, 82 % of the lookups exact -- lane = wavelength is the wrong layout for the
+// remaining gathers (72 vs 47 ms there), while skin.scene has coverage 0.62 and runs 42 vs 60 ms.
+#define MOC_MIN_COVERAGE 0.35
+static bool molWanted(const skc_ctx *ctx) {
+    if (!ctx->moTable || !ctx->mocRows || 7 * (int)ctx->otLevels + 1 > MOL_STACK) return false;
+    return ctx->moTable == 2 || ctx->mocCoverage >= MOC_MIN_COVERAGE;
+}
+
 static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride,
                     uint64_t n, float maxError, float *MoDev, unsigned long long *cntDev = nullptr, const LiEpilogue *li = nullptr,
                     bool callerOrder = true) {
@@ -736,7 +746,7 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (!n) return 0;
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
-    if (ctx->moPacket && ctx->moTable && ctx->mocRows && 7 * (int)ctx->otLevels + 1 <= MOL_STACK) {
+    if (ctx->moPacket && molWanted(ctx)) {
         if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
         MoCompactDev C; C.rows = ctx->mocRows; C.heads = ctx->mocHeads; C.lam = ctx->mocLam; C.headOff = ctx->mocHeadOff;
         C.rowFloats = ctx->mocRowCount * 32; C.headFloats = ctx->mocHeadFloats;
@@ -1076,7 +1086,7 @@ extern "C" int skc_mo_static(skc_ctx *ctx, const float *p3, uint64_t n, float ma
     MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
     const LiEpilogue ep{nullptr, nullptr, nullptr, 0.f, nullptr};
-    if (ctx->moTable && ctx->mocRows && 7 * (int)ctx->otLevels + 1 <= MOL_STACK) {
+    if (molWanted(ctx)) {
         MoCompactDev C; C.rows = ctx->mocRows; C.heads = ctx->mocHeads; C.lam = ctx->mocLam; C.headOff = ctx->mocHeadOff;
         C.rowFloats = ctx->mocRowCount * 32; C.headFloats = ctx->mocHeadFloats;
         C.P.invA = ctx->mocInvA; C.P.cellsPerBinade = ctx->mocM; C.P.K = (int)ctx->mocRowCount - 3;

@@ -19,6 +19,7 @@
 //                     data independent) and its lower_bound + fp32 lerp
 #include <algorithm>
 #include <map>
+#include <thread>
 #include <vector>
 #include <math.h>
 #include <string.h>
@@ -150,8 +151,10 @@ __global__ void k_layer_profile(const DipoleSet *__restrict__ dsAll, uint32_t G,
 }
 
 // Z[N][N] <- ScaleAndShift(grid, center) (numutil.h:192-204): grid cell (i,j) -> ((i-c) mod N, (j-c) mod N)
+// Only the G rows that hold grid cells are written (blockIdx.y counts from the first of them, (N - c) mod N): the other rows
+// are zero by construction and nothing reads them -- the first row pass skips them and the transpose substitutes zeros.
 __global__ void k_pack(const double2 *__restrict__ z, uint32_t G, uint32_t N, double2 *__restrict__ Z) {
-    uint32_t jj = blockIdx.x * blockDim.x + threadIdx.x, ii = blockIdx.y;
+    uint32_t jj = blockIdx.x * blockDim.x + threadIdx.x, ii = (N - (G - 1) / 2 + blockIdx.y) & (N - 1);
     if (jj >= N) return;
     z += (size_t)blockIdx.z * G * G; Z += (size_t)blockIdx.z * N * N;
     uint32_t c = (G - 1) / 2;
@@ -214,14 +217,100 @@ __global__ void __launch_bounds__(512) k_fft_rows(double2 *__restrict__ Z, uint3
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) row[i] = s[fftSlot(i)];
 }
 
-__global__ void k_transpose(const double2 *__restrict__ in, uint32_t N, double2 *__restrict__ out) {
+// ---- N = 2048 (desiredLength 512, the size BASELINE.json configs[4] and skin.pbrt use): the same radix-2 DIT butterflies in
+// the same order (bit-identical results), re-tiled so that a row crosses shared memory twice instead of five times:
+//   pass 1 = stages 1..4 on 16 values that come STRAIGHT FROM GLOBAL MEMORY: position i of the bit-reversed sequence holds
+//            x[brev(i)], so the 16 inputs of item brev7(j) are x[j + brev4(k) * 128] -- for a fixed k the 128 threads of a row read
+//            128 consecutive elements (coalesced), and no bit-reversed scatter through shared memory is needed;
+//   pass 2 = stages 5..8, 16 values per thread, shared memory in place;
+//   pass 3 = stages 9..11 on 8 values, whose results are positions pos + k * 256 of the natural-order output: written straight
+//            to global memory, coalesced.
+// 128 threads per row, two rows per CTA (independent: named barriers), 33 KB of shared memory per row with the index padding
+// i + (i >> 7) + (i >> 10), which makes every 16-byte access pattern of the three passes conflict-free per quarter-warp.
+// Shared-memory traffic per row: 128 KB + 58 KB of twiddles (k_fft_rows: 320 KB + 110 KB).
+#define FFT2_N 2048u
+#define FFT2_SLOTS 2080u      // >= slot(2047) + 1 = 2064, kept a multiple of 16
+__device__ __forceinline__ uint32_t fft2Slot(uint32_t i) { return i + (i >> 7) + (i >> 10); }
+
+template <int R>
+__device__ __forceinline__ void fftButterflies(double2 (&v)[1 << R], uint32_t pos, uint32_t half, uint32_t st, uint32_t N,
+                                               const double2 *__restrict__ tw, int inverse) {
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+        const int hs = 1 << q;
+        const double2 *stage = tw + (N >> 1) + (1u << (st + q - 1)) - 1u;       // this stage's own contiguous copy of its twiddles
+#pragma unroll
+        for (int k = 0; k < (1 << R); ++k) {
+            if (k & hs) continue;
+            double2 w = __ldg(&stage[pos + (k & (hs - 1)) * half]);
+            if (inverse) w.y = -w.y;
+            double2 a = v[k], c = v[k + hs];
+            double2 t = make_double2(w.x * c.x - w.y * c.y, w.x * c.y + w.y * c.x);
+            v[k] = make_double2(a.x + t.x, a.y + t.y);
+            v[k + hs] = make_double2(a.x - t.x, a.y - t.y);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fft_rows2048(double2 *__restrict__ Z, const double2 *__restrict__ tw, int inverse,
+                                                      uint32_t rowStart, uint32_t nRows) {
+    constexpr uint32_t N = FFT2_N;
+    extern __shared__ double2 s2[];
+    const uint32_t sub = threadIdx.x >> 7, t = threadIdx.x & 127;
+    const uint32_t r = blockIdx.x * 2 + sub;
+    if (r >= nRows) return;                  // the whole 128-thread half leaves; the barriers below are per half
+    double2 *s = s2 + sub * FFT2_SLOTS;
+    double2 *row = Z + ((size_t)blockIdx.y * N + ((rowStart + r) & (N - 1))) * N;
+    const uint32_t barId = 1 + sub;
+    {
+        double2 v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = row[t + (uint32_t)(((k & 1) << 3) | ((k & 2) << 1) | ((k & 4) >> 1) | ((k & 8) >> 3)) * 128u];
+        fftButterflies<4>(v, 0u, 1u, 1u, N, tw, inverse);
+        const uint32_t base = (__brev(t) >> 25) * 16u;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s[fft2Slot(base + k)] = v[k];
+    }
+    asm volatile("bar.sync %0, 128;" ::"r"(barId) : "memory");
+    {
+        double2 v[16];
+        const uint32_t pos = t & 15u, base = (t >> 4) * 256u + pos;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = s[fft2Slot(base + k * 16u)];
+        fftButterflies<4>(v, pos, 16u, 5u, N, tw, inverse);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s[fft2Slot(base + k * 16u)] = v[k];
+    }
+    asm volatile("bar.sync %0, 128;" ::"r"(barId) : "memory");
+#pragma unroll 1
+    for (uint32_t pos = t; pos < 256u; pos += 128u) {
+        double2 u[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) u[k] = s[fft2Slot(pos + k * 256u)];
+        fftButterflies<3>(u, pos, 256u, 9u, N, tw, inverse);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) row[pos + k * 256u] = u[k];
+    }
+}
+
+// mode 0: all of it.  mode 1 (forward transform): input rows outside the band [bandStart, bandStart + G) mod N are zero and are
+// not read.  mode 2 (inverse): only the output rows inside the band are needed (the last row pass and k_unpack touch no others):
+// the other input columns are neither read nor written.
+__global__ void k_transpose(const double2 *__restrict__ in, uint32_t N, double2 *__restrict__ out, int mode, uint32_t bandStart, uint32_t G) {
     __shared__ double2 tile[32][33];
     in += (size_t)blockIdx.z * N * N; out += (size_t)blockIdx.z * N * N;
     uint32_t x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * 32;
-    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) tile[k][threadIdx.x] = in[(size_t)(y0 + k) * N + x];
+    const bool xIn = mode != 2 || ((x - bandStart) & (N - 1)) < G;
+    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) {
+        const bool yIn = mode != 1 || ((y0 + k - bandStart) & (N - 1)) < G;
+        tile[k][threadIdx.x] = (xIn && yIn) ? in[(size_t)(y0 + k) * N + x] : make_double2(0., 0.);
+    }
     __syncthreads();
     uint32_t xo = blockIdx.y * 32 + threadIdx.x, yo0 = blockIdx.x * 32;
-    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) out[(size_t)(yo0 + k) * N + xo] = tile[threadIdx.x][k];
+    for (uint32_t k = threadIdx.y; k < 32; k += blockDim.y) {
+        if (mode == 2 && ((yo0 + k - bandStart) & (N - 1)) >= G) continue;
+        out[(size_t)(yo0 + k) * N + xo] = tile[threadIdx.x][k];
+    }
 }
 
 // adding equations in the frequency domain (MultipoleProfileCalculator.cpp:253-280).  R and T are real, so the
@@ -240,20 +329,30 @@ __device__ __forceinline__ void splitSpectra(double2 zk, double2 zm, double2 &FR
     double dx = zk.x - zm.x, dy = zk.y + zm.y;              // Z(k) - conj Z(-k)
     FT = make_double2(0.5 * dy, -0.5 * dx);                // divided by 2i
 }
-__global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restrict__ Z2, uint32_t N, double2 *__restrict__ W) {
-    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, a = blockIdx.y;
-    if (b >= N) return;
-    Z1 += (size_t)blockIdx.z * N * N; Z2 += (size_t)blockIdx.z * N * N; W += (size_t)blockIdx.z * N * N;
-    size_t i = (size_t)a * N + b, j = (size_t)((N - a) & (N - 1)) * N + ((N - b) & (N - 1));
+__device__ __forceinline__ double2 addingAt(double2 z1k, double2 z1m, double2 z2k, double2 z2m) {
     double2 R1, T1, R2, T2;
-    splitSpectra(Z1[i], Z1[j], R1, T1);
-    splitSpectra(Z2[i], Z2[j], R2, T2);
+    splitSpectra(z1k, z1m, R1, T1);
+    splitSpectra(z2k, z2m, R2, T2);
     double2 one = cmul(R2, R1);
     one = make_double2(1. - one.x, -one.y);
     double2 R12 = cdiv(cmul(cmul(T1, R2), T1), one);
     R12.x += R1.x; R12.y += R1.y;
     double2 T12 = cdiv(cmul(T1, T2), one);
-    W[i] = make_double2(R12.x - T12.y, R12.y + T12.x);
+    return make_double2(R12.x - T12.y, R12.y + T12.x);
+}
+// One thread per PAIR of mirror frequencies {k, -k}: W(k) needs Z(k) and Z(-k) of both layers and W(-k) needs the same four
+// values, so each element is read once instead of twice.  blockIdx.y = row a in [0, N/2]; rows 0 and N/2 are their own mirrors
+// (there the pair partner is the mirrored column of the same row and only columns <= N/2 start a pair).
+__global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restrict__ Z2, uint32_t N, double2 *__restrict__ W) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x, a = blockIdx.y;
+    if (b >= N) return;
+    const uint32_t am = (N - a) & (N - 1), bm = (N - b) & (N - 1);
+    if (am == a && b > bm) return;
+    Z1 += (size_t)blockIdx.z * N * N; Z2 += (size_t)blockIdx.z * N * N; W += (size_t)blockIdx.z * N * N;
+    const size_t i = (size_t)a * N + b, j = (size_t)am * N + bm;
+    const double2 z1i = Z1[i], z1j = Z1[j], z2i = Z2[i], z2j = Z2[j];
+    W[i] = addingAt(z1i, z1j, z2i, z2j);
+    if (j != i) W[j] = addingAt(z1j, z1i, z2j, z2i);
 }
 
 // ScaleAndShiftReversed (numutil.h:205-217) of the inverse transform, scaled by 1/N^2 (:132-139)
@@ -377,12 +476,23 @@ static int fft2d(skc_ctx *ctx, ProfileWork &w, double2 *A, double2 *B, uint32_t 
     // a forward transform's first pass meets N - G rows of zeros (whose transform is zeros, already in place), and of the
     // inverse's last pass only that band of rows is ever read (k_unpack) -- both passes run on the G-row band alone.
     uint32_t N = w.N, G = w.G, threads = std::max(32u, std::min(N / 8, 512u)), band = N - (G - 1) / 2;
-    k_fft_rows<<<dim3(inverse ? N : G, k), threads, fftSmemBytes(N), ctx->stream>>>(A, N, logN, w.tw, inverse, inverse ? 0u : band);
-    SKC_LAUNCHED("k_fft_rows");
-    k_transpose<<<dim3(N / 32, N / 32, k), dim3(32, 8), 0, ctx->stream>>>(A, N, B);
+    const bool oldRows = getenv("SKC_FFT_ROWS") && !strcmp(getenv("SKC_FFT_ROWS"), "generic");
+    auto rows = [&](double2 *M, uint32_t nRows, uint32_t rowStart) {
+        if (N == FFT2_N && !oldRows) {
+            const size_t smem = 2 * FFT2_SLOTS * sizeof(double2);
+            static bool attr = false;
+            if (!attr) { cudaFuncSetAttribute(k_fft_rows2048, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
+            k_fft_rows2048<<<dim3((nRows + 1) / 2, k), 256, smem, ctx->stream>>>(M, w.tw, inverse, rowStart, nRows);
+            SKC_LAUNCHED("k_fft_rows2048");
+        } else {
+            k_fft_rows<<<dim3(nRows, k), threads, fftSmemBytes(N), ctx->stream>>>(M, N, logN, w.tw, inverse, rowStart);
+            SKC_LAUNCHED("k_fft_rows");
+        }
+    };
+    rows(A, inverse ? N : G, inverse ? 0u : band);
+    k_transpose<<<dim3(N / 32, N / 32, k), dim3(32, 8), 0, ctx->stream>>>(A, N, B, inverse ? 2 : 1, band, G);
     SKC_LAUNCHED("k_transpose");
-    k_fft_rows<<<dim3(inverse ? G : N, k), threads, fftSmemBytes(N), ctx->stream>>>(B, N, logN, w.tw, inverse, inverse ? band : 0u);
-    SKC_LAUNCHED("k_fft_rows");
+    rows(B, inverse ? G : N, inverse ? band : 0u);
     return 0;
 }
 
@@ -430,7 +540,12 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
             for (int k = 0; k < 3; ++k) ok &= cudaMalloc((void **)&w.Z[k], (size_t)K * N * N * sizeof(double2)) == cudaSuccess;
             if (!ok) break;
             std::vector<double2> tw(N / 2);
+            tw.reserve(N / 2 + N);
             for (uint32_t k = 0; k < N / 2; ++k) { long double a = -2.0L * 3.14159265358979323846264338327950288L * k / N; tw[k] = make_double2((double)cosl(a), (double)sinl(a)); }
+            // the same entries again, stage by stage (stage st reads tw[i * (N >> st)], i < 2^(st-1)): contiguous per stage, so that
+            // k_fft_rows2048's twiddle reads are coalesced; stage st starts at N/2 + 2^(st-1) - 1
+            for (uint32_t st = 1; (1u << st) <= N; ++st)
+                for (uint32_t i = 0; i < (1u << (st - 1)); ++i) tw.push_back(tw[(size_t)i * (N >> st)]);
             if (cudaMalloc((void **)&w.tw, tw.size() * sizeof(double2)) != cudaSuccess) break;
             if (cudaMemcpyAsync(w.tw, tw.data(), tw.size() * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
             if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
@@ -467,9 +582,11 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
     uint32_t ext = (G - 1) / 2 + 1;
     dim3 lpBlock(32, 8);
     // a group = up to K consecutive sets with the same number of layers: layer l of all of them goes through each stage at once
-    uint32_t groupIndex = 0, prevS0 = 0, prevK = 0;
-    int prevB = 0;
-    bool havePrev = false;
+    uint32_t groupIndex = 0;
+    struct Joining { std::thread t; ~Joining() { if (t.joinable()) t.join(); } } bg;      // joins on every way out of the function
+    std::thread &worker = bg.t;
+    int workerStatus = 0;
+    const int device = ctx->device;
     for (uint32_t s0 = 0; s0 < nSets && !rc;) {
         const uint32_t nL = layersPerSet[s0];
         uint32_t k = 1;
@@ -490,14 +607,14 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
         rc = layer(0, w.grid[0]);
         for (uint32_t l = 1; l < nL && !rc; ++l) {
             if ((rc = layer(l, w.grid[1]))) break;
-            dim3 pg((N + 255) / 256, N, k);
+            dim3 pg((N + 255) / 256, G, k);
             k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[0], G, N, w.Z[0]);
             k_pack<<<pg, 256, 0, ctx->stream>>>(w.grid[1], G, N, w.Z[1]);
             ctx->launches += 2;
             // forward: Z0 -> Z2 (transposed spectrum of layer 1); Z1 -> Z0 (layer 2)
             if ((rc = fft2d(ctx, w, w.Z[0], w.Z[2], logN, 0, k))) break;
             if ((rc = fft2d(ctx, w, w.Z[1], w.Z[0], logN, 0, k))) break;
-            k_adding<<<dim3((N + 255) / 256, N, k), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
+            k_adding<<<dim3((N + 255) / 256, N / 2 + 1, k), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
             ctx->launches++;
             if ((rc = fft2d(ctx, w, w.Z[1], w.Z[2], logN, 1, k))) break;      // back to the natural layout
             k_unpack<<<dim3((G + 255) / 256, G, k), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0]);
@@ -545,28 +662,38 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
         SKC_CUDA(cudaMemcpyAsync(w.hostOut[bsel], o, (size_t)k * 3 * outLen * sizeof(float), cudaMemcpyDeviceToHost, ctx->copyStream));
         if (totals) SKC_CUDA(cudaMemcpyAsync(w.hostPart[bsel], part, (size_t)k * 256 * sizeof(double2), cudaMemcpyDeviceToHost, ctx->copyStream));
         SKC_CUDA(cudaEventRecord(w.copied[bsel], ctx->copyStream));
-        // rows [set][d2 | R | T][outLen] of a finished group -> the caller's three [set][outLen] arrays
-        auto deliver = [&](int bb, uint32_t gs0, uint32_t gk) -> int {
-            if (cudaEventSynchronize(w.copied[bb]) != cudaSuccess) return 1;
+        // rows [set][d2 | R | T][outLen] of a finished group -> the caller's three [set][outLen] arrays: on a worker thread (the
+        // scatter itself on up to four), so that the launching thread goes on to the next group -- a 46 MB pageable scatter
+        // per group on the launching thread kept the GPU waiting for its next launches
+        auto deliver = [&w, d2, R, T, totals, outLen, device](int bb, uint32_t gs0, uint32_t gk, int *status) {
+            if (cudaSetDevice(device) != cudaSuccess || cudaEventSynchronize(w.copied[bb]) != cudaSuccess) { *status = 1; return; }
             const float *h = w.hostOut[bb];
             float *dsts[3] = {d2, R, T};
-            for (uint32_t q = 0; q < gk; ++q)
-                for (int a = 0; a < 3; ++a)
-                    if (dsts[a]) memcpy(dsts[a] + (size_t)(gs0 + q) * outLen, h + ((size_t)q * 3 + a) * outLen, (size_t)outLen * sizeof(float));
+            auto part = [&](uint32_t t, uint32_t nT) {
+                for (uint32_t q = t; q < gk; q += nT)
+                    for (int a = 0; a < 3; ++a)
+                        if (dsts[a]) memcpy(dsts[a] + (size_t)(gs0 + q) * outLen, h + ((size_t)q * 3 + a) * outLen, (size_t)outLen * sizeof(float));
+            };
+            const uint32_t nT = std::min<uint32_t>(4u, gk);
+            std::vector<std::thread> helpers;
+            for (uint32_t t = 1; t < nT; ++t) helpers.emplace_back(part, t, nT);
+            part(0, nT);
+            for (auto &th : helpers) th.join();
             if (totals)
                 for (uint32_t q = 0; q < gk; ++q) {
                     double r = 0., t = 0.;
                     for (int j = 0; j < 256; ++j) { r += w.hostPart[bb][(size_t)q * 256 + j].x; t += w.hostPart[bb][(size_t)q * 256 + j].y; }
                     totals[2 * (gs0 + q)] = (float)r; totals[2 * (gs0 + q) + 1] = (float)t;
                 }
-            return 0;
         };
-        if (havePrev && deliver(prevB, prevS0, prevK)) { rc = 1; break; }
-        havePrev = true; prevB = bsel; prevS0 = s0; prevK = k;
-        if (s0 + k >= nSets && deliver(prevB, prevS0, prevK)) { rc = 1; break; }
+        // the worker of the group before the previous one read hostOut[bsel ^ 1] ... it must be done before that buffer's next copy
+        // is enqueued, which is the copy of the NEXT group: joining here, one group of GPU work after it started, rarely waits
+        if (worker.joinable()) { worker.join(); if (workerStatus) { rc = 1; break; } }
+        worker = std::thread(deliver, bsel, s0, k, &workerStatus);
         s0 += k;
         ++groupIndex;
     }
+    if (worker.joinable()) { worker.join(); if (workerStatus) rc = 1; }
     if (!rc) skc_stage_end(ctx, 6);
     cudaError_t e = cudaGetLastError();
     cudaStreamSynchronize(ctx->stream);

@@ -96,6 +96,26 @@ def test_profile_batch_512_known_answers(pkg, frame):
     assert i == 4
 
 
+def test_fft_rows_2048_equals_generic_kernel(pkg, frame, monkeypatch):
+    """k_fft_rows2048 (two shared-memory crossings per row) does the butterflies of k_fft_rows in the same order: identical tables."""
+    dev = frame["dev"]
+    z = np.load(os.path.join(ROOT, "tests", "golden", "mpc_kat512.npz"))
+    s = z["case1_spec"]
+    nl, dl, lerp = int(s[0]), int(s[1]), int(s[2])
+    layers = s[5:].reshape(nl, 4).astype(np.float32)
+    specs = np.array([(l[0], l[1], l[2], l[3], 0.0) for l in layers], pkg.skc.DT_LAYER)
+    opts = np.array([(np.float32(0.01), dl, lerp)], pkg.skc.DT_MPC_OPTIONS)
+    out = {}
+    for mode in ("generic", "tiled"):
+        if mode == "generic":
+            monkeypatch.setenv("SKC_FFT_ROWS", "generic")
+        else:
+            monkeypatch.delenv("SKC_FFT_ROWS", raising=False)
+        out[mode] = dev.profile_batch(specs, [nl], opts, resample=False)
+    for a, b in zip(out["generic"], out["tiled"]):
+        assert np.array_equal(np.asarray(a).view(np.uint32), np.asarray(b).view(np.uint32))
+
+
 def test_irradiance_points_vs_reference(frame, full):
     z, meta = full
     dev = frame["dev"]
