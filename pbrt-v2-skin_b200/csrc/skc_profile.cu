@@ -26,6 +26,7 @@
 #include "skc_internal.h"
 
 // ---------------------------------------------------------------------------------------------
+#define SKC_PROFILE_MAX_LAYERS 16
 struct DipoleSet {            // DipoleCalculator members for zi = -5..5 (DipoleCalculator.cpp:51-69)
     float zpos[11], zneg[11];
     float d, sigma_tr, alphap;
@@ -106,7 +107,7 @@ __device__ __forceinline__ float expf_glibc(float x, const unsigned long long *t
 
 // z[G][G] (double2 = {R, T}); one thread per (row<=col) cell of the [0,extent]^2 quadrant
 // blockIdx.z = set of the batch (its DipoleSet and its grid)
-__global__ void k_layer_profile(const DipoleSet *__restrict__ dsAll, uint32_t G, double2 *__restrict__ z) {
+__global__ void k_layer_profile(const DipoleSet *__restrict__ dsAll, uint32_t G, double2 *__restrict__ z, uint32_t *__restrict__ tNonZero) {
     const DipoleSet ds = dsAll[blockIdx.z];
     z += (size_t)blockIdx.z * G * G;
     uint32_t center = (G - 1) / 2, extent = center;
@@ -140,6 +141,8 @@ __global__ void k_layer_profile(const DipoleSet *__restrict__ dsAll, uint32_t G,
         R *= ds.lerp; T *= ds.lerp;
         if (row == 0 && col == 0) T += 1. - ds.lerp;
     }
+    // see k_unpack; 1e-36: below it the reference's fp32 dipole terms are denormal or zero
+    if (fabs(T) >= 1e-36 * ds.normalize && ((volatile uint32_t *)tNonZero)[blockIdx.z] == 0u) tNonZero[blockIdx.z] = 1u;
     double2 v = make_double2(R, T);
     // symmetric fill (MultipoleProfileCalculator.cpp:210-229)
     uint32_t rr[2] = {center + row, center - row}, cc[2] = {center + col, center - col};
@@ -356,15 +359,23 @@ __global__ void k_adding(const double2 *__restrict__ Z1, const double2 *__restri
 }
 
 // ScaleAndShiftReversed (numutil.h:205-217) of the inverse transform, scaled by 1/N^2 (:132-139)
-__global__ void k_unpack(const double2 *__restrict__ W, uint32_t N, uint32_t G, double2 *__restrict__ z) {
+// A layer that transmits nothing (every dipole term underflows or is denormal in fp32: an optically thick slab) has T == 0, or
+// ~1e-41, in every cell, and the reference, which transforms R and T separately, then gets T12 == 0 exactly (or denormals that
+// its float tables round to 0).  Here T travels as the imaginary part of R + iT and would come back as rounding noise (1e-24 of
+// R); tNonZero[layer][set] (k_layer_profile) says which layers had any representable T, and a stack with a layer that had
+// none gets the reference's zero.
+__global__ void k_unpack(const double2 *__restrict__ W, uint32_t N, uint32_t G, double2 *__restrict__ z, const uint32_t *__restrict__ tNonZero,
+                         uint32_t nLayersSoFar, uint32_t setStride) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
     if (j >= G) return;
     W += (size_t)blockIdx.z * N * N; z += (size_t)blockIdx.z * G * G;
+    bool opaque = false;
+    for (uint32_t l = 0; l < nLayersSoFar; ++l) opaque |= tNonZero[(size_t)l * setStride + blockIdx.z] == 0u;
     uint32_t c = (G - 1) / 2;
     uint32_t ii = (N - c + i) % N, jj = (N - c + j) % N;
     double scale = (double)1 / ((double)N * (double)N);
     double2 v = W[(size_t)ii * N + jj];
-    z[(size_t)i * G + j] = make_double2(v.x * scale, v.y * scale);
+    z[(size_t)i * G + j] = make_double2(v.x * scale, opaque ? 0. : v.y * scale);
 }
 
 // block sums of R and T over the grid (totalReflectance / totalTransmittance, :338-339)
@@ -454,9 +465,10 @@ struct ProfileWork {
     double2 *hostPart[2] = {nullptr, nullptr};
     cudaEvent_t computed[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
     DipoleSet *ds = nullptr;
+    uint32_t *tNonZero = nullptr;      // [SKC_PROFILE_MAX_LAYERS][K]
     uint32_t G = 0, N = 0, nEntries = 0, K = 1;
     void release() {
-        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res, steps, ds, out[0], out[1]};
+        void *p[] = {grid[0], grid[1], Z[0], Z[1], Z[2], tw, partial, idx, raw, res, steps, ds, tNonZero, out[0], out[1]};
         for (void *q : p) if (q) cudaFree(q);
         for (int b = 0; b < 2; ++b) {
             if (hostOut[b]) cudaFreeHost(hostOut[b]);
@@ -566,6 +578,7 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
         if (cudaMalloc((void **)&w.raw, (size_t)K * 3 * nEntries * sizeof(float)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.steps, (size_t)K * sizeof(float)) != cudaSuccess) break;
         if (cudaMalloc((void **)&w.ds, (size_t)K * sizeof(DipoleSet)) != cudaSuccess) break;
+        if (cudaMalloc((void **)&w.tNonZero, (size_t)SKC_PROFILE_MAX_LAYERS * K * sizeof(uint32_t)) != cudaSuccess) break;
         if (cudaMemcpyAsync(w.idx, radii.data(), nEntries * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) break;
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) break;
         rc = 0;
@@ -600,10 +613,12 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
             }
             SKC_CUDA(cudaMemcpyAsync(w.ds, hds.data(), k * sizeof(DipoleSet), cudaMemcpyHostToDevice, ctx->stream));      // pageable source: staged before the call returns
             SKC_CUDA(cudaMemsetAsync(dst, 0, (size_t)k * G * G * sizeof(double2), ctx->stream));   // profile.Clear()
-            k_layer_profile<<<dim3((ext + 31) / 32, (ext + 7) / 8, k), lpBlock, 0, ctx->stream>>>(w.ds, G, dst);
+            k_layer_profile<<<dim3((ext + 31) / 32, (ext + 7) / 8, k), lpBlock, 0, ctx->stream>>>(w.ds, G, dst, w.tNonZero + (size_t)l * K);
             SKC_LAUNCHED("k_layer_profile");
             return 0;
         };
+        if (nL > SKC_PROFILE_MAX_LAYERS) { rc = skc_fail(ctx, "skc_profile_batch: %u layers in one set (at most %d)", nL, SKC_PROFILE_MAX_LAYERS); break; }
+        SKC_CUDA(cudaMemsetAsync(w.tNonZero, 0, (size_t)SKC_PROFILE_MAX_LAYERS * K * sizeof(uint32_t), ctx->stream));
         rc = layer(0, w.grid[0]);
         for (uint32_t l = 1; l < nL && !rc; ++l) {
             if ((rc = layer(l, w.grid[1]))) break;
@@ -617,7 +632,7 @@ extern "C" int skc_profile_batch(skc_ctx *ctx, const skc_layer_spec *specs, cons
             k_adding<<<dim3((N + 255) / 256, N / 2 + 1, k), 256, 0, ctx->stream>>>(w.Z[2], w.Z[0], N, w.Z[1]);
             ctx->launches++;
             if ((rc = fft2d(ctx, w, w.Z[1], w.Z[2], logN, 1, k))) break;      // back to the natural layout
-            k_unpack<<<dim3((G + 255) / 256, G, k), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0]);
+            k_unpack<<<dim3((G + 255) / 256, G, k), 256, 0, ctx->stream>>>(w.Z[2], N, G, w.grid[0], w.tNonZero, l + 1, K);
             ctx->launches++;
         }
         if (rc) break;
