@@ -80,6 +80,7 @@ extern "C" skc_ctx *skc_create(int device) {
     if (const char *k = getenv("SKC_MO_KERNEL")) ctx->moPacket = strcmp(k, "warp") != 0;
     if (cudaDeviceGetAttribute(&ctx->smemOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess) ctx->smemOptin = 48 * 1024;
     if (const char *k = getenv("SKC_MO_GROUP")) ctx->moGroup = atoi(k);
+    if (const char *k = getenv("SKC_MO_PACKET_HITS")) { int v = atoi(k); ctx->moPacketHits = (v == 8 || v == 16 || v == 32) ? v : 0; }
     if (const char *k = getenv("SKC_MO_WARPS")) ctx->moWarps = atoi(k);
     if (const char *k = getenv("SKC_BVH_WIDE")) ctx->bvhWideOn = atoi(k) != 0;
     if (const char *k = getenv("SKC_MO_TABLE")) ctx->moTable = !strcmp(k, "exact") ? 0 : !strcmp(k, "compact") ? 2 : 1;

@@ -469,7 +469,7 @@ template <bool COUNT, bool PERM, bool HEADS, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables T, MoCompactDev C, const float *__restrict__ p3, uint64_t strideFloats,
                                                                      const int32_t *__restrict__ enable, uint64_t enableStrideInts,
                                                                      uint64_t n, float maxError, float *__restrict__ Mo, unsigned long long *cnt, LiEpilogue li,
-                                                                     uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm) {
+                                                                     uint32_t *__restrict__ nextPacket, const uint32_t *__restrict__ perm, uint32_t packetHits) {
     extern __shared__ float4 molSmem[];
     float *sRows = reinterpret_cast<float *>(molSmem);
     float *sHeads = sRows + C.rowFloats;
@@ -495,15 +495,19 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
     uint32_t hist[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // contributions by size of their accept group (<8, 8-15, 16-27, 28-32): clusters, then leaf points (COUNT only)
     uint32_t grp[2] = {0, 0};          // accept events of this warp: (cluster, packet) and (leaf point, packet) groups (COUNT only)
     uint32_t gc[3] = {0, 0, 0};        // this lane's profile lookups: all in range / from the shared-memory heads / from the global tables
-    const uint32_t nPackets = (uint32_t)((n + 31) / 32);
+    // packetHits = 32, or 16 / 8 for short launches (shards of a multi-GPU frame): the contributions -- most of the work -- are
+    // summed one accepting hit at a time whatever the packet size, so smaller packets cost only node-test lanes and cut the
+    // run time of the heaviest packet, which is what a launch with a few packets per warp waits for
+    const uint32_t nPackets = (uint32_t)((n + packetHits - 1) / packetHits);
     for (;;) {
         uint32_t packet = 0;
         if (lane == 0) packet = atomicAdd(nextPacket, 1u);
         packet = __shfl_sync(0xffffffffu, packet, 0);
         if (packet >= nPackets) break;
-        uint64_t h0 = (uint64_t)packet * 32, h = h0 + lane;
-        const uint32_t src = (PERM && h < n) ? __ldg(&perm[h]) : (uint32_t)h;
-        bool on = h < n && (enable ? (__ldg(&enable[(uint64_t)src * enableStrideInts]) != 0) : true);
+        uint64_t h0 = (uint64_t)packet * packetHits, h = h0 + lane;
+        const bool inPacket = (uint32_t)lane < packetHits && h < n;
+        const uint32_t src = (PERM && inPacket) ? __ldg(&perm[h]) : (uint32_t)h;
+        bool on = inPacket && (enable ? (__ldg(&enable[(uint64_t)src * enableStrideInts]) != 0) : true);
         float px = 0.f, py = 0.f, pz = 0.f;
         if (on) { const float *pp = p3 + (uint64_t)src * strideFloats; px = __ldg(pp); py = __ldg(pp + 1); pz = __ldg(pp + 2); }
 #pragma unroll
@@ -574,7 +578,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
             }
         }
         // lane = wavelength already: stream the 32 rows out
-        for (int r = 0; r < 32; ++r) {
+        for (int r = 0; r < (int)packetHits; ++r) {
             uint64_t hh = h0 + r;
             if (hh >= n) break;
             if (PERM) hh = (uint64_t)__shfl_sync(0xffffffffu, src, r);
@@ -756,7 +760,14 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         if (ctx->moWarps > 0) warps = std::min(warps, ctx->moWarps);
         if (warps < 4) return skc_fail(ctx, "skc_mo: the compact profile table (%zu B) leaves no room for the traversal state in shared memory", tableBytes);
         const size_t smem = tableBytes + (size_t)warps * MOL_WARP_BYTES;
-        const uint64_t nPk = (n + 31) / 32;
+        // packets per resident warp decide the packet size (see the kernel): 32 hits from 8 packets per warp up, else 16
+        // (tools/mo_shard_ab.py, a rank's share of the skin.scene frame: 1/4 of it 13.1 -> 11.6 ms, 1/8 8.3 -> 7.1 ms; packets of
+        // 8 are no better than 16, and on the whole frame 16 costs 3 %)
+        const uint64_t residentWarps = (uint64_t)ctx->smCount * warps;
+        uint32_t packetHits = 32;
+        if (ctx->moPacketHits > 0) packetHits = (uint32_t)ctx->moPacketHits;
+        else if ((n + 31) / 32 < 8 * residentWarps) packetHits = 16;
+        const uint64_t nPk = (n + packetHits - 1) / packetHits;
         const unsigned grid = (unsigned)std::min<uint64_t>((nPk + warps - 1) / warps, (uint64_t)ctx->smCount);
         LiEpilogue ep = li ? *li : LiEpilogue{nullptr, nullptr, nullptr, 0.f, nullptr};
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
@@ -765,7 +776,7 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n) : nullptr;
 #define MOL_GO2(CNT, P, H, W) do { \
             SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<CNT, P, H, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            k_mo_lambda<CNT, P, H, W><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm); } while (0)
+            k_mo_lambda<CNT, P, H, W><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm, packetHits); } while (0)
 #define MOL_GO(CNT, P) do { if (C.headFloats <= 4) { if (warps > 20) MOL_GO2(CNT, P, false, 28); else MOL_GO2(CNT, P, false, 20); } else { if (warps > 20) MOL_GO2(CNT, P, true, 28); else MOL_GO2(CNT, P, true, 20); } } while (0)
         if (cntDev) { if (perm) MOL_GO(true, true); else MOL_GO(true, false); } else { if (perm) MOL_GO(false, true); else MOL_GO(false, false); }
 #undef MOL_GO2
@@ -1097,10 +1108,10 @@ extern "C" int skc_mo_static(skc_ctx *ctx, const float *p3, uint64_t n, float ma
         const unsigned grid = (unsigned)std::min<uint64_t>(((n + 31) / 32 + warps - 1) / warps, (uint64_t)ctx->smCount);
         if (C.headFloats <= 4) {
             SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<false, false, false, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_mo_lambda<false, false, false, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr);
+            k_mo_lambda<false, false, false, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr, 32u);
         } else {
             SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<false, false, true, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_mo_lambda<false, false, true, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr);
+            k_mo_lambda<false, false, true, 20><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, dP, 3, nullptr, 0, n, maxError, dPad, nullptr, ep, next, nullptr, 32u);
         }
         SKC_LAUNCHED("k_mo_lambda (static scratch)");
     } else {
