@@ -92,7 +92,6 @@ struct skc_ctx {
     float *otEt = nullptr;         // [nNodes][32]
     uint32_t *otPointIdx = nullptr;// leaf-ordered permutation of irradiance points
     float4 *otLeafPosArea = nullptr; // irradiance points gathered in leaf order
-    float *otLeafE = nullptr;        // [n][32] in leaf order
     uint32_t otNodes = 0, otCap = 0, otLevels = 0;
     uint32_t lightNS[16] = {0};   // RoundUpPow2(nSamples) per light (host copy for launch shapes)
     std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize

@@ -261,6 +261,7 @@ int skc_ensure_points(skc_ctx *ctx, uint64_t n) {
     if (ctx->ipPosArea) cudaFree(ctx->ipPosArea);
     if (ctx->ipE) cudaFree(ctx->ipE);
     ctx->ipPosArea = pa; ctx->ipE = e; ctx->ipCap = n;
+    ctx->otNodes = 0; ctx->otTopologyReady = false;      // an octree built over the old arrays read its E rows from them
     return 0;
 }
 

@@ -48,9 +48,11 @@ struct MoTables {
 struct MoTree {
     const float4 *nodes;     // 3 per node
     const float *Et;         // [nodes][32]
-    const float4 *leafPosArea;
-    const float *leafE;      // [points][32]
+    const float4 *leafPosArea;   // {p, area} in leaf order
+    const uint32_t *pointIdx;    // leaf slot -> point: the E rows are read in place, in point order
+    const float *E;              // [points][32]
 };
+__device__ __forceinline__ const float *leafRow(const MoTree &tr, uint32_t slot) { return tr.E + (size_t)__ldg(&tr.pointIdx[slot]) * SKC_EPAD; }
 
 // sampleProfile (core/multipole.cpp:60-73).  d2*rcp is an fp32 product there too (the
 // promotion to double happens after the multiply); the compare against size-1 and the
@@ -135,7 +137,7 @@ __device__ __forceinline__ void moOne(const MoTree &tr, const MoTables &T, float
             uint32_t r = __shfl_sync(0xffffffffu, rowIdx, src);
             float dd = __shfl_sync(0xffffffffu, d2, src);
             float sc = __shfl_sync(0xffffffffu, scale, src);
-            const float *row = (r & MO_POINT) ? tr.leafE + (size_t)(r & ~MO_POINT) * SKC_EPAD : tr.Et + (size_t)r * SKC_EPAD;
+            const float *row = (r & MO_POINT) ? leafRow(tr, r & ~MO_POINT) : tr.Et + (size_t)r * SKC_EPAD;
             float e = __ldg(&row[lane]);
             float rd = sampleRd(T, lam, rcp, dd);
             acc += (rd * e) * sc;          // diffusionutil.h:186 / :197
@@ -321,7 +323,7 @@ __global__ void __launch_bounds__(MOP_WARPS * 32, SPLIT == 1 ? MOP_CTAS1 : (SPLI
                     unsigned pm = __ballot_sync(0xffffffffu, c);
                     if (pm) {
                         if (COUNT && part == 0) wc[3] += __popc(pm);
-                        mopContribute<COUNT, NQ>(T, sRcp, reinterpret_cast<const float4 *>(tr.leafE + (size_t)slot * SKC_EPAD), q0, q2, pa.w, c, acc, gathers);
+                        mopContribute<COUNT, NQ>(T, sRcp, reinterpret_cast<const float4 *>(leafRow(tr, slot)), q0, q2, pa.w, c, acc, gathers);
                     }
                 }
             } else {
@@ -553,6 +555,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
                 if (w1 & SKC_OT_LEAF) {
                     uint32_t cntP = w1 & 0xffu;
                     if (COUNT) wc[1] += cntP * __popc(dm);
+                    const uint32_t myPoint = (uint32_t)lane < cntP ? __ldg(&tr.pointIdx[w0 + lane]) : 0u;      // the leaf's <= 8 rows, looked up once
                     for (uint32_t kp = 0; kp < cntP; ++kp) {
                         uint32_t slot = w0 + kp;
                         float4 pa = __ldg(&tr.leafPosArea[slot]);
@@ -562,7 +565,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
                         unsigned pm = __ballot_sync(0xffffffffu, c);
                         if (pm) {
                             if (COUNT) { wc[3] += __popc(pm); ++grp[1]; const int A = __popc(pm); hist[4 + (A >= 28 ? 3 : A >= 16 ? 2 : A >= 8 ? 1 : 0)] += A; }
-                            const float e = __ldg(tr.leafE + (size_t)slot * SKC_EPAD + lane);
+                            const float e = __ldg(tr.E + (size_t)__shfl_sync(0xffffffffu, myPoint, (int)kp) * SKC_EPAD + lane);
                             if (c) molRecord(rec, __popc(pm & lanesBelow), C.P, kMax32, q2, pa.w, lane);
                             __syncwarp();
                             molContribute<COUNT, HEADS>(__popc(pm), e, rec, acc, sRows, sHeads, T, lane, lp, hoff, lenM1L, gc);
@@ -748,7 +751,7 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
     if (!ctx->otGeo || !ctx->otNodes) return skc_fail(ctx, "skc_mo: no octree built (skc_build_octree)");
     if (!ctx->profPairs) return skc_fail(ctx, "skc_mo: no profile table uploaded (skc_upload_profile)");
     if (!n) return 0;
-    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
+    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.pointIdx = ctx->otPointIdx; tr.E = ctx->ipE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
     if (ctx->moPacket && molWanted(ctx)) {
         if (n >= (1ull << 32)) return skc_fail(ctx, "skc_mo: more than 2^32 hit points in one call");
@@ -1094,7 +1097,7 @@ extern "C" int skc_mo_static(skc_ctx *ctx, const float *p3, uint64_t n, float ma
     // p3 / Mo30 may be host or device memory (unified addressing picks the direction)
     SKC_CUDA(cudaMemcpyAsync(dP, p3, n * 3 * sizeof(float), cudaMemcpyDefault, ctx->stream));
     SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
-    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.leafE = ctx->otLeafE;
+    MoTree tr; tr.nodes = ctx->otGeo; tr.Et = ctx->otEt; tr.leafPosArea = ctx->otLeafPosArea; tr.pointIdx = ctx->otPointIdx; tr.E = ctx->ipE;
     MoTables T; T.pairs = ctx->profPairs; T.rcp = ctx->profRcp; T.len = ctx->profLen; T.rcpMin = ctx->profMaxD2; T.lenM1 = (float)(ctx->profLen - 1);
     const LiEpilogue ep{nullptr, nullptr, nullptr, 0.f, nullptr};
     if (molWanted(ctx)) {
