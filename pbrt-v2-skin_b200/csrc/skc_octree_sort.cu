@@ -91,13 +91,18 @@ __global__ void __launch_bounds__(256) k_leaf_depth(const unsigned long long *__
 // blockCount[l * nBlocks + block] = nodes of level l started inside the block
 __global__ void __launch_bounds__(OTS_BLOCK) k_level_counts(const uint32_t *__restrict__ info, uint32_t n, uint32_t nBlocks,
                                                             uint32_t *__restrict__ blockCount) {
+    __shared__ uint32_t cnt[OTS_LEVELS + 1];
     uint32_t i = blockIdx.x * OTS_BLOCK + threadIdx.x;
     int depth = -1, lo = 0;
     if (i < n) { uint32_t v = info[i]; depth = v & 0xff; lo = (v >> 8) & 0xff; }
+    if (threadIdx.x <= OTS_LEVELS) cnt[threadIdx.x] = 0;
+    __syncthreads();
     for (int l = 0; l <= OTS_LEVELS; ++l) {
-        int c = __syncthreads_count(lo <= l && l <= depth);
-        if (threadIdx.x == 0) blockCount[(size_t)l * nBlocks + blockIdx.x] = (uint32_t)c;
+        unsigned m = __ballot_sync(0xffffffffu, lo <= l && l <= depth);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&cnt[l], (uint32_t)__popc(m));
     }
+    __syncthreads();
+    if (threadIdx.x <= OTS_LEVELS) blockCount[(size_t)threadIdx.x * nBlocks + blockIdx.x] = cnt[threadIdx.x];
 }
 
 // one CTA per level: exclusive scan of the block counts in place, total into levelCount[l]
@@ -125,27 +130,33 @@ struct OtsLevels { uint32_t start[OTS_LEVELS + 2]; };
 __global__ void __launch_bounds__(OTS_BLOCK) k_emit_nodes(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ info,
                                                           uint32_t n, uint32_t nBlocks, const uint32_t *__restrict__ blockBase, OtsLevels lv,
                                                           OtsBounds root, float4 *__restrict__ nodes, int maxLevel) {
-    __shared__ uint32_t warpTot[OTS_BLOCK / 32];
+    // warpTot[l][w] = nodes of level l started by warp w of this block: all levels' ballots first, ONE barrier, then every thread
+    // ranks itself per level from the table (the first version had two barriers per level)
+    __shared__ uint32_t warpTot[OTS_LEVELS + 1][OTS_BLOCK / 32];
     uint32_t i = blockIdx.x * OTS_BLOCK + threadIdx.x;
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int depth = -1, lo = 0; uint32_t count = 0;
     unsigned long long key = 0;
     if (i < n) { uint32_t v = info[i]; depth = v & 0xff; lo = (v >> 8) & 0xff; count = v >> 16; key = keys[i]; }
+    const unsigned below = (1u << lane) - 1u;
+    for (int l = 0; l <= maxLevel; ++l) {
+        unsigned m = __ballot_sync(0xffffffffu, lo <= l && l <= depth);
+        if (lane == 0) warpTot[l][warp] = __popc(m);
+    }
+    __syncthreads();
     OtsBounds b = root;
     uint32_t containing = 0;      // node of the previous level that holds this point
     uint32_t prevOwn = 0xffffffffu;  // node this thread started at the previous level (if interior: awaits its first child)
-    for (int l = 0; l <= maxLevel; ++l) {
+    const int warpDepth = __reduce_max_sync(0xffffffffu, depth);
+    for (int l = 0; l <= warpDepth; ++l) {
         bool alive = l <= depth;
         uint32_t digit = 0;
         if (l > 0 && alive) { digit = (uint32_t)(key >> (3 * (OTS_LEVELS - l))) & 7u; otsChild(b, digit); }
         bool start = alive && lo <= l;
         unsigned m = __ballot_sync(0xffffffffu, start);
-        if (lane == 0) warpTot[warp] = __popc(m);
-        __syncthreads();
         uint32_t before = 0;
-        for (int w = 0; w < warp; ++w) before += warpTot[w];
-        __syncthreads();
-        uint32_t excl = before + __popc(m & ((1u << lane) - 1u));
+        for (int w = 0; w < warp; ++w) before += warpTot[l][w];
+        uint32_t excl = before + __popc(m & below);
         uint32_t base = lv.start[l] + __ldg(&blockBase[(size_t)l * nBlocks + blockIdx.x]);
         if (start) {
             uint32_t id = base + excl;
