@@ -76,14 +76,21 @@ __global__ void __launch_bounds__(256) k_leaf_depth(const unsigned long long *__
         cl[t] = i >= (uint32_t)(t + 1) ? otsCommonLevels(k, keys[i - t - 1]) : -1;
         cr[t] = i + t + 1 < n ? otsCommonLevels(k, keys[i + t + 1]) : -1;
     }
-    int depth = -1, count = 0;
-    for (int l = 0; l <= sortedLevels; ++l) {
-        int c = 1;
+    // The cell of level l around point i holds 1 + L(l) + R(l) points, L / R = neighbours on either side that share >= l levels
+    // (cl, cr are non-increasing in t).  It holds more than 8 iff for some a in 0..8 the a-th left and the (8-a)-th right
+    // neighbour both share >= l levels, i.e. iff l <= max_a min(cl[a-1], cr[7-a]); the leaf's depth is one more than that.
+    int deepestCrowded = -1;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) c += (cl[t] >= l) + (cr[t] >= l);
-        if (c <= 8) { depth = l; count = c; break; }
+    for (int a = 0; a <= 8; ++a) {
+        const int x = a == 0 ? 1000 : cl[a - 1], y = a == 8 ? 1000 : cr[7 - a];
+        deepestCrowded = max(deepestCrowded, min(x, y));
     }
-    if (depth < 0) { atomicExch(overflow, 1u); depth = OTS_LEVELS; count = 8; }
+    int depth = deepestCrowded + 1, count = 1;
+    if (depth > sortedLevels) { atomicExch(overflow, 1u); depth = OTS_LEVELS; count = 8; }
+    else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) count += (cl[t] >= depth) + (cr[t] >= depth);
+    }
     int lo = i == 0 ? 0 : cl[0] + 1;
     info[i] = (uint32_t)depth | ((uint32_t)lo << 8) | ((uint32_t)count << 16);
 }
