@@ -219,6 +219,11 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * only.  stats8 = {rows, shared-memory bytes, coverage, largest verified relative error inside the windows, and
  * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
  * global tables, 0}. */
+/* LayeredSkin's constant "color albedo" (materials/layeredskin.cpp:183,247; multipolesubsurface.cpp:139-140,287): the
+ * irradiance pass scales E by Pow(albedo, mix), Li scales the subsurface term by Pow(albedo, 1 - mix).  The caller passes the two
+ * 30-entry factors, made with the host's powf (the reference's own values); they apply to every later skc_irradiance* and
+ * skc_camera_pass* / skc_frame_render / skc_li_sss call that is not given per-point albedos.  NULL, NULL = Spectrum(1). */
+int skc_set_albedo_factors(skc_ctx *ctx, const float *powMix30, const float *powOneMinusMix30);
 int skc_mo_table_stats(skc_ctx *ctx, double *stats8);
 /* Contributions of the last counted skc_camera_pass_resident by the number of hits of their packet that accepted the same
  * cluster / leaf point together: clusters {<8, 8-15, 16-27, 28-32}, then leaf points {same four bins}. */

@@ -115,6 +115,7 @@ struct SceneDesc {
     std::map<std::string, float> skin;
     float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
     float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};     // "color Kr" / "color Kt" as the skin scenes give them
+    float albedo[3] = {1, 1, 1}; bool hasAlbedo = false;      // "color albedo" (materials/layeredskin.cpp:247)
     struct Xf { std::string kind; float v[4]; };
     struct Mesh { std::vector<Xf> xf; std::string file; };
     std::vector<Mesh> meshes;
@@ -157,6 +158,7 @@ static SceneDesc parseScene(const std::string &path) {
                 if (k == "layers") { for (int i = 0; i < 4; ++i) ls >> sd.layers[i]; }
                 else if (k == "Kr") { for (int i = 0; i < 3; ++i) ls >> sd.Kr[i]; }
                 else if (k == "Kt") { for (int i = 0; i < 3; ++i) ls >> sd.Kt[i]; }
+                else if (k == "albedo") { for (int i = 0; i < 3; ++i) ls >> sd.albedo[i]; sd.hasAlbedo = true; }
                 else { float v; ls >> v; sd.skin[k] = v; }
             }
         }
@@ -232,6 +234,7 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
                 else addF(ps, kv.first.c_str(), kv.second);
             }
             ps.AddRGBSpectrum("Kr", sd.Kr, 3); ps.AddRGBSpectrum("Kt", sd.Kt, 3);
+            if (sd.hasAlbedo) ps.AddRGBSpectrum("albedo", sd.albedo, 3);
             SkinLayer sl[2]; sl[0].thickness = sd.layers[0]; sl[0].ior = sd.layers[1];
             sl[1].thickness = sd.layers[2]; sl[1].ior = sd.layers[3];
             ps.AddSkinLayer("layers", sl, 2);

@@ -69,6 +69,7 @@ struct skc_ctx {
     float mocInvA = 0.f, mocM = 0.f;
     int moTable = 1;               // 1 = k_mo_lambda (compact table in shared memory + exact fallback) when the table's windows cover enough of the tables (MOC_MIN_COVERAGE), else k_mo_packet; 0 = always k_mo_packet, 2 = always k_mo_lambda; env SKC_MO_TABLE=exact|auto|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
+    float *albedoFactors = nullptr;   // [2][32]: Pow(albedo, mix), Pow(albedo, 1 - mix) of a constant "color albedo" (skc_set_albedo_factors); null = Spectrum(1)
     uint64_t moHist[8] = {0};
     int moPacketHits = 0;        // SKC_MO_PACKET_HITS: 0 = by launch size, else 8 / 16 / 32 hits per packet of k_mo_lambda
     uint64_t moGroups[2] = {0, 0};       // last counted pass: (cluster, packet) and (leaf point, packet) accept groups

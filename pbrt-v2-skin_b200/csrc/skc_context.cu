@@ -96,7 +96,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhWide, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->mocRows, ctx->mocHeads, ctx->mocLam, ctx->mocHeadOff, ctx->lights, ctx->ipPosArea, ctx->ipE,
-                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea};
+                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
     for (int i = 0; i < 24; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -125,6 +125,24 @@ extern "C" int skc_synchronize(skc_ctx *ctx) {
 }
 
 extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
+// LayeredSkin's "color albedo" (materials/layeredskin.cpp:183,247): the irradiance pass scales E by Pow(albedo, mix) and Li the
+// subsurface term by Pow(albedo, 1 - mix) (multipolesubsurface.cpp:139-140,287).  For a constant albedo both are 30 numbers,
+// made by the caller with the host's powf so that they are the reference's own values.  NULL, NULL = Spectrum(1).
+extern "C" int skc_set_albedo_factors(skc_ctx *ctx, const float *powMix30, const float *powOneMinusMix30) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    if (!powMix30 || !powOneMinusMix30) {
+        if (ctx->albedoFactors) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->albedoFactors); ctx->albedoFactors = nullptr; }
+        return 0;
+    }
+    float h[64];
+    for (int i = 0; i < 32; ++i) { h[i] = i < SKC_NS ? powMix30[i] : 1.f; h[32 + i] = i < SKC_NS ? powOneMinusMix30[i] : 1.f; }
+    if (!ctx->albedoFactors) SKC_CUDA(cudaMalloc((void **)&ctx->albedoFactors, sizeof h));
+    SKC_CUDA(cudaMemcpyAsync(ctx->albedoFactors, h, sizeof h, cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
 extern "C" int skc_sm_count(const skc_ctx *ctx) { return ctx ? ctx->smCount : 0; }
 extern "C" float skc_stage_ms(const skc_ctx *ctx, int stage) {
     return (stage >= 0 && stage < SKC_NSTAGES) ? ctx->stageMs[stage] : -1.f;

@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__
 template <bool DELTA>
 __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
         uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
-        float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea) {
+        float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea, const float *__restrict__ albedoPowMix) {
     int lane = threadIdx.x & 31;
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
         uint64_t pi = ptBase + point;
         float e = lane < SKC_NS ? E : 0.f;            // lanes 30,31 write the zero pad of the 128 B row
         if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
+        else if (albedoPowMix && lane < SKC_NS) e *= __ldg(&albedoPowMix[lane]);      // a constant albedo: Pow(albedo, mix) made on the host with libm's powf
         Eout[(outBase + pi) * SKC_EPAD + lane] = e;
     }
 }
@@ -362,8 +363,8 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
             else k_irr_sample<false, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
             k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
         }
-        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
-        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea);
+        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors);
+        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors);
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }

@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 // Optional fused Li epilogue of the packet kernel (multipolesubsurface.cpp:279-287): the subsurface radiance of each
 // hit is written straight from the Mo sums -- into device memory, or into mapped pinned host memory, in which case the
 // 120 B/sample result crosses PCIe while the kernel is still running instead of in a copy after it.
-struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; };
+struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; const float *albedoPow = nullptr; };   // albedoPow: Pow(albedo, 1 - mix) of a constant albedo, made on the host with libm's powf
 
 // NQ float4 groups of the 32-float row starting at group q0: 8 = the whole spectrum, 4 = half of it (a packet shared
 // by two warps, see k_mo_packet)
@@ -235,6 +235,7 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
     float Ft = 1.f - rho;
     float a = 1.f;
     if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + wl]), (double)(1.f - li.mix));
+    else if (li.albedoPow) a = __ldg(&li.albedoPow[wl]);
     return fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
 }
 
@@ -605,7 +606,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) k_mo_lambda(MoTree tr, MoTables 
 
 // Li subsurface term (multipolesubsurface.cpp:279-287); one warp per hit, lane = wavelength
 __global__ void k_li_sss(const skc_hit *__restrict__ hits, uint64_t n, const float *__restrict__ Mo, const float *__restrict__ rhoHd,
-                         const float *__restrict__ albedo, float mix, float *__restrict__ L) {
+                         const float *__restrict__ albedo, float mix, float *__restrict__ L, const float *__restrict__ albedoPow) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t h = t >> 5; int lane = t & 31;
     if (h >= n) return;
@@ -622,6 +623,7 @@ __global__ void k_li_sss(const skc_hit *__restrict__ hits, uint64_t n, const flo
         float Ft = 1.f - rho;
         float a = 1.f;
         if (albedo) a = (float)pow((double)__ldg(&albedo[h * SKC_NS + lane]), (double)(1.f - mix));
+        else if (albedoPow) a = __ldg(&albedoPow[lane]);
         float v = ((0.31830988618379067154f * Ft) * Mo[h * SKC_EPAD + lane]) * a;
         out = fmaxf(v, 0.f);       // Spectrum::Clamp(0)
     }
@@ -872,7 +874,7 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
     skc_stage_end(ctx, 4);
     uint64_t threads = n * 32;
     if (L30 || computeL) {
-        k_li_sss<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dHits, n, dMo, ctx->rhoHd, dAlb, mix, dL);
+        k_li_sss<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dHits, n, dMo, ctx->rhoHd, dAlb, mix, dL, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr);
         SKC_LAUNCHED("k_li_sss");
         if (L30) SKC_CUDA(cudaMemcpyAsync(L30, dL, n * SKC_NS * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     }
@@ -891,7 +893,7 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
 int skc_li_fused_dev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, float *dL) {
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_li: no rho table uploaded (skc_upload_profile)");
     if (!ctx->moPacket) return skc_fail(ctx, "skc_li: the fused Li epilogue needs the packet kernel");
-    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL};
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr};
     skc_stage_begin(ctx);
     if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep, false)) return 1;
     skc_stage_end(ctx, 4);
@@ -948,7 +950,7 @@ extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, fl
         if (!dL) return 1;
         target = dL;
     }
-    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, target};
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, target, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr};
     skc_stage_begin(ctx);
     if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep)) return 1;
     skc_stage_end(ctx, 4);

@@ -112,6 +112,8 @@ void skh_skin_params(const skh_scene *s, float *out12) {
                    k.layerThickness[0], k.layerIor[0], k.layerThickness[1], k.layerIor[1]};
     memcpy(out12, v, sizeof v);
 }
+// "color albedo" of the material: rgb, and whether it was given at all (Spectrum(1) otherwise)
+int skh_skin_albedo(const skh_scene *s, float *rgb3) { memcpy(rgb3, s->sd.skin.albedo, 12); return s->sd.skin.hasAlbedo ? 1 : 0; }
 // Tessellation (Preprocess' point source).  Returns the count; pointer valid until the next call.
 uint64_t skh_tessellate(skh_scene *s, float minDist, int incenter, const void **pts) {
     s->points.clear();
@@ -202,7 +204,8 @@ int skh_build_profile(skh_scene *s, skc_ctx *ctx, const float *rhoHd, uint32_t *
             if ((rc = skc_rho_table(ctx, s->sd.skin.roughness, 1.f, s->sd.skin.layerIor[0], 0, rho.data()))) return rc;
             rhoHd = rho.data();
         }
-        return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd);
+        if ((rc = skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rhoHd))) return rc;
+        return InstallAlbedo(ctx, s->sd.skin, s->sd.mix);
     }
     return 0;
 }

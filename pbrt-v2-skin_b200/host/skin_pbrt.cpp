@@ -359,12 +359,13 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
         if (t.empty()) t = mp.FindTexture(tex);
         if (!t.empty()) { Error("layeredskin \"texture %s\" \"%s\": textures on the skin are not supported on the device path (constant albedo, no bump map)", tex, t.c_str()); return false; }
     }
-    // Parameters the device path cannot honour are refused by name, not dropped: "color albedo" scales E by albedo^mix and
-    // Li by albedo^(1-mix) (multipolesubsurface.cpp:139-140,287), "doublerefsslf" swaps in FixedFresnelDielectric
+    // Parameters the device path cannot honour are refused by name, not dropped: "doublerefsslf" swaps in FixedFresnelDielectric
     // (layeredskin.cpp:103-109), "genprofile false" / "usemontecarlo true" select other profile sources (:97-101).
     auto B = [&](const char *n, bool d) { return shapeParams.FindOneBool(n, mp.FindOneBool(n, d)); };
-    if (mp.FindFloats("albedo", "color", "spectrum") || shapeParams.FindFloats("albedo", "color", "spectrum")) {
-        Error("layeredskin \"color albedo\": a constant albedo other than the default Spectrum(1) is not supported on the device path"); return false; }
+    if (mp.FindFloats("albedo", "color", "spectrum") || shapeParams.FindFloats("albedo", "color", "spectrum")) {      // GetSpectrumTexture("albedo", Spectrum(1.f)) :247
+        if (!greyColor(mp, "albedo", k.albedo, "layeredskin") || !greyColor(shapeParams, "albedo", k.albedo, "layeredskin")) return false;
+        k.hasAlbedo = true;
+    }
     if (B("doublerefsslf", false)) { Error("layeredskin \"bool doublerefsslf\" \"true\" is not supported on the device path"); return false; }
     if (!B("genprofile", true)) { Error("layeredskin \"bool genprofile\" \"false\" is not supported on the device path (the multipole profile is always generated)"); return false; }
     if (B("usemontecarlo", false)) { Error("layeredskin \"bool usemontecarlo\" \"true\" is not supported on the device path (multipole profiles only)"); return false; }

@@ -51,6 +51,14 @@ int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm) {
     return skc_upload_profile(ctx, t.rd.data(), t.rcpDsqSpacing, t.len, rho.data());
 }
 
+int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix) {
+    if (!skin.hasAlbedo) return skc_set_albedo_factors(ctx, nullptr, nullptr);
+    float al[30], a[30], b[30];
+    RGBToSpectrum(skin.albedo, al);                                           // "color albedo": Spectrum::FromRGB, reflectance
+    for (int i = 0; i < 30; ++i) { a[i] = powf(al[i], mix); b[i] = powf(al[i], 1.f - mix); }      // Pow(Spectrum, float): powf per sample
+    return skc_set_albedo_factors(ctx, a, b);
+}
+
 int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
     const TriangleMesh &m = *b.mesh;
     float o2w[32];
@@ -75,7 +83,7 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     double t0 = now();
     if (!dev(UploadScene(ctx, built))) return false;
     double t1 = now();
-    if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(skc_synchronize(ctx))) return false;
+    if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(InstallAlbedo(ctx, sd.skin, sd.mix)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
     // the camera pass's Preprocess-independent part (sampler stream, camera rays, closest hits, direct lighting) goes to the
     // second stream first and runs beside Preprocess

@@ -343,6 +343,7 @@ bool SceneDesc::LoadLines(const std::string &path) {
                 if (k == "layers") ls >> skin.layerThickness[0] >> skin.layerIor[0] >> skin.layerThickness[1] >> skin.layerIor[1];
                 else if (k == "Kr") ls >> skin.Kr[0] >> skin.Kr[1] >> skin.Kr[2];
                 else if (k == "Kt") ls >> skin.Kt[0] >> skin.Kt[1] >> skin.Kt[2];
+                else if (k == "albedo") { ls >> skin.albedo[0] >> skin.albedo[1] >> skin.albedo[2]; skin.hasAlbedo = true; }
                 else {
                     float v; ls >> v;
                     if (k == "roughness") skin.roughness = v; else if (k == "nmperunit") skin.nmperunit = v;

@@ -55,6 +55,10 @@ struct SkinParams {
     // "color Kr" / "color Kt" as the skin scenes give them (results/PigmentManips/Eum0.1_Deoxy0.5.pbrt:37-38); the scene-file
     // format issues these two like the reference driver does.  (The material's own defaults are Spectrum(1) for both.)
     float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};
+    // "color albedo" (layeredskin.cpp:247; default Spectrum(1)): a constant; E is scaled by Pow(albedo, mix), Li's subsurface term by
+    // Pow(albedo, 1 - mix) (multipolesubsurface.cpp:139-140,287)
+    float albedo[3] = {1, 1, 1};
+    bool hasAlbedo = false;
     bool lerponthinslab = true;
     float layerThickness[2] = {0.25e6f, 20e6f}, layerIor[2] = {1.4f, 1.4f};
 };
@@ -155,7 +159,9 @@ void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, in
 
 // What api.cpp's MakeCamera / MakeFilm / MakeSampler / MakeRenderer derive from the scene for the device frame pass
 void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d);
-int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nullptr);   // comm: the wavelengths dealt over its ranks
+int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nullptr);
+// the two albedo factors of the material for an integrator's `mix` -> skc_set_albedo_factors (cleared when the albedo is the default)
+int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,

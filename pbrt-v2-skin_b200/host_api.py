@@ -36,6 +36,7 @@ def load_host_library():
     lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
     lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
+    lib.skh_skin_albedo.restype = C.c_int; lib.skh_skin_albedo.argtypes = [vp, vp]
     lib.skh_tessellate.restype = C.c_uint64; lib.skh_tessellate.argtypes = [vp, C.c_float, C.c_int, C.POINTER(vp)]
     lib.skh_count_points.restype = C.c_uint64; lib.skh_count_points.argtypes = [vp, C.c_float]
     lib.skh_camera_rays.restype = None; lib.skh_camera_rays.argtypes = [vp, vp, C.c_uint64, vp]
@@ -140,6 +141,11 @@ class HostScene:
         p = C.c_void_p()
         n = self.lib.skh_bench_rays(self.h, C.byref(p))
         return _view(p.value, 32 * n, np.float32).reshape(-1, 8)
+
+    def albedo_rgb(self):
+        """The material's \"color albedo\" (rgb), or None when the scene leaves it at Spectrum(1)."""
+        rgb = np.zeros(3, np.float32)
+        return rgb if self.lib.skh_skin_albedo(self.h, rgb.ctypes.data_as(C.c_void_p)) else None
 
     def irradiance_tasks(self, n_points, n_cores=1):
         return int(self.lib.skh_irradiance_tasks(n_points, n_cores))

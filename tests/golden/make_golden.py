@@ -313,8 +313,8 @@ def mpc512_golden():
 
 
 if __name__ == "__main__":
-    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "skin_lights", "mpc_kat"]
+    what = sys.argv[1:] or ["skin_tiny", "skin_ld4", "tissue", "skin_lights", "skin_albedo", "mpc_kat"]
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w == "skin_lights" else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo") else scene_golden(w)
