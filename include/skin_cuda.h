@@ -45,7 +45,8 @@ typedef struct {
  *   radius < 0: a delta light without a shape -- radius = -1 PointLight (lights/point.cpp), -2 SpotLight
  *     (lights/spot.cpp), -3 DistantLight (lights/distant.cpp); o2w / w2o = LightToWorld / WorldToLight; spot: zmin =
  *     cosTotalWidth, zmax = cosFalloffStart; distant: (zmin, zmax, phiMax) = lightDir (world space, normalised); Lemit =
- *     Intensity (point, spot) or L (distant); nSamples = 1; the other fields 0. */
+ *     Intensity (point, spot) or L (distant); nSamples = 1; the other fields 0.  radius = -4: InfiniteAreaLight (lights/infinite.cpp),
+ *     not a delta light: zmin / zmax = width / height of its radiance map (skc_upload_envmap), nSamples; Lemit unused. */
 typedef struct {
     float o2w[16], w2o[16];            /* ObjectToWorld matrix and its inverse, row-major */
     float radius, zmin, zmax, phiMax;
@@ -219,6 +220,13 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * only.  stats8 = {rows, shared-memory bytes, coverage, largest verified relative error inside the windows, and
  * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
  * global tables, 0}. */
+/* LightSource "infinite" (lights/infinite.cpp): its light record has radius -4, o2w / w2o = LightToWorld / WorldToLight, zmin / zmax =
+ * the radiance map's width / height, nSamples; the map and its Distribution2D (core/montecarlo.h) come through this call, as
+ * InfiniteAreaLight's constructor prepares them (the host mirror does: host/skin_envmap.cpp): rgb [h][w][3] level-0 texels,
+ * condFunc [h][w], condCdf [h][w + 1], condInt [h] (the rows' Distribution1D), margFunc [h], margCdf [h + 1], margInt (the
+ * marginal).  One infinite light per scene; w == 0 removes the map. */
+int skc_upload_envmap(skc_ctx *ctx, uint32_t w, uint32_t h, const float *rgb, const float *condFunc, const float *condCdf,
+                      const float *condInt, const float *margFunc, const float *margCdf, float margInt);
 /* LayeredSkin's constant "color albedo" (materials/layeredskin.cpp:183,247; multipolesubsurface.cpp:139-140,287): the
  * irradiance pass scales E by Pow(albedo, mix), Li scales the subsurface term by Pow(albedo, 1 - mix).  The caller passes the two
  * 30-entry factors, made with the host's powf (the reference's own values); they apply to every later skc_irradiance* and

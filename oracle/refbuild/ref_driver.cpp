@@ -50,6 +50,7 @@
 #include "lights/point.h"
 #include "lights/spot.h"
 #include "lights/distant.h"
+#include "lights/infinite.h"
 #include "core/multipole.h"
 #include "core/reflection.h"
 #include "core/film.h"
@@ -110,7 +111,7 @@ struct SceneDesc {
     float lookat[9] = {0, -5, 0, 0, 0, 0, 0, 0, 1};
     float fov = 30.f;
     std::map<std::string, float> integ;
-    struct Light { float t[3], radius, L[3]; int ns; int kind = 0; float to[3] = {0, 0, 1}, cone = 30.f, delta = 5.f; };   // kind 0 sphere area, 1 point, 2 spot, 3 distant
+    struct Light { float t[3], radius, L[3]; int ns; int kind = 0; float to[3] = {0, 0, 1}, cone = 30.f, delta = 5.f; std::string map; float rotz = 0.f; };   // kind 0 sphere area, 1 point, 2 spot, 3 distant, 4 infinite
     std::vector<Light> lights;
     std::map<std::string, float> skin;
     float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
@@ -150,6 +151,14 @@ static SceneDesc parseScene(const std::string &path) {
             if (l.kind != 1) ls >> l.to[0] >> l.to[1] >> l.to[2];
             ls >> l.L[0] >> l.L[1] >> l.L[2];
             if (l.kind == 2) ls >> l.cone >> l.delta;
+            sd.lights.push_back(l);
+        }
+        else if (key == "envlight") {
+            // envlight <map.pfm | none> r g b nsamples rotz : LightSource "infinite" "color L" [r g b] "integer nsamples" "string mapname",
+            // under Rotate rotz 0 0 1 (lights/infinite.cpp:185-193)
+            SceneDesc::Light l; l.kind = 4; l.radius = 0.f; l.t[0] = l.t[1] = l.t[2] = 0.f;
+            ls >> l.map >> l.L[0] >> l.L[1] >> l.L[2] >> l.ns >> l.rotz;
+            if (l.map == "none") l.map.clear(); else if (l.map[0] != '/') l.map = dir + l.map;
             sd.lights.push_back(l);
         }
         else if (key == "skin") {
@@ -204,6 +213,15 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
     pbrtWorldBegin();
     for (auto &l : sd.lights) {
         pbrtAttributeBegin();
+        if (l.kind == 4) {
+            ParamSet ps;
+            ps.AddRGBSpectrum("L", l.L, 3); addI(ps, "nsamples", l.ns);
+            if (!l.map.empty()) ps.AddString("mapname", &l.map, 1);
+            pbrtRotate(l.rotz, 0.f, 0.f, 1.f);
+            pbrtLightSource("infinite", ps);
+            pbrtAttributeEnd();
+            continue;
+        }
         if (l.kind != 0) {
             ParamSet ps;
             Point from(l.t[0], l.t[1], l.t[2]), to(l.to[0], l.to[1], l.to[2]);
@@ -295,6 +313,13 @@ static void dumpSpectrumConsts(const std::string &dir) {
                                     &SampledSpectrum::rgbRefl2SpectBlue};
     for (int k = 0; k < 7; ++k) for (int i = 0; i < nSpectralSamples; ++i) bases.push_back(bs[k]->c[i]);
     dump(dir + "/rgb_refl_bases30.bin", bases.data(), bases.size());
+    // ... and the illuminant set (FromRGB(.., SPECTRUM_ILLUMINANT), what InfiniteAreaLight turns its map's texels into): kRGBIllum2Spect30
+    std::vector<float> ill;
+    const SampledSpectrum *is[7] = {&SampledSpectrum::rgbIllum2SpectWhite, &SampledSpectrum::rgbIllum2SpectCyan, &SampledSpectrum::rgbIllum2SpectMagenta,
+                                    &SampledSpectrum::rgbIllum2SpectYellow, &SampledSpectrum::rgbIllum2SpectRed, &SampledSpectrum::rgbIllum2SpectGreen,
+                                    &SampledSpectrum::rgbIllum2SpectBlue};
+    for (int k = 0; k < 7; ++k) for (int i = 0; i < nSpectralSamples; ++i) ill.push_back(is[k]->c[i]);
+    dump(dir + "/rgb_illum_bases30.bin", ill.data(), ill.size());
 }
 
 static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
@@ -414,6 +439,26 @@ static void dumpLights(const std::string &dir, const Scene *scene, Meta &meta) {
             dumpTransform(out, dd->LightToWorld);
             float r[8] = {-3.f, dd->lightDir.x, dd->lightDir.y, dd->lightDir.z, 1.f, 0, 0, 0}; out.insert(out.end(), r, r + 8);
             for (int i = 0; i < nSpectralSamples; ++i) out.push_back(dd->L.c[i]);
+            continue;
+        }
+        if (const InfiniteAreaLight *il = dynamic_cast<const InfiniteAreaLight *>(l)) {
+            // radius -4; zmin / zmax = the map's width / height; the map and its sampling distribution go to envmap.bin:
+            // int32 w, h; level-0 texels rgb[h][w][3]; conditional func[h][w], cdf[h][w+1], funcInt[h]; marginal func[h], cdf[h+1], funcInt
+            dumpTransform(out, il->LightToWorld);
+            const int w = (int)il->radianceMap->width, h = (int)il->radianceMap->height;
+            float r[8] = {-4.f, (float)w, (float)h, 0, (float)il->nSamples, 0, 0, 0}; out.insert(out.end(), r, r + 8);
+            for (int i = 0; i < nSpectralSamples; ++i) out.push_back(0.f);
+            std::vector<float> env;
+            int32_t wh[2] = {w, h}; float whf[2]; memcpy(whf, wh, 8); env.push_back(whf[0]); env.push_back(whf[1]);
+            for (int t = 0; t < h; ++t) for (int s2 = 0; s2 < w; ++s2) { float c3[3]; il->radianceMap->Texel(0, s2, t).ToRGB(c3); env.push_back(c3[0]); env.push_back(c3[1]); env.push_back(c3[2]); }
+            const Distribution2D *d2 = il->distribution;
+            for (int v = 0; v < h; ++v) env.insert(env.end(), d2->pConditionalV[v]->func, d2->pConditionalV[v]->func + w);
+            for (int v = 0; v < h; ++v) env.insert(env.end(), d2->pConditionalV[v]->cdf, d2->pConditionalV[v]->cdf + w + 1);
+            for (int v = 0; v < h; ++v) env.push_back(d2->pConditionalV[v]->funcInt);
+            env.insert(env.end(), d2->pMarginal->func, d2->pMarginal->func + h);
+            env.insert(env.end(), d2->pMarginal->cdf, d2->pMarginal->cdf + h + 1);
+            env.push_back(d2->pMarginal->funcInt);
+            dump(dir + "/envmap.bin", env.data(), env.size());
             continue;
         }
         const DiffuseAreaLight *dl = dynamic_cast<const DiffuseAreaLight *>(l);

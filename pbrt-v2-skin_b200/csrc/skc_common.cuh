@@ -18,6 +18,15 @@
 #define SKC_EPAD 32            // spectral rows are padded to 32 floats = one 128 B line
 #define SKC_NSTAGES 12
 
+// InfiniteAreaLight's radiance map and Distribution2D on the device (skc_upload_envmap; lights/infinite.cpp, core/montecarlo.h)
+struct EnvMapDev {
+    const float *rgb = nullptr;                      // [h][w][3] level-0 texels
+    const float *condFunc = nullptr, *condCdf = nullptr, *condInt = nullptr;      // [h][w], [h][w + 1], [h]
+    const float *margFunc = nullptr, *margCdf = nullptr;                          // [h], [h + 1]
+    float margInt = 0.f;
+    int w = 0, h = 0;
+};
+
 struct skc_ctx {
     int device = 0;
     int smCount = 148;
@@ -69,6 +78,8 @@ struct skc_ctx {
     float mocInvA = 0.f, mocM = 0.f;
     int moTable = 1;               // 1 = k_mo_lambda (compact table in shared memory + exact fallback) when the table's windows cover enough of the tables (MOC_MIN_COVERAGE), else k_mo_packet; 0 = always k_mo_packet, 2 = always k_mo_lambda; env SKC_MO_TABLE=exact|auto|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
+    EnvMapDev env;                    // of the scene's infinite light (light record with radius -4); env.rgb == nullptr: none
+    float *envStore = nullptr;        // one allocation behind env's pointers
     float *albedoFactors = nullptr;   // [2][32]: Pow(albedo, mix), Pow(albedo, 1 - mix) of a constant "color albedo" (skc_set_albedo_factors); null = Spectrum(1)
     uint64_t moHist[8] = {0};
     int moPacketHits = 0;        // SKC_MO_PACKET_HITS: 0 = by launch size, else 8 / 16 / 32 hits per packet of k_mo_lambda
@@ -290,4 +301,53 @@ __device__ __forceinline__ float skc_atanf(float x) {      // sysdeps/ieee754/fl
     if (id < 0) return __fsub_rn(x, __fmul_rn(x, __fadd_rn(s1, s2)));
     const float zr = __fsub_rn(atanhi[id], __fsub_rn(__fsub_rn(__fmul_rn(x, __fadd_rn(s1, s2)), atanlo[id]), x));
     return hx < 0 ? -zr : zr;
+}
+
+__device__ __forceinline__ float skc_acosf(float x) {      // sysdeps/ieee754/flt-32/e_acosf.c (fdlibm, fp32, no contraction); tools/libm_check.c
+    const float pi = 3.1415925026e+00f, pio2_hi = 1.5707962513e+00f, pio2_lo = 7.5497894159e-08f;
+    const float pS0 = 1.6666667163e-01f, pS1 = -3.2556581497e-01f, pS2 = 2.0121252537e-01f, pS3 = -4.0055535734e-02f, pS4 = 7.9153501429e-04f, pS5 = 3.4793309169e-05f;
+    const float qS1 = -2.4033949375e+00f, qS2 = 2.0209457874e+00f, qS3 = -6.8828397989e-01f, qS4 = 7.7038154006e-02f;
+    const int32_t hx = __float_as_int(x), ix = hx & 0x7fffffff;
+    if (ix == 0x3f800000) return hx > 0 ? 0.0f : __fadd_rn(pi, __fmul_rn(2.0f, pio2_lo));
+    if (ix > 0x3f800000) return __int_as_float(0x7fc00000);
+    auto P = [&](float z) { return __fmul_rn(z, __fadd_rn(pS0, __fmul_rn(z, __fadd_rn(pS1, __fmul_rn(z, __fadd_rn(pS2, __fmul_rn(z, __fadd_rn(pS3, __fmul_rn(z, __fadd_rn(pS4, __fmul_rn(z, pS5))))))))))); };
+    auto Q = [&](float z) { return __fadd_rn(1.0f, __fmul_rn(z, __fadd_rn(qS1, __fmul_rn(z, __fadd_rn(qS2, __fmul_rn(z, __fadd_rn(qS3, __fmul_rn(z, qS4)))))))); };
+    if (ix < 0x3f000000) {
+        if (ix <= 0x23000000) return __fadd_rn(pio2_hi, pio2_lo);
+        const float z = __fmul_rn(x, x), r = __fdiv_rn(P(z), Q(z));
+        return __fsub_rn(pio2_hi, __fsub_rn(x, __fsub_rn(pio2_lo, __fmul_rn(x, r))));
+    }
+    if (hx < 0) {
+        const float z = __fmul_rn(__fadd_rn(1.0f, x), 0.5f), s = __fsqrt_rn(z), r = __fdiv_rn(P(z), Q(z));
+        const float w = __fsub_rn(__fmul_rn(r, s), pio2_lo);
+        return __fsub_rn(pi, __fmul_rn(2.0f, __fadd_rn(s, w)));
+    }
+    const float z = __fmul_rn(__fsub_rn(1.0f, x), 0.5f), s = __fsqrt_rn(z);
+    const float df = __int_as_float(__float_as_int(s) & 0xfffff000);
+    const float c = __fdiv_rn(__fsub_rn(z, __fmul_rn(df, df)), __fadd_rn(s, df));
+    const float r = __fdiv_rn(P(z), Q(z)), w = __fadd_rn(__fmul_rn(r, s), c);
+    return __fmul_rn(2.0f, __fadd_rn(df, w));
+}
+__device__ __forceinline__ float skc_atan2f(float y, float x) {      // sysdeps/ieee754/flt-32/e_atan2f.c (fdlibm); tools/libm_check.c
+    const float tiny = 1.0e-30f, pi_o_4 = 7.8539818525e-01f, pi_o_2 = 1.5707963705e+00f, pi = 3.1415927410e+00f, pi_lo = -8.7422776573e-08f;
+    const int32_t hx = __float_as_int(x), hy = __float_as_int(y), ix = hx & 0x7fffffff, iy = hy & 0x7fffffff;
+    if (ix > 0x7f800000 || iy > 0x7f800000) return x + y;
+    if (hx == 0x3f800000) return skc_atanf(y);
+    const int m = ((hy >> 31) & 1) | ((hx >> 30) & 2);
+    if (iy == 0) return m < 2 ? y : (m == 2 ? __fadd_rn(pi, tiny) : __fsub_rn(-pi, tiny));
+    if (ix == 0) return hy < 0 ? __fsub_rn(-pi_o_2, tiny) : __fadd_rn(pi_o_2, tiny);
+    if (ix == 0x7f800000) {
+        if (iy == 0x7f800000) return m == 0 ? __fadd_rn(pi_o_4, tiny) : m == 1 ? __fsub_rn(-pi_o_4, tiny) : m == 2 ? __fadd_rn(__fmul_rn(3.0f, pi_o_4), tiny) : __fsub_rn(__fmul_rn(-3.0f, pi_o_4), tiny);
+        return m == 0 ? 0.0f : m == 1 ? -0.0f : m == 2 ? __fadd_rn(pi, tiny) : __fsub_rn(-pi, tiny);
+    }
+    if (iy == 0x7f800000) return hy < 0 ? __fsub_rn(-pi_o_2, tiny) : __fadd_rn(pi_o_2, tiny);
+    const int k = (iy - ix) >> 23;
+    float z;
+    if (k > 60) z = __fadd_rn(pi_o_2, __fmul_rn(0.5f, pi_lo));
+    else if (hx < 0 && k < -60) z = 0.0f;
+    else z = skc_atanf(fabsf(__fdiv_rn(y, x)));
+    if (m == 0) return z;
+    if (m == 1) return __int_as_float(__float_as_int(z) ^ 0x80000000);
+    if (m == 2) return __fsub_rn(pi, __fsub_rn(z, pi_lo));
+    return __fsub_rn(__fsub_rn(z, pi_lo), pi);
 }

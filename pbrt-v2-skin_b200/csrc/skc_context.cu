@@ -96,7 +96,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhWide, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->mocRows, ctx->mocHeads, ctx->mocLam, ctx->mocHeadOff, ctx->lights, ctx->ipPosArea, ctx->ipE,
-                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors};
+                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors, ctx->envStore};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
     for (int i = 0; i < 24; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -125,6 +125,30 @@ extern "C" int skc_synchronize(skc_ctx *ctx) {
 }
 
 extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
+// The radiance map and sampling distribution of the scene's infinite light (light record with radius -4).  w, h: texels; rgb
+// [h][w][3]; condFunc [h][w], condCdf [h][w + 1], condInt [h]; margFunc [h], margCdf [h + 1].  w == 0 removes it.
+extern "C" int skc_upload_envmap(skc_ctx *ctx, uint32_t w, uint32_t h, const float *rgb, const float *condFunc, const float *condCdf,
+                                 const float *condInt, const float *margFunc, const float *margCdf, float margInt) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->envStore) { cudaFree(ctx->envStore); ctx->envStore = nullptr; }
+    ctx->env = EnvMapDev();
+    if (!w || !h) return 0;
+    if (!rgb || !condFunc || !condCdf || !condInt || !margFunc || !margCdf) return skc_fail(ctx, "skc_upload_envmap: null array");
+    const size_t n = (size_t)w * h, sizes[6] = {3 * n, n, (size_t)h * (w + 1), h, h, (size_t)h + 1};
+    const float *src[6] = {rgb, condFunc, condCdf, condInt, margFunc, margCdf};
+    size_t total = 0, off[6];
+    for (int k = 0; k < 6; ++k) { off[k] = total; total += (sizes[k] + 3) & ~(size_t)3; }
+    SKC_CUDA(cudaMalloc((void **)&ctx->envStore, total * sizeof(float)));
+    for (int k = 0; k < 6; ++k) SKC_CUDA(cudaMemcpyAsync(ctx->envStore + off[k], src[k], sizes[k] * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    EnvMapDev &e = ctx->env;
+    e.rgb = ctx->envStore + off[0]; e.condFunc = ctx->envStore + off[1]; e.condCdf = ctx->envStore + off[2]; e.condInt = ctx->envStore + off[3];
+    e.margFunc = ctx->envStore + off[4]; e.margCdf = ctx->envStore + off[5]; e.margInt = margInt; e.w = (int)w; e.h = (int)h;
+    return 0;
+}
+
 // LayeredSkin's "color albedo" (materials/layeredskin.cpp:183,247): the irradiance pass scales E by Pow(albedo, mix) and Li the
 // subsurface term by Pow(albedo, 1 - mix) (multipolesubsurface.cpp:139-140,287).  For a constant albedo both are 30 numbers,
 // made by the caller with the host's powf so that they are the reference's own values.  NULL, NULL = Spectrum(1).
@@ -203,9 +227,9 @@ __global__ void k_test_sincosf(const float *__restrict__ x, uint64_t n, float *_
 }
 __global__ void k_test_libmf(int fn, const float *__restrict__ x, uint64_t n, float *__restrict__ out) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = fn == 2 ? skc_logf(x[i]) : fn == 3 ? skc_expf(x[i]) : fn == 4 ? skc_atanf(x[i]) : fn == 1 ? skc_cosf(x[i]) : skc_sinf(x[i]);
+    if (i < n) out[i] = fn == 6 ? skc_atan2f(x[i], x[n - 1 - i]) : fn == 5 ? skc_acosf(x[i]) : fn == 2 ? skc_logf(x[i]) : fn == 3 ? skc_expf(x[i]) : fn == 4 ? skc_atanf(x[i]) : fn == 1 ? skc_cosf(x[i]) : skc_sinf(x[i]);
 }
-// fn: 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf
+// fn: 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf, 5 acosf, 6 atan2f(x[i], x[n - 1 - i])
 extern "C" int skc_test_libmf(skc_ctx *ctx, int fn, const float *x, uint64_t n, float *out) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);

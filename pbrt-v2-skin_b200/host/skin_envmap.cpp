@@ -1,0 +1,174 @@
+// skin_envmap.cpp -- LightSource "infinite" on the host side: what InfiniteAreaLight's constructor prepares
+// (lights/infinite.cpp:67-103), as flat arrays for the device.
+//
+//   texels      ReadImagePFM (core/imageio.cpp:315-395: rows in file order, no flip) times L.ToRGBSpectrum(); without a map one
+//               texel = L.ToRGBSpectrum()
+//   pyramid     MIPMap<RGBSpectrum> (core/mipmap.h:111-196) for power-of-two maps: each level the .25f-weighted sum of four
+//               texels of the finer one; other resolutions would be Lanczos-resampled first and are refused
+//   img         Lookup(u / w, v / h, 1 / max(w, h)).y() * sinf(M_PI * (v + .5f) / h): the trilinear lookup of mipmap.h:239-271
+//   sampling    Distribution2D / Distribution1D (core/montecarlo.h:55-77, montecarlo.cpp:358-370): step-function cdfs,
+//               fp32 running sums in index order
+//
+// The results must equal the reference's arrays bit for bit (tests/test_envlight.py compares them with its export), so the
+// arithmetic is spelt in its operation order and uses the same libm (logf for the level, sinf for the row weight).
+#include "skin_scene.h"
+#include "skin_cie.h"
+#include <cstdio>
+
+namespace skin {
+
+namespace {
+
+inline int WrapIndex(int a, int b) { int n = a / b; a -= n * b; if (a < 0) a += b; return a; }      // Mod (core/pbrt.h)
+inline int FloorToInt(float v) { return (int)floorf(v); }
+
+struct Rgb { float r, g, b; };
+inline Rgb operator+(Rgb a, Rgb b) { return {a.r + b.r, a.g + b.g, a.b + b.b}; }
+inline Rgb operator*(float s, Rgb a) { return {a.r * s, a.g * s, a.b * s}; }         // Spectrum * float, per component
+
+struct Pyramid {
+    struct Level { int w, h; std::vector<Rgb> px; };
+    std::vector<Level> levels;
+    const Rgb &At(int level, int s, int t) const {                                   // Texel, TEXTURE_REPEAT
+        const Level &l = levels[level];
+        return l.px[(size_t)WrapIndex(t, l.h) * l.w + WrapIndex(s, l.w)];
+    }
+    void Build(int w, int h, const std::vector<Rgb> &img) {
+        const float invLog2 = 1.f / logf(2.f);
+        const int n = 1 + FloorToInt(logf(float(std::max(w, h))) * invLog2);          // 1 + Log2Int(float(max(sres, tres)))
+        levels.resize(n);
+        levels[0] = {w, h, img};
+        for (int i = 1; i < n; ++i) {
+            const int sw = std::max(1, levels[i - 1].w / 2), sh = std::max(1, levels[i - 1].h / 2);
+            levels[i].w = sw; levels[i].h = sh; levels[i].px.resize((size_t)sw * sh);
+            for (int t = 0; t < sh; ++t)
+                for (int s = 0; s < sw; ++s)
+                    levels[i].px[(size_t)t * sw + s] = .25f * (At(i - 1, 2 * s, 2 * t) + At(i - 1, 2 * s + 1, 2 * t) + At(i - 1, 2 * s, 2 * t + 1) + At(i - 1, 2 * s + 1, 2 * t + 1));
+        }
+    }
+    Rgb Bilinear(int level, float s, float t) const {                               // MIPMap::triangle
+        level = std::min(std::max(level, 0), (int)levels.size() - 1);
+        s = s * levels[level].w - 0.5f;
+        t = t * levels[level].h - 0.5f;
+        const int s0 = FloorToInt(s), t0 = FloorToInt(t);
+        const float ds = s - s0, dt = t - t0;
+        return (1.f - ds) * (1.f - dt) * At(level, s0, t0) + (1.f - ds) * dt * At(level, s0, t0 + 1) +
+               ds * (1.f - dt) * At(level, s0 + 1, t0) + ds * dt * At(level, s0 + 1, t0 + 1);
+    }
+    Rgb Lookup(float s, float t, float width) const {                               // MIPMap::Lookup(s, t, width)
+        const unsigned nLevels = (unsigned)levels.size();
+        const float invLog2 = 1.f / logf(2.f);
+        const float level = nLevels - 1 + logf(std::max(width, 1e-8f)) * invLog2;
+        if (level < 0) return Bilinear(0, s, t);
+        if (level >= nLevels - 1) return At((int)nLevels - 1, 0, 0);
+        const unsigned iLevel = (unsigned)FloorToInt(level);
+        const float delta = level - iLevel;
+        return (1.f - delta) * Bilinear((int)iLevel, s, t) + delta * Bilinear((int)iLevel + 1, s, t);
+    }
+};
+
+// Distribution1D's constructor: cdf[n + 1] and the integral of the step function
+float StepCdf(const float *f, int n, float *cdf) {
+    cdf[0] = 0.f;
+    for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + f[i - 1] / n;
+    const float funcInt = cdf[n];
+    if (funcInt == 0.f) for (int i = 1; i < n + 1; ++i) cdf[i] = float(i) / float(n);
+    else for (int i = 1; i < n + 1; ++i) cdf[i] /= funcInt;
+    return funcInt;
+}
+
+bool ReadPfm(const std::string &path, int *w, int *h, std::vector<Rgb> *out, std::string *err) {
+    FILE *fp = fopen(path.c_str(), "rb");
+    if (!fp) { *err = "Unable to read image \"" + path + "\""; return false; }
+    auto word = [&](char *buf, int cap) {          // one whitespace-terminated word, as the reference's reader takes them
+        int n = 0, c = fgetc(fp);
+        while (c != EOF && c != ' ' && c != '\n' && c != '\t' && c != '\r' && n < cap - 1) { buf[n++] = (char)c; c = fgetc(fp); }
+        buf[n] = 0;
+        return n;
+    };
+    char buf[80];
+    bool ok = word(buf, 80) > 0;
+    const int nCh = !strcmp(buf, "PF") ? 3 : !strcmp(buf, "Pf") ? 1 : 0;
+    float scale = 0.f;
+    ok = ok && nCh && word(buf, 80) > 0; *w = atoi(buf);
+    ok = ok && word(buf, 80) > 0; *h = atoi(buf);
+    ok = ok && word(buf, 80) > 0 && sscanf(buf, "%f", &scale) == 1 && *w > 0 && *h > 0;
+    std::vector<float> data;
+    if (ok) { data.resize((size_t)nCh * *w * *h); ok = fread(data.data(), 4, data.size(), fp) == data.size(); }
+    fclose(fp);
+    if (!ok) { *err = "Unable to read image \"" + path + "\" (PFM expected)"; return false; }
+    if (!(scale < 0.f))                            // big-endian file on a little-endian host
+        for (float &v : data) { unsigned char b[4]; memcpy(b, &v, 4); std::swap(b[0], b[3]); std::swap(b[1], b[2]); memcpy(&v, b, 4); }
+    if (fabsf(scale) != 1.f) for (float &v : data) v *= fabsf(scale);
+    out->resize((size_t)*w * *h);
+    for (size_t i = 0; i < out->size(); ++i) (*out)[i] = nCh == 1 ? Rgb{data[i], data[i], data[i]} : Rgb{data[3 * i], data[3 * i + 1], data[3 * i + 2]};
+    return true;
+}
+
+}  // namespace
+
+// SampledSpectrum::ToRGB (core/spectrum.h:374-398): ToXYZ's running sums over the 30 samples, then XYZToRGB
+void SpectrumToRGB(const float c[30], float rgb[3]) {
+    float xyz[3] = {0.f, 0.f, 0.f};
+    for (int i = 0; i < 30; ++i) { xyz[0] += kCieXYZ30[0][i] * c[i]; xyz[1] += kCieXYZ30[1][i] * c[i]; xyz[2] += kCieXYZ30[2][i] * c[i]; }
+    const float scale = float(700 - 400) / float(kCieYIntegral * 30);
+    xyz[0] *= scale; xyz[1] *= scale; xyz[2] *= scale;
+    rgb[0] = 3.240479f * xyz[0] - 1.537150f * xyz[1] - 0.498535f * xyz[2];
+    rgb[1] = -0.969256f * xyz[0] + 1.875991f * xyz[1] + 0.041556f * xyz[2];
+    rgb[2] = 0.055648f * xyz[0] - 0.204043f * xyz[1] + 1.057311f * xyz[2];
+}
+
+// CreateInfiniteLight + the InfiniteAreaLight constructor (lights/infinite.cpp:67-103,185-193)
+bool MakeInfiniteLight(const Transform &l2w, const float Lrgb[3], const float *scaleRgb, int nSamples, const std::string &mapname,
+                       bool quickRender, SphereLight *light, EnvMap *env, std::string *err) {
+    float L[30], sc[30], rgbL[3];
+    RGBToSpectrum(Lrgb, L);                                                       // FindOneSpectrum("L"): FromRGB, reflectance
+    if (scaleRgb) { RGBToSpectrum(scaleRgb, sc); for (int i = 0; i < 30; ++i) L[i] *= sc[i]; }      // L * sc; the default scale is Spectrum(1.0)
+    SpectrumToRGB(L, rgbL);                                                       // L.ToRGBSpectrum()
+    int w = 1, h = 1;
+    std::vector<Rgb> texels;
+    if (!mapname.empty()) {
+        if (!ReadPfm(mapname, &w, &h, &texels, err)) return false;
+        if ((w & (w - 1)) || (h & (h - 1))) {
+            *err = "LightSource \"infinite\": environment map \"" + mapname + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)";
+            return false;
+        }
+        for (Rgb &t : texels) { t.r *= rgbL[0]; t.g *= rgbL[1]; t.b *= rgbL[2]; }
+    } else texels.assign(1, Rgb{rgbL[0], rgbL[1], rgbL[2]});
+    Pyramid mip;
+    mip.Build(w, h, texels);
+    // scalar image for the sampling distribution
+    const float filter = 1.f / std::max(w, h);
+    const float pi = 3.14159265358979323846f;                                     // M_PI is a float literal in the reference (core/pbrt.h)
+    std::vector<float> img((size_t)w * h);
+    for (int v = 0; v < h; ++v) {
+        const float vp = (float)v / (float)h;
+        const float sinTheta = sinf(pi * float(v + .5f) / float(h));
+        for (int u = 0; u < w; ++u) {
+            const float up = (float)u / (float)w;
+            const Rgb c = mip.Lookup(up, vp, filter);
+            float y = 0.212671f * c.r + 0.715160f * c.g + 0.072169f * c.b;       // RGBSpectrum::y()
+            y *= sinTheta;
+            img[(size_t)u + (size_t)v * w] = y;
+        }
+    }
+    env->w = w; env->h = h;
+    env->rgb.resize((size_t)3 * w * h);
+    for (size_t i = 0; i < texels.size(); ++i) { env->rgb[3 * i] = texels[i].r; env->rgb[3 * i + 1] = texels[i].g; env->rgb[3 * i + 2] = texels[i].b; }
+    env->condFunc = img;
+    env->condCdf.resize((size_t)h * (w + 1)); env->condInt.resize(h);
+    for (int v = 0; v < h; ++v) env->condInt[v] = StepCdf(&img[(size_t)v * w], w, &env->condCdf[(size_t)v * (w + 1)]);
+    env->margFunc = env->condInt;
+    env->margCdf.resize(h + 1);
+    env->margInt = StepCdf(env->margFunc.data(), h, env->margCdf.data());
+    env->present = true;
+    SphereLight l; l.kind = 4; l.radius = 0.f;
+    l.nSamples = quickRender ? std::max(1, nSamples / 4) : nSamples;
+    l.ObjectToWorld = l2w;
+    l.envW = w; l.envH = h;
+    memcpy(l.Lrgb, Lrgb, 12);
+    *light = l;
+    return true;
+}
+
+}  // namespace skin

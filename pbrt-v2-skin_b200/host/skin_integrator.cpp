@@ -112,6 +112,14 @@ void skh_skin_params(const skh_scene *s, float *out12) {
                    k.layerThickness[0], k.layerIor[0], k.layerThickness[1], k.layerIor[1]};
     memcpy(out12, v, sizeof v);
 }
+// The infinite light's map and distribution (SceneDesc::env): sizes {w, h} (0, 0 = none), then the arrays by index
+// 0 rgb, 1 condFunc, 2 condCdf, 3 condInt, 4 margFunc, 5 margCdf; margInt through the return value of skh_env_sizes' float
+float skh_env_sizes(const skh_scene *s, int *wh2) { wh2[0] = s->sd.env.present ? s->sd.env.w : 0; wh2[1] = s->sd.env.present ? s->sd.env.h : 0; return s->sd.env.margInt; }
+const float *skh_env_array(const skh_scene *s, int which) {
+    const EnvMap &e = s->sd.env;
+    const std::vector<float> *v[6] = {&e.rgb, &e.condFunc, &e.condCdf, &e.condInt, &e.margFunc, &e.margCdf};
+    return which >= 0 && which < 6 ? v[which]->data() : nullptr;
+}
 // "color albedo" of the material: rgb, and whether it was given at all (Spectrum(1) otherwise)
 int skh_skin_albedo(const skh_scene *s, float *rgb3) { memcpy(rgb3, s->sd.skin.albedo, 12); return s->sd.skin.hasAlbedo ? 1 : 0; }
 // Tessellation (Preprocess' point source).  Returns the count; pointer valid until the next call.

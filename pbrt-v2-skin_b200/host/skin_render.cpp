@@ -71,6 +71,11 @@ int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
     return skc_upload_lights(ctx, b.lights.data(), (uint32_t)b.lights.size());
 }
 
+int UploadEnvMap(skc_ctx *ctx, const EnvMap &e) {
+    if (!e.present) return skc_upload_envmap(ctx, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0.f);
+    return skc_upload_envmap(ctx, (uint32_t)e.w, (uint32_t)e.h, e.rgb.data(), e.condFunc.data(), e.condCdf.data(), e.condInt.data(), e.margFunc.data(), e.margCdf.data(), e.margInt);
+}
+
 static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 // One rank's share of SamplerRenderer::Render.  comm == nullptr: the whole frame on one GPU.  With a communicator:
@@ -81,7 +86,7 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
     const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
     double t0 = now();
-    if (!dev(UploadScene(ctx, built))) return false;
+    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env))) return false;
     double t1 = now();
     if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(InstallAlbedo(ctx, sd.skin, sd.mix)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
@@ -192,7 +197,7 @@ bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *
     BuiltScene built;
     if (!BuildScene(sd, nullptr, &built, err)) return false;
     uint64_t n = 0;
-    if (UploadScene(ctx, built) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
+    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
     *nPoints = n;
     if (sd.rendererFilename.empty()) return true;                            // "(Not writing to file)"
     std::vector<skc_surface_point> pts(n);

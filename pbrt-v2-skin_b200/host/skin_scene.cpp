@@ -189,6 +189,11 @@ skc_light SphereLight::Pack(const float *Lemit30) const {
         L.radius = -(float)kind; L.zmin = L.zmax = L.phiMax = 0.f;
         if (kind == 2) { L.zmin = cosTotalWidth; L.zmax = cosFalloffStart; }
         if (kind == 3) { L.zmin = lightDir.x; L.zmax = lightDir.y; L.phiMax = lightDir.z; }
+        if (kind == 4) {      // infinite: the radiance is the map's; Lemit is not used
+            L.zmin = (float)envW; L.zmax = (float)envH; L.nSamples = (float)nSamples; L.reverseOrientation = 0.f; L.thetaMin = L.thetaMax = 0.f;
+            for (int i = 0; i < 30; ++i) L.Lemit[i] = 0.f;
+            return L;
+        }
         L.nSamples = 1.f; L.reverseOrientation = 0.f; L.thetaMin = L.thetaMax = 0.f;
         for (int i = 0; i < 30; ++i) L.Lemit[i] = Lemit30[i];
         return L;
@@ -337,6 +342,15 @@ bool SceneDesc::LoadLines(const std::string &path) {
             V3 from(f[0], f[1], f[2]), to(t[0], t[1], t[2]);
             lights.push_back(key == "pointlight" ? MakePointLight(Transform(), from, c) : key == "spotlight" ? MakeSpotLight(Transform(), from, to, c, cone, delta)
                                                  : MakeDistantLight(Transform(), from, to, c));
+        } else if (key == "envlight") {
+            // envlight <map.pfm | none> r g b nsamples rotz: LightSource "infinite" under Rotate rotz 0 0 1
+            std::string map; float c[3], rotz = 0.f; int ns = 1;
+            ls >> map >> c[0] >> c[1] >> c[2] >> ns >> rotz;
+            if (map == "none") map.clear(); else if (map[0] != '/') map = dir + map;
+            if (env.present) { error = "more than one infinite light"; return false; }
+            SphereLight l;
+            if (!MakeInfiniteLight(Transform() * Rotate(rotz, V3(0, 0, 1)), c, nullptr, ns, map, false, &l, &env, &error)) return false;
+            lights.push_back(l);
         } else if (key == "skin") {
             std::string k;
             while (ls >> k) {

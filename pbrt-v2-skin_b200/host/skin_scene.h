@@ -33,9 +33,11 @@ struct TriangleMesh {
 
 // A light of scene->lights, in scene order.  kind 0: Shape "sphere" + AreaLightSource "area" (shapes/sphere.cpp,
 // lights/diffuse.cpp); kind 1 / 2 / 3: LightSource "point" / "spot" / "distant" (lights/point.cpp, spot.cpp, distant.cpp) --
-// delta lights, no shape in the BVH.  ObjectToWorld is the shape's / the light's LightToWorld.
+// delta lights, no shape in the BVH; kind 4: LightSource "infinite" (lights/infinite.cpp), whose map and sampling distribution
+// live in SceneDesc::env.  ObjectToWorld is the shape's / the light's LightToWorld.
 struct SphereLight {
     int kind = 0;
+    int envW = 0, envH = 0;                              // infinite: resolution of the radiance map
     float cosTotalWidth = 0.f, cosFalloffStart = 0.f;    // spot (lights/spot.cpp:42-50)
     V3 lightDir;                                        // distant: Normalize(LightToWorld(from - to)) (lights/distant.cpp:42-47)
     Transform ObjectToWorld;
@@ -45,6 +47,16 @@ struct SphereLight {
     bool ReverseOrientation = false;
     skc_light Pack(const float *Lemit30) const;
     BBox WorldBound() const;
+};
+
+// InfiniteAreaLight's radiance map and Distribution2D as flat arrays (host/skin_envmap.cpp; device: skc_upload_envmap)
+struct EnvMap {
+    bool present = false;
+    int w = 0, h = 0;
+    std::vector<float> rgb;                                  // [h][w][3]: level-0 texels (map * L.ToRGBSpectrum())
+    std::vector<float> condFunc, condCdf, condInt;           // [h][w], [h][w + 1], [h]
+    std::vector<float> margFunc, margCdf;                    // [h], [h + 1]
+    float margInt = 0.f;
 };
 
 // LayeredSkin parameters (materials/layeredskin.cpp:222-262)
@@ -109,6 +121,7 @@ struct SceneDesc {
     float rendererMinDist = .25f;
     std::string rendererFilename;
     std::vector<SphereLight> lights;
+    EnvMap env;                       // of the scene's infinite light (at most one)
     SkinParams skin;
     std::vector<TriangleMesh> meshes;
     std::string error;
@@ -152,6 +165,10 @@ struct BuiltScene {
 SphereLight MakePointLight(const Transform &l2w, V3 from, const float rgb[3]);
 SphereLight MakeSpotLight(const Transform &l2w, V3 from, V3 to, const float rgb[3], float coneangle, float conedelta);
 SphereLight MakeDistantLight(const Transform &l2w, V3 from, V3 to, const float rgb[3]);
+// CreateInfiniteLight + InfiniteAreaLight's constructor (lights/infinite.cpp:67-103,185-193); scaleRgb may be null (Spectrum(1))
+bool MakeInfiniteLight(const Transform &l2w, const float Lrgb[3], const float *scaleRgb, int nSamples, const std::string &mapname,
+                       bool quickRender, SphereLight *light, EnvMap *env, std::string *err);
+void SpectrumToRGB(const float c30[30], float rgb[3]);
 bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *out, std::string *err);
 // TriangleMesh from object-space arrays the way CreateTriangleMeshShape + the TriangleMesh ctor do (shapes/trianglemesh.cpp:55-80,360-420)
 void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, int nverts, const float *P, const float *N, const float *uv,
@@ -161,7 +178,8 @@ void InitMesh(TriangleMesh *m, const Transform &o2w, bool reverseOrientation, in
 void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d);
 int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nullptr);
 // the two albedo factors of the material for an integrator's `mix` -> skc_set_albedo_factors (cleared when the albedo is the default)
-int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);   // comm: the wavelengths dealt over its ranks
+int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);
+int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,

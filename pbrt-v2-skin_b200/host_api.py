@@ -36,6 +36,8 @@ def load_host_library():
     lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
     lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
+    lib.skh_env_sizes.restype = C.c_float; lib.skh_env_sizes.argtypes = [vp, vp]
+    lib.skh_env_array.restype = vp; lib.skh_env_array.argtypes = [vp, C.c_int]
     lib.skh_skin_albedo.restype = C.c_int; lib.skh_skin_albedo.argtypes = [vp, vp]
     lib.skh_tessellate.restype = C.c_uint64; lib.skh_tessellate.argtypes = [vp, C.c_float, C.c_int, C.POINTER(vp)]
     lib.skh_count_points.restype = C.c_uint64; lib.skh_count_points.argtypes = [vp, C.c_float]
@@ -150,9 +152,23 @@ class HostScene:
     def irradiance_tasks(self, n_points, n_cores=1):
         return int(self.lib.skh_irradiance_tasks(n_points, n_cores))
 
+    def envmap(self):
+        """The infinite light's radiance map and sampling distribution (host/skin_envmap.cpp), or None."""
+        wh = np.zeros(2, np.int32)
+        marg_int = float(self.lib.skh_env_sizes(self.h, wh.ctypes.data_as(C.c_void_p)))
+        w, h = int(wh[0]), int(wh[1])
+        if not w:
+            return None
+        n = {"rgb": 3 * w * h, "condFunc": w * h, "condCdf": h * (w + 1), "condInt": h, "margFunc": h, "margCdf": h + 1}
+        out = {"w": w, "h": h, "margInt": np.float32(marg_int)}
+        for i, k in enumerate(n):
+            out[k] = _view(self.lib.skh_env_array(self.h, i), 4 * n[k], np.float32).copy()
+        return out
+
     def upload(self, dev):
         dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
         dev.upload_lights(self.lights)
+        dev.upload_envmap(self.envmap())
 
     FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1 + 2)
 

@@ -36,7 +36,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
            "skc_comm_unique_id", "skc_comm_create", "skc_comm_create_local", "skc_comm_destroy", "skc_comm_rank", "skc_comm_world",
            "skc_comm_allgather_positions", "skc_comm_allgather_rows_begin", "skc_comm_allgather_rows_wait", "skc_comm_reduce_film",
-           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_upload_envmap", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -130,6 +130,7 @@ def load_library():
     lib.skc_comm_barrier.restype = i32; lib.skc_comm_barrier.argtypes = [vp]
     lib.skc_comm_allgather_host.restype = i32; lib.skc_comm_allgather_host.argtypes = [vp, vp, u64]
     lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
+    lib.skc_upload_envmap.restype = i32; lib.skc_upload_envmap.argtypes = [vp, u32, u32, vp, vp, vp, vp, vp, vp, f32]
     lib.skc_set_albedo_factors.restype = i32; lib.skc_set_albedo_factors.argtypes = [vp, vp, vp]
     lib.skc_mo_group_histogram.restype = i32; lib.skc_mo_group_histogram.argtypes = [vp, vp]
     lib.skc_mo_table_stats.restype = i32; lib.skc_mo_table_stats.argtypes = [vp, vp]
@@ -338,6 +339,13 @@ class SkinDevice:
         self._ck(self.lib.skc_mo_table_stats(self.ctx, _ptr(st)))
         return dict(rows=int(st[0]), smem_bytes=int(st[1]), coverage=float(st[2]), max_err=float(st[3]),
                     lookups=int(st[4]), from_heads=int(st[5]), from_global=int(st[6]), accept_groups=int(st[7]))
+
+    def upload_envmap(self, env):
+        """env: dict with w, h, rgb, condFunc, condCdf, condInt, margFunc, margCdf, margInt (HostScene.envmap()), or None to remove it."""
+        if env is None:
+            return self._ck(self.lib.skc_upload_envmap(self.ctx, 0, 0, None, None, None, None, None, None, 0.0))
+        a = [np.ascontiguousarray(env[k], np.float32) for k in ("rgb", "condFunc", "condCdf", "condInt", "margFunc", "margCdf")]
+        self._ck(self.lib.skc_upload_envmap(self.ctx, int(env["w"]), int(env["h"]), *[_ptr(x) for x in a], float(env["margInt"])))
 
     def set_albedo_factors(self, pow_mix=None, pow_one_minus_mix=None):
         a = None if pow_mix is None else np.ascontiguousarray(pow_mix, np.float32); b = None if pow_one_minus_mix is None else np.ascontiguousarray(pow_one_minus_mix, np.float32)
