@@ -23,6 +23,7 @@ struct EnvMapDev {
     const float *rgb = nullptr;                      // [h][w][3] level-0 texels
     const float *condFunc = nullptr, *condCdf = nullptr, *condInt = nullptr;      // [h][w], [h][w + 1], [h]
     const float *margFunc = nullptr, *margCdf = nullptr;                          // [h], [h + 1]
+    const float *illum = nullptr;                    // [7][32]: the illuminant basis spectra of Spectrum(RGBSpectrum, SPECTRUM_ILLUMINANT)
     float margInt = 0.f;
     int w = 0, h = 0;
 };
@@ -106,6 +107,7 @@ struct skc_ctx {
     float4 *otLeafPosArea = nullptr; // irradiance points gathered in leaf order
     uint32_t otNodes = 0, otCap = 0, otLevels = 0;
     uint32_t lightNS[16] = {0};   // RoundUpPow2(nSamples) per light (host copy for launch shapes)
+    int lightKinds[16] = {0};     // 0 sphere emitter, 1 point, 2 spot, 3 distant, 4 infinite (host copy)
     std::vector<uint32_t> otLevelStart;   // first node of each level (+ sentinel), kept between topology and finalize
     bool otTopologyReady = false;
     int moSplit = 0;         // warps per Mo packet (each sums 1/moSplit of the spectrum): 0 = by launch size; env SKC_MO_SPLIT=1|2

@@ -3,6 +3,7 @@
 #include <cstring>
 #include <stdarg.h>
 #include "skc_common.cuh"
+#include "../host/skin_tables.h"      // kRGBIllum2Spect30: data exported from the reference (skc_upload_envmap)
 
 static std::string g_createError;
 
@@ -136,16 +137,18 @@ extern "C" int skc_upload_envmap(skc_ctx *ctx, uint32_t w, uint32_t h, const flo
     ctx->env = EnvMapDev();
     if (!w || !h) return 0;
     if (!rgb || !condFunc || !condCdf || !condInt || !margFunc || !margCdf) return skc_fail(ctx, "skc_upload_envmap: null array");
-    const size_t n = (size_t)w * h, sizes[6] = {3 * n, n, (size_t)h * (w + 1), h, h, (size_t)h + 1};
-    const float *src[6] = {rgb, condFunc, condCdf, condInt, margFunc, margCdf};
-    size_t total = 0, off[6];
-    for (int k = 0; k < 6; ++k) { off[k] = total; total += (sizes[k] + 3) & ~(size_t)3; }
+    float illum[7 * 32];
+    for (int k = 0; k < 7; ++k) for (int i = 0; i < 32; ++i) illum[k * 32 + i] = i < 30 ? kRGBIllum2Spect30[k][i] : 0.f;
+    const size_t n = (size_t)w * h, sizes[7] = {3 * n, n, (size_t)h * (w + 1), h, h, (size_t)h + 1, 7 * 32};
+    const float *src[7] = {rgb, condFunc, condCdf, condInt, margFunc, margCdf, illum};
+    size_t total = 0, off[7];
+    for (int k = 0; k < 7; ++k) { off[k] = total; total += (sizes[k] + 3) & ~(size_t)3; }
     SKC_CUDA(cudaMalloc((void **)&ctx->envStore, total * sizeof(float)));
-    for (int k = 0; k < 6; ++k) SKC_CUDA(cudaMemcpyAsync(ctx->envStore + off[k], src[k], sizes[k] * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    for (int k = 0; k < 7; ++k) SKC_CUDA(cudaMemcpyAsync(ctx->envStore + off[k], src[k], sizes[k] * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
     EnvMapDev &e = ctx->env;
     e.rgb = ctx->envStore + off[0]; e.condFunc = ctx->envStore + off[1]; e.condCdf = ctx->envStore + off[2]; e.condInt = ctx->envStore + off[3];
-    e.margFunc = ctx->envStore + off[4]; e.margCdf = ctx->envStore + off[5]; e.margInt = margInt; e.w = (int)w; e.h = (int)h;
+    e.margFunc = ctx->envStore + off[4]; e.margCdf = ctx->envStore + off[5]; e.illum = ctx->envStore + off[6]; e.margInt = margInt; e.w = (int)w; e.h = (int)h;
     return 0;
 }
 

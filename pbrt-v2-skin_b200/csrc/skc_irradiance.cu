@@ -97,7 +97,7 @@ template <bool COUNT, bool DELTA>
 __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__restrict__ lights, IrrSlots sl,
         const skc_surface_point *__restrict__ pts, const uint32_t *__restrict__ scr, uint64_t ptBase, uint32_t nPts,
         float2 *__restrict__ cosPdf, float4 *__restrict__ rayO, float4 *__restrict__ rayD, uint32_t *__restrict__ rayTarget,
-        uint32_t *__restrict__ nRays, float4 *__restrict__ posArea, uint64_t outBase, unsigned long long *cnt) {
+        uint32_t *__restrict__ nRays, float4 *__restrict__ posArea, uint64_t outBase, unsigned long long *cnt, EnvMapDev env, float4 *__restrict__ envRgb) {
     __shared__ uint32_t sWarpCount[IRR_BLOCK / 32];
     __shared__ uint32_t sBase;
     // thread order is LIGHT-major: all samples towards light 0 of the batch's points first, then light 1, ... so the
@@ -128,6 +128,13 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
             if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
                 need = true;
                 cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
+            }
+        } else if (kind == 4) {      // infinite light (lights/infinite.cpp:195-221): the map's RGB in the sampled direction goes to envRgb
+            f3 rgb;
+            if (sampleInfiniteLight(lights[j], env, p, eps, u0, u1, &wi, &lp, &rgb, &sh) && dot3(wi, n) > 0.f && lp != 0.f) {
+                need = true;
+                cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
+                envRgb[target] = make_float4(rgb.x, rgb.y, rgb.z, 0.f);
             }
         } else {      // delta light: lightPdf = 1; the pdf slot carries DistanceSquared(lightPos, p) for k_irr_spectral's Li
             float d2, fall;
@@ -173,7 +180,8 @@ __global__ void __launch_bounds__(128) k_irr_shadow(BvhView bv, const float4 *__
 template <bool DELTA>
 __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
         uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
-        float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea, const float *__restrict__ albedoPowMix) {
+        float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea, const float *__restrict__ albedoPowMix,
+        const float4 *__restrict__ envRgb, const float *__restrict__ envIllum) {
     int lane = threadIdx.x & 31;
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
@@ -182,6 +190,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
         uint32_t point = p0 + k;
         if (point >= nPts) return;
         const float2 *cp = cosPdf + (size_t)point * sl.S;
+        const float4 *ep = DELTA && envRgb ? envRgb + (size_t)point * sl.S : nullptr;      // per-sample RGB of the infinite light's samples
         float E = 0.f;
         for (uint32_t j = 0; j < sl.nLights; ++j) {
             uint32_t nS = sl.nS[j];
@@ -210,11 +219,13 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
                     float rho = (1.f - lerp) * r0 + lerp * r1;
                     float Ft = 1.f - rho;
                     float Li = Lc;
-                    if (DELTA && kind != 0) { Li = (Lc * fall) / pdf; pdf = 1.f; }      // Intensity * Falloff / DistanceSquared; lightPdf = 1
+                    if (DELTA && kind == 4) { const float4 c4 = __ldg(&ep[sBase + c]); Li = envSpectrum(envIllum, c4.x, c4.y, c4.z, lam); }      // Spectrum(RGB, SPECTRUM_ILLUMINANT)
+                    else if (DELTA && kind != 0) { Li = (Lc * fall) / pdf; pdf = 1.f; }      // Intensity * Falloff / DistanceSquared; lightPdf = 1
                     el += ((Ft * Li) * cosT) / pdf;      // multipolesubsurface.cpp:133
                 }
             }
             cp += nS;
+            if (ep) ep += nS;
             E += el / (float)(int)nS;                    // :136
         }
         uint64_t pi = ptBase + point;
@@ -278,6 +289,7 @@ extern "C" int skc_upload_lights(skc_ctx *ctx, const skc_light *lights, uint32_t
     ctx->nLights = nLights;
     for (uint32_t j = 0; j < nLights && j < IRR_MAX_LIGHTS; ++j) {
         int ns = (int)lights[j].nSamples;
+        ctx->lightKinds[j] = lights[j].radius < 0.f ? (int)(-lights[j].radius) : 0;
         uint32_t nS = 1; while ((int)nS < ns) nS <<= 1;    // RoundUpPow2 (multipolesubsurface.cpp:101)
         ctx->lightNS[j] = nS;
     }
@@ -331,6 +343,12 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
     char *dRays = (char *)skc_scratch(ctx, 5, slots * 36);
     uint32_t *dNRays = (uint32_t *)skc_scratch(ctx, 6, nBatches * sizeof(uint32_t));
     if (!dCosPdf || !dRays || !dNRays) return 1;
+    // an infinite light's samples carry the map's RGB in their direction (16 B per slot; scenes without one do not pay for it)
+    float4 *dEnvRgb = nullptr;
+    for (uint32_t j = 0; j < ctx->nLights; ++j) if (ctx->lightKinds[j] == 4) {
+        if (!ctx->env.rgb) return skc_fail(ctx, "skc_irradiance: the scene has an infinite light but no environment map was uploaded (skc_upload_envmap)");
+        if (!(dEnvRgb = (float4 *)skc_scratch(ctx, 21, slots * sizeof(float4)))) return 1;
+    }
     float4 *rayO = (float4 *)dRays, *rayD = rayO + slots;
     uint32_t *rayTarget = (uint32_t *)(rayD + slots);
     if (hostPts) {
@@ -355,16 +373,16 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
         unsigned gSample = (unsigned)((ns + IRR_BLOCK - 1) / IRR_BLOCK), gShadow = (unsigned)((ns + 127) / 128);
         unsigned gSpec = (unsigned)(((uint64_t)np + IRR_SPECTRAL_POINTS * 8 - 1) / (IRR_SPECTRAL_POINTS * 8));
         if (cntDev) {
-            if (ctx->hasDeltaLights) k_irr_sample<true, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
-            else k_irr_sample<true, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev);
+            if (ctx->hasDeltaLights) k_irr_sample<true, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev, ctx->env, dEnvRgb);
+            else k_irr_sample<true, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, cntDev, ctx->env, nullptr);
             k_irr_shadow<true><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, cntDev);
         } else {
-            if (ctx->hasDeltaLights) k_irr_sample<false, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
-            else k_irr_sample<false, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr);
+            if (ctx->hasDeltaLights) k_irr_sample<false, true><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr, ctx->env, dEnvRgb);
+            else k_irr_sample<false, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr, ctx->env, nullptr);
             k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
         }
-        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors);
-        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors);
+        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, dEnvRgb, ctx->env.illum);
+        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, nullptr, nullptr);
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }

@@ -176,6 +176,107 @@ __device__ inline bool sampleSphereLight(const skc_light &L, f3 p, float pEps, f
     return true;
 }
 
+// ---- LightSource "infinite" (SURVEY.md 8f N4): lights/infinite.cpp:114-119,195-234, core/montecarlo.h:78-97,151-168, core/mipmap.h:253-264 ----
+// Record: radius = -4, o2w / w2o = LightToWorld / WorldToLight, zmin / zmax = the map's size; the map's level-0 texels and its
+// Distribution2D are in EnvMapDev (skc_upload_envmap).  The radiance of a direction is an RGB value (a bilinear lookup), turned
+// into a 30-sample spectrum per use by Spectrum(RGBSpectrum, SPECTRUM_ILLUMINANT) = FromRGB's illuminant branch
+// (core/spectrum.cpp:146-186): the smallest component on the white basis, the two differences on a secondary and a primary one.
+#define SKC_INV_PI_F 0.31830988618379067154f
+#define SKC_INV_TWOPI_F 0.15915494309189533577f
+// illum: [7][32] white, cyan, magenta, yellow, red, green, blue (host/skin_tables.h kRGBIllum2Spect30; EnvMapDev::illum)
+__device__ __forceinline__ float envSpectrum(const float *__restrict__ illum, float r, float g, float b, int lane) {
+    enum { W, C, M, Y, R, G, B };
+    float a, d1, d2; int i1, i2;
+    if (r <= g && r <= b) {
+        a = r;
+        if (g <= b) { d1 = g - r; i1 = C; d2 = b - g; i2 = B; } else { d1 = b - r; i1 = C; d2 = g - b; i2 = G; }
+    } else if (g <= r && g <= b) {
+        a = g;
+        if (r <= b) { d1 = r - g; i1 = M; d2 = b - r; i2 = B; } else { d1 = b - g; i1 = M; d2 = r - b; i2 = R; }
+    } else {
+        a = b;
+        if (r <= g) { d1 = r - b; i1 = Y; d2 = g - r; i2 = G; } else { d1 = g - b; i1 = Y; d2 = r - g; i2 = R; }
+    }
+    float v = 0.f;
+    v += a * __ldg(&illum[W * 32 + lane]);
+    v += d1 * __ldg(&illum[i1 * 32 + lane]);
+    v += d2 * __ldg(&illum[i2 * 32 + lane]);
+    v *= .86445f;
+    return fmaxf(v, 0.f);          // Clamp()
+}
+
+// Distribution1D::SampleContinuous over cdf[0..n]: returns the sample in [0,1), its pdf and the segment
+__device__ inline float envSample1D(const float *__restrict__ func, const float *__restrict__ cdf, float funcInt, int n, float u, float *pdf, int *off) {
+    int lo = 0, hi = n + 1;                       // std::upper_bound: first element > u
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (!(u < __ldg(&cdf[mid]))) lo = mid + 1; else hi = mid; }
+    const int offset = max(0, lo - 1);
+    *off = offset;
+    const float c0 = __ldg(&cdf[offset]), c1 = __ldg(&cdf[offset + 1]);
+    const float du = (u - c0) / (c1 - c0);
+    *pdf = __ldg(&func[offset]) / funcInt;
+    return ((float)offset + du) / (float)n;
+}
+__device__ inline void envSample(const EnvMapDev &e, float u0, float u1, float *uv0, float *uv1, float *pdf) {      // Distribution2D::SampleContinuous
+    float p0, p1; int v, dummy;
+    *uv1 = envSample1D(e.margFunc, e.margCdf, e.margInt, e.h, u1, &p1, &v);
+    *uv0 = envSample1D(e.condFunc + (size_t)v * e.w, e.condCdf + (size_t)v * (e.w + 1), __ldg(&e.condInt[v]), e.w, u0, &p0, &dummy);
+    *pdf = p0 * p1;
+}
+__device__ inline float envDistPdf(const EnvMapDev &e, float u, float v) {                                            // Distribution2D::Pdf
+    const int iu = min(max((int)(u * (float)e.w), 0), e.w - 1), iv = min(max((int)(v * (float)e.h), 0), e.h - 1);
+    const float ci = __ldg(&e.condInt[iv]);
+    if (ci * e.margInt == 0.f) return 0.f;
+    return (__ldg(&e.condFunc[(size_t)iv * e.w + iu]) * __ldg(&e.margFunc[iv])) / (ci * e.margInt);
+}
+__device__ __forceinline__ int envWrap(int a, int b) { int n = a / b; a -= n * b; if (a < 0) a += b; return a; }
+// MIPMap::Lookup(s, t) with width 0 = triangle(0, s, t), TEXTURE_REPEAT
+__device__ inline f3 envLookup(const EnvMapDev &e, float s, float t) {
+    s = s * (float)e.w - 0.5f;
+    t = t * (float)e.h - 0.5f;
+    const int s0 = (int)floorf(s), t0 = (int)floorf(t);
+    const float ds = s - (float)s0, dt = t - (float)t0;
+    const int sa = envWrap(s0, e.w), sb = envWrap(s0 + 1, e.w), ta = envWrap(t0, e.h), tb = envWrap(t0 + 1, e.h);
+    const float w00 = (1.f - ds) * (1.f - dt), w01 = (1.f - ds) * dt, w10 = ds * (1.f - dt), w11 = ds * dt;
+    const float *c00 = e.rgb + 3 * ((size_t)ta * e.w + sa), *c01 = e.rgb + 3 * ((size_t)tb * e.w + sa);
+    const float *c10 = e.rgb + 3 * ((size_t)ta * e.w + sb), *c11 = e.rgb + 3 * ((size_t)tb * e.w + sb);
+    f3 o;
+    o.x = __ldg(c00) * w00 + __ldg(c01) * w01 + __ldg(c10) * w10 + __ldg(c11) * w11;
+    o.y = __ldg(c00 + 1) * w00 + __ldg(c01 + 1) * w01 + __ldg(c10 + 1) * w10 + __ldg(c11 + 1) * w11;
+    o.z = __ldg(c00 + 2) * w00 + __ldg(c01 + 2) * w01 + __ldg(c10 + 2) * w10 + __ldg(c11 + 2) * w11;
+    return o;
+}
+__device__ __forceinline__ float sphericalTheta(f3 v) { return skc_acosf(fminf(fmaxf(v.z, -1.f), 1.f)); }
+__device__ __forceinline__ float sphericalPhi(f3 v) { const float p = skc_atan2f(v.y, v.x); return p < 0.f ? p + 2.f * SKC_PI_F : p; }
+
+// InfiniteAreaLight::Sample_L (lights/infinite.cpp:195-221): wi, pdf, the map's RGB in that direction, the VisibilityTester's ray
+__device__ inline bool sampleInfiniteLight(const skc_light &L, const EnvMapDev &e, f3 p, float pEps, float u0, float u1, f3 *wi, float *pdf, f3 *rgb, DRay *shadow) {
+    float uv0, uv1, mapPdf;
+    envSample(e, u0, u1, &uv0, &uv1, &mapPdf);
+    if (mapPdf == 0.f) return false;
+    const float theta = uv1 * SKC_PI_F, phi = uv0 * 2.f * SKC_PI_F;
+    const float costheta = skc_cosf(theta), sintheta = skc_sinf(theta);
+    const float sinphi = skc_sinf(phi), cosphi = skc_cosf(phi);
+    *wi = xformVector(L.o2w, mk3(sintheta * cosphi, sintheta * sinphi, costheta));
+    *pdf = mapPdf / (2.f * SKC_PI_F * SKC_PI_F * sintheta);
+    if (sintheta == 0.f) *pdf = 0.f;
+    shadow->o = p; shadow->d = *wi; shadow->mint = pEps; shadow->maxt = INFINITY;      // VisibilityTester::SetRay (core/light.h:94-99)
+    *rgb = envLookup(e, uv0, uv1);
+    return true;
+}
+// InfiniteAreaLight::Pdf (lights/infinite.cpp:224-234)
+__device__ inline float infiniteLightPdf(const skc_light &L, const EnvMapDev &e, f3 w) {
+    const f3 wi = xformVector(L.w2o, w);
+    const float theta = sphericalTheta(wi), phi = sphericalPhi(wi);
+    const float sintheta = skc_sinf(theta);
+    if (sintheta == 0.f) return 0.f;
+    return envDistPdf(e, phi * SKC_INV_TWOPI_F, theta * SKC_INV_PI_F) / (2.f * SKC_PI_F * SKC_PI_F * sintheta);
+}
+// InfiniteAreaLight::Le (lights/infinite.cpp:114-119): the map's RGB for a ray that leaves the scene
+__device__ inline f3 infiniteLightLe(const skc_light &L, const EnvMapDev &e, f3 d) {
+    const f3 wh = normalize3(xformVector(L.w2o, d));
+    return envLookup(e, sphericalPhi(wh) * SKC_INV_TWOPI_F, sphericalTheta(wh) * SKC_INV_PI_F);
+}
+
 // ---- delta lights: lights/point.cpp:49-56, lights/spot.cpp:52-72, lights/distant.cpp:49-56 -------------
 // They reuse the 70-float record (include/skin_cuda.h): radius = -1 point, -2 spot, -3 distant; o2w / w2o = LightToWorld and
 // its inverse; spot: zmin = cosTotalWidth, zmax = cosFalloffStart; distant: (zmin, zmax, phiMax) = lightDir; Lemit = the

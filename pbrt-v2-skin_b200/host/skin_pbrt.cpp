@@ -627,9 +627,22 @@ bool Front::statement(const std::string &id) {
     }
     if (id == "LightSource") {
         if (!named("LightSource") || !needWorld("LightSource")) return false;
-        // MakeLight (core/api.cpp:470-500) -> CreatePointLight / CreateSpotLight / CreateDistantLight
+        // MakeLight (core/api.cpp:470-500) -> CreatePointLight / CreateSpotLight / CreateDistantLight / CreateInfiniteLight
+        if (name == "infinite") {      // lights/infinite.cpp:185-193
+            float L[3] = {1, 1, 1}, scl[3] = {1, 1, 1};
+            const bool haveScale = ps.FindFloats("scale", "color", "spectrum") != nullptr;
+            if (!greyColor(ps, "L", L, "LightSource") || !greyColor(ps, "scale", scl, "LightSource")) return false;
+            std::string map = ps.FindOneString("mapname", "");
+            if (!map.empty()) map = resolve(map);
+            if (sd->env.present) { Error("LightSource \"infinite\": one infinite light per scene is supported on the device path"); return false; }
+            SphereLight l; std::string err;
+            if (!MakeInfiniteLight(ctm, L, haveScale ? scl : nullptr, ps.FindOneInt("nsamples", 1), map, options.quickRender, &l, &sd->env, &err)) { Error("%s", err.c_str()); return false; }
+            sd->lights.push_back(l);
+            reportUnused(ps, "LightSource");
+            return true;
+        }
         if (name != "point" && name != "spot" && name != "distant") {
-            Error("LightSource \"%s\": the device path has sphere AreaLightSource emitters and point / spot / distant lights", name.c_str());
+            Error("LightSource \"%s\": the device path has sphere AreaLightSource emitters and point / spot / distant / infinite lights", name.c_str());
             return false;
         }
         float rgb[3] = {1, 1, 1}, sc[3] = {1, 1, 1};

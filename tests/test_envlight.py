@@ -79,3 +79,50 @@ def test_non_power_of_two_map_is_refused(pkg, tmp_path):
     (tmp_path / "o.scene").write_text(src)
     with pytest.raises(Exception, match="power of two"):
         pkg.HostScene(str(tmp_path / "o.scene"))
+
+
+@pytest.mark.gpu
+def test_device_acosf_atan2f_equal_libm(dev):
+    """InfiniteAreaLight::Pdf / Le go through SphericalTheta / SphericalPhi = acosf / atan2f (core/geometry.h); the device restates
+    glibc's (csrc/skc_common.cuh; tools/libm_check.c checked them over the whole domain / 4e8 pairs on the CPU)."""
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")
+    rng = np.random.default_rng(11)
+    x = np.concatenate([rng.uniform(-1, 1, 150000), 1 - rng.random(30000) ** 6, -1 + rng.random(30000) ** 6, rng.random(20000) ** 8 - 0.5 * 0, [0.0, 0.5, -0.5, 1.0, -1.0, 2.0 ** -30]]).astype(np.float32)
+    f = libm.acosf; f.restype = ctypes.c_float; f.argtypes = [ctypes.c_float]
+    host = np.array([f(float(v)) for v in x], np.float32)
+    assert np.array_equal(dev.test_libmf(5, x).view(np.uint32), host.view(np.uint32))
+    ang = rng.uniform(0, 2 * np.pi, 200000); r = np.exp(rng.uniform(-8, 8, 200000))
+    y = (r * np.sin(ang)).astype(np.float32); xx = (r * np.cos(ang)).astype(np.float32)
+    y[:200] = 0; xx[200:400] = 0; xx[400:600] = 1
+    pairs = np.concatenate([y, xx[::-1]]).astype(np.float32)          # kernel: atan2f(v[i], v[n - 1 - i])
+    g = libm.atan2f; g.restype = ctypes.c_float; g.argtypes = [ctypes.c_float, ctypes.c_float]
+    n = len(pairs)
+    host = np.array([g(float(pairs[i]), float(pairs[n - 1 - i])) for i in range(n)], np.float32)
+    assert np.array_equal(dev.test_libmf(6, pairs).view(np.uint32), host.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_irradiance_under_the_infinite_light(pkg, golden):
+    z, meta = golden
+    dev = pkg.SkinDevice(0)
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_env.scene"))
+    try:
+        hs.upload(dev)
+        hs.build_profile(dev)
+        n_pts = dev.tessellate_resident(hs.minsampledistance, False, material_id=int(meta["skin_material_id"]))
+        assert n_pts == int(meta["surface_points"])
+        dev.irradiance_resident(0, n_pts, hs.irradiance_tasks(n_pts, 1), hs.mix)
+        _, E = dev.irradiance_rows(0, n_pts, 1)
+        ref = z["irradiance_E"]
+        e = gu.row_rel_err(E, ref)
+        lit = ref.max(axis=1) > 0
+        print("irradiance under the environment map + 1 sphere: %d points (%d lit), bit-exact rows %.4f, max rel %.3g" % (len(ref), lit.sum(), np.mean(e == 0), e.max()))
+        assert np.array_equal(E.max(axis=1) > 0, lit)
+        assert e.max() < 1e-6, e.max()
+        _, root, _ = dev.build_octree()
+        er = np.abs(root - z["octree_root"]) / np.maximum(np.abs(z["octree_root"]), 1e-30)
+        assert er.max() < 1e-5
+    finally:
+        hs.close()
+        dev.close()

@@ -146,7 +146,7 @@ def test_shape_parameters_override_material_parameters(pkg, tmp_path):
 @pytest.mark.parametrize("text,needle", [
     (scene_text('SurfaceIntegrator "path"'), 'SurfaceIntegrator "path"'),
     (scene_text(""), "multipolesubsurface"),
-    (scene_text(world='LightSource "infinite"\n' + TRI % ("", "")), 'LightSource "infinite"'),
+    (scene_text(world='LightSource "goniometric"\n' + TRI % ("", "")), 'LightSource "goniometric"'),
     (scene_text(mat='"texture albedo" "tex"'), "texture albedo"),
     (scene_text(mat='"color albedo" [0.8 0.6]'), "albedo"),      # a constant albedo is supported (tests/test_gpu_albedo.py); a malformed one is not
     (scene_text(mat='"bool doublerefsslf" "true"'), "doublerefsslf"),
