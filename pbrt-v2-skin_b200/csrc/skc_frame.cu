@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
                                                      RhoBxdf mf, float ior, float kd, int hasR, int hasT,
                                                      const skc_hit *__restrict__ hits, const float4 *__restrict__ frame,
                                                      const float *__restrict__ arrays, const uint32_t *__restrict__ order, uint64_t first,
-                                                     uint64_t n, float4 *__restrict__ terms) {
+                                                     uint64_t n, float4 *__restrict__ terms, EnvMapDev env, float4 *__restrict__ termsEnv) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * lay.slots) return;
     uint64_t s = t / lay.slots;
@@ -377,6 +377,38 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
         float bc = __ldg(A + lay.off1B[li] + j), bu0 = __ldg(A + lay.off2B[li] + 2 * j), bu1 = __ldg(A + lay.off2B[li] + 2 * j + 1);
         const skc_light &L = lights[li];
         const int kind = lightKind(L);
+        if (kind == 4) {
+            // infinite light (lights/infinite.cpp): both MIS terms as for an emitter shape, but the radiance is the map's RGB in the
+            // term's direction (termsEnv[2t], [2t+1]; k_frame_sum turns it into a spectrum), and the BSDF-sampled ray sees the
+            // light only if it leaves the scene (integrator.cpp:144-148: `else Li = light->Le(ray)`)
+            f3 wi, rgbA = mk3(0.f, 0.f, 0.f), rgbB = rgbA; float lightPdf; DRay sh;
+            if (sampleInfiniteLight(L, env, p, eps, lu0, lu1, &wi, &lightPdf, &rgbA, &sh) && lightPdf > 0.) {
+                float4 comp;
+                float f = bsdfF(B, wo, wi, &comp);
+                if (f != 0.f && !bvhOccludedFast(bv, sh)) {
+                    float bp = bsdfPdf(B, wo, wi);
+                    float weight = powerHeuristic(lightPdf, bp);
+                    T0 = comp; T1.x = fabsf(dot3(wi, B.nn)) * weight / lightPdf;
+                }
+            }
+            float bp;
+            float4 comp2;
+            float f = bsdfSample(B, wo, bc, bu0, bu1, &wi, &bp, &comp2);
+            if (f != 0.f && bp > 0.) {
+                float lp = infiniteLightPdf(L, env, wi);
+                if (lp != 0.) {
+                    float weight = powerHeuristic(bp, lp);
+                    DRay ray; ray.o = p; ray.d = wi; ray.mint = eps; ray.maxt = INFINITY;
+                    if (!bvhOccludedFast(bv, ray)) {
+                        rgbB = infiniteLightLe(L, env, wi);
+                        T2 = comp2; T1.y = fabsf(dot3(wi, B.nn)); T1.z = weight; T1.w = bp;
+                    }
+                }
+            }
+            terms[3 * t] = T0; terms[3 * t + 1] = T1; terms[3 * t + 2] = T2;
+            termsEnv[2 * t] = make_float4(rgbA.x, rgbA.y, rgbA.z, 0.f); termsEnv[2 * t + 1] = make_float4(rgbB.x, rgbB.y, rgbB.z, 0.f);
+            return;
+        }
         if (kind != 0) {
             // delta light (integrator.cpp:114-126): Ld += f * Li * (AbsDot(wi, n) / lightPdf), lightPdf = 1, and no BSDF-sampling
             // term (:134).  T1.y / T1.z carry DistanceSquared and the spot falloff: Li = (I * falloff) / d2 in k_frame_sum.
@@ -443,16 +475,23 @@ __device__ __forceinline__ float lobeValue(float4 c, float Kr, float Kt) {
 }
 // UniformSampleAllLights (integrator.cpp:47-75) of one camera sample in one spectral channel, from k_direct_terms' factors
 __device__ __forceinline__ float directSum(const skc_light *__restrict__ lights, const FrameLayout &lay, const float4 *__restrict__ terms,
-                                           uint64_t s, int lane, float Kr, float Kt) {
+                                           uint64_t s, int lane, float Kr, float Kt, const float4 *__restrict__ termsEnv, const float *__restrict__ illum) {
     float Ldir = 0.f;
     uint64_t t = s * lay.slots;
     for (uint32_t i = 0; i < lay.nLights; ++i) {
         float Le = __ldg(&lights[i].Lemit[lane]);
-        const bool delta = lights[i].radius < 0.f;
+        const int kind = lightKind(lights[i]);
+        const bool delta = kind >= 1 && kind <= 3;
         float Ld = 0.f;
         for (uint32_t j = 0; j < lay.nS[i]; ++j, ++t) {
             float4 T0 = __ldg(&terms[3 * t]), T1 = __ldg(&terms[3 * t + 1]), T2 = __ldg(&terms[3 * t + 2]);
             float est = 0.f;
+            if (kind == 4) {      // infinite light: the two terms carry their own radiance (the map's RGB -> Spectrum(.., SPECTRUM_ILLUMINANT))
+                if (T0.w != 0.f) { const float4 c = __ldg(&termsEnv[2 * t]); est += (lobeValue(T0, Kr, Kt) * envSpectrum(illum, c.x, c.y, c.z, lane)) * T1.x; }
+                if (T2.w != 0.f) { const float4 c = __ldg(&termsEnv[2 * t + 1]); est += (((lobeValue(T2, Kr, Kt) * envSpectrum(illum, c.x, c.y, c.z, lane)) * T1.y) * T1.z) / T1.w; }
+                Ld += est;
+                continue;
+            }
             if (delta) {                                                   // Li = Intensity * Falloff / DistanceSquared (lights/point.cpp:55, spot.cpp:58)
                 if (T0.w != 0.f) est += (lobeValue(T0, Kr, Kt) * ((Le * T1.z) / T1.y)) * T1.x;
                 Ld += est;
@@ -471,12 +510,12 @@ __device__ __forceinline__ float directSum(const skc_light *__restrict__ lights,
 // k_frame_sum then only adds the row): Ldir[s][lane], zero for samples that hit nothing.
 __global__ void __launch_bounds__(FS_WARPS * 32) k_direct_sum(const skc_light *__restrict__ lights, FrameLayout lay, const FrameConsts *__restrict__ C,
                                                              const skc_hit *__restrict__ hits, const float4 *__restrict__ terms, uint64_t n,
-                                                             float *__restrict__ Ldir) {
+                                                             float *__restrict__ Ldir, const float4 *__restrict__ termsEnv, const float *__restrict__ illum) {
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t s = (uint64_t)blockIdx.x * FS_WARPS + warp;
     if (s >= n || lane >= SKC_NS) return;
     float v = 0.f;
-    if (__float_as_int(__ldg(reinterpret_cast<const float *>(hits + s)))) v = directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane]);
+    if (__float_as_int(__ldg(reinterpret_cast<const float *>(hits + s)))) v = directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane], termsEnv, illum);
     Ldir[s * SKC_NS + lane] = v;
 }
 
@@ -485,7 +524,8 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
                                                             const float4 *__restrict__ terms, const float2 *__restrict__ xy,
                                                             const uint32_t *__restrict__ order, uint64_t first,
                                                             uint64_t n, float *__restrict__ Lrows, float4 *__restrict__ film,
-                                                            const float *__restrict__ LdirRows) {
+                                                            const float *__restrict__ LdirRows, const float4 *__restrict__ termsEnv, EnvMapDev env, int envLight,
+                                                            const skc_ray *__restrict__ rays) {
     __shared__ float sL[FS_WARPS][32];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint64_t s = (uint64_t)blockIdx.x * FS_WARPS + warp;
@@ -501,8 +541,13 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
         }
         Lc += Lrows[s * SKC_NS + lane];       // subsurface term (0 for non-subsurface hits)
         // UniformSampleAllLights (integrator.cpp:47-75): summed here, or already by k_direct_sum (same arithmetic, same order)
-        float Ldir = LdirRows ? __ldg(&LdirRows[s * SKC_NS + lane]) : directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane]);
+        float Ldir = LdirRows ? __ldg(&LdirRows[s * SKC_NS + lane]) : directSum(lights, lay, terms, s, lane, C->Kr[lane], C->Kt[lane], termsEnv, env.illum);
         Lc += Ldir;
+    } else if (envLight >= 0 && lane < SKC_NS && !__float_as_int(__ldg(hp))) {
+        // a camera ray that leaves the scene sees the infinite light (samplerrenderer.cpp:239-246: Li += lights[i]->Le(ray))
+        const float *rp = reinterpret_cast<const float *>(rays + s);
+        const f3 rgb = infiniteLightLe(lights[envLight], env, mk3(__ldg(rp + 3), __ldg(rp + 4), __ldg(rp + 5)));
+        Lc += envSpectrum(env.illum, rgb.x, rgb.y, rgb.z, lane);
     }
     sL[warp][lane] = lane < SKC_NS ? Lc : 0.f;
     __syncwarp();
@@ -711,8 +756,20 @@ extern "C" int skc_frame_get_samples(skc_ctx *ctx, uint64_t first, uint64_t coun
 }
 
 // Scene::Intersect for the camera rays and EstimateDirect's terms (everything of Li that does not need the octree)
+// index of the scene's infinite light (-1: none) and, with one, the per-term RGB array of `count` samples (scratch slot 22)
+static int frameEnv(skc_ctx *ctx, const FrameLayout &lay, uint64_t count, int *light, float4 **termsEnv) {
+    *light = -1; *termsEnv = nullptr;
+    for (uint32_t j = 0; j < ctx->nLights && j < 16; ++j) if (ctx->lightKinds[j] == 4) *light = (int)j;
+    if (*light < 0) return 0;
+    if (!ctx->env.rgb) return skc_fail(ctx, "the scene has an infinite light but no environment map was uploaded (skc_upload_envmap)");
+    *termsEnv = (float4 *)skc_scratch(ctx, 22, count * lay.slots * 2 * sizeof(float4));
+    return *termsEnv ? 0 : 1;
+}
+
 static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, uint64_t count, skc_hit *dHits, float4 *dFrame, float4 *dTerms,
                               cudaEvent_t hitsDone = nullptr, float *dLdir = nullptr) {
+    int envLight; float4 *dTermsEnv;
+    if (frameEnv(ctx, f->lay, count, &envLight, &dTermsEnv)) return 1;
     const FrameLayout &lay = f->lay;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
@@ -726,10 +783,10 @@ static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, 
     skc_stage_begin(ctx);
     uint64_t nThreads = count * lay.slots;
     k_direct_terms<<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
-                                                                                dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms);
+                                                                                dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms, ctx->env, dTermsEnv);
     SKC_LAUNCHED("k_direct_terms");
     if (dLdir) {
-        k_direct_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(ctx->lights, lay, f->dConsts, dHits, dTerms, count, dLdir);
+        k_direct_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(ctx->lights, lay, f->dConsts, dHits, dTerms, count, dLdir, dTermsEnv, ctx->env.illum);
         SKC_LAUNCHED("k_direct_sum");
     }
     skc_stage_end(ctx, 10);
@@ -794,10 +851,13 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
         SKC_CUDA(cudaMemsetAsync(dL, 0, count * SKC_NS * sizeof(float), ctx->stream));    // no octree: `if (bssrdf && octree)` (multipolesubsurface.cpp:267)
     }
     if (usePrefetch) SKC_CUDA(cudaStreamWaitEvent(ctx->stream, f->evP1, 0));
+    int envLight; float4 *dTermsEnv;
+    if (frameEnv(ctx, lay, count, &envLight, &dTermsEnv)) return 1;
     skc_stage_begin(ctx);
     k_frame_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, f->dConsts, dHits, dTerms,
                                                                                                  f->dXY, f->dOrder, first, count, dL, f->dFilm,
-                                                                                                 usePrefetch ? (const float *)skc_scratch(ctx, 19, count * SKC_NS * sizeof(float)) : nullptr);
+                                                                                                 usePrefetch ? (const float *)skc_scratch(ctx, 19, count * SKC_NS * sizeof(float)) : nullptr,
+                                                                                                 dTermsEnv, ctx->env, envLight, ctx->resRays + first);
     SKC_LAUNCHED("k_frame_sum");
     skc_stage_end(ctx, 11);
     if (usePrefetch) {      // the prefetched part, as timed on its own stream

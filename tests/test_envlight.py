@@ -103,7 +103,7 @@ def test_device_acosf_atan2f_equal_libm(dev):
 
 
 @pytest.mark.gpu
-def test_irradiance_under_the_infinite_light(pkg, golden):
+def test_irradiance_and_frame_under_the_infinite_light(pkg, golden):
     z, meta = golden
     dev = pkg.SkinDevice(0)
     hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_env.scene"))
@@ -123,6 +123,29 @@ def test_irradiance_under_the_infinite_light(pkg, golden):
         _, root, _ = dev.build_octree()
         er = np.abs(root - z["octree_root"]) / np.maximum(np.abs(z["octree_root"]), 1e-30)
         assert er.max() < 1e-5
+        # ---- the frame: every camera sample carries radiance now (the ones that miss see the map)
+        n = dev.frame_setup(hs.frame_desc(n_cores=1))
+        assert n == int(meta["camera_samples"])
+        dev.frame_samples()
+        xy, _, _ = dev.frame_get_samples(0, n)
+        assert np.array_equal(xy.view(np.uint32), z["camera_xy"].view(np.uint32)), "the sampler stream with an 8-sample and a 4-sample light"
+        dev.frame_film_clear()
+        Lr = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+        order = dev.frame_order(0, n)
+        L = np.empty_like(Lr); L[order] = Lr
+        ref = z["L"]
+        lit = ref.max(axis=1) > 0
+        assert lit.mean() > 0.95 and np.array_equal(L.max(axis=1) > 0, lit)
+        e = gu.row_rel_err(L, ref)
+        miss = z["L_sss"].max(axis=1) == 0
+        print("full Li under the environment map: %d samples, max rel %.3g (rows without a subsurface term -- background and emitter: %d, bit-exact %.4f)"
+              % (len(ref), e.max(), miss.sum(), np.mean(e[miss] == 0)))
+        assert e.max() < 1e-5, e.max()
+        rgb = hs.film_to_rgb(dev.frame_film())
+        for c in range(3):
+            rmse = np.sqrt(np.mean((rgb[..., c] - z["image"][..., c]) ** 2)); s = np.sqrt(np.mean(z["image"][..., c] ** 2))
+            print("channel %d: RMSE / RMS = %.3g" % (c, rmse / s))
+            assert rmse < 1e-3 * s
     finally:
         hs.close()
         dev.close()
