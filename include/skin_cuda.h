@@ -220,6 +220,11 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * only.  stats8 = {rows, shared-memory bytes, coverage, largest verified relative error inside the windows, and
  * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
  * global tables, 0}. */
+/* Alpha-tested triangles (shapes/trianglemesh.inl:117-126,174-207): the mesh's "texture alpha", a float image map.  texels [h][w] are
+ * the values ImageTexture<float, float> holds at MIPMap level 0 -- scale * (powf(luminance, gamma) + shift), made by the caller
+ * (textures/imagemap.h:94-97); su, sv, du, dv its UVMapping2D.  Every ray-triangle hit, closest or any, whose texture value at the
+ * hit's (u, v) is exactly 0 is ignored.  Call after skc_upload_bvh (and again after a new mesh); w == 0 removes it. */
+int skc_upload_alpha(skc_ctx *ctx, uint32_t w, uint32_t h, const float *texels, float su, float sv, float du, float dv);
 /* LightSource "infinite" (lights/infinite.cpp): its light record has radius -4, o2w / w2o = LightToWorld / WorldToLight, zmin / zmax =
  * the radiance map's width / height, nSamples; the map and its Distribution2D (core/montecarlo.h) come through this call, as
  * InfiniteAreaLight's constructor prepares them (the host mirror does: host/skin_envmap.cpp): rgb [h][w][3] level-0 texels,

@@ -51,6 +51,7 @@
 #include "lights/spot.h"
 #include "lights/distant.h"
 #include "lights/infinite.h"
+#include "textures/imagemap.h"
 #include "core/multipole.h"
 #include "core/reflection.h"
 #include "core/film.h"
@@ -118,7 +119,7 @@ struct SceneDesc {
     float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};     // "color Kr" / "color Kt" as the skin scenes give them
     float albedo[3] = {1, 1, 1}; bool hasAlbedo = false;      // "color albedo" (materials/layeredskin.cpp:247)
     struct Xf { std::string kind; float v[4]; };
-    struct Mesh { std::vector<Xf> xf; std::string file; };
+    struct Mesh { std::vector<Xf> xf; std::string file; std::string alpha; };      // alpha: PFM of the mesh's "texture alpha" (float imagemap)
     std::vector<Mesh> meshes;
 };
 
@@ -129,6 +130,7 @@ static SceneDesc parseScene(const std::string &path) {
     std::string dir = path.substr(0, path.find_last_of('/') + 1);
     std::string line;
     std::vector<SceneDesc::Xf> pending;
+    std::string pendingAlpha;
     while (std::getline(in, line)) {
         std::istringstream ls(line);
         std::string key;
@@ -177,9 +179,11 @@ static SceneDesc parseScene(const std::string &path) {
             for (int i = 0; i < n; ++i) ls >> x.v[i];
             pending.push_back(x);
         }
+        else if (key == "alpha") { ls >> pendingAlpha; if (pendingAlpha[0] != '/') pendingAlpha = dir + pendingAlpha; }
         else if (key == "mesh") {
             SceneDesc::Mesh m; ls >> m.file;
             if (m.file[0] != '/') m.file = dir + m.file;
+            m.alpha = pendingAlpha; pendingAlpha.clear();
             m.xf = pending; pending.clear();
             sd.meshes.push_back(m);
         }
@@ -271,6 +275,11 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
             if (fread(idx.data(), 12, nt, f) != (size_t)nt) exit(2);
             fclose(f);
             ParamSet ps;
+            if (!m.alpha.empty()) {      // Texture "alphamap" "float" "imagemap" "string filename" + "texture alpha" (shapes/trianglemesh.cpp:411-421)
+                ParamSet tp; tp.AddString("filename", &m.alpha, 1);
+                pbrtTexture("alphamap", "float", "imagemap", tp);
+                std::string nm = "alphamap"; ps.AddTexture("alpha", nm);
+            }
             ps.AddInt("indices", idx.data(), 3 * nt);
             ps.AddPoint("P", P.data(), nv);
             if (hdr[2]) ps.AddNormal("N", N.data(), nv);
@@ -409,6 +418,14 @@ static void dumpBVH(const std::string &dir, const Scene *scene, Meta &meta,
         dump(b + "idx.bin", m->vertexIndex, 3 * m->ntris);
         std::vector<float> xf; dumpTransform(xf, *m->ObjectToWorld);
         dump(b + "o2w.bin", xf.data(), xf.size());
+        if (m->alphaTexture) {      // its MIPMap's level-0 texels: int32 w, h, then [h][w] floats
+            const ImageTexture<float, float> *it = dynamic_cast<const ImageTexture<float, float> *>(m->alphaTexture.GetPtr());
+            if (!it) { fprintf(stderr, "alpha texture is not a float image map\n"); exit(2); }
+            const int w = (int)it->mipmap->width, h = (int)it->mipmap->height;
+            std::vector<float> a; int32_t wh[2] = {w, h}; float whf[2]; memcpy(whf, wh, 8); a.push_back(whf[0]); a.push_back(whf[1]);
+            for (int t = 0; t < h; ++t) for (int s2 = 0; s2 < w; ++s2) a.push_back(it->mipmap->Texel(0, s2, t));
+            dump(b + "alpha.bin", a.data(), a.size());
+        }
         meta.kv((std::string("mesh") + std::to_string(mi) + "_nverts").c_str(), m->nverts);
         meta.kv((std::string("mesh") + std::to_string(mi) + "_ntris").c_str(), m->ntris);
         meta.kv((std::string("mesh") + std::to_string(mi) + "_hasN").c_str(), m->n ? 1 : 0);

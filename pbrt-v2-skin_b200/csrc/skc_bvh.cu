@@ -77,8 +77,45 @@ __global__ void __launch_bounds__(128) k_trace_closest(BvhView bv, MeshView mv, 
 
 // ---- host side --------------------------------------------------------------------------
 BvhView skc_bvh_view(const skc_ctx *ctx) {
-    BvhView bv; bv.nodes = ctx->bvhNodes; bv.prims = ctx->bvhPrims; bv.spheres = ctx->spheres; bv.wide = ctx->bvhWideOn ? ctx->bvhWide : nullptr; return bv;
+    BvhView bv; bv.nodes = ctx->bvhNodes; bv.prims = ctx->bvhPrims; bv.spheres = ctx->spheres; bv.wide = ctx->bvhWideOn ? ctx->bvhWide : nullptr;
+    bv.alphaTex = ctx->alphaTex; bv.alphaUV = ctx->alphaUV; bv.alphaW = ctx->alphaW; bv.alphaH = ctx->alphaH;
+    bv.alphaSu = ctx->alphaMap[0]; bv.alphaSv = ctx->alphaMap[1]; bv.alphaDu = ctx->alphaMap[2]; bv.alphaDv = ctx->alphaMap[3];
+    return bv;
 }
+// Triangle::GetUVs (shapes/trianglemesh.h:84-97) of every BVH primitive: the mesh's uvs, or (0,0) (1,0) (1,1)
+__global__ void k_alpha_uv(const int4 *__restrict__ primInfo, const float *__restrict__ UV, uint32_t nPrims, float *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPrims) return;
+    const int4 v = primInfo[i];
+    float *o = out + 6 * (size_t)i;
+    if (UV && v.w == 0) { o[0] = UV[2 * v.x]; o[1] = UV[2 * v.x + 1]; o[2] = UV[2 * v.y]; o[3] = UV[2 * v.y + 1]; o[4] = UV[2 * v.z]; o[5] = UV[2 * v.z + 1]; }
+    else { o[0] = 0.f; o[1] = 0.f; o[2] = 1.f; o[3] = 0.f; o[4] = 1.f; o[5] = 1.f; }
+}
+
+// The mesh's "texture alpha" (a float imagemap: shapes/trianglemesh.cpp:411-421, textures/imagemap.cpp): level-0 texels [h][w] as
+// ImageTexture<float, float> holds them (scale * (powf(y, gamma) + shift), made by the caller), and the UVMapping2D.  Call after
+// skc_upload_bvh (the primitives' uvs are taken from the uploaded mesh).  w == 0 removes it.
+extern "C" int skc_upload_alpha(skc_ctx *ctx, uint32_t w, uint32_t h, const float *texels, float su, float sv, float du, float dv) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->alphaTex) { cudaFree(ctx->alphaTex); ctx->alphaTex = nullptr; }
+    if (ctx->alphaUV) { cudaFree(ctx->alphaUV); ctx->alphaUV = nullptr; }
+    ctx->alphaW = ctx->alphaH = 0;
+    if (!w || !h) return 0;
+    if (!texels) return skc_fail(ctx, "skc_upload_alpha: null texels");
+    if (!ctx->primInfo || !ctx->nPrims) return skc_fail(ctx, "skc_upload_alpha: upload the BVH and the mesh first (skc_upload_bvh)");
+    SKC_CUDA(cudaMalloc((void **)&ctx->alphaTex, (size_t)w * h * sizeof(float)));
+    SKC_CUDA(cudaMalloc((void **)&ctx->alphaUV, (size_t)ctx->nPrims * 6 * sizeof(float)));
+    SKC_CUDA(cudaMemcpyAsync(ctx->alphaTex, texels, (size_t)w * h * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_alpha_uv<<<(ctx->nPrims + 255) / 256, 256, 0, ctx->stream>>>(ctx->primInfo, ctx->meshUV, ctx->nPrims, ctx->alphaUV);
+    SKC_LAUNCHED("k_alpha_uv");
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->alphaW = (int)w; ctx->alphaH = (int)h;
+    ctx->alphaMap[0] = su; ctx->alphaMap[1] = sv; ctx->alphaMap[2] = du; ctx->alphaMap[3] = dv;
+    return 0;
+}
+
 MeshView skc_mesh_view(const skc_ctx *ctx) {
     MeshView mv; mv.primInfo = ctx->primInfo; mv.P = ctx->meshP; mv.N = ctx->meshN; mv.UV = ctx->meshUV;
     memcpy(mv.o2w, ctx->meshO2W, 64); memcpy(mv.w2o, ctx->meshO2W + 16, 64); mv.flip = ctx->meshFlip;

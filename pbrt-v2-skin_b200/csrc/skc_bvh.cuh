@@ -19,6 +19,11 @@ struct BvhView {
     const float4 *prims;
     const skc_light *spheres;
     const float4 *wide;        // 4-wide form of the same tree for any-hit rays (8 float4 per node, see bvhOccludedWide), or nullptr
+    // alpha-tested triangles (shapes/trianglemesh.inl:117-126,174-207): the mesh's "texture alpha" as level-0 float texels with
+    // its UVMapping2D, and the three vertices' (u, v) of every BVH primitive; alphaTex == nullptr: no alpha texture
+    const float *alphaTex = nullptr, *alphaUV = nullptr;
+    int alphaW = 0, alphaH = 0;
+    float alphaSu = 1.f, alphaSv = 1.f, alphaDu = 0.f, alphaDv = 0.f;
 };
 
 // What closest-hit shading needs of the triangle mesh (shapes/trianglemesh.inl:224-299).
@@ -28,6 +33,26 @@ struct MeshView {
     float o2w[16], w2o[16];    // mesh ObjectToWorld matrix and inverse
     int flip;                  // ReverseOrientation ^ TransformSwapsHandedness
 };
+
+// Triangle::Intersect / IntersectP's alpha test: the texture at the hit's interpolated (u, v) -- UVMapping2D, then
+// MIPMap<float>::Lookup with zero differentials = triangle(0, s, t) (textures/imagemap.cpp:92-101, core/mipmap.h:253-264,
+// TEXTURE_REPEAT) -- and the hit is ignored where it evaluates to exactly 0.
+__device__ __forceinline__ int alphaWrap(int a, int b) { int n = a / b; a -= n * b; if (a < 0) a += b; return a; }
+__device__ inline bool alphaOpaque(const BvhView &bv, uint32_t prim, float b1, float b2) {
+    const float *uv = bv.alphaUV + 6 * (size_t)prim;
+    const float b0 = 1 - b1 - b2;
+    const float tu = b0 * __ldg(uv) + b1 * __ldg(uv + 2) + b2 * __ldg(uv + 4);
+    const float tv = b0 * __ldg(uv + 1) + b1 * __ldg(uv + 3) + b2 * __ldg(uv + 5);
+    float s = bv.alphaSu * tu + bv.alphaDu, t = bv.alphaSv * tv + bv.alphaDv;
+    s = s * (float)bv.alphaW - 0.5f;
+    t = t * (float)bv.alphaH - 0.5f;
+    const int s0 = (int)floorf(s), t0 = (int)floorf(t);
+    const float ds = s - (float)s0, dt = t - (float)t0;
+    const int sa = alphaWrap(s0, bv.alphaW), sb = alphaWrap(s0 + 1, bv.alphaW), ta = alphaWrap(t0, bv.alphaH), tb = alphaWrap(t0 + 1, bv.alphaH);
+    const float v = (1.f - ds) * (1.f - dt) * __ldg(&bv.alphaTex[(size_t)ta * bv.alphaW + sa]) + (1.f - ds) * dt * __ldg(&bv.alphaTex[(size_t)tb * bv.alphaW + sa]) +
+                    ds * (1.f - dt) * __ldg(&bv.alphaTex[(size_t)ta * bv.alphaW + sb]) + ds * dt * __ldg(&bv.alphaTex[(size_t)tb * bv.alphaW + sb]);
+    return v != 0.f;
+}
 
 __device__ __forceinline__ f3 xformPoint(const float *m, f3 p) {
     float xp = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];
@@ -258,9 +283,10 @@ __device__ inline bool bvhOccluded(const BvhView &bv, const DRay &ray, unsigned 
                     if (COUNT) nPrim++;
                     float t, b1, b2;
                     bool h;
-                    if (__float_as_int(c.y) == 0)
+                    if (__float_as_int(c.y) == 0) {
                         h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
-                    else
+                        if (h && bv.alphaTex) h = alphaOpaque(bv, offset + i, b1, b2);
+                    } else
                         h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
                     if (h) { occluded = true; break; }
                 }
@@ -318,8 +344,10 @@ __device__ __forceinline__ bool leafOccluded(const BvhView &bv, uint32_t first, 
         float4 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2);
         float t, b1, b2;
         bool h;
-        if (__float_as_int(c.y) == 0) h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
-        else h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
+        if (__float_as_int(c.y) == 0) {
+            h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
+            if (h && bv.alphaTex) h = alphaOpaque(bv, first + i, b1, b2);
+        } else h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
         if (h) return true;
     }
     return false;
@@ -375,9 +403,10 @@ __device__ inline int bvhClosest(const BvhView &bv, DRay &ray, float *b1Hit, flo
                     if (COUNT) nPrim++;
                     float t, b1 = 0.f, b2 = 0.f;
                     bool h;
-                    if (__float_as_int(c.y) == 0)
+                    if (__float_as_int(c.y) == 0) {
                         h = triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
-                    else
+                        if (h && bv.alphaTex) h = alphaOpaque(bv, offset + i, b1, b2);
+                    } else
                         h = sphereIntersect(bv.spheres[__float_as_int(c.z)], ray, &t);
                     if (h) { ray.maxt = t; hitPrim = (int)(offset + i); *b1Hit = b1; *b2Hit = b2; }
                 }

@@ -79,6 +79,9 @@ struct skc_ctx {
     float mocInvA = 0.f, mocM = 0.f;
     int moTable = 1;               // 1 = k_mo_lambda (compact table in shared memory + exact fallback) when the table's windows cover enough of the tables (MOC_MIN_COVERAGE), else k_mo_packet; 0 = always k_mo_packet, 2 = always k_mo_lambda; env SKC_MO_TABLE=exact|auto|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
+    float *alphaTex = nullptr, *alphaUV = nullptr;     // the mesh's alpha texture (skc_upload_alpha) and per-primitive vertex uvs; null: none
+    int alphaW = 0, alphaH = 0;
+    float alphaMap[4] = {1.f, 1.f, 0.f, 0.f};          // UVMapping2D su, sv, du, dv
     EnvMapDev env;                    // of the scene's infinite light (light record with radius -4); env.rgb == nullptr: none
     float *envStore = nullptr;        // one allocation behind env's pointers
     float *albedoFactors = nullptr;   // [2][32]: Pow(albedo, mix), Pow(albedo, 1 - mix) of a constant "color albedo" (skc_set_albedo_factors); null = Spectrum(1)

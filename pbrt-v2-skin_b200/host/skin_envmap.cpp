@@ -107,6 +107,19 @@ bool ReadPfm(const std::string &path, int *w, int *h, std::vector<Rgb> *out, std
 
 }  // namespace
 
+bool LoadAlphaTexture(const std::string &file, float shift, float scale, float gamma, AlphaTexture *out, std::string *err) {
+    int w = 0, h = 0;
+    std::vector<Rgb> px;
+    if (!ReadPfm(file, &w, &h, &px, err)) return false;
+    if ((w & (w - 1)) || (h & (h - 1))) { *err = "texture \"" + file + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)"; return false; }
+    out->present = true; out->w = w; out->h = h; out->texels.resize(px.size());
+    for (size_t i = 0; i < px.size(); ++i) {
+        const float y = 0.212671f * px[i].r + 0.715160f * px[i].g + 0.072169f * px[i].b;       // RGBSpectrum::y()
+        out->texels[i] = scale * (powf(y, gamma) + shift);                                  // convertIn (textures/imagemap.h:94-97)
+    }
+    return true;
+}
+
 // SampledSpectrum::ToRGB (core/spectrum.h:374-398): ToXYZ's running sums over the 30 samples, then XYZToRGB
 void SpectrumToRGB(const float c[30], float rgb[3]) {
     float xyz[3] = {0.f, 0.f, 0.f};

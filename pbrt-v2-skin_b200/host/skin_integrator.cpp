@@ -120,6 +120,14 @@ const float *skh_env_array(const skh_scene *s, int which) {
     const std::vector<float> *v[6] = {&e.rgb, &e.condFunc, &e.condCdf, &e.condInt, &e.margFunc, &e.margCdf};
     return which >= 0 && which < 6 ? v[which]->data() : nullptr;
 }
+// The device mesh's alpha texture: sizes {w, h} (0 = none) and mapping {su, sv, du, dv}; the texels
+static const AlphaTexture &alphaOf(const skh_scene *s) { return s->built.mesh ? s->built.mesh->alpha : s->sd.meshes[0].alpha; }
+void skh_alpha_info(const skh_scene *s, int *wh2, float *map4) {
+    const AlphaTexture &a = alphaOf(s);
+    wh2[0] = a.present ? a.w : 0; wh2[1] = a.present ? a.h : 0;
+    map4[0] = a.su; map4[1] = a.sv; map4[2] = a.du; map4[3] = a.dv;
+}
+const float *skh_alpha_texels(const skh_scene *s) { return alphaOf(s).texels.data(); }
 // "color albedo" of the material: rgb, and whether it was given at all (Spectrum(1) otherwise)
 int skh_skin_albedo(const skh_scene *s, float *rgb3) { memcpy(rgb3, s->sd.skin.albedo, 12); return s->sd.skin.hasAlbedo ? 1 : 0; }
 // Tessellation (Preprocess' point source).  Returns the count; pointer valid until the next call.

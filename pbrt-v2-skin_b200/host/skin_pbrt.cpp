@@ -86,6 +86,8 @@ private:
     std::vector<GraphicsState> pushedGraphicsStates;
     std::vector<Transform> pushedTransforms;
     std::map<std::string, std::string> textures;              // name -> class, declared but not evaluable here
+    std::map<std::string, std::string> floatImageMapErrors;
+    std::map<std::string, AlphaTexture> floatImageMaps;        // Texture ".." "float" "imagemap": usable as a mesh's "texture alpha"
     std::map<std::string, GraphicsState> namedMaterials;      // MakeNamedMaterial: type in .material, params in .materialParams
     uint32_t nextMaterialId = 0;                              // core/material.h:63 (one Material object per Shape / MakeNamedMaterial)
     std::map<std::string, uint32_t> namedMaterialIds;
@@ -443,7 +445,16 @@ void Front::shape(const std::string &name, const ParamSet &ps) {
         idx[i] = (int)(*vi)[i];
         if (idx[i] >= npi) { Error("trianglemesh has out of-bounds vertex index %d (%d \"P\" values were given", idx[i], npi); return; }
     }
-    if (!ps.FindTexture("alpha").empty() || ps.FindOneFloat("alpha", 1.f) == 0.f) { Error("trianglemesh \"alpha\" is not supported on the device path"); return; }
+    AlphaTexture alpha;                                       // shapes/trianglemesh.cpp:411-421
+    const std::string alphaName = ps.FindTexture("alpha");
+    if (!alphaName.empty()) {
+        if (!floatImageMaps.count(alphaName)) {
+            Error("trianglemesh \"texture alpha\" \"%s\": %s", alphaName.c_str(), floatImageMapErrors.count(alphaName) ? floatImageMapErrors[alphaName].c_str()
+                  : textures.count(alphaName) ? "only float \"imagemap\" textures are supported as alpha on the device path" : "Couldn't find float texture");
+            return;
+        }
+        alpha = floatImageMaps[alphaName];
+    } else if (ps.FindOneFloat("alpha", 1.f) == 0.f) { Error("trianglemesh \"float alpha\" 0 (a fully transparent mesh) is not supported on the device path"); return; }
     SkinParams k;
     if (!skinFromParams(*matParams, ps, &k)) return;
     reportUnused(*matParams, "Material \"layeredskin\"");
@@ -452,6 +463,7 @@ void Front::shape(const std::string &name, const ParamSet &ps) {
     TriangleMesh m;
     InitMesh(&m, ctm, gs.reverseOrientation, npi, P->data(), N ? N->data() : nullptr, uvs ? uvs->data() : nullptr, nvi / 3, idx.data());
     m.materialId = materialId;
+    m.alpha = alpha;
     reportUnused(ps, "Shape \"trianglemesh\"");
     sd->primOrder.push_back(PrimRef{0, (int)sd->meshes.size()});
     sd->meshes.push_back(std::move(m));
@@ -676,6 +688,16 @@ bool Front::statement(const std::string &id) {
         std::string type, texname;
         if (!string(&name, "Texture") || !string(&type, "Texture") || !string(&texname, "Texture") || !paramlist(&ps) || !needWorld("Texture")) return false;
         textures[name] = texname;                             // declared; refused where a skin material binds it
+        if (type == "float" && texname == "imagemap") {       // CreateImageFloatTexture (textures/imagemap.cpp:103-140): kept for "texture alpha"
+            const std::string mapping = ps.FindOneString("mapping", "uv"), wrap = ps.FindOneString("wrap", "repeat");
+            AlphaTexture a; std::string err;
+            if (mapping == "uv" && wrap == "repeat" &&
+                LoadAlphaTexture(resolve(ps.FindOneString("filename", "")), ps.FindOneFloat("shift", 0.f), ps.FindOneFloat("scale", 1.f), ps.FindOneFloat("gamma", 1.f), &a, &err)) {
+                a.su = ps.FindOneFloat("uscale", 1.f); a.sv = ps.FindOneFloat("vscale", 1.f); a.du = ps.FindOneFloat("udelta", 0.f); a.dv = ps.FindOneFloat("vdelta", 0.f);
+                ps.FindOneFloat("maxanisotropy", 8.f); ps.FindOneBool("trilinear", false);      // without effect on a lookup with zero differentials
+                floatImageMaps[name] = a;
+            } else floatImageMapErrors[name] = err.empty() ? "only \"uv\" mapping with \"repeat\" wrap is supported" : err;
+        }
         return true;
     }
     if (id == "Shape") {

@@ -71,6 +71,11 @@ int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
     return skc_upload_lights(ctx, b.lights.data(), (uint32_t)b.lights.size());
 }
 
+int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a) {
+    if (!a.present) return skc_upload_alpha(ctx, 0, 0, nullptr, 1.f, 1.f, 0.f, 0.f);
+    return skc_upload_alpha(ctx, (uint32_t)a.w, (uint32_t)a.h, a.texels.data(), a.su, a.sv, a.du, a.dv);
+}
+
 int UploadEnvMap(skc_ctx *ctx, const EnvMap &e) {
     if (!e.present) return skc_upload_envmap(ctx, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0.f);
     return skc_upload_envmap(ctx, (uint32_t)e.w, (uint32_t)e.h, e.rgb.data(), e.condFunc.data(), e.condCdf.data(), e.condInt.data(), e.margFunc.data(), e.margCdf.data(), e.margInt);
@@ -86,7 +91,7 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
     const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
     double t0 = now();
-    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env))) return false;
+    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env)) || !dev(UploadAlpha(ctx, built.mesh->alpha))) return false;
     double t1 = now();
     if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(InstallAlbedo(ctx, sd.skin, sd.mix)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
@@ -197,7 +202,7 @@ bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *
     BuiltScene built;
     if (!BuildScene(sd, nullptr, &built, err)) return false;
     uint64_t n = 0;
-    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
+    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || UploadAlpha(ctx, built.mesh->alpha) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
     *nPoints = n;
     if (sd.rendererFilename.empty()) return true;                            // "(Not writing to file)"
     std::vector<skc_surface_point> pts(n);

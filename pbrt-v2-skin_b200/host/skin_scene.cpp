@@ -307,6 +307,7 @@ bool SceneDesc::LoadLines(const std::string &path) {
     std::ifstream in(path);
     if (!in) { error = "cannot open scene " + path; return false; }
     std::string dir = path.substr(0, path.find_last_of('/') + 1), line;
+    AlphaTexture pendingAlpha;
     Transform cur;   // CTM of the next mesh (pbrtTranslate etc. post-multiply: core/api.cpp:720-756)
     uint32_t nextMaterialId = 0;
     while (std::getline(in, line)) {
@@ -376,11 +377,17 @@ bool SceneDesc::LoadLines(const std::string &path) {
             else if (kind == "rotate") cur = cur * Rotate(v[0], V3(v[1], v[2], v[3]));
             else if (kind == "scale") cur = cur * Scale(v[0], v[1], v[2]);
             else { error = "unknown xform " + kind; return false; }
+        } else if (key == "alpha") {
+            // alpha <map.pfm>: Texture "a" "float" "imagemap" "string filename" + "texture alpha" "a" on the next mesh
+            std::string file; ls >> file;
+            if (file[0] != '/') file = dir + file;
+            if (!LoadAlphaTexture(file, 0.f, 1.f, 1.f, &pendingAlpha, &error)) return false;
         } else if (key == "mesh") {
             std::string file; ls >> file;
             if (file[0] != '/') file = dir + file;
             TriangleMesh m;
             if (!loadMesh(file, cur, &m, &error)) return false;
+            m.alpha = pendingAlpha; pendingAlpha = AlphaTexture();
             m.materialId = nextMaterialId++;
             meshes.push_back(std::move(m));
             cur = Transform();
@@ -402,8 +409,10 @@ bool BuildScene(const SceneDesc &sd, const float *Lemit30PerLight, BuiltScene *o
         const TriangleMesh &m0 = sd.meshes[0];
         m.ObjectToWorld = m0.ObjectToWorld; m.ReverseOrientation = m0.ReverseOrientation; m.TransformSwapsHandedness = m0.TransformSwapsHandedness;
         m.materialId = m0.materialId;
+        m.alpha = m0.alpha;
         for (size_t k = 0; k < sd.meshes.size(); ++k) {
             const TriangleMesh &mk = sd.meshes[k];
+            if (!(mk.alpha == m0.alpha)) { *err = "several skin meshes with different alpha textures cannot be joined into the one mesh the device path holds"; return false; }
             if (mk.ReverseOrientation != m0.ReverseOrientation || mk.TransformSwapsHandedness != m0.TransformSwapsHandedness || mk.n.empty() != m0.n.empty() ||
                 mk.uvs.empty() != m0.uvs.empty() ||
                 (!m0.n.empty() && memcmp(&mk.ObjectToWorld, &m0.ObjectToWorld, sizeof(Transform)) != 0)) {

@@ -17,8 +17,21 @@
 
 namespace skin {
 
+// The mesh's "texture alpha": a float image map (textures/imagemap.cpp CreateImageFloatTexture) as its MIPMap's level-0 texels and its
+// UVMapping2D; the triangle tests ignore a hit whose texture value is exactly 0 (shapes/trianglemesh.inl:117-126,174-207)
+struct AlphaTexture {
+    bool present = false;
+    int w = 0, h = 0;
+    std::vector<float> texels;                  // [h][w]: scale * (powf(luminance, gamma) + shift)
+    float su = 1.f, sv = 1.f, du = 0.f, dv = 0.f;
+    bool operator==(const AlphaTexture &o) const { return present == o.present && w == o.w && h == o.h && texels == o.texels && su == o.su && sv == o.sv && du == o.du && dv == o.dv; }
+};
+// ImageTexture<float, float> of a PFM file (power-of-two sizes), textures/imagemap.cpp:56-86 + imagemap.h:94-97
+bool LoadAlphaTexture(const std::string &file, float shift, float scale, float gamma, AlphaTexture *out, std::string *err);
+
 struct TriangleMesh {
     int ntris = 0, nverts = 0;
+    AlphaTexture alpha;
     std::vector<int> vertexIndex;
     std::vector<V3> p;       // WORLD space (shapes/trianglemesh.cpp:72-73)
     std::vector<V3> n;       // object space, may be empty
@@ -179,7 +192,8 @@ void MakeFrameDesc(const SceneDesc &sd, int nCores, skc_frame_desc *d);
 int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nullptr);
 // the two albedo factors of the material for an integrator's `mix` -> skc_set_albedo_factors (cleared when the albedo is the default)
 int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);
-int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
+int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);
+int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a);    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,

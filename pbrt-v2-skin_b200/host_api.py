@@ -36,6 +36,8 @@ def load_host_library():
     lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
     lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
+    lib.skh_alpha_info.restype = None; lib.skh_alpha_info.argtypes = [vp, vp, vp]
+    lib.skh_alpha_texels.restype = vp; lib.skh_alpha_texels.argtypes = [vp]
     lib.skh_env_sizes.restype = C.c_float; lib.skh_env_sizes.argtypes = [vp, vp]
     lib.skh_env_array.restype = vp; lib.skh_env_array.argtypes = [vp, C.c_int]
     lib.skh_skin_albedo.restype = C.c_int; lib.skh_skin_albedo.argtypes = [vp, vp]
@@ -165,10 +167,20 @@ class HostScene:
             out[k] = _view(self.lib.skh_env_array(self.h, i), 4 * n[k], np.float32).copy()
         return out
 
+    def alpha_texture(self):
+        """The mesh's "texture alpha" (level-0 float texels and its uv mapping), or None."""
+        wh = np.zeros(2, np.int32); m = np.zeros(4, np.float32)
+        self.lib.skh_alpha_info(self.h, wh.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p))
+        if not wh[0]:
+            return None
+        w, h = int(wh[0]), int(wh[1])
+        return {"w": w, "h": h, "map": tuple(float(x) for x in m), "texels": _view(self.lib.skh_alpha_texels(self.h), 4 * w * h, np.float32).reshape(h, w).copy()}
+
     def upload(self, dev):
         dev.upload_bvh(self.nodes, self.prims, self.P, self.N, self.uv, self.idx, self.o2w, self.reverse, self.swaps, self.lights)
         dev.upload_lights(self.lights)
         dev.upload_envmap(self.envmap())
+        dev.upload_alpha(self.alpha_texture())
 
     FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1 + 2)
 

@@ -130,6 +130,10 @@ def lights_golden(name="skin_lights"):
             camera_xy=f32("camera_xy.bin").reshape(-1, 2), L=f32("L.bin").reshape(-1, 30), L_sss=f32("L_sss.bin").reshape(-1, 30),
             image=read_pfm(os.path.join(d, "image.pfm")),
         )
+        if os.path.exists(os.path.join(d, "mesh0_alpha.bin")):  # "texture alpha": the float image map's level-0 texels
+            arrays["alpha"] = f32("mesh0_alpha.bin")
+            arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
+            arrays["camera_rays"] = f32("camera_rays.bin").reshape(-1, 8)
         if os.path.exists(os.path.join(d, "envmap.bin")):      # LightSource "infinite": its map and Distribution2D (ref_driver dumpLights)
             arrays["envmap"] = f32("envmap.bin")
     path = os.path.join(OUT, name + ".npz")
@@ -319,4 +323,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env") else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha") else scene_golden(w)

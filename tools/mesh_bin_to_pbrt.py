@@ -8,7 +8,8 @@ import sys
 import numpy as np
 
 
-def convert(src, dst):
+def convert(src, dst, extra=""):
+    """extra: further parameters of the Shape directive, e.g. '"texture alpha" "alphamap"'."""
     raw = open(src, "rb").read()
     nv, nt, has_n, has_uv = np.frombuffer(raw, np.int32, 4)
     off = 16
@@ -29,7 +30,10 @@ def convert(src, dst):
             f.write('    "normal N" [\n%s\n    ]\n' % rows(N))
         if uv is not None:
             f.write('    "float uv" [\n%s\n    ]\n' % rows(uv))
-        f.write('    "integer indices" [\n%s\n    ]\nAttributeEnd\n' % "\n".join("      %d %d %d" % tuple(r) for r in idx))
+        f.write('    "integer indices" [\n%s\n    ]\n' % "\n".join("      %d %d %d" % tuple(r) for r in idx))
+        if extra:
+            f.write("    %s\n" % extra)
+        f.write("AttributeEnd\n")
     return int(nv), int(nt)
 
 
