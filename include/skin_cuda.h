@@ -220,6 +220,14 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * only.  stats8 = {rows, shared-memory bytes, coverage, largest verified relative error inside the windows, and
  * from the last counted skc_camera_pass_resident: lookups in range, from the shared-memory table heads, from the
  * global tables, 0}. */
+/* LayeredSkin's "texture albedo" as an image map (materials/layeredskin.cpp:183,247; textures/imagemap.cpp): the nLevels levels of its
+ * MIPMap<RGBSpectrum> (w[l] x h[l] texels each, rgb = the levels one after the other, [h][w][3]; values as ImageTexture holds them),
+ * the EWA weight table (core/mipmap.h:186-193) and the UVMapping2D.  E of an irradiance point is scaled by Pow(albedo(u, v), mix)
+ * (multipolesubsurface.cpp:139-140; zero differentials: bilinear lookup at level 0), the subsurface term of a camera hit by
+ * Pow(albedo, 1 - mix) (:287) with the EWA lookup under the camera ray's differentials (skc_frame_* path only).  Overrides
+ * skc_set_albedo_factors.  nLevels == 0 removes it. */
+int skc_upload_albedo_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *rgb, const float *weightLut128,
+                              float su, float sv, float du, float dv);
 /* Alpha-tested triangles (shapes/trianglemesh.inl:117-126,174-207): the mesh's "texture alpha", a float image map.  texels [h][w] are
  * the values ImageTexture<float, float> holds at MIPMap level 0 -- scale * (powf(luminance, gamma) + shift), made by the caller
  * (textures/imagemap.h:94-97); su, sv, du, dv its UVMapping2D.  Every ray-triangle hit, closest or any, whose texture value at the

@@ -118,6 +118,7 @@ struct SceneDesc {
     float layers[4] = {0.25e6f, 1.4f, 20e6f, 1.4f};
     float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};     // "color Kr" / "color Kt" as the skin scenes give them
     float albedo[3] = {1, 1, 1}; bool hasAlbedo = false;      // "color albedo" (materials/layeredskin.cpp:247)
+    std::string albedoTex;                                     // "texture albedo": PFM of a "color" image map
     struct Xf { std::string kind; float v[4]; };
     struct Mesh { std::vector<Xf> xf; std::string file; std::string alpha; };      // alpha: PFM of the mesh's "texture alpha" (float imagemap)
     std::vector<Mesh> meshes;
@@ -170,6 +171,7 @@ static SceneDesc parseScene(const std::string &path) {
                 else if (k == "Kr") { for (int i = 0; i < 3; ++i) ls >> sd.Kr[i]; }
                 else if (k == "Kt") { for (int i = 0; i < 3; ++i) ls >> sd.Kt[i]; }
                 else if (k == "albedo") { for (int i = 0; i < 3; ++i) ls >> sd.albedo[i]; sd.hasAlbedo = true; }
+                else if (k == "albedotex") { ls >> sd.albedoTex; if (sd.albedoTex[0] != '/') sd.albedoTex = dir + sd.albedoTex; }
                 else { float v; ls >> v; sd.skin[k] = v; }
             }
         }
@@ -257,6 +259,11 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
             }
             ps.AddRGBSpectrum("Kr", sd.Kr, 3); ps.AddRGBSpectrum("Kt", sd.Kt, 3);
             if (sd.hasAlbedo) ps.AddRGBSpectrum("albedo", sd.albedo, 3);
+            if (!sd.albedoTex.empty()) {      // Texture "albedomap" "color" "imagemap" "string filename" + "texture albedo" (materials/layeredskin.cpp:247)
+                ParamSet tp; tp.AddString("filename", &sd.albedoTex, 1);
+                pbrtTexture("albedomap", "color", "imagemap", tp);
+                std::string nm = "albedomap"; ps.AddTexture("albedo", nm);
+            }
             SkinLayer sl[2]; sl[0].thickness = sd.layers[0]; sl[0].ior = sd.layers[1];
             sl[1].thickness = sd.layers[2]; sl[1].ior = sd.layers[3];
             ps.AddSkinLayer("layers", sl, 2);
@@ -332,6 +339,19 @@ static void dumpSpectrumConsts(const std::string &dir) {
 }
 
 static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
+    if (const ImageTexture<RGBSpectrum, Spectrum> *it = dynamic_cast<const ImageTexture<RGBSpectrum, Spectrum> *>(skin->albedo.GetPtr())) {
+        // "texture albedo": the MIPMap's whole pyramid -- int32 nLevels, then per level int32 w, h and rgb[h][w][3] -- and the EWA weight table
+        std::vector<float> a;
+        auto pushInt = [&](int32_t v) { float f; memcpy(&f, &v, 4); a.push_back(f); };
+        pushInt((int32_t)it->mipmap->nLevels);
+        for (uint32_t l = 0; l < it->mipmap->nLevels; ++l) {
+            const int w = (int)it->mipmap->pyramid[l]->uSize(), h = (int)it->mipmap->pyramid[l]->vSize();
+            pushInt(w); pushInt(h);
+            for (int t = 0; t < h; ++t) for (int s2 = 0; s2 < w; ++s2) { float c3[3]; it->mipmap->Texel(l, s2, t).ToRGB(c3); a.push_back(c3[0]); a.push_back(c3[1]); a.push_back(c3[2]); }
+        }
+        for (int i = 0; i < WEIGHT_LUT_SIZE; ++i) a.push_back(MIPMap<RGBSpectrum>::weightLut[i]);
+        dump(dir + "/albedo_tex.bin", a.data(), a.size());
+    }
     const MultipoleBSSRDFData *bd = skin->preparedBSSRDFData;
     std::vector<float> coeff;   // [layer][mua30 | musp30], then eta[2], thickness[2]
     for (int l = 0; l < 2; ++l) {

@@ -28,6 +28,19 @@ struct EnvMapDev {
     int w = 0, h = 0;
 };
 
+// LayeredSkin's "texture albedo" on the device (skc_upload_albedo_texture): the MIPMap pyramid, the EWA weight table, the
+// UVMapping2D and the reflectance basis spectra of Spectrum::FromRGB (textures/imagemap.h:98-102)
+#define SKC_TEX_MAX_LEVELS 14
+struct AlbedoTexDev {
+    const float *rgb = nullptr;                    // levels one after the other, [h][w][3] each; nullptr: no texture
+    const float *lut = nullptr;                    // [128]
+    const float *refl = nullptr;                   // [7][32] white, cyan, magenta, yellow, red, green, blue
+    int nLevels = 0;
+    int w[SKC_TEX_MAX_LEVELS] = {0}, h[SKC_TEX_MAX_LEVELS] = {0};
+    uint32_t off[SKC_TEX_MAX_LEVELS] = {0};        // first float of each level
+    float su = 1.f, sv = 1.f, du = 0.f, dv = 0.f;
+};
+
 struct skc_ctx {
     int device = 0;
     int smCount = 148;
@@ -79,6 +92,8 @@ struct skc_ctx {
     float mocInvA = 0.f, mocM = 0.f;
     int moTable = 1;               // 1 = k_mo_lambda (compact table in shared memory + exact fallback) when the table's windows cover enough of the tables (MOC_MIN_COVERAGE), else k_mo_packet; 0 = always k_mo_packet, 2 = always k_mo_lambda; env SKC_MO_TABLE=exact|auto|compact
     float mocCoverage = 0.f, mocMaxErr = 0.f;
+    AlbedoTexDev albedoTex;           // "texture albedo" of the skin material; albedoTex.rgb == nullptr: none
+    float *albedoTexStore = nullptr;
     float *alphaTex = nullptr, *alphaUV = nullptr;     // the mesh's alpha texture (skc_upload_alpha) and per-primitive vertex uvs; null: none
     int alphaW = 0, alphaH = 0;
     float alphaMap[4] = {1.f, 1.f, 0.f, 0.f};          // UVMapping2D su, sv, du, dv
@@ -306,6 +321,61 @@ __device__ __forceinline__ float skc_atanf(float x) {      // sysdeps/ieee754/fl
     if (id < 0) return __fsub_rn(x, __fmul_rn(x, __fadd_rn(s1, s2)));
     const float zr = __fsub_rn(atanhi[id], __fsub_rn(__fsub_rn(__fmul_rn(x, __fadd_rn(s1, s2)), atanlo[id]), x));
     return hx < 0 ? -zr : zr;
+}
+
+// powf as glibc 2.39 computes it (sysdeps/ieee754/flt-32/e_powf.c, the FMA build): log2(x) from a 16-entry table and a degree-5
+// polynomial in double, y * log2(x), then exp2 from skc_expf's 2^(i/32) table and a cubic, one rounding to float.  The tables are the
+// system libm's own (__powf_log2_data); checked against libm's powf on 3e8 arguments on the CPU, 0 differences.  x >= 0, y >= 0
+// finite (Pow(Spectrum, float) of reflectances: core/spectrum.h).
+static __device__ const double skcPowLog2Tab[16][2] = {
+  {0x1.661ec79f8f3bep+0, -0x1.efec65b963019p-2},
+  {0x1.571ed4aaf883dp+0, -0x1.b0b6832d4fca4p-2},
+  {0x1.49539f0f010b0p+0, -0x1.7418b0a1fb77bp-2},
+  {0x1.3c995b0b80385p+0, -0x1.39de91a6dcf7bp-2},
+  {0x1.30d190c8864a5p+0, -0x1.01d9bf3f2b631p-2},
+  {0x1.25e227b0b8ea0p+0, -0x1.97c1d1b3b7af0p-3},
+  {0x1.1bb4a4a1a343fp+0, -0x1.2f9e393af3c9fp-3},
+  {0x1.12358f08ae5bap+0, -0x1.960cbbf788d5cp-4},
+  {0x1.0953f419900a7p+0, -0x1.a6f9db6475fcep-5},
+  {0x1.0000000000000p+0, 0x0.0p+0},
+  {0x1.e608cfd9a47acp-1, 0x1.338ca9f24f53dp-4},
+  {0x1.ca4b31f026aa0p-1, 0x1.476a9543891bap-3},
+  {0x1.b2036576afce6p-1, 0x1.e840b4ac4e4d2p-3},
+  {0x1.9c2d163a1aa2dp-1, 0x1.40645f0c6651cp-2},
+  {0x1.886e6037841edp-1, 0x1.88e9c2c1b9ff8p-2},
+  {0x1.767dcf5534862p-1, 0x1.ce0a44eb17bccp-2}
+};
+__device__ __forceinline__ float skc_powf(float x, float y) {
+    if (x == 0.f) return y == 0.f ? 1.f : 0.f;
+    if (y == 0.f) return 1.f;
+    uint32_t ix = __float_as_uint(x);
+    if (ix < 0x00800000u) { ix = __float_as_uint(__fmul_rn(x, 8388608.f)) & 0x7fffffffu; ix -= 23u << 23; }      // subnormal x
+    const uint32_t tmp = ix - 0x3f330000u, top = tmp & 0xff800000u;
+    const int i = (int)((tmp >> 19) & 15u), k = (int)top >> 23;
+    const double invc = skcPowLog2Tab[i][0], logc = skcPowLog2Tab[i][1];
+    const double z = (double)__uint_as_float(ix - top);
+    const double r = __fma_rn(z, invc, -1.0);
+    const double y0 = __dadd_rn(logc, (double)k);
+    const double A0 = 0x1.27616c9496e0bp-2, A1 = -0x1.71969a075c67ap-2, A2 = 0x1.ec70a6ca7baddp-2, A3 = -0x1.7154748bef6c8p-1, A4 = 0x1.71547652ab82bp+0;
+    const double r2 = __dmul_rn(r, r);
+    double yy = __fma_rn(A0, r, A1);
+    const double p = __fma_rn(A2, r, A3);
+    const double r4 = __dmul_rn(r2, r2);
+    double q = __fma_rn(A4, r, y0);
+    q = __fma_rn(p, r2, q);
+    yy = __fma_rn(yy, r4, q);
+    const double ylogx = __dmul_rn((double)y, yy);
+    if (fabs(ylogx) >= 126.0) return ylogx > 0 ? __int_as_float(0x7f800000) : 0.f;      // out of the callers' range; not the reference's edge handling
+    const double SHIFT = 0x1.8p+52 / 32, C0 = 0x1.c6af84b912394p-5, C1 = 0x1.ebfce50fac4f3p-3, C2 = 0x1.62e42ff0c52d6p-1;
+    double kd = __dadd_rn(ylogx, SHIFT);
+    const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd = __dsub_rn(kd, SHIFT);
+    const double rr = __dsub_rn(ylogx, kd);
+    const double s = __longlong_as_double((long long)(skcExp2Tab[ki & 31] + (ki << 47)));
+    const double zz = __fma_rn(C0, rr, C1), rr2 = __dmul_rn(rr, rr);
+    double w = __fma_rn(C2, rr, 1.0);
+    w = __fma_rn(zz, rr2, w);
+    return (float)__dmul_rn(w, s);
 }
 
 __device__ __forceinline__ float skc_acosf(float x) {      // sysdeps/ieee754/flt-32/e_acosf.c (fdlibm, fp32, no contraction); tools/libm_check.c

@@ -97,7 +97,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhWide, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->mocRows, ctx->mocHeads, ctx->mocLam, ctx->mocHeadOff, ctx->lights, ctx->ipPosArea, ctx->ipE,
-                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors, ctx->envStore, ctx->alphaTex, ctx->alphaUV};
+                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors, ctx->envStore, ctx->alphaTex, ctx->alphaUV, ctx->albedoTexStore};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
     for (int i = 0; i < 24; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -126,6 +126,37 @@ extern "C" int skc_synchronize(skc_ctx *ctx) {
 }
 
 extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches; }
+// LayeredSkin's "texture albedo" (materials/layeredskin.cpp:183,247), an image map: nLevels levels of its MIPMap<RGBSpectrum> (sizes w[], h[],
+// texels rgb = the levels one after the other, [h][w][3] each, as ImageTexture holds them: scale * (Pow(rgb, gamma) + shift)), the EWA
+// filter's weight table (128 entries, core/mipmap.h:186-193) and the UVMapping2D.  The irradiance pass scales a point's E by
+// Pow(albedo(u, v), mix) (lookup with zero differentials = bilinear at level 0), Li a hit's subsurface term by Pow(albedo, 1 - mix)
+// with the EWA lookup under the camera ray's differentials.  nLevels == 0 removes it.
+extern "C" int skc_upload_albedo_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *rgb, const float *weightLut128,
+                                         float su, float sv, float du, float dv) {
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->albedoTexStore) { cudaFree(ctx->albedoTexStore); ctx->albedoTexStore = nullptr; }
+    ctx->albedoTex = AlbedoTexDev();
+    if (!nLevels) return 0;
+    if (nLevels > SKC_TEX_MAX_LEVELS || !w || !h || !rgb || !weightLut128) return skc_fail(ctx, "skc_upload_albedo_texture: bad arguments (at most %d levels)", SKC_TEX_MAX_LEVELS);
+    AlbedoTexDev t;
+    size_t total = 0;
+    for (uint32_t l = 0; l < nLevels; ++l) { t.w[l] = w[l]; t.h[l] = h[l]; t.off[l] = (uint32_t)total; total += (size_t)3 * w[l] * h[l]; }
+    float refl[7 * 32];
+    for (int k = 0; k < 7; ++k) for (int i = 0; i < 32; ++i) refl[k * 32 + i] = i < 30 ? kRGBRefl2Spect30[k][i] : 0.f;
+    const size_t texFloats = (total + 3) & ~(size_t)3;
+    SKC_CUDA(cudaMalloc((void **)&ctx->albedoTexStore, (texFloats + 128 + 7 * 32) * sizeof(float)));
+    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore, rgb, total * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore + texFloats, weightLut128, 128 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore + texFloats + 128, refl, sizeof refl, cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaStreamSynchronize(ctx->stream));
+    t.rgb = ctx->albedoTexStore; t.lut = ctx->albedoTexStore + texFloats; t.refl = t.lut + 128;
+    t.nLevels = (int)nLevels; t.su = su; t.sv = sv; t.du = du; t.dv = dv;
+    ctx->albedoTex = t;
+    return 0;
+}
+
 // The radiance map and sampling distribution of the scene's infinite light (light record with radius -4).  w, h: texels; rgb
 // [h][w][3]; condFunc [h][w], condCdf [h][w + 1], condInt [h]; margFunc [h], margCdf [h + 1].  w == 0 removes it.
 extern "C" int skc_upload_envmap(skc_ctx *ctx, uint32_t w, uint32_t h, const float *rgb, const float *condFunc, const float *condCdf,
@@ -230,9 +261,9 @@ __global__ void k_test_sincosf(const float *__restrict__ x, uint64_t n, float *_
 }
 __global__ void k_test_libmf(int fn, const float *__restrict__ x, uint64_t n, float *__restrict__ out) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = fn == 6 ? skc_atan2f(x[i], x[n - 1 - i]) : fn == 5 ? skc_acosf(x[i]) : fn == 2 ? skc_logf(x[i]) : fn == 3 ? skc_expf(x[i]) : fn == 4 ? skc_atanf(x[i]) : fn == 1 ? skc_cosf(x[i]) : skc_sinf(x[i]);
+    if (i < n) out[i] = fn == 7 ? skc_powf(x[i], x[n - 1 - i]) : fn == 6 ? skc_atan2f(x[i], x[n - 1 - i]) : fn == 5 ? skc_acosf(x[i]) : fn == 2 ? skc_logf(x[i]) : fn == 3 ? skc_expf(x[i]) : fn == 4 ? skc_atanf(x[i]) : fn == 1 ? skc_cosf(x[i]) : skc_sinf(x[i]);
 }
-// fn: 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf, 5 acosf, 6 atan2f(x[i], x[n - 1 - i])
+// fn: 0 sinf, 1 cosf, 2 logf, 3 expf, 4 atanf, 5 acosf, 6 atan2f(x[i], x[n - 1 - i]), 7 powf(x[i], x[n - 1 - i])
 extern "C" int skc_test_libmf(skc_ctx *ctx, int fn, const float *x, uint64_t n, float *out) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);

@@ -19,6 +19,7 @@
 #include <utility>
 #include <vector>
 #include "skc_light.cuh"
+#include "skc_texture.cuh"
 #include "skc_internal.h"
 
 // grid = tasks [taskFirst, taskFirst + gridDim.x); block = 256 threads
@@ -181,7 +182,7 @@ template <bool DELTA>
 __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restrict__ lights, IrrSlots sl, const float2 *__restrict__ cosPdf,
         uint64_t ptBase, uint32_t nPts, const float *__restrict__ rhoHd, const float *__restrict__ albedo, float mix,
         float *__restrict__ Eout, uint64_t outBase, const float4 *__restrict__ posArea, const float *__restrict__ albedoPowMix,
-        const float4 *__restrict__ envRgb, const float *__restrict__ envIllum) {
+        const float4 *__restrict__ envRgb, const float *__restrict__ envIllum, AlbedoTexDev tex, const skc_surface_point *__restrict__ pts) {
     int lane = threadIdx.x & 31;
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
@@ -231,6 +232,11 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
         uint64_t pi = ptBase + point;
         float e = lane < SKC_NS ? E : 0.f;            // lanes 30,31 write the zero pad of the 128 B row
         if (albedo && lane < SKC_NS) e *= (float)pow((double)__ldg(&albedo[pi * SKC_NS + lane]), (double)mix);   // :139-140
+        else if (DELTA && tex.rgb && lane < SKC_NS) {      // "texture albedo": ImageTexture::Evaluate at the point's (u, v) with zero differentials
+            const float *sp = reinterpret_cast<const float *>(pts + pi);
+            const f3 c = texBilinear(tex, 0, tex.su * __ldg(sp + 6) + tex.du, tex.sv * __ldg(sp + 7) + tex.dv);
+            e *= skc_powf(texReflectance(tex.refl, c.x, c.y, c.z, lane), mix);                     // E *= Pow(albedo, mix)
+        }
         else if (albedoPowMix && lane < SKC_NS) e *= __ldg(&albedoPowMix[lane]);      // a constant albedo: Pow(albedo, mix) made on the host with libm's powf
         Eout[(outBase + pi) * SKC_EPAD + lane] = e;
     }
@@ -381,8 +387,8 @@ static int irradianceDev(skc_ctx *ctx, skc_surface_point *dPts, uint64_t nTotal,
             else k_irr_sample<false, false><<<gSample, IRR_BLOCK, 0, ctx->stream>>>(ctx->lights, sl, dPts, dScr, pb, np, dCosPdf, rayO, rayD, rayTarget, dNRays + b, ctx->ipPosArea, first, nullptr, ctx->env, nullptr);
             k_irr_shadow<false><<<gShadow, 128, 0, ctx->stream>>>(skc_bvh_view(ctx), rayO, rayD, rayTarget, dNRays + b, dCosPdf, nullptr);
         }
-        if (ctx->hasDeltaLights) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, dEnvRgb, ctx->env.illum);
-        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, nullptr, nullptr);
+        if (ctx->hasDeltaLights || ctx->albedoTex.rgb) k_irr_spectral<true><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, dEnvRgb, ctx->env.illum, ctx->albedoTex, dPts);
+        else k_irr_spectral<false><<<gSpec, 256, 0, ctx->stream>>>(ctx->lights, sl, dCosPdf, pb, np, ctx->rhoHd, dAlb, mix, ctx->ipE, first, ctx->ipPosArea, ctx->albedoFactors, nullptr, nullptr, AlbedoTexDev(), nullptr);
         ctx->launches += 2;
         SKC_LAUNCHED("k_irr_spectral");
     }

@@ -120,6 +120,29 @@ bool LoadAlphaTexture(const std::string &file, float shift, float scale, float g
     return true;
 }
 
+// ImageTexture<RGBSpectrum, Spectrum> (textures/imagemap.cpp:56-86, imagemap.h:90-93): texels scale * (Pow(rgb, gamma) + shift), the
+// MIPMap pyramid, and the EWA weight table exp(-2 r2) - exp(-2) (core/mipmap.h:186-193)
+bool LoadAlbedoTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err) {
+    int w = 0, h = 0;
+    std::vector<Rgb> px;
+    if (!ReadPfm(file, &w, &h, &px, err)) return false;
+    if ((w & (w - 1)) || (h & (h - 1))) { *err = "texture \"" + file + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)"; return false; }
+    for (Rgb &c : px) { c.r = scale * (powf(c.r, gamma) + shift); c.g = scale * (powf(c.g, gamma) + shift); c.b = scale * (powf(c.b, gamma) + shift); }
+    Pyramid mip;
+    mip.Build(w, h, px);
+    *out = AlbedoTexture();
+    out->present = true;
+    for (const Pyramid::Level &l : mip.levels) {
+        out->w.push_back(l.w); out->h.push_back(l.h);
+        for (const Rgb &c : l.px) { out->rgb.push_back(c.r); out->rgb.push_back(c.g); out->rgb.push_back(c.b); }
+    }
+    for (int i = 0; i < 128; ++i) {
+        const float alpha = 2, r2 = float(i) / float(128 - 1);
+        out->weightLut[i] = expf(-alpha * r2) - expf(-alpha);
+    }
+    return true;
+}
+
 // SampledSpectrum::ToRGB (core/spectrum.h:374-398): ToXYZ's running sums over the 30 samples, then XYZToRGB
 void SpectrumToRGB(const float c[30], float rgb[3]) {
     float xyz[3] = {0.f, 0.f, 0.f};

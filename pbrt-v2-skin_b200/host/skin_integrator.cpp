@@ -120,6 +120,16 @@ const float *skh_env_array(const skh_scene *s, int which) {
     const std::vector<float> *v[6] = {&e.rgb, &e.condFunc, &e.condCdf, &e.condInt, &e.margFunc, &e.margCdf};
     return which >= 0 && which < 6 ? v[which]->data() : nullptr;
 }
+// The material's albedo texture: number of levels (0 = none), per-level sizes, mapping; then the texels and the weight table
+int skh_albedo_tex_info(const skh_scene *s, int *w12, int *h12, float *map4) {
+    const AlbedoTexture &a = s->sd.skin.albedoTex;
+    if (!a.present) return 0;
+    for (size_t i = 0; i < a.w.size() && i < 12; ++i) { w12[i] = a.w[i]; h12[i] = a.h[i]; }
+    map4[0] = a.su; map4[1] = a.sv; map4[2] = a.du; map4[3] = a.dv;
+    return (int)a.w.size();
+}
+const float *skh_albedo_tex_rgb(const skh_scene *s) { return s->sd.skin.albedoTex.rgb.data(); }
+const float *skh_albedo_tex_lut(const skh_scene *s) { return s->sd.skin.albedoTex.weightLut; }
 // The device mesh's alpha texture: sizes {w, h} (0 = none) and mapping {su, sv, du, dv}; the texels
 static const AlphaTexture &alphaOf(const skh_scene *s) { return s->built.mesh ? s->built.mesh->alpha : s->sd.meshes[0].alpha; }
 void skh_alpha_info(const skh_scene *s, int *wh2, float *map4) {

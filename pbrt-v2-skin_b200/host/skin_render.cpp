@@ -52,7 +52,7 @@ int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm) {
 }
 
 int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix) {
-    if (!skin.hasAlbedo) return skc_set_albedo_factors(ctx, nullptr, nullptr);
+    if (!skin.hasAlbedo || skin.albedoTex.present) return skc_set_albedo_factors(ctx, nullptr, nullptr);
     float al[30], a[30], b[30];
     RGBToSpectrum(skin.albedo, al);                                           // "color albedo": Spectrum::FromRGB, reflectance
     for (int i = 0; i < 30; ++i) { a[i] = powf(al[i], mix); b[i] = powf(al[i], 1.f - mix); }      // Pow(Spectrum, float): powf per sample
@@ -69,6 +69,11 @@ int UploadScene(skc_ctx *ctx, const BuiltScene &b) {
                             b.lights.data(), (uint32_t)b.lights.size());
     if (rc) return rc;
     return skc_upload_lights(ctx, b.lights.data(), (uint32_t)b.lights.size());
+}
+
+int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a) {
+    if (!a.present) return skc_upload_albedo_texture(ctx, 0, nullptr, nullptr, nullptr, nullptr, 1.f, 1.f, 0.f, 0.f);
+    return skc_upload_albedo_texture(ctx, (uint32_t)a.w.size(), a.w.data(), a.h.data(), a.rgb.data(), a.weightLut, a.su, a.sv, a.du, a.dv);
 }
 
 int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a) {
@@ -91,7 +96,7 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
     const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
     double t0 = now();
-    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env)) || !dev(UploadAlpha(ctx, built.mesh->alpha))) return false;
+    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env)) || !dev(UploadAlpha(ctx, built.mesh->alpha)) || !dev(UploadAlbedoTexture(ctx, sd.skin.albedoTex))) return false;
     double t1 = now();
     if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(InstallAlbedo(ctx, sd.skin, sd.mix)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();

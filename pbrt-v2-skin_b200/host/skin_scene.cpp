@@ -359,6 +359,11 @@ bool SceneDesc::LoadLines(const std::string &path) {
                 else if (k == "Kr") ls >> skin.Kr[0] >> skin.Kr[1] >> skin.Kr[2];
                 else if (k == "Kt") ls >> skin.Kt[0] >> skin.Kt[1] >> skin.Kt[2];
                 else if (k == "albedo") { ls >> skin.albedo[0] >> skin.albedo[1] >> skin.albedo[2]; skin.hasAlbedo = true; }
+                else if (k == "albedotex") {      // Texture ".." "color" "imagemap" + "texture albedo"
+                    std::string file; ls >> file;
+                    if (file[0] != '/') file = dir + file;
+                    if (!LoadAlbedoTexture(file, 0.f, 1.f, 1.f, &skin.albedoTex, &error)) return false;
+                }
                 else {
                     float v; ls >> v;
                     if (k == "roughness") skin.roughness = v; else if (k == "nmperunit") skin.nmperunit = v;

@@ -72,6 +72,18 @@ struct EnvMap {
     float margInt = 0.f;
 };
 
+// LayeredSkin's "texture albedo": a "color" image map (textures/imagemap.cpp CreateImageSpectrumTexture) as its MIPMap's whole pyramid
+// (the EWA filter reads every level), the filter's weight table and its UVMapping2D
+struct AlbedoTexture {
+    bool present = false;
+    std::vector<int> w, h;                      // per level
+    std::vector<float> rgb;                     // the levels one after the other, [h][w][3] each
+    float weightLut[128] = {0};                 // core/mipmap.h:186-193
+    float su = 1.f, sv = 1.f, du = 0.f, dv = 0.f;
+    bool operator==(const AlbedoTexture &o) const { return present == o.present && w == o.w && h == o.h && rgb == o.rgb && su == o.su && sv == o.sv && du == o.du && dv == o.dv; }
+};
+bool LoadAlbedoTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err);
+
 // LayeredSkin parameters (materials/layeredskin.cpp:222-262)
 struct SkinParams {
     float roughness = 0.4f, nmperunit = 100e6f;      // materials/layeredskin.cpp:234-235
@@ -84,6 +96,7 @@ struct SkinParams {
     // Pow(albedo, 1 - mix) (multipolesubsurface.cpp:139-140,287)
     float albedo[3] = {1, 1, 1};
     bool hasAlbedo = false;
+    AlbedoTexture albedoTex;                    // "texture albedo" (an image map); excludes hasAlbedo
     bool lerponthinslab = true;
     float layerThickness[2] = {0.25e6f, 20e6f}, layerIor[2] = {1.4f, 1.4f};
 };
@@ -193,7 +206,8 @@ int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nul
 // the two albedo factors of the material for an integrator's `mix` -> skc_set_albedo_factors (cleared when the albedo is the default)
 int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);
 int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);
-int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a);    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
+int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a);
+int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a);   // skc_upload_albedo_texture (or its removal)    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,

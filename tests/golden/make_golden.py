@@ -134,6 +134,9 @@ def lights_golden(name="skin_lights"):
             arrays["alpha"] = f32("mesh0_alpha.bin")
             arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
             arrays["camera_rays"] = f32("camera_rays.bin").reshape(-1, 8)
+        if os.path.exists(os.path.join(d, "albedo_tex.bin")):   # "texture albedo": the MIPMap pyramid and the EWA weight table
+            arrays["albedo_tex"] = f32("albedo_tex.bin")
+            arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
         if os.path.exists(os.path.join(d, "envmap.bin")):      # LightSource "infinite": its map and Distribution2D (ref_driver dumpLights)
             arrays["envmap"] = f32("envmap.bin")
     path = os.path.join(OUT, name + ".npz")
@@ -323,4 +326,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha") else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex") else scene_golden(w)
