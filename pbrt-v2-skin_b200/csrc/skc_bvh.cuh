@@ -233,6 +233,38 @@ __host__ __device__ inline void triShadingGeometry(const MeshView &mv, int4 vi, 
 }
 
 
+// The hit's DifferentialGeometry as Triangle::Intersect builds it (shapes/trianglemesh.inl:80-135): dpdu / dpdv from the uv parameterisation,
+// the interpolated (u, v), and nn = Normalize(Cross(dpdu, dpdv)), flipped with the mesh's orientation (core/diffgeom.cpp:36-55)
+__host__ __device__ inline void triDiffGeom(const MeshView &mv, int4 vi, float b0, float b1, float b2, f3 *dpduOut, f3 *dpdvOut, float *tuOut, float *tvOut, f3 *nnOut) {
+    f3 p1 = ld3(mv.P, vi.x), p2 = ld3(mv.P, vi.y), p3 = ld3(mv.P, vi.z);
+    f3 e1 = sub3(p2, p1), e2 = sub3(p3, p1);
+    float uvs[3][2];
+    if (mv.UV) {
+        uvs[0][0] = mv.UV[2 * vi.x]; uvs[0][1] = mv.UV[2 * vi.x + 1];
+        uvs[1][0] = mv.UV[2 * vi.y]; uvs[1][1] = mv.UV[2 * vi.y + 1];
+        uvs[2][0] = mv.UV[2 * vi.z]; uvs[2][1] = mv.UV[2 * vi.z + 1];
+    } else {
+        uvs[0][0] = 0.f; uvs[0][1] = 0.f; uvs[1][0] = 1.f; uvs[1][1] = 0.f; uvs[2][0] = 1.f; uvs[2][1] = 1.f;
+    }
+    float du1 = uvs[0][0] - uvs[2][0], du2 = uvs[1][0] - uvs[2][0];
+    float dv1 = uvs[0][1] - uvs[2][1], dv2 = uvs[1][1] - uvs[2][1];
+    f3 dp1 = sub3(p1, p3), dp2 = sub3(p2, p3);
+    f3 dpdu, dpdv;
+    float determinant = du1 * dv2 - dv1 * du2;
+    if (determinant == 0.f) {
+        coordinateSystem(normalize3(cross3(e2, e1)), &dpdu, &dpdv);
+    } else {
+        float invdet = 1.f / determinant;
+        dpdu = mul3(sub3(mul3(dp1, dv2), mul3(dp2, dv1)), invdet);
+        dpdv = mul3(add3(mul3(dp1, -du2), mul3(dp2, du1)), invdet);
+    }
+    *tuOut = b0 * uvs[0][0] + b1 * uvs[1][0] + b2 * uvs[2][0];
+    *tvOut = b0 * uvs[0][1] + b1 * uvs[1][1] + b2 * uvs[2][1];
+    *dpduOut = dpdu; *dpdvOut = dpdv;
+    f3 ng = normalize3(cross3(dpdu, dpdv));
+    *nnOut = mv.flip ? mul3(ng, -1.f) : ng;
+}
+
 struct SlabSetup { f3 invDir; int neg[3]; int negMask; };   // negMask: the three signs as bits, for the child order by split axis (no dynamically indexed array -> no local memory)
 __device__ __forceinline__ SlabSetup slabSetup(const DRay &r) {
     SlabSetup s;

@@ -29,6 +29,7 @@
 #include <algorithm>
 #include <vector>
 #include "skc_light.cuh"
+#include "skc_texture.cuh"
 #include "skc_bsdf.cuh"
 #include "skc_internal.h"
 
@@ -209,6 +210,75 @@ __global__ void __launch_bounds__(256) k_camera_rays(const FrameConsts *__restri
     float4 *dst = reinterpret_cast<float4 *>(rays + i);
     dst[0] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
     dst[1] = make_float4(r.d.y, r.d.z, 0.f, INFINITY);
+}
+
+// "texture albedo" at the camera hits (materials/layeredskin.cpp:179-185 through Intersection::GetMultipoleBSSRDF): one thread per camera
+// sample that hit the skin.  The hit's DifferentialGeometry as Triangle::Intersect builds it (shapes/trianglemesh.inl:80-135: dpdu, dpdv
+// from the uv parameterisation, (u, v), the geometric normal), the camera ray's differentials (cameras/perspective.cpp:106-112, scaled by
+// 1 / sqrt(spp): samplerrenderer.cpp:97), DifferentialGeometry::ComputeDifferentials (core/diffgeom.cpp:58-113), UVMapping2D and the EWA
+// lookup.  Output: the albedo's RGB per sample (the Li epilogue turns it into Pow(Spectrum::FromRGB(rgb), 1 - mix)).
+__device__ __forceinline__ bool solve2x2(const float A[2][2], const float B[2], float *x0, float *x1) {      // core/transform.cpp:39-49
+    const float det = A[0][0] * A[1][1] - A[0][1] * A[1][0];
+    if (fabsf(det) < 1e-10f) return false;
+    *x0 = (A[1][1] * B[0] - A[0][1] * B[1]) / det;
+    *x1 = (A[0][0] * B[1] - A[1][0] * B[0]) / det;
+    return !(isnan(*x0) || isnan(*x1));
+}
+__device__ __forceinline__ float comp3(f3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
+__global__ void __launch_bounds__(128) k_hit_albedo(BvhView bv, MeshView mv, AlbedoTexDev tex, const FrameConsts *__restrict__ C, const float2 *__restrict__ xy,
+                                                    const uint32_t *__restrict__ order, uint32_t spp, uint64_t first, float diffScale,
+                                                    const skc_ray *__restrict__ rays, const skc_hit *__restrict__ hits, uint64_t n,
+                                                    float4 *__restrict__ albedoRgb) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *hp = reinterpret_cast<const float *>(hits + i);
+    float4 out = make_float4(1.f, 1.f, 1.f, 0.f);
+    if (__float_as_int(__ldg(hp)) && __float_as_int(__ldg(hp + 13))) {
+        const int prim = __float_as_int(__ldg(hp + 1));
+        const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+        const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+        DRay ray; ray.o = mk3(r0.x, r0.y, r0.z); ray.d = mk3(r0.w, r1.x, r1.y); ray.mint = r1.z; ray.maxt = r1.w;
+        // the barycentrics of the hit: the same test on the same operands as the traversal's
+        const float4 *pp = &bv.prims[3 * prim];
+        const float4 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2);
+        float t, b1 = 0.f, b2 = 0.f;
+        triIntersect(mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), mk3(b.z, b.w, c.x), ray, &t, &b1, &b2);
+        const int4 vi = __ldg(&mv.primInfo[prim]);
+        f3 dpdu, dpdv, nn; float tu, tv;
+        triDiffGeom(mv, vi, 1 - b1 - b2, b1, b2, &dpdu, &dpdv, &tu, &tv, &nn);
+        const f3 p = mk3(__ldg(hp + 4), __ldg(hp + 5), __ldg(hp + 6));
+        // the offset rays
+        const float2 s = xy[renderToStream(order, spp, first + i)];
+        const f3 Pcamera = xformPoint(C->r2c, mk3(s.x, s.y, 0.f));
+        const f3 P000 = xformPoint(C->r2c, mk3(0.f, 0.f, 0.f));
+        const f3 dxCamera = sub3(xformPoint(C->r2c, mk3(1.f, 0.f, 0.f)), P000), dyCamera = sub3(xformPoint(C->r2c, mk3(0.f, 1.f, 0.f)), P000);
+        f3 rxD = xformVector(C->c2w, normalize3(add3(Pcamera, dxCamera))), ryD = xformVector(C->c2w, normalize3(add3(Pcamera, dyCamera)));
+        rxD = add3(ray.d, mul3(sub3(rxD, ray.d), diffScale));                 // ScaleDifferentials (core/geometry.h:412-417); the origins stay ray.o
+        ryD = add3(ray.d, mul3(sub3(ryD, ray.d), diffScale));
+        const f3 rxO = add3(ray.o, mul3(sub3(ray.o, ray.o), diffScale)), ryO = rxO;
+        // ComputeDifferentials
+        float dudx = 0.f, dvdx = 0.f, dudy = 0.f, dvdy = 0.f;
+        const float d = -dot3(nn, p);
+        const float tx = -(dot3(nn, rxO) + d) / dot3(nn, rxD);
+        const float ty = -(dot3(nn, ryO) + d) / dot3(nn, ryD);
+        if (!isnan(tx) && !isnan(ty)) {
+            const f3 px = add3(rxO, mul3(rxD, tx)), py = add3(ryO, mul3(ryD, ty));
+            int ax0, ax1;
+            if (fabsf(nn.x) > fabsf(nn.y) && fabsf(nn.x) > fabsf(nn.z)) { ax0 = 1; ax1 = 2; }
+            else if (fabsf(nn.y) > fabsf(nn.z)) { ax0 = 0; ax1 = 2; }
+            else { ax0 = 0; ax1 = 1; }
+            float A[2][2], Bx[2], By[2];
+            A[0][0] = comp3(dpdu, ax0); A[0][1] = comp3(dpdv, ax0); A[1][0] = comp3(dpdu, ax1); A[1][1] = comp3(dpdv, ax1);
+            Bx[0] = comp3(px, ax0) - comp3(p, ax0); Bx[1] = comp3(px, ax1) - comp3(p, ax1);
+            By[0] = comp3(py, ax0) - comp3(p, ax0); By[1] = comp3(py, ax1) - comp3(p, ax1);
+            if (!solve2x2(A, Bx, &dudx, &dvdx)) { dudx = 0.f; dvdx = 0.f; }
+            if (!solve2x2(A, By, &dudy, &dvdy)) { dudy = 0.f; dvdy = 0.f; }
+        }
+        // UVMapping2D::Map (core/texture.cpp) and MIPMap::Lookup
+        const f3 rgb = texLookup(tex, tex.su * tu + tex.du, tex.sv * tv + tex.dv, tex.su * dudx, tex.sv * dvdx, tex.su * dudy, tex.sv * dvdy);
+        out = make_float4(rgb.x, rgb.y, rgb.z, 1.f);
+    }
+    albedoRgb[i] = out;
 }
 
 // Start of every pixel's words in its task's stream: off[k] = k*K + 6 * (camera rays of pixels < k that hit).
@@ -773,6 +843,13 @@ static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, 
     const FrameLayout &lay = f->lay;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
+    if (ctx->albedoTex.rgb) {      // "texture albedo": the albedo of every skin hit, for the Li epilogue of the Mo kernel
+        float4 *dAlb = (float4 *)skc_scratch(ctx, 23, count * sizeof(float4));
+        if (!dAlb) return 1;
+        k_hit_albedo<<<(unsigned)((count + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), ctx->albedoTex, f->dConsts, f->dXY, f->dOrder, lay.spp, first,
+                                                                            1.f / sqrtf((float)lay.spp), ctx->resRays + first, dHits, count, dAlb);
+        SKC_LAUNCHED("k_hit_albedo");
+    }
     skc_stage_end(ctx, 3);
     if (hitsDone) SKC_CUDA(cudaEventRecord(hitsDone, ctx->stream));
     RhoBxdf mf;
@@ -846,7 +923,10 @@ extern "C" int skc_frame_render(skc_ctx *ctx, uint64_t first, uint64_t count, fl
     f->prefetched = false;
     if (!usePrefetch) if (frameHitsAndDirect(ctx, f, first, count, dHits, dFrame, dTerms)) return 1;
     if (ctx->otGeo && ctx->otNodes) {
-        if (skc_li_fused_dev(ctx, dHits, count, maxError, mix, dL)) return 1;
+        ctx->hitAlbedo = ctx->albedoTex.rgb ? (const float4 *)skc_scratch(ctx, 23, count * sizeof(float4)) : nullptr;      // filled by frameHitsAndDirect
+        const int rcLi = skc_li_fused_dev(ctx, dHits, count, maxError, mix, dL);
+        ctx->hitAlbedo = nullptr;
+        if (rcLi) return 1;
     } else {
         SKC_CUDA(cudaMemsetAsync(dL, 0, count * SKC_NS * sizeof(float), ctx->stream));    // no octree: `if (bssrdf && octree)` (multipolesubsurface.cpp:267)
     }

@@ -22,6 +22,7 @@
 #include <cub/cub.cuh>
 #include "skc_internal.h"
 #include "skc_mo_table.h"
+#include "skc_texture.cuh"
 
 // Launch shape: a CTA of MO_WARPS warps works through a CONTIGUOUS run of MO_WARPS*MO_HITS_PER_WARP
 // shading points (neighbouring camera samples walk the same nodes, rows and table sectors, so
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(MO_WARPS * 32) k_mo(MoTree tr, MoTables T, con
 // Optional fused Li epilogue of the packet kernel (multipolesubsurface.cpp:279-287): the subsurface radiance of each
 // hit is written straight from the Mo sums -- into device memory, or into mapped pinned host memory, in which case the
 // 120 B/sample result crosses PCIe while the kernel is still running instead of in a copy after it.
-struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; const float *albedoPow = nullptr; };   // albedoPow: Pow(albedo, 1 - mix) of a constant albedo, made on the host with libm's powf
+struct LiEpilogue { const skc_hit *hits; const float *rhoHd; const float *albedo; float mix; float *L; const float *albedoPow = nullptr; const float4 *hitAlbedo = nullptr; const float *refl = nullptr; };   // albedoPow: Pow(albedo, 1 - mix) of a constant albedo, made on the host with libm's powf
 
 // NQ float4 groups of the 32-float row starting at group q0: 8 = the whole spectrum, 4 = half of it (a packet shared
 // by two warps, see k_mo_packet)
@@ -235,6 +236,7 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
     float Ft = 1.f - rho;
     float a = 1.f;
     if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + wl]), (double)(1.f - li.mix));
+    else if (li.hitAlbedo) { const float4 c = __ldg(&li.hitAlbedo[hh]); a = skc_powf(texReflectance(li.refl, c.x, c.y, c.z, wl), 1.f - li.mix); }      // "texture albedo" (k_hit_albedo)
     else if (li.albedoPow) a = __ldg(&li.albedoPow[wl]);
     return fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
 }
@@ -893,7 +895,7 @@ static int liDev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError,
 int skc_li_fused_dev(skc_ctx *ctx, const skc_hit *dHits, uint64_t n, float maxError, float mix, float *dL) {
     if (!ctx->rhoHd) return skc_fail(ctx, "skc_li: no rho table uploaded (skc_upload_profile)");
     if (!ctx->moPacket) return skc_fail(ctx, "skc_li: the fused Li epilogue needs the packet kernel");
-    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr};
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, dL, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr, ctx->hitAlbedo, ctx->albedoTex.refl};
     skc_stage_begin(ctx);
     if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep, false)) return 1;
     skc_stage_end(ctx, 4);
@@ -950,7 +952,7 @@ extern "C" int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, fl
         if (!dL) return 1;
         target = dL;
     }
-    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, target, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr};
+    LiEpilogue ep{dHits, ctx->rhoHd, nullptr, mix, target, ctx->albedoFactors ? ctx->albedoFactors + 32 : nullptr, ctx->hitAlbedo, ctx->albedoTex.refl};
     skc_stage_begin(ctx);
     if (moLaunch(ctx, reinterpret_cast<const float *>(dHits) + 4, 14, reinterpret_cast<const int32_t *>(dHits) + 13, 14, n, maxError, nullptr, nullptr, &ep)) return 1;
     skc_stage_end(ctx, 4);

@@ -80,6 +80,25 @@ def test_irradiance_and_frame_with_an_albedo_texture(pkg, golden):
         print("irradiance with a textured albedo: %d points (%d lit), bit-exact rows %.4f, max rel %.3g" % (len(ref), lit.sum(), np.mean(e == 0), e.max()))
         assert np.array_equal(E.max(axis=1) > 0, lit)
         assert e.max() < 1e-6, e.max()
+        dev.build_octree()
+        n = dev.frame_setup(hs.frame_desc(n_cores=1))
+        assert n == int(meta["camera_samples"])
+        dev.frame_samples()
+        dev.frame_film_clear()
+        Lr = dev.frame_render(0, n, hs.maxerror, hs.mix, want_L=True)
+        order = dev.frame_order(0, n)
+        L = np.empty_like(Lr); L[order] = Lr
+        ref = z["L"]
+        lit = ref.max(axis=1) > 0
+        assert np.array_equal(L.max(axis=1) > 0, lit)
+        e = gu.row_rel_err(L, ref)[lit]
+        print("full Li with the EWA-filtered albedo: %d lit samples, max rel %.3g, within 1e-5: %.4f" % (lit.sum(), e.max(), np.mean(e < 1e-5)))
+        assert e.max() < 1e-4, e.max()
+        rgb = hs.film_to_rgb(dev.frame_film())
+        for c in range(3):
+            rmse = np.sqrt(np.mean((rgb[..., c] - z["image"][..., c]) ** 2)); s = np.sqrt(np.mean(z["image"][..., c] ** 2))
+            print("channel %d: RMSE / RMS = %.3g" % (c, rmse / s))
+            assert rmse < 1e-3 * s
     finally:
         hs.close()
         dev.close()
