@@ -32,9 +32,17 @@ def _split_tex(flat):
     return w, h, np.concatenate(levels), lut
 
 
-def test_albedo_texture_construction_bit_exact(pkg, golden):
+@pytest.mark.parametrize("ext", ["scene", "pbrt"])
+def test_albedo_texture_construction_bit_exact(pkg, golden, ext):
     z, _ = golden
-    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tex.scene"))
+    if ext == "pbrt":
+        import sys
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import mesh_bin_to_pbrt
+        dst = os.path.join(ROOT, "scenes", "geometry", "head.pbrt")
+        if not os.path.exists(dst):
+            mesh_bin_to_pbrt.convert(os.path.join(ROOT, "scenes", "head.mesh.bin"), dst)
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tex." + ext))
     try:
         t = hs.albedo_texture()
         w, h, rgb, lut = _split_tex(z["albedo_tex"])
