@@ -228,6 +228,13 @@ int skc_camera_pass(skc_ctx *ctx, const skc_ray *rays, uint64_t n, float maxErro
  * skc_set_albedo_factors.  nLevels == 0 removes it. */
 int skc_upload_albedo_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *rgb, const float *weightLut128,
                               float su, float sv, float du, float dv);
+/* LayeredSkin's "texture bumpmap" as a float image map (materials/layeredskin.cpp:139,299-304; core/material.cpp:47-104 Material::Bump,
+ * this fork's central-difference variant): the nLevels levels of its MIPMap<float> (displacement [h][w] per level, finest first), the EWA
+ * weight table and the UVMapping2D.  skc_tessellate_resident / _range then give every irradiance point the bumped normal
+ * (shapes/trianglemesh.cpp:236-242: zero differentials, du = dv = .01, bilinear lookups), and skc_frame_render builds the BSDF of every
+ * skin hit on the bumped shading normal and dpdu (differentials from the camera ray).  nLevels == 0 removes it. */
+int skc_upload_bump_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *displacement, const float *weightLut128,
+                            float su, float sv, float du, float dv);
 /* Alpha-tested triangles (shapes/trianglemesh.inl:117-126,174-207): the mesh's "texture alpha", a float image map.  texels [h][w] are
  * the values ImageTexture<float, float> holds at MIPMap level 0 -- scale * (powf(luminance, gamma) + shift), made by the caller
  * (textures/imagemap.h:94-97); su, sv, du, dv its UVMapping2D.  Every ray-triangle hit, closest or any, whose texture value at the

@@ -119,6 +119,7 @@ struct SceneDesc {
     float Kr[3] = {1, 1, 1}, Kt[3] = {0, 0, 0};     // "color Kr" / "color Kt" as the skin scenes give them
     float albedo[3] = {1, 1, 1}; bool hasAlbedo = false;      // "color albedo" (materials/layeredskin.cpp:247)
     std::string albedoTex;                                     // "texture albedo": PFM of a "color" image map
+    std::string bumpTex;                                       // "texture bumpmap": PFM of a "float" image map
     struct Xf { std::string kind; float v[4]; };
     struct Mesh { std::vector<Xf> xf; std::string file; std::string alpha; };      // alpha: PFM of the mesh's "texture alpha" (float imagemap)
     std::vector<Mesh> meshes;
@@ -172,6 +173,7 @@ static SceneDesc parseScene(const std::string &path) {
                 else if (k == "Kt") { for (int i = 0; i < 3; ++i) ls >> sd.Kt[i]; }
                 else if (k == "albedo") { for (int i = 0; i < 3; ++i) ls >> sd.albedo[i]; sd.hasAlbedo = true; }
                 else if (k == "albedotex") { ls >> sd.albedoTex; if (sd.albedoTex[0] != '/') sd.albedoTex = dir + sd.albedoTex; }
+                else if (k == "bumptex") { ls >> sd.bumpTex; if (sd.bumpTex[0] != '/') sd.bumpTex = dir + sd.bumpTex; }
                 else { float v; ls >> v; sd.skin[k] = v; }
             }
         }
@@ -264,6 +266,11 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
                 pbrtTexture("albedomap", "color", "imagemap", tp);
                 std::string nm = "albedomap"; ps.AddTexture("albedo", nm);
             }
+            if (!sd.bumpTex.empty()) {        // Texture "bumpmap" "float" "imagemap" + "texture bumpmap" (materials/layeredskin.cpp:246)
+                ParamSet tp; tp.AddString("filename", &sd.bumpTex, 1);
+                pbrtTexture("skinbump", "float", "imagemap", tp);
+                std::string nm = "skinbump"; ps.AddTexture("bumpmap", nm);
+            }
             SkinLayer sl[2]; sl[0].thickness = sd.layers[0]; sl[0].ior = sd.layers[1];
             sl[1].thickness = sd.layers[2]; sl[1].ior = sd.layers[3];
             ps.AddSkinLayer("layers", sl, 2);
@@ -339,6 +346,18 @@ static void dumpSpectrumConsts(const std::string &dir) {
 }
 
 static void dumpMaterial(const std::string &dir, const LayeredSkin *skin, Meta &meta) {
+    if (const ImageTexture<float, float> *it = dynamic_cast<const ImageTexture<float, float> *>(skin->bumpMap.GetPtr())) {
+        // "texture bumpmap": the MIPMap<float> pyramid -- int32 nLevels, then per level int32 w, h and [h][w] floats
+        std::vector<float> a;
+        auto pushInt = [&](int32_t v) { float f; memcpy(&f, &v, 4); a.push_back(f); };
+        pushInt((int32_t)it->mipmap->nLevels);
+        for (uint32_t l = 0; l < it->mipmap->nLevels; ++l) {
+            const int w = (int)it->mipmap->pyramid[l]->uSize(), h = (int)it->mipmap->pyramid[l]->vSize();
+            pushInt(w); pushInt(h);
+            for (int t = 0; t < h; ++t) for (int s2 = 0; s2 < w; ++s2) a.push_back(it->mipmap->Texel(l, s2, t));
+        }
+        dump(dir + "/bump_tex.bin", a.data(), a.size());
+    }
     if (const ImageTexture<RGBSpectrum, Spectrum> *it = dynamic_cast<const ImageTexture<RGBSpectrum, Spectrum> *>(skin->albedo.GetPtr())) {
         // "texture albedo": the MIPMap's whole pyramid -- int32 nLevels, then per level int32 w, h and rgb[h][w][3] -- and the EWA weight table
         std::vector<float> a;

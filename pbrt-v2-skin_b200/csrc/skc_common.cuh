@@ -94,7 +94,9 @@ struct skc_ctx {
     float mocCoverage = 0.f, mocMaxErr = 0.f;
     AlbedoTexDev albedoTex;           // "texture albedo" of the skin material; albedoTex.rgb == nullptr: none
     float *albedoTexStore = nullptr;
-    const float4 *hitAlbedo = nullptr;   // per camera hit: the texture's RGB (k_hit_albedo), set by skc_frame_render around its Mo pass
+    AlbedoTexDev bumpTex;             // "texture bumpmap" (r = g = b = the displacement); bumpTex.rgb == nullptr: none
+    float *bumpTexStore = nullptr;
+    const float4 *hitAlbedo = nullptr;   // per camera hit: the texture's RGB (k_hit_textures), set by skc_frame_render around its Mo pass
     float *alphaTex = nullptr, *alphaUV = nullptr;     // the mesh's alpha texture (skc_upload_alpha) and per-primitive vertex uvs; null: none
     int alphaW = 0, alphaH = 0;
     float alphaMap[4] = {1.f, 1.f, 0.f, 0.f};          // UVMapping2D su, sv, du, dv

@@ -97,7 +97,7 @@ extern "C" void skc_destroy(skc_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->meshIdx, ctx->bvhNodes, ctx->bvhWide, ctx->bvhPrims, ctx->primInfo, ctx->meshP, ctx->meshN, ctx->meshUV, ctx->spheres,
                     ctx->profPairs, ctx->profRcp, ctx->rhoHd, ctx->mocRows, ctx->mocHeads, ctx->mocLam, ctx->mocHeadOff, ctx->lights, ctx->ipPosArea, ctx->ipE,
-                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors, ctx->envStore, ctx->alphaTex, ctx->alphaUV, ctx->albedoTexStore};
+                    ctx->otGeo, ctx->otEt, ctx->resPts, ctx->resRays, ctx->otPointIdx, ctx->otLeafPosArea, ctx->albedoFactors, ctx->envStore, ctx->alphaTex, ctx->alphaUV, ctx->albedoTexStore, ctx->bumpTexStore};
     for (void *p : ptrs) if (p) cudaFree(p);
     skc_frame_release(ctx);
     for (int i = 0; i < 24; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -131,30 +131,51 @@ extern "C" uint64_t skc_launch_count(const skc_ctx *ctx) { return ctx->launches;
 // filter's weight table (128 entries, core/mipmap.h:186-193) and the UVMapping2D.  The irradiance pass scales a point's E by
 // Pow(albedo(u, v), mix) (lookup with zero differentials = bilinear at level 0), Li a hit's subsurface term by Pow(albedo, 1 - mix)
 // with the EWA lookup under the camera ray's differentials.  nLevels == 0 removes it.
-extern "C" int skc_upload_albedo_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *rgb, const float *weightLut128,
-                                         float su, float sv, float du, float dv) {
+static int uploadTexture(skc_ctx *ctx, const char *what, float **store, AlbedoTexDev *dev, uint32_t nLevels, const int *w, const int *h, const float *texels, int channels,
+                         const float *weightLut128, float su, float sv, float du, float dv) {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    if (ctx->albedoTexStore) { cudaFree(ctx->albedoTexStore); ctx->albedoTexStore = nullptr; }
-    ctx->albedoTex = AlbedoTexDev();
+    if (*store) { cudaFree(*store); *store = nullptr; }
+    *dev = AlbedoTexDev();
     if (!nLevels) return 0;
-    if (nLevels > SKC_TEX_MAX_LEVELS || !w || !h || !rgb || !weightLut128) return skc_fail(ctx, "skc_upload_albedo_texture: bad arguments (at most %d levels)", SKC_TEX_MAX_LEVELS);
+    if (nLevels > SKC_TEX_MAX_LEVELS || !w || !h || !texels || !weightLut128) return skc_fail(ctx, "%s: bad arguments (at most %d levels)", what, SKC_TEX_MAX_LEVELS);
     AlbedoTexDev t;
     size_t total = 0;
     for (uint32_t l = 0; l < nLevels; ++l) { t.w[l] = w[l]; t.h[l] = h[l]; t.off[l] = (uint32_t)total; total += (size_t)3 * w[l] * h[l]; }
+    std::vector<float> expanded;
+    if (channels == 1) {          // a float texture: the same filter code on three equal channels
+        expanded.resize(total);
+        for (size_t k = 0; k < total / 3; ++k) expanded[3 * k] = expanded[3 * k + 1] = expanded[3 * k + 2] = texels[k];
+        texels = expanded.data();
+    }
     float refl[7 * 32];
     for (int k = 0; k < 7; ++k) for (int i = 0; i < 32; ++i) refl[k * 32 + i] = i < 30 ? kRGBRefl2Spect30[k][i] : 0.f;
     const size_t texFloats = (total + 3) & ~(size_t)3;
-    SKC_CUDA(cudaMalloc((void **)&ctx->albedoTexStore, (texFloats + 128 + 7 * 32) * sizeof(float)));
-    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore, rgb, total * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore + texFloats, weightLut128, 128 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    SKC_CUDA(cudaMemcpyAsync(ctx->albedoTexStore + texFloats + 128, refl, sizeof refl, cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMalloc((void **)store, (texFloats + 128 + 7 * 32) * sizeof(float)));
+    SKC_CUDA(cudaMemcpyAsync(*store, texels, total * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(*store + texFloats, weightLut128, 128 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    SKC_CUDA(cudaMemcpyAsync(*store + texFloats + 128, refl, sizeof refl, cudaMemcpyHostToDevice, ctx->stream));
     SKC_CUDA(cudaStreamSynchronize(ctx->stream));
-    t.rgb = ctx->albedoTexStore; t.lut = ctx->albedoTexStore + texFloats; t.refl = t.lut + 128;
+    t.rgb = *store; t.lut = *store + texFloats; t.refl = t.lut + 128;
     t.nLevels = (int)nLevels; t.su = su; t.sv = sv; t.du = du; t.dv = dv;
-    ctx->albedoTex = t;
+    *dev = t;
     return 0;
+}
+
+extern "C" int skc_upload_albedo_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *rgb, const float *weightLut128,
+                                         float su, float sv, float du, float dv) {
+    if (!ctx) return 1;
+    return uploadTexture(ctx, "skc_upload_albedo_texture", &ctx->albedoTexStore, &ctx->albedoTex, nLevels, w, h, rgb, 3, weightLut128, su, sv, du, dv);
+}
+
+// The LayeredSkin material's displacement texture ("texture bumpmap", a float imagemap: materials/layeredskin.cpp:139,299-304): MIP pyramid
+// of one float per texel, finest first, the same filter table and UV mapping as the albedo texture.  It bends the normals of the tessellated
+// irradiance points (trianglemesh.cpp:236-242) and of every skin hit's BSDF (core/material.cpp:47-104).  nLevels == 0 removes it.
+extern "C" int skc_upload_bump_texture(skc_ctx *ctx, uint32_t nLevels, const int *w, const int *h, const float *displacement, const float *weightLut128,
+                                       float su, float sv, float du, float dv) {
+    if (!ctx) return 1;
+    return uploadTexture(ctx, "skc_upload_bump_texture", &ctx->bumpTexStore, &ctx->bumpTex, nLevels, w, h, displacement, 1, weightLut128, su, sv, du, dv);
 }
 
 // The radiance map and sampling distribution of the scene's infinite light (light record with radius -4).  w, h: texels; rgb

@@ -225,16 +225,17 @@ __device__ __forceinline__ bool solve2x2(const float A[2][2], const float B[2], 
     return !(isnan(*x0) || isnan(*x1));
 }
 __device__ __forceinline__ float comp3(f3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
-__global__ void __launch_bounds__(128) k_hit_albedo(BvhView bv, MeshView mv, AlbedoTexDev tex, const FrameConsts *__restrict__ C, const float2 *__restrict__ xy,
-                                                    const uint32_t *__restrict__ order, uint32_t spp, uint64_t first, float diffScale,
-                                                    const skc_ray *__restrict__ rays, const skc_hit *__restrict__ hits, uint64_t n,
-                                                    float4 *__restrict__ albedoRgb) {
+__global__ void __launch_bounds__(128) k_hit_textures(BvhView bv, MeshView mv, const __grid_constant__ AlbedoTexDev tex, const __grid_constant__ AlbedoTexDev bump,
+                                                      const FrameConsts *__restrict__ C, const float2 *__restrict__ xy,
+                                                      const uint32_t *__restrict__ order, uint32_t spp, uint64_t first, float diffScale,
+                                                      const skc_ray *__restrict__ rays, skc_hit *__restrict__ hits, uint64_t n,
+                                                      float4 *__restrict__ albedoRgb, float4 *__restrict__ frame) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float *hp = reinterpret_cast<const float *>(hits + i);
     float4 out = make_float4(1.f, 1.f, 1.f, 0.f);
-    if (__float_as_int(__ldg(hp)) && __float_as_int(__ldg(hp + 13))) {
-        const int prim = __float_as_int(__ldg(hp + 1));
+    if (__float_as_int(hp[0]) && __float_as_int(hp[13])) {
+        const int prim = __float_as_int(hp[1]);
         const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
         const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
         DRay ray; ray.o = mk3(r0.x, r0.y, r0.z); ray.d = mk3(r0.w, r1.x, r1.y); ray.mint = r1.z; ray.maxt = r1.w;
@@ -246,7 +247,7 @@ __global__ void __launch_bounds__(128) k_hit_albedo(BvhView bv, MeshView mv, Alb
         const int4 vi = __ldg(&mv.primInfo[prim]);
         f3 dpdu, dpdv, nn; float tu, tv;
         triDiffGeom(mv, vi, 1 - b1 - b2, b1, b2, &dpdu, &dpdv, &tu, &tv, &nn);
-        const f3 p = mk3(__ldg(hp + 4), __ldg(hp + 5), __ldg(hp + 6));
+        const f3 p = mk3(hp[4], hp[5], hp[6]);
         // the offset rays
         const float2 s = xy[renderToStream(order, spp, first + i)];
         const f3 Pcamera = xformPoint(C->r2c, mk3(s.x, s.y, 0.f));
@@ -275,10 +276,19 @@ __global__ void __launch_bounds__(128) k_hit_albedo(BvhView bv, MeshView mv, Alb
             if (!solve2x2(A, By, &dudy, &dvdy)) { dudy = 0.f; dvdy = 0.f; }
         }
         // UVMapping2D::Map (core/texture.cpp) and MIPMap::Lookup
-        const f3 rgb = texLookup(tex, tex.su * tu + tex.du, tex.sv * tv + tex.dv, tex.su * dudx, tex.sv * dvdx, tex.su * dudy, tex.sv * dvdy);
-        out = make_float4(rgb.x, rgb.y, rgb.z, 1.f);
+        if (tex.rgb) {
+            const f3 rgb = texLookup(tex, tex.su * tu + tex.du, tex.sv * tv + tex.dv, tex.su * dudx, tex.sv * dvdx, tex.su * dudy, tex.sv * dvdy);
+            out = make_float4(rgb.x, rgb.y, rgb.z, 1.f);
+        }
+        if (bump.rgb) {     // LayeredSkin::GetBSDF -> Material::Bump: the BSDF's shading normal and dpdu (the geometric normal stays)
+            f3 nnB, dpduB;
+            triBump(mv, vi, 1 - b1 - b2, b1, b2, bump, dudx, dvdx, dudy, dvdy, &nnB, &dpduB);
+            float *hw = reinterpret_cast<float *>(hits + i);
+            hw[7] = nnB.x; hw[8] = nnB.y; hw[9] = nnB.z;
+            frame[2 * i].w = dpduB.x; frame[2 * i + 1].x = dpduB.y; frame[2 * i + 1].y = dpduB.z;
+        }
     }
-    albedoRgb[i] = out;
+    if (albedoRgb) albedoRgb[i] = out;
 }
 
 // Start of every pixel's words in its task's stream: off[k] = k*K + 6 * (camera rays of pixels < k that hit).
@@ -843,12 +853,12 @@ static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, 
     const FrameLayout &lay = f->lay;
     skc_stage_begin(ctx);
     if (skc_trace_closest_dev(ctx, ctx->resRays + first, count, dHits, nullptr, dFrame)) return 1;
-    if (ctx->albedoTex.rgb) {      // "texture albedo": the albedo of every skin hit, for the Li epilogue of the Mo kernel
-        float4 *dAlb = (float4 *)skc_scratch(ctx, 23, count * sizeof(float4));
-        if (!dAlb) return 1;
-        k_hit_albedo<<<(unsigned)((count + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), ctx->albedoTex, f->dConsts, f->dXY, f->dOrder, lay.spp, first,
-                                                                            1.f / sqrtf((float)lay.spp), ctx->resRays + first, dHits, count, dAlb);
-        SKC_LAUNCHED("k_hit_albedo");
+    if (ctx->albedoTex.rgb || ctx->bumpTex.rgb) {      // "texture albedo": the albedo of every skin hit, for the Li epilogue of the Mo kernel; "texture bumpmap": its bumped shading frame
+        float4 *dAlb = ctx->albedoTex.rgb ? (float4 *)skc_scratch(ctx, 23, count * sizeof(float4)) : nullptr;
+        if (ctx->albedoTex.rgb && !dAlb) return 1;
+        k_hit_textures<<<(unsigned)((count + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), skc_mesh_view(ctx), ctx->albedoTex, ctx->bumpTex, f->dConsts, f->dXY, f->dOrder, lay.spp, first,
+                                                                              1.f / sqrtf((float)lay.spp), ctx->resRays + first, dHits, count, dAlb, dFrame);
+        SKC_LAUNCHED("k_hit_textures");
     }
     skc_stage_end(ctx, 3);
     if (hitsDone) SKC_CUDA(cudaEventRecord(hitsDone, ctx->stream));

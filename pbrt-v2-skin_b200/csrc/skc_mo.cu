@@ -236,7 +236,7 @@ __device__ __forceinline__ float liSssValue(const LiEpilogue &li, uint64_t hh, i
     float Ft = 1.f - rho;
     float a = 1.f;
     if (li.albedo) a = (float)pow((double)__ldg(&li.albedo[hh * SKC_NS + wl]), (double)(1.f - li.mix));
-    else if (li.hitAlbedo) { const float4 c = __ldg(&li.hitAlbedo[hh]); a = skc_powf(texReflectance(li.refl, c.x, c.y, c.z, wl), 1.f - li.mix); }      // "texture albedo" (k_hit_albedo)
+    else if (li.hitAlbedo) { const float4 c = __ldg(&li.hitAlbedo[hh]); a = skc_powf(texReflectance(li.refl, c.x, c.y, c.z, wl), 1.f - li.mix); }      // "texture albedo" (k_hit_textures)
     else if (li.albedoPow) a = __ldg(&li.albedoPow[wl]);
     return fmaxf(((0.31830988618379067154f * Ft) * mo) * a, 0.f);       // Spectrum::Clamp(0)
 }

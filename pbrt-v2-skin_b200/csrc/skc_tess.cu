@@ -15,6 +15,7 @@
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include "skc_internal.h"
+#include "skc_texture.cuh"
 
 struct TessBC { float b0, b1, b2; };
 __host__ __device__ __forceinline__ TessBC bc3(float a, float b, float c) { TessBC r; r.b0 = a; r.b1 = b; r.b2 = c; return r; }
@@ -67,6 +68,7 @@ struct TessEmit {
     MeshView mv; int4 vi; f3 v0, v1, v2;
     int incenter; uint32_t materialId; float rayEpsilon;
     skc_surface_point *out;
+    const AlbedoTexDev *bump;           // "texture bumpmap" of the material (device only), or NULL
 };
 
 // the domain shader of TessellateSurfacePoints (trianglemesh.cpp:216-255)
@@ -81,6 +83,9 @@ __host__ __device__ inline void tessPoint(const TessEmit &e, TessBC bv0, TessBC 
     f3 pp = bcPoint(bc, e.v0, e.v1, e.v2), nn;
     float tu, tv;
     triShadingGeometry(e.mv, e.vi, bc.b0, bc.b1, bc.b2, &nn, &tu, &tv);
+#ifdef __CUDA_ARCH__
+    if (e.bump) { f3 dpduBump; triBump(e.mv, e.vi, bc.b0, bc.b1, bc.b2, *e.bump, 0.f, 0.f, 0.f, 0.f, &nn, &dpduBump); }    // sp.n = dgBump.nn (trianglemesh.cpp:236-242)
+#endif
     float area = .5f * len3(cross3(sub3(sv1, sv0), sub3(sv2, sv0)));
     float *o = reinterpret_cast<float *>(e.out + slot);
     o[0] = pp.x; o[1] = pp.y; o[2] = pp.z; o[3] = nn.x; o[4] = nn.y; o[5] = nn.z; o[6] = tu; o[7] = tv;
@@ -150,7 +155,7 @@ __host__ __device__ inline void tessJob(const TessEmit &e, const TessFactors &t,
 
 __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *__restrict__ idx, uint32_t nTris, float minDist, int incenter,
                                                    uint32_t materialId, const uint32_t *__restrict__ offsets, skc_surface_point *__restrict__ out,
-                                                   uint32_t rangeLo, uint32_t rangeHi) {
+                                                   uint32_t rangeLo, uint32_t rangeHi, const __grid_constant__ AlbedoTexDev bump) {
     uint32_t tri = blockIdx.x;
     if (tri >= nTris) return;
     if (offsets[tri + 1] <= rangeLo || offsets[tri] >= rangeHi) return;      // none of this triangle's points is wanted (a shard of the set)
@@ -158,6 +163,7 @@ __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *_
     e.mv = mv; e.vi = make_int4(idx[3 * tri], idx[3 * tri + 1], idx[3 * tri + 2], 0);
     e.v0 = ld3(mv.P, e.vi.x); e.v1 = ld3(mv.P, e.vi.y); e.v2 = ld3(mv.P, e.vi.z);
     e.incenter = incenter; e.materialId = materialId; e.rayEpsilon = minDist / 10.f; e.out = out + offsets[tri];
+    e.bump = bump.rgb ? &bump : nullptr;
     TessFactors t = tessFactors(e.v0, e.v1, e.v2, minDist);
     for (int job = threadIdx.x; job < 3 * t.rings; job += blockDim.x) tessJob(e, t, job);
 }
@@ -194,7 +200,7 @@ static int tessellate(skc_ctx *ctx, float minDist, int incenter, uint32_t materi
     }
     if (total) {
         uint32_t lo = ranged ? (uint32_t)std::min<uint64_t>(first, total) : 0u, hi = ranged ? (uint32_t)std::min<uint64_t>(first + count, total) : total;
-        k_tess_emit<<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi);
+        k_tess_emit<<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi, ctx->bumpTex);
         SKC_LAUNCHED("k_tess_emit");
     }
     skc_stage_end(ctx, 8);
@@ -241,7 +247,7 @@ extern "C" int skc_tessellate_host(const float *P, const float *N, const float *
         TessEmit e;
         e.mv = mv; e.vi = make_int4(idx[3 * tri], idx[3 * tri + 1], idx[3 * tri + 2], 0);
         e.v0 = ld3(P, e.vi.x); e.v1 = ld3(P, e.vi.y); e.v2 = ld3(P, e.vi.z);
-        e.incenter = incenter; e.materialId = materialId; e.rayEpsilon = minDist / 10.f;
+        e.incenter = incenter; e.materialId = materialId; e.rayEpsilon = minDist / 10.f; e.bump = nullptr;
         const TessFactors t = tessFactors(e.v0, e.v1, e.v2, minDist);
         uint64_t n = 0;
         for (int r = 0; r < t.rings; ++r) n += ringPoints(t, r);

@@ -4,6 +4,7 @@
 // CreateImageSpectrumTexture's defaults (textures/imagemap.cpp).
 #pragma once
 #include "skc_common.cuh"
+#include "skc_bvh.cuh"
 
 __device__ __forceinline__ int texWrap(int a, int b) { int n = a / b; a -= n * b; if (a < 0) a += b; return a; }
 __device__ __forceinline__ f3 texTexel(const AlbedoTexDev &T, int level, int s, int t) {
@@ -90,4 +91,66 @@ __device__ __forceinline__ float texReflectance(const float *__restrict__ refl, 
     v += d2 * __ldg(&refl[i2 * 32 + lane]);
     v *= .94f;
     return fmaxf(v, 0.f);
+}
+
+// Material::Bump of this fork (core/material.cpp:47-104: central differences, five evaluations of the displacement texture) on the shading
+// geometry of a point of triangle vi with barycentrics b0, b1, b2 (Triangle::GetShadingGeometry, shapes/trianglemesh.inl:224-299, incl.
+// dndu / dndv).  (dudx, dvdx, dudy, dvdy): the screen-space differentials of (u, v) -- zero for the tessellator's points, from
+// ComputeDifferentials for camera hits.  Returns the bumped shading normal and dpdu (what LayeredSkin::GetBSDF builds its frame from).
+// The reference negates du / dv for its backward samples and then divides by 2 * du with the negated value, and takes its backward u
+// sample at v + dv: both kept.
+__device__ inline void triBump(const MeshView &mv, int4 vi, float b0, float b1, float b2, const AlbedoTexDev &tex, float dudx, float dvdx, float dudy, float dvdy,
+                               f3 *nnOut, f3 *dpduOut) {
+    f3 dpduG, dpdvG, ng; float tu, tv;
+    triDiffGeom(mv, vi, b0, b1, b2, &dpduG, &dpdvG, &tu, &tv, &ng);
+    f3 ss = dpduG, ts = dpdvG, nns = ng, dndu = mk3(0.f, 0.f, 0.f), dndv = dndu;
+    if (mv.N) {
+        float uvs[3][2];
+        if (mv.UV) {
+            uvs[0][0] = mv.UV[2 * vi.x]; uvs[0][1] = mv.UV[2 * vi.x + 1]; uvs[1][0] = mv.UV[2 * vi.y]; uvs[1][1] = mv.UV[2 * vi.y + 1];
+            uvs[2][0] = mv.UV[2 * vi.z]; uvs[2][1] = mv.UV[2 * vi.z + 1];
+        } else { uvs[0][0] = 0.f; uvs[0][1] = 0.f; uvs[1][0] = 1.f; uvs[1][1] = 0.f; uvs[2][0] = 1.f; uvs[2][1] = 1.f; }
+        float A00 = uvs[1][0] - uvs[0][0], A01 = uvs[2][0] - uvs[0][0], A10 = uvs[1][1] - uvs[0][1], A11 = uvs[2][1] - uvs[0][1];
+        float C0 = tu - uvs[0][0], C1 = tv - uvs[0][1];
+        float bb[3];
+        float det = A00 * A11 - A01 * A10;
+        bool ok = !(fabsf(det) < 1e-10f);
+        if (ok) { bb[1] = (A11 * C0 - A01 * C1) / det; bb[2] = (A00 * C1 - A10 * C0) / det; if (isnan(bb[1]) || isnan(bb[2])) ok = false; }
+        if (!ok) bb[0] = bb[1] = bb[2] = 1.f / 3.f; else bb[0] = 1.f - bb[1] - bb[2];
+        const f3 n0 = ld3(mv.N, vi.x), n1 = ld3(mv.N, vi.y), n2 = ld3(mv.N, vi.z);
+        const f3 ns = normalize3(xformNormal(mv.w2o, add3(add3(mul3(n0, bb[0]), mul3(n1, bb[1])), mul3(n2, bb[2]))));
+        ss = normalize3(dpduG);
+        ts = cross3(ss, ns);
+        if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) { ts = normalize3(ts); ss = cross3(ts, ns); }
+        else coordinateSystem(ns, &ss, &ts);
+        const float du1 = uvs[0][0] - uvs[2][0], du2 = uvs[1][0] - uvs[2][0], dv1 = uvs[0][1] - uvs[2][1], dv2 = uvs[1][1] - uvs[2][1];
+        const f3 dn1 = sub3(n0, n2), dn2 = sub3(n1, n2);
+        const float determinant = du1 * dv2 - dv1 * du2;
+        if (determinant != 0.f) {
+            const float invdet = 1.f / determinant;
+            dndu = xformNormal(mv.w2o, mul3(sub3(mul3(dn1, dv2), mul3(dn2, dv1)), invdet));
+            dndv = xformNormal(mv.w2o, mul3(add3(mul3(dn1, -du2), mul3(dn2, du1)), invdet));
+        }
+        nns = normalize3(cross3(ss, ts));
+        if (mv.flip) nns = mul3(nns, -1.f);
+    }
+    const float dsdx = tex.su * dudx, dtdx = tex.sv * dvdx, dsdy = tex.su * dudy, dtdy = tex.sv * dvdy;
+    auto eval = [&](float u, float v) { return texLookup(tex, tex.su * u + tex.du, tex.sv * v + tex.dv, dsdx, dtdx, dsdy, dtdy).x; };
+    float du = fabsf(dudx) + fabsf(dudy);
+    if (du == 0.f) du = .01f;
+    const float upDisplace = eval(tu + du, tv);
+    float dv = fabsf(dvdx) + fabsf(dvdy);
+    if (dv == 0.f) dv = .01f;
+    const float vpDisplace = eval(tu, tv + dv);
+    const float displace = eval(tu, tv);
+    du = -du;
+    const float unDisplace = eval(tu + du, tv + dv);               // the reference does not reset dgEval.v here: (u - du, v + dv)
+    dv = -dv;
+    const float vnDisplace = eval(tu, tv + dv);
+    const f3 dpdu = add3(add3(ss, mul3(nns, (upDisplace - unDisplace) / (2 * du))), mul3(dndu, displace));
+    const f3 dpdv = add3(add3(ts, mul3(nns, (vpDisplace - vnDisplace) / (2 * dv))), mul3(dndv, displace));
+    f3 nn = normalize3(cross3(dpdu, dpdv));
+    if (mv.flip) nn = mul3(nn, -1.f);
+    if (dot3(nn, ng) < 0.f) nn = mul3(nn, -1.f);                    // Faceforward(dgBump->nn, dgGeom.nn)
+    *nnOut = nn; *dpduOut = dpdu;
 }

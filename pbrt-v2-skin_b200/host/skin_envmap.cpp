@@ -143,6 +143,28 @@ bool LoadAlbedoTexture(const std::string &file, float shift, float scale, float 
     return true;
 }
 
+// ImageTexture<float, float> (textures/imagemap.cpp:56-86, imagemap.h:94-97): texels scale * (powf(luminance, gamma) + shift) and their
+// MIPMap<float> pyramid -- the box filter of three equal channels is the float box filter
+bool LoadBumpTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err) {
+    AlphaTexture level0;
+    if (!LoadAlphaTexture(file, shift, scale, gamma, &level0, err)) return false;
+    std::vector<Rgb> px(level0.texels.size());
+    for (size_t i = 0; i < px.size(); ++i) px[i] = Rgb{level0.texels[i], level0.texels[i], level0.texels[i]};
+    Pyramid mip;
+    mip.Build(level0.w, level0.h, px);
+    *out = AlbedoTexture();
+    out->present = true; out->channels = 1;
+    for (const Pyramid::Level &l : mip.levels) {
+        out->w.push_back(l.w); out->h.push_back(l.h);
+        for (const Rgb &c : l.px) out->rgb.push_back(c.r);
+    }
+    for (int i = 0; i < 128; ++i) {
+        const float alpha = 2, r2 = float(i) / float(128 - 1);
+        out->weightLut[i] = expf(-alpha * r2) - expf(-alpha);
+    }
+    return true;
+}
+
 // SampledSpectrum::ToRGB (core/spectrum.h:374-398): ToXYZ's running sums over the 30 samples, then XYZToRGB
 void SpectrumToRGB(const float c[30], float rgb[3]) {
     float xyz[3] = {0.f, 0.f, 0.f};

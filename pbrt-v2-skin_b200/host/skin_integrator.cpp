@@ -128,6 +128,16 @@ int skh_albedo_tex_info(const skh_scene *s, int *w12, int *h12, float *map4) {
     map4[0] = a.su; map4[1] = a.sv; map4[2] = a.du; map4[3] = a.dv;
     return (int)a.w.size();
 }
+// The material's bump map, same layout with one float per texel
+int skh_bump_tex_info(const skh_scene *s, int *w12, int *h12, float *map4) {
+    const AlbedoTexture &a = s->sd.skin.bumpTex;
+    if (!a.present) return 0;
+    for (size_t i = 0; i < a.w.size() && i < 12; ++i) { w12[i] = a.w[i]; h12[i] = a.h[i]; }
+    map4[0] = a.su; map4[1] = a.sv; map4[2] = a.du; map4[3] = a.dv;
+    return (int)a.w.size();
+}
+const float *skh_bump_tex_texels(const skh_scene *s) { return s->sd.skin.bumpTex.rgb.data(); }
+const float *skh_bump_tex_lut(const skh_scene *s) { return s->sd.skin.bumpTex.weightLut; }
 const float *skh_albedo_tex_rgb(const skh_scene *s) { return s->sd.skin.albedoTex.rgb.data(); }
 const float *skh_albedo_tex_lut(const skh_scene *s) { return s->sd.skin.albedoTex.weightLut; }
 // The device mesh's alpha texture: sizes {w, h} (0 = none) and mapping {su, sv, du, dv}; the texels

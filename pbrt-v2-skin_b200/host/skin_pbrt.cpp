@@ -86,6 +86,7 @@ private:
     std::vector<GraphicsState> pushedGraphicsStates;
     std::vector<Transform> pushedTransforms;
     std::map<std::string, std::string> textures;              // name -> class, declared but not evaluable here
+    std::map<std::string, AlbedoTexture> floatPyramids;        // the same float image maps with their MIPMap (EWA, maxanisotropy 8): usable as the skin's "texture bumpmap"
     std::map<std::string, AlbedoTexture> colorImageMaps;       // Texture ".." "color" | "spectrum" "imagemap": usable as the skin's "texture albedo"
     std::map<std::string, std::string> floatImageMapErrors;
     std::map<std::string, AlphaTexture> floatImageMaps;        // Texture ".." "float" "imagemap": usable as a mesh's "texture alpha"
@@ -366,7 +367,13 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
                   : "only \"color\" / \"spectrum\" \"imagemap\" textures are supported on the device path");
             return false;
         }
-        if (!t.empty()) { Error("layeredskin \"texture %s\" \"%s\": this texture slot of the skin is not supported on the device path (\"texture albedo\" with an image map is; no bump map, constant Kr / Kt)", tex, t.c_str()); return false; }
+        if (!t.empty() && !strcmp(tex, "bumpmap")) {     // GetFloatTextureOrNull("bumpmap"), materials/layeredskin.cpp -- an image map is supported
+            if (floatPyramids.count(t)) { k.bumpTex = floatPyramids[t]; continue; }
+            Error("layeredskin \"texture bumpmap\" \"%s\": %s", t.c_str(), floatImageMapErrors.count(t) ? floatImageMapErrors[t].c_str()
+                  : "only \"float\" \"imagemap\" textures (EWA filter, maxanisotropy 8) are supported on the device path");
+            return false;
+        }
+        if (!t.empty()) { Error("layeredskin \"texture %s\" \"%s\": this texture slot of the skin is not supported on the device path (\"texture albedo\" and \"texture bumpmap\" with image maps are; constant Kr / Kt)", tex, t.c_str()); return false; }
     }
     // Parameters the device path cannot honour are refused by name, not dropped: "doublerefsslf" swaps in FixedFresnelDielectric
     // (layeredskin.cpp:103-109), "genprofile false" / "usemontecarlo true" select other profile sources (:97-101).
@@ -392,7 +399,7 @@ bool Front::skinFromParams(const ParamSet &mp, const ParamSet &shapeParams, Skin
 static bool sameSkin(const SkinParams &a, const SkinParams &b) {
     return a.roughness == b.roughness && a.nmperunit == b.nmperunit && a.f_mel == b.f_mel && a.f_eu == b.f_eu && a.f_blood == b.f_blood && a.f_ohg == b.f_ohg &&
            a.desiredlength == b.desiredlength && !memcmp(a.Kr, b.Kr, 12) && !memcmp(a.Kt, b.Kt, 12) && !memcmp(a.albedo, b.albedo, 12) && a.hasAlbedo == b.hasAlbedo &&
-           a.albedoTex == b.albedoTex && a.lerponthinslab == b.lerponthinslab && !memcmp(a.layerThickness, b.layerThickness, 8) && !memcmp(a.layerIor, b.layerIor, 8);
+           a.albedoTex == b.albedoTex && a.bumpTex == b.bumpTex && a.lerponthinslab == b.lerponthinslab && !memcmp(a.layerThickness, b.layerThickness, 8) && !memcmp(a.layerIor, b.layerIor, 8);
 }
 
 // pbrtShape (core/api.cpp:982-1070)
@@ -707,6 +714,12 @@ bool Front::statement(const std::string &id) {
                 a.su = ps.FindOneFloat("uscale", 1.f); a.sv = ps.FindOneFloat("vscale", 1.f); a.du = ps.FindOneFloat("udelta", 0.f); a.dv = ps.FindOneFloat("vdelta", 0.f);
                 ps.FindOneFloat("maxanisotropy", 8.f); ps.FindOneBool("trilinear", false);      // without effect on a lookup with zero differentials
                 floatImageMaps[name] = a;
+                AlbedoTexture b;
+                if (!ps.FindOneBool("trilinear", false) && ps.FindOneFloat("maxanisotropy", 8.f) == 8.f &&
+                    LoadBumpTexture(resolve(ps.FindOneString("filename", "")), ps.FindOneFloat("shift", 0.f), ps.FindOneFloat("scale", 1.f), ps.FindOneFloat("gamma", 1.f), &b, &err)) {
+                    b.su = a.su; b.sv = a.sv; b.du = a.du; b.dv = a.dv;
+                    floatPyramids[name] = b;
+                }
             } else floatImageMapErrors[name] = err.empty() ? "only \"uv\" mapping with \"repeat\" wrap is supported" : err;
         }
         if ((type == "color" || type == "spectrum") && texname == "imagemap") {      // CreateImageSpectrumTexture (textures/imagemap.cpp): kept for "texture albedo"

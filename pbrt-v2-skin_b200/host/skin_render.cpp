@@ -76,6 +76,11 @@ int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a) {
     return skc_upload_albedo_texture(ctx, (uint32_t)a.w.size(), a.w.data(), a.h.data(), a.rgb.data(), a.weightLut, a.su, a.sv, a.du, a.dv);
 }
 
+int UploadBumpTexture(skc_ctx *ctx, const AlbedoTexture &a) {
+    if (!a.present) return skc_upload_bump_texture(ctx, 0, nullptr, nullptr, nullptr, nullptr, 1.f, 1.f, 0.f, 0.f);
+    return skc_upload_bump_texture(ctx, (uint32_t)a.w.size(), a.w.data(), a.h.data(), a.rgb.data(), a.weightLut, a.su, a.sv, a.du, a.dv);
+}
+
 int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a) {
     if (!a.present) return skc_upload_alpha(ctx, 0, 0, nullptr, 1.f, 1.f, 0.f, 0.f);
     return skc_upload_alpha(ctx, (uint32_t)a.w, (uint32_t)a.h, a.texels.data(), a.su, a.sv, a.du, a.dv);
@@ -96,7 +101,8 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     auto dev = [&](int rc) { if (rc) *err = skc_last_error(ctx); return rc == 0; };
     const int world = comm ? skc_comm_world(comm) : 1, rank = comm ? skc_comm_rank(comm) : 0;
     double t0 = now();
-    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env)) || !dev(UploadAlpha(ctx, built.mesh->alpha)) || !dev(UploadAlbedoTexture(ctx, sd.skin.albedoTex))) return false;
+    if (!dev(UploadScene(ctx, built)) || !dev(UploadEnvMap(ctx, sd.env)) || !dev(UploadAlpha(ctx, built.mesh->alpha)) || !dev(UploadAlbedoTexture(ctx, sd.skin.albedoTex)) ||
+        !dev(UploadBumpTexture(ctx, sd.skin.bumpTex))) return false;
     double t1 = now();
     if (!dev(BuildSkinMaterial(ctx, sd.skin, comm)) || !dev(InstallAlbedo(ctx, sd.skin, sd.mix)) || !dev(skc_synchronize(ctx))) return false;
     double t2 = now();
@@ -207,7 +213,7 @@ bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *
     BuiltScene built;
     if (!BuildScene(sd, nullptr, &built, err)) return false;
     uint64_t n = 0;
-    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || UploadAlpha(ctx, built.mesh->alpha) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
+    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || UploadAlpha(ctx, built.mesh->alpha) || UploadBumpTexture(ctx, sd.skin.bumpTex) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
     *nPoints = n;
     if (sd.rendererFilename.empty()) return true;                            // "(Not writing to file)"
     std::vector<skc_surface_point> pts(n);

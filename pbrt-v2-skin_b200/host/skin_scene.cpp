@@ -364,6 +364,11 @@ bool SceneDesc::LoadLines(const std::string &path) {
                     if (file[0] != '/') file = dir + file;
                     if (!LoadAlbedoTexture(file, 0.f, 1.f, 1.f, &skin.albedoTex, &error)) return false;
                 }
+                else if (k == "bumptex") {        // Texture ".." "float" "imagemap" + "texture bumpmap"
+                    std::string file; ls >> file;
+                    if (file[0] != '/') file = dir + file;
+                    if (!LoadBumpTexture(file, 0.f, 1.f, 1.f, &skin.bumpTex, &error)) return false;
+                }
                 else {
                     float v; ls >> v;
                     if (k == "roughness") skin.roughness = v; else if (k == "nmperunit") skin.nmperunit = v;

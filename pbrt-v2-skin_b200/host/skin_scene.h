@@ -77,12 +77,15 @@ struct EnvMap {
 struct AlbedoTexture {
     bool present = false;
     std::vector<int> w, h;                      // per level
-    std::vector<float> rgb;                     // the levels one after the other, [h][w][3] each
+    int channels = 3;                           // 3: a colour map; 1: a float map (the bump map's displacement)
+    std::vector<float> rgb;                     // the levels one after the other, [h][w][channels] each
     float weightLut[128] = {0};                 // core/mipmap.h:186-193
     float su = 1.f, sv = 1.f, du = 0.f, dv = 0.f;
-    bool operator==(const AlbedoTexture &o) const { return present == o.present && w == o.w && h == o.h && rgb == o.rgb && su == o.su && sv == o.sv && du == o.du && dv == o.dv; }
+    bool operator==(const AlbedoTexture &o) const { return present == o.present && channels == o.channels && w == o.w && h == o.h && rgb == o.rgb && su == o.su && sv == o.sv && du == o.du && dv == o.dv; }
 };
 bool LoadAlbedoTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err);
+// ImageTexture<float, float> with its whole MIPMap<float> (channels = 1): the skin's "texture bumpmap"
+bool LoadBumpTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err);
 
 // LayeredSkin parameters (materials/layeredskin.cpp:222-262)
 struct SkinParams {
@@ -97,6 +100,7 @@ struct SkinParams {
     float albedo[3] = {1, 1, 1};
     bool hasAlbedo = false;
     AlbedoTexture albedoTex;                    // "texture albedo" (an image map); excludes hasAlbedo
+    AlbedoTexture bumpTex;                      // "texture bumpmap" (a float image map, channels = 1)
     bool lerponthinslab = true;
     float layerThickness[2] = {0.25e6f, 20e6f}, layerIor[2] = {1.4f, 1.4f};
 };
@@ -207,7 +211,9 @@ int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nul
 int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);
 int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);
 int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a);
-int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a);   // skc_upload_albedo_texture (or its removal)    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
+int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a);
+int UploadBumpTexture(skc_ctx *ctx, const AlbedoTexture &a);     // skc_upload_bump_texture (or its removal)
+   // skc_upload_albedo_texture (or its removal)    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks
 int UploadScene(skc_ctx *ctx, const BuiltScene &b);
 
 // SamplerRenderer::Render (renderers/samplerrenderer.cpp:191-225) on the device: scene + material upload, Preprocess,

@@ -39,6 +39,9 @@ def load_host_library():
     lib.skh_albedo_tex_info.restype = C.c_int; lib.skh_albedo_tex_info.argtypes = [vp, vp, vp, vp]
     lib.skh_albedo_tex_rgb.restype = vp; lib.skh_albedo_tex_rgb.argtypes = [vp]
     lib.skh_albedo_tex_lut.restype = vp; lib.skh_albedo_tex_lut.argtypes = [vp]
+    lib.skh_bump_tex_info.restype = C.c_int; lib.skh_bump_tex_info.argtypes = [vp, vp, vp, vp]
+    lib.skh_bump_tex_texels.restype = vp; lib.skh_bump_tex_texels.argtypes = [vp]
+    lib.skh_bump_tex_lut.restype = vp; lib.skh_bump_tex_lut.argtypes = [vp]
     lib.skh_alpha_info.restype = None; lib.skh_alpha_info.argtypes = [vp, vp, vp]
     lib.skh_alpha_texels.restype = vp; lib.skh_alpha_texels.argtypes = [vp]
     lib.skh_env_sizes.restype = C.c_float; lib.skh_env_sizes.argtypes = [vp, vp]
@@ -180,6 +183,16 @@ class HostScene:
         return {"w": w[:n].copy(), "h": h[:n].copy(), "map": tuple(float(x) for x in m),
                 "rgb": _view(self.lib.skh_albedo_tex_rgb(self.h), 4 * total, np.float32).copy(), "lut": _view(self.lib.skh_albedo_tex_lut(self.h), 512, np.float32).copy()}
 
+    def bump_texture(self):
+        """The material's "texture bumpmap": the MIPMap<float> pyramid (levels' sizes, one displacement per texel), the EWA weight table and the uv mapping; or None."""
+        w = np.zeros(12, np.int32); h = np.zeros(12, np.int32); m = np.zeros(4, np.float32)
+        n = self.lib.skh_bump_tex_info(self.h, w.ctypes.data_as(C.c_void_p), h.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p))
+        if not n:
+            return None
+        total = int(sum(int(w[i]) * int(h[i]) for i in range(n)))
+        return {"w": w[:n].copy(), "h": h[:n].copy(), "map": tuple(float(x) for x in m),
+                "texels": _view(self.lib.skh_bump_tex_texels(self.h), 4 * total, np.float32).copy(), "lut": _view(self.lib.skh_bump_tex_lut(self.h), 512, np.float32).copy()}
+
     def alpha_texture(self):
         """The mesh's "texture alpha" (level-0 float texels and its uv mapping), or None."""
         wh = np.zeros(2, np.int32); m = np.zeros(4, np.float32)
@@ -195,6 +208,7 @@ class HostScene:
         dev.upload_envmap(self.envmap())
         dev.upload_alpha(self.alpha_texture())
         dev.upload_albedo_texture(self.albedo_texture())
+        dev.upload_bump_texture(self.bump_texture())
 
     FRAME_DESC_BYTES = 4 * (5 + 16 + 16 + 2 + 256 + 90 + 1 + 2 + 60 + 1 + 2)
 

@@ -36,7 +36,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
            "skc_comm_unique_id", "skc_comm_create", "skc_comm_create_local", "skc_comm_destroy", "skc_comm_rank", "skc_comm_world",
            "skc_comm_allgather_positions", "skc_comm_allgather_rows_begin", "skc_comm_allgather_rows_wait", "skc_comm_reduce_film",
-           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_upload_envmap", "skc_upload_alpha", "skc_upload_albedo_texture", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_upload_envmap", "skc_upload_alpha", "skc_upload_albedo_texture", "skc_upload_bump_texture", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -131,6 +131,7 @@ def load_library():
     lib.skc_comm_allgather_host.restype = i32; lib.skc_comm_allgather_host.argtypes = [vp, vp, u64]
     lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_upload_albedo_texture.restype = i32; lib.skc_upload_albedo_texture.argtypes = [vp, u32, vp, vp, vp, vp, f32, f32, f32, f32]
+    lib.skc_upload_bump_texture.restype = i32; lib.skc_upload_bump_texture.argtypes = [vp, u32, vp, vp, vp, vp, f32, f32, f32, f32]
     lib.skc_upload_alpha.restype = i32; lib.skc_upload_alpha.argtypes = [vp, u32, u32, vp, f32, f32, f32, f32]
     lib.skc_upload_envmap.restype = i32; lib.skc_upload_envmap.argtypes = [vp, u32, u32, vp, vp, vp, vp, vp, vp, f32]
     lib.skc_set_albedo_factors.restype = i32; lib.skc_set_albedo_factors.argtypes = [vp, vp, vp]
@@ -349,6 +350,14 @@ class SkinDevice:
         w = np.ascontiguousarray(tex["w"], np.int32); h = np.ascontiguousarray(tex["h"], np.int32)
         rgb = np.ascontiguousarray(tex["rgb"], np.float32); lut = np.ascontiguousarray(tex["lut"], np.float32)
         self._ck(self.lib.skc_upload_albedo_texture(self.ctx, len(w), _ptr(w), _ptr(h), _ptr(rgb), _ptr(lut), *[float(x) for x in tex["map"]]))
+
+    def upload_bump_texture(self, tex):
+        """tex: dict with w, h (per level), texels (one displacement each), lut, map = (su, sv, du, dv) (HostScene.bump_texture()), or None to remove it."""
+        if tex is None:
+            return self._ck(self.lib.skc_upload_bump_texture(self.ctx, 0, None, None, None, None, 1.0, 1.0, 0.0, 0.0))
+        w = np.ascontiguousarray(tex["w"], np.int32); h = np.ascontiguousarray(tex["h"], np.int32)
+        t = np.ascontiguousarray(tex["texels"], np.float32); lut = np.ascontiguousarray(tex["lut"], np.float32)
+        self._ck(self.lib.skc_upload_bump_texture(self.ctx, len(w), _ptr(w), _ptr(h), _ptr(t), _ptr(lut), *[float(x) for x in tex["map"]]))
 
     def upload_alpha(self, alpha):
         """alpha: dict with w, h, texels, map = (su, sv, du, dv) (HostScene.alpha_texture()), or None to remove it."""

@@ -137,6 +137,10 @@ def lights_golden(name="skin_lights"):
         if os.path.exists(os.path.join(d, "albedo_tex.bin")):   # "texture albedo": the MIPMap pyramid and the EWA weight table
             arrays["albedo_tex"] = f32("albedo_tex.bin")
             arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
+        if os.path.exists(os.path.join(d, "bump_tex.bin")):     # "texture bumpmap": the MIPMap<float> pyramid, the bumped normals of the surface points and of the hits
+            arrays["bump_tex"] = f32("bump_tex.bin")
+            arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
+            arrays["surface_normals"] = f32("surface_points.bin").reshape(-1, 11)[:, 3:6].copy()
         if os.path.exists(os.path.join(d, "envmap.bin")):      # LightSource "infinite": its map and Distribution2D (ref_driver dumpLights)
             arrays["envmap"] = f32("envmap.bin")
     path = os.path.join(OUT, name + ".npz")
@@ -326,4 +330,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex") else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex", "skin_bump") else scene_golden(w)
