@@ -72,7 +72,7 @@ struct TessEmit {
 };
 
 // the domain shader of TessellateSurfacePoints (trianglemesh.cpp:216-255)
-__host__ __device__ inline void tessPoint(const TessEmit &e, TessBC bv0, TessBC bv1, TessBC bv2, uint32_t slot) {
+template <bool BUMP> __host__ __device__ inline void tessPoint(const TessEmit &e, TessBC bv0, TessBC bv1, TessBC bv2, uint32_t slot) {
     f3 sv0 = bcPoint(bv0, e.v0, e.v1, e.v2), sv1 = bcPoint(bv1, e.v0, e.v1, e.v2), sv2 = bcPoint(bv2, e.v0, e.v1, e.v2);
     TessBC bc;
     if (!e.incenter) bc = bcOfBc(bc3(1.f / 3.f, 1.f / 3.f, 1.f / 3.f), bv0, bv1, bv2);
@@ -84,7 +84,7 @@ __host__ __device__ inline void tessPoint(const TessEmit &e, TessBC bv0, TessBC 
     float tu, tv;
     triShadingGeometry(e.mv, e.vi, bc.b0, bc.b1, bc.b2, &nn, &tu, &tv);
 #ifdef __CUDA_ARCH__
-    if (e.bump) { f3 dpduBump; triBump(e.mv, e.vi, bc.b0, bc.b1, bc.b2, *e.bump, 0.f, 0.f, 0.f, 0.f, &nn, &dpduBump); }    // sp.n = dgBump.nn (trianglemesh.cpp:236-242)
+    if (BUMP) { f3 dpduBump; triBump(e.mv, e.vi, bc.b0, bc.b1, bc.b2, *e.bump, 0.f, 0.f, 0.f, 0.f, &nn, &dpduBump); }    // sp.n = dgBump.nn (trianglemesh.cpp:236-242)
 #endif
     float area = .5f * len3(cross3(sub3(sv1, sv0), sub3(sv2, sv0)));
     float *o = reinterpret_cast<float *>(e.out + slot);
@@ -93,7 +93,7 @@ __host__ __device__ inline void tessPoint(const TessEmit &e, TessBC bv0, TessBC 
 }
 
 // matching (trianglemesh.cpp:319-351): zipper between an inner edge of segsInner and an outer edge of segsOuter segments
-__host__ __device__ inline void tessMatching(const TessEmit &e, TessBC b0Inner, TessBC b1Inner, int segsInner, TessBC b0Outer, TessBC b1Outer, int segsOuter, uint32_t slot) {
+template <bool BUMP> __host__ __device__ inline void tessMatching(const TessEmit &e, TessBC b0Inner, TessBC b1Inner, int segsInner, TessBC b0Outer, TessBC b1Outer, int segsOuter, uint32_t slot) {
     int innerPos = 0, outerPos = 0;
     while (innerPos < segsInner || outerPos < segsOuter) {
         TessBC bInner = segsInner ? bcLerp((float)innerPos / (float)segsInner, b0Inner, b1Inner) : b0Inner;
@@ -102,11 +102,11 @@ __host__ __device__ inline void tessMatching(const TessEmit &e, TessBC b0Inner, 
         float slopeOuter = (outerPos < segsOuter) ? fabsf((float)innerPos + 1.f - (float)(outerPos + 1) / (float)segsOuter * (float)(segsInner + 2)) : INFINITY;
         if (slopeInner < slopeOuter) {
             TessBC bInnerNew = bcLerp((float)(innerPos + 1) / (float)segsInner, b0Inner, b1Inner);
-            tessPoint(e, bInnerNew, bInner, bOuter, slot++);
+            tessPoint<BUMP>(e, bInnerNew, bInner, bOuter, slot++);
             innerPos++;
         } else {
             TessBC bOuterNew = bcLerp((float)(outerPos + 1) / (float)segsOuter, b0Outer, b1Outer);
-            tessPoint(e, bInner, bOuter, bOuterNew, slot++);
+            tessPoint<BUMP>(e, bInner, bOuter, bOuterNew, slot++);
             outerPos++;
         }
     }
@@ -115,7 +115,7 @@ __host__ __device__ inline void tessMatching(const TessEmit &e, TessBC b0Inner, 
 // One job = one (ring, side) walk of a triangle's tessellation; a ring without an inner edge is a single job (side 0).  Every
 // job knows where its points go (see the header comment), so the jobs of a triangle run in any order -- threads of a CTA on
 // the device, a plain loop in skc_tessellate_host.
-__host__ __device__ inline void tessJob(const TessEmit &e, const TessFactors &t, int job) {
+template <bool BUMP> __host__ __device__ inline void tessJob(const TessEmit &e, const TessFactors &t, int job) {
     const TessBC b0 = bc3(1.f, 0.f, 0.f), b1 = bc3(0.f, 1.f, 0.f), b2 = bc3(0.f, 0.f, 1.f), bcC = bc3(1.f / 3.f, 1.f / 3.f, 1.f / 3.f);
     const TessBC corner[3] = {b0, b1, b2};
     int r = job / 3, side = job - 3 * r;
@@ -125,10 +125,10 @@ __host__ __device__ inline void tessJob(const TessEmit &e, const TessFactors &t,
     int edgeInner = last ? t.c - 2 : t.c - (t.rings - r) * 2;
     if (edgeInner < 0) {
         if (side == 0) {
-            if (last) tessPoint(e, b0, b1, b2, slot);
+            if (last) tessPoint<BUMP>(e, b0, b1, b2, slot);
             else {
                 float f = (float)(r + 1) / (float)t.rings;
-                tessPoint(e, bcLerp(f, bcC, b0), bcLerp(f, bcC, b1), bcLerp(f, bcC, b2), slot);
+                tessPoint<BUMP>(e, bcLerp(f, bcC, b0), bcLerp(f, bcC, b1), bcLerp(f, bcC, b2), slot);
             }
         }
         return;
@@ -150,10 +150,10 @@ __host__ __device__ inline void tessJob(const TessEmit &e, const TessFactors &t,
         outerBefore = side * segsOuter;
     }
     slot += (uint32_t)(side * edgeInner + outerBefore);
-    tessMatching(e, inA, inB, edgeInner, outA, outB, segsOuter, slot);
+    tessMatching<BUMP>(e, inA, inB, edgeInner, outA, outB, segsOuter, slot);
 }
 
-__global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *__restrict__ idx, uint32_t nTris, float minDist, int incenter,
+template <bool BUMP> __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *__restrict__ idx, uint32_t nTris, float minDist, int incenter,
                                                    uint32_t materialId, const uint32_t *__restrict__ offsets, skc_surface_point *__restrict__ out,
                                                    uint32_t rangeLo, uint32_t rangeHi, const __grid_constant__ AlbedoTexDev bump) {
     uint32_t tri = blockIdx.x;
@@ -163,9 +163,9 @@ __global__ void __launch_bounds__(128) k_tess_emit(MeshView mv, const int32_t *_
     e.mv = mv; e.vi = make_int4(idx[3 * tri], idx[3 * tri + 1], idx[3 * tri + 2], 0);
     e.v0 = ld3(mv.P, e.vi.x); e.v1 = ld3(mv.P, e.vi.y); e.v2 = ld3(mv.P, e.vi.z);
     e.incenter = incenter; e.materialId = materialId; e.rayEpsilon = minDist / 10.f; e.out = out + offsets[tri];
-    e.bump = bump.rgb ? &bump : nullptr;
+    e.bump = BUMP ? &bump : nullptr;
     TessFactors t = tessFactors(e.v0, e.v1, e.v2, minDist);
-    for (int job = threadIdx.x; job < 3 * t.rings; job += blockDim.x) tessJob(e, t, job);
+    for (int job = threadIdx.x; job < 3 * t.rings; job += blockDim.x) tessJob<BUMP>(e, t, job);
 }
 
 // GetSurfacePointsThroughTessellation for the uploaded mesh, written into the resident surface-point set
@@ -200,7 +200,8 @@ static int tessellate(skc_ctx *ctx, float minDist, int incenter, uint32_t materi
     }
     if (total) {
         uint32_t lo = ranged ? (uint32_t)std::min<uint64_t>(first, total) : 0u, hi = ranged ? (uint32_t)std::min<uint64_t>(first + count, total) : total;
-        k_tess_emit<<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi, ctx->bumpTex);
+        if (ctx->bumpTex.rgb) k_tess_emit<true><<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi, ctx->bumpTex);
+        else k_tess_emit<false><<<nTris, 128, 0, ctx->stream>>>(skc_mesh_view(ctx), ctx->meshIdx, nTris, minDist, incenter, materialId, offsets, ctx->resPts, lo, hi, ctx->bumpTex);
         SKC_LAUNCHED("k_tess_emit");
     }
     skc_stage_end(ctx, 8);
@@ -254,7 +255,7 @@ extern "C" int skc_tessellate_host(const float *P, const float *N, const float *
         if (out) {
             if (total + n > cap) return 1;
             e.out = out + total;
-            for (int job = 0; job < 3 * t.rings; ++job) tessJob(e, t, job);
+            for (int job = 0; job < 3 * t.rings; ++job) tessJob<false>(e, t, job);
         }
         total += n;
     }
