@@ -185,6 +185,14 @@ int skc_get_surface_points(skc_ctx *ctx, uint64_t first, uint64_t count, skc_sur
  * out == NULL counts only; returns non-zero when cap is too small or an argument is missing. */
 int skc_tessellate_host(const float *P, const float *N, const float *UV, const int32_t *idx, uint32_t nTris, const float *o2w32, int flip,
                         float minDist, int incenter, uint32_t materialId, skc_surface_point *out, uint64_t cap, uint64_t *countOut);
+/* The Poisson-disk surface-point finder, MultipoleSubsurfaceIntegrator's "bool usepoissonpointfinder" (renderers/surfacepoints.cpp:103-284,
+ * FindPoissonPointDistribution :354-359), as the reference runs it with ONE SurfacePointTask (--ncores 1: RNG(0); with more tasks the
+ * reference's result depends on thread timing): rounds of 20 000 random walks of 30 bounces from origin3 (the camera position) through
+ * the uploaded scene and its bounding sphere on the device, the accept / reject chain (no accepted point within minSampleDist;
+ * stop after maxFails rejections in a row: 2000, 200 under --quick) on the host.  The accepted points become the resident
+ * surface-point set, as after skc_tessellate_resident (skc_get_surface_points reads them).  stats4 (optional): {points, paths
+ * traced, rays traced, rounds}. */
+int skc_poisson_resident(skc_ctx *ctx, const float *origin3, float minSampleDist, uint32_t materialId, int maxFails, uint64_t *countOut, uint64_t *stats4);
 
 /* MultipoleSubsurfaceIntegrator::Preprocess (multipolesubsurface.cpp:170-238) as ONE call: the irradiance pass over
  * points [first, first+count) and, concurrently on a second stream, the octree topology of ALL nTotal points (it

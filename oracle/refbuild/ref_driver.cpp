@@ -214,6 +214,7 @@ static void buildScene(const SceneDesc &sd, const std::string &pfmOut) {
         ParamSet ps;
         for (auto &kv : sd.integ) {
             if (kv.first == "maxdepth") addI(ps, "maxdepth", (int)kv.second);
+            else if (kv.first == "usepoissonpointfinder" || kv.first == "incenter") { bool b = kv.second != 0.f; ps.AddBool(kv.first.c_str(), &b, 1); }
             else addF(ps, kv.first.c_str(), kv.second);
         }
         pbrtSurfaceIntegrator("multipolesubsurface", ps);
@@ -622,8 +623,13 @@ static int runScene(int argc, char **argv) {
         }
         dumpBVH(dir, scene, meta, meshes);
         dumpLights(dir, scene, meta);
-        // Surface points exactly as Preprocess will regenerate them (deterministic tessellation).
+        // Surface points exactly as Preprocess will regenerate them (deterministic tessellation; the Poisson finder is
+        // deterministic with one task, i.e. --ncores 1).
         vector<SurfacePoint> pts;
+        if (integ->usePoissonPointFinder) {
+            Point pCamera = camera->CameraToWorld(camera->shutterOpen, Point(0, 0, 0));
+            FindPoissonPointDistribution(pCamera, camera->shutterOpen, integ->minSampleDist, scene, &pts);
+        } else
         GetSurfacePointsThroughTessellation(camera->shutterOpen, integ->minSampleDist, scene,
                                             &integ->originalPrimitives, &pts, integ->incenter);
         dump(dir + "/surface_points.bin", pts.data(), pts.size());

@@ -105,6 +105,13 @@ void skh_mesh_o2w(const skh_scene *s, float *out32, int *reverse, int *swaps) {
 void skh_integrator_params(const skh_scene *s, float *out4) {
     out4[0] = s->sd.maxerror; out4[1] = s->sd.minsampledistance; out4[2] = s->sd.mix; out4[3] = (float)s->sd.maxdepth;
 }
+// "bool usepoissonpointfinder": {use, maxFails} and the finder's origin, the camera position CameraToWorld(Point(0, 0, 0))
+void skh_poisson_params(const skh_scene *s, int *use2, float *origin3) {
+    use2[0] = s->sd.usePoissonPointFinder ? 1 : 0; use2[1] = s->sd.poissonMaxFails;
+    const PerspectiveCameraDesc cam = s->sd.Camera();
+    const float *m = cam.CameraToWorld.m.m[0];
+    origin3[0] = m[3]; origin3[1] = m[7]; origin3[2] = m[11];
+}
 // skin params: roughness nmperunit f_mel f_eu f_blood f_ohg desiredlength lerp t0 ior0 t1 ior1
 void skh_skin_params(const skh_scene *s, float *out12) {
     const SkinParams &k = s->sd.skin;

@@ -587,7 +587,8 @@ bool Front::statement(const std::string &id) {
         sd->pointsFile = ps.FindOneString("pointsfile", "");
         if (!sd->pointsFile.empty()) sd->pointsFile = resolve(sd->pointsFile);
         if (ps.FindOneBool("showirradiancepoints", false)) { Error("multipolesubsurface \"showirradiancepoints\" is not supported on the device path"); return false; }
-        if (ps.FindOneBool("usepoissonpointfinder", false)) { Error("multipolesubsurface \"usepoissonpointfinder\" is not supported on the device path (tessellated surface points only)"); return false; }
+        sd->usePoissonPointFinder = ps.FindOneBool("usepoissonpointfinder", false);
+        if (options.quickRender) sd->poissonMaxFails = std::max(10, 2000 / 10);
         if (options.quickRender) { /* the reference's integrator has no quick-render branch */ }
         haveIntegrator = true;
         reportUnused(ps, "SurfaceIntegrator");

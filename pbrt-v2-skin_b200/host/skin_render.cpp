@@ -128,10 +128,14 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
                 fclose(f);
             }
         }
-        const bool fromFile = !filePts.empty();
+        bool fromFile = !filePts.empty();
         if (fromFile) {
             nPts = filePts.size();
             if (!dev(skc_set_surface_points(ctx, filePts.data(), nPts))) return false;
+        } else if (sd.usePoissonPointFinder) {                               // :183-185; deterministic (one SurfacePointTask), so every rank finds the same set
+            const float origin[3] = {fd.cameraToWorld[3], fd.cameraToWorld[7], fd.cameraToWorld[11]};      // CameraToWorld(shutterOpen, Point(0, 0, 0))
+            if (!dev(skc_poisson_resident(ctx, origin, sd.minsampledistance, built.mesh->materialId, sd.poissonMaxFails, &nPts, nullptr))) return false;
+            fromFile = true;                                                  // the whole set is resident from here on
         } else if (world == 1) {                                             // pts.size() == 0 -> tessellate (:182-190)
             if (!dev(skc_tessellate_resident(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, &nPts))) return false;
         } else if (!dev(skc_tessellate_range(ctx, sd.minsampledistance, sd.incenter, built.mesh->materialId, 0, 0, &nPts))) return false;   // the count

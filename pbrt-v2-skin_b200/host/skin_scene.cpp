@@ -324,6 +324,7 @@ bool SceneDesc::LoadLines(const std::string &path) {
                 if (k == "maxdepth") maxdepth = (int)v; else if (k == "maxerror") maxerror = v;
                 else if (k == "minsampledistance") minsampledistance = v; else if (k == "mix") mix = v;
                 else if (k == "incenter") incenter = v != 0.f;
+                else if (k == "usepoissonpointfinder") usePoissonPointFinder = v != 0.f;
                 else { error = "unknown integrator parameter " + k; return false; }
             }
         } else if (key == "light") {

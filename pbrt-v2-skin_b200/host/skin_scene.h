@@ -144,6 +144,8 @@ struct SceneDesc {
     int maxdepth = 5;
     float maxerror = .05f, minsampledistance = .25f, mix = .5f;
     bool incenter = false;
+    int poissonMaxFails = 2000;           // surfacepoints.cpp:134-135: 2000, max(10, 2000 / 10) under --quick
+    bool usePoissonPointFinder = false;   // "bool usepoissonpointfinder": FindPoissonPointDistribution instead of the tessellator (skc_poisson_resident)
     std::string pointsFile;           // "string pointsfile": raw SurfacePoint[44 B] records (multipolesubsurface.cpp:176-181, core/floatfile.h:45-63)
     // Renderer: "sampler" renders the frame; "tessellatesurfacepoints" only writes the surface points of the scene's
     // translucent meshes to "string filename" (renderers/surfacepoints.cpp:335-347,381-388) -- the file `pointsfile` reads

@@ -35,6 +35,7 @@ def load_host_library():
         getattr(lib, f).restype = vp; getattr(lib, f).argtypes = [vp]
     lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
+    lib.skh_poisson_params.restype = None; lib.skh_poisson_params.argtypes = [vp, vp, vp]
     lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
     lib.skh_albedo_tex_info.restype = C.c_int; lib.skh_albedo_tex_info.argtypes = [vp, vp, vp, vp]
     lib.skh_albedo_tex_rgb.restype = vp; lib.skh_albedo_tex_rgb.argtypes = [vp]
@@ -111,6 +112,9 @@ class HostScene:
         self.reverse, self.swaps = r.value, s.value
         ip = np.zeros(4, np.float32); L.skh_integrator_params(self.h, ip.ctypes.data_as(C.c_void_p))
         self.maxerror, self.minsampledistance, self.mix, self.maxdepth = float(ip[0]), float(ip[1]), float(ip[2]), int(ip[3])
+        pu = np.zeros(2, np.int32); self.camera_position = np.zeros(3, np.float32)
+        L.skh_poisson_params(self.h, pu.ctypes.data_as(C.c_void_p), self.camera_position.ctypes.data_as(C.c_void_p))
+        self.use_poisson, self.poisson_max_fails = bool(pu[0]), int(pu[1])
         self.skin = np.zeros(12, np.float32); L.skh_skin_params(self.h, self.skin.ctypes.data_as(C.c_void_p))
 
     def pixel_filter(self):

@@ -36,7 +36,7 @@ SYMBOLS = ["skc_create", "skc_destroy", "skc_last_error", "skc_synchronize", "sk
            "skc_frame_film_clear", "skc_frame_film_dev", "skc_frame_film_get", "skc_frame_film_rgb", "skc_frame_get_order",
            "skc_comm_unique_id", "skc_comm_create", "skc_comm_create_local", "skc_comm_destroy", "skc_comm_rank", "skc_comm_world",
            "skc_comm_allgather_positions", "skc_comm_allgather_rows_begin", "skc_comm_allgather_rows_wait", "skc_comm_reduce_film",
-           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_upload_envmap", "skc_upload_alpha", "skc_upload_albedo_texture", "skc_upload_bump_texture", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
+           "skc_comm_max_f32", "skc_comm_barrier", "skc_comm_allgather_host", "skc_mo_static", "skc_test_sincosf", "skc_test_libmf", "skc_get_irradiance_rows", "skc_set_irradiance_rows", "skc_mo_table_stats", "skc_mo_group_histogram", "skc_set_albedo_factors", "skc_upload_envmap", "skc_upload_alpha", "skc_upload_albedo_texture", "skc_upload_bump_texture", "skc_poisson_resident", "skc_moc_build", "skc_moc_info", "skc_moc_eval", "skc_moc_free"]
 
 
 class SkcError(RuntimeError):
@@ -131,6 +131,7 @@ def load_library():
     lib.skc_comm_allgather_host.restype = i32; lib.skc_comm_allgather_host.argtypes = [vp, vp, u64]
     lib.skc_mo_static.restype = i32; lib.skc_mo_static.argtypes = [vp, vp, u64, f32, vp]
     lib.skc_upload_albedo_texture.restype = i32; lib.skc_upload_albedo_texture.argtypes = [vp, u32, vp, vp, vp, vp, f32, f32, f32, f32]
+    lib.skc_poisson_resident.restype = i32; lib.skc_poisson_resident.argtypes = [vp, vp, f32, u32, i32, vp, vp]
     lib.skc_upload_bump_texture.restype = i32; lib.skc_upload_bump_texture.argtypes = [vp, u32, vp, vp, vp, vp, f32, f32, f32, f32]
     lib.skc_upload_alpha.restype = i32; lib.skc_upload_alpha.argtypes = [vp, u32, u32, vp, f32, f32, f32, f32]
     lib.skc_upload_envmap.restype = i32; lib.skc_upload_envmap.argtypes = [vp, u32, u32, vp, vp, vp, vp, vp, vp, f32]
@@ -296,6 +297,12 @@ class SkinDevice:
         n = C.c_uint64(0)
         self._ck(self.lib.skc_tessellate_range(self.ctx, float(min_dist), int(incenter), int(material_id), int(first), int(count), C.byref(n)))
         return int(n.value)
+
+    def poisson_resident(self, origin, min_sample_dist, material_id=0, max_fails=2000):
+        """FindPoissonPointDistribution as the reference runs it on one core (skc_poisson_resident); returns (count, stats dict)."""
+        o = np.ascontiguousarray(origin, np.float32); n = C.c_uint64(0); st = np.zeros(4, np.uint64)
+        self._ck(self.lib.skc_poisson_resident(self.ctx, _ptr(o), float(min_sample_dist), int(material_id), int(max_fails), C.byref(n), _ptr(st)))
+        return int(n.value), dict(points=int(st[0]), paths=int(st[1]), rays=int(st[2]), rounds=int(st[3]))
 
     def get_surface_points(self, first, count):
         out = np.empty(count, DT_SURFACE_POINT)

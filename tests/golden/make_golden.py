@@ -141,6 +141,8 @@ def lights_golden(name="skin_lights"):
             arrays["bump_tex"] = f32("bump_tex.bin")
             arrays["hits"] = np.fromfile(os.path.join(d, "hits.bin"), np.uint8)
             arrays["surface_normals"] = f32("surface_points.bin").reshape(-1, 11)[:, 3:6].copy()
+        if int(meta.get("surface_points", 0)) and name == "skin_poisson":      # "bool usepoissonpointfinder": the finder's points (one task)
+            arrays["surface_points"] = f32("surface_points.bin").reshape(-1, 11)
         if os.path.exists(os.path.join(d, "envmap.bin")):      # LightSource "infinite": its map and Distribution2D (ref_driver dumpLights)
             arrays["envmap"] = f32("envmap.bin")
     path = os.path.join(OUT, name + ".npz")
@@ -330,4 +332,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex", "skin_bump") else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex", "skin_bump", "skin_poisson") else scene_golden(w)

@@ -152,7 +152,7 @@ def test_shape_parameters_override_material_parameters(pkg, tmp_path):
     (scene_text(mat='"bool doublerefsslf" "true"'), "doublerefsslf"),
     (scene_text(mat='"bool usemontecarlo" "true"'), "usemontecarlo"),
     (scene_text(mat='"bool genprofile" "false"'), "genprofile"),
-    (scene_text('SurfaceIntegrator "multipolesubsurface" "bool usepoissonpointfinder" "true"'), "usepoissonpointfinder"),
+    (scene_text('SurfaceIntegrator "multipolesubsurface" "bool showirradiancepoints" "true"'), "showirradiancepoints"),
     (scene_text('Renderer "metropolis"\nSurfaceIntegrator "multipolesubsurface"'), 'Renderer "metropolis"'),
     (scene_text(world=LIGHT + 'Shape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]'), 'Material "matte"'),
     (scene_text(world=LIGHT + 'Material "layeredskin"\nShape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]'), "No layers"),
