@@ -43,7 +43,7 @@ int main(int argc, char *argv[]) {
         std::vector<float> rgb;
         skin::RenderStats st = {};
         std::string err;
-        if (sd.rendererName == "tessellatesurfacepoints") {
+        if (sd.rendererName == "tessellatesurfacepoints" || sd.rendererName == "surfacepoints") {
             uint64_t n = 0;
             if (!skin::TessellateSurfacePointsToFile(ctx, sd, &n, &err)) { fprintf(stderr, "Error: %s: %s\n", f.c_str(), err.c_str()); rc = 1; continue; }
             if (!quiet) printf("Obtained %llu surface points%s%s\n", (unsigned long long)n, sd.rendererFilename.empty() ? ". (Not writing to file)" : ", writing to file ",

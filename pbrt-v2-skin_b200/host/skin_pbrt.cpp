@@ -601,17 +601,17 @@ bool Front::statement(const std::string &id) {
     }
     if (id == "Renderer") {
         if (!named("Renderer") || !needOptions("Renderer")) return false;
-        if (name == "tessellatesurfacepoints") {              // CreateTessellateSurfacePointsRenderer, renderers/surfacepoints.cpp:381-388
+        if (name == "tessellatesurfacepoints" || name == "surfacepoints") {      // CreateTessellateSurfacePointsRenderer / CreateSurfacePointsRenderer, renderers/surfacepoints.cpp:372-388
             sd->rendererName = name;
             sd->rendererMinDist = ps.FindOneFloat("minsampledistance", .25f);
             sd->rendererFilename = ps.FindOneString("filename", "");
             if (!sd->rendererFilename.empty()) sd->rendererFilename = resolve(sd->rendererFilename);
-            if (options.quickRender) sd->rendererMinDist *= 4.f;
+            if (options.quickRender) { sd->rendererMinDist *= 4.f; sd->poissonMaxFails = std::max(10, 2000 / 10); }
             haveIntegrator = true;                            // this renderer never calls the surface integrator
             reportUnused(ps, "Renderer");
             return true;
         }
-        if (name != "sampler") { Error("Renderer \"%s\": only \"sampler\" and \"tessellatesurfacepoints\" are supported on the device path", name.c_str()); return false; }
+        if (name != "sampler") { Error("Renderer \"%s\": only \"sampler\", \"tessellatesurfacepoints\" and \"surfacepoints\" are supported on the device path", name.c_str()); return false; }
         if (ps.FindOneBool("visualizeobjectids", false)) { Error("Renderer \"visualizeobjectids\" is not supported on the device path"); return false; }
         sd->rendererName = name;
         return true;

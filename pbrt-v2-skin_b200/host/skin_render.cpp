@@ -217,11 +217,28 @@ bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *
     BuiltScene built;
     if (!BuildScene(sd, nullptr, &built, err)) return false;
     uint64_t n = 0;
-    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || UploadAlpha(ctx, built.mesh->alpha) || UploadBumpTexture(ctx, sd.skin.bumpTex) || skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
+    if (UploadScene(ctx, built) || UploadEnvMap(ctx, sd.env) || UploadAlpha(ctx, built.mesh->alpha) || UploadBumpTexture(ctx, sd.skin.bumpTex)) { *err = skc_last_error(ctx); return false; }
+    const bool poisson = sd.rendererName == "surfacepoints";                 // SurfacePointsRenderer (the Poisson finder) instead of the tessellator
+    if (poisson) {
+        const PerspectiveCameraDesc cam = sd.Camera();
+        const float *m = cam.CameraToWorld.m.m[0];
+        const float origin[3] = {m[3], m[7], m[11]};                         // pCamera = CameraToWorld(shutterOpen, Point(0, 0, 0)), core/api.cpp:1256
+        if (skc_poisson_resident(ctx, origin, sd.rendererMinDist, built.mesh->materialId, sd.poissonMaxFails, &n, nullptr)) { *err = skc_last_error(ctx); return false; }
+    } else if (skc_tessellate_resident(ctx, sd.rendererMinDist, 0, built.mesh->materialId, &n)) { *err = skc_last_error(ctx); return false; }
     *nPoints = n;
     if (sd.rendererFilename.empty()) return true;                            // "(Not writing to file)"
     std::vector<skc_surface_point> pts(n);
     if (n && skc_get_surface_points(ctx, 0, n, pts.data())) { *err = skc_last_error(ctx); return false; }
+    if (poisson) {                                                           // the text file of SurfacePointsRenderer::Render (surfacepoints.cpp:150-166)
+        FILE *f = fopen(sd.rendererFilename.c_str(), "w");
+        if (!f) { *err = "Unable to open output file \"" + sd.rendererFilename + "\""; return false; }
+        fprintf(f, "# points generated by SurfacePointsRenderer\n");
+        fprintf(f, "# position (x,y,z), normal (x,y,z), area, rayEpsilon\n");
+        for (const skc_surface_point &sp : pts)
+            fprintf(f, "%g %g %g %g %g %g %g %g\n", sp.p[0], sp.p[1], sp.p[2], sp.n[0], sp.n[1], sp.n[2], sp.area, sp.rayEpsilon);
+        fclose(f);
+        return true;
+    }
     FILE *f = fopen(sd.rendererFilename.c_str(), "wb");
     if (!f) { *err = "Unable to open output file \"" + sd.rendererFilename + "\""; return false; }
     bool ok = fwrite(pts.data(), sizeof(skc_surface_point), pts.size(), f) == pts.size();
@@ -283,7 +300,7 @@ int skh_pbrt_render(const char *scenePath, int device, int nCores, int quick, co
     if (!rgbOut && !writeImage) return 0;
     skc_ctx *ctx = skc_create(device);
     if (!ctx) return fail(std::string("skc_create: ") + skc_last_error(nullptr));
-    if (sd.rendererName == "tessellatesurfacepoints") {
+    if (sd.rendererName == "tessellatesurfacepoints" || sd.rendererName == "surfacepoints") {
         uint64_t n = 0;
         std::string e;
         bool ok = TessellateSurfacePointsToFile(ctx, sd, &n, &e);

@@ -84,3 +84,30 @@ def test_poisson_points_irradiance_and_frame(pkg, golden):
     finally:
         hs.close()
         dev.close()
+
+
+@pytest.mark.gpu
+def test_surfacepoints_renderer_and_pbrt_executable(pkg, golden, tmp_path):
+    """`Renderer "surfacepoints" "string filename"` writes the text file of SurfacePointsRenderer::Render (surfacepoints.cpp:150-166:
+    two comment lines, then position, normal, area, rayEpsilon with %g) -- the golden's points printed the same way -- and
+    `pbrt scenes/skin_poisson.pbrt` renders the reference's image from the finder's points."""
+    import subprocess
+    z, meta = golden
+    exe = os.path.join(ROOT, "pbrt-v2-skin_b200", "pbrt")
+    src = open(os.path.join(ROOT, "scenes", "skin_poisson.pbrt")).read()
+    src = src.replace('Include "geometry/head.pbrt"', 'Include "%s"' % os.path.join(ROOT, "scenes", "geometry", "head.pbrt"))
+    a = src.replace('SurfaceIntegrator "multipolesubsurface"', 'Renderer "surfacepoints" "float minsampledistance" 0.1 "string filename" "pts.txt"\nSurfaceIntegrator "multipolesubsurface"')
+    (tmp_path / "points.pbrt").write_text(a)
+    r = subprocess.run([exe, "--ncores", "1", str(tmp_path / "points.pbrt")], cwd=str(tmp_path), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    ref = z["surface_points"]
+    assert "Obtained %d surface points" % len(ref) in r.stdout
+    lines = open(tmp_path / "pts.txt").read().splitlines()
+    assert lines[0] == "# points generated by SurfacePointsRenderer" and lines[1] == "# position (x,y,z), normal (x,y,z), area, rayEpsilon"
+    want = ["%g %g %g %g %g %g %g %g" % tuple(float(v) for v in np.r_[p[:6], p[9:11]]) for p in ref]
+    assert lines[2:] == want
+    img, st = pkg.pbrt_render(os.path.join(ROOT, "scenes", "skin_poisson.pbrt"), n_cores=1)
+    assert st["points"] == len(ref)
+    for c in range(3):
+        rmse = np.sqrt(np.mean((img[..., c] - z["image"][..., c]) ** 2)); s = np.sqrt(np.mean(z["image"][..., c] ** 2))
+        assert rmse < 1e-3 * s
