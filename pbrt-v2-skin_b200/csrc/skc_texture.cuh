@@ -22,54 +22,60 @@ __device__ inline f3 texBilinear(const AlbedoTexDev &T, int level, float s, floa
     const float wa = (1.f - ds) * (1.f - dt), wb = (1.f - ds) * dt, wc = ds * (1.f - dt), wd = ds * dt;
     return mk3(a.x * wa + b.x * wb + c.x * wc + d.x * wd, a.y * wa + b.y * wb + c.y * wc + d.y * wd, a.z * wa + b.z * wb + c.z * wc + d.z * wd);
 }
-__device__ inline f3 texEWA(const AlbedoTexDev &T, int level, float s, float t, float ds0, float dt0, float ds1, float dt1) {
+// The elliptical weighted average of one pyramid level (core/mipmap.h:312-365).  The footprint's two axes (ax, ay) and (bx, by), in
+// texels of the level, give the quadric q(dx, dy) = qxx dx^2 + qxy dx dy + qyy dy^2 (normalised so that q = 1 is the ellipse); texels
+// with q < 1 inside its bounding box are weighted by the 128-entry table of exp(-2 q) - exp(-2).  Same operations in the same order
+// as the reference, so the filtered value is the reference's bit for bit.
+struct EwaQuadric { float qxx, qxy, qyy; };
+__device__ __forceinline__ EwaQuadric ewaQuadric(float ax, float ay, float bx, float by) {
+    EwaQuadric q;
+    q.qxx = ay * ay + by * by + 1;
+    q.qxy = -2.f * (ax * ay + bx * by);
+    q.qyy = ax * ax + bx * bx + 1;
+    const float norm = 1.f / (q.qxx * q.qyy - q.qxy * q.qxy * 0.25f);
+    q.qxx *= norm; q.qxy *= norm; q.qyy *= norm;
+    return q;
+}
+__device__ inline f3 texEWA(const AlbedoTexDev &T, int level, float s, float t, float ax, float ay, float bx, float by) {
     if (level >= T.nLevels) return texTexel(T, T.nLevels - 1, 0, 0);
-    const float us = (float)T.w[level], vs = (float)T.h[level];
-    s = s * us - 0.5f;
-    t = t * vs - 0.5f;
-    ds0 *= us; dt0 *= vs; ds1 *= us; dt1 *= vs;
-    float A = dt0 * dt0 + dt1 * dt1 + 1;
-    float B = -2.f * (ds0 * dt0 + ds1 * dt1);
-    float C = ds0 * ds0 + ds1 * ds1 + 1;
-    const float invF = 1.f / (A * C - B * B * 0.25f);
-    A *= invF; B *= invF; C *= invF;
-    const float det = -B * B + 4.f * A * C;
-    const float invDet = 1.f / det;
-    const float uSqrt = sqrtf(det * C), vSqrt = sqrtf(A * det);
-    const int s0 = (int)ceilf(s - 2.f * invDet * uSqrt), s1 = (int)floorf(s + 2.f * invDet * uSqrt);
-    const int t0 = (int)ceilf(t - 2.f * invDet * vSqrt), t1 = (int)floorf(t + 2.f * invDet * vSqrt);
-    f3 sum = mk3(0.f, 0.f, 0.f);
-    float sumWts = 0.f;
-    for (int it = t0; it <= t1; ++it) {
-        const float tt = (float)it - t;
-        for (int is = s0; is <= s1; ++is) {
-            const float ss = (float)is - s;
-            const float r2 = A * ss * ss + B * ss * tt + C * tt * tt;
-            if (r2 < 1.) {
-                const float weight = __ldg(&T.lut[min((int)(r2 * 128), 127)]);
-                sum = texAxpy(sum, weight, texTexel(T, level, is, it));
-                sumWts += weight;
-            }
+    const float wTex = (float)T.w[level], hTex = (float)T.h[level];
+    const float cx = s * wTex - 0.5f, cy = t * hTex - 0.5f;                  // the lookup point in texel coordinates
+    const EwaQuadric q = ewaQuadric(ax * wTex, ay * hTex, bx * wTex, by * hTex);
+    const float disc = -q.qxy * q.qxy + 4.f * q.qxx * q.qyy, rcpDisc = 1.f / disc;
+    const float halfX = 2.f * rcpDisc * sqrtf(disc * q.qyy), halfY = 2.f * rcpDisc * sqrtf(q.qxx * disc);
+    const int xLo = (int)ceilf(cx - halfX), xHi = (int)floorf(cx + halfX), yLo = (int)ceilf(cy - halfY), yHi = (int)floorf(cy + halfY);
+    f3 acc = mk3(0.f, 0.f, 0.f);
+    float wSum = 0.f;
+    for (int y = yLo; y <= yHi; ++y) {
+        const float dy = (float)y - cy;
+        for (int x = xLo; x <= xHi; ++x) {
+            const float dx = (float)x - cx;
+            const float r2 = q.qxx * dx * dx + q.qxy * dx * dy + q.qyy * dy * dy;
+            if (!(r2 < 1.)) continue;
+            const float wgt = __ldg(&T.lut[min((int)(r2 * 128), 127)]);
+            acc = texAxpy(acc, wgt, texTexel(T, level, x, y));
+            wSum += wgt;
         }
     }
-    return mk3(sum.x / sumWts, sum.y / sumWts, sum.z / sumWts);
+    return mk3(acc.x / wSum, acc.y / wSum, acc.z / wSum);
 }
-// MIPMap::Lookup(s, t, ds0, dt0, ds1, dt1), EWA
-__device__ inline f3 texLookup(const AlbedoTexDev &T, float s, float t, float ds0, float dt0, float ds1, float dt1) {
-    if (ds0 * ds0 + dt0 * dt0 < ds1 * ds1 + dt1 * dt1) { float x = ds0; ds0 = ds1; ds1 = x; x = dt0; dt0 = dt1; dt1 = x; }
-    const float majorLength = sqrtf(ds0 * ds0 + dt0 * dt0);
-    float minorLength = sqrtf(ds1 * ds1 + dt1 * dt1);
-    if (minorLength * 8.f < majorLength && minorLength > 0.f) {
-        const float scale = majorLength / (minorLength * 8.f);
-        ds1 *= scale; dt1 *= scale; minorLength *= scale;
+// MIPMap::Lookup(s, t, ds0, dt0, ds1, dt1) with the EWA filter (core/mipmap.h:277-309): the longer of the two footprint vectors is the
+// major axis; the minor one is lengthened until the anisotropy is at most 8; its length picks the two levels that are blended.
+__device__ inline f3 texLookup(const AlbedoTexDev &T, float s, float t, float ax, float ay, float bx, float by) {
+    if (ax * ax + ay * ay < bx * bx + by * by) { float x = ax; ax = bx; bx = x; x = ay; ay = by; by = x; }
+    const float lenMajor = sqrtf(ax * ax + ay * ay);
+    float lenMinor = sqrtf(bx * bx + by * by);
+    if (lenMinor * 8.f < lenMajor && lenMinor > 0.f) {
+        const float stretch = lenMajor / (lenMinor * 8.f);
+        bx *= stretch; by *= stretch; lenMinor *= stretch;
     }
-    if (minorLength == 0.f) return texBilinear(T, 0, s, t);
-    const float invLog2 = 1.f / skc_logf(2.f);
-    const float lod = fmaxf(0.f, (float)T.nLevels - 1.f + skc_logf(minorLength) * invLog2);
-    const int ilod = (int)floorf(lod);
-    const float d = lod - (float)ilod;
-    const f3 a = texEWA(T, ilod, s, t, ds0, dt0, ds1, dt1), b = texEWA(T, ilod + 1, s, t, ds0, dt0, ds1, dt1);
-    return mk3(a.x * (1.f - d) + b.x * d, a.y * (1.f - d) + b.y * d, a.z * (1.f - d) + b.z * d);
+    if (lenMinor == 0.f) return texBilinear(T, 0, s, t);
+    const float rcpLn2 = 1.f / skc_logf(2.f);                               // Log2(x) = logf(x) * (1.f / logf(2.f)), core/pbrt.h
+    const float lod = fmaxf(0.f, (float)T.nLevels - 1.f + skc_logf(lenMinor) * rcpLn2);
+    const int fine = (int)floorf(lod);
+    const float blend = lod - (float)fine;
+    const f3 lo = texEWA(T, fine, s, t, ax, ay, bx, by), hi = texEWA(T, fine + 1, s, t, ax, ay, bx, by);
+    return mk3(lo.x * (1.f - blend) + hi.x * blend, lo.y * (1.f - blend) + hi.y * blend, lo.z * (1.f - blend) + hi.z * blend);
 }
 // Spectrum::FromRGB(rgb, SPECTRUM_REFLECTANCE)[lane] (core/spectrum.cpp:103-145); refl = [7][32] white, cyan, magenta, yellow, red, green, blue
 __device__ __forceinline__ float texReflectance(const float *__restrict__ refl, float r, float g, float b, int lane) {
