@@ -1,6 +1,8 @@
 // skc_mo_table.cu -- host-side builder and verifier of the compact Rd table (skc_mo_table.h).
 #include <algorithm>
 #include <cstring>
+#include <atomic>
+#include <thread>
 #include "skc_mo_table.h"
 #include "../../include/skin_cuda.h"
 
@@ -30,9 +32,12 @@ bool mocBuild(const float *table, const float *rcp, uint32_t len, float tol, int
     bool any = false;
     uint32_t headUsed = 0;
     double covSum = 0.0;
-    std::vector<double> v(K + 3);
     for (int l = 0; l < 32; ++l) { C.headOff[l] = 0; C.headLen[l] = 0; C.fLo[l] = 0.f; C.fHi[l] = 0.f; C.maxErr[l] = 0.f; }
-    for (int l = 0; l < SKC_NSPECTRAL; ++l) {
+    // the wavelengths are independent (each owns one column of C.rows and its own window): rows and verification on worker threads,
+    // then the shared-memory heads are handed out in wavelength order
+    bool haveWindow[32] = {false};
+    auto oneWavelength = [&](int l) {
+        std::vector<double> v(K + 3);
         const float *data = table + (size_t)l * len;
         const double r = (double)rcp[l];
         // the last table segment may fall to a 0 end marker: sample the rows from the segments before it
@@ -48,7 +53,7 @@ bool mocBuild(const float *table, const float *rcp, uint32_t len, float tol, int
                 hi = i;
             }
         }
-        if (lo < 0 || hi - lo < 4) continue;
+        if (lo < 0 || hi - lo < 4) return;
         // rows outside the table's own range continue the cubic through the last four inside it
         for (int i = lo - 1; i >= 0; --i) v[i] = 4 * v[i + 1] - 6 * v[i + 2] + 4 * v[i + 3] - v[i + 4];
         for (int i = hi + 1; i < K + 3; ++i) v[i] = 4 * v[i - 1] - 6 * v[i - 2] + 4 * v[i - 3] - v[i - 4];
@@ -79,10 +84,25 @@ bool mocBuild(const float *table, const float *rcp, uint32_t len, float tol, int
             if (stop) break;
         }
         closeRun();
-        if (bestHi - bestLo < 64.0) continue;                     // not worth a window
+        if (bestHi - bestLo < 64.0) return;                       // not worth a window
         // one segment of margin either side
         float fLo = bestLo <= 0.0 ? 0.f : (float)ceil(bestLo + 1.0), fHi = (float)floor(bestHi - 1.0);
         C.fLo[l] = fLo; C.fHi[l] = fHi; C.maxErr[l] = (float)bestMax;
+        haveWindow[l] = true;
+    };
+    {
+        std::atomic<int> next(0);
+        auto work = [&]() { for (int l = next.fetch_add(1); l < SKC_NSPECTRAL; l = next.fetch_add(1)) oneWavelength(l); };
+        unsigned nThreads = std::min(std::max(std::thread::hardware_concurrency(), 1u), (unsigned)SKC_NSPECTRAL);
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nThreads; ++t) pool.emplace_back(work);
+        work();
+        for (std::thread &t : pool) t.join();
+    }
+    for (int l = 0; l < SKC_NSPECTRAL; ++l) {
+        if (!haveWindow[l]) continue;
+        const float *data = table + (size_t)l * len;
+        const float fLo = C.fLo[l], fHi = C.fHi[l];
         any = true;
         // head of the exact table below the window, in shared memory as far as the budget goes
         uint32_t want = (uint32_t)fLo;
