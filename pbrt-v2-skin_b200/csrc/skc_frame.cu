@@ -742,7 +742,17 @@ extern "C" int skc_frame_setup(skc_ctx *ctx, const skc_frame_desc *d, uint64_t *
                 keyed[f->pixBase[t] + k] = std::make_pair(part1by1(x) | (part1by1(y) << 1), f->pixBase[t] + k);
             }
         }
-        std::sort(keyed.begin(), keyed.end());
+        // the keys are distinct (one per film position): two stable 16-bit counting passes give the sorted order (std::sort of the
+        // 0.9 M pairs of a 1280x720 film took 35 ms of every skc_frame_setup)
+        std::vector<std::pair<uint32_t, uint32_t>> tmp(keyed.size());
+        for (int pass = 0; pass < 2; ++pass) {
+            std::vector<uint32_t> start(65537, 0u);
+            const int shift = 16 * pass;
+            for (const auto &e : keyed) ++start[((e.first >> shift) & 0xffffu) + 1];
+            for (int b = 0; b < 65536; ++b) start[b + 1] += start[b];
+            for (const auto &e : keyed) tmp[start[(e.first >> shift) & 0xffffu]++] = e;
+            keyed.swap(tmp);
+        }
         for (size_t k = 0; k < keyed.size(); ++k) order[k] = keyed[k].second;
     }
     f->nSamples = f->nPixels * L.spp;
