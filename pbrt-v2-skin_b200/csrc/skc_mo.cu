@@ -650,11 +650,13 @@ extern "C" int skc_upload_profile(skc_ctx *ctx, const float *table, const float 
                 pairs[(size_t)l * len + i] = make_float2(table[(size_t)l * len + i], i + 1 < len ? table[(size_t)l * len + i + 1] : 0.f);
         float rcp[32]; float rmin = INFINITY;
         for (int l = 0; l < 32; ++l) { rcp[l] = l < SKC_NS ? rcpDsqSpacing[l] : rcpDsqSpacing[SKC_NS - 1]; if (l < SKC_NS) rmin = fminf(rmin, rcp[l]); }
-        if (ctx->profPairs) cudaFree(ctx->profPairs);
-        if (ctx->profRcp) cudaFree(ctx->profRcp);
-        ctx->profPairs = nullptr; ctx->profRcp = nullptr;
-        SKC_CUDA(cudaMalloc((void **)&ctx->profPairs, pairs.size() * sizeof(float2)));
-        SKC_CUDA(cudaMalloc((void **)&ctx->profRcp, sizeof rcp));
+        if (!ctx->profPairs || !ctx->profRcp || ctx->profLen != len) {      // a table of the same length goes into the arrays that are there
+            if (ctx->profPairs) cudaFree(ctx->profPairs);
+            if (ctx->profRcp) cudaFree(ctx->profRcp);
+            ctx->profPairs = nullptr; ctx->profRcp = nullptr; ctx->profLen = 0;
+            SKC_CUDA(cudaMalloc((void **)&ctx->profPairs, pairs.size() * sizeof(float2)));
+            SKC_CUDA(cudaMalloc((void **)&ctx->profRcp, sizeof rcp));
+        }
         SKC_CUDA(cudaMemcpyAsync(ctx->profPairs, pairs.data(), pairs.size() * sizeof(float2), cudaMemcpyHostToDevice, ctx->stream));
         SKC_CUDA(cudaMemcpyAsync(ctx->profRcp, rcp, sizeof rcp, cudaMemcpyHostToDevice, ctx->stream));
         SKC_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -719,14 +721,17 @@ __global__ void __launch_bounds__(256) k_mo_sort_keys(const float *__restrict__ 
 // renders its samples along a Z-curve over the film; callers of skc_mo / skc_li_sss / skc_camera_pass* own the order of
 // their points, so those are sorted here along a Morton curve through the octree's bounds (one 32-bit radix sort) and the
 // kernel reads and writes through the permutation -- results land at the caller's indices, bit-identical to the unsorted run.
-static const uint32_t *moSortHits(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride, uint64_t n) {
+// *failed: the sort was wanted and could not run (scratch allocation or launch error; skc_last_error says which) -- the caller fails
+// instead of silently running the kernel on unsorted points at a fraction of its speed
+static const uint32_t *moSortHits(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, const int32_t *enableDev, uint64_t enableStride, uint64_t n, bool *failed) {
+    *failed = false;
     if (n < 64 || n >= (1ull << 31)) return nullptr;
     size_t tempBytes = 0;
     cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
     cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, dk, dv, (int)n, 0, 31, ctx->stream);
     size_t arr = ((size_t)n * 4 + 255) & ~(size_t)255;
     char *buf = (char *)skc_scratch(ctx, 16, 4 * arr + tempBytes);
-    if (!buf) return nullptr;
+    if (!buf) { *failed = true; return nullptr; }
     dk = cub::DoubleBuffer<uint32_t>((uint32_t *)buf, (uint32_t *)(buf + arr));
     dv = cub::DoubleBuffer<uint32_t>((uint32_t *)(buf + 2 * arr), (uint32_t *)(buf + 3 * arr));
     const float *b = ctx->otBoundsHost;
@@ -735,7 +740,10 @@ static const uint32_t *moSortHits(skc_ctx *ctx, const float *p3Dev, uint64_t str
     float3 scale = make_float3(sc(b[0], b[3]), sc(b[1], b[4]), sc(b[2], b[5]));
     k_mo_sort_keys<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(p3Dev, strideFloats, enableDev, enableStride, (uint32_t)n, bmin, scale, dk.Current(), dv.Current());
     ctx->launches += 2;
-    if (cudaGetLastError() != cudaSuccess || cub::DeviceRadixSort::SortPairs(buf + 4 * arr, tempBytes, dk, dv, (int)n, 0, 31, ctx->stream) != cudaSuccess) return nullptr;
+    if (cudaGetLastError() != cudaSuccess || cub::DeviceRadixSort::SortPairs(buf + 4 * arr, tempBytes, dk, dv, (int)n, 0, 31, ctx->stream) != cudaSuccess) {
+        skc_fail(ctx, "skc_mo: sorting the hit points failed: %s", cudaGetErrorString(cudaGetLastError()));
+        *failed = true; return nullptr;
+    }
     return dv.Current();
 }
 
@@ -780,7 +788,9 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
         if (!next) return 1;
         SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
-        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n) : nullptr;
+        bool sortFailed = false;
+        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n, &sortFailed) : nullptr;
+        if (sortFailed) return 1;
 #define MOL_GO2(CNT, P, H, W) do { \
             SKC_CUDA(cudaFuncSetAttribute(k_mo_lambda<CNT, P, H, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
             k_mo_lambda<CNT, P, H, W><<<grid, warps * 32, smem, ctx->stream>>>(tr, T, C, p3Dev, strideFloats, enableDev, enableStride, n, maxError, MoDev, cntDev, ep, next, perm, packetHits); } while (0)
@@ -800,7 +810,9 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         uint32_t *next = (uint32_t *)skc_scratch(ctx, 6, 256);
         if (!next) return 1;
         SKC_CUDA(cudaMemsetAsync(next, 0, sizeof(uint32_t), ctx->stream));
-        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n) : nullptr;
+        bool sortFailed = false;
+        const uint32_t *perm = (ctx->moSort > 0 || (ctx->moSort < 0 && callerOrder)) ? moSortHits(ctx, p3Dev, strideFloats, enableDev, enableStride, n, &sortFailed) : nullptr;
+        if (sortFailed) return 1;
         // one warp per packet when there are plenty of packets per resident warp; two warps per packet (half the spectrum each)
         // when a launch is short (multi-GPU shards), where the heaviest packets' run time is what the launch waits for.
         // Measured on skin.scene: 28 packets/warp 60.4 vs 61.9 ms, 14 packets/warp 38.1 vs 35.7 ms, 3.5 packets/warp 23.0 vs 17.5 ms
