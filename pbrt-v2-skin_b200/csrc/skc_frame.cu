@@ -428,6 +428,7 @@ __device__ __forceinline__ float powerHeuristic(float fPdf, float gPdf) {   // c
 // terms[3t]   = BSDF factors of the light-sampling term (bsdfEvalLocal's comp; den = 0: term absent)
 // terms[3t+1] = {|wi.n| * weight / lightPdf of the light-sampling term;  |wi.n|, weight, bsdfPdf of the BSDF-sampling term}
 // terms[3t+2] = BSDF factors of the BSDF-sampling term (den = 0: absent)
+template <bool ENV>      // ENV: the scene has an infinite light (the instance without it is the benchmarked frame's: no map parameter, no branch)
 __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_light *__restrict__ lights, FrameLayout lay,
                                                      RhoBxdf mf, float ior, float kd, int hasR, int hasT,
                                                      const skc_hit *__restrict__ hits, const float4 *__restrict__ frame,
@@ -457,7 +458,7 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
         float bc = __ldg(A + lay.off1B[li] + j), bu0 = __ldg(A + lay.off2B[li] + 2 * j), bu1 = __ldg(A + lay.off2B[li] + 2 * j + 1);
         const skc_light &L = lights[li];
         const int kind = lightKind(L);
-        if (kind == 4) {
+        if (ENV && kind == 4) {
             // infinite light (lights/infinite.cpp): both MIS terms as for an emitter shape, but the radiance is the map's RGB in the
             // term's direction (termsEnv[2t], [2t+1]; k_frame_sum turns it into a spectrum), and the BSDF-sampled ray sees the
             // light only if it leaves the scene (integrator.cpp:144-148: `else Li = light->Le(ray)`)
@@ -879,8 +880,12 @@ static int frameHitsAndDirect(skc_ctx *ctx, skc_frame_state *f, uint64_t first, 
     for (int i = 0; i < SKC_NS; ++i) { hasR |= f->desc.Kr[i] != 0.f; hasT |= f->desc.Kt[i] != 0.f; }
     skc_stage_begin(ctx);
     uint64_t nThreads = count * lay.slots;
-    k_direct_terms<<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
-                                                                                dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms, ctx->env, dTermsEnv);
+    if (envLight >= 0)
+        k_direct_terms<true><<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
+                                                                                          dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms, ctx->env, dTermsEnv);
+    else
+        k_direct_terms<false><<<(unsigned)((nThreads + 127) / 128), 128, 0, ctx->stream>>>(skc_bvh_view(ctx), ctx->lights, lay, mf, f->desc.ior, f->desc.matteKd, hasR, hasT,
+                                                                                           dHits, dFrame, f->dArrays, f->dOrder, first, count, dTerms, EnvMapDev(), nullptr);
     SKC_LAUNCHED("k_direct_terms");
     if (dLdir) {
         k_direct_sum<<<(unsigned)((count + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, ctx->stream>>>(ctx->lights, lay, f->dConsts, dHits, dTerms, count, dLdir, dTermsEnv, ctx->env.illum);
