@@ -126,7 +126,15 @@ __global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__res
         float cosT = 0.f, pdf = 0.f;
         const int kind = DELTA ? lightKind(lights[j]) : 0;
         if (kind == 0) {
-            if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
+            // The whole emitter below the point's horizon: every point the sampler can return -- on the sphere (cone or uniform
+            // sampling) or, for a grazing ray that misses it numerically, within rounding of it -- gives Dot(wi, n) <= 0, so the
+            // sample is the reference's `continue` (multipolesubsurface.cpp:121) whatever (u0, u1) are: {0, 0}, no shadow ray.
+            // The margin (1 % of the radius + 1e-5 of the distance) is orders above the rounding of the sampled direction.
+            const f3 toCentre = sub3(xformPoint(lights[j].o2w, mk3(0.f, 0.f, 0.f)), p);
+            const float reach = fabsf(toCentre.x) + fabsf(toCentre.y) + fabsf(toCentre.z);
+            if (dot3(toCentre, n) <= -1.01f * lights[j].radius - 1e-5f * reach) {
+                // nothing to do
+            } else if (sampleSphereLight(lights[j], p, eps, n, u0, u1, &wi, &lp, &sh)) {
                 need = true;
                 cosT = fminf(fabsf(dot3(wi, n)), 1.f); pdf = lp;
             }
