@@ -195,6 +195,9 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
     const int lam = lane < SKC_NS ? lane : 0;
+    // the first two lights' emission at this lane's wavelength stays in registers for the warp's points
+    const float Lc0 = __ldg(&lights[0].Lemit[lam]), Lc1 = sl.nLights > 1 ? __ldg(&lights[1].Lemit[lam]) : 0.f;
+    const float rN0 = 1.f / (float)(int)sl.nS[0], rN1 = sl.nLights > 1 ? 1.f / (float)(int)sl.nS[1] : 0.f;
     for (uint32_t k = 0; k < IRR_SPECTRAL_POINTS; ++k) {
         uint32_t point = p0 + k;
         if (point >= nPts) return;
@@ -203,7 +206,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
         float E = 0.f;
         for (uint32_t j = 0; j < sl.nLights; ++j) {
             uint32_t nS = sl.nS[j];
-            float Lc = __ldg(&lights[j].Lemit[lam]);
+            float Lc = j < 2 ? (j == 0 ? Lc0 : Lc1) : __ldg(&lights[j].Lemit[lam]);
             float el = 0.f;
             const int kind = DELTA ? lightKind(lights[j]) : 0;
             float fall = 1.f;
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
             }
             cp += nS;
             if (ep) ep += nS;
-            E += el / (float)(int)nS;                    // :136
+            E += el * (j < 2 ? (j == 0 ? rN0 : rN1) : 1.f / (float)(int)nS);      // :136, `/ nSamples`: nS is a power of two (RoundUpPow2, :101), so the product with its reciprocal is the quotient
         }
         uint64_t pi = ptBase + point;
         float e = lane < SKC_NS ? E : 0.f;            // lanes 30,31 write the zero pad of the 128 B row
