@@ -195,6 +195,11 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
     uint32_t warpId = (blockIdx.x * 256 + threadIdx.x) >> 5;
     uint32_t p0 = warpId * IRR_SPECTRAL_POINTS;
     const int lam = lane < SKC_NS ? lane : 0;
+    // the per-light sample counts in shared memory: indexing the kernel parameter with the loop variable compiles to a
+    // 16-way select chain (40 instructions per point and light)
+    __shared__ uint32_t sNS[IRR_MAX_LIGHTS];
+    if (threadIdx.x < IRR_MAX_LIGHTS) sNS[threadIdx.x] = sl.nS[threadIdx.x];
+    __syncthreads();
     // the first two lights' emission at this lane's wavelength stays in registers for the warp's points
     const float Lc0 = __ldg(&lights[0].Lemit[lam]), Lc1 = sl.nLights > 1 ? __ldg(&lights[1].Lemit[lam]) : 0.f;
     const float rN0 = 1.f / (float)(int)sl.nS[0], rN1 = sl.nLights > 1 ? 1.f / (float)(int)sl.nS[1] : 0.f;
@@ -205,7 +210,7 @@ __global__ void __launch_bounds__(256) k_irr_spectral(const skc_light *__restric
         const float4 *ep = DELTA && envRgb ? envRgb + (size_t)point * sl.S : nullptr;      // per-sample RGB of the infinite light's samples
         float E = 0.f;
         for (uint32_t j = 0; j < sl.nLights; ++j) {
-            uint32_t nS = sl.nS[j];
+            uint32_t nS = sNS[j];
             float Lc = j < 2 ? (j == 0 ? Lc0 : Lc1) : __ldg(&lights[j].Lemit[lam]);
             float el = 0.f;
             const int kind = DELTA ? lightKind(lights[j]) : 0;
