@@ -525,7 +525,12 @@ __global__ void __launch_bounds__(128) k_direct_terms(BvhView bv, const skc_ligh
                 DRay ray; ray.o = p; ray.d = wi; ray.mint = eps; ray.maxt = INFINITY;
                 DRay r0 = ray;
                 float b1, b2;
-                int prim = bvhClosest<false>(bv, ray, &b1, &b2, nullptr);
+                // Li is the light's only if the closest hit IS the light (integrator.cpp:141-145).  A ray that misses the emitter
+                // sphere under the very test the traversal applies to it (same function, same record, a maxt that only shrinks
+                // there) cannot have it as its closest hit: the walk is skipped.  The lobe rarely points at a small emitter, so
+                // this removes nearly all closest-hit walks of the BSDF-sampling term.
+                float tLight;
+                int prim = sphereIntersect(L, r0, &tLight) ? bvhClosest<false>(bv, ray, &b1, &b2, nullptr) : -1;
                 bool emits = false;
                 if (prim >= 0) {
                     float4 c = __ldg(&bv.prims[3 * prim + 2]);
