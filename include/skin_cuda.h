@@ -366,7 +366,9 @@ int skc_frame_samples(skc_ctx *ctx);
 /* The part of the frame that does not depend on Preprocess -- skc_frame_samples, Scene::Intersect of every camera ray and
  * EstimateDirect's terms (core/integrator.cpp:108-155) -- enqueued on the context's second stream; returns without
  * waiting.  Call it before the Preprocess calls; skc_frame_render(ctx, 0, nSamples, ...) then picks the results up on
- * the device.  Replaces skc_frame_samples in that flow; results are bit-identical to the staged calls. */
+ * the device.  Replaces skc_frame_samples in that flow; results are bit-identical to the staged calls.  One difference a
+ * caller of skc_frame_get_samples can see: on this path the integrator's sample arrays are generated only for pixels with at
+ * least one camera ray that hits something (nothing reads the others; image samples and rays are complete). */
 int skc_frame_prefetch(skc_ctx *ctx);
 /* Test access: image positions [count][2], the 1-D/2-D arrays of each sample [count][floatsPerSample]
  * (every 1-D array, then every 2-D array, as Sample::oneD / twoD) and the rays.  Any output may be NULL. */

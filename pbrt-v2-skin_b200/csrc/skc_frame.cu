@@ -69,6 +69,7 @@ struct skc_frame_state {
     bool samplesReady = false;
     // skc_frame_prefetch: the part of the frame that does not depend on Preprocess, enqueued on prefetchStream
     bool prefetched = false;
+    bool lazyArrays = false;            // skc_frame_prefetch: no integrator arrays for pixels whose camera rays all miss (k_ld_pixel)
     cudaEvent_t evP0 = nullptr, evP1 = nullptr, evDone = nullptr, evHits = nullptr;   // evHits: closest hits done (what Mo needs); evP1: direct terms done (what the spectral sum needs)
 };
 
@@ -152,7 +153,7 @@ __device__ inline void ldScrambled2D(uint32_t nSamples, uint32_t nPixel, float *
 // LDPixelSample (core/montecarlo.cpp:200-252) for one pixel per thread
 __global__ void __launch_bounds__(128) k_ld_pixel(FrameLayout lay, const int4 *__restrict__ win, const uint32_t *__restrict__ pixBase,
                                                  uint32_t nTasks, const uint32_t *__restrict__ words, const uint64_t *__restrict__ pixOff,
-                                                 float2 *__restrict__ xy, float *__restrict__ arrays) {
+                                                 float2 *__restrict__ xy, float *__restrict__ arrays, int skipUnhit) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= pixBase[nTasks]) return;
     uint32_t lo = 0, hi = nTasks - 1;
@@ -167,6 +168,10 @@ __global__ void __launch_bounds__(128) k_ld_pixel(FrameLayout lay, const int4 *_
     uint64_t s0 = (uint64_t)g * spp;
     ldScrambled2D(1, spp, buf, r, ri);                               // image samples
     for (uint32_t i = 0; i < spp; ++i) xy[s0 + i] = make_float2((float)xPos + buf[2 * i], (float)yPos + buf[2 * i + 1]);
+    // The integrator's arrays of a pixel are read only for camera rays that hit something (EstimateDirect).  k_ld_chain already
+    // knows which pixels those are -- every hit moves the next pixel's start by 6 words -- so on the prefetch path the arrays of
+    // pixels without a hit are not generated (their words are still accounted for: the offsets come from the chain).
+    if (skipUnhit && g + 1 < pixBase[lo + 1] && pixOff[g + 1] - pixOff[g] == (uint64_t)lay.draws) return;
     ldScrambled2D(1, spp, buf, r, ri);                               // lens samples (pinhole: unused)
     ldScrambled1D(1, spp, buf, r, ri);                               // time samples (shutter 0..0: unused)
     float *out = arrays + s0 * lay.floats;
@@ -822,7 +827,7 @@ extern "C" int skc_frame_samples(skc_ctx *ctx) {
     if (chainSmem > 48 * 1024) SKC_CUDA(cudaFuncSetAttribute(k_ld_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)chainSmem));
     k_ld_chain<<<nT, LC_THREADS, chainSmem, ctx->stream>>>(skc_bvh_view(ctx), f->dConsts, f->lay, f->dWin, f->dPixBase, cap, dWords, dPixOff, f->dXY);
     SKC_LAUNCHED("k_ld_chain");
-    k_ld_pixel<<<(unsigned)((f->nPixels + 127) / 128), 128, 0, ctx->stream>>>(f->lay, f->dWin, f->dPixBase, nT, dWords, dPixOff, f->dXY, f->dArrays);
+    k_ld_pixel<<<(unsigned)((f->nPixels + 127) / 128), 128, 0, ctx->stream>>>(f->lay, f->dWin, f->dPixBase, nT, dWords, dPixOff, f->dXY, f->dArrays, f->lazyArrays ? 1 : 0);
     SKC_LAUNCHED("k_ld_pixel");
     k_camera_rays<<<(unsigned)((f->nSamples + 255) / 256), 256, 0, ctx->stream>>>(f->dConsts, f->dXY, f->nSamples, f->dOrder, f->lay.spp, ctx->resRays);
     SKC_LAUNCHED("k_camera_rays");
@@ -925,7 +930,9 @@ extern "C" int skc_frame_prefetch(skc_ctx *ctx) {
     cudaStream_t mainStream = ctx->stream;
     ctx->stream = ctx->prefetchStream; ctx->stageOff = true;
     cudaEventRecord(f->evP0, ctx->stream);
+    f->lazyArrays = !getenv("SKC_EAGER_ARRAYS");
     int rc = skc_frame_samples(ctx);
+    f->lazyArrays = false;
     if (!rc) rc = frameHitsAndDirect(ctx, f, 0, count, dHits, dFrame, dTerms, f->evHits, dLdir);
     cudaEventRecord(f->evP1, ctx->stream);
     ctx->stream = mainStream; ctx->stageOff = false;
