@@ -623,6 +623,28 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_frame_sum(BvhView bv, const s
     if (s >= n) return;
     const float *hp = reinterpret_cast<const float *>(hits + s);
     float Lc = 0.f;
+    if (!__float_as_int(__ldg(hp)) && envLight < 0) {
+        // A camera ray that leaves a scene without an infinite light: L = 0 exactly, so the sanity checks pass, XYZ = 0, and
+        // AddSample adds wt * 0 to the pixel's X, Y, Z (no change to any float) and wt to its weight sum -- only that is done.
+        if (lane < SKC_NS) Lrows[s * SKC_NS + lane] = 0.f;
+        if (lane == 0) {
+            float2 p = xy[renderToStream(order, lay.spp, first + s)];
+            float dimageX = p.x - 0.5f, dimageY = p.y - 0.5f;
+            int x0 = (int)ceilf(dimageX - C->filterXWidth), x1 = (int)floorf(dimageX + C->filterXWidth);
+            int y0 = (int)ceilf(dimageY - C->filterYWidth), y1 = (int)floorf(dimageY + C->filterYWidth);
+            x0 = max(x0, 0); x1 = min(x1, C->xres - 1); y0 = max(y0, 0); y1 = min(y1, C->yres - 1);
+            for (int yy2 = y0; yy2 <= y1; ++yy2) {
+                float fy = fabsf((yy2 - dimageY) * C->invYWidth * 16);
+                int iy = min((int)floorf(fy), 15);
+                for (int xx = x0; xx <= x1; ++xx) {
+                    float fx = fabsf((xx - dimageX) * C->invXWidth * 16);
+                    int ix = min((int)floorf(fx), 15);
+                    atomicAdd(reinterpret_cast<float *>(film + (size_t)yy2 * C->xres + xx) + 3, C->filterTable[iy * 16 + ix]);
+                }
+            }
+        }
+        return;
+    }
     if (__float_as_int(__ldg(hp)) && lane < SKC_NS) {
         int prim = __float_as_int(__ldg(hp + 1));
         float4 c = __ldg(&bv.prims[3 * prim + 2]);
