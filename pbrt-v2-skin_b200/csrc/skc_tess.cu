@@ -100,15 +100,13 @@ template <bool BUMP> __host__ __device__ inline void tessMatching(const TessEmit
         TessBC bOuter = bcLerp((float)outerPos / (float)segsOuter, b0Outer, b1Outer);
         float slopeInner = (innerPos < segsInner) ? fabsf((float)(innerPos + 1) + 1.f - (float)outerPos / (float)segsOuter * (float)(segsInner + 2)) : INFINITY;
         float slopeOuter = (outerPos < segsOuter) ? fabsf((float)innerPos + 1.f - (float)(outerPos + 1) / (float)segsOuter * (float)(segsInner + 2)) : INFINITY;
-        if (slopeInner < slopeOuter) {
-            TessBC bInnerNew = bcLerp((float)(innerPos + 1) / (float)segsInner, b0Inner, b1Inner);
-            tessPoint<BUMP>(e, bInnerNew, bInner, bOuter, slot++);
-            innerPos++;
-        } else {
-            TessBC bOuterNew = bcLerp((float)(outerPos + 1) / (float)segsOuter, b0Outer, b1Outer);
-            tessPoint<BUMP>(e, bInner, bOuter, bOuterNew, slot++);
-            outerPos++;
-        }
+        // one call site for the two cases (a warp whose lanes disagree would otherwise run the domain shader twice): the new vertex
+        // is on the inner edge -> sub-triangle (new, inner, outer), else on the outer edge -> (inner, outer, new)
+        const bool stepInner = slopeInner < slopeOuter;
+        const TessBC bNew = bcLerp(stepInner ? (float)(innerPos + 1) / (float)segsInner : (float)(outerPos + 1) / (float)segsOuter,
+                                   stepInner ? b0Inner : b0Outer, stepInner ? b1Inner : b1Outer);
+        tessPoint<BUMP>(e, stepInner ? bNew : bInner, stepInner ? bInner : bOuter, stepInner ? bOuter : bNew, slot++);
+        if (stepInner) innerPos++; else outerPos++;
     }
 }
 
