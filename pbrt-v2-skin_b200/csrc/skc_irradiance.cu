@@ -95,7 +95,7 @@ struct IrrSlots { uint32_t nLights, S; uint32_t nS[IRR_MAX_LIGHTS]; };   // S = 
 
 // DELTA: the scene has point / spot / distant lights (row N4); without them the instance is the sphere-emitter code alone
 template <bool COUNT, bool DELTA>
-__global__ void __launch_bounds__(IRR_BLOCK) k_irr_sample(const skc_light *__restrict__ lights, IrrSlots sl,
+__global__ void __launch_bounds__(IRR_BLOCK, 4) k_irr_sample(const skc_light *__restrict__ lights, IrrSlots sl,
         const skc_surface_point *__restrict__ pts, const uint32_t *__restrict__ scr, uint64_t ptBase, uint32_t nPts,
         float2 *__restrict__ cosPdf, float4 *__restrict__ rayO, float4 *__restrict__ rayD, uint32_t *__restrict__ rayTarget,
         uint32_t *__restrict__ nRays, float4 *__restrict__ posArea, uint64_t outBase, unsigned long long *cnt, EnvMapDev env, float4 *__restrict__ envRgb) {
