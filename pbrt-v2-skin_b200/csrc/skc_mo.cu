@@ -773,6 +773,10 @@ static int moLaunch(skc_ctx *ctx, const float *p3Dev, uint64_t strideFloats, con
         const size_t tableBytes = ((size_t)C.rowFloats + C.headFloats) * sizeof(float);
         int warps = (int)std::min<size_t>(MOL_MAX_WARPS, ((size_t)ctx->smemOptin - 1024 - tableBytes) / MOL_WARP_BYTES);
         if (ctx->moWarps > 0) warps = std::min(warps, ctx->moWarps);
+        // long launches (from 16 packets of 32 per resident warp: a whole frame) run 2 % faster with 23 warps per CTA than with the 27
+        // that fit -- skin.scene 40.6 -> 39.8 ms alone, 82.6 -> 82.0 ms in the frame, three runs each -- while a rank's share of a
+        // frame is faster with 27 (1/2: 21.7 vs 22.1 ms, 1/8: 7.07 vs 7.34 ms; tools/mo_shard_ab.py with SKC_MO_WARPS)
+        else if (warps > 23 && (n + 31) / 32 >= 16ull * (uint64_t)ctx->smCount * (uint64_t)warps) warps = 23;
         if (warps < 4) return skc_fail(ctx, "skc_mo: the compact profile table (%zu B) leaves no room for the traversal state in shared memory", tableBytes);
         const size_t smem = tableBytes + (size_t)warps * MOL_WARP_BYTES;
         // packets per resident warp decide the packet size (see the kernel): 32 hits from 8 packets per warp up, else 16
