@@ -3,8 +3,9 @@
 //
 //   texels      ReadImagePFM (core/imageio.cpp:315-395: rows in file order, no flip) times L.ToRGBSpectrum(); without a map one
 //               texel = L.ToRGBSpectrum()
-//   pyramid     MIPMap<RGBSpectrum> (core/mipmap.h:111-196) for power-of-two maps: each level the .25f-weighted sum of four
-//               texels of the finer one; other resolutions would be Lanczos-resampled first and are refused
+//   pyramid     MIPMap<RGBSpectrum> (core/mipmap.h:111-196): each level the .25f-weighted sum of four texels of the finer one;
+//               images that are not a power of two in size are Lanczos-zoomed to the next one first (textures; refused for the
+//               environment map, whose distribution keeps the file's size)
 //   img         Lookup(u / w, v / h, 1 / max(w, h)).y() * sinf(M_PI * (v + .5f) / h): the trilinear lookup of mipmap.h:239-271
 //   sampling    Distribution2D / Distribution1D (core/montecarlo.h:55-77, montecarlo.cpp:358-370): step-function cdfs,
 //               fp32 running sums in index order
@@ -21,6 +22,7 @@ namespace {
 
 inline int WrapIndex(int a, int b) { int n = a / b; a -= n * b; if (a < 0) a += b; return a; }      // Mod (core/pbrt.h)
 inline int FloorToInt(float v) { return (int)floorf(v); }
+const float kPiF = 3.14159265358979323846f;          // M_PI is a float literal in the reference (core/pbrt.h:193-196)
 
 struct Rgb { float r, g, b; };
 inline Rgb operator+(Rgb a, Rgb b) { return {a.r + b.r, a.g + b.g, a.b + b.b}; }
@@ -33,7 +35,60 @@ struct Pyramid {
         const Level &l = levels[level];
         return l.px[(size_t)WrapIndex(t, l.h) * l.w + WrapIndex(s, l.w)];
     }
-    void Build(int w, int h, const std::vector<Rgb> &img) {
+    // Lanczos (core/texture.cpp:266-274) and MIPMap::resampleWeights (core/mipmap.h:67-87): four weights per texel of the finer grid
+    static float LanczosWindow(float x, float tau = 2.f) {
+        x = fabsf(x);
+        if (x < 1e-5) return 1;
+        if (x > 1.) return 0;
+        x *= kPiF;
+        const float s = sinf(x * tau) / (x * tau);
+        const float lanczos = sinf(x) / x;
+        return s * lanczos;
+    }
+    struct Tap { int first; float w[4]; };
+    static std::vector<Tap> ResampleTaps(unsigned oldres, unsigned newres) {
+        std::vector<Tap> taps(newres);
+        const float filterwidth = 2.f;
+        for (unsigned i = 0; i < newres; ++i) {
+            const float center = (i + .5f) * oldres / newres;
+            taps[i].first = FloorToInt((center - filterwidth) + 0.5f);
+            for (int j = 0; j < 4; ++j) {
+                const float pos = taps[i].first + j + .5f;
+                taps[i].w[j] = LanczosWindow((pos - center) / filterwidth);
+            }
+            const float invSum = 1.f / (taps[i].w[0] + taps[i].w[1] + taps[i].w[2] + taps[i].w[3]);
+            for (int j = 0; j < 4; ++j) taps[i].w[j] *= invSum;
+        }
+        return taps;
+    }
+    // An image whose size is not a power of two is first zoomed to the next one, rows then columns, with TEXTURE_REPEAT
+    // (core/mipmap.h:119-170); only the second pass clamps at 0
+    static void ZoomToPow2(int *w, int *h, std::vector<Rgb> *img) {
+        auto pow2 = [](unsigned v) { unsigned p = 1; while (p < v) p <<= 1; return p; };
+        const unsigned sres = (unsigned)*w, tres = (unsigned)*h, sP = pow2(sres), tP = pow2(tres);
+        if (sP == sres && tP == tres) return;
+        std::vector<Rgb> zoomed((size_t)sP * tP, Rgb{0.f, 0.f, 0.f});
+        const std::vector<Tap> sTaps = ResampleTaps(sres, sP);
+        for (unsigned t = 0; t < tres; ++t)
+            for (unsigned s = 0; s < sP; ++s) {
+                Rgb acc{0.f, 0.f, 0.f};
+                for (int j = 0; j < 4; ++j) acc = acc + sTaps[s].w[j] * (*img)[(size_t)t * sres + WrapIndex(sTaps[s].first + j, (int)sres)];
+                zoomed[(size_t)t * sP + s] = acc;
+            }
+        const std::vector<Tap> tTaps = ResampleTaps(tres, tP);
+        std::vector<Rgb> column(tP);
+        for (unsigned s = 0; s < sP; ++s) {
+            for (unsigned t = 0; t < tP; ++t) {
+                Rgb acc{0.f, 0.f, 0.f};
+                for (int j = 0; j < 4; ++j) acc = acc + tTaps[t].w[j] * zoomed[(size_t)WrapIndex(tTaps[t].first + j, (int)tres) * sP + s];
+                column[t] = acc;
+            }
+            for (unsigned t = 0; t < tP; ++t) zoomed[(size_t)t * sP + s] = Rgb{std::max(column[t].r, 0.f), std::max(column[t].g, 0.f), std::max(column[t].b, 0.f)};
+        }
+        img->swap(zoomed); *w = (int)sP; *h = (int)tP;
+    }
+    void Build(int w, int h, std::vector<Rgb> img) {
+        ZoomToPow2(&w, &h, &img);
         const float invLog2 = 1.f / logf(2.f);
         const int n = 1 + FloorToInt(logf(float(std::max(w, h))) * invLog2);          // 1 + Log2Int(float(max(sres, tres)))
         levels.resize(n);
@@ -105,18 +160,83 @@ bool ReadPfm(const std::string &path, int *w, int *h, std::vector<Rgb> *out, std
     return true;
 }
 
+// ReadImageTGA (core/imageio.cpp:214-256 over core/targa.c) for true-colour (24 / 32 bit, types 2 and 10) and grey (8 bit, types 3
+// and 11) files, raw or run-length encoded.  The reference normalises the picture to left-to-right / top-to-bottom and then copies
+// its rows from the LAST to the first: texel row 0 is the bottom of the picture.  Colour-mapped files are refused.
+bool ReadTga(const std::string &path, int *w, int *h, std::vector<Rgb> *out, std::string *err) {
+    FILE *fp = fopen(path.c_str(), "rb");
+    if (!fp) { *err = "Unable to read from TGA file \"" + path + "\""; return false; }
+    std::vector<unsigned char> file;
+    { unsigned char buf[65536]; size_t n; while ((n = fread(buf, 1, sizeof buf, fp)) > 0) file.insert(file.end(), buf, buf + n); }
+    fclose(fp);
+    auto fail = [&](const char *why) { *err = "Unable to read from TGA file \"" + path + "\" (" + why + ")"; return false; };
+    if (file.size() < 18) return fail("short header");
+    const int idLen = file[0], cmapType = file[1], type = file[2], cmapLen = file[5] | (file[6] << 8), cmapDepth = file[7];
+    const int width = file[12] | (file[13] << 8), height = file[14] | (file[15] << 8), depth = file[16], desc = file[17];
+    const bool rle = type == 10 || type == 11, grey = type == 3 || type == 11;
+    if (type == 1 || type == 9) return fail("colour-mapped files are not supported on the device path");
+    if (!(type == 2 || type == 10 || grey)) return fail("unknown image type");
+    if (width <= 0 || height <= 0) return fail("empty image");
+    if (!(grey ? depth == 8 : (depth == 24 || depth == 32))) return fail("unsupported pixel depth");
+    const size_t bpp = (size_t)depth / 8, nPix = (size_t)width * height;
+    size_t at = 18 + (size_t)idLen + (cmapType ? (size_t)cmapLen * ((cmapDepth + 7) / 8) : 0);
+    std::vector<unsigned char> px(nPix * bpp);
+    if (!rle) {
+        if (file.size() < at + px.size()) return fail("short image data");
+        memcpy(px.data(), file.data() + at, px.size());
+    } else {
+        size_t done = 0;
+        while (done < nPix) {
+            if (at >= file.size()) return fail("short run-length data");
+            const int head = file[at++], count = (head & 0x7f) + 1;
+            if (done + count > nPix) return fail("run-length packet past the end of the image");
+            if (head & 0x80) {
+                if (at + bpp > file.size()) return fail("short run-length data");
+                for (int k = 0; k < count; ++k) memcpy(&px[(done + k) * bpp], &file[at], bpp);
+                at += bpp;
+            } else {
+                if (at + bpp * count > file.size()) return fail("short run-length data");
+                memcpy(&px[done * bpp], &file[at], bpp * count);
+                at += bpp * count;
+            }
+            done += count;
+        }
+    }
+    const bool topToBottom = (desc & 0x20) != 0, rightToLeft = (desc & 0x10) != 0;
+    out->resize(nPix);
+    for (int row = 0; row < height; ++row) {                  // texel row `row` = picture row height-1-row counted from the top
+        const int fromTop = height - 1 - row, fileRow = topToBottom ? fromTop : height - 1 - fromTop;
+        for (int x = 0; x < width; ++x) {
+            const unsigned char *src = &px[((size_t)fileRow * width + (rightToLeft ? width - 1 - x : x)) * bpp];
+            (*out)[(size_t)row * width + x] = grey ? Rgb{src[0] / 255.f, src[0] / 255.f, src[0] / 255.f} : Rgb{src[2] / 255.f, src[1] / 255.f, src[0] / 255.f};
+        }
+    }
+    *w = width; *h = height;
+    return true;
+}
+
+// ReadImage (core/imageio.cpp:54-75): the file type is the name's last four characters
+bool ReadImageFile(const std::string &path, int *w, int *h, std::vector<Rgb> *out, std::string *err) {
+    const std::string suffix = path.size() >= 5 ? path.substr(path.size() - 4) : std::string();
+    if (suffix == ".tga" || suffix == ".TGA") return ReadTga(path, w, h, out, err);
+    if (suffix == ".pfm" || suffix == ".PFM") return ReadPfm(path, w, h, out, err);
+    *err = "Can't determine image file type from suffix of filename \"" + path + "\" (.pfm and .tga are read; no OpenEXR on this path)";
+    return false;
+}
+
 }  // namespace
 
 bool LoadAlphaTexture(const std::string &file, float shift, float scale, float gamma, AlphaTexture *out, std::string *err) {
     int w = 0, h = 0;
     std::vector<Rgb> px;
-    if (!ReadPfm(file, &w, &h, &px, err)) return false;
-    if ((w & (w - 1)) || (h & (h - 1))) { *err = "texture \"" + file + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)"; return false; }
-    out->present = true; out->w = w; out->h = h; out->texels.resize(px.size());
-    for (size_t i = 0; i < px.size(); ++i) {
-        const float y = 0.212671f * px[i].r + 0.715160f * px[i].g + 0.072169f * px[i].b;       // RGBSpectrum::y()
-        out->texels[i] = scale * (powf(y, gamma) + shift);                                  // convertIn (textures/imagemap.h:94-97)
+    if (!ReadImageFile(file, &w, &h, &px, err)) return false;
+    for (Rgb &c : px) {
+        const float y = 0.212671f * c.r + 0.715160f * c.g + 0.072169f * c.b;                // RGBSpectrum::y()
+        c.r = c.g = c.b = scale * (powf(y, gamma) + shift);                                 // convertIn (textures/imagemap.h:94-97)
     }
+    Pyramid::ZoomToPow2(&w, &h, &px);                 // MIPMap<float>'s level 0 (three equal channels resample like one)
+    out->present = true; out->w = w; out->h = h; out->texels.resize(px.size());
+    for (size_t i = 0; i < px.size(); ++i) out->texels[i] = px[i].r;
     return true;
 }
 
@@ -125,8 +245,7 @@ bool LoadAlphaTexture(const std::string &file, float shift, float scale, float g
 bool LoadAlbedoTexture(const std::string &file, float shift, float scale, float gamma, AlbedoTexture *out, std::string *err) {
     int w = 0, h = 0;
     std::vector<Rgb> px;
-    if (!ReadPfm(file, &w, &h, &px, err)) return false;
-    if ((w & (w - 1)) || (h & (h - 1))) { *err = "texture \"" + file + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)"; return false; }
+    if (!ReadImageFile(file, &w, &h, &px, err)) return false;
     for (Rgb &c : px) { c.r = scale * (powf(c.r, gamma) + shift); c.g = scale * (powf(c.g, gamma) + shift); c.b = scale * (powf(c.b, gamma) + shift); }
     Pyramid mip;
     mip.Build(w, h, px);
@@ -186,9 +305,9 @@ bool MakeInfiniteLight(const Transform &l2w, const float Lrgb[3], const float *s
     int w = 1, h = 1;
     std::vector<Rgb> texels;
     if (!mapname.empty()) {
-        if (!ReadPfm(mapname, &w, &h, &texels, err)) return false;
+        if (!ReadImageFile(mapname, &w, &h, &texels, err)) return false;
         if ((w & (w - 1)) || (h & (h - 1))) {
-            *err = "LightSource \"infinite\": environment map \"" + mapname + "\" is not a power of two in both directions (the resampling MIPMap would apply is not built)";
+            *err = "LightSource \"infinite\": environment map \"" + mapname + "\" is not a power of two in both directions (its sampling distribution keeps the file's size while the MIPMap is resampled: the device holds one size)";
             return false;
         }
         for (Rgb &t : texels) { t.r *= rgbL[0]; t.g *= rgbL[1]; t.b *= rgbL[2]; }

@@ -150,6 +150,18 @@ def lights_golden(name="skin_lights"):
     print(path, os.path.getsize(path) // 1024, "KiB", {k: meta[k] for k in ("surface_points", "camera_samples", "lights")})
 
 
+def tga_golden(name="tex_tga"):
+    """scenes/skin_tga.scene: the MIPMap pyramids the reference builds from the two TGA textures (ReadImageTGA, convertIn, the
+    Lanczos zoom of a 48x40 image to 64x64, the box-filtered levels) -- what the host mirror has to hand to the device."""
+    scene = os.path.join(ROOT, "scenes", "skin_tga.scene")
+    with tempfile.TemporaryDirectory() as d:
+        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        arrays = dict(albedo_tex=np.fromfile(os.path.join(d, "albedo_tex.bin"), np.float32), bump_tex=np.fromfile(os.path.join(d, "bump_tex.bin"), np.float32))
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(path, os.path.getsize(path) // 1024, "KiB")
+
+
 def tissue_golden(name="tissue"):
     """BASELINE.json configs[0] stand-in (scenes/tissue.scene = scenes/tissue.pbrt: LayeredSkin slab at the material's
     defaults incl. the transmission lobe, mesh without normals / uvs): image, octree root and bounds, and every 37th
@@ -332,4 +344,4 @@ if __name__ == "__main__":
     if not os.path.exists(DRIVER):
         sys.exit("oracle/_ref/ref_driver missing: run oracle/build_ref.sh (needs /root/reference)")
     for w in what:
-        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex", "skin_bump", "skin_poisson") else scene_golden(w)
+        mpc_golden() if w == "mpc_kat" else mpc512_golden() if w == "mpc_kat512" else mpc_api_golden() if w == "mpc_api" else tga_golden(w) if w == "tex_tga" else skin_full_golden(w) if w == "skin_full" else frame_golden(w) if w == "skin_ld4" else tissue_golden(w) if w == "tissue" else lights_golden(w) if w in ("skin_lights", "skin_albedo", "skin_env", "skin_alpha", "skin_tex", "skin_bump", "skin_poisson") else scene_golden(w)
