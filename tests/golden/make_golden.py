@@ -153,10 +153,13 @@ def lights_golden(name="skin_lights"):
 def tga_golden(name="tex_tga"):
     """scenes/skin_tga.scene: the MIPMap pyramids the reference builds from the two TGA textures (ReadImageTGA, convertIn, the
     Lanczos zoom of a 48x40 image to 64x64, the box-filtered levels) -- what the host mirror has to hand to the device."""
-    scene = os.path.join(ROOT, "scenes", "skin_tga.scene")
-    with tempfile.TemporaryDirectory() as d:
-        subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-        arrays = dict(albedo_tex=np.fromfile(os.path.join(d, "albedo_tex.bin"), np.float32), bump_tex=np.fromfile(os.path.join(d, "bump_tex.bin"), np.float32))
+    arrays = {}
+    for suffix, scene_name in (("", "skin_tga.scene"), ("_b", "skin_tga_b.scene")):      # _b: the other TGA encodings (tools/make_tga_textures.py)
+        scene = os.path.join(ROOT, "scenes", scene_name)
+        with tempfile.TemporaryDirectory() as d:
+            subprocess.run([DRIVER, "scene", scene, d, "--ncores", "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            arrays["albedo_tex" + suffix] = np.fromfile(os.path.join(d, "albedo_tex.bin"), np.float32)
+            arrays["bump_tex" + suffix] = np.fromfile(os.path.join(d, "bump_tex.bin"), np.float32)
     path = os.path.join(OUT, name + ".npz")
     np.savez_compressed(path, **arrays)
     print(path, os.path.getsize(path) // 1024, "KiB")

@@ -25,9 +25,12 @@ def _split(flat, channels, has_lut):
     return w, h, np.concatenate(levels)
 
 
-@pytest.mark.parametrize("ext", ["scene", "pbrt"])
+@pytest.mark.parametrize("ext", ["scene", "pbrt", "b"])
 def test_tga_textures_zoomed_pyramids_bit_exact(pkg, ext):
+    """"b": the same pictures (the grey one with an extra flat patch) in the other encodings -- 32-bit raw stored right to left with a
+    bottom-left origin, grey run-length encoded with a top-left origin (scenes/skin_tga_b.scene)."""
     z = np.load(os.path.join(ROOT, "tests", "golden", "tex_tga.npz"))
+    suffix = "_b" if ext == "b" else ""
     if ext == "pbrt":
         import sys
         sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -35,14 +38,14 @@ def test_tga_textures_zoomed_pyramids_bit_exact(pkg, ext):
         dst = os.path.join(ROOT, "scenes", "geometry", "head.pbrt")
         if not os.path.exists(dst):
             mesh_bin_to_pbrt.convert(os.path.join(ROOT, "scenes", "head.mesh.bin"), dst)
-    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tga." + ext))
+    hs = pkg.HostScene(os.path.join(ROOT, "scenes", "skin_tga_b.scene" if ext == "b" else "skin_tga." + ext))
     try:
         a = hs.albedo_texture(); b = hs.bump_texture()
-        w, h, rgb = _split(z["albedo_tex"], 3, True)
+        w, h, rgb = _split(z["albedo_tex" + suffix], 3, True)
         assert list(a["w"]) == w == [64, 32, 16, 8, 4, 2, 1] and list(a["h"]) == h          # 48 x 40 zoomed to 64 x 64
         same = a["rgb"].view(np.uint32) == rgb.view(np.uint32)
         assert same.all(), "albedo pyramid: %d of %d floats differ, first at %d" % ((~same).sum(), same.size, int(np.argmin(same)))
-        w, h, disp = _split(z["bump_tex"], 1, False)
+        w, h, disp = _split(z["bump_tex" + suffix], 1, False)
         assert list(b["w"]) == w == [64, 32, 16, 8, 4, 2, 1] and list(b["h"]) == h
         same = b["texels"].view(np.uint32) == disp.view(np.uint32)
         assert same.all(), "bump pyramid: %d of %d floats differ, first at %d" % ((~same).sum(), same.size, int(np.argmin(same)))

@@ -53,7 +53,17 @@ def main():
     with open(os.path.join(ROOT, "scenes", "bump48x40.tga"), "wb") as f:
         f.write(header(3, 8, 0x00))
         f.write(grey.tobytes())
-    print("wrote scenes/albedo48x40.tga, scenes/bump48x40.tga")
+    # second pair, the remaining encodings: true colour with an alpha byte (32 bit), raw, bottom-left origin, stored right to left;
+    # grey, run-length encoded (type 11), top-left origin
+    bgra = np.concatenate([rgb, np.full((H, W, 1), 255, np.uint8)], axis=-1)
+    with open(os.path.join(ROOT, "scenes", "albedo48x40_b.tga"), "wb") as f:
+        f.write(header(2, 32, 0x18))                   # 8 alpha bits + right-to-left
+        f.write(bgra[:, ::-1].tobytes())
+    grey2 = grey.copy(); grey2[12:20, 4:40] = 200
+    with open(os.path.join(ROOT, "scenes", "bump48x40_b.tga"), "wb") as f:
+        f.write(header(11, 8, 0x20))
+        f.write(rle_rows(grey2[:, :, None]))
+    print("wrote scenes/albedo48x40.tga, scenes/bump48x40.tga, scenes/albedo48x40_b.tga, scenes/bump48x40_b.tga")
 
 
 if __name__ == "__main__":
