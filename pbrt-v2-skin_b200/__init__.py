@@ -15,5 +15,5 @@ interfaces (host/).  There is no CPU fallback: every entry point raises if the l
 GPU is missing.
 """
 from .skc import SkinDevice, SkinComm, SkcError, load_library, lib_path, DT_HIT, DT_RAY, DT_SURFACE_POINT, DT_IRR_POINT, DT_BVH_NODE, DT_LIGHT  # noqa: F401
-from .host_api import HostScene, load_host_library, skin_spectra, pbrt_render  # noqa: F401
+from .host_api import HostScene, load_host_library, skin_spectra, pbrt_render, read_points_file, write_points_file  # noqa: F401
 from .multigpu import shard_range, exchange_unique_id  # noqa: F401

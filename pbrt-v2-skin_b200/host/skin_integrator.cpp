@@ -158,6 +158,20 @@ const float *skh_alpha_texels(const skh_scene *s) { return alphaOf(s).texels.dat
 // "color albedo" of the material: rgb, and whether it was given at all (Spectrum(1) otherwise)
 int skh_skin_albedo(const skh_scene *s, float *rgb3) { memcpy(rgb3, s->sd.skin.albedo, 12); return s->sd.skin.hasAlbedo ? 1 : 0; }
 // Tessellation (Preprocess' point source).  Returns the count; pointer valid until the next call.
+// The points file in both its forms (skin_scene.h ReadPointsFile / WritePointsFile); out may be NULL to ask for the count only
+int skh_points_write(const char *path, const void *pts, uint64_t n, int versioned, char *errbuf, int errlen) {
+    std::string err;
+    if (WritePointsFile(path, (const skc_surface_point *)pts, n, versioned != 0, &err)) return 0;
+    if (errbuf && errlen > 0) snprintf(errbuf, errlen, "%s", err.c_str());
+    return 1;
+}
+int skh_points_read(const char *path, void *out, uint64_t cap, uint64_t *n, char *errbuf, int errlen) {
+    std::vector<skc_surface_point> pts; std::string err;
+    if (!ReadPointsFile(path, &pts, &err)) { if (errbuf && errlen > 0) snprintf(errbuf, errlen, "%s", err.c_str()); return 1; }
+    *n = pts.size();
+    if (out && cap >= pts.size() && !pts.empty()) memcpy(out, pts.data(), pts.size() * sizeof(skc_surface_point));
+    return 0;
+}
 uint64_t skh_tessellate(skh_scene *s, float minDist, int incenter, const void **pts) {
     s->points.clear();
     for (const TriangleMesh &m : s->sd.meshes) m.TessellateSurfacePoints(minDist, m.materialId, s->points, incenter != 0);

@@ -606,6 +606,7 @@ bool Front::statement(const std::string &id) {
             sd->rendererMinDist = ps.FindOneFloat("minsampledistance", .25f);
             sd->rendererFilename = ps.FindOneString("filename", "");
             if (!sd->rendererFilename.empty()) sd->rendererFilename = resolve(sd->rendererFilename);
+            sd->rendererVersionedFile = ps.FindOneBool("versioned", false);      // not in the reference: the tagged points file (skin_scene.h)
             if (options.quickRender) { sd->rendererMinDist *= 4.f; sd->poissonMaxFails = std::max(10, 2000 / 10); }
             haveIntegrator = true;                            // this renderer never calls the surface integrator
             reportUnused(ps, "Renderer");

@@ -91,6 +91,57 @@ int UploadEnvMap(skc_ctx *ctx, const EnvMap &e) {
     return skc_upload_envmap(ctx, (uint32_t)e.w, (uint32_t)e.h, e.rgb.data(), e.condFunc.data(), e.condCdf.data(), e.condInt.data(), e.margFunc.data(), e.margCdf.data(), e.margInt);
 }
 
+namespace {
+struct PointsFileHeader {            // 32 bytes, little-endian fields as written by the machine that made the file
+    char magic[8];                   // "SKINPTS\1"
+    uint32_t version;                // 1
+    uint32_t recordBytes;            // sizeof(skc_surface_point) = 44
+    uint64_t count;
+    uint32_t byteOrder;              // 0x01020304 as the writer's uint32
+    uint32_t reserved;
+};
+const char kPointsMagic[8] = {'S', 'K', 'I', 'N', 'P', 'T', 'S', 1};
+}  // namespace
+
+bool ReadPointsFile(const std::string &path, std::vector<skc_surface_point> *pts, std::string *err) {
+    pts->clear();
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) { *err = "Unable to open file \"" + path + "\""; return false; }
+    fseek(f, 0, SEEK_END); const long size = ftell(f); fseek(f, 0, SEEK_SET);
+    PointsFileHeader h;
+    bool tagged = size >= (long)sizeof h && fread(&h, sizeof h, 1, f) == 1 && !memcmp(h.magic, kPointsMagic, 8);
+    bool ok = true;
+    if (tagged) {
+        if (h.byteOrder != 0x01020304u) { *err = "points file \"" + path + "\" was written with another byte order"; ok = false; }
+        else if (h.version != 1 || h.recordBytes != sizeof(skc_surface_point)) { *err = "points file \"" + path + "\": unknown version or record size"; ok = false; }
+        else if ((uint64_t)(size - (long)sizeof h) != h.count * sizeof(skc_surface_point)) { *err = "points file \"" + path + "\" is truncated or has trailing bytes"; ok = false; }
+        else { pts->resize(h.count); ok = !h.count || fread(pts->data(), sizeof(skc_surface_point), h.count, f) == h.count; if (!ok) *err = "short read from \"" + path + "\""; }
+    } else {
+        fseek(f, 0, SEEK_SET);
+        pts->resize((size_t)size / sizeof(skc_surface_point));
+        ok = pts->empty() || fread(pts->data(), sizeof(skc_surface_point), pts->size(), f) == pts->size();
+        if (!ok) *err = "short read from \"" + path + "\"";
+    }
+    fclose(f);
+    if (!ok) pts->clear();
+    return ok;
+}
+
+bool WritePointsFile(const std::string &path, const skc_surface_point *pts, uint64_t n, bool versioned, std::string *err) {
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) { *err = "Unable to open output file \"" + path + "\""; return false; }
+    bool ok = true;
+    if (versioned) {
+        PointsFileHeader h; memset(&h, 0, sizeof h);
+        memcpy(h.magic, kPointsMagic, 8); h.version = 1; h.recordBytes = (uint32_t)sizeof(skc_surface_point); h.count = n; h.byteOrder = 0x01020304u;
+        ok = fwrite(&h, sizeof h, 1, f) == 1;
+    }
+    ok = ok && (!n || fwrite(pts, sizeof(skc_surface_point), n, f) == n);
+    fclose(f);
+    if (!ok) *err = "short write to \"" + path + "\"";
+    return ok;
+}
+
 static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 // One rank's share of SamplerRenderer::Render.  comm == nullptr: the whole frame on one GPU.  With a communicator:
@@ -118,15 +169,9 @@ bool RenderSceneRank(skc_ctx *ctx, skc_comm *comm, const SceneDesc &sd, const Bu
     uint64_t nPts = 0;
     {
         std::vector<skc_surface_point> filePts;
-        if (!sd.pointsFile.empty()) {                                        // :176-181, ReadBinaryFile (core/floatfile.h:45-63)
-            FILE *f = fopen(sd.pointsFile.c_str(), "rb");
-            if (!f) fprintf(stderr, "Error: Unable to open file \"%s\"\n", sd.pointsFile.c_str());
-            else {
-                fseek(f, 0, SEEK_END); long size = ftell(f); fseek(f, 0, SEEK_SET);
-                filePts.resize((size_t)size / sizeof(skc_surface_point));
-                if (!filePts.empty() && fread(filePts.data(), sizeof(skc_surface_point), filePts.size(), f) != filePts.size()) filePts.clear();
-                fclose(f);
-            }
+        if (!sd.pointsFile.empty()) {                                        // :176-181, ReadBinaryFile (core/floatfile.h:45-63); a file that cannot be used
+            std::string why;                                                 // leaves pts empty and the points are generated, as in the reference
+            if (!ReadPointsFile(sd.pointsFile, &filePts, &why)) fprintf(stderr, "Error: %s\n", why.c_str());
         }
         bool fromFile = !filePts.empty();
         if (fromFile) {
@@ -239,12 +284,7 @@ bool TessellateSurfacePointsToFile(skc_ctx *ctx, const SceneDesc &sd, uint64_t *
         fclose(f);
         return true;
     }
-    FILE *f = fopen(sd.rendererFilename.c_str(), "wb");
-    if (!f) { *err = "Unable to open output file \"" + sd.rendererFilename + "\""; return false; }
-    bool ok = fwrite(pts.data(), sizeof(skc_surface_point), pts.size(), f) == pts.size();
-    fclose(f);
-    if (!ok) *err = "short write to \"" + sd.rendererFilename + "\"";
-    return ok;
+    return WritePointsFile(sd.rendererFilename, pts.data(), pts.size(), sd.rendererVersionedFile, err);
 }
 
 // WriteImageTGA (core/imageio.cpp:185-215): 24-bit BGR, gamma 2.2, top row first

@@ -152,6 +152,7 @@ struct SceneDesc {
     std::string rendererName = "sampler";
     float rendererMinDist = .25f;
     std::string rendererFilename;
+    bool rendererVersionedFile = false;   // "bool versioned": write the tagged points file (WritePointsFile) instead of the reference's raw dump
     std::vector<SphereLight> lights;
     EnvMap env;                       // of the scene's infinite light (at most one)
     SkinParams skin;
@@ -213,6 +214,14 @@ int BuildSkinMaterial(skc_ctx *ctx, const SkinParams &skin, skc_comm *comm = nul
 int InstallAlbedo(skc_ctx *ctx, const SkinParams &skin, float mix);
 int UploadEnvMap(skc_ctx *ctx, const EnvMap &env);
 int UploadAlpha(skc_ctx *ctx, const AlphaTexture &a);
+// The `pointsfile` of MultipoleSubsurfaceIntegrator / Renderer "tessellatesurfacepoints" (multipolesubsurface.cpp:176-181,
+// surfacepoints.cpp:335-347).  The reference's file is a raw dump of SurfacePoint[44 B] in host byte order with no
+// header; it stays the default in both directions.  The tagged variant adds 32 bytes in front -- "SKINPTS\1", version, record size,
+// count, a byte-order mark -- so that a reader can tell a points file from anything else, a truncated one from a whole one, and a
+// foreign byte order from its own.  ReadPointsFile takes either (the tag decides); a raw file's trailing partial record is ignored
+// as ReadBinaryFile does (core/floatfile.h:45-63).
+bool ReadPointsFile(const std::string &path, std::vector<skc_surface_point> *pts, std::string *err);
+bool WritePointsFile(const std::string &path, const skc_surface_point *pts, uint64_t n, bool versioned, std::string *err);
 int UploadAlbedoTexture(skc_ctx *ctx, const AlbedoTexture &a);
 int UploadBumpTexture(skc_ctx *ctx, const AlbedoTexture &a);     // skc_upload_bump_texture (or its removal)
    // skc_upload_albedo_texture (or its removal)    // skc_upload_alpha (or its removal)     // skc_upload_envmap (or its removal when the scene has no infinite light)   // comm: the wavelengths dealt over its ranks

@@ -35,6 +35,8 @@ def load_host_library():
         getattr(lib, f).restype = vp; getattr(lib, f).argtypes = [vp]
     lib.skh_mesh_o2w.restype = None; lib.skh_mesh_o2w.argtypes = [vp, vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.skh_integrator_params.restype = None; lib.skh_integrator_params.argtypes = [vp, vp]
+    lib.skh_points_write.restype = C.c_int; lib.skh_points_write.argtypes = [C.c_char_p, vp, C.c_uint64, C.c_int, C.c_char_p, C.c_int]
+    lib.skh_points_read.restype = C.c_int; lib.skh_points_read.argtypes = [C.c_char_p, vp, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_int]
     lib.skh_poisson_params.restype = None; lib.skh_poisson_params.argtypes = [vp, vp, vp]
     lib.skh_skin_params.restype = None; lib.skh_skin_params.argtypes = [vp, vp]
     lib.skh_albedo_tex_info.restype = C.c_int; lib.skh_albedo_tex_info.argtypes = [vp, vp, vp, vp]
@@ -79,6 +81,28 @@ def skin_spectra(f_mel=0.15, f_eu=1.0, f_blood=0.002, f_ohg=0.3, nmperunit=100e6
     lib.skh_skin_spectra(p.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p))
     c = v[:120].reshape(2, 2, 30)
     return {"flat": v, "mua": c[:, 0], "musp": c[:, 1], "eta": v[120:122], "thickness": v[122:124]}
+
+
+def write_points_file(path, points, versioned=False):
+    """The integrator's `pointsfile`: the reference's raw SurfacePoint[44 B] dump, or with the 32-byte tag in front (host/skin_scene.h)."""
+    from .skc import DT_SURFACE_POINT
+    pts = np.ascontiguousarray(points if points.dtype == DT_SURFACE_POINT else points.view(DT_SURFACE_POINT))
+    err = C.create_string_buffer(512)
+    if load_host_library().skh_points_write(os.fsencode(path), pts.ctypes.data_as(C.c_void_p), len(pts), int(versioned), err, 512):
+        raise RuntimeError(err.value.decode())
+
+
+def read_points_file(path):
+    """Either form of the points file (the tag decides); raises on a tagged file that is truncated, foreign or of another version."""
+    from .skc import DT_SURFACE_POINT
+    lib = load_host_library()
+    err = C.create_string_buffer(512); n = C.c_uint64(0)
+    if lib.skh_points_read(os.fsencode(path), None, 0, C.byref(n), err, 512):
+        raise RuntimeError(err.value.decode())
+    out = np.zeros(n.value, DT_SURFACE_POINT)
+    if n.value and lib.skh_points_read(os.fsencode(path), out.ctypes.data_as(C.c_void_p), n.value, C.byref(n), err, 512):
+        raise RuntimeError(err.value.decode())
+    return out
 
 
 class HostScene:
